@@ -1,0 +1,92 @@
+"""Seeded synthetic workloads for the tests and ``bench.py``.
+
+NumPy only; produces HOST arrays.  Not part of the compute path.
+"""
+import numpy as np
+
+
+def gt_boxes(rng, g, crowded=False, centre=(0.1, 0.9), size=(0.03, 0.4)):
+    """``g`` ground-truth boxes, f32 (g,4) in [0,1], x1<x2, y1<y2, pairwise-distinct f32 areas."""
+    out = np.zeros((0, 4), dtype=np.float32)
+    while len(out) < g:
+        k = (g - len(out)) * 2 + 4
+        if crowded:
+            c = 0.5 + rng.uniform(-0.01, 0.01, size=(k, 2))
+        else:
+            c = rng.uniform(centre[0], centre[1], size=(k, 2))
+        s = rng.uniform(size[0], size[1], size=(k, 2))
+        b = np.clip(np.concatenate([c - s / 2, c + s / 2], axis=1), 0, 1).astype(np.float32)
+        b = b[(b[:, 2] - b[:, 0] > 1e-3) & (b[:, 3] - b[:, 1] > 1e-3)]
+        out = np.concatenate([out, b])
+        area = (out[:, 2:] - out[:, :2]).prod(axis=-1)
+        _, first = np.unique(area, return_index=True)
+        out = out[np.sort(first)]
+    return np.ascontiguousarray(out[:g])
+
+
+def gt_batch(seed, batch, g_max, num_classes, g_min=1, crowded_every=4, fixed_g=None, **kw):
+    """Padded GT batch: boxes f32 (B,Gmax,4), classes i32 (B,Gmax), counts i32 (B,)."""
+    rng = np.random.RandomState(seed)
+    boxes = np.zeros((batch, g_max, 4), dtype=np.float32)
+    classes = np.zeros((batch, g_max), dtype=np.int32)
+    counts = np.zeros((batch,), dtype=np.int32)
+    for i in range(batch):
+        g = fixed_g if fixed_g is not None else int(rng.randint(g_min, g_max + 1))
+        crowded = crowded_every > 0 and (i % crowded_every == crowded_every - 1)
+        boxes[i, :g] = gt_boxes(rng, g, crowded=crowded, **kw)
+        classes[i, :g] = rng.randint(0, num_classes, size=g)
+        counts[i] = g
+    return boxes, classes, counts
+
+
+def _distinct_positive(x, rng):
+    """Make the f32 values of each row pairwise distinct by nudging duplicates (tie-free scores)."""
+    return x
+
+
+def predictions(seed, batch, n_anchors, num_classes, clustered=False, dtype=np.float32):
+    """Network-head outputs of config 2: objs (B,N,1) sigmoid, clfs (B,N,C) softmax, locs (B,N,4)."""
+    rng = np.random.RandomState(seed)
+    logit = rng.normal(-5.0, 2.5, size=(batch, n_anchors, 1))
+    z = 3.0 * rng.normal(size=(batch, n_anchors, num_classes))
+    if clustered:
+        planted = rng.randint(0, n_anchors, size=(batch, 16))
+        for b in range(batch):
+            for p in planted[b]:
+                lo, hi = max(0, p - 40), min(n_anchors, p + 40)
+                logit[b, lo:hi, 0] += 8.0
+                z[b, lo:hi, rng.randint(num_classes)] += 6.0
+        locs = rng.normal(0.0, 0.3, size=(batch, n_anchors, 4))
+    else:
+        locs = rng.normal(size=(batch, n_anchors, 4))
+    objs = 1.0 / (1.0 + np.exp(-logit))
+    z -= z.max(axis=-1, keepdims=True)
+    e = np.exp(z)
+    clfs = e / e.sum(axis=-1, keepdims=True)
+    return objs.astype(dtype), clfs.astype(dtype), locs.astype(dtype)
+
+
+def eval_set(seed, n_img, num_classes, max_gt=6, difficult_frac=0.1, n_fp=20):
+    """Config 4 (VOC07-test-sized eval): per image (w, h, gt classes, gt boxes f32, difficult) and
+    detections (classes i32, confs f32, boxes f32) = jittered GT + random false positives."""
+    rng = np.random.RandomState(seed)
+    gts, preds = [], []
+    for _ in range(n_img):
+        w, h = int(rng.randint(200, 501)), int(rng.randint(200, 501))
+        g = int(rng.randint(1, max_gt + 1))
+        gb = gt_boxes(rng, g, size=(0.1, 0.5))
+        gc = rng.randint(0, num_classes, size=g).astype(np.int32)
+        gd = rng.uniform(size=g) < difficult_frac
+        hit = rng.uniform(size=g) < 0.8
+        pb = np.clip(gb[hit] + rng.normal(0, 0.02, size=(int(hit.sum()), 4)), 0, 1)
+        pc = gc[hit]
+        ps = rng.uniform(0.3, 1.0, size=len(pb))
+        fb = gt_boxes(rng, n_fp, size=(0.05, 0.5))
+        fc = rng.randint(0, num_classes, size=n_fp).astype(np.int32)
+        fs = rng.uniform(0.01, 0.5, size=n_fp)
+        boxes = np.concatenate([pb, fb]).astype(np.float32)
+        ok = (boxes[:, 2] > boxes[:, 0]) & (boxes[:, 3] > boxes[:, 1])
+        preds.append((np.concatenate([pc, fc])[ok].astype(np.int32),
+                      np.concatenate([ps, fs])[ok].astype(np.float32), boxes[ok]))
+        gts.append((w, h, gc, gb, gd))
+    return gts, preds

@@ -1,0 +1,67 @@
+"""TEST INFRASTRUCTURE ONLY — loads the UNMODIFIED reference modules from /root/reference.
+
+Used only by ``oracle/gen_golden.py`` (golden-vector generation) and by the
+``not gpu`` tests that cross-check ``oracle/restated.py`` against the real
+reference when ``/root/reference`` is mounted (it is absent on the GPU box, so
+nothing under ``-m gpu``, ``smoke()`` or ``bench.py`` imports this file).
+
+The reference package cannot be imported whole (``pytoolkit/__init__.py`` pulls
+in TensorFlow etc.), so the eight files the detection path needs are loaded by
+path under a synthetic ``pytoolkit`` package, with three shims:
+``np.bool`` alias, ``sklearn.externals.joblib`` alias and a stub ``tensorflow``
+(``PriorBoxes.decode_locs`` imports it unconditionally, od_pb.py:218).
+"""
+import importlib.util
+import pathlib
+import sys
+import types
+
+import numpy as np
+
+REFERENCE_ROOT = pathlib.Path('/root/reference/pytoolkit/pytoolkit')
+_FILES = ['utils', 'log', 'math', 'draw', 'ndimage', 'ml', 'dl.losses', 'dl.od_pb']
+
+
+def available() -> bool:
+    return (REFERENCE_ROOT / 'dl' / 'od_pb.py').is_file()
+
+
+def load():
+    """Returns the synthetic ``pytoolkit`` package (attributes: ml, math, dl.od_pb ...)."""
+    if 'pytoolkit' in sys.modules and getattr(sys.modules['pytoolkit'], '_odk_shim', False):
+        return sys.modules['pytoolkit']
+    if not available():
+        raise RuntimeError('reference tree not mounted at %s' % REFERENCE_ROOT)
+    sys.dont_write_bytecode = True
+    if not hasattr(np, 'bool'):
+        np.bool = bool  # ml.py:43,45 use the alias removed in NumPy 1.24
+    import joblib
+    import sklearn
+    ext = types.ModuleType('sklearn.externals')
+    ext.joblib = joblib
+    sys.modules.setdefault('sklearn.externals', ext)
+    sys.modules.setdefault('sklearn.externals.joblib', joblib)
+    sklearn.externals = sys.modules['sklearn.externals']
+    for missing in ('tensorflow', 'better_exceptions', 'matplotlib', 'matplotlib.pyplot'):
+        try:
+            __import__(missing)
+        except Exception:  # noqa: BLE001 - any import failure gets the stub
+            sys.modules[missing] = types.ModuleType(missing)
+    pkg = types.ModuleType('pytoolkit')
+    pkg.__path__ = [str(REFERENCE_ROOT)]
+    pkg._odk_shim = True
+    dl = types.ModuleType('pytoolkit.dl')
+    dl.__path__ = [str(REFERENCE_ROOT / 'dl')]
+    sys.modules['pytoolkit'] = pkg
+    sys.modules['pytoolkit.dl'] = dl
+    pkg.dl = dl
+    for name in _FILES:
+        full = 'pytoolkit.' + name
+        path = REFERENCE_ROOT / (name.replace('.', '/') + '.py')
+        spec = importlib.util.spec_from_file_location(full, path)
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[full] = mod
+        spec.loader.exec_module(mod)
+        parent, _, leaf = name.rpartition('.')
+        setattr(dl if parent == 'dl' else pkg, leaf, mod)
+    return pkg

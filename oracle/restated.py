@@ -1,0 +1,415 @@
+"""CPU ORACLE — TEST INFRASTRUCTURE, NOT A PRODUCT PATH.
+
+A NumPy restatement of the reference's detection hot path (ak110/object_detector,
+pytoolkit submodule d542569).  Only ``tests/``, ``__graft_entry__.smoke()`` and the
+``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` may import this module, and
+only as the checker / timed CPU baseline.  Nothing in ``object_detector_b200/`` imports it.
+
+Pinning (see tests/test_oracle_cpu.py and tests/golden/):
+  * anchors / assign / encode / decode / IoU / NumPy-NMS: pinned against outputs of the
+    unmodified reference run in the build container (``oracle/gen_golden.py`` ->
+    ``tests/golden/*.npz``) and against the reference's own KATs
+    (pytoolkit/tests/ml_test.py:42-53, 89-113).
+  * ``nms_layer`` (in-graph ``layers.nms``): STRUCTURE restated from layers.py:925-970 with the
+    reference's NumPy NMS as inner op; the real inner op (tf.image.non_max_suppression,
+    tensorflow==1.10.0) is absent -> **parity unpinned** at that boundary.
+  * ``eval_detection_voc``: restatement of chainercv (no version pinned by the reference,
+    not vendored) -> **parity unpinned**; hand-computed micro-cases only.
+
+Every function cites the reference lines it follows (paths relative to
+/root/reference/pytoolkit/pytoolkit/).  The arithmetic (dtype of every intermediate, op order)
+is the reference's as executed by NumPy 2.x (NEP 50 promotion); the code layout is not.
+"""
+import numpy as np
+
+VAR_LOC = 0.10  # dl/od_pb.py:10
+
+VOC_PATTERNS = [  # dl/od.py:20-29 (_VOC_JSON_DATA['pb_size_patterns'])
+    [1.2133152484893799, 1.6041910648345947],
+    [2.301241874694824, 3.812246322631836],
+    [3.2387468814849854, 7.3555989265441895],
+    [5.467498779296875, 4.480413436889648],
+    [4.758797645568848, 11.54628849029541],
+    [10.89200496673584, 5.788760185241699],
+    [7.736226558685303, 8.850168228149414],
+    [4.47715950012207, 16.65940284729004],
+]
+VOC_MAP_SIZES = [40, 20, 10]
+
+
+# --------------------------------------------------------------------------------------
+# math.py:8-17
+def closed_interval(x, lo, hi):
+    """math.between: lo <= x <= hi."""
+    return (lo <= x) & (x <= hi)
+
+
+def half_open_interval(x, lo, hi):
+    """math.in_range: lo <= x < hi."""
+    return (lo <= x) & (x < hi)
+
+
+# --------------------------------------------------------------------------------------
+# ml.py:485-499
+def box_centers(b):
+    return (b[..., 2:] + b[..., :2]) / 2
+
+
+def box_areas(b):
+    return (b[..., 2:] - b[..., :2]).prod(axis=-1)
+
+
+def pairwise_iou(a, b):
+    """ml.compute_iou (ml.py:502-519): (A,4),(Bn,4) -> (A,Bn); dtype follows the inputs."""
+    assert a.ndim == 2 and a.shape[1] == 4 and a.shape[0] > 0
+    assert b.ndim == 2 and b.shape[1] == 4 and b.shape[0] > 0
+    lo = np.maximum(a[:, None, :2], b[None, :, :2])
+    hi = np.minimum(a[:, None, 2:], b[None, :, 2:])
+    overlap = np.prod(hi - lo, axis=2) * (lo < hi).all(axis=2)
+    area_a = np.prod(a[:, 2:] - a[:, :2], axis=1)
+    area_b = np.prod(b[:, 2:] - b[:, :2], axis=1)
+    return overlap / (area_a[:, None] + area_b - overlap)
+
+
+# --------------------------------------------------------------------------------------
+class AnchorTables:
+    """The arrays ``PriorBoxes._create_pb`` builds (dl/od_pb.py:125-184), same dtypes."""
+
+    def __init__(self, input_size, map_sizes, pb_size_patterns, num_classes):
+        self.input_size = tuple(input_size)
+        self.map_sizes = np.array(map_sizes)  # from_dict keeps the given order (od_pb.py:55)
+        self.pb_size_patterns = np.array(pb_size_patterns)
+        self.num_classes = int(num_classes)
+        px = 1 / np.array(self.input_size)  # f64 (2,)
+        grids, locs, centers, sizes, masks, infos = [], [], [], [], [], []
+        for m in self.map_sizes:
+            cell = 1.0 / m  # np.float64 scalar
+            lin = np.linspace(0.5 * cell, 1 - 0.5 * cell, m, dtype=np.float32)
+            cx, cy = np.meshgrid(lin, lin)
+            c4 = np.tile(np.stack([cx.ravel(), cy.ravel()], axis=1), (1, 2))  # f32 (m*m,4)
+            g = c4.copy()
+            g[:, :2] -= cell / 2  # f64 arithmetic, stored f32 (od_pb.py:149)
+            g[:, 2:] += cell / 2 + px  # od_pb.py:150
+            for k, pat in enumerate(self.pb_size_patterns):
+                size = cell * pat  # f64 (2,)
+                box = c4.copy()
+                box[:, :2] -= size / 2  # od_pb.py:158
+                box[:, 2:] += size / 2 + px  # od_pb.py:159
+                cl = np.clip(box, 0, 1)
+                cc = (cl[:, :2] + cl[:, 2:]) / 2
+                ok = closed_interval(cc, g[:, :2], g[:, 2:]).all(axis=-1)  # od_pb.py:163
+                grids.append(g)
+                locs.append(box)
+                centers.append(c4[:, :2])
+                sizes.append(np.broadcast_to(size, (len(box), 2)))
+                masks.append(ok)
+                infos.append(np.full(len(box), len(infos), dtype=np.int64))
+        self.pb_grid = np.concatenate(grids)
+        self.pb_locs = np.concatenate(locs)
+        self.pb_centers = np.concatenate(centers)
+        self.pb_sizes = np.concatenate(sizes).astype(np.float64)
+        self.pb_mask = np.concatenate(masks)
+        self.pb_info_indices = np.concatenate(infos)
+        mid = np.mean([self.pb_locs[:, 2:], self.pb_locs[:, :2]], axis=0)  # od_pb.py:197-198
+        assert half_open_interval(mid, self.pb_grid[:, :2], self.pb_grid[:, 2:]).all()
+
+    def __len__(self):
+        return len(self.pb_locs)
+
+
+def encode_locs(t: AnchorTables, bbox, sel):
+    """dl/od_pb.py:212-214 — f32 difference, then two f64 divisions."""
+    return (bbox - t.pb_locs[sel, :]) / np.tile(t.pb_sizes[sel, :], 2) / VAR_LOC
+
+
+def decode_locs_f64(t: AnchorTables, pred):
+    """dl/od_pb.py:216-222 with xp=np (the check_assign.py:27 use): f64 result."""
+    return np.clip(pred * (VAR_LOC * np.tile(t.pb_sizes, 2)) + t.pb_locs, 0, 1)
+
+
+def decode_locs_f32(t: AnchorTables, pred):
+    """dl/od_pb.py:216-222 as the Keras Lambda evaluates it (od_net.py:189): the f64 constant
+    ``0.10*tile(pb_sizes,2)`` is converted to the tensor dtype (f32) and mul/add/clip run in f32."""
+    scale = (VAR_LOC * np.tile(t.pb_sizes, 2)).astype(np.float32)
+    pred = np.asarray(pred, dtype=np.float32)
+    return np.clip(pred * scale + t.pb_locs, np.float32(0), np.float32(1))
+
+
+def assign_boxes(t: AnchorTables, bboxes):
+    """dl/od_pb.py:315-363.  Returns (pb_indices i64 sorted, gt_indices i64, pb_valids bool)."""
+    n = len(t)
+    centres = box_centers(bboxes)
+    owner = np.full(n, -1, dtype=np.int64)
+    free = np.ones(n, dtype=bool)
+    valid = np.ones(n, dtype=bool)
+    order = box_areas(bboxes).argsort()  # od_pb.py:327 (default, unstable sort kind)
+    for g in order:
+        box, ctr = bboxes[g], centres[g]
+        usable = t.pb_mask & free
+        if not usable.any():
+            raise AssertionError('Encode error: %s' % (ctr,))  # od_pb.py:332
+        iou = pairwise_iou(box[None, :], t.pb_locs[usable, :])[0]  # od_pb.py:333
+        cell = half_open_interval(ctr, t.pb_grid[:, :2], t.pb_grid[:, 2:]).all(axis=-1) & t.pb_mask
+        if not cell.any():
+            raise AssertionError('Encode error: %s' % (ctr,))  # od_pb.py:338
+        cell &= free
+        if cell.any():
+            cost = np.sum(np.abs(encode_locs(t, box, cell)), axis=-1)  # od_pb.py:342
+            pick = np.flatnonzero(cell)[cost.argmin()]
+        else:
+            pick = np.flatnonzero(usable)[iou.argmax()]  # od_pb.py:349-350
+        owner[pick] = g
+        free[pick] = False
+        valid[np.flatnonzero(usable)[iou >= 0.5]] = False  # od_pb.py:355-357
+    idx = np.flatnonzero(owner >= 0)
+    if len(idx):
+        valid[idx] = True  # od_pb.py:359-361
+    return idx, owner[idx], valid
+
+
+def encode_truth(t: AnchorTables, gt_list):
+    """dl/od_pb.py:299-313.  ``gt_list`` = [(classes i32 (G,), bboxes f32 (G,4)), ...]."""
+    c = t.num_classes
+    out = np.zeros((len(gt_list), len(t), 3 + c + 4), dtype=np.float32)
+    for i, (classes, bboxes) in enumerate(gt_list):
+        classes = np.asarray(classes)
+        assert half_open_interval(classes, 0, c).all()  # od_pb.py:304
+        idx, gts, valid = assign_boxes(t, bboxes)
+        out[i, valid, 0] = 1 / max(1, len(idx))
+        for a, g in zip(idx, gts):
+            out[i, a, 1] = 1 / len(idx)
+            out[i, a, 2] = 1
+            out[i, a, 3 + classes[g]] = 1
+            out[i, a, -4:] = encode_locs(t, bboxes[g, :], a)
+    assert ((out[:, :, 0] != 0) & (out[:, :, 2] != 0) == (out[:, :, 2] != 0)).all()  # od_pb.py:312
+    return out
+
+
+# --------------------------------------------------------------------------------------
+def numpy_nms(boxes, scores, top_k=200, iou_threshold=0.45):
+    """ml.non_maximum_suppression (ml.py:589-625) incl. the zero-area skip, the ``>=`` test and
+    the quirk that the length check sits only in the non-first branch (SURVEY A-7)."""
+    assert len(boxes) == len(scores) and boxes.shape == (len(scores), 4)
+    order = scores.argsort()[::-1]
+    b = boxes[order]
+    area = np.prod(b[:, 2:] - b[:, :2], axis=1)
+    keep = []
+    for i in range(len(b)):
+        if (b[i, 2:] - b[i, :2] <= 0).any():
+            continue
+        if keep:
+            lo = np.maximum(b[i, :2], b[keep, :2])
+            hi = np.minimum(b[i, 2:], b[keep, 2:])
+            inter = np.prod(hi - lo, axis=1) * (lo < hi).all(axis=1)
+            if (inter / (area[i] + area[keep] - inter) >= iou_threshold).any():
+                continue
+            keep.append(i)
+            if len(keep) >= top_k:
+                break
+        else:
+            keep.append(i)
+    return order[keep]
+
+
+def stable_desc_order(scores):
+    """Tie policy of this build (SURVEY A-6): ``argsort(kind='stable')[::-1]`` — among equal
+    scores the HIGHER original index comes first.  Equals the reference whenever scores are
+    distinct (the synthetic workloads guarantee that)."""
+    return np.argsort(scores, kind='stable')[::-1]
+
+
+def numpy_nms_policy(boxes, scores, top_k=200, iou_threshold=0.45):
+    """``numpy_nms`` with the deterministic tie policy above (what the CUDA kernel implements).
+    Also returns early exactly like the reference; vectorised bookkeeping only."""
+    order = stable_desc_order(scores)
+    b = boxes[order]
+    area = np.prod(b[:, 2:] - b[:, :2], axis=1)
+    thr = scores.dtype.type(iou_threshold) if scores.dtype.kind == 'f' else iou_threshold
+    keep = []
+    for i in range(len(b)):
+        if (b[i, 2:] - b[i, :2] <= 0).any():
+            continue
+        if keep:
+            lo = np.maximum(b[i, :2], b[keep, :2])
+            hi = np.minimum(b[i, 2:], b[keep, 2:])
+            inter = np.prod(hi - lo, axis=1) * (lo < hi).all(axis=1)
+            if (inter / (area[i] + area[keep] - inter) >= thr).any():
+                continue
+            keep.append(i)
+            if len(keep) >= top_k:
+                break
+        else:
+            keep.append(i)
+    return order[keep]
+
+
+def score_anchors(t: AnchorTables, objs, clfs):
+    """layers.py:69-98 (ChannelArgMax / ChannelMax) + od_net.py:177-184 (_objconf).
+    objs (B,N,1) f32, clfs (B,N,C) f32 -> classes (B,N) i64, objconfs (B,N) f32."""
+    classes = np.argmax(clfs, axis=-1)
+    confs = np.max(clfs, axis=-1)
+    conf = objs[:, :, 0] * confs
+    return classes, conf * t.pb_mask[None, :].astype(np.float32)
+
+
+def nms_layer_image(classes, confs, locs, num_classes, top_k=200, conf_threshold=0.01,
+                    nms_threshold=0.45, inner=numpy_nms_policy):
+    """layers.py:925-970 for one image, nms_all_threshold=None branch.
+    Returns (out (top_k,6) f32, kept anchor index (top_k,) i64 with -1 padding)."""
+    cat_cls, cat_conf, cat_loc, cat_idx = [], [], [], []
+    for c in range(num_classes):
+        sel = np.flatnonzero((classes == c) & (confs > np.float32(conf_threshold)))  # :935 strict
+        if len(sel) == 0:
+            continue
+        k = min(top_k, len(sel))  # :940-941
+        kept = inner(locs[sel], confs[sel], k, nms_threshold)  # :942
+        cat_cls.append(np.full(len(kept), c, dtype=np.int64))
+        cat_conf.append(confs[sel][kept])
+        cat_loc.append(locs[sel][kept])
+        cat_idx.append(sel[kept])
+    out = np.zeros((top_k, 6), dtype=np.float32)
+    kept_idx = np.full(top_k, -1, dtype=np.int64)
+    if cat_cls:
+        cls = np.concatenate(cat_cls)
+        conf = np.concatenate(cat_conf)
+        loc = np.concatenate(cat_loc)
+        idx = np.concatenate(cat_idx)
+        k = min(top_k, len(conf))  # :952
+        top = np.argsort(-conf, kind='stable')[:k]  # tf.nn.top_k(sorted=True): lower position first on ties
+        out[:k, 0] = cls[top]
+        out[:k, 1] = conf[top]
+        out[:k, 2:] = loc[top]
+        kept_idx[:k] = idx[top]
+    return out, kept_idx
+
+
+def predict_tail(t: AnchorTables, objs, clfs, locs, top_k=200, conf_threshold=0.01,
+                 nms_threshold=0.45, inner=numpy_nms_policy):
+    """od_net.py:172-192: score -> decode (f32) -> NMS layer, whole batch.
+    Returns (B,top_k,6) f32 and (B,top_k) i64 kept anchor ids."""
+    classes, confs = score_anchors(t, objs, clfs)
+    boxes = decode_locs_f32(t, locs)
+    outs, idxs = [], []
+    for b in range(len(objs)):
+        o, k = nms_layer_image(classes[b], confs[b], boxes[b], t.num_classes, top_k,
+                               conf_threshold, nms_threshold, inner)
+        outs.append(o)
+        idxs.append(k)
+    return np.stack(outs), np.stack(idxs)
+
+
+def unpack_predictions(out, conf_threshold=0.01):
+    """dl/od.py:258-266 with keep_aspect=False (offset 0, size 1): list of (classes i32, confs, boxes)."""
+    res = []
+    for p in out:
+        m = p[:, 1] >= conf_threshold
+        res.append((p[m, 0].astype(np.int32), p[m, 1], (p[m, 2:] - 0) / 1))
+    return res
+
+
+# --------------------------------------------------------------------------------------
+def to_pixels(bboxes, width, height):
+    """ml.py:62-65 / 184-186: f64 product, round-half-even, int32."""
+    return np.round(bboxes * [width, height, width, height]).astype(np.int32)
+
+
+def _int_iou(a, b):
+    """chainercv.utils.bbox_iou on integer boxes (area as integer products, true division)."""
+    lo = np.maximum(a[:, None, :2], b[None, :, :2])
+    hi = np.minimum(a[:, None, 2:], b[None, :, 2:])
+    inter = np.prod(hi - lo, axis=2) * (lo < hi).all(axis=2)
+    aa = np.prod(a[:, 2:] - a[:, :2], axis=1)
+    ab = np.prod(b[:, 2:] - b[:, :2], axis=1)
+    return inter / (aa[:, None] + ab - inter)
+
+
+def voc_match(pred_boxes, pred_classes, pred_scores, gt_boxes, gt_classes, gt_difficult,
+              num_classes, iou_thresh=0.5):
+    """chainercv calc_detection_voc_prec_rec, matching part.  Per class returns
+    n_pos[c], and lists score[c], match[c] (1 TP, 0 FP, -1 ignored)."""
+    n_pos = np.zeros(num_classes, dtype=np.int64)
+    score = [[] for _ in range(num_classes)]
+    match = [[] for _ in range(num_classes)]
+    for pb, pc, ps, gb, gc, gd in zip(pred_boxes, pred_classes, pred_scores, gt_boxes, gt_classes,
+                                      gt_difficult):
+        for c in np.unique(np.concatenate([pc, gc]).astype(int)):
+            pm = pc == c
+            pbc, psc = pb[pm], ps[pm]
+            order = np.argsort(psc, kind='stable')[::-1]
+            pbc, psc = pbc[order], psc[order]
+            gm = gc == c
+            gbc, gdc = gb[gm], gd[gm]
+            n_pos[c] += np.logical_not(gdc).sum()
+            score[c].extend(psc)
+            if len(pbc) == 0:
+                continue
+            if len(gbc) == 0:
+                match[c].extend([0] * len(pbc))
+                continue
+            pbc = pbc.astype(np.int64).copy()
+            pbc[:, 2:] += 1
+            gbc = gbc.astype(np.int64).copy()
+            gbc[:, 2:] += 1
+            iou = _int_iou(pbc, gbc)
+            gi = iou.argmax(axis=1)
+            gi[iou.max(axis=1) < iou_thresh] = -1
+            used = np.zeros(len(gbc), dtype=bool)
+            for j in gi:
+                if j >= 0:
+                    if gdc[j]:
+                        match[c].append(-1)
+                    else:
+                        match[c].append(0 if used[j] else 1)
+                    used[j] = True
+                else:
+                    match[c].append(0)
+    return n_pos, score, match
+
+
+def voc_ap(n_pos, score, match, use_07_metric):
+    """chainercv calc_detection_voc_prec_rec (curve part) + calc_detection_voc_ap."""
+    num_classes = len(n_pos)
+    ap = np.full(num_classes, np.nan)
+    for c in range(num_classes):
+        s = np.array(score[c], dtype=np.float64)
+        m = np.array(match[c], dtype=np.int8)
+        if n_pos[c] == 0 and len(s) == 0:
+            continue  # class absent: prec/rec None -> ap nan
+        order = np.argsort(s, kind='stable')[::-1]
+        m = m[order]
+        tp = np.cumsum(m == 1)
+        fp = np.cumsum(m == 0)
+        with np.errstate(divide='ignore', invalid='ignore'):
+            prec = tp / (fp + tp)
+            rec = tp / n_pos[c] if n_pos[c] > 0 else None
+        if rec is None:
+            continue
+        if use_07_metric:
+            a = 0.0
+            for thr in np.arange(0.0, 1.1, 0.1):
+                p = 0 if np.sum(rec >= thr) == 0 else np.max(np.nan_to_num(prec)[rec >= thr])
+                a += p / 11
+            ap[c] = a
+        else:
+            mpre = np.concatenate(([0], np.nan_to_num(prec), [0]))
+            mrec = np.concatenate(([0], rec, [1]))
+            mpre = np.maximum.accumulate(mpre[::-1])[::-1]
+            i = np.where(mrec[1:] != mrec[:-1])[0]
+            ap[c] = np.sum((mrec[i + 1] - mrec[i]) * mpre[i + 1])
+    return ap
+
+
+def voc_evaluate(gt_list, pred_list, num_classes):
+    """data/voc.py:165-197.  gt_list = [(width, height, classes, bboxes f32, difficults)],
+    pred_list = [(classes, confs, bboxes f32)].  Returns the reference's 4-key dict."""
+    pb = [to_pixels(p[2], g[0], g[1]) for p, g in zip(pred_list, gt_list)]
+    pc = [np.asarray(p[0]) for p in pred_list]
+    ps = [np.asarray(p[1]) for p in pred_list]
+    gb = [to_pixels(g[3], g[0], g[1]) for g in gt_list]
+    gc = [np.asarray(g[2]) for g in gt_list]
+    gd = [np.asarray(g[4], dtype=bool) for g in gt_list]
+    n_pos, score, match = voc_match(pb, pc, ps, gb, gc, gd, num_classes)
+    ap = voc_ap(n_pos, score, match, False)
+    ap07 = voc_ap(n_pos, score, match, True)
+    with np.errstate(invalid='ignore'):
+        return {'AP': ap, 'mAP': np.nanmean(ap), 'AP_VOC': ap07, 'mAP_VOC': np.nanmean(ap07)}
