@@ -1,0 +1,147 @@
+/* odk.h — C-ABI of libodk.so: the B200 (sm_100a) detection hot path.
+ *
+ * The reference (ak110/object_detector, pytoolkit @ d542569) has no FFI: its boundary for this
+ * path is a set of Python call signatures.  Each entry point below names the reference function
+ * it replaces (paths relative to pytoolkit/pytoolkit/).  The Python mirror in
+ * object_detector_b200/ binds these with ctypes; INTEGRATION.md shows the stub a pytoolkit
+ * maintainer would add.
+ *
+ * Conventions
+ *  - every pointer marked [dev] is a DEVICE pointer owned by the caller (a torch tensor's
+ *    data_ptr()); [host] pointers are host memory, read during the call only;
+ *  - `stream` is a cudaStream_t passed as void* (0 = legacy default stream).  Launches are
+ *    asynchronous: no entry point synchronises the stream;
+ *  - every function returns 0 on success or a negative odk_status; the message is retrievable
+ *    per host thread with odk_last_error().  No global mutable state: safe to call from many
+ *    host threads on distinct streams (generator.py:160-166 calls encode_truth from a thread
+ *    pool);
+ *  - the library allocates device memory only inside odk_anchors_create (freed by
+ *    odk_anchors_destroy).  Scratch memory is passed in by the caller (odk_*_workspace_bytes).
+ */
+#ifndef ODK_H_
+#define ODK_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  ODK_OK = 0,
+  ODK_ERR_INVALID_ARGUMENT = -1, /* shape / range / alignment: the reference's assert on shapes       */
+  ODK_ERR_CUDA = -2,             /* a CUDA runtime call failed (message has cudaGetErrorString)       */
+  ODK_ERR_WORKSPACE = -3,        /* workspace smaller than odk_*_workspace_bytes()                    */
+  ODK_ERR_UNSUPPORTED = -4       /* size outside what the kernels are built for                       */
+} odk_status;
+
+/* Per-image status words written by odk_assign / odk_assign_encode into `status[B]` [dev]
+ * (they replace the reference's AssertionErrors, which are raised per image):            */
+#define ODK_IMG_OK 0
+#define ODK_IMG_ENCODE_ERROR 1   /* 'Encode error: {centre}'  od_pb.py:332,338                       */
+#define ODK_IMG_BAD_CLASS 2      /* assert in_range(classes, 0, C)  od_pb.py:304                      */
+#define ODK_IMG_BAD_COUNT 3      /* gt_count[b] outside [0, Gmax]                                     */
+
+typedef struct odk_anchors odk_anchors; /* opaque: device copies of the PriorBoxes tables */
+
+const char* odk_version(void);
+const char* odk_last_error(void);
+
+/* PriorBoxes._create_pb tables (dl/od_pb.py:125-184), built on the host by the Python mirror and
+ * uploaded once.  Anchor order is the reference's: maps in `map_sizes` order, then pattern, then
+ * row-major y*m+x (SURVEY A-1); n must equal n_patterns * sum(m*m).  pb_sizes stays fp64 because
+ * encode_locs divides in fp64 (od_pb.py:212-214); the fp32 decode scale float32(0.10*pb_sizes)
+ * (od_pb.py:221 as evaluated in the fp32 graph) is derived here. */
+int odk_anchors_create(odk_anchors** out, int n, int num_classes, int n_maps,
+                       const int32_t* map_sizes /*[host n_maps]*/, int n_patterns,
+                       const float* pb_locs /*[host n,4]*/, const float* pb_grid /*[host n,4]*/,
+                       const double* pb_sizes /*[host n,2]*/, const uint8_t* pb_mask /*[host n]*/);
+int odk_anchors_destroy(odk_anchors* a);
+int odk_anchors_count(const odk_anchors* a);
+int odk_anchors_num_classes(const odk_anchors* a);
+
+/* ml.compute_iou (ml.py:502-519) on fp32 boxes: out[i*nb+j] = IoU(a[i], b[j]). */
+int odk_compute_iou(const float* a /*[dev na,4]*/, int na, const float* b /*[dev nb,4]*/, int nb,
+                    float* out /*[dev na,nb]*/, void* stream);
+
+/* PriorBoxes.encode_locs (od_pb.py:212-214): out[k] = (boxes[k] - pb_locs[ix[k]]) / sizes / 0.10,
+ * fp64 result like the reference. */
+int odk_encode_locs(const odk_anchors* a, int k, const float* boxes /*[dev k,4]*/,
+                    const int32_t* ix /*[dev k]*/, double* out /*[dev k,4]*/, void* stream);
+
+/* PriorBoxes.decode_locs as the fp32 Keras Lambda (od_pb.py:216-222, od_net.py:189):
+ * out = clip(pred * float32(0.10*sizes) + pb_locs, 0, 1) over `rows` = B*N anchors rows. */
+int odk_decode_locs(const odk_anchors* a, int64_t rows, const float* pred /*[dev rows,4]*/,
+                    float* out /*[dev rows,4]*/, void* stream);
+
+/* PriorBoxes._assign_boxes (od_pb.py:315-363) for a padded batch.  Outputs per image b with
+ * G = gt_count[b]: pb_indices[b, 0:G] ascending anchor ids, gt_indices[b, 0:G] the GT each one
+ * owns (both -1 beyond G), status[b] one of ODK_IMG_*. */
+int odk_assign(const odk_anchors* a, int batch, const float* gt_boxes /*[dev B,Gmax,4]*/,
+               const int32_t* gt_count /*[dev B]*/, int gmax,
+               int64_t* pb_indices /*[dev B,Gmax]*/, int64_t* gt_indices /*[dev B,Gmax]*/,
+               int32_t* status /*[dev B]*/, void* stream);
+
+/* PriorBoxes.encode_truth (od_pb.py:299-313) = odk_assign + the y_true writer.
+ * y_true[b, n, :] = [mask, weight, obj, onehot(C), locs(4)] fp32, written in full (no pre-zeroing
+ * needed).  pb_valids (optional, may be NULL) receives _assign_boxes' third result. */
+int odk_assign_encode(const odk_anchors* a, int batch, const float* gt_boxes /*[dev B,Gmax,4]*/,
+                      const int32_t* gt_classes /*[dev B,Gmax]*/,
+                      const int32_t* gt_count /*[dev B]*/, int gmax,
+                      float* y_true /*[dev B,N,3+C+4]*/, int64_t* pb_indices /*[dev B,Gmax]*/,
+                      int64_t* gt_indices /*[dev B,Gmax]*/, uint8_t* pb_valids /*[dev B,N] or NULL*/,
+                      int32_t* status /*[dev B]*/, void* stream);
+
+/* ChannelArgMax + ChannelMax + _objconf + decode_locs (layers.py:69-98, od_net.py:177-189):
+ * classes = argmax_c clfs, confs = objs*max_c clfs*pb_mask, boxes = decode(locs). */
+int odk_decode_score(const odk_anchors* a, int batch, const float* objs /*[dev B,N,1]*/,
+                     const float* clfs /*[dev B,N,C]*/, const float* locs /*[dev B,N,4]*/,
+                     int32_t* classes /*[dev B,N]*/, float* confs /*[dev B,N]*/,
+                     float* boxes /*[dev B,N,4]*/, void* stream);
+
+/* Scratch size for odk_nms_layer / odk_decode_nms / odk_nms. */
+size_t odk_nms_workspace_bytes(int batch, int n, int num_classes, int top_k);
+
+/* layers.nms() -> NMS._process_image (layers.py:925-970), nms_all_threshold=None branch:
+ * per class: candidates classes==c & confs > conf_thr, greedy NMS, then top_k over all classes,
+ * zero padding.  out[b, r, :] = [class, conf, x1, y1, x2, y2]; kept_index[b, r] = anchor id or -1.
+ * iou_ge = 1: the reference's NumPy NMS semantics (ml.py:589-625: suppress if IoU >= thr, boxes
+ * with w<=0 or h<=0 skipped, length check quirk) — the bit-exact, pinned mode.
+ * iou_ge = 0: TensorFlow-1.10-style (suppress if IoU > thr, no zero-area skip, exact cut) —
+ * PARITY UNPINNED (TF source absent from the reference tree). */
+int odk_nms_layer(int batch, int n, int num_classes, const int32_t* classes /*[dev B,N]*/,
+                  const float* confs /*[dev B,N]*/, const float* boxes /*[dev B,N,4]*/,
+                  float conf_thr, float iou_thr, int top_k, int iou_ge,
+                  float* out /*[dev B,top_k,6]*/, int32_t* kept_index /*[dev B,top_k]*/,
+                  void* workspace /*[dev]*/, size_t workspace_bytes, void* stream);
+
+/* Fused odk_decode_score + odk_nms_layer (od_net.py:186-190 in one pass): the dense
+ * classes/confs/boxes intermediates never reach HBM. */
+int odk_decode_nms(const odk_anchors* a, int batch, const float* objs, const float* clfs,
+                   const float* locs, float conf_thr, float iou_thr, int top_k, int iou_ge,
+                   float* out /*[dev B,top_k,6]*/, int32_t* kept_index /*[dev B,top_k]*/,
+                   void* workspace /*[dev]*/, size_t workspace_bytes, void* stream);
+
+/* ml.non_maximum_suppression (ml.py:589-625) on one fp32 box set: writes the kept input indices
+ * in descending-score order to out_index[0:*out_count] (capacity max(top_k,2)). */
+int odk_nms(const float* boxes /*[dev n,4]*/, const float* scores /*[dev n]*/, int n, int top_k,
+            float iou_thr, int iou_ge, int32_t* out_index /*[dev max(top_k,2)]*/,
+            int32_t* out_count /*[dev 1]*/, void* workspace, size_t workspace_bytes, void* stream);
+
+/* data.voc.evaluate (data/voc.py:165-197 -> chainercv eval_detection_voc; PARITY UNPINNED).
+ * dets: the NMS layer output for n_img images; rows with conf < conf_thr are dropped
+ * (od.py:265).  gt_offsets[n_img+1] indexes the flat GT arrays.  Boxes are converted to integer
+ * pixels with round-half-even of the fp64 product (ml.py:62-65,184-186). */
+size_t odk_voc_ap_workspace_bytes(int n_img, int top_k, int num_classes, int n_gt_total);
+int odk_voc_ap(int n_img, int top_k, int num_classes, const float* dets /*[dev n_img,top_k,6]*/,
+               float conf_thr, const int32_t* img_wh /*[dev n_img,2]*/,
+               const float* gt_boxes /*[dev n_gt,4] normalised*/, const int32_t* gt_classes /*[dev n_gt]*/,
+               const uint8_t* gt_difficult /*[dev n_gt]*/, const int32_t* gt_offsets /*[dev n_img+1]*/,
+               int n_gt_total, double* ap_area /*[dev C]*/, double* ap07 /*[dev C]*/,
+               void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ODK_H_ */

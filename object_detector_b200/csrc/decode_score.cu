@@ -1,0 +1,252 @@
+// K1 — score + decode (+ candidate emission), the streaming HBM-bound kernel of the predict side.
+//
+// Replaces ChannelArgMax/ChannelMax (layers.py:69-98), _objconf (od_net.py:177-184) and the
+// decode_locs Lambda (od_pb.py:216-222, od_net.py:189) — three separate TF elementwise passes in
+// the reference — with one pass over the head outputs:
+//   classes = argmax_c clfs (first max wins), conf = (objs * max_c clfs) * pb_mask,
+//   box = clip(locs * float32(0.10*sizes) + pb_locs, 0, 1)
+// and, for the NMS that follows, appends a 64-bit sort key for every anchor with conf > conf_thr
+// (strict, layers.py:935) to the image's candidate list.
+//
+// Data movement: persistent CTAs, one tile = TILE consecutive anchors of one image.  The three input
+// slabs of a tile (clfs TILE*C*4 B, locs TILE*16 B, objs TILE*4 B) are contiguous in HBM, so each is
+// fetched with ONE 1-D bulk TMA copy (cp.async.bulk, SASS UBLKCP) into a 3-stage shared-memory ring
+// guarded by mbarriers; a thread then owns one anchor row in shared memory.  Tiles whose source
+// addresses / sizes are not 16-byte multiples fall back to cooperative plain loads into the same
+// ring slot.  Algorithmic HBM bytes per anchor: read 4*(1+C+4); write 4+4+16 (dense mode) or
+// 8 B per candidate + 16 B per candidate box (fused mode).
+#include "odk_common.cuh"
+
+namespace {
+
+constexpr int kStages = 3;
+
+struct DecodeArgs {
+  AnchorView av;
+  int batch, n, c;
+  const float* objs;
+  const float* clfs;
+  const float* locs;
+  int32_t* classes;  // dense outputs (null in fused mode)
+  float* confs;
+  float4* boxes;     // dense mode: all rows; fused mode: candidate rows only
+  float conf_thr;
+  unsigned long long* cand_keys;  // [B, cand_cap] or null
+  int* cand_count;                // [B]
+  int cand_cap;
+  int tiles_per_image;
+};
+
+template <int TILE, bool DENSE>
+__global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int c = p.c;
+  const size_t clf_bytes = (size_t)TILE * c * 4;
+  const size_t stage_bytes = clf_bytes + (size_t)TILE * 16 + (size_t)TILE * 4;  // all multiples of 16
+  __shared__ uint64_t full_bar[kStages];
+
+  const long long total_tiles = (long long)p.batch * p.tiles_per_image;
+  const int tid = threadIdx.x;
+
+  if (tid == 0) {
+    for (int s = 0; s < kStages; ++s) odk_mbar_init(&full_bar[s], 1);
+    odk_mbar_fence_init();
+  }
+  __syncthreads();
+
+  auto stage_ptr = [&](int s) { return smem_raw + (size_t)s * stage_bytes; };
+
+  // Issue the loads of tile `t` into ring slot `s`.  Returns via the mbarrier in both paths.
+  auto issue = [&](long long t, int s) {
+    const int b = (int)(t / p.tiles_per_image);
+    const int a0 = (int)(t % p.tiles_per_image) * TILE;
+    const int rows = min(TILE, p.n - a0);
+    const size_t row0 = (size_t)b * p.n + a0;
+    const float* src_clf = p.clfs + row0 * c;
+    const float* src_loc = p.locs + row0 * 4;
+    const float* src_obj = p.objs + row0;
+    unsigned char* dst = stage_ptr(s);
+    const bool tma_ok = ((rows & 3) == 0) && ((((uintptr_t)src_clf | (uintptr_t)src_loc | (uintptr_t)src_obj) & 15) == 0);
+    if (tma_ok) {
+      if (tid == 0) {
+        const uint32_t b0 = (uint32_t)rows * c * 4, b1 = (uint32_t)rows * 16, b2 = (uint32_t)rows * 4;
+        odk_mbar_expect_tx(&full_bar[s], b0 + b1 + b2);
+        odk_bulk_g2s(dst, src_clf, b0, &full_bar[s]);
+        odk_bulk_g2s(dst + clf_bytes, src_loc, b1, &full_bar[s]);
+        odk_bulk_g2s(dst + clf_bytes + (size_t)TILE * 16, src_obj, b2, &full_bar[s]);
+      }
+    } else {
+      float* d0 = reinterpret_cast<float*>(dst);
+      float* d1 = reinterpret_cast<float*>(dst + clf_bytes);
+      float* d2 = reinterpret_cast<float*>(dst + clf_bytes + (size_t)TILE * 16);
+      for (int i = tid; i < rows * c; i += TILE) d0[i] = __ldg(src_clf + i);
+      for (int i = tid; i < rows * 4; i += TILE) d1[i] = __ldg(src_loc + i);
+      for (int i = tid; i < rows; i += TILE) d2[i] = __ldg(src_obj + i);
+      __syncthreads();  // plain stores visible before the single arrive below
+      if (tid == 0) odk_mbar_arrive(&full_bar[s]);
+    }
+  };
+
+  // prologue: fill the ring
+  long long t_issue = blockIdx.x;
+  for (int s = 0; s < kStages; ++s, t_issue += gridDim.x)
+    if (t_issue < total_tiles) issue(t_issue, s);
+
+  int slot = 0;
+  uint32_t phase = 0;
+  for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    odk_mbar_wait(&full_bar[slot], phase);
+    const int b = (int)(t / p.tiles_per_image);
+    const int a0 = (int)(t % p.tiles_per_image) * TILE;
+    const int rows = min(TILE, p.n - a0);
+    const unsigned char* st = stage_ptr(slot);
+    const float* s_clf = reinterpret_cast<const float*>(st);
+    const float4* s_loc = reinterpret_cast<const float4*>(st + clf_bytes);
+    const float* s_obj = reinterpret_cast<const float*>(st + clf_bytes + (size_t)TILE * 16);
+
+    bool is_cand = false;
+    int cls = 0;
+    float conf = 0.0f;
+    float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int a = a0 + tid;
+    if (tid < rows) {
+      const float* row = s_clf + (size_t)tid * c;
+      float best;
+      if ((c & 3) == 0) {
+        const float4* row4 = reinterpret_cast<const float4*>(row);
+        float4 v = row4[0];
+        best = v.x;
+        if (v.y > best) { best = v.y; cls = 1; }
+        if (v.z > best) { best = v.z; cls = 2; }
+        if (v.w > best) { best = v.w; cls = 3; }
+        for (int j = 1; j < (c >> 2); ++j) {
+          v = row4[j];
+          if (v.x > best) { best = v.x; cls = 4 * j; }
+          if (v.y > best) { best = v.y; cls = 4 * j + 1; }
+          if (v.z > best) { best = v.z; cls = 4 * j + 2; }
+          if (v.w > best) { best = v.w; cls = 4 * j + 3; }
+        }
+      } else {
+        best = row[0];
+        for (int j = 1; j < c; ++j) {
+          const float v = row[j];
+          if (v > best) { best = v; cls = j; }
+        }
+      }
+      const float maskf = p.av.mask[a] ? 1.0f : 0.0f;
+      conf = __fmul_rn(__fmul_rn(s_obj[tid], best), maskf);  // (objs*confs)*pb_mask, od_net.py:183-184
+      const float4 pr = s_loc[tid];
+      const float4 lc = __ldg(p.av.locs + a);
+      const float2 sc = __ldg(p.av.scale + a);
+      box.x = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.x, sc.x), lc.x), 0.0f), 1.0f);
+      box.y = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.y, sc.y), lc.y), 0.0f), 1.0f);
+      box.z = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.z, sc.x), lc.z), 0.0f), 1.0f);
+      box.w = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.w, sc.y), lc.w), 0.0f), 1.0f);
+      is_cand = (p.cand_keys != nullptr) && (conf > p.conf_thr);
+      const size_t r = (size_t)b * p.n + a;
+      if (DENSE) {
+        p.classes[r] = cls;
+        p.confs[r] = conf;
+        p.boxes[r] = box;
+      } else if (is_cand) {
+        p.boxes[r] = box;
+      }
+    }
+    // candidate append, one atomic per warp
+    if (p.cand_keys != nullptr) {
+      const unsigned m = __ballot_sync(0xffffffffu, is_cand);
+      if (m) {
+        const unsigned lane = odk_lane();
+        int base = 0;
+        if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(p.cand_count + b, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+        if (is_cand) {
+          const int pos = base + __popc(m & ((1u << lane) - 1u));
+          if (pos < p.cand_cap) p.cand_keys[(size_t)b * p.cand_cap + pos] = odk_make_key1(cls, conf, a);
+        }
+      }
+    }
+    __syncthreads();  // every thread is done with ring slot `slot`
+    if (t_issue < total_tiles) issue(t_issue, slot);
+    t_issue += gridDim.x;
+    if (++slot == kStages) { slot = 0; phase ^= 1u; }
+  }
+}
+
+// decode_locs alone (the Keras Lambda): pure elementwise float4 stream.
+__global__ void __launch_bounds__(256) decode_locs_kernel(AnchorView av, long long rows, const float4* __restrict__ pred,
+                                                          float4* __restrict__ out) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += (long long)gridDim.x * blockDim.x) {
+    const int a = (int)(r % av.n);
+    const float4 pr = pred[r];
+    const float4 lc = __ldg(av.locs + a);
+    const float2 sc = __ldg(av.scale + a);
+    float4 box;
+    box.x = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.x, sc.x), lc.x), 0.0f), 1.0f);
+    box.y = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.y, sc.y), lc.y), 0.0f), 1.0f);
+    box.z = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.z, sc.x), lc.z), 0.0f), 1.0f);
+    box.w = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.w, sc.y), lc.w), 0.0f), 1.0f);
+    out[r] = box;
+  }
+}
+
+int sm_count_cached() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+  }
+  return sms;
+}
+
+template <int TILE, bool DENSE>
+int launch_tile(DecodeArgs& args, cudaStream_t stream) {
+  const size_t stage = (size_t)TILE * args.c * 4 + (size_t)TILE * 20;
+  const size_t smem = stage * kStages;
+  auto kern = decode_score_kernel<TILE, DENSE>;
+  ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  args.tiles_per_image = (args.n + TILE - 1) / TILE;
+  const long long total = (long long)args.batch * args.tiles_per_image;
+  int per_sm = (int)((220 * 1024) / (smem + 1024));
+  per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / TILE ? 2048 / TILE : per_sm);
+  long long grid = (long long)sm_count_cached() * per_sm;
+  if (grid > total) grid = total;
+  if (grid < 1) grid = 1;
+  kern<<<(unsigned)grid, TILE, smem, stream>>>(args);
+  ODK_LAUNCH_CHECK("decode_score_kernel");
+  return ODK_OK;
+}
+
+}  // namespace
+
+// Internal entry used by odk_decode_score (dense) and odk_decode_nms (fused).
+int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
+                            int32_t* classes, float* confs, float* boxes, bool dense, float conf_thr,
+                            unsigned long long* cand_keys, int* cand_count, int cand_cap, cudaStream_t stream) {
+  DecodeArgs args;
+  args.av = odk_view(a);
+  args.batch = batch; args.n = a->n; args.c = a->num_classes;
+  args.objs = objs; args.clfs = clfs; args.locs = locs;
+  args.classes = classes; args.confs = confs; args.boxes = reinterpret_cast<float4*>(boxes);
+  args.conf_thr = conf_thr; args.cand_keys = cand_keys; args.cand_count = cand_count; args.cand_cap = cand_cap;
+  args.tiles_per_image = 0;
+  const int c = a->num_classes;
+  // tile height chosen so a 3-stage ring stays under ~100 KB (2+ CTAs per SM)
+  if (c <= 32) return dense ? launch_tile<256, true>(args, stream) : launch_tile<256, false>(args, stream);
+  if (c <= 96) return dense ? launch_tile<64, true>(args, stream) : launch_tile<64, false>(args, stream);
+  ODK_REQUIRE(c <= 512, ODK_ERR_UNSUPPORTED, "num_classes=%d > 512 not supported by decode_score", c);
+  return dense ? launch_tile<32, true>(args, stream) : launch_tile<32, false>(args, stream);
+}
+
+int odk_launch_decode_locs(const odk_anchors* a, long long rows, const float* pred, float* out, cudaStream_t stream) {
+  long long blocks = (rows + 255) / 256;
+  const long long cap = (long long)sm_count_cached() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  decode_locs_kernel<<<(unsigned)blocks, 256, 0, stream>>>(odk_view(a), rows, reinterpret_cast<const float4*>(pred),
+                                                            reinterpret_cast<float4*>(out));
+  ODK_LAUNCH_CHECK("decode_locs_kernel");
+  return ODK_OK;
+}

@@ -1,0 +1,119 @@
+// libodk C-ABI glue: error reporting, the anchors handle, and the thin entry points that only
+// validate and launch (the kernels live in decode_score.cu / nms.cu / assign_encode.cu / voc_ap.cu).
+#include <math.h>
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "odk_common.cuh"
+
+static thread_local char g_last_error[512] = "";
+
+int odk_set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_last_error, sizeof(g_last_error), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
+                            int32_t* classes, float* confs, float* boxes, bool dense, float conf_thr,
+                            unsigned long long* cand_keys, int* cand_count, int cand_cap, cudaStream_t stream);
+int odk_launch_decode_locs(const odk_anchors* a, long long rows, const float* pred, float* out, cudaStream_t stream);
+
+extern "C" const char* odk_version(void) { return "odk 0.1.0 (sm_100a)"; }
+extern "C" const char* odk_last_error(void) { return g_last_error; }
+
+template <typename T>
+static int upload(T** dst, const void* src, size_t count) {
+  ODK_CUDA(cudaMalloc(reinterpret_cast<void**>(dst), sizeof(T) * count));
+  ODK_CUDA(cudaMemcpy(*dst, src, sizeof(T) * count, cudaMemcpyHostToDevice));
+  return ODK_OK;
+}
+
+extern "C" int odk_anchors_destroy(odk_anchors* a) {
+  if (a == nullptr) return ODK_OK;
+  cudaFree(a->d_locs); cudaFree(a->d_grid); cudaFree(a->d_sizes); cudaFree(a->d_scale); cudaFree(a->d_mask);
+  free(a);
+  return ODK_OK;
+}
+
+extern "C" int odk_anchors_create(odk_anchors** out, int n, int num_classes, int n_maps, const int32_t* map_sizes, int n_patterns,
+                                  const float* pb_locs, const float* pb_grid, const double* pb_sizes, const uint8_t* pb_mask) {
+  ODK_REQUIRE(out != nullptr, ODK_ERR_INVALID_ARGUMENT, "anchors_create: null output handle");
+  *out = nullptr;
+  ODK_REQUIRE(n >= 1 && num_classes >= 1, ODK_ERR_INVALID_ARGUMENT, "anchors_create: n=%d num_classes=%d (od_pb.py:40-42)", n, num_classes);
+  ODK_REQUIRE(n_maps >= 1 && n_maps <= ODK_MAX_MAPS && n_patterns >= 1, ODK_ERR_INVALID_ARGUMENT,
+              "anchors_create: n_maps=%d (1..%d) n_patterns=%d", n_maps, ODK_MAX_MAPS, n_patterns);
+  ODK_REQUIRE(map_sizes && pb_locs && pb_grid && pb_sizes && pb_mask, ODK_ERR_INVALID_ARGUMENT, "anchors_create: null table pointer");
+  ODK_REQUIRE(n <= (int)ODK_IDX_MASK, ODK_ERR_UNSUPPORTED, "anchors_create: n=%d exceeds 2^20-1 anchors", n);
+  ODK_REQUIRE(num_classes <= ODK_MAX_CLASSES, ODK_ERR_UNSUPPORTED, "anchors_create: num_classes=%d > %d", num_classes, ODK_MAX_CLASSES);
+  odk_anchors* a = static_cast<odk_anchors*>(calloc(1, sizeof(odk_anchors)));
+  ODK_REQUIRE(a != nullptr, ODK_ERR_CUDA, "anchors_create: out of host memory");
+  a->n = n; a->num_classes = num_classes; a->n_maps = n_maps; a->n_patterns = n_patterns;
+  long long total = 0;
+  for (int i = 0; i < n_maps; ++i) {
+    if (map_sizes[i] < 1) { free(a); return odk_set_error(ODK_ERR_INVALID_ARGUMENT, "anchors_create: map_sizes[%d]=%d", i, map_sizes[i]); }
+    a->map_size[i] = map_sizes[i];
+    a->map_off[i] = (int)total;
+    total += (long long)map_sizes[i] * map_sizes[i] * n_patterns;
+  }
+  for (int i = n_maps; i <= ODK_MAX_MAPS; ++i) a->map_off[i] = (int)total;
+  if (total != n) { free(a); return odk_set_error(ODK_ERR_INVALID_ARGUMENT, "anchors_create: n=%d but the layout holds %lld anchors", n, total); }
+  // The assignment kernel locates candidate cells as floor(c*m)+{-1,0,1}; that is exhaustive iff
+  // every cell [lo, hi) satisfies  ix/m - eps <= lo  and  hi <= (ix+2)/m  for its own (ix, iy).
+  for (int mi = 0; mi < n_maps; ++mi) {
+    const int m = a->map_size[mi];
+    for (int pat = 0; pat < n_patterns; ++pat)
+      for (int iy = 0; iy < m; ++iy)
+        for (int ix = 0; ix < m; ++ix) {
+          const float* g = pb_grid + 4 * ((size_t)a->map_off[mi] + (size_t)pat * m * m + (size_t)iy * m + ix);
+          const double eps = 1e-6;
+          const bool okx = g[0] >= (double)ix / m - eps && g[2] <= (double)(ix + 2) / m && g[0] < g[2];
+          const bool oky = g[1] >= (double)iy / m - eps && g[3] <= (double)(iy + 2) / m && g[1] < g[3];
+          if (!okx || !oky) {
+            free(a);
+            return odk_set_error(ODK_ERR_INVALID_ARGUMENT,
+                                 "anchors_create: pb_grid row for map %d cell (%d,%d) pattern %d does not follow the PriorBoxes layout", m, ix, iy, pat);
+          }
+        }
+  }
+  int valid = 0;
+  for (int i = 0; i < n; ++i) valid += pb_mask[i] ? 1 : 0;
+  a->n_valid = valid;
+  float* scale = static_cast<float*>(malloc(sizeof(float) * 2 * (size_t)n));
+  if (scale == nullptr) { free(a); return odk_set_error(ODK_ERR_CUDA, "anchors_create: out of host memory"); }
+  for (size_t i = 0; i < 2 * (size_t)n; ++i) scale[i] = (float)(0.10 * pb_sizes[i]);  // float32(_VAR_LOC * pb_sizes), od_pb.py:221
+  cudaGetDevice(&a->device);
+  int rc = upload(&a->d_locs, pb_locs, n);
+  if (!rc) rc = upload(&a->d_grid, pb_grid, n);
+  if (!rc) rc = upload(&a->d_sizes, pb_sizes, n);
+  if (!rc) rc = upload(&a->d_scale, scale, n);
+  if (!rc) rc = upload(&a->d_mask, pb_mask, n);
+  free(scale);
+  if (rc) { odk_anchors_destroy(a); return rc; }
+  *out = a;
+  return ODK_OK;
+}
+
+extern "C" int odk_anchors_count(const odk_anchors* a) { return a ? a->n : 0; }
+extern "C" int odk_anchors_num_classes(const odk_anchors* a) { return a ? a->num_classes : 0; }
+
+extern "C" int odk_decode_locs(const odk_anchors* a, int64_t rows, const float* pred, float* out, void* stream) {
+  ODK_REQUIRE(a != nullptr && rows >= 0, ODK_ERR_INVALID_ARGUMENT, "decode_locs: bad arguments");
+  ODK_REQUIRE(rows % a->n == 0, ODK_ERR_INVALID_ARGUMENT, "decode_locs: rows=%lld is not a multiple of N=%d", (long long)rows, a->n);
+  if (rows == 0) return ODK_OK;
+  ODK_REQUIRE(pred && out, ODK_ERR_INVALID_ARGUMENT, "decode_locs: null pointer");
+  ODK_REQUIRE((((uintptr_t)pred | (uintptr_t)out) & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_locs: buffers must be 16-byte aligned");
+  return odk_launch_decode_locs(a, rows, pred, out, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int odk_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs, int32_t* classes,
+                                float* confs, float* boxes, void* stream) {
+  ODK_REQUIRE(a != nullptr && batch >= 1, ODK_ERR_INVALID_ARGUMENT, "decode_score: bad arguments");
+  ODK_REQUIRE(objs && clfs && locs && classes && confs && boxes, ODK_ERR_INVALID_ARGUMENT, "decode_score: null pointer");
+  ODK_REQUIRE(((uintptr_t)boxes & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_score: boxes must be 16-byte aligned");
+  return odk_launch_decode_score(a, batch, objs, clfs, locs, classes, confs, boxes, true, 0.f, nullptr, nullptr, 0,
+                                 static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,187 @@
+// Shared device/host helpers of libodk (sm_100a only).
+//
+// Bit-exactness rule: every arithmetic step that the reference performs in NumPy is
+// written with the round-to-nearest intrinsics (__fadd_rn/__fsub_rn/__fmul_rn/__fdiv_rn), which the
+// compiler never contracts into FMAs, in the reference's operation order.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/odk.h"
+
+#define ODK_MAX_MAPS 8
+#define ODK_IDX_BITS 20                 // anchor index field of the sort keys (N < 2^20)
+#define ODK_IDX_MASK ((1u << ODK_IDX_BITS) - 1u)
+#define ODK_MAX_CLASSES 4096            // class field of the sort keys (12 bits)
+
+struct odk_anchors {
+  int n, num_classes, n_maps, n_patterns, n_valid, device;
+  int map_size[ODK_MAX_MAPS];
+  int map_off[ODK_MAX_MAPS + 1];
+  float4* d_locs;    // pb_locs  (x1,y1,x2,y2) unclipped
+  float4* d_grid;    // pb_grid  cell bounds
+  double2* d_sizes;  // pb_sizes (w,h) fp64
+  float2* d_scale;   // float32(0.10 * pb_sizes)
+  uint8_t* d_mask;   // pb_mask
+};
+
+// By-value kernel argument (pointers + layout); no device-side handle dereference.
+struct AnchorView {
+  int n, num_classes, n_maps, n_patterns, n_valid;
+  int map_size[ODK_MAX_MAPS];
+  int map_off[ODK_MAX_MAPS + 1];
+  const float4* locs;
+  const float4* grid;
+  const double2* sizes;
+  const float2* scale;
+  const uint8_t* mask;
+};
+
+inline AnchorView odk_view(const odk_anchors* a) {
+  AnchorView v;
+  v.n = a->n; v.num_classes = a->num_classes; v.n_maps = a->n_maps; v.n_patterns = a->n_patterns;
+  v.n_valid = a->n_valid;
+  for (int i = 0; i < ODK_MAX_MAPS; ++i) v.map_size[i] = a->map_size[i];
+  for (int i = 0; i <= ODK_MAX_MAPS; ++i) v.map_off[i] = a->map_off[i];
+  v.locs = a->d_locs; v.grid = a->d_grid; v.sizes = a->d_sizes; v.scale = a->d_scale; v.mask = a->d_mask;
+  return v;
+}
+
+// ---- host-side error plumbing ------------------------------------------------------------------
+int odk_set_error(int code, const char* fmt, ...);
+#define ODK_REQUIRE(cond, code, ...) \
+  do { if (!(cond)) return odk_set_error((code), __VA_ARGS__); } while (0)
+#define ODK_CUDA(expr) \
+  do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) \
+    return odk_set_error(ODK_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_)); } while (0)
+#define ODK_LAUNCH_CHECK(name) \
+  do { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) \
+    return odk_set_error(ODK_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e_)); } while (0)
+
+__host__ __device__ static inline size_t odk_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+static inline int odk_next_pow2(int x) { int p = 1; while (p < x) p <<= 1; return p; }
+
+// ---- exact fp32 box arithmetic (ml.py:485-519, 605-618) ------------------------------------------
+__device__ __forceinline__ float odk_area(const float4 b) {
+  return __fmul_rn(__fsub_rn(b.z, b.x), __fsub_rn(b.w, b.y));
+}
+
+// Intersection area exactly as compute_iou: prod(rb - lt) * all(lt < rb).  `hit` tells whether the
+// boxes overlap with positive extent (otherwise the product is multiplied by 0).
+__device__ __forceinline__ float odk_inter(const float4 a, const float4 b, bool& hit) {
+  const float lx = fmaxf(a.x, b.x), ly = fmaxf(a.y, b.y);
+  const float rx = fminf(a.z, b.z), ry = fminf(a.w, b.w);
+  hit = (lx < rx) && (ly < ry);
+  return __fmul_rn(__fsub_rn(rx, lx), __fsub_rn(ry, ly));
+}
+
+// fl(inter / ((area_a + area_b) - inter)): the reference's IoU value.
+__device__ __forceinline__ float odk_iou_value(const float4 a, float area_a, const float4 b, float area_b) {
+  bool hit;
+  float inter = odk_inter(a, b, hit);
+  inter = hit ? inter : 0.0f;
+  const float uni = __fsub_rn(__fadd_rn(area_a, area_b), inter);
+  return __fdiv_rn(inter, uni);
+}
+
+// Exact evaluation of  fl(inter/union) >= thr  (or > thr) with a division-free fast path: outside a
+// 1e-5 relative guard band around thr*union the rounded quotient cannot cross thr (rounding is
+// monotonic and thr is representable), inside it the IEEE division decides.
+template <bool GE>
+__device__ __forceinline__ bool odk_iou_passes(const float4 a, float area_a, const float4 b, float area_b,
+                                               float thr) {
+  bool hit;
+  const float inter = odk_inter(a, b, hit);
+  if (!hit) return GE ? (0.0f >= thr) : (0.0f > thr);
+  const float uni = __fsub_rn(__fadd_rn(area_a, area_b), inter);
+  const float p = thr * uni;
+  if (inter > p * 1.00001f && uni > 0.0f) return true;
+  if (inter < p * 0.99999f && uni > 0.0f) return false;
+  const float q = __fdiv_rn(inter, uni);
+  return GE ? (q >= thr) : (q > thr);
+}
+
+// ---- 64-bit sort keys of the NMS pipeline -------------------------------------------------------------
+// flip_score maps fp32 to uint32 so that unsigned order == float order (negative scores included).
+__device__ __forceinline__ uint32_t odk_flip_score(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return u ^ ((u >> 31) ? 0xffffffffu : 0x80000000u);
+}
+__device__ __forceinline__ float odk_unflip_score(uint32_t u) {
+  return __uint_as_float((u & 0x80000000u) ? (u ^ 0x80000000u) : ~u);
+}
+// key1 = [4095-class : 12][flip(score) : 32][anchor : 20]; descending key1 == class ascending, score
+// descending, anchor index descending.
+__device__ __forceinline__ unsigned long long odk_make_key1(int cls, float conf, int idx) {
+  return ((unsigned long long)(ODK_MAX_CLASSES - 1 - cls) << (32 + ODK_IDX_BITS)) |
+         ((unsigned long long)odk_flip_score(conf) << ODK_IDX_BITS) | (unsigned long long)idx;
+}
+__device__ __forceinline__ int odk_key1_class(unsigned long long k) {
+  return ODK_MAX_CLASSES - 1 - (int)(k >> (32 + ODK_IDX_BITS));
+}
+// key2 = [flip(score) : 32][4095-class : 12][anchor : 20]
+__device__ __forceinline__ unsigned long long odk_key1_to_key2(unsigned long long k) {
+  const unsigned long long cls_field = k >> (32 + ODK_IDX_BITS);
+  const unsigned long long score = (k >> ODK_IDX_BITS) & 0xffffffffull;
+  return (score << 32) | (cls_field << ODK_IDX_BITS) | (k & ODK_IDX_MASK);
+}
+
+// ---- warp helpers ------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned odk_lane() { return threadIdx.x & 31u; }
+
+// ---- mbarrier + 1-D bulk TMA (cp.async.bulk -> SASS UBLKCP) -------------------------------------------
+__device__ __forceinline__ uint32_t odk_smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void odk_mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(odk_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void odk_mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void odk_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(odk_smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void odk_mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(odk_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void odk_mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "DONE:\n"
+      "}\n" ::"r"(odk_smem_u32(bar)), "r"(parity)
+      : "memory");
+}
+// global -> shared bulk copy; dst/src 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void odk_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   odk_smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(odk_smem_u32(bar))
+               : "memory");
+}
+// shared -> global bulk copy (bulk async-group completion).
+__device__ __forceinline__ void odk_bulk_s2g(void* dst, const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(odk_smem_u32(src)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void odk_bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void odk_bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void odk_bulk_wait() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void odk_fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}

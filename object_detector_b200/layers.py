@@ -1,0 +1,85 @@
+"""Mirror of the prediction-tail layers of pytoolkit/pytoolkit/dl/layers.py: ``nms()``,
+``channel_argmax()``, ``channel_max()`` (layers.py:69-98, 876-972) as plain callables over CUDA
+tensors (there is no Keras graph here)."""
+import torch
+
+from . import _dev, _lib
+
+
+def nms():
+    """Factory, like the reference (layers.py:876): returns the ``NMS`` class."""
+
+    class NMS:
+        """layers.py:890-970.  ``NMS(num_classes, prior_boxes, ...)([classes, confs, locs]) -> (B, top_k, 6)``
+        rows [class, conf, x1, y1, x2, y2], zero padded.  ``nms_all_threshold`` (strict all-class NMS,
+        od_net.py:175) is SURVEY §8 row f4 and not built yet."""
+
+        def __init__(self, num_classes, prior_boxes, top_k=200, conf_threshold=0.01, nms_threshold=0.45,
+                     nms_all_threshold=None, iou_ge=True, **kwargs):
+            del kwargs
+            self.num_classes = num_classes
+            self.prior_boxes = prior_boxes
+            self.top_k = top_k
+            self.conf_threshold = conf_threshold
+            self.nms_threshold = nms_threshold
+            self.nms_all_threshold = nms_all_threshold
+            self.iou_ge = iou_ge  # True: reference NumPy-NMS semantics (pinned); False: TF-1.10 style (unpinned)
+            if nms_all_threshold:
+                raise NotImplementedError('nms_all_threshold (strict_nms) is not built yet (SURVEY §8 f4)')
+
+        def compute_output_shape(self, input_shape):
+            assert input_shape and len(input_shape) >= 2
+            return (input_shape[0][0], self.top_k, 1 + 1 + 4)
+
+        def get_config(self):
+            return {
+                'num_classes': self.num_classes, 'prior_boxes': self.prior_boxes, 'top_k': self.top_k,
+                'conf_threshold': self.conf_threshold, 'nms_threshold': self.nms_threshold,
+                'nms_all_threshold': self.nms_all_threshold,
+            }
+
+        def call(self, inputs, return_index=False, **kwargs):
+            del kwargs
+            classes, confs, locs = inputs
+            is_np = not isinstance(confs, torch.Tensor)
+            dev = _dev.device(None if is_np or not confs.is_cuda else confs.device)
+            n = self.prior_boxes
+            classes = _dev.to_device(classes, torch.int32, dev).reshape(-1, n)
+            confs = _dev.to_device(confs, torch.float32, dev).reshape(-1, n)
+            locs = _dev.to_device(locs, torch.float32, dev).reshape(-1, n, 4)
+            b = confs.shape[0]
+            out = torch.empty((b, self.top_k, 6), dtype=torch.float32, device=dev)
+            kept = torch.empty((b, self.top_k), dtype=torch.int32, device=dev)
+            ws_bytes = _lib.load().odk_nms_workspace_bytes(b, n, self.num_classes, self.top_k)
+            ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+            with torch.cuda.device(dev):
+                _lib.call('odk_nms_layer', b, n, self.num_classes, classes.data_ptr(), confs.data_ptr(), locs.data_ptr(),
+                          float(self.conf_threshold), float(self.nms_threshold), int(self.top_k), 1 if self.iou_ge else 0,
+                          out.data_ptr(), kept.data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
+            if is_np:
+                out, kept = out.cpu().numpy(), kept.cpu().numpy()
+            return (out, kept) if return_index else out
+
+        __call__ = call
+
+    return NMS
+
+
+def channel_argmax():
+    """layers.py:69-82."""
+
+    class ChannelArgMax:
+        def __call__(self, inputs):
+            return torch.argmax(inputs, dim=-1)
+
+    return ChannelArgMax
+
+
+def channel_max():
+    """layers.py:85-98."""
+
+    class ChannelMax:
+        def __call__(self, inputs):
+            return torch.max(inputs, dim=-1).values
+
+    return ChannelMax

@@ -1,0 +1,114 @@
+"""Mirror of the detection parts of pytoolkit/pytoolkit/ml.py: the two datatypes, ``compute_iou`` and
+``non_maximum_suppression`` (ml.py:15-197, 485-519, 589-625).  The array maths runs in libodk kernels.
+"""
+import pathlib
+
+import numpy as np
+import torch
+
+from . import _dev, _lib
+
+
+class ObjectsAnnotation:
+    """Ground truth of one image (ml.py:15-112): classes (G,) i32, bboxes (G,4) f32 in [0,1]."""
+
+    def __init__(self, path, width, height, classes, bboxes, difficults=None, areas=None, crowdeds=None):
+        assert len(classes) == len(bboxes)
+        assert difficults is None or len(classes) == len(difficults)
+        self.path = pathlib.Path(path)
+        self.width = width
+        self.height = height
+        self.classes = np.asarray(classes, dtype=np.int32)
+        self.bboxes = np.asarray(bboxes, dtype=np.float32).reshape((len(self.classes), 4))
+        self.difficults = (np.asarray(difficults, dtype=bool) if difficults is not None
+                           else np.zeros(len(self.classes), dtype=bool))
+        self.areas = np.asarray(areas, dtype=np.float32) if areas is not None else None
+        self.crowdeds = np.asarray(crowdeds, dtype=bool) if crowdeds is not None else None
+        assert self.width >= 1 and self.height >= 1
+        assert (self.bboxes >= 0).all() and (self.bboxes <= 1).all()
+        assert (self.bboxes[:, :2] < self.bboxes[:, 2:]).all()
+        assert self.difficults.shape == (self.num_objects,)
+
+    @property
+    def num_objects(self):
+        return len(self.classes)
+
+    @property
+    def real_bboxes(self):
+        """Pixel boxes: round-half-even of the f64 product (ml.py:62-65)."""
+        return np.round(self.bboxes * [self.width, self.height, self.width, self.height]).astype(np.int32)
+
+
+class ObjectsPrediction:
+    """Detections of one image (ml.py:115-197)."""
+
+    def __init__(self, classes, confs, bboxes):
+        self.classes = np.asarray(classes)
+        self.confs = np.asarray(confs)
+        self.bboxes = np.asarray(bboxes)
+        assert self.classes.shape == (self.num_objects,)
+        assert self.confs.shape == (self.num_objects,)
+        assert self.bboxes.shape == (self.num_objects, 4)
+
+    @property
+    def num_objects(self):
+        return len(self.classes)
+
+    def get_real_bboxes(self, width, height):
+        return np.round(self.bboxes * [width, height, width, height]).astype(np.int32)  # ml.py:184-186
+
+    def __repr__(self):
+        return (f'{type(self).__module__}.{type(self).__name__}(classes={self.classes!r}, '
+                f'confs={self.confs!r}, bboxes={self.bboxes!r})')
+
+
+def bboxes_center(bboxes):
+    assert bboxes.shape[-1] == 4
+    return (bboxes[..., 2:] + bboxes[..., :2]) / 2
+
+
+def bboxes_size(bboxes):
+    assert bboxes.shape[-1] == 4
+    return bboxes[..., 2:] - bboxes[..., :2]
+
+
+def bboxes_area(bboxes):
+    return bboxes_size(bboxes).prod(axis=-1)
+
+
+def compute_iou(bboxes_a, bboxes_b):
+    """ml.py:502-519 -> (len(a), len(b)) fp32.  Inputs are converted to fp32 (the detection path's
+    dtype); NumPy in -> NumPy out, CUDA tensors in -> CUDA tensor out."""
+    is_np = not isinstance(bboxes_a, torch.Tensor)
+    dev = _dev.device(None if is_np or not bboxes_a.is_cuda else bboxes_a.device)
+    a = _dev.to_device(bboxes_a, torch.float32, dev)
+    b = _dev.to_device(bboxes_b, torch.float32, dev)
+    assert a.shape[0] > 0 and b.shape[0] > 0
+    assert a.shape == (len(a), 4) and b.shape == (len(b), 4)
+    out = torch.empty((len(a), len(b)), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call('odk_compute_iou', a.data_ptr(), len(a), b.data_ptr(), len(b), out.data_ptr(), _dev.stream_ptr(dev))
+    return out.cpu().numpy() if is_np else out
+
+
+def non_maximum_suppression(boxes, scores, top_k=200, iou_threshold=0.45):
+    """ml.py:589-625 -> indices of the kept boxes in descending-score order (int64).
+    fp32 arithmetic (inputs converted); equal scores are ordered higher-index-first
+    (``argsort(kind='stable')[::-1]``, SURVEY A-6)."""
+    is_np = not isinstance(boxes, torch.Tensor)
+    dev = _dev.device(None if is_np or not boxes.is_cuda else boxes.device)
+    b = _dev.to_device(boxes, torch.float32, dev)
+    s = _dev.to_device(scores, torch.float32, dev)
+    assert len(b) == len(s)
+    assert b.shape == (len(s), 4)
+    n, cap = len(s), max(int(top_k), 2)
+    out = torch.empty((cap,), dtype=torch.int32, device=dev)
+    cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
+    ws_bytes = _lib.load().odk_nms_workspace_bytes(1, max(n, 1), 1, int(top_k))
+    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call('odk_nms', b.data_ptr(), s.data_ptr(), n, int(top_k), float(iou_threshold), 1, out.data_ptr(),
+                  cnt.data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
+    k = int(cnt.item())
+    res = out[:k].to(torch.int64)
+    return res.cpu().numpy() if is_np else res

@@ -1,0 +1,311 @@
+"""``PriorBoxes`` — drop-in mirror of pytoolkit/pytoolkit/dl/od_pb.py for the detection hot path.
+
+Same constructor, ``from_dict``/``to_dict``, ``encode_truth``, ``_assign_boxes``, ``encode_locs`` and
+``decode_locs`` signatures, argument meaning, output layouts and error behaviour as the reference
+class (od_pb.py:13-363); the arithmetic runs in libodk's sm_100a kernels.  Anchor tables are built
+on the host exactly as ``_create_pb`` does (od_pb.py:125-184) because the kernels compare against
+them bit for bit, then uploaded once per device.
+
+Out of scope here: ``fit`` (offline KMeans), ``check_prior_boxes``, the Keras
+``loss*`` / ``metrics`` graph functions.
+
+Besides the reference's host-array API there is a batched device API (``encode_truth_batch``,
+``decode_score``, ``decode_nms``) that takes / returns torch CUDA tensors and never synchronises.
+"""
+import ctypes
+import threading
+
+import numpy as np
+import torch
+
+from . import _dev, _lib
+
+_VAR_LOC = 0.10  # od_pb.py:10
+
+
+class PriorBoxes:
+    """Anchor ("prior box") set + target encoding / prediction decoding (od_pb.py:13)."""
+
+    def __init__(self, input_size, map_sizes, num_classes):
+        self.input_size = tuple(input_size)
+        self.map_sizes = np.array(sorted(map_sizes)[::-1])  # od_pb.py:20
+        self.num_classes = num_classes
+        self.pb_size_patterns = np.empty((0,))
+        self.pb_grid = np.empty((0,))
+        self.pb_locs = np.empty((0,))
+        self.pb_info_indices = np.empty((0,))
+        self.pb_centers = np.empty((0,))
+        self.pb_sizes = np.empty((0,))
+        self.pb_mask = np.empty((0,))
+        self.pb_info = []
+        assert np.array(self.input_size).shape == (2,)
+        assert len(self.map_sizes.shape) == 1 and len(self.map_sizes) >= 1
+        assert self.num_classes >= 1
+        self._handles = {}  # device index -> odk_anchors*
+        self._lock = threading.Lock()
+
+    # ------------------------------------------------------------------ persistence (od_pb.py:44-60)
+    def to_dict(self):
+        return {'map_sizes': self.map_sizes, 'pb_size_patterns': self.pb_size_patterns}
+
+    def from_dict(self, data: dict):
+        try:
+            self.map_sizes = np.array(data['map_sizes'])
+            self.pb_size_patterns = np.array(data['pb_size_patterns'])
+        except KeyError as e:
+            raise ValueError(f'PriorBoxes load error: data={data}') from e
+        self._create_pb()
+
+    # ------------------------------------------------------------------ tables (od_pb.py:125-198)
+    def _create_pb(self):
+        """Host-side table construction; every rounding step follows od_pb.py:133-177 (f32 linspace,
+        f64 offsets added in place into f32 arrays, closed-interval validity test)."""
+        self._release()
+        inv_px = 1 / np.array(self.input_size)
+        n_pat = len(self.pb_size_patterns)
+        parts = {k: [] for k in ('grid', 'locs', 'centers', 'sizes', 'mask', 'info')}
+        self.pb_info = []
+        for map_size in self.map_sizes:
+            cell = 1.0 / map_size
+            ticks = np.linspace(0.5 * cell, 1 - 0.5 * cell, map_size, dtype=np.float32)
+            xs, ys = np.meshgrid(ticks, ticks)
+            xy = np.concatenate((xs.reshape(-1, 1), ys.reshape(-1, 1)), axis=1)
+            centre4 = np.tile(xy, (1, 2))
+            grid = np.copy(centre4)
+            grid[:, :2] -= cell / 2
+            grid[:, 2:] += cell / 2 + inv_px
+            for pattern in self.pb_size_patterns:
+                size = cell * pattern
+                box = np.copy(centre4)
+                box[:, :2] -= size / 2
+                box[:, 2:] += size / 2 + inv_px
+                clipped = np.clip(box, 0, 1)
+                cc = (clipped[:, :2] + clipped[:, 2:]) / 2
+                inside = np.all((grid[:, :2] <= cc) & (cc <= grid[:, 2:]), axis=-1)  # math.between
+                parts['grid'].append(grid)
+                parts['locs'].append(box)
+                parts['centers'].append(centre4[:, :2])
+                parts['sizes'].append(np.tile(size, (len(box), 1)))
+                parts['mask'].append(inside)
+                parts['info'].append(np.full(len(box), len(self.pb_info), dtype=np.int64))
+                self.pb_info.append({
+                    'map_size': map_size,
+                    'size': np.sqrt(size.prod()),
+                    'aspect_ratio': size[0] / size[1],
+                    'count': len(box),
+                })
+        self.pb_grid = np.concatenate(parts['grid'])
+        self.pb_locs = np.concatenate(parts['locs'])
+        self.pb_info_indices = np.concatenate(parts['info'])
+        self.pb_centers = np.concatenate(parts['centers'])
+        self.pb_sizes = np.concatenate(parts['sizes'])
+        self.pb_mask = np.concatenate(parts['mask'])
+        assert len(self.pb_info) == len(self.map_sizes) * n_pat
+        self._check_state()
+
+    def _check_state(self):
+        n = len(self.pb_locs)
+        assert self.pb_locs.shape == (n, 4), f'shape error: {self.pb_locs.shape}'
+        assert self.pb_info_indices.shape == (n,), f'shape error: {self.pb_info_indices.shape}'
+        assert self.pb_centers.shape == (n, 2), f'shape error: {self.pb_centers.shape}'
+        assert self.pb_sizes.shape == (n, 2), f'shape error: {self.pb_sizes.shape}'
+        assert self.pb_mask.shape == (n,), f'shape error: {self.pb_mask.shape}'
+        ct = np.mean([self.pb_locs[:, 2:], self.pb_locs[:, :2]], axis=0)
+        assert ((self.pb_grid[:, :2] <= ct) & (ct < self.pb_grid[:, 2:])).all()  # math.in_range
+
+    def __len__(self):
+        return len(self.pb_locs)
+
+    # ------------------------------------------------------------------ device handle
+    def _handle(self, dev: torch.device):
+        """odk_anchors* for ``dev`` (uploaded on first use; od_pb tables are immutable after _create_pb)."""
+        key = dev.index if dev.index is not None else torch.cuda.current_device()
+        with self._lock:
+            h = self._handles.get(key)
+            if h is None:
+                if len(self.pb_locs) == 0:
+                    raise RuntimeError('PriorBoxes has no tables yet: call from_dict() first')
+                maps = np.ascontiguousarray(self.map_sizes, dtype=np.int32)
+                locs = np.ascontiguousarray(self.pb_locs, dtype=np.float32)
+                grid = np.ascontiguousarray(self.pb_grid, dtype=np.float32)
+                sizes = np.ascontiguousarray(self.pb_sizes, dtype=np.float64)
+                mask = np.ascontiguousarray(self.pb_mask, dtype=np.uint8)
+                out = ctypes.c_void_p()
+                with torch.cuda.device(key):
+                    _lib.call('odk_anchors_create', ctypes.byref(out), len(locs), int(self.num_classes), len(maps),
+                              maps.ctypes.data, len(self.pb_size_patterns), locs.ctypes.data, grid.ctypes.data,
+                              sizes.ctypes.data, mask.ctypes.data)
+                h = out.value
+                self._handles[key] = h
+        return h
+
+    def _release(self):
+        for key, h in list(getattr(self, '_handles', {}).items()):
+            try:
+                with torch.cuda.device(key):
+                    _lib.load().odk_anchors_destroy(h)
+            except Exception:  # noqa: BLE001 - interpreter shutdown
+                pass
+        self._handles = {}
+
+    def __del__(self):
+        self._release()
+
+    # ------------------------------------------------------------------ encode / decode (od_pb.py:212-222)
+    def encode_locs(self, bbox, pb_ix):
+        """od_pb.py:212-214: (bbox - pb_locs[pb_ix]) / tile(pb_sizes[pb_ix], 2) / 0.10 -> float64.
+        ``pb_ix`` may be an int, an index array or a boolean mask, as in the reference."""
+        dev = _dev.device()
+        ix = np.arange(len(self.pb_locs))[pb_ix]
+        scalar = np.ndim(ix) == 0
+        ix = np.atleast_1d(ix).astype(np.int32)
+        boxes = np.ascontiguousarray(np.broadcast_to(np.asarray(bbox, dtype=np.float32), (len(ix), 4)))
+        out = torch.empty((len(ix), 4), dtype=torch.float64, device=dev)
+        d_boxes = _dev.to_device(boxes, torch.float32, dev)
+        d_ix = _dev.to_device(ix, torch.int32, dev)
+        with torch.cuda.device(dev):
+            _lib.call('odk_encode_locs', self._handle(dev), len(ix), d_boxes.data_ptr(), d_ix.data_ptr(), out.data_ptr(),
+                      _dev.stream_ptr(dev))
+        res = out.cpu().numpy()
+        return res[0] if scalar else res
+
+    def decode_locs(self, pred, xp=None):
+        """od_pb.py:216-222 evaluated as the fp32 Keras Lambda (od_net.py:189):
+        clip(pred * float32(0.10*tile(pb_sizes,2)) + pb_locs, 0, 1).  NumPy in -> NumPy fp32 out,
+        torch CUDA tensor in -> torch tensor out (no sync).  ``xp`` is accepted for signature
+        compatibility and ignored (the reference's xp=np path computes the same expression in fp64)."""
+        del xp
+        is_np = not isinstance(pred, torch.Tensor)
+        dev = _dev.device(None if is_np or not pred.is_cuda else pred.device)
+        t = _dev.to_device(pred, torch.float32, dev)
+        if t.shape[-1] != 4 or t.shape[-2] != len(self.pb_locs):
+            raise ValueError(f'decode_locs: expected (..., {len(self.pb_locs)}, 4), got {tuple(t.shape)}')
+        out = torch.empty_like(t)
+        with torch.cuda.device(dev):
+            _lib.call('odk_decode_locs', self._handle(dev), t.numel() // 4, t.data_ptr(), out.data_ptr(), _dev.stream_ptr(dev))
+        return out.cpu().numpy() if is_np else out
+
+    # ------------------------------------------------------------------ training targets (od_pb.py:299-363)
+    @staticmethod
+    def _pad_gt(y_gt):
+        counts = np.array([len(y.classes) for y in y_gt], dtype=np.int32)
+        gmax = max(1, int(counts.max()) if len(counts) else 1)
+        boxes = np.zeros((len(y_gt), gmax, 4), dtype=np.float32)
+        classes = np.zeros((len(y_gt), gmax), dtype=np.int32)
+        for i, y in enumerate(y_gt):
+            g = counts[i]
+            if g:
+                boxes[i, :g] = np.asarray(y.bboxes, dtype=np.float32).reshape(g, 4)
+                classes[i, :g] = np.asarray(y.classes, dtype=np.int32)
+        return boxes, classes, counts
+
+    def encode_truth_batch(self, gt_boxes, gt_classes, gt_count, y_true=None, want_valids=False):
+        """Batched device entry (no host sync): padded GT (B,Gmax,4) f32 / (B,Gmax) i32 / (B,) i32 on the
+        GPU (host arrays are uploaded) -> dict of CUDA tensors: ``y_true`` (B,N,3+C+4) f32,
+        ``pb_indices``/``gt_indices`` (B,Gmax) i64 (-1 padded), ``status`` (B,) i32 (odk.h ODK_IMG_*),
+        optionally ``pb_valids`` (B,N) bool."""
+        dev = _dev.device(gt_boxes.device if isinstance(gt_boxes, torch.Tensor) and gt_boxes.is_cuda else None)
+        boxes = _dev.to_device(gt_boxes, torch.float32, dev)
+        classes = _dev.to_device(gt_classes, torch.int32, dev)
+        count = _dev.to_device(gt_count, torch.int32, dev)
+        b, gmax = boxes.shape[0], boxes.shape[1]
+        assert boxes.shape == (b, gmax, 4) and classes.shape == (b, gmax) and count.shape == (b,)
+        n, w = len(self.pb_locs), 3 + self.num_classes + 4
+        if y_true is None:
+            y_true = torch.empty((b, n, w), dtype=torch.float32, device=dev)
+        assert y_true.shape == (b, n, w) and y_true.dtype == torch.float32 and y_true.is_contiguous()
+        pb_idx = torch.empty((b, gmax), dtype=torch.int64, device=dev)
+        gt_idx = torch.empty((b, gmax), dtype=torch.int64, device=dev)
+        status = torch.empty((b,), dtype=torch.int32, device=dev)
+        valids = torch.empty((b, n), dtype=torch.uint8, device=dev) if want_valids else None
+        with torch.cuda.device(dev):
+            _lib.call('odk_assign_encode', self._handle(dev), b, boxes.data_ptr(), classes.data_ptr(), count.data_ptr(), gmax,
+                      y_true.data_ptr(), pb_idx.data_ptr(), gt_idx.data_ptr(), _dev.ptr(valids), status.data_ptr(),
+                      _dev.stream_ptr(dev))
+        res = {'y_true': y_true, 'pb_indices': pb_idx, 'gt_indices': gt_idx, 'status': status}
+        if want_valids:
+            res['pb_valids'] = valids.view(torch.bool)
+        return res
+
+    @staticmethod
+    def _raise_for_status(status, y_gt):
+        """Maps device status words to the reference's AssertionErrors (od_pb.py:304,332,338)."""
+        for i, s in enumerate(status):
+            if s == 1:
+                raise AssertionError(f'Encode error: image {i}: {_centres(y_gt[i].bboxes)}')
+            if s == 2:
+                raise AssertionError(f'class id out of range [0, num_classes) in image {i}')
+            if s != 0:
+                raise AssertionError(f'bad ground-truth count in image {i}')
+
+    def encode_truth(self, y_gt):
+        """od_pb.py:299-313: list of annotations (``.classes``, ``.bboxes``) -> np.float32
+        (len(y_gt), N, 3+C+4) = [mask, weight, obj, onehot, locs]."""
+        if len(y_gt) == 0:
+            return np.zeros((0, len(self.pb_locs), 3 + self.num_classes + 4), dtype=np.float32)
+        boxes, classes, counts = self._pad_gt(y_gt)
+        res = self.encode_truth_batch(boxes, classes, counts)
+        self._raise_for_status(res['status'].cpu().numpy(), y_gt)
+        return res['y_true'].cpu().numpy()
+
+    def _assign_boxes(self, bboxes):
+        """od_pb.py:315-363 -> (pb_indices i64 ascending, assigned gt index i64, pb_valids bool (N,))."""
+        bboxes = np.asarray(bboxes, dtype=np.float32).reshape(-1, 4)
+        g = len(bboxes)
+        boxes = np.zeros((1, max(1, g), 4), dtype=np.float32)
+        boxes[0, :g] = bboxes
+        res = self.encode_truth_batch(boxes, np.zeros((1, max(1, g)), np.int32), np.array([g], np.int32), want_valids=True)
+        status = res['status'].cpu().numpy()
+        if status[0] != 0:
+            raise AssertionError(f'Encode error: {_centres(bboxes)}')
+        return (res['pb_indices'][0, :g].cpu().numpy(), res['gt_indices'][0, :g].cpu().numpy(),
+                res['pb_valids'][0].cpu().numpy())
+
+    # ------------------------------------------------------------------ prediction side (od_net.py:172-192)
+    def _head_inputs(self, objs, clfs, locs):
+        dev = _dev.device(objs.device if isinstance(objs, torch.Tensor) and objs.is_cuda else None)
+        objs = _dev.to_device(objs, torch.float32, dev)
+        clfs = _dev.to_device(clfs, torch.float32, dev)
+        locs = _dev.to_device(locs, torch.float32, dev)
+        b, n, c = clfs.shape[0], len(self.pb_locs), self.num_classes
+        if clfs.shape != (b, n, c) or locs.shape != (b, n, 4) or objs.numel() != b * n:
+            raise ValueError(f'head outputs must be objs (B,{n},1), clfs (B,{n},{c}), locs (B,{n},4); got '
+                             f'{tuple(objs.shape)}, {tuple(clfs.shape)}, {tuple(locs.shape)}')
+        return dev, b, objs, clfs, locs
+
+    def decode_score(self, objs, clfs, locs):
+        """ChannelArgMax/ChannelMax/_objconf/decode_locs in one pass (od_net.py:186-189):
+        -> classes (B,N) i32, objconfs (B,N) f32, boxes (B,N,4) f32 CUDA tensors."""
+        dev, b, objs, clfs, locs = self._head_inputs(objs, clfs, locs)
+        n = len(self.pb_locs)
+        classes = torch.empty((b, n), dtype=torch.int32, device=dev)
+        confs = torch.empty((b, n), dtype=torch.float32, device=dev)
+        boxes = torch.empty((b, n, 4), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.call('odk_decode_score', self._handle(dev), b, objs.data_ptr(), clfs.data_ptr(), locs.data_ptr(),
+                      classes.data_ptr(), confs.data_ptr(), boxes.data_ptr(), _dev.stream_ptr(dev))
+        return classes, confs, boxes
+
+    def decode_nms(self, objs, clfs, locs, top_k=200, conf_threshold=0.01, nms_threshold=0.45, iou_ge=True,
+                   out=None, return_index=False):
+        """The whole prediction tail (od_net.py:186-190) fused: head outputs -> (B, top_k, 6)
+        [class, conf, x1, y1, x2, y2], zero padded (layers.py:963-970).  ``out`` may be a slice of a
+        larger (e.g. all-gather) buffer."""
+        dev, b, objs, clfs, locs = self._head_inputs(objs, clfs, locs)
+        n, c = len(self.pb_locs), self.num_classes
+        if out is None:
+            out = torch.empty((b, top_k, 6), dtype=torch.float32, device=dev)
+        assert out.shape == (b, top_k, 6) and out.dtype == torch.float32 and out.is_contiguous()
+        kept = torch.empty((b, top_k), dtype=torch.int32, device=dev)
+        ws_bytes = _lib.load().odk_nms_workspace_bytes(b, n, c, top_k)
+        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _lib.call('odk_decode_nms', self._handle(dev), b, objs.data_ptr(), clfs.data_ptr(), locs.data_ptr(),
+                      float(conf_threshold), float(nms_threshold), int(top_k), 1 if iou_ge else 0, out.data_ptr(),
+                      kept.data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
+        return (out, kept) if return_index else out
+
+
+def _centres(bboxes):
+    b = np.asarray(bboxes, dtype=np.float32).reshape(-1, 4)
+    return (b[:, 2:] + b[:, :2]) / 2

@@ -1,0 +1,105 @@
+"""Host-side logic that runs without a GPU: table construction, the C-ABI surface, loud failure."""
+import ctypes
+import hashlib
+import pathlib
+import re
+
+import numpy as np
+import pytest
+
+import object_detector_b200 as odk
+from object_detector_b200 import _lib, build
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+TABLES = ['pb_grid', 'pb_locs', 'pb_centers', 'pb_sizes', 'pb_mask', 'pb_info_indices']
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.fixture(scope='module', autouse=True)
+def built():
+    build.build()
+
+
+def header_symbols():
+    text = (ROOT / 'include' / 'odk.h').read_text()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    return sorted(set(re.findall(r'\b(odk_[a-z0-9_]+)\s*\(', text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = ctypes.CDLL(str(_lib.LIB_PATH))
+    names = header_symbols()
+    assert len(names) >= 18
+    for name in names:
+        assert hasattr(lib, name), f'{name} declared in include/odk.h but not exported by libodk.so'
+
+
+def test_ctypes_table_covers_header():
+    assert sorted(_lib.SIGNATURES) == header_symbols()
+    assert _lib.version().startswith('odk ')
+
+
+def test_workspace_size_query_needs_no_gpu():
+    lib = _lib.load()
+    small = lib.odk_nms_workspace_bytes(1, 16800, 20, 200)
+    big = lib.odk_nms_workspace_bytes(64, 16800, 20, 200)
+    assert 0 < small < big and big % 256 == 0
+    assert lib.odk_nms_workspace_bytes(0, 16800, 20, 200) == 0
+
+
+@pytest.mark.parametrize('name', ['voc320', 'voc640', 'tiny128', 'stress1120'])
+def test_product_tables_bit_identical_to_reference(golden, prior_boxes, name):
+    g, pb = golden['anchors'], prior_boxes(name)
+    for k in TABLES:
+        a = getattr(pb, k)
+        assert str(a.dtype) == str(g[f'{name}/{k}/dtype']), (name, k)
+        assert sha(a) == str(g[f'{name}/{k}/sha256']), (name, k)
+
+
+def test_from_dict_errors_like_reference():
+    pb = odk.PriorBoxes((320, 320), [40, 20, 10], 20)
+    with pytest.raises(ValueError, match='PriorBoxes load error'):
+        pb.from_dict({'map_sizes': [40]})  # od_pb.py:57-58
+    assert pb.map_sizes.tolist() == [40]
+    with pytest.raises(AssertionError):
+        odk.PriorBoxes((320,), [40], 20)
+
+
+def test_load_voc_and_version_migration():
+    od = odk.ObjectDetector.load_voc((640, 640))
+    assert len(od.pb) == 16800 and int(od.pb.pb_mask.sum()) == 12512
+    old = {'version': '0.0.1', 'input_size': [320, 320], 'map_sizes': [40, 20, 10], 'num_classes': 20,
+           'pb': {'pb_size_patterns': odk.od._VOC_JSON_DATA['pb_size_patterns']}}
+    od1 = odk.ObjectDetector.load_from_dict(old)  # od.py:70-71
+    assert len(od1.pb) == 16800
+    assert set(od1.to_dict()) >= {'version', 'input_size', 'map_sizes', 'num_classes', 'pb_size_patterns'}
+
+
+def test_annotation_types_validate_like_reference():
+    a = odk.ml.ObjectsAnnotation('.', 768, 614, [1], np.array([[203, 255, 601, 355]]) / [768, 614, 768, 614])
+    assert a.real_bboxes.tolist() == [[203, 255, 601, 355]]  # data_voc_test.py:21
+    with pytest.raises(AssertionError):
+        odk.ml.ObjectsAnnotation('.', 10, 10, [0], [[0.5, 0.5, 0.4, 0.6]])
+    p = odk.ml.ObjectsPrediction([0], [0.9], [[0.5, 0.25, 0.75, 1.0]])
+    assert p.get_real_bboxes(5, 10).tolist() == [[2, 2, 4, 10]]
+    e = odk.ml.ObjectsAnnotation('.', 10, 10, [], [])
+    assert e.bboxes.shape == (0, 4)
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip('GPU present')
+    pb = odk.ObjectDetector.load_voc().pb
+    with pytest.raises(RuntimeError, match='no CPU path'):
+        pb.encode_truth([odk.ml.ObjectsAnnotation('.', 10, 10, [0], [[0.1, 0.1, 0.5, 0.5]])])
+    with pytest.raises(RuntimeError, match='no CPU path'):
+        odk.ml.non_maximum_suppression(np.zeros((1, 4), np.float32), np.zeros((1,), np.float32))
+
+
+def test_product_never_imports_oracle():
+    for p in (ROOT / 'object_detector_b200').rglob('*.py'):
+        assert 'oracle' not in re.sub(r'#.*', '', p.read_text()), f'{p} mentions the oracle'

@@ -1,0 +1,157 @@
+"""The CPU oracle (oracle/restated.py) against the golden vectors generated from the unmodified
+reference (oracle/gen_golden.py) and the reference's own known-answer tests."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from oracle import ref_loader, restated as R
+
+TABLES = ['pb_grid', 'pb_locs', 'pb_centers', 'pb_sizes', 'pb_mask', 'pb_info_indices']
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.mark.parametrize('name', ['voc320', 'voc640', 'tiny128', 'stress1120'])
+def test_anchor_tables_match_reference(golden, oracle_tables, name):
+    g, t = golden['anchors'], oracle_tables(name)
+    for k in TABLES:
+        a = getattr(t, k)
+        assert str(a.dtype) == str(g[f'{name}/{k}/dtype'])
+        assert tuple(a.shape) == tuple(g[f'{name}/{k}/shape'])
+        assert sha(a) == str(g[f'{name}/{k}/sha256']), (name, k)
+    assert int(t.pb_mask.sum()) == int(g[f'{name}/valid'])
+
+
+def test_anchor_counts_from_survey(oracle_tables):
+    # N = 16 800, valid 12 546 @320 / 12 512 @640; stress N = 205 800, valid 189 682
+    assert (len(oracle_tables('voc320')), int(oracle_tables('voc320').pb_mask.sum())) == (16800, 12546)
+    assert (len(oracle_tables('voc640')), int(oracle_tables('voc640').pb_mask.sum())) == (16800, 12512)
+    assert (len(oracle_tables('stress1120')), int(oracle_tables('stress1120').pb_mask.sum())) == (205800, 189682)
+    assert 0 < oracle_tables("voc320").pb_grid[0, 0] < 2e-10  # 1.8626e-10, not 0
+
+
+def _assign_cases(g):
+    return sorted({k.split('/')[0] for k in g.files})
+
+
+def test_assign_and_encode_match_reference(golden, oracle_tables):
+    g = golden['assign']
+    for case in _assign_cases(g):
+        t = oracle_tables(str(g[f'{case}/anchors']))
+        boxes, classes = g[f'{case}/boxes'], g[f'{case}/classes']
+        idx, gts, valid = R.assign_boxes(t, boxes)
+        assert np.array_equal(idx, g[f'{case}/pb_indices']), case
+        assert np.array_equal(gts, g[f'{case}/gt_indices']), case
+        assert np.array_equal(np.packbits(valid), g[f'{case}/pb_valids']), case
+        y = R.encode_truth(t, [(classes, boxes)])[0]
+        assert sha(y) == str(g[f'{case}/y_sha256']), case
+        assert np.array_equal(y[idx], g[f'{case}/y_pos_rows']), case
+    assert np.array_equal(R.encode_truth(oracle_tables('tiny128'), [(g['tiny128_g12/classes'], g['tiny128_g12/boxes'])])[0],
+                          g['tiny128_g12/y_full'])
+
+
+def test_fallback_branch_is_exercised(golden, oracle_tables):
+    """crowded120 has more GTs than its cell neighbourhood has anchors -> the IoU arg-max fallback
+    (od_pb.py:347-352) must have produced some assignments outside the centre cells."""
+    g, t = golden['assign'], oracle_tables('voc640')
+    boxes = g['voc640_crowded120/boxes']
+    idx, gts = g['voc640_crowded120/pb_indices'], g['voc640_crowded120/gt_indices']
+    ctr = R.box_centers(boxes)
+    outside = 0
+    for a, gt in zip(idx, gts):
+        inside = R.half_open_interval(ctr[gt], t.pb_grid[a, :2], t.pb_grid[a, 2:]).all()
+        outside += not inside
+    assert outside > 0
+
+
+def test_iou_kat_and_golden(golden):
+    g = golden['iou_nms_decode']
+    out = R.pairwise_iou(g['iou_kat/a'], g['iou_kat/b'])
+    assert out.shape == (2, 1)
+    assert out[0, 0] == pytest.approx(100 * 100 / (200 * 200 * 2 - 100 * 100))  # ml_test.py:52
+    assert out[1, 0] == 0
+    assert np.array_equal(out, g['iou_kat/out'])
+    out = R.pairwise_iou(g['iou_f32/a'], g['iou_f32/b'])
+    assert out.dtype == np.float32 and np.array_equal(out, g['iou_f32/out'])
+
+
+def test_nms_kat_and_golden(golden):
+    g = golden['iou_nms_decode']
+    # ml_test.py:89-113
+    assert np.array_equal(R.numpy_nms(g['nms_kat/boxes'], g['nms_kat/scores'], 200, 0.45), [5, 3])
+    assert np.array_equal(R.numpy_nms(np.array([[0, 0, 200, 200]]), np.array([0.2]), 200, 0.45), [0])
+    assert R.numpy_nms(np.array([[200, 0, 200, 200]]), np.array([0.1]), 200, 0.45).shape == (0,)
+    for i in range(6):
+        b, s, k = g[f'nms_f32_{i}/boxes'], g[f'nms_f32_{i}/scores'], int(g[f'nms_f32_{i}/top_k'])
+        ref = g[f'nms_f32_{i}/out']
+        assert np.array_equal(R.numpy_nms(b, s, k, 0.45), ref)
+        assert np.array_equal(R.numpy_nms_policy(b, s, k, 0.45), ref)  # distinct scores: policy == reference
+    # the top_k quirk (SURVEY A-7): top_k=1 can return 2
+    assert len(g['nms_f32_4/out']) == 2
+
+
+def test_decode_and_encode_locs_golden(golden, oracle_tables):
+    g = golden['iou_nms_decode']
+    tiny, voc = oracle_tables('tiny128'), oracle_tables('voc640')
+    out = R.decode_locs_f64(tiny, g['decode_tiny/pred'])
+    assert out.dtype == np.float64 and np.array_equal(out, g['decode_tiny/out_f64'])
+    np.testing.assert_allclose(R.decode_locs_f32(tiny, g['decode_tiny/pred']), out, rtol=0, atol=2e-7)
+    pred = np.random.RandomState(int(g['decode_voc640/seed'])).normal(size=(1, len(voc), 4)).astype(np.float32)
+    assert sha(R.decode_locs_f64(voc, pred)) == str(g['decode_voc640/out_f64_sha256'])
+    assert np.array_equal(R.encode_locs(voc, g['encode_locs/box'], g['encode_locs/ix']), g['encode_locs/out'])
+
+
+def test_nms_layer_structure():
+    """layers.py:925-970 restated: per-class NMS, class-order concat, global top-k, zero pad."""
+    boxes = np.array([[0, 0, .5, .5], [0, 0, .5, .52], [.5, .5, 1, 1], [0, 0, .5, .5], [.1, .1, .2, .2]], np.float32)
+    classes = np.array([1, 1, 0, 0, 1])
+    confs = np.array([.9, .8, .7, .6, .005], np.float32)
+    out, idx = R.nms_layer_image(classes, confs, boxes, 2, top_k=4)
+    assert idx.tolist() == [0, 2, 3, -1]  # box 1 suppressed by 0 (same class); 3 kept (other class); 4 below 0.01
+    assert out[:3, 0].tolist() == [1, 0, 0] and np.allclose(out[:3, 1], [.9, .7, .6]) and (out[3] == 0).all()
+
+
+def test_voc_ap_micro_cases():
+    """Hand-computed cases for the chainercv restatement (PARITY UNPINNED: chainercv absent)."""
+    gt = [(100, 100, np.array([0]), np.array([[.1, .1, .5, .5]], np.float32), np.array([False]))]
+    perfect = [(np.array([0]), np.array([.9], np.float32), np.array([[.1, .1, .5, .5]], np.float32))]
+    r = R.voc_evaluate(gt, perfect, 2)
+    assert r['AP'][0] == 1.0 and r['AP_VOC'][0] == pytest.approx(1.0) and np.isnan(r['AP'][1]) and r['mAP'] == 1.0
+    miss = [(np.array([0]), np.array([.9], np.float32), np.array([[.6, .6, .9, .9]], np.float32))]
+    r = R.voc_evaluate(gt, miss, 2)
+    assert r['AP'][0] == 0.0 and r['AP_VOC'][0] == 0.0
+    dup = [(np.array([0, 0]), np.array([.9, .8], np.float32), np.array([[.1, .1, .5, .5], [.1, .1, .5, .5]], np.float32))]
+    r = R.voc_evaluate(gt, dup, 2)  # TP then FP: prec [1, .5], rec [1, 1] -> AP 1 (both metrics)
+    assert r['AP'][0] == 1.0 and r['AP_VOC'][0] == pytest.approx(1.0)
+    fp_first = [(np.array([0, 0]), np.array([.9, .8], np.float32), np.array([[.6, .6, .9, .9], [.1, .1, .5, .5]], np.float32))]
+    r = R.voc_evaluate(gt, fp_first, 2)  # FP then TP: prec [0, .5], rec [0, 1] -> AP .5
+    assert r['AP'][0] == pytest.approx(0.5) and r['AP_VOC'][0] == pytest.approx(0.5)
+    gt_d = [(100, 100, np.array([0, 0]), np.array([[.1, .1, .5, .5], [.6, .6, .9, .9]], np.float32), np.array([True, False]))]
+    r = R.voc_evaluate(gt_d, perfect, 2)  # only match is the difficult GT -> ignored; one non-difficult GT missed
+    assert r['AP'][0] == 0.0
+
+
+def test_pixel_rounding_half_even():
+    assert R.to_pixels(np.array([[0.5, 0.25, 0.75, 1.0]], np.float32), 5, 10).tolist() == [[2, 2, 4, 10]]
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason='reference tree not mounted (GPU box)')
+def test_restatement_against_live_reference(oracle_tables):
+    """Only in the build container: random GT sets through the real reference vs the restatement."""
+    from object_detector_b200 import synth
+    tk = ref_loader.load()
+    pb = tk.dl.od_pb.PriorBoxes((320, 320), [40, 20, 10], 20)
+    pb.from_dict({'map_sizes': [40, 20, 10], 'pb_size_patterns': R.VOC_PATTERNS})
+    t = oracle_tables('voc320')
+    boxes, classes, counts = synth.gt_batch(21, 6, 24, 20)
+    for i in range(6):
+        g = counts[i]
+        for x, y in zip(pb._assign_boxes(boxes[i, :g]), R.assign_boxes(t, boxes[i, :g])):
+            assert np.array_equal(x, y)
+    rng = np.random.RandomState(2)
+    b = synth.gt_boxes(rng, 300, size=(0.05, 0.3))
+    s = rng.permutation(300).astype(np.float32) / 300
+    assert np.array_equal(tk.ml.non_maximum_suppression(b, s, 50, 0.45), R.numpy_nms_policy(b, s, 50, 0.45))
