@@ -141,6 +141,13 @@ int odk_voc_ap(int n_img, int top_k, int num_classes, const float* dets /*[dev n
                int n_gt_total, double* ap_area /*[dev C]*/, double* ap07 /*[dev C]*/,
                void* workspace, size_t workspace_bytes, void* stream);
 
+/* Measurement aid (bench.py): when enabled for the calling host thread every kernel launch of the
+ * library is bracketed by CUDA events on its stream; odk_profile_read synchronises them and returns,
+ * per kernel name, the summed device time and the launch count, then clears the log. */
+int odk_profile_enable(int on);
+int odk_profile_read(char* names /*[host cap*name_stride]*/, int name_stride, float* total_ms /*[host cap]*/,
+                     int32_t* launches /*[host cap]*/, int cap, int32_t* n_out /*[host 1]*/);
+
 #ifdef __cplusplus
 }
 #endif

@@ -24,7 +24,8 @@ def to_device(x, dtype, dev, non_blocking=False) -> torch.Tensor:
     if isinstance(x, torch.Tensor):
         t = x
     else:
-        t = torch.from_numpy(np.ascontiguousarray(x))
+        x = np.ascontiguousarray(x)
+        t = torch.from_numpy(x if x.flags.writeable else x.copy())
     if t.dtype != dtype:
         t = t.to(dtype)
     if t.device != dev:

@@ -39,6 +39,8 @@ SIGNATURES = {
     'odk_voc_ap_workspace_bytes': (c_size_t, [c_int, c_int, c_int, c_int]),
     'odk_voc_ap': (c_int, [c_int, c_int, c_int, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p,
                            c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    'odk_profile_enable': (c_int, [c_int]),
+    'odk_profile_read': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
 }
 
 _lock = threading.Lock()
@@ -81,3 +83,18 @@ def call(name, *args):
 
 def version() -> str:
     return load().odk_version().decode()
+
+
+def profile_enable(on: bool):
+    call('odk_profile_enable', 1 if on else 0)
+
+
+def profile_read(cap=32):
+    """{kernel name: (total device ms, launches)} since profiling was enabled; clears the log."""
+    names = ctypes.create_string_buffer(cap * 64)
+    ms = (ctypes.c_float * cap)()
+    cnt = (ctypes.c_int32 * cap)()
+    n = ctypes.c_int32(0)
+    call('odk_profile_read', ctypes.cast(names, c_void_p), 64, ctypes.cast(ms, c_void_p), ctypes.cast(cnt, c_void_p), cap,
+         ctypes.cast(ctypes.byref(n), c_void_p))
+    return {names.raw[i * 64:(i + 1) * 64].split(b'\0')[0].decode(): (float(ms[i]), int(cnt[i])) for i in range(n.value)}

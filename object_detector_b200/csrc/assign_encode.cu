@@ -311,7 +311,10 @@ int launch_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const 
   if (batch <= 148 * 2) wpb = 1;
   const size_t smem = (size_t)wpb * args.warp_smem_bytes;
   ODK_CUDA(cudaFuncSetAttribute(assign_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  assign_greedy_kernel<<<(batch + wpb - 1) / wpb, wpb * 32, smem, stream>>>(args);
+  {
+    OdkProfileScope prof_("assign_greedy_kernel", stream);
+    assign_greedy_kernel<<<(batch + wpb - 1) / wpb, wpb * 32, smem, stream>>>(args);
+  }
   ODK_LAUNCH_CHECK("assign_greedy_kernel");
   return ODK_OK;
 }
@@ -355,7 +358,10 @@ extern "C" int odk_assign_encode(const odk_anchors* a, int batch, const float* g
   ODK_CUDA(cudaFuncSetAttribute(encode_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   dim3 grid((a->n + kEncodeTile - 1) / kEncodeTile, batch);
   ODK_REQUIRE(batch <= 65535, ODK_ERR_UNSUPPORTED, "assign_encode: batch=%d > 65535", batch);
-  encode_rows_kernel<<<grid, kEncodeTile, smem, stream>>>(e);
+  {
+    OdkProfileScope prof_("encode_rows_kernel", stream);
+    encode_rows_kernel<<<grid, kEncodeTile, smem, stream>>>(e);
+  }
   ODK_LAUNCH_CHECK("encode_rows_kernel");
   return ODK_OK;
 }
@@ -367,8 +373,11 @@ extern "C" int odk_compute_iou(const float* a, int na, const float* b, int nb, f
   const long long total = (long long)na * nb;
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
-  compute_iou_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const float4*>(a), na,
-                                                                                      reinterpret_cast<const float4*>(b), nb, out);
+  {
+    OdkProfileScope prof_("compute_iou_kernel", static_cast<cudaStream_t>(stream));
+    compute_iou_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const float4*>(a), na,
+                                                                                        reinterpret_cast<const float4*>(b), nb, out);
+  }
   ODK_LAUNCH_CHECK("compute_iou_kernel");
   return ODK_OK;
 }
@@ -378,7 +387,10 @@ extern "C" int odk_encode_locs(const odk_anchors* a, int k, const float* boxes, 
   if (k == 0) return ODK_OK;
   ODK_REQUIRE(boxes && ix && out, ODK_ERR_INVALID_ARGUMENT, "encode_locs: null pointer");
   ODK_REQUIRE(((uintptr_t)boxes & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "encode_locs: boxes must be 16-byte aligned");
-  encode_locs_kernel<<<(k + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(odk_view(a), k, reinterpret_cast<const float4*>(boxes), ix, out);
+  {
+    OdkProfileScope prof_("encode_locs_kernel", static_cast<cudaStream_t>(stream));
+    encode_locs_kernel<<<(k + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(odk_view(a), k, reinterpret_cast<const float4*>(boxes), ix, out);
+  }
   ODK_LAUNCH_CHECK("encode_locs_kernel");
   return ODK_OK;
 }

@@ -214,7 +214,10 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   long long grid = (long long)sm_count_cached() * per_sm;
   if (grid > total) grid = total;
   if (grid < 1) grid = 1;
-  kern<<<(unsigned)grid, TILE, smem, stream>>>(args);
+  {
+    OdkProfileScope prof_("decode_score_kernel", stream);
+    kern<<<(unsigned)grid, TILE, smem, stream>>>(args);
+  }
   ODK_LAUNCH_CHECK("decode_score_kernel");
   return ODK_OK;
 }
@@ -245,8 +248,11 @@ int odk_launch_decode_locs(const odk_anchors* a, long long rows, const float* pr
   const long long cap = (long long)sm_count_cached() * 8;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  decode_locs_kernel<<<(unsigned)blocks, 256, 0, stream>>>(odk_view(a), rows, reinterpret_cast<const float4*>(pred),
-                                                            reinterpret_cast<float4*>(out));
+  {
+    OdkProfileScope prof_("decode_locs_kernel", stream);
+    decode_locs_kernel<<<(unsigned)blocks, 256, 0, stream>>>(odk_view(a), rows, reinterpret_cast<const float4*>(pred),
+                                                              reinterpret_cast<float4*>(out));
+  }
   ODK_LAUNCH_CHECK("decode_locs_kernel");
   return ODK_OK;
 }

@@ -337,23 +337,35 @@ static int nms_run(const NmsWorkspace& w, int batch, int n, int num_classes, con
   ODK_CUDA(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortChunk * 8));
   ODK_CUDA(cudaFuncSetAttribute(nms_sweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   ODK_CUDA(cudaFuncSetAttribute(nms_sweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  sort_candidates_kernel<<<batch, kSortThreads, kSortChunk * 8, stream>>>(w.cand_keys, w.cand_count, w.cap, num_classes, w.seg_off);
+  {
+    OdkProfileScope prof_("sort_candidates_kernel", stream);
+    sort_candidates_kernel<<<batch, kSortThreads, kSortChunk * 8, stream>>>(w.cand_keys, w.cand_count, w.cap, num_classes, w.seg_off);
+  }
   ODK_LAUNCH_CHECK("sort_candidates_kernel");
   const int limit = iou_ge ? w.limit : top_k;
   dim3 grid((num_classes + kSweepWarps - 1) / kSweepWarps, batch);
   const size_t sweep_smem = (size_t)kSweepWarps * w.limit * 20;
   if (iou_ge)
-    nms_sweep_kernel<true><<<grid, kSweepWarps * 32, sweep_smem, stream>>>(w.cand_keys, w.cap, w.seg_off, num_classes, n, boxes, iou_thr,
-                                                                           limit, w.limit, 1, w.kept_keys, w.kept_count);
+    {
+      OdkProfileScope prof_("nms_sweep_kernel", stream);
+      nms_sweep_kernel<true><<<grid, kSweepWarps * 32, sweep_smem, stream>>>(w.cand_keys, w.cap, w.seg_off, num_classes, n, boxes, iou_thr,
+                                                                             limit, w.limit, 1, w.kept_keys, w.kept_count);
+    }
   else
-    nms_sweep_kernel<false><<<grid, kSweepWarps * 32, sweep_smem, stream>>>(w.cand_keys, w.cap, w.seg_off, num_classes, n, boxes, iou_thr,
-                                                                            limit, w.limit, 0, w.kept_keys, w.kept_count);
+    {
+      OdkProfileScope prof_("nms_sweep_kernel", stream);
+      nms_sweep_kernel<false><<<grid, kSweepWarps * 32, sweep_smem, stream>>>(w.cand_keys, w.cap, w.seg_off, num_classes, n, boxes, iou_thr,
+                                                                              limit, w.limit, 0, w.kept_keys, w.kept_count);
+    }
   ODK_LAUNCH_CHECK("nms_sweep_kernel");
   if (out != nullptr) {
     int pad = odk_next_pow2(num_classes * w.limit);
     if (pad < 2) pad = 2;
-    topk_merge_kernel<<<batch, 256, (size_t)pad * 8, stream>>>(w.kept_keys, w.kept_count, num_classes, w.limit, n, boxes, top_k, out,
-                                                               kept_index);
+    {
+      OdkProfileScope prof_("topk_merge_kernel", stream);
+      topk_merge_kernel<<<batch, 256, (size_t)pad * 8, stream>>>(w.kept_keys, w.kept_count, num_classes, w.limit, n, boxes, top_k, out,
+                                                                 kept_index);
+    }
     ODK_LAUNCH_CHECK("topk_merge_kernel");
   }
   return ODK_OK;
@@ -378,7 +390,10 @@ extern "C" int odk_nms_layer(int batch, int n, int num_classes, const int32_t* c
   NmsWorkspace w = nms_layout(workspace, batch, n, num_classes, top_k);
   ODK_CUDA(cudaMemsetAsync(w.cand_count, 0, sizeof(int) * (size_t)batch, stream));
   dim3 grid((n + 255) / 256, batch);
-  collect_candidates_kernel<<<grid, 256, 0, stream>>>(n, num_classes, classes, confs, conf_thr, 0, w.cand_keys, w.cand_count, w.cap);
+  {
+    OdkProfileScope prof_("collect_candidates_kernel", stream);
+    collect_candidates_kernel<<<grid, 256, 0, stream>>>(n, num_classes, classes, confs, conf_thr, 0, w.cand_keys, w.cand_count, w.cap);
+  }
   ODK_LAUNCH_CHECK("collect_candidates_kernel");
   return nms_run(w, batch, n, num_classes, reinterpret_cast<const float4*>(boxes), iou_thr, top_k, iou_ge, out, kept_index, stream);
 }
@@ -413,10 +428,16 @@ extern "C" int odk_nms(const float* boxes, const float* scores, int n, int top_k
   NmsWorkspace w = nms_layout(workspace, 1, n, 1, top_k);
   ODK_CUDA(cudaMemsetAsync(w.cand_count, 0, sizeof(int), stream));
   dim3 grid((n + 255) / 256, 1);
-  collect_candidates_kernel<<<grid, 256, 0, stream>>>(n, 1, nullptr, scores, 0.f, 1, w.cand_keys, w.cand_count, w.cap);
+  {
+    OdkProfileScope prof_("collect_candidates_kernel", stream);
+    collect_candidates_kernel<<<grid, 256, 0, stream>>>(n, 1, nullptr, scores, 0.f, 1, w.cand_keys, w.cand_count, w.cap);
+  }
   ODK_LAUNCH_CHECK("collect_candidates_kernel");
   if (int rc = nms_run(w, 1, n, 1, reinterpret_cast<const float4*>(boxes), iou_thr, top_k, iou_ge, nullptr, nullptr, stream)) return rc;
-  export_kept_kernel<<<1, 256, 0, stream>>>(w.kept_keys, w.kept_count, out_index, out_count);
+  {
+    OdkProfileScope prof_("export_kept_kernel", stream);
+    export_kept_kernel<<<1, 256, 0, stream>>>(w.kept_keys, w.kept_count, out_index, out_count);
+  }
   ODK_LAUNCH_CHECK("export_kept_kernel");
   return ODK_OK;
 }

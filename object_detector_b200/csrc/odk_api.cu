@@ -22,6 +22,62 @@ int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, 
                             unsigned long long* cand_keys, int* cand_count, int cand_cap, cudaStream_t stream);
 int odk_launch_decode_locs(const odk_anchors* a, long long rows, const float* pred, float* out, cudaStream_t stream);
 
+// ---- per-launch event timing (used by bench.py for the roofline line) -------------------------------
+#include <string>
+#include <vector>
+namespace {
+struct ProfEntry { const char* name; cudaEvent_t start, stop; };
+thread_local bool g_prof_on = false;
+thread_local std::vector<ProfEntry> g_prof;
+}  // namespace
+
+OdkProfileScope::OdkProfileScope(const char* name, cudaStream_t stream) : slot_(-1), stream_(stream) {
+  if (!g_prof_on) return;
+  ProfEntry e;
+  e.name = name;
+  if (cudaEventCreate(&e.start) != cudaSuccess || cudaEventCreate(&e.stop) != cudaSuccess) return;
+  cudaEventRecord(e.start, stream);
+  g_prof.push_back(e);
+  slot_ = (int)g_prof.size() - 1;
+}
+OdkProfileScope::~OdkProfileScope() {
+  if (slot_ >= 0) cudaEventRecord(g_prof[slot_].stop, stream_);
+}
+
+extern "C" int odk_profile_enable(int on) {
+  g_prof_on = on != 0;
+  return ODK_OK;
+}
+
+// Synchronises the recorded events, aggregates by kernel name and clears the log.
+extern "C" int odk_profile_read(char* names, int name_stride, float* total_ms, int32_t* launches, int cap, int32_t* n_out) {
+  ODK_REQUIRE(names && total_ms && launches && n_out && name_stride >= 8 && cap >= 1, ODK_ERR_INVALID_ARGUMENT, "profile_read: bad arguments");
+  std::vector<std::string> keys;
+  int n = 0;
+  for (auto& e : g_prof) {
+    float ms = 0.f;
+    cudaEventSynchronize(e.stop);
+    cudaEventElapsedTime(&ms, e.start, e.stop);
+    cudaEventDestroy(e.start);
+    cudaEventDestroy(e.stop);
+    int k = -1;
+    for (int i = 0; i < n; ++i) if (keys[i] == e.name) { k = i; break; }
+    if (k < 0) {
+      if (n >= cap) continue;
+      k = n++;
+      keys.push_back(e.name);
+      total_ms[k] = 0.f;
+      launches[k] = 0;
+      snprintf(names + (size_t)k * name_stride, name_stride, "%s", e.name);
+    }
+    total_ms[k] += ms;
+    launches[k] += 1;
+  }
+  g_prof.clear();
+  *n_out = n;
+  return ODK_OK;
+}
+
 extern "C" const char* odk_version(void) { return "odk 0.1.0 (sm_100a)"; }
 extern "C" const char* odk_last_error(void) { return g_last_error; }
 

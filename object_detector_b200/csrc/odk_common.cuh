@@ -60,6 +60,14 @@ int odk_set_error(int code, const char* fmt, ...);
     return odk_set_error(ODK_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e_)); } while (0)
 
 __host__ __device__ static inline size_t odk_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+// Optional per-launch CUDA-event timing (odk_profile_enable / odk_profile_read); a no-op unless enabled.
+struct OdkProfileScope {
+  OdkProfileScope(const char* name, cudaStream_t stream);
+  ~OdkProfileScope();
+  int slot_;
+  cudaStream_t stream_;
+};
+
 static inline int odk_next_pow2(int x) { int p = 1; while (p < x) p <<= 1; return p; }
 
 // ---- exact fp32 box arithmetic (ml.py:485-519, 605-618) ------------------------------------------

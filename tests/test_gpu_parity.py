@@ -231,7 +231,7 @@ def test_nms_layer_vs_oracle(prior_boxes, oracle_tables, clustered):
         ro, rk = R.nms_layer_image(classes[b], confs[b], boxes[b], 20)
         assert np.array_equal(kept[b], rk), b   # kept-index sets AND order: bit-exact
         assert np.array_equal(out[b], ro), b    # rows [class, conf, box]: bit-exact fp32
-    assert layer.compute_output_shape([(2, len(pb))]) == (2, 200, 6)
+    assert layer.compute_output_shape([(2, len(pb)), (2, len(pb)), (2, len(pb), 4)]) == (2, 200, 6)
 
 
 @pytest.mark.parametrize('name,batch,top_k', [('voc640', 3, 200), ('tiny128', 4, 200), ('tiny128', 2, 5), ('voc320', 1, 200)])
