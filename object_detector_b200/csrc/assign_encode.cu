@@ -48,41 +48,92 @@ __device__ __forceinline__ double encode_cost(const float4 box, const float4 loc
   return __dadd_rn(__dadd_rn(__dadd_rn(d0, d1), d2), d3);
 }
 
-__global__ void __launch_bounds__(128) assign_greedy_kernel(const AssignArgs p) {
+constexpr int kGreedyThreads = 128;
+constexpr int kTopCand = 4;  // best candidates remembered per GT by the parallel phase
+
+// Probes the <= 9 cells around floor(c*m) of every map with the exact in_range test (od_pb.py:336) and
+// calls f(anchor) for every anchor (cell x pattern) whose cell contains the centre and whose pb_mask
+// is set — i.e. the reference's `pb_mask2` before the "assignable" filter.  Warp-collective.
+template <typename F>
+__device__ __forceinline__ int for_each_cell_candidate(const AnchorView& av, float cx, float cy, int lane, F f) {
+  int total = 0;
+  const int n_probe = av.n_maps * 9;
+  for (int t0 = 0; t0 < n_probe; t0 += 32) {
+    const int t = t0 + lane;
+    int cell_anchor = -1, m = 1;
+    if (t < n_probe) {
+      const int mi = t / 9, cell = t - mi * 9;
+      m = av.map_size[mi];
+      const int ix = (int)floorf(cx * (float)m) + (cell % 3) - 1;
+      const int iy = (int)floorf(cy * (float)m) + (cell / 3) - 1;
+      if (ix >= 0 && iy >= 0 && ix < m && iy < m) {
+        const int a = av.map_off[mi] + iy * m + ix;  // pattern 0 of that cell; pb_grid is pattern-independent
+        const float4 gr = __ldg(av.grid + a);
+        if (gr.x <= cx && cx < gr.z && gr.y <= cy && cy < gr.w) cell_anchor = a;
+      }
+    }
+    unsigned hits = __ballot_sync(0xffffffffu, cell_anchor >= 0);
+    // candidates of this round: (hit cell, pattern) pairs, spread over the lanes
+    const int n_hit = __popc(hits);
+    const int n_cand = n_hit * av.n_patterns;
+    for (int c0 = 0; c0 < n_cand; c0 += 32) {
+      const int c = c0 + lane;
+      const bool in_range = c < n_cand;
+      const int h = in_range ? c / av.n_patterns : 0;
+      const int pat = in_range ? c - h * av.n_patterns : 0;
+      const int src = __fns(hits, 0, h + 1) & 31;  // lane holding the h-th hit cell (n_hit >= 1 here)
+      const int base = __shfl_sync(0xffffffffu, cell_anchor, src);
+      const int mm = __shfl_sync(0xffffffffu, m, src);
+      const int a = base + pat * mm * mm;
+      const bool ok = in_range && av.mask[a] != 0;  // od_pb.py:337
+      if (ok) f(a);
+      total += __popc(__ballot_sync(0xffffffffu, ok));
+    }
+  }
+  return total;
+}
+
+__device__ __forceinline__ bool cand_less(double c0, int a0, double c1, int a1) {
+  return c0 < c1 || (c0 == c1 && a0 < a1);  // argmin -> first minimum = lowest anchor index (od_pb.py:343)
+}
+
+__global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const AssignArgs p) {
   extern __shared__ __align__(16) unsigned char greedy_smem[];
   const int warp = threadIdx.x >> 5;
   const int lane = (int)odk_lane();
-  const int b = blockIdx.x * (blockDim.x >> 5) + warp;
-  if (b >= p.batch) return;
-  unsigned char* base = greedy_smem + (size_t)warp * p.warp_smem_bytes;
-  float4* gbox = reinterpret_cast<float4*>(base);
-  float* garea = reinterpret_cast<float*>(base + (size_t)p.gmax * 16);
-  int* order = reinterpret_cast<int*>(base + (size_t)p.gmax * 20);
-  int* pick = reinterpret_cast<int*>(base + (size_t)p.gmax * 24);
-  unsigned* taken = reinterpret_cast<unsigned*>(base + (size_t)p.gmax * 28);
+  const int b = blockIdx.x;
+  float4* gbox = reinterpret_cast<float4*>(greedy_smem);
+  float* garea = reinterpret_cast<float*>(greedy_smem + (size_t)p.gmax * 16);
+  int* order = reinterpret_cast<int*>(greedy_smem + (size_t)p.gmax * 20);
+  int* pick = reinterpret_cast<int*>(greedy_smem + (size_t)p.gmax * 24);
+  int* ncand = reinterpret_cast<int*>(greedy_smem + (size_t)p.gmax * 28);
+  int* cand = reinterpret_cast<int*>(greedy_smem + (size_t)p.gmax * 32);  // [gmax][kTopCand]
+  unsigned* taken = reinterpret_cast<unsigned*>(greedy_smem + (size_t)p.gmax * (32 + 4 * kTopCand));
+  __shared__ int s_err;
 
   long long* out_pb = p.pb_indices + (size_t)b * p.gmax;
   long long* out_gt = p.gt_indices + (size_t)b * p.gmax;
   const int g_count = p.gt_count[b];
-  int err = ODK_IMG_OK;
-  if (g_count < 0 || g_count > p.gmax) err = ODK_IMG_BAD_COUNT;
-  const int G = err ? 0 : g_count;
+  const bool bad_count = g_count < 0 || g_count > p.gmax;
+  const int G = bad_count ? 0 : g_count;
+  if (threadIdx.x == 0) s_err = bad_count ? ODK_IMG_BAD_COUNT : ODK_IMG_OK;
+  __syncthreads();
 
-  for (int g = lane; g < G; g += 32) {
+  for (int g = threadIdx.x; g < G; g += kGreedyThreads) {
     const float4 bx = p.gt_boxes[(size_t)b * p.gmax + g];
     gbox[g] = bx;
     garea[g] = odk_area(bx);
     if (p.gt_classes != nullptr) {
       const int c = p.gt_classes[(size_t)b * p.gmax + g];
-      if (c < 0 || c >= p.av.num_classes) err = ODK_IMG_BAD_CLASS;  // od_pb.py:304
+      if (c < 0 || c >= p.av.num_classes) atomicMax(&s_err, ODK_IMG_BAD_CLASS);  // od_pb.py:304
     }
   }
-  for (int w = lane; w < p.bitmap_words; w += 32) taken[w] = 0u;
-  err = __reduce_max_sync(0xffffffffu, err);
-  __syncwarp();
-  if (!err) {
-    // ascending-area rank, ties by index
-    for (int g = lane; g < G; g += 32) {
+  for (int w = threadIdx.x; w < p.bitmap_words; w += kGreedyThreads) taken[w] = 0u;
+  __syncthreads();
+
+  if (s_err == ODK_IMG_OK) {
+    // ascending-area rank, ties by index (od_pb.py:327)
+    for (int g = threadIdx.x; g < G; g += kGreedyThreads) {
       const float ag = garea[g];
       int r = 0;
       for (int j = 0; j < G; ++j) {
@@ -91,60 +142,103 @@ __global__ void __launch_bounds__(128) assign_greedy_kernel(const AssignArgs p) 
       }
       order[r] = g;
     }
-    __syncwarp();
-    const int per_map = 9 * p.av.n_patterns;
-    const int n_probe = p.av.n_maps * per_map;
-    for (int r = 0; r < G && !err; ++r) {
-      const int g = order[r];
+    // ---- phase A (parallel over GTs, one warp each): the kTopCand cheapest in-cell anchors, ignoring "taken"
+    for (int g = warp; g < G; g += kGreedyThreads / 32) {
       const float4 box = gbox[g];
       const float cx = __fmul_rn(__fadd_rn(box.z, box.x), 0.5f);  // ml.py:485-488
       const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
-      if (r >= p.av.n_valid) { err = ODK_IMG_ENCODE_ERROR; break; }  // od_pb.py:331-332: no free valid anchor left
-      double best_cost = DBL_MAX;
-      int best_a = INT_MAX;
-      bool any_cell = false;
-      for (int t = lane; t < n_probe; t += 32) {
-        const int mi = t / per_map;
-        const int rem = t - mi * per_map;
-        const int cell = rem / p.av.n_patterns;
-        const int pat = rem - cell * p.av.n_patterns;
-        const int m = p.av.map_size[mi];
-        const int ix = (int)floorf(cx * (float)m) + (cell % 3) - 1;
-        const int iy = (int)floorf(cy * (float)m) + (cell / 3) - 1;
-        if (ix < 0 || iy < 0 || ix >= m || iy >= m) continue;
-        const int a = p.av.map_off[mi] + pat * m * m + iy * m + ix;
-        const float4 gr = __ldg(p.av.grid + a);
-        // math.in_range: lo <= x < hi on both axes (od_pb.py:336), AND pb_mask (:337)
-        if (!(gr.x <= cx && cx < gr.z && gr.y <= cy && cy < gr.w) || !p.av.mask[a]) continue;
-        any_cell = true;
-        if ((taken[a >> 5] >> (a & 31)) & 1u) continue;  // od_pb.py:339
-        const double cost = encode_cost(box, __ldg(p.av.locs + a), p.av.sizes[a]);
-        if (cost < best_cost || (cost == best_cost && a < best_a)) { best_cost = cost; best_a = a; }
-      }
-      if (!__any_sync(0xffffffffu, any_cell)) { err = ODK_IMG_ENCODE_ERROR; break; }  // od_pb.py:338
+      double bc[kTopCand];
+      int ba[kTopCand];
 #pragma unroll
-      for (int d = 16; d > 0; d >>= 1) {
-        const double oc = __shfl_xor_sync(0xffffffffu, best_cost, d);
-        const int oa = __shfl_xor_sync(0xffffffffu, best_a, d);
-        if (oc < best_cost || (oc == best_cost && oa < best_a)) { best_cost = oc; best_a = oa; }
+      for (int k = 0; k < kTopCand; ++k) { bc[k] = DBL_MAX; ba[k] = INT_MAX; }
+      const int total = for_each_cell_candidate(p.av, cx, cy, lane, [&](int a) {
+        double c = encode_cost(box, __ldg(p.av.locs + a), p.av.sizes[a]);
+        int ca = a;
+#pragma unroll
+        for (int k = 0; k < kTopCand; ++k) {  // insertion into the lane's sorted best list
+          if (cand_less(c, ca, bc[k], ba[k])) {
+            const double tc = bc[k]; const int ta = ba[k];
+            bc[k] = c; ba[k] = ca; c = tc; ca = ta;
+          }
+        }
+      });
+      // warp merge: kTopCand rounds of arg-min over the lanes' list heads
+#pragma unroll
+      for (int k = 0; k < kTopCand; ++k) {
+        double mc = bc[0];
+        int ma = ba[0];
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+          const double oc = __shfl_xor_sync(0xffffffffu, mc, d);
+          const int oa = __shfl_xor_sync(0xffffffffu, ma, d);
+          if (cand_less(oc, oa, mc, ma)) { mc = oc; ma = oa; }
+        }
+        if (lane == 0) cand[g * kTopCand + k] = (ma == INT_MAX) ? -1 : ma;
+        if (ma != INT_MAX && ba[0] == ma) {  // the winning lane pops its head
+#pragma unroll
+          for (int q = 0; q + 1 < kTopCand; ++q) { bc[q] = bc[q + 1]; ba[q] = ba[q + 1]; }
+          bc[kTopCand - 1] = DBL_MAX; ba[kTopCand - 1] = INT_MAX;
+        }
       }
-      if (best_a == INT_MAX) {
+      if (lane == 0) ncand[g] = total;
+    }
+  }
+  __syncthreads();
+  if (warp != 0) return;
+
+  // ---- phase B (warp 0, sequential over GTs in area order): first free anchor of each GT's list
+  int err = s_err;
+  if (!err) {
+    for (int r = 0; r < G; ++r) {
+      const int g = order[r];
+      if (r >= p.av.n_valid) { err = ODK_IMG_ENCODE_ERROR; break; }  // od_pb.py:331-332
+      const int nc = ncand[g];
+      if (nc == 0) { err = ODK_IMG_ENCODE_ERROR; break; }             // od_pb.py:338
+      int best_a = -1;
+#pragma unroll
+      for (int k = 0; k < kTopCand; ++k) {
+        const int a = cand[g * kTopCand + k];
+        if (best_a < 0 && a >= 0 && !((taken[a >> 5] >> (a & 31)) & 1u)) best_a = a;
+      }
+      const float4 box = gbox[g];
+      if (best_a < 0 && nc > kTopCand) {
+        // the remembered candidates are all taken: exact re-evaluation over the free in-cell anchors
+        const float cx = __fmul_rn(__fadd_rn(box.z, box.x), 0.5f);
+        const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
+        double mc = DBL_MAX;
+        int ma = INT_MAX;
+        for_each_cell_candidate(p.av, cx, cy, lane, [&](int a) {
+          if ((taken[a >> 5] >> (a & 31)) & 1u) return;  // od_pb.py:339
+          const double c = encode_cost(box, __ldg(p.av.locs + a), p.av.sizes[a]);
+          if (cand_less(c, a, mc, ma)) { mc = c; ma = a; }
+        });
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+          const double oc = __shfl_xor_sync(0xffffffffu, mc, d);
+          const int oa = __shfl_xor_sync(0xffffffffu, ma, d);
+          if (cand_less(oc, oa, mc, ma)) { mc = oc; ma = oa; }
+        }
+        if (ma != INT_MAX) best_a = ma;
+      }
+      if (best_a < 0) {
         // fallback: arg-max IoU over the free valid anchors, first maximum wins (od_pb.py:347-352)
         float best_v = -1.0f;
+        int fa = INT_MAX;
         const float ga = garea[g];
         for (int a = lane; a < p.av.n; a += 32) {
           if (!p.av.mask[a] || ((taken[a >> 5] >> (a & 31)) & 1u)) continue;
           const float4 lc = __ldg(p.av.locs + a);
           const float v = odk_iou_value(box, ga, lc, odk_area(lc));
-          if (v > best_v) { best_v = v; best_a = a; }
+          if (v > best_v) { best_v = v; fa = a; }
         }
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) {
           const float ov = __shfl_xor_sync(0xffffffffu, best_v, d);
-          const int oa = __shfl_xor_sync(0xffffffffu, best_a, d);
-          if (ov > best_v || (ov == best_v && oa < best_a)) { best_v = ov; best_a = oa; }
+          const int oa = __shfl_xor_sync(0xffffffffu, fa, d);
+          if (ov > best_v || (ov == best_v && oa < fa)) { best_v = ov; fa = oa; }
         }
-        if (best_a == INT_MAX) { err = ODK_IMG_ENCODE_ERROR; break; }
+        if (fa == INT_MAX) { err = ODK_IMG_ENCODE_ERROR; break; }
+        best_a = fa;
       }
       if (lane == 0) {
         taken[best_a >> 5] |= 1u << (best_a & 31);
@@ -197,6 +291,10 @@ __global__ void __launch_bounds__(kEncodeTile) encode_rows_kernel(const EncodeAr
   float* s_garea = reinterpret_cast<float*>(enc_smem + rows_bytes + (size_t)p.gmax * 16);
   __shared__ unsigned char s_assigned[kEncodeTile];
 
+  int* s_list = reinterpret_cast<int*>(enc_smem + rows_bytes + (size_t)p.gmax * 20);  // [gmax] GTs that can reach this tile
+  __shared__ float s_red[6][kEncodeTile / 32];
+  __shared__ int s_nlist;
+
   const bool ok = p.status[b] == ODK_IMG_OK;
   const int G = ok ? p.gt_count[b] : 0;
   for (int g = tid; g < G; g += kEncodeTile) {
@@ -210,20 +308,60 @@ __global__ void __launch_bounds__(kEncodeTile) encode_rows_kernel(const EncodeAr
     for (int i = tid; i < n4; i += kEncodeTile) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   s_assigned[tid] = 0;
+  if (tid == 0) s_nlist = 0;
+
+  // this thread's anchor, and the tile's bounding box / area range over its VALID anchors
+  const int a = a0 + tid;
+  const bool active = tid < rows && ok && G > 0 && p.av.mask[a];
+  float4 ab = make_float4(0.f, 0.f, 0.f, 0.f);
+  float aa = 0.f;
+  float r0 = FLT_MAX, r1 = FLT_MAX, r2 = -FLT_MAX, r3 = -FLT_MAX, r4 = FLT_MAX, r5 = -FLT_MAX;
+  if (active) {
+    ab = __ldg(p.av.locs + a);
+    aa = odk_area(ab);
+    r0 = ab.x; r1 = ab.y; r2 = ab.z; r3 = ab.w; r4 = aa; r5 = aa;
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    r0 = fminf(r0, __shfl_xor_sync(0xffffffffu, r0, d));
+    r1 = fminf(r1, __shfl_xor_sync(0xffffffffu, r1, d));
+    r2 = fmaxf(r2, __shfl_xor_sync(0xffffffffu, r2, d));
+    r3 = fmaxf(r3, __shfl_xor_sync(0xffffffffu, r3, d));
+    r4 = fminf(r4, __shfl_xor_sync(0xffffffffu, r4, d));
+    r5 = fmaxf(r5, __shfl_xor_sync(0xffffffffu, r5, d));
+  }
+  if ((tid & 31) == 0) {
+    const int w = tid >> 5;
+    s_red[0][w] = r0; s_red[1][w] = r1; s_red[2][w] = r2; s_red[3][w] = r3; s_red[4][w] = r4; s_red[5][w] = r5;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int w = 0; w < kEncodeTile / 32; ++w) {
+    r0 = fminf(r0, s_red[0][w]); r1 = fminf(r1, s_red[1][w]); r2 = fmaxf(r2, s_red[2][w]);
+    r3 = fmaxf(r3, s_red[3][w]); r4 = fminf(r4, s_red[4][w]); r5 = fmaxf(r5, s_red[5][w]);
+  }
+  // Conservative cull: fl(IoU) >= 0.5 needs a positive-extent overlap with some anchor of the tile
+  // (=> with the tile's bounding box) and min(Ag,Aa)/max(Ag,Aa) >= IoU, i.e. Ag within [0.5,2]x the
+  // anchor area; 0.49 / 2.05 leave ~2% slack against the few-ulp rounding of the fp32 areas.
+  for (int g = tid; g < G; g += kEncodeTile) {
+    const float4 gb = s_gbox[g];
+    const float ga = s_garea[g];
+    const bool reach = gb.x < r2 && gb.z > r0 && gb.y < r3 && gb.w > r1 && ga >= 0.49f * r4 && ga <= 2.05f * r5;
+    if (reach) s_list[atomicAdd(&s_nlist, 1)] = g;
+  }
   __syncthreads();
 
   const float w0 = (float)(1.0 / (double)max(1, G));  // od_pb.py:306
   bool valid = true;
-  const int a = a0 + tid;
-  if (tid < rows && ok) {
-    if (G > 0 && p.av.mask[a]) {
-      const float4 ab = __ldg(p.av.locs + a);
-      const float aa = odk_area(ab);
-      for (int g = 0; g < G; ++g) {
-        if (odk_iou_passes<true>(s_gbox[g], s_garea[g], ab, aa, 0.5f)) { valid = false; break; }  // od_pb.py:355
-      }
+  {
+    const int nl = s_nlist;  // block-uniform trip count; the loop body has no divergent exits
+    bool ignored = false;
+    for (int k = 0; k < nl; ++k) {
+      const int g = s_list[k];
+      ignored |= odk_iou_passes<true>(s_gbox[g], s_garea[g], ab, aa, 0.5f);  // od_pb.py:355
     }
-    if (valid) s_rows[tid * W] = w0;
+    valid = !(active && ignored);
+    if (tid < rows && ok && valid) s_rows[tid * W] = w0;
   }
   __syncthreads();
   // positives (one per GT): od_pb.py:307-311
@@ -302,18 +440,13 @@ int launch_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const 
   args.gt_indices = reinterpret_cast<long long*>(gt_indices);
   args.status = status;
   args.bitmap_words = (a->n + 31) / 32;
-  args.warp_smem_bytes = (int)odk_align_up((size_t)gmax * 28 + (size_t)args.bitmap_words * 4, 16);
-  ODK_REQUIRE(args.warp_smem_bytes <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign: N=%d / Gmax=%d need %d bytes of shared memory per image",
-              a->n, gmax, args.warp_smem_bytes);
-  int wpb = (200 * 1024) / args.warp_smem_bytes;
-  wpb = wpb > 4 ? 4 : wpb;
-  // few images: spread them over more CTAs (one warp each) so more SMs work
-  if (batch <= 148 * 2) wpb = 1;
-  const size_t smem = (size_t)wpb * args.warp_smem_bytes;
+  args.warp_smem_bytes = 0;
+  const size_t smem = odk_align_up((size_t)gmax * (32 + 4 * kTopCand) + (size_t)args.bitmap_words * 4, 16);
+  ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign: N=%d / Gmax=%d need %zu bytes of shared memory per image", a->n, gmax, smem);
   ODK_CUDA(cudaFuncSetAttribute(assign_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   {
     OdkProfileScope prof_("assign_greedy_kernel", stream);
-    assign_greedy_kernel<<<(batch + wpb - 1) / wpb, wpb * 32, smem, stream>>>(args);
+    assign_greedy_kernel<<<batch, kGreedyThreads, smem, stream>>>(args);
   }
   ODK_LAUNCH_CHECK("assign_greedy_kernel");
   return ODK_OK;
@@ -353,7 +486,7 @@ extern "C" int odk_assign_encode(const odk_anchors* a, int batch, const float* g
   e.gt_indices = reinterpret_cast<const long long*>(gt_indices);
   e.status = status; e.y_true = y_true; e.pb_valids = pb_valids;
   const int W = 3 + a->num_classes + 4;
-  const size_t smem = odk_align_up((size_t)kEncodeTile * W * 4, 16) + (size_t)gmax * 20;
+  const size_t smem = odk_align_up((size_t)kEncodeTile * W * 4, 16) + (size_t)gmax * 24;
   ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign_encode: C=%d / Gmax=%d need %zu bytes of shared memory", a->num_classes, gmax, smem);
   ODK_CUDA(cudaFuncSetAttribute(encode_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   dim3 grid((a->n + kEncodeTile - 1) / kEncodeTile, batch);

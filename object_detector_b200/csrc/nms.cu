@@ -164,10 +164,12 @@ __global__ void __launch_bounds__(kSweepWarps * 32) nms_sweep_kernel(const unsig
     const float w = __fsub_rn(box.z, box.x), h = __fsub_rn(box.w, box.y);
     const float area = __fmul_rn(w, h);
     bool alive = have && !(skip_empty && (w <= 0.0f || h <= 0.0f));  // ml.py:610-611
-    if (alive) {
-      for (int k = 0; k < nkept; ++k) {
-        if (odk_iou_passes<GE>(box, area, kbox[k], karea[k], iou_thr)) { alive = false; break; }
-      }
+    // every lane walks the whole kept list (warp-uniform trip count, no divergent exits)
+    if (__any_sync(0xffffffffu, alive)) {
+      bool hit_kept = false;
+#pragma unroll 4
+      for (int k = 0; k < nkept; ++k) hit_kept |= odk_iou_passes<GE>(box, area, kbox[k], karea[k], iou_thr);
+      alive = alive && !hit_kept;
     }
     const unsigned am = __ballot_sync(0xffffffffu, alive);
     if (am == 0) continue;

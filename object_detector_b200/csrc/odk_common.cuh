@@ -99,15 +99,21 @@ __device__ __forceinline__ float odk_iou_value(const float4 a, float area_a, con
 template <bool GE>
 __device__ __forceinline__ bool odk_iou_passes(const float4 a, float area_a, const float4 b, float area_b,
                                                float thr) {
+  // Written without early returns so that callers' loops stay warp-convergent (a divergent `return`
+  // inside a loop body serialises the lanes for the rest of the loop on sm_70+).
   bool hit;
   const float inter = odk_inter(a, b, hit);
-  if (!hit) return GE ? (0.0f >= thr) : (0.0f > thr);
   const float uni = __fsub_rn(__fadd_rn(area_a, area_b), inter);
   const float p = thr * uni;
-  if (inter > p * 1.00001f && uni > 0.0f) return true;
-  if (inter < p * 0.99999f && uni > 0.0f) return false;
-  const float q = __fdiv_rn(inter, uni);
-  return GE ? (q >= thr) : (q > thr);
+  const bool sure_yes = (inter > p * 1.00001f) && (uni > 0.0f);
+  const bool sure_no = (inter < p * 0.99999f) && (uni > 0.0f);
+  bool res = sure_yes;
+  if (hit && !sure_yes && !sure_no) {  // rare: inside the guard band (or degenerate union)
+    const float q = __fdiv_rn(inter, uni);
+    res = GE ? (q >= thr) : (q > thr);
+  }
+  const bool miss = GE ? (0.0f >= thr) : (0.0f > thr);  // IoU is exactly 0 without overlap
+  return hit ? res : miss;
 }
 
 // ---- 64-bit sort keys of the NMS pipeline -------------------------------------------------------------
