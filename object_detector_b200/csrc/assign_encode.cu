@@ -35,7 +35,7 @@ struct AssignArgs {
   long long* pb_indices;
   long long* gt_indices;
   int32_t* status;
-  int warp_smem_bytes;
+  int list_len;  // ranked candidates remembered per GT
   int bitmap_words;
 };
 
@@ -48,12 +48,14 @@ __device__ __forceinline__ double encode_cost(const float4 box, const float4 loc
   return __dadd_rn(__dadd_rn(__dadd_rn(d0, d1), d2), d3);
 }
 
-constexpr int kGreedyThreads = 128;
-constexpr int kTopCand = 4;  // best candidates remembered per GT by the parallel phase
+constexpr int kGreedyThreads = 256;
+constexpr int kGreedyWarps = kGreedyThreads / 32;
+constexpr int kScratch = 256;  // in-cell candidates ranked per GT (VOC layout: at most 96)
 
 // Probes the <= 9 cells around floor(c*m) of every map with the exact in_range test (od_pb.py:336) and
-// calls f(anchor) for every anchor (cell x pattern) whose cell contains the centre and whose pb_mask
-// is set — i.e. the reference's `pb_mask2` before the "assignable" filter.  Warp-collective.
+// calls f(anchor, ok) CONVERGENTLY (all 32 lanes, so f may use warp collectives) where ok marks the
+// anchors (cell x pattern) whose cell contains the centre and whose pb_mask is set — the reference's
+// `pb_mask2` before the "assignable" filter.  Returns the number of such anchors.
 template <typename F>
 __device__ __forceinline__ int for_each_cell_candidate(const AnchorView& av, float cx, float cy, int lane, F f) {
   int total = 0;
@@ -72,10 +74,8 @@ __device__ __forceinline__ int for_each_cell_candidate(const AnchorView& av, flo
         if (gr.x <= cx && cx < gr.z && gr.y <= cy && cy < gr.w) cell_anchor = a;
       }
     }
-    unsigned hits = __ballot_sync(0xffffffffu, cell_anchor >= 0);
-    // candidates of this round: (hit cell, pattern) pairs, spread over the lanes
-    const int n_hit = __popc(hits);
-    const int n_cand = n_hit * av.n_patterns;
+    const unsigned hits = __ballot_sync(0xffffffffu, cell_anchor >= 0);
+    const int n_cand = __popc(hits) * av.n_patterns;  // (hit cell, pattern) pairs, spread over the lanes
     for (int c0 = 0; c0 < n_cand; c0 += 32) {
       const int c = c0 + lane;
       const bool in_range = c < n_cand;
@@ -86,7 +86,7 @@ __device__ __forceinline__ int for_each_cell_candidate(const AnchorView& av, flo
       const int mm = __shfl_sync(0xffffffffu, m, src);
       const int a = base + pat * mm * mm;
       const bool ok = in_range && av.mask[a] != 0;  // od_pb.py:337
-      if (ok) f(a);
+      f(a, ok);
       total += __popc(__ballot_sync(0xffffffffu, ok));
     }
   }
@@ -102,13 +102,18 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   const int warp = threadIdx.x >> 5;
   const int lane = (int)odk_lane();
   const int b = blockIdx.x;
-  float4* gbox = reinterpret_cast<float4*>(greedy_smem);
-  float* garea = reinterpret_cast<float*>(greedy_smem + (size_t)p.gmax * 16);
-  int* order = reinterpret_cast<int*>(greedy_smem + (size_t)p.gmax * 20);
-  int* pick = reinterpret_cast<int*>(greedy_smem + (size_t)p.gmax * 24);
-  int* ncand = reinterpret_cast<int*>(greedy_smem + (size_t)p.gmax * 28);
-  int* cand = reinterpret_cast<int*>(greedy_smem + (size_t)p.gmax * 32);  // [gmax][kTopCand]
-  unsigned* taken = reinterpret_cast<unsigned*>(greedy_smem + (size_t)p.gmax * (32 + 4 * kTopCand));
+  const int L = p.list_len;
+  unsigned char* sp = greedy_smem;
+  float4* gbox = reinterpret_cast<float4*>(sp);            sp += (size_t)p.gmax * 16;
+  double* s_cost = reinterpret_cast<double*>(sp);          sp += (size_t)kGreedyWarps * kScratch * 8;
+  int* s_idx = reinterpret_cast<int*>(sp);                 sp += (size_t)kGreedyWarps * kScratch * 4;
+  float* garea = reinterpret_cast<float*>(sp);             sp += (size_t)p.gmax * 4;
+  int* order = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
+  int* pick = reinterpret_cast<int*>(sp);                  sp += (size_t)p.gmax * 4;
+  int* ncand = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;  // in-cell valid anchors of the GT
+  int* nlist = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;  // entries stored in its ranked list
+  int* list = reinterpret_cast<int*>(sp);                  sp += (size_t)p.gmax * L * 4;
+  unsigned* taken = reinterpret_cast<unsigned*>(sp);
   __shared__ int s_err;
 
   long long* out_pb = p.pb_indices + (size_t)b * p.gmax;
@@ -142,45 +147,40 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
       }
       order[r] = g;
     }
-    // ---- phase A (parallel over GTs, one warp each): the kTopCand cheapest in-cell anchors, ignoring "taken"
-    for (int g = warp; g < G; g += kGreedyThreads / 32) {
+    // ---- phase A (parallel over GTs, one warp each): every in-cell anchor of the GT ranked by
+    //      (fp64 cost, index), ignoring "taken"; the first L ranks are kept.
+    double* wc = s_cost + (size_t)warp * kScratch;
+    int* wi = s_idx + (size_t)warp * kScratch;
+    for (int g = warp; g < G; g += kGreedyWarps) {
       const float4 box = gbox[g];
       const float cx = __fmul_rn(__fadd_rn(box.z, box.x), 0.5f);  // ml.py:485-488
       const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
-      double bc[kTopCand];
-      int ba[kTopCand];
-#pragma unroll
-      for (int k = 0; k < kTopCand; ++k) { bc[k] = DBL_MAX; ba[k] = INT_MAX; }
-      const int total = for_each_cell_candidate(p.av, cx, cy, lane, [&](int a) {
-        double c = encode_cost(box, __ldg(p.av.locs + a), p.av.sizes[a]);
-        int ca = a;
-#pragma unroll
-        for (int k = 0; k < kTopCand; ++k) {  // insertion into the lane's sorted best list
-          if (cand_less(c, ca, bc[k], ba[k])) {
-            const double tc = bc[k]; const int ta = ba[k];
-            bc[k] = c; ba[k] = ca; c = tc; ca = ta;
+      int filled = 0;
+      const int total = for_each_cell_candidate(p.av, cx, cy, lane, [&](int a, bool ok) {
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (ok) {
+          const int pos = filled + __popc(m & ((1u << lane) - 1u));
+          if (pos < kScratch) {
+            wc[pos] = encode_cost(box, __ldg(p.av.locs + a), p.av.sizes[a]);
+            wi[pos] = a;
           }
         }
+        filled += __popc(m);
       });
-      // warp merge: kTopCand rounds of arg-min over the lanes' list heads
-#pragma unroll
-      for (int k = 0; k < kTopCand; ++k) {
-        double mc = bc[0];
-        int ma = ba[0];
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) {
-          const double oc = __shfl_xor_sync(0xffffffffu, mc, d);
-          const int oa = __shfl_xor_sync(0xffffffffu, ma, d);
-          if (cand_less(oc, oa, mc, ma)) { mc = oc; ma = oa; }
+      __syncwarp();
+      int stored = 0;
+      if (total <= kScratch) {  // ranks are global only if every candidate made it into the scratch
+        for (int e = lane; e < total; e += 32) {
+          const double ce = wc[e];
+          const int ae = wi[e];
+          int r = 0;
+          for (int q = 0; q < total; ++q) r += cand_less(wc[q], wi[q], ce, ae);
+          if (r < L) list[(size_t)g * L + r] = ae;
         }
-        if (lane == 0) cand[g * kTopCand + k] = (ma == INT_MAX) ? -1 : ma;
-        if (ma != INT_MAX && ba[0] == ma) {  // the winning lane pops its head
-#pragma unroll
-          for (int q = 0; q + 1 < kTopCand; ++q) { bc[q] = bc[q + 1]; ba[q] = ba[q + 1]; }
-          bc[kTopCand - 1] = DBL_MAX; ba[kTopCand - 1] = INT_MAX;
-        }
+        stored = min(total, L);
       }
-      if (lane == 0) ncand[g] = total;
+      if (lane == 0) { ncand[g] = total; nlist[g] = stored; }
+      __syncwarp();
     }
   }
   __syncthreads();
@@ -194,21 +194,24 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
       if (r >= p.av.n_valid) { err = ODK_IMG_ENCODE_ERROR; break; }  // od_pb.py:331-332
       const int nc = ncand[g];
       if (nc == 0) { err = ODK_IMG_ENCODE_ERROR; break; }             // od_pb.py:338
+      const int nl = nlist[g];
       int best_a = -1;
-#pragma unroll
-      for (int k = 0; k < kTopCand; ++k) {
-        const int a = cand[g * kTopCand + k];
-        if (best_a < 0 && a >= 0 && !((taken[a >> 5] >> (a & 31)) & 1u)) best_a = a;
+      for (int k0 = 0; k0 < nl && best_a < 0; k0 += 32) {
+        const int k = k0 + lane;
+        const int a = (k < nl) ? list[(size_t)g * L + k] : -1;
+        const bool is_free = a >= 0 && !((taken[a >> 5] >> (a & 31)) & 1u);
+        const unsigned fm = __ballot_sync(0xffffffffu, is_free);
+        if (fm) best_a = __shfl_sync(0xffffffffu, a, __ffs(fm) - 1);
       }
       const float4 box = gbox[g];
-      if (best_a < 0 && nc > kTopCand) {
-        // the remembered candidates are all taken: exact re-evaluation over the free in-cell anchors
+      if (best_a < 0 && nc > nl) {
+        // the ranked prefix is exhausted but more in-cell anchors exist: exact re-evaluation over the free ones
         const float cx = __fmul_rn(__fadd_rn(box.z, box.x), 0.5f);
         const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
         double mc = DBL_MAX;
         int ma = INT_MAX;
-        for_each_cell_candidate(p.av, cx, cy, lane, [&](int a) {
-          if ((taken[a >> 5] >> (a & 31)) & 1u) return;  // od_pb.py:339
+        for_each_cell_candidate(p.av, cx, cy, lane, [&](int a, bool ok) {
+          if (!ok || ((taken[a >> 5] >> (a & 31)) & 1u)) return;  // od_pb.py:339
           const double c = encode_cost(box, __ldg(p.av.locs + a), p.av.sizes[a]);
           if (cand_less(c, a, mc, ma)) { mc = c; ma = a; }
         });
@@ -440,8 +443,11 @@ int launch_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const 
   args.gt_indices = reinterpret_cast<long long*>(gt_indices);
   args.status = status;
   args.bitmap_words = (a->n + 31) / 32;
-  args.warp_smem_bytes = 0;
-  const size_t smem = odk_align_up((size_t)gmax * (32 + 4 * kTopCand) + (size_t)args.bitmap_words * 4, 16);
+  int list_len = (int)((96 * 1024) / (4 * (size_t)gmax)) & ~7;
+  list_len = list_len > 128 ? 128 : (list_len < 8 ? 8 : list_len);
+  args.list_len = list_len;
+  const size_t smem = odk_align_up((size_t)gmax * (16 + 20 + 4 * (size_t)list_len) + (size_t)kGreedyWarps * kScratch * 12 +
+                                   (size_t)args.bitmap_words * 4, 16);
   ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign: N=%d / Gmax=%d need %zu bytes of shared memory per image", a->n, gmax, smem);
   ODK_CUDA(cudaFuncSetAttribute(assign_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   {

@@ -132,7 +132,11 @@ __global__ void __launch_bounds__(kSortThreads) sort_candidates_kernel(unsigned 
   }
 }
 
-// ---- greedy sweep, one warp per (image, class) ----------------------------------------------------------
+// ---- greedy sweep, one CTA (4 cooperating warps) per (image, class) ------------------------------------
+// Candidates are consumed 32 at a time in score order.  All four warps hold the same 32 candidates
+// (lane = candidate); the kept list and the intra-chunk pair tests are split 4 ways across the warps
+// and the partial suppression masks are OR-ed through shared memory, so the per-chunk critical path is
+// 1/4 of the one-warp version and 4x more warps are resident to hide latency.
 template <bool GE>
 __global__ void __launch_bounds__(kSweepWarps * 32) nms_sweep_kernel(const unsigned long long* __restrict__ cand_keys, int cand_cap,
                                                                     const int* __restrict__ seg_off, int num_classes, int n,
@@ -140,20 +144,23 @@ __global__ void __launch_bounds__(kSweepWarps * 32) nms_sweep_kernel(const unsig
                                                                     int stride, int skip_empty, unsigned long long* __restrict__ kept_keys,
                                                                     int* __restrict__ kept_count) {
   extern __shared__ __align__(16) unsigned char sweep_smem[];
+  __shared__ unsigned s_dead[kSweepWarps];
+  __shared__ unsigned s_sup[32];
   const int warp = threadIdx.x >> 5;
   const unsigned lane = odk_lane();
-  const int c = blockIdx.x * kSweepWarps + warp;
+  const int c = blockIdx.x;
   const int b = blockIdx.y;
-  if (c >= num_classes) return;
-  float4* kbox = reinterpret_cast<float4*>(sweep_smem) + (size_t)warp * stride;
-  float* karea = reinterpret_cast<float*>(sweep_smem + (size_t)kSweepWarps * stride * 16) + (size_t)warp * stride;
+  float4* kbox = reinterpret_cast<float4*>(sweep_smem);
+  float* karea = reinterpret_cast<float*>(sweep_smem + (size_t)stride * 16);
 
   const int s = seg_off[(size_t)b * (num_classes + 1) + c];
   const int e = seg_off[(size_t)b * (num_classes + 1) + c + 1];
   const unsigned long long* keys = cand_keys + (size_t)b * cand_cap;
   const float4* bx = boxes + (size_t)b * n;
   unsigned long long* out = kept_keys + ((size_t)b * num_classes + c) * stride;
-  int nkept = 0;
+  int nkept = 0;  // identical in every thread of the CTA
+  if (threadIdx.x < 32) s_sup[threadIdx.x] = 0u;
+  __syncthreads();
 
   for (int base = s; base < e && nkept < limit; base += 32) {
     const int i = base + (int)lane;
@@ -163,49 +170,60 @@ __global__ void __launch_bounds__(kSweepWarps * 32) nms_sweep_kernel(const unsig
     if (have) box = bx[(int)(key & ODK_IDX_MASK)];
     const float w = __fsub_rn(box.z, box.x), h = __fsub_rn(box.w, box.y);
     const float area = __fmul_rn(w, h);
-    bool alive = have && !(skip_empty && (w <= 0.0f || h <= 0.0f));  // ml.py:610-611
-    // every lane walks the whole kept list (warp-uniform trip count, no divergent exits)
-    if (__any_sync(0xffffffffu, alive)) {
-      bool hit_kept = false;
+    const bool alive0 = have && !(skip_empty && (w <= 0.0f || h <= 0.0f));  // ml.py:610-611
+    // (1) this warp's quarter of the kept list (uniform trip count, no divergent exits)
+    bool hit_kept = false;
 #pragma unroll 4
-      for (int k = 0; k < nkept; ++k) hit_kept |= odk_iou_passes<GE>(box, area, kbox[k], karea[k], iou_thr);
-      alive = alive && !hit_kept;
-    }
-    const unsigned am = __ballot_sync(0xffffffffu, alive);
-    if (am == 0) continue;
-    // sup: higher lanes of this chunk that this lane's box suppresses
+    for (int k = warp; k < nkept; k += kSweepWarps) hit_kept |= odk_iou_passes<GE>(box, area, kbox[k], karea[k], iou_thr);
+    const unsigned dead = __ballot_sync(0xffffffffu, hit_kept);
+    if (lane == 0) s_dead[warp] = dead;
+    // (2) this warp's quarter of the intra-chunk pairs: sup bit j = "this lane's box suppresses lane j"
+    const unsigned am0 = __ballot_sync(0xffffffffu, alive0);
     unsigned sup = 0;
-    for (unsigned rem = am & (am - 1); rem; rem &= rem - 1) {  // skip the lowest alive lane: nothing precedes it
+    for (unsigned rem = am0 & (am0 - 1); rem; rem &= rem - 1) {  // the lowest alive lane has no predecessor
       const int j = __ffs(rem) - 1;
+      if ((j & (kSweepWarps - 1)) != warp) continue;
       float4 bj;
       bj.x = __shfl_sync(0xffffffffu, box.x, j);
       bj.y = __shfl_sync(0xffffffffu, box.y, j);
       bj.z = __shfl_sync(0xffffffffu, box.z, j);
       bj.w = __shfl_sync(0xffffffffu, box.w, j);
       const float aj = __shfl_sync(0xffffffffu, area, j);
-      if (alive && (int)lane < j && odk_iou_passes<GE>(bj, aj, box, area, iou_thr)) sup |= 1u << j;
+      const bool sj = odk_iou_passes<GE>(bj, aj, box, area, iou_thr);
+      if (alive0 && (int)lane < j && sj) sup |= 1u << j;
     }
+    if (sup) atomicOr(&s_sup[lane], sup);
+    __syncthreads();
+    // (3) combine and resolve (every warp computes the same result)
+    unsigned am = am0;
+#pragma unroll
+    for (int q = 0; q < kSweepWarps; ++q) am &= ~s_dead[q];
+    const unsigned sup_all = s_sup[lane];
     unsigned removed = 0, keep = 0;
     int cnt = nkept;
     for (unsigned rem = am; rem; rem &= rem - 1) {
       const int l = __ffs(rem) - 1;
-      const unsigned sup_l = __shfl_sync(0xffffffffu, sup, l);
+      const unsigned sup_l = __shfl_sync(0xffffffffu, sup_all, l);
       if ((removed >> l) & 1u) continue;
       if (cnt >= limit) break;  // ml.py:622-623
       keep |= 1u << l;
       ++cnt;
       removed |= sup_l;
     }
-    if ((keep >> lane) & 1u) {
-      const int pos = nkept + __popc(keep & ((1u << lane) - 1u));
-      kbox[pos] = box;
-      karea[pos] = area;
-      out[pos] = odk_key1_to_key2(key);
+    __syncthreads();  // everyone has read s_dead / s_sup
+    if (warp == 0) {
+      if ((keep >> lane) & 1u) {
+        const int pos = nkept + __popc(keep & ((1u << lane) - 1u));
+        kbox[pos] = box;
+        karea[pos] = area;
+        out[pos] = odk_key1_to_key2(key);
+      }
+      s_sup[lane] = 0u;
     }
     nkept = cnt;
-    __syncwarp();
+    __syncthreads();  // kept list + cleared masks visible
   }
-  if (lane == 0) kept_count[(size_t)b * num_classes + c] = nkept;
+  if (threadIdx.x == 0) kept_count[(size_t)b * num_classes + c] = nkept;
 }
 
 // ---- cross-class top-k + output rows -------------------------------------------------------------------
@@ -324,7 +342,7 @@ static int nms_check(int batch, int n, int num_classes, int top_k, const void* w
   const long long kept_cap = (long long)num_classes * (top_k < 2 ? 2 : top_k);
   ODK_REQUIRE(kept_cap <= kSortChunk, ODK_ERR_UNSUPPORTED,
               "nms: num_classes*max(top_k,2)=%lld exceeds the %d-key shared-memory merge", kept_cap, kSortChunk);
-  ODK_REQUIRE((size_t)kSweepWarps * (top_k < 2 ? 2 : top_k) * 20 <= 200 * 1024, ODK_ERR_UNSUPPORTED, "nms: top_k=%d too large", top_k);
+  ODK_REQUIRE((size_t)(top_k < 2 ? 2 : top_k) * 20 <= 200 * 1024, ODK_ERR_UNSUPPORTED, "nms: top_k=%d too large", top_k);
   ODK_REQUIRE(ws != nullptr && ws_bytes >= odk_nms_workspace_bytes_impl(batch, n, num_classes, top_k), ODK_ERR_WORKSPACE,
               "nms: workspace of %zu bytes is smaller than the required %zu", ws_bytes,
               odk_nms_workspace_bytes_impl(batch, n, num_classes, top_k));
@@ -345,8 +363,8 @@ static int nms_run(const NmsWorkspace& w, int batch, int n, int num_classes, con
   }
   ODK_LAUNCH_CHECK("sort_candidates_kernel");
   const int limit = iou_ge ? w.limit : top_k;
-  dim3 grid((num_classes + kSweepWarps - 1) / kSweepWarps, batch);
-  const size_t sweep_smem = (size_t)kSweepWarps * w.limit * 20;
+  dim3 grid(num_classes, batch);
+  const size_t sweep_smem = (size_t)w.limit * 20;
   if (iou_ge)
     {
       OdkProfileScope prof_("nms_sweep_kernel", stream);

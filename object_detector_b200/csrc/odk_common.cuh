@@ -105,8 +105,9 @@ __device__ __forceinline__ bool odk_iou_passes(const float4 a, float area_a, con
   const float inter = odk_inter(a, b, hit);
   const float uni = __fsub_rn(__fadd_rn(area_a, area_b), inter);
   const float p = thr * uni;
-  const bool sure_yes = (inter > p * 1.00001f) && (uni > 0.0f);
-  const bool sure_no = (inter < p * 0.99999f) && (uni > 0.0f);
+  // (hit implies both boxes have positive extent, hence uni > 0; NaNs fail both tests and take the division)
+  const bool sure_yes = inter > p * 1.00001f;
+  const bool sure_no = inter < p * 0.99999f;
   bool res = sure_yes;
   if (hit && !sure_yes && !sure_no) {  // rare: inside the guard band (or degenerate union)
     const float q = __fdiv_rn(inter, uni);
