@@ -42,7 +42,11 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int c = p.c;
   const size_t clf_bytes = (size_t)TILE * c * 4;
-  const size_t stage_bytes = clf_bytes + (size_t)TILE * 16 + (size_t)TILE * 4;  // all multiples of 16
+  // stage = clfs | locs | objs | pb_locs | decode scale | pb_mask  (every offset a multiple of 16)
+  constexpr size_t kOffLoc = 0, kOffObj = (size_t)TILE * 16, kOffALoc = kOffObj + (size_t)TILE * 4,
+                   kOffAScale = kOffALoc + (size_t)TILE * 16, kOffAMask = kOffAScale + (size_t)TILE * 8,
+                   kTail = kOffAMask + (size_t)((TILE + 15) / 16 * 16);
+  const size_t stage_bytes = clf_bytes + kTail;
   __shared__ uint64_t full_bar[kStages];
 
   const long long total_tiles = (long long)p.batch * p.tiles_per_image;
@@ -66,22 +70,35 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
     const float* src_loc = p.locs + row0 * 4;
     const float* src_obj = p.objs + row0;
     unsigned char* dst = stage_ptr(s);
-    const bool tma_ok = ((rows & 3) == 0) && ((((uintptr_t)src_clf | (uintptr_t)src_loc | (uintptr_t)src_obj) & 15) == 0);
+    unsigned char* tail = dst + clf_bytes;
+    const bool tma_ok = ((rows & 15) == 0) && ((((uintptr_t)src_clf | (uintptr_t)src_loc | (uintptr_t)src_obj) & 15) == 0);
     if (tma_ok) {
       if (tid == 0) {
-        const uint32_t b0 = (uint32_t)rows * c * 4, b1 = (uint32_t)rows * 16, b2 = (uint32_t)rows * 4;
-        odk_mbar_expect_tx(&full_bar[s], b0 + b1 + b2);
-        odk_bulk_g2s(dst, src_clf, b0, &full_bar[s]);
-        odk_bulk_g2s(dst + clf_bytes, src_loc, b1, &full_bar[s]);
-        odk_bulk_g2s(dst + clf_bytes + (size_t)TILE * 16, src_obj, b2, &full_bar[s]);
+        const uint32_t r = (uint32_t)rows;
+        odk_mbar_expect_tx(&full_bar[s], r * c * 4 + r * 16 + r * 4 + r * 16 + r * 8 + r);
+        odk_bulk_g2s(dst, src_clf, r * c * 4, &full_bar[s]);
+        odk_bulk_g2s(tail + kOffLoc, src_loc, r * 16, &full_bar[s]);
+        odk_bulk_g2s(tail + kOffObj, src_obj, r * 4, &full_bar[s]);
+        // the tile's slice of the anchor tables (L2-resident) rides the same barrier
+        odk_bulk_g2s(tail + kOffALoc, p.av.locs + a0, r * 16, &full_bar[s]);
+        odk_bulk_g2s(tail + kOffAScale, p.av.scale + a0, r * 8, &full_bar[s]);
+        odk_bulk_g2s(tail + kOffAMask, p.av.mask + a0, r, &full_bar[s]);
       }
     } else {
       float* d0 = reinterpret_cast<float*>(dst);
-      float* d1 = reinterpret_cast<float*>(dst + clf_bytes);
-      float* d2 = reinterpret_cast<float*>(dst + clf_bytes + (size_t)TILE * 16);
+      float* d1 = reinterpret_cast<float*>(tail + kOffLoc);
+      float* d2 = reinterpret_cast<float*>(tail + kOffObj);
+      float4* d3 = reinterpret_cast<float4*>(tail + kOffALoc);
+      float2* d4 = reinterpret_cast<float2*>(tail + kOffAScale);
+      unsigned char* d5 = tail + kOffAMask;
       for (int i = tid; i < rows * c; i += TILE) d0[i] = __ldg(src_clf + i);
       for (int i = tid; i < rows * 4; i += TILE) d1[i] = __ldg(src_loc + i);
-      for (int i = tid; i < rows; i += TILE) d2[i] = __ldg(src_obj + i);
+      for (int i = tid; i < rows; i += TILE) {
+        d2[i] = __ldg(src_obj + i);
+        d3[i] = __ldg(p.av.locs + a0 + i);
+        d4[i] = __ldg(p.av.scale + a0 + i);
+        d5[i] = p.av.mask[a0 + i];
+      }
       __syncthreads();  // plain stores visible before the single arrive below
       if (tid == 0) odk_mbar_arrive(&full_bar[s]);
     }
@@ -101,8 +118,11 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
     const int rows = min(TILE, p.n - a0);
     const unsigned char* st = stage_ptr(slot);
     const float* s_clf = reinterpret_cast<const float*>(st);
-    const float4* s_loc = reinterpret_cast<const float4*>(st + clf_bytes);
-    const float* s_obj = reinterpret_cast<const float*>(st + clf_bytes + (size_t)TILE * 16);
+    const float4* s_loc = reinterpret_cast<const float4*>(st + clf_bytes + kOffLoc);
+    const float* s_obj = reinterpret_cast<const float*>(st + clf_bytes + kOffObj);
+    const float4* s_aloc = reinterpret_cast<const float4*>(st + clf_bytes + kOffALoc);
+    const float2* s_ascale = reinterpret_cast<const float2*>(st + clf_bytes + kOffAScale);
+    const unsigned char* s_amask = st + clf_bytes + kOffAMask;
 
     bool is_cand = false;
     int cls = 0;
@@ -133,11 +153,11 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
           if (v > best) { best = v; cls = j; }
         }
       }
-      const float maskf = p.av.mask[a] ? 1.0f : 0.0f;
+      const float maskf = s_amask[tid] ? 1.0f : 0.0f;
       conf = __fmul_rn(__fmul_rn(s_obj[tid], best), maskf);  // (objs*confs)*pb_mask, od_net.py:183-184
       const float4 pr = s_loc[tid];
-      const float4 lc = __ldg(p.av.locs + a);
-      const float2 sc = __ldg(p.av.scale + a);
+      const float4 lc = s_aloc[tid];
+      const float2 sc = s_ascale[tid];
       box.x = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.x, sc.x), lc.x), 0.0f), 1.0f);
       box.y = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.y, sc.y), lc.y), 0.0f), 1.0f);
       box.z = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.z, sc.x), lc.z), 0.0f), 1.0f);
@@ -203,7 +223,7 @@ int sm_count_cached() {
 
 template <int TILE, bool DENSE>
 int launch_tile(DecodeArgs& args, cudaStream_t stream) {
-  const size_t stage = (size_t)TILE * args.c * 4 + (size_t)TILE * 20;
+  const size_t stage = (size_t)TILE * args.c * 4 + (size_t)TILE * 44 + (size_t)((TILE + 15) / 16 * 16);
   const size_t smem = stage * kStages;
   auto kern = decode_score_kernel<TILE, DENSE>;
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -135,23 +135,44 @@ __global__ void __launch_bounds__(kSortThreads) sort_candidates_kernel(unsigned 
 // ---- greedy sweep, one CTA (4 cooperating warps) per (image, class) ------------------------------------
 // Candidates are consumed 32 at a time in score order.  All four warps hold the same 32 candidates
 // (lane = candidate); the kept list and the intra-chunk pair tests are split 4 ways across the warps
-// and the partial suppression masks are OR-ed through shared memory, so the per-chunk critical path is
-// 1/4 of the one-warp version and 4x more warps are resident to hide latency.
+// and the partial suppression masks are OR-ed through shared memory.
+//
+// Pair test.  IoU >= thr  <=>  inter >= k*(area_a+area_b) with k = thr/(1+thr).  The hot loops use
+// that division-free form with a +-3e-5 relative guard band (two FFMAs against per-lane constants);
+// a pair that lands inside the band (or any pair when the fast form does not apply) is re-evaluated
+// with the reference's exact fp32 expression (odk_iou_passes), so the decision is always the
+// reference's.
+struct FastThr {
+  float k_hi, k_lo;
+  int enabled;
+};
+
+__device__ __forceinline__ void fast_pair(const float4 a, float a_hi, float a_lo, const float4 b, float area_b, const FastThr ft,
+                                          bool& yes, bool& maybe) {
+  const float w = fmaxf(fminf(a.z, b.z) - fmaxf(a.x, b.x), 0.0f);
+  const float h = fmaxf(fminf(a.w, b.w) - fmaxf(a.y, b.y), 0.0f);
+  const float inter = w * h;
+  yes = inter > fmaf(area_b, ft.k_hi, a_hi);
+  maybe = (inter >= fmaf(area_b, ft.k_lo, a_lo)) && !yes;
+}
+
 template <bool GE>
 __global__ void __launch_bounds__(kSweepWarps * 32) nms_sweep_kernel(const unsigned long long* __restrict__ cand_keys, int cand_cap,
                                                                     const int* __restrict__ seg_off, int num_classes, int n,
-                                                                    const float4* __restrict__ boxes, float iou_thr, int limit,
+                                                                    const float4* __restrict__ boxes, float iou_thr, FastThr ft, int limit,
                                                                     int stride, int skip_empty, unsigned long long* __restrict__ kept_keys,
                                                                     int* __restrict__ kept_count) {
   extern __shared__ __align__(16) unsigned char sweep_smem[];
   __shared__ unsigned s_dead[kSweepWarps];
   __shared__ unsigned s_sup[32];
+  __shared__ int s_cnt;
   const int warp = threadIdx.x >> 5;
   const unsigned lane = odk_lane();
   const int c = blockIdx.x;
   const int b = blockIdx.y;
   float4* kbox = reinterpret_cast<float4*>(sweep_smem);
   float* karea = reinterpret_cast<float*>(sweep_smem + (size_t)stride * 16);
+  const bool fast = GE && ft.enabled;  // the fast form needs positive-extent boxes: guaranteed by the zero-area skip
 
   const int s = seg_off[(size_t)b * (num_classes + 1) + c];
   const int e = seg_off[(size_t)b * (num_classes + 1) + c + 1];
@@ -171,47 +192,67 @@ __global__ void __launch_bounds__(kSweepWarps * 32) nms_sweep_kernel(const unsig
     const float w = __fsub_rn(box.z, box.x), h = __fsub_rn(box.w, box.y);
     const float area = __fmul_rn(w, h);
     const bool alive0 = have && !(skip_empty && (w <= 0.0f || h <= 0.0f));  // ml.py:610-611
+    const float a_hi = area * ft.k_hi, a_lo = area * ft.k_lo;
     // (1) this warp's quarter of the kept list (uniform trip count, no divergent exits)
     bool hit_kept = false;
+    if (fast) {
+      bool unsure = false;
 #pragma unroll 4
-    for (int k = warp; k < nkept; k += kSweepWarps) hit_kept |= odk_iou_passes<GE>(box, area, kbox[k], karea[k], iou_thr);
+      for (int k = warp; k < nkept; k += kSweepWarps) {
+        bool yes, maybe;
+        fast_pair(box, a_hi, a_lo, kbox[k], karea[k], ft, yes, maybe);
+        hit_kept |= yes;
+        unsure |= maybe;
+      }
+      if (__any_sync(0xffffffffu, unsure && !hit_kept && alive0)) {  // rare: some pair sits inside the guard band
+        for (int k = warp; k < nkept; k += kSweepWarps) hit_kept |= odk_iou_passes<GE>(box, area, kbox[k], karea[k], iou_thr);
+      }
+    } else {
+#pragma unroll 2
+      for (int k = warp; k < nkept; k += kSweepWarps) hit_kept |= odk_iou_passes<GE>(box, area, kbox[k], karea[k], iou_thr);
+    }
     const unsigned dead = __ballot_sync(0xffffffffu, hit_kept);
     if (lane == 0) s_dead[warp] = dead;
     // (2) this warp's quarter of the intra-chunk pairs: sup bit j = "this lane's box suppresses lane j"
     const unsigned am0 = __ballot_sync(0xffffffffu, alive0);
     unsigned sup = 0;
-    for (unsigned rem = am0 & (am0 - 1); rem; rem &= rem - 1) {  // the lowest alive lane has no predecessor
+    for (unsigned rem = (am0 & (am0 - 1)) & (0x11111111u << warp); rem; rem &= rem - 1) {  // j = warp (mod 4), j != lowest alive
       const int j = __ffs(rem) - 1;
-      if ((j & (kSweepWarps - 1)) != warp) continue;
       float4 bj;
       bj.x = __shfl_sync(0xffffffffu, box.x, j);
       bj.y = __shfl_sync(0xffffffffu, box.y, j);
       bj.z = __shfl_sync(0xffffffffu, box.z, j);
       bj.w = __shfl_sync(0xffffffffu, box.w, j);
       const float aj = __shfl_sync(0xffffffffu, area, j);
-      const bool sj = odk_iou_passes<GE>(bj, aj, box, area, iou_thr);
+      bool sj;
+      if (fast) {
+        bool maybe;
+        fast_pair(box, a_hi, a_lo, bj, aj, ft, sj, maybe);
+        if (maybe) sj = odk_iou_passes<GE>(bj, aj, box, area, iou_thr);
+      } else {
+        sj = odk_iou_passes<GE>(bj, aj, box, area, iou_thr);
+      }
       if (alive0 && (int)lane < j && sj) sup |= 1u << j;
     }
     if (sup) atomicOr(&s_sup[lane], sup);
     __syncthreads();
-    // (3) combine and resolve (every warp computes the same result)
-    unsigned am = am0;
-#pragma unroll
-    for (int q = 0; q < kSweepWarps; ++q) am &= ~s_dead[q];
-    const unsigned sup_all = s_sup[lane];
-    unsigned removed = 0, keep = 0;
-    int cnt = nkept;
-    for (unsigned rem = am; rem; rem &= rem - 1) {
-      const int l = __ffs(rem) - 1;
-      const unsigned sup_l = __shfl_sync(0xffffffffu, sup_all, l);
-      if ((removed >> l) & 1u) continue;
-      if (cnt >= limit) break;  // ml.py:622-623
-      keep |= 1u << l;
-      ++cnt;
-      removed |= sup_l;
-    }
-    __syncthreads();  // everyone has read s_dead / s_sup
+    // (3) combine and resolve: warp 0 walks the alive lanes in score order
     if (warp == 0) {
+      unsigned am = am0;
+#pragma unroll
+      for (int q = 0; q < kSweepWarps; ++q) am &= ~s_dead[q];
+      const unsigned sup_all = s_sup[lane];
+      unsigned removed = 0, keep = 0;
+      int cnt = nkept;
+      for (unsigned rem = am; rem; rem &= rem - 1) {
+        const int l = __ffs(rem) - 1;
+        const unsigned sup_l = __shfl_sync(0xffffffffu, sup_all, l);
+        if ((removed >> l) & 1u) continue;
+        if (cnt >= limit) break;  // ml.py:622-623
+        keep |= 1u << l;
+        ++cnt;
+        removed |= sup_l;
+      }
       if ((keep >> lane) & 1u) {
         const int pos = nkept + __popc(keep & ((1u << lane) - 1u));
         kbox[pos] = box;
@@ -219,9 +260,10 @@ __global__ void __launch_bounds__(kSweepWarps * 32) nms_sweep_kernel(const unsig
         out[pos] = odk_key1_to_key2(key);
       }
       s_sup[lane] = 0u;
+      if (lane == 0) s_cnt = cnt;
     }
-    nkept = cnt;
-    __syncthreads();  // kept list + cleared masks visible
+    __syncthreads();  // kept list, count and cleared masks visible
+    nkept = s_cnt;
   }
   if (threadIdx.x == 0) kept_count[(size_t)b * num_classes + c] = nkept;
 }
@@ -363,19 +405,24 @@ static int nms_run(const NmsWorkspace& w, int batch, int n, int num_classes, con
   }
   ODK_LAUNCH_CHECK("sort_candidates_kernel");
   const int limit = iou_ge ? w.limit : top_k;
+  FastThr ft;
+  ft.enabled = (iou_thr > 1e-3f && iou_thr < 0.999f) ? 1 : 0;
+  const double kk = ft.enabled ? (double)iou_thr / (1.0 + (double)iou_thr) : 0.0;
+  ft.k_hi = (float)(kk * (1.0 + 3e-5));
+  ft.k_lo = (float)(kk * (1.0 - 3e-5));
   dim3 grid(num_classes, batch);
   const size_t sweep_smem = (size_t)w.limit * 20;
   if (iou_ge)
     {
       OdkProfileScope prof_("nms_sweep_kernel", stream);
       nms_sweep_kernel<true><<<grid, kSweepWarps * 32, sweep_smem, stream>>>(w.cand_keys, w.cap, w.seg_off, num_classes, n, boxes, iou_thr,
-                                                                             limit, w.limit, 1, w.kept_keys, w.kept_count);
+                                                                             ft, limit, w.limit, 1, w.kept_keys, w.kept_count);
     }
   else
     {
       OdkProfileScope prof_("nms_sweep_kernel", stream);
       nms_sweep_kernel<false><<<grid, kSweepWarps * 32, sweep_smem, stream>>>(w.cand_keys, w.cap, w.seg_off, num_classes, n, boxes, iou_thr,
-                                                                              limit, w.limit, 0, w.kept_keys, w.kept_count);
+                                                                              ft, limit, w.limit, 0, w.kept_keys, w.kept_count);
     }
   ODK_LAUNCH_CHECK("nms_sweep_kernel");
   if (out != nullptr) {

@@ -289,3 +289,30 @@ def test_predict_from_head_matches_oracle_unpack(prior_boxes, oracle_tables):
     for p, (rc, rs, rb) in zip(preds, ref):
         assert p.classes.dtype == np.int32 and np.array_equal(p.classes, rc)
         assert np.array_equal(p.confs, rs) and np.array_equal(p.bboxes, rb)
+
+
+def test_nms_guard_band_pairs_exact():
+    """Pairs whose IoU sits within a few ulps of the threshold: the division-free fast test must hand
+    them to the exact fp32 expression (ml.py:615-619), in both the kept-list and intra-chunk paths."""
+    rng = np.random.RandomState(42)
+    n_img, thr = 512, np.float32(0.45)
+    boxes = np.zeros((n_img, 3, 4), np.float32)
+    for i in range(n_img):
+        w = np.float32(rng.uniform(0.2, 0.9))
+        h = np.float32(rng.uniform(0.2, 0.9))
+        # B = A cut at height t*h: IoU = t exactly in real arithmetic; nudge t by a few ulps around thr
+        t = np.nextafter(thr, np.float32(1 if rng.rand() < 0.5 else 0), dtype=np.float32) if i % 3 else thr
+        for _ in range(int(rng.randint(0, 4))):
+            t = np.nextafter(t, np.float32(rng.choice([0, 1])), dtype=np.float32)
+        boxes[i, 0] = [0, 0, w, h]
+        boxes[i, 1] = [0, 0, w, np.float32(h * t)]
+        boxes[i, 2] = [0, 0, np.float32(w * t), h]
+    confs = np.tile(np.array([[0.9, 0.8, 0.7]], np.float32), (n_img, 1))
+    classes = np.zeros((n_img, 3), np.int32)
+    out, kept = odk.layers.nms()(1, 3, top_k=3)([classes, confs, boxes], return_index=True)
+    decided_both_ways = set()
+    for i in range(n_img):
+        ro, rk = R.nms_layer_image(classes[i], confs[i], boxes[i], 1, top_k=3)
+        assert np.array_equal(kept[i], rk), (i, boxes[i])
+        decided_both_ways.add(int((rk >= 0).sum()))
+    assert len(decided_both_ways) >= 2  # the set really straddles the threshold
