@@ -133,12 +133,12 @@ int odk_nms(const float* boxes /*[dev n,4]*/, const float* scores /*[dev n]*/, i
  * dets: the NMS layer output for n_img images; rows with conf < conf_thr are dropped
  * (od.py:265).  gt_offsets[n_img+1] indexes the flat GT arrays.  Boxes are converted to integer
  * pixels with round-half-even of the fp64 product (ml.py:62-65,184-186). */
-size_t odk_voc_ap_workspace_bytes(int n_img, int top_k, int num_classes, int n_gt_total);
+size_t odk_voc_ap_workspace_bytes(int n_img, int top_k, int num_classes, int gt_max_per_image);
 int odk_voc_ap(int n_img, int top_k, int num_classes, const float* dets /*[dev n_img,top_k,6]*/,
-               float conf_thr, const int32_t* img_wh /*[dev n_img,2]*/,
+               float conf_thr, const int32_t* img_wh /*[dev n_img,2] (width, height)*/,
                const float* gt_boxes /*[dev n_gt,4] normalised*/, const int32_t* gt_classes /*[dev n_gt]*/,
                const uint8_t* gt_difficult /*[dev n_gt]*/, const int32_t* gt_offsets /*[dev n_img+1]*/,
-               int n_gt_total, double* ap_area /*[dev C]*/, double* ap07 /*[dev C]*/,
+               int gt_max_per_image, double* ap_area /*[dev C]*/, double* ap07 /*[dev C]*/,
                void* workspace, size_t workspace_bytes, void* stream);
 
 /* Measurement aid (bench.py): when enabled for the calling host thread every kernel launch of the

@@ -18,6 +18,7 @@
 //      written as [class, conf, x1, y1, x2, y2], zero padded (layers.py:963-970).
 // All IoU tests are the reference's fp32 expression, evaluated exactly (odk_iou_passes).
 #include "odk_common.cuh"
+#include "odk_sort.cuh"
 
 namespace {
 
@@ -55,26 +56,6 @@ __global__ void __launch_bounds__(256) collect_candidates_kernel(int n, int num_
   }
 }
 
-// ---- bitonic sort (descending) ----------------------------------------------------------------------------
-// One merge pass (k, j) over s[0..m): element `local` has global index base+local (direction bit).
-__device__ __forceinline__ void bitonic_pass(unsigned long long* s, int m, int base, int k, int j) {
-  for (int t = threadIdx.x; t < (m >> 1); t += blockDim.x) {
-    const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-    const int l = i | j;
-    const unsigned long long x = s[i], y = s[l];
-    const bool desc = (((base + i) & k) == 0);
-    if (desc ? (x < y) : (x > y)) { s[i] = y; s[l] = x; }
-  }
-}
-
-__device__ void bitonic_sort_shared(unsigned long long* s, int m, int base, int k_from, int k_to) {
-  for (int k = k_from; k <= k_to; k <<= 1)
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      bitonic_pass(s, m, base, k, j);
-      __syncthreads();
-    }
-}
-
 __global__ void __launch_bounds__(kSortThreads) sort_candidates_kernel(unsigned long long* __restrict__ cand_keys,
                                                                       const int* __restrict__ cand_count, int cand_cap,
                                                                       int num_classes, int* __restrict__ seg_off) {
@@ -82,44 +63,8 @@ __global__ void __launch_bounds__(kSortThreads) sort_candidates_kernel(unsigned 
   const int b = blockIdx.x;
   unsigned long long* g = cand_keys + (size_t)b * cand_cap;
   const int cnt = min(cand_count[b], cand_cap);
-  int n_pad = 2;
-  while (n_pad < cnt) n_pad <<= 1;
 
-  if (cnt > 1) {
-    if (n_pad <= kSortChunk) {
-      for (int i = threadIdx.x; i < n_pad; i += blockDim.x) s_keys[i] = (i < cnt) ? g[i] : 0ull;
-      __syncthreads();
-      bitonic_sort_shared(s_keys, n_pad, 0, 2, n_pad);
-      for (int i = threadIdx.x; i < cnt; i += blockDim.x) g[i] = s_keys[i];
-    } else {
-      // hybrid: chunks of kSortChunk sorted in shared memory, long-range merges in global (L2)
-      for (int i = cnt + threadIdx.x; i < n_pad; i += blockDim.x) g[i] = 0ull;  // cand_cap is a power of two >= n_pad
-      __syncthreads();
-      for (int base = 0; base < n_pad; base += kSortChunk) {
-        for (int i = threadIdx.x; i < kSortChunk; i += blockDim.x) s_keys[i] = g[base + i];
-        __syncthreads();
-        bitonic_sort_shared(s_keys, kSortChunk, base, 2, kSortChunk);
-        for (int i = threadIdx.x; i < kSortChunk; i += blockDim.x) g[base + i] = s_keys[i];
-        __syncthreads();
-      }
-      for (int k = kSortChunk << 1; k <= n_pad; k <<= 1) {
-        for (int j = k >> 1; j >= kSortChunk; j >>= 1) {
-          bitonic_pass(g, n_pad, 0, k, j);
-          __syncthreads();
-        }
-        for (int base = 0; base < n_pad; base += kSortChunk) {
-          for (int i = threadIdx.x; i < kSortChunk; i += blockDim.x) s_keys[i] = g[base + i];
-          __syncthreads();
-          for (int j = kSortChunk >> 1; j > 0; j >>= 1) {
-            bitonic_pass(s_keys, kSortChunk, base, k, j);
-            __syncthreads();
-          }
-          for (int i = threadIdx.x; i < kSortChunk; i += blockDim.x) g[base + i] = s_keys[i];
-          __syncthreads();
-        }
-      }
-    }
-  }
+  odk_block_sort_desc(g, cnt, s_keys, kSortChunk);  // in shared memory up to kSortChunk keys, hybrid above
   __syncthreads();
   // class segment offsets: seg_off[b, c] = first sorted position whose class >= c
   for (int c = threadIdx.x; c <= num_classes; c += blockDim.x) {

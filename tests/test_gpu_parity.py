@@ -316,3 +316,64 @@ def test_nms_guard_band_pairs_exact():
         assert np.array_equal(kept[i], rk), (i, boxes[i])
         decided_both_ways.add(int((rk >= 0).sum()))
     assert len(decided_both_ways) >= 2  # the set really straddles the threshold
+
+
+# ----------------------------------------------------------------------------------------- VOC AP (parity unpinned: chainercv absent)
+def _to_objects(gts, preds):
+    y_true = [odk.ml.ObjectsAnnotation('.', w, h, c, b, d) for (w, h, c, b, d) in gts]
+    y_pred = [odk.ml.ObjectsPrediction(c, s, b) for (c, s, b) in preds]
+    return y_true, y_pred
+
+
+def _assert_ap_equal(res, ref):
+    for k in ('AP', 'AP_VOC'):
+        assert np.array_equal(np.isnan(res[k]), np.isnan(ref[k])), k
+        np.testing.assert_allclose(res[k], ref[k], rtol=1e-5, atol=1e-12, equal_nan=True)  # north_star: AP within 1e-5 relative
+    for k in ('mAP', 'mAP_VOC'):
+        np.testing.assert_allclose(res[k], ref[k], rtol=1e-5, equal_nan=True)
+
+
+def test_voc_ap_micro_cases_on_gpu():
+    f = np.float32
+    gt = [(100, 100, np.array([0]), np.array([[.1, .1, .5, .5]], f), np.array([False]))]
+    cases = [
+        [(np.array([0]), np.array([.9], f), np.array([[.1, .1, .5, .5]], f))],                                  # perfect
+        [(np.array([0]), np.array([.9], f), np.array([[.6, .6, .9, .9]], f))],                                  # miss
+        [(np.array([0, 0]), np.array([.9, .8], f), np.array([[.1, .1, .5, .5], [.1, .1, .5, .5]], f))],         # duplicate
+        [(np.array([0, 0]), np.array([.9, .8], f), np.array([[.6, .6, .9, .9], [.1, .1, .5, .5]], f))],         # FP first
+        [(np.zeros((0,), np.int32), np.zeros((0,), f), np.zeros((0, 4), f))],                                   # no detections
+    ]
+    for preds in cases:
+        y_true, y_pred = _to_objects(gt, preds)
+        _assert_ap_equal(odk.voc.evaluate(y_true, y_pred, num_classes=2), R.voc_evaluate(gt, preds, 2))
+    gt_d = [(100, 100, np.array([0, 0]), np.array([[.1, .1, .5, .5], [.6, .6, .9, .9]], f), np.array([True, False]))]
+    y_true, y_pred = _to_objects(gt_d, cases[0])
+    res = odk.voc.evaluate(y_true, y_pred, num_classes=2)
+    _assert_ap_equal(res, R.voc_evaluate(gt_d, cases[0], 2))
+    assert res['AP'][0] == 0.0 and np.isnan(res['AP'][1])
+
+
+@pytest.mark.parametrize('n_img,classes,seed', [(300, 20, 2007), (4952, 20, 2007), (4952, 2, 11)])
+def test_voc_ap_vs_oracle(n_img, classes, seed):
+    """Config 4 shape (4952 images); C=2 pushes > 16384 detections into one class -> hybrid sort path."""
+    gts, preds = synth.eval_set(seed, n_img, classes)
+    y_true, y_pred = _to_objects(gts, preds)
+    res = odk.voc.evaluate(y_true, y_pred, num_classes=classes)
+    ref = R.voc_evaluate(gts, preds, classes)
+    _assert_ap_equal(res, ref)
+    assert 0.05 < res['mAP'] < 1.0 and 0.05 < res['mAP_VOC'] < 1.0
+
+
+def test_voc_ap_from_nms_layer_output(prior_boxes, oracle_tables):
+    """The evaluation path end to end on one GPU: head outputs -> decode+NMS -> AP, vs the oracle chain."""
+    pb, t = prior_boxes('voc320'), oracle_tables('voc320')
+    objs, clfs, locs = synth.predictions(9, 4, len(pb), 20, clustered=True)
+    gts, _ = synth.eval_set(5, 4, 20)
+    out = pb.decode_nms(objs, clfs, locs)
+    y_true = [odk.ml.ObjectsAnnotation('.', w, h, c, b, d) for (w, h, c, b, d) in gts]
+    gt = odk.voc.pack_ground_truth(y_true, out.device)
+    ap, ap07 = (x.cpu().numpy() for x in odk.voc.evaluate_detections(out, gt, 20, conf_threshold=0.01))
+    ro, _ = R.predict_tail(t, objs, clfs, locs)
+    ref = R.voc_evaluate(gts, R.unpack_predictions(ro, 0.01), 20)
+    np.testing.assert_allclose(ap, ref['AP'], rtol=1e-5, atol=1e-12, equal_nan=True)
+    np.testing.assert_allclose(ap07, ref['AP_VOC'], rtol=1e-5, atol=1e-12, equal_nan=True)
