@@ -30,7 +30,8 @@ ROT = 3  # distinct input sets rotated through so every step reads data that is 
 WORKLOAD = 'cfg2+cfg3: Darknet53 640x640 VOC anchors (N=16800, C=20), batch 64: assign+encode (<=64 GT/img) + decode + per-class NMS (top-k 200)'
 
 # algorithmic HBM bytes per image
-BYTES_DECODE_NMS = 4 * N * (1 + C + 4) + 4800          # 1 684 800: read head outputs, write (200,6)
+BYTES_DECODE_NMS = 4 * N * (1 + C + 4) + 4800          # 1 684 800: read head outputs, write (200,6)  (whole fused op)
+BYTES_SCORE_EMIT = 4 * N * (1 + C)                     # 1 411 200: what score_emit_kernel itself must read (locs are decoded lazily by NMS)
 BYTES_ASSIGN_ENCODE = 20 * GMAX + 4 * N * (3 + C + 4)  # 1 815 680: read GT, write y_true
 
 
@@ -225,7 +226,7 @@ def run_cuda(args):
     prof = _lib.profile_read()
     launches_per_step = sum(c for _, c in prof.values()) // max(args.steps, 1)
     peak, peak_src = load_peaks()
-    alg_bytes = {'decode_score_kernel': B * BYTES_DECODE_NMS, 'encode_rows_kernel': B * BYTES_ASSIGN_ENCODE}
+    alg_bytes = {'score_emit_kernel': B * BYTES_SCORE_EMIT, 'encode_rows_kernel': B * BYTES_ASSIGN_ENCODE}
     kernels = {k: {'ms_per_launch': ms / c, 'launches': c, 'share': ms / max(1e-9, sum(m for m, _ in prof.values()))}
                for k, (ms, c) in prof.items()}
     # the roofline line is for the dominant HBM-streaming kernel (largest device time among the two

@@ -1,25 +1,31 @@
-// K1 — score + decode (+ candidate emission), the streaming HBM-bound kernel of the predict side.
+// K1 — the streaming HBM-bound kernel of the predict side, in two flavours of one template:
 //
-// Replaces ChannelArgMax/ChannelMax (layers.py:69-98), _objconf (od_net.py:177-184) and the
-// decode_locs Lambda (od_pb.py:216-222, od_net.py:189) — three separate TF elementwise passes in
-// the reference — with one pass over the head outputs:
-//   classes = argmax_c clfs (first max wins), conf = (objs * max_c clfs) * pb_mask,
-//   box = clip(locs * float32(0.10*sizes) + pb_locs, 0, 1)
-// and, for the NMS that follows, appends a 64-bit sort key for every anchor with conf > conf_thr
-// (strict, layers.py:935) to the image's candidate list.
+//   DENSE  (odk_decode_score)  replaces ChannelArgMax/ChannelMax (layers.py:69-98), _objconf
+//          (od_net.py:177-184) and the decode_locs Lambda (od_pb.py:216-222, od_net.py:189) — three
+//          separate TF elementwise passes in the reference — with one pass over the head outputs:
+//            classes = argmax_c clfs (first max wins), conf = (objs * max_c clfs) * pb_mask,
+//            box = clip(locs * float32(0.10*sizes) + pb_locs, 0, 1)
+//   EMIT   (first half of odk_decode_nms)  computes classes/conf only and emits one 64-bit sort key
+//          per anchor with conf > conf_thr (strict, layers.py:935).  `locs` is NOT read here: the
+//          NMS kernel decodes lazily only the boxes it visits, so the dense classes/confs/boxes
+//          intermediates never exist.
 //
-// Data movement: persistent CTAs, one tile = TILE consecutive anchors of one image.  The three input
-// slabs of a tile (clfs TILE*C*4 B, locs TILE*16 B, objs TILE*4 B) are contiguous in HBM, so each is
-// fetched with ONE 1-D bulk TMA copy (cp.async.bulk, SASS UBLKCP) into a 3-stage shared-memory ring
-// guarded by mbarriers; a thread then owns one anchor row in shared memory.  Tiles whose source
-// addresses / sizes are not 16-byte multiples fall back to cooperative plain loads into the same
-// ring slot.  Algorithmic HBM bytes per anchor: read 4*(1+C+4); write 4+4+16 (dense mode) or
-// 8 B per candidate + 16 B per candidate box (fused mode).
+// Data movement: persistent CTAs, one tile = TILE consecutive anchors of one image.  The input slabs
+// of a tile (clfs TILE*C*4 B, objs TILE*4 B, pb_mask TILE B; DENSE adds locs / pb_locs / scale) are
+// contiguous in HBM, so each is fetched with ONE 1-D bulk TMA copy (cp.async.bulk, SASS UBLKCP) into a
+// shared-memory ring guarded by mbarriers; a thread then owns one anchor row in shared memory.  Tiles
+// whose source addresses / sizes are not 16-byte multiples fall back to cooperative plain loads into
+// the same ring slot.
+//
+// Candidate emission is atomic-free and deterministic: a tile owns the fixed slab
+// cand_keys[b][tile*TILE .. +TILE) and compacts its candidates to the front of it (warp ballots + a
+// per-tile scan of the warp counts); piece_count[b][tile] holds how many there are.
+//
+// Algorithmic HBM bytes per anchor: DENSE read 4*(1+C+4), write 4+4+16; EMIT read 4*(1+C), write 8 per
+// candidate.
 #include "odk_common.cuh"
 
 namespace {
-
-constexpr int kStages = 3;
 
 struct DecodeArgs {
   AnchorView av;
@@ -27,27 +33,36 @@ struct DecodeArgs {
   const float* objs;
   const float* clfs;
   const float* locs;
-  int32_t* classes;  // dense outputs (null in fused mode)
+  int32_t* classes;  // DENSE outputs
   float* confs;
-  float4* boxes;     // dense mode: all rows; fused mode: candidate rows only
-  float conf_thr;
-  unsigned long long* cand_keys;  // [B, cand_cap] or null
-  int* cand_count;                // [B]
-  int cand_cap;
+  float4* boxes;
+  float conf_thr;                 // EMIT
+  unsigned long long* cand_keys;  // [B, tiles_per_image * TILE]
+  int* piece_count;               // [B, tiles_per_image]
   int tiles_per_image;
 };
 
 template <int TILE, bool DENSE>
+struct StageLayout {
+  // clfs | objs | pb_mask | (DENSE: locs | pb_locs | decode scale); every offset a multiple of 16
+  static constexpr size_t kOffObj = 0, kOffAMask = (size_t)TILE * 4, kOffLoc = kOffAMask + (size_t)((TILE + 15) / 16 * 16),
+                          kOffALoc = kOffLoc + (DENSE ? (size_t)TILE * 16 : 0), kOffAScale = kOffALoc + (DENSE ? (size_t)TILE * 16 : 0),
+                          kTail = kOffAScale + (DENSE ? (size_t)TILE * 8 : 0);
+  static constexpr int kStages = DENSE ? 3 : 4;
+  static size_t stage_bytes(int c) { return (size_t)TILE * c * 4 + kTail; }
+};
+
+template <int TILE, bool DENSE>
 __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) {
+  using L = StageLayout<TILE, DENSE>;
+  constexpr int kStages = L::kStages;
+  constexpr int kWarps = TILE / 32;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int c = p.c;
   const size_t clf_bytes = (size_t)TILE * c * 4;
-  // stage = clfs | locs | objs | pb_locs | decode scale | pb_mask  (every offset a multiple of 16)
-  constexpr size_t kOffLoc = 0, kOffObj = (size_t)TILE * 16, kOffALoc = kOffObj + (size_t)TILE * 4,
-                   kOffAScale = kOffALoc + (size_t)TILE * 16, kOffAMask = kOffAScale + (size_t)TILE * 8,
-                   kTail = kOffAMask + (size_t)((TILE + 15) / 16 * 16);
-  const size_t stage_bytes = clf_bytes + kTail;
+  const size_t stage_bytes = clf_bytes + L::kTail;
   __shared__ uint64_t full_bar[kStages];
+  __shared__ int s_wcnt[2][kWarps];
 
   const long long total_tiles = (long long)p.batch * p.tiles_per_image;
   const int tid = threadIdx.x;
@@ -60,44 +75,50 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
 
   auto stage_ptr = [&](int s) { return smem_raw + (size_t)s * stage_bytes; };
 
-  // Issue the loads of tile `t` into ring slot `s`.  Returns via the mbarrier in both paths.
+  // Issue the loads of tile `t` into ring slot `s`.  Completion is signalled on the mbarrier in both paths.
   auto issue = [&](long long t, int s) {
     const int b = (int)(t / p.tiles_per_image);
     const int a0 = (int)(t % p.tiles_per_image) * TILE;
     const int rows = min(TILE, p.n - a0);
     const size_t row0 = (size_t)b * p.n + a0;
     const float* src_clf = p.clfs + row0 * c;
-    const float* src_loc = p.locs + row0 * 4;
     const float* src_obj = p.objs + row0;
+    const float* src_loc = DENSE ? p.locs + row0 * 4 : nullptr;
     unsigned char* dst = stage_ptr(s);
     unsigned char* tail = dst + clf_bytes;
-    const bool tma_ok = ((rows & 15) == 0) && ((((uintptr_t)src_clf | (uintptr_t)src_loc | (uintptr_t)src_obj) & 15) == 0);
+    bool tma_ok = ((rows & 15) == 0) && ((((uintptr_t)src_clf | (uintptr_t)src_obj) & 15) == 0);
+    if (DENSE) tma_ok = tma_ok && (((uintptr_t)src_loc & 15) == 0);
     if (tma_ok) {
       if (tid == 0) {
         const uint32_t r = (uint32_t)rows;
-        odk_mbar_expect_tx(&full_bar[s], r * c * 4 + r * 16 + r * 4 + r * 16 + r * 8 + r);
+        odk_mbar_expect_tx(&full_bar[s], r * c * 4 + r * 4 + r + (DENSE ? r * 16 + r * 16 + r * 8 : 0));
         odk_bulk_g2s(dst, src_clf, r * c * 4, &full_bar[s]);
-        odk_bulk_g2s(tail + kOffLoc, src_loc, r * 16, &full_bar[s]);
-        odk_bulk_g2s(tail + kOffObj, src_obj, r * 4, &full_bar[s]);
-        // the tile's slice of the anchor tables (L2-resident) rides the same barrier
-        odk_bulk_g2s(tail + kOffALoc, p.av.locs + a0, r * 16, &full_bar[s]);
-        odk_bulk_g2s(tail + kOffAScale, p.av.scale + a0, r * 8, &full_bar[s]);
-        odk_bulk_g2s(tail + kOffAMask, p.av.mask + a0, r, &full_bar[s]);
+        odk_bulk_g2s(tail + L::kOffObj, src_obj, r * 4, &full_bar[s]);
+        odk_bulk_g2s(tail + L::kOffAMask, p.av.mask + a0, r, &full_bar[s]);  // anchor tables are L2-resident
+        if (DENSE) {
+          odk_bulk_g2s(tail + L::kOffLoc, src_loc, r * 16, &full_bar[s]);
+          odk_bulk_g2s(tail + L::kOffALoc, p.av.locs + a0, r * 16, &full_bar[s]);
+          odk_bulk_g2s(tail + L::kOffAScale, p.av.scale + a0, r * 8, &full_bar[s]);
+        }
       }
     } else {
       float* d0 = reinterpret_cast<float*>(dst);
-      float* d1 = reinterpret_cast<float*>(tail + kOffLoc);
-      float* d2 = reinterpret_cast<float*>(tail + kOffObj);
-      float4* d3 = reinterpret_cast<float4*>(tail + kOffALoc);
-      float2* d4 = reinterpret_cast<float2*>(tail + kOffAScale);
-      unsigned char* d5 = tail + kOffAMask;
+      float* d2 = reinterpret_cast<float*>(tail + L::kOffObj);
+      unsigned char* d5 = tail + L::kOffAMask;
       for (int i = tid; i < rows * c; i += TILE) d0[i] = __ldg(src_clf + i);
-      for (int i = tid; i < rows * 4; i += TILE) d1[i] = __ldg(src_loc + i);
       for (int i = tid; i < rows; i += TILE) {
         d2[i] = __ldg(src_obj + i);
-        d3[i] = __ldg(p.av.locs + a0 + i);
-        d4[i] = __ldg(p.av.scale + a0 + i);
         d5[i] = p.av.mask[a0 + i];
+      }
+      if (DENSE) {
+        float* d1 = reinterpret_cast<float*>(tail + L::kOffLoc);
+        float4* d3 = reinterpret_cast<float4*>(tail + L::kOffALoc);
+        float2* d4 = reinterpret_cast<float2*>(tail + L::kOffAScale);
+        for (int i = tid; i < rows * 4; i += TILE) d1[i] = __ldg(src_loc + i);
+        for (int i = tid; i < rows; i += TILE) {
+          d3[i] = __ldg(p.av.locs + a0 + i);
+          d4[i] = __ldg(p.av.scale + a0 + i);
+        }
       }
       __syncthreads();  // plain stores visible before the single arrive below
       if (tid == 0) odk_mbar_arrive(&full_bar[s]);
@@ -109,25 +130,21 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
   for (int s = 0; s < kStages; ++s, t_issue += gridDim.x)
     if (t_issue < total_tiles) issue(t_issue, s);
 
-  int slot = 0;
+  int slot = 0, buf = 0;
   uint32_t phase = 0;
   for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
     odk_mbar_wait(&full_bar[slot], phase);
     const int b = (int)(t / p.tiles_per_image);
-    const int a0 = (int)(t % p.tiles_per_image) * TILE;
+    const int tile = (int)(t % p.tiles_per_image);
+    const int a0 = tile * TILE;
     const int rows = min(TILE, p.n - a0);
     const unsigned char* st = stage_ptr(slot);
     const float* s_clf = reinterpret_cast<const float*>(st);
-    const float4* s_loc = reinterpret_cast<const float4*>(st + clf_bytes + kOffLoc);
-    const float* s_obj = reinterpret_cast<const float*>(st + clf_bytes + kOffObj);
-    const float4* s_aloc = reinterpret_cast<const float4*>(st + clf_bytes + kOffALoc);
-    const float2* s_ascale = reinterpret_cast<const float2*>(st + clf_bytes + kOffAScale);
-    const unsigned char* s_amask = st + clf_bytes + kOffAMask;
+    const float* s_obj = reinterpret_cast<const float*>(st + clf_bytes + L::kOffObj);
+    const unsigned char* s_amask = st + clf_bytes + L::kOffAMask;
 
-    bool is_cand = false;
     int cls = 0;
     float conf = 0.0f;
-    float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
     const int a = a0 + tid;
     if (tid < rows) {
       const float* row = s_clf + (size_t)tid * c;
@@ -155,39 +172,40 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
       }
       const float maskf = s_amask[tid] ? 1.0f : 0.0f;
       conf = __fmul_rn(__fmul_rn(s_obj[tid], best), maskf);  // (objs*confs)*pb_mask, od_net.py:183-184
-      const float4 pr = s_loc[tid];
-      const float4 lc = s_aloc[tid];
-      const float2 sc = s_ascale[tid];
-      box.x = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.x, sc.x), lc.x), 0.0f), 1.0f);
-      box.y = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.y, sc.y), lc.y), 0.0f), 1.0f);
-      box.z = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.z, sc.x), lc.z), 0.0f), 1.0f);
-      box.w = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.w, sc.y), lc.w), 0.0f), 1.0f);
-      is_cand = (p.cand_keys != nullptr) && (conf > p.conf_thr);
-      const size_t r = (size_t)b * p.n + a;
-      if (DENSE) {
+    }
+    if (DENSE) {
+      if (tid < rows) {
+        const float4* s_loc = reinterpret_cast<const float4*>(st + clf_bytes + L::kOffLoc);
+        const float4* s_aloc = reinterpret_cast<const float4*>(st + clf_bytes + L::kOffALoc);
+        const float2* s_ascale = reinterpret_cast<const float2*>(st + clf_bytes + L::kOffAScale);
+        const float4 box = odk_decode_box(s_loc[tid], s_aloc[tid], s_ascale[tid]);
+        const size_t r = (size_t)b * p.n + a;
         p.classes[r] = cls;
         p.confs[r] = conf;
         p.boxes[r] = box;
-      } else if (is_cand) {
-        p.boxes[r] = box;
       }
-    }
-    // candidate append, one atomic per warp
-    if (p.cand_keys != nullptr) {
+      __syncthreads();  // every thread is done with ring slot `slot`
+      if (t_issue < total_tiles) issue(t_issue, slot);
+    } else {
+      const bool is_cand = (tid < rows) && (conf > p.conf_thr);
       const unsigned m = __ballot_sync(0xffffffffu, is_cand);
-      if (m) {
-        const unsigned lane = odk_lane();
-        int base = 0;
-        if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(p.cand_count + b, __popc(m));
-        base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-        if (is_cand) {
-          const int pos = base + __popc(m & ((1u << lane) - 1u));
-          if (pos < p.cand_cap) p.cand_keys[(size_t)b * p.cand_cap + pos] = odk_make_key1(cls, conf, a);
-        }
+      const unsigned lane = odk_lane();
+      const int warp = tid >> 5;
+      if (lane == 0) s_wcnt[buf][warp] = __popc(m);
+      __syncthreads();  // ring slot free (all rows are in registers) + warp counts visible
+      if (t_issue < total_tiles) issue(t_issue, slot);
+      int base = 0, total = 0;
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) {
+        const int v = s_wcnt[buf][w];
+        base += (w < warp) ? v : 0;
+        total += v;
       }
+      const size_t piece = (size_t)b * p.tiles_per_image + tile;
+      if (is_cand) p.cand_keys[piece * TILE + base + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
+      if (tid == 0) p.piece_count[piece] = total;
+      buf ^= 1;  // the next tile's counts go to the other buffer; this one is rewritten two barriers later
     }
-    __syncthreads();  // every thread is done with ring slot `slot`
-    if (t_issue < total_tiles) issue(t_issue, slot);
     t_issue += gridDim.x;
     if (++slot == kStages) { slot = 0; phase ^= 1u; }
   }
@@ -201,12 +219,7 @@ __global__ void __launch_bounds__(256) decode_locs_kernel(AnchorView av, long lo
     const float4 pr = pred[r];
     const float4 lc = __ldg(av.locs + a);
     const float2 sc = __ldg(av.scale + a);
-    float4 box;
-    box.x = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.x, sc.x), lc.x), 0.0f), 1.0f);
-    box.y = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.y, sc.y), lc.y), 0.0f), 1.0f);
-    box.z = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.z, sc.x), lc.z), 0.0f), 1.0f);
-    box.w = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.w, sc.y), lc.w), 0.0f), 1.0f);
-    out[r] = box;
+    out[r] = odk_decode_box(pr, lc, sc);
   }
 }
 
@@ -223,8 +236,8 @@ int sm_count_cached() {
 
 template <int TILE, bool DENSE>
 int launch_tile(DecodeArgs& args, cudaStream_t stream) {
-  const size_t stage = (size_t)TILE * args.c * 4 + (size_t)TILE * 44 + (size_t)((TILE + 15) / 16 * 16);
-  const size_t smem = stage * kStages;
+  using L = StageLayout<TILE, DENSE>;
+  const size_t smem = L::stage_bytes(args.c) * L::kStages;
   auto kern = decode_score_kernel<TILE, DENSE>;
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   args.tiles_per_image = (args.n + TILE - 1) / TILE;
@@ -235,32 +248,37 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   if (grid > total) grid = total;
   if (grid < 1) grid = 1;
   {
-    OdkProfileScope prof_("decode_score_kernel", stream);
+    OdkProfileScope prof_(DENSE ? "decode_score_kernel" : "score_emit_kernel", stream);
     kern<<<(unsigned)grid, TILE, smem, stream>>>(args);
   }
-  ODK_LAUNCH_CHECK("decode_score_kernel");
+  ODK_LAUNCH_CHECK(DENSE ? "decode_score_kernel" : "score_emit_kernel");
   return ODK_OK;
 }
 
 }  // namespace
 
-// Internal entry used by odk_decode_score (dense) and odk_decode_nms (fused).
+// Candidate piece (= tile) height used for `num_classes` channels: chosen so that the shared-memory ring
+// stays under ~100 KB (2+ CTAs per SM).  The NMS workspace layout depends on it.
+int odk_piece_size(int num_classes) { return num_classes <= 32 ? 256 : (num_classes <= 96 ? 64 : 32); }
+
+// Internal entry used by odk_decode_score (dense) and odk_decode_nms (emit).
 int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
                             int32_t* classes, float* confs, float* boxes, bool dense, float conf_thr,
-                            unsigned long long* cand_keys, int* cand_count, int cand_cap, cudaStream_t stream) {
+                            unsigned long long* cand_keys, int* piece_count, cudaStream_t stream) {
   DecodeArgs args;
   args.av = odk_view(a);
   args.batch = batch; args.n = a->n; args.c = a->num_classes;
   args.objs = objs; args.clfs = clfs; args.locs = locs;
   args.classes = classes; args.confs = confs; args.boxes = reinterpret_cast<float4*>(boxes);
-  args.conf_thr = conf_thr; args.cand_keys = cand_keys; args.cand_count = cand_count; args.cand_cap = cand_cap;
+  args.conf_thr = conf_thr; args.cand_keys = cand_keys; args.piece_count = piece_count;
   args.tiles_per_image = 0;
   const int c = a->num_classes;
-  // tile height chosen so a 3-stage ring stays under ~100 KB (2+ CTAs per SM)
-  if (c <= 32) return dense ? launch_tile<256, true>(args, stream) : launch_tile<256, false>(args, stream);
-  if (c <= 96) return dense ? launch_tile<64, true>(args, stream) : launch_tile<64, false>(args, stream);
   ODK_REQUIRE(c <= 512, ODK_ERR_UNSUPPORTED, "num_classes=%d > 512 not supported by decode_score", c);
-  return dense ? launch_tile<32, true>(args, stream) : launch_tile<32, false>(args, stream);
+  switch (odk_piece_size(c)) {
+    case 256: return dense ? launch_tile<256, true>(args, stream) : launch_tile<256, false>(args, stream);
+    case 64: return dense ? launch_tile<64, true>(args, stream) : launch_tile<64, false>(args, stream);
+    default: return dense ? launch_tile<32, true>(args, stream) : launch_tile<32, false>(args, stream);
+  }
 }
 
 int odk_launch_decode_locs(const odk_anchors* a, long long rows, const float* pred, float* out, cudaStream_t stream) {

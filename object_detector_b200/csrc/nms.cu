@@ -1,38 +1,56 @@
-// K2 — per-class NMS + cross-class top-k (layers.py:925-970; inner greedy NMS ml.py:589-625).
+// K2 — per-class NMS + cross-class top-k (layers.py:925-970; inner greedy NMS ml.py:589-625), one
+// kernel, one CTA per image.
 //
-// Pipeline on the candidate list produced by K1 (or by collect_candidates_kernel for the unfused
-// layer entry):
-//   1. sort_candidates_kernel  one CTA per image: bitonic sort of the 64-bit keys
-//        key1 = [4095-class : 12][flip(score) : 32][anchor : 20]   (descending)
-//      => class ascending, score descending, index descending (= argsort(stable)[::-1], SURVEY A-6);
-//      in shared memory up to 16384 keys, hybrid shared/global above that.  Emits class segment
-//      offsets by binary search.
-//   2. nms_sweep_kernel        one WARP per (image, class) segment: candidates are taken 32 at a
-//      time in score order; each lane tests its box against the kept list (shared memory), then the
-//      32x32 intra-chunk suppression bitmask is built with warp shuffles and resolved by a
-//      warp-uniform sweep (ballot-style), stopping at the reference's length limit.
-//   3. topk_merge_kernel       one CTA per image: the <= C*L kept keys, re-keyed as
-//        key2 = [flip(score) : 32][4095-class : 12][anchor : 20]
-//      are sorted descending (score desc; lower class, then per-class NMS order on ties — the order
-//      tf.nn.top_k(sorted=True) yields on the class-concatenated list) and the first top_k rows are
-//      written as [class, conf, x1, y1, x2, y2], zero padded (layers.py:963-970).
-// All IoU tests are the reference's fp32 expression, evaluated exactly (odk_iou_passes).
+// Formulation.  The reference runs one greedy NMS per class (each over that class's candidates in
+// descending score, limited to min(top_k, n_c) results), concatenates the results in class order and
+// takes the global top_k by score (tf.nn.top_k, sorted, lower position first on ties).  Greedy NMS of
+// different classes never interact, so visiting the candidates of ALL classes in one global order
+//     key2 = [flip(score):32][4095-class:12][anchor:20]  descending
+// with a class-aware suppression test yields every class's kept list simultaneously, already merged in
+// the output order — and the sweep can stop as soon as top_k boxes are kept: a box cut by its class's
+// own limit min(top_k, n_c) has at least top_k better boxes of its own class in front of it, so it can
+// never be among the global top_k.  Typically only a few hundred of the ~4k candidates of an image are
+// ever touched.
+//
+// Per image:
+//   1. candidates arrive as per-tile compacted pieces (score_emit_kernel / collect_pieces_kernel);
+//      a block scan of the piece counts gives a flat index space.
+//   2. rounds, until top_k boxes are kept or the candidates run out:
+//        a. MSB radix select (11-bit digits, shared-memory histograms) finds a key threshold such that
+//           the next band holds <= 512 of the best remaining keys;
+//        b. the band is gathered and bitonic-sorted in shared memory by (class, score desc, anchor desc);
+//        c. ONLY the band's boxes are fetched — in the fused path they are decoded here from `locs`
+//           (od_pb.py:216-222), so the dense decoded-box tensor never exists;
+//        d. band candidates suppressed by boxes kept in earlier rounds are dropped (all threads);
+//        e. one warp per class segment: 32 candidates at a time, 32x32 suppression bitmask built with
+//           warp shuffles, resolved by a warp-uniform ballot-style sweep;
+//        f. the round's survivors are sorted into global order and appended to the kept list / written
+//           as output rows [class, conf, x1, y1, x2, y2] (layers.py:963-970), cut at top_k.
+// All IoU tests evaluate the reference's fp32 expression exactly (odk_iou_passes); the division-free
+// fast form is used only outside a guard band.
 #include "odk_common.cuh"
 #include "odk_sort.cuh"
 
 namespace {
 
-constexpr int kSortThreads = 1024;
-constexpr int kSortChunk = 16384;  // keys held in shared memory (128 KB)
-constexpr int kSweepWarps = 4;
+constexpr int kNmsThreads = 512;
+constexpr int kNmsWarps = kNmsThreads / 32;
+constexpr int kBand = 512;
+constexpr int kBandMin = 256;   // a select level is accepted once it yields at least this many keys
+constexpr int kDigitBits = 11;
+constexpr int kBins = 1 << kDigitBits;
+constexpr int kCollectPiece = 256;
+constexpr int kMaxPieces = 8192;
 
-// ---- candidate collection for the unfused layer entry (layers.py:935) ------------------------------------
-__global__ void __launch_bounds__(256) collect_candidates_kernel(int n, int num_classes, const int32_t* __restrict__ classes,
-                                                                 const float* __restrict__ confs, float conf_thr, int take_all,
-                                                                 unsigned long long* __restrict__ cand_keys,
-                                                                 int* __restrict__ cand_count, int cand_cap) {
+// ---- candidate collection for the unfused entries (layers.py:935) ----------------------------------------
+// One CTA = one piece of 256 anchors, same piece format as score_emit_kernel.
+__global__ void __launch_bounds__(kCollectPiece) collect_pieces_kernel(int n, int num_classes, const int32_t* __restrict__ classes,
+                                                                       const float* __restrict__ confs, float conf_thr, int take_all,
+                                                                       unsigned long long* __restrict__ cand_keys,
+                                                                       int* __restrict__ piece_count) {
+  __shared__ int s_wcnt[kCollectPiece / 32];
   const int b = blockIdx.y;
-  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  const int a = blockIdx.x * kCollectPiece + threadIdx.x;
   bool is_cand = false;
   int cls = 0;
   float conf = 0.f;
@@ -43,45 +61,22 @@ __global__ void __launch_bounds__(256) collect_candidates_kernel(int n, int num_
     is_cand = (take_all || conf > conf_thr) && cls >= 0 && cls < num_classes;
   }
   const unsigned m = __ballot_sync(0xffffffffu, is_cand);
-  if (m) {
-    const unsigned lane = odk_lane();
-    const int leader = __ffs(m) - 1;
-    int base = 0;
-    if ((int)lane == leader) base = atomicAdd(cand_count + b, __popc(m));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (is_cand) {
-      const int pos = base + __popc(m & ((1u << lane) - 1u));
-      if (pos < cand_cap) cand_keys[(size_t)b * cand_cap + pos] = odk_make_key1(cls, conf, a);
-    }
-  }
-}
-
-__global__ void __launch_bounds__(kSortThreads) sort_candidates_kernel(unsigned long long* __restrict__ cand_keys,
-                                                                      const int* __restrict__ cand_count, int cand_cap,
-                                                                      int num_classes, int* __restrict__ seg_off) {
-  extern __shared__ __align__(16) unsigned long long s_keys[];
-  const int b = blockIdx.x;
-  unsigned long long* g = cand_keys + (size_t)b * cand_cap;
-  const int cnt = min(cand_count[b], cand_cap);
-
-  odk_block_sort_desc(g, cnt, s_keys, kSortChunk);  // in shared memory up to kSortChunk keys, hybrid above
+  const unsigned lane = odk_lane();
+  const int warp = threadIdx.x >> 5;
+  if (lane == 0) s_wcnt[warp] = __popc(m);
   __syncthreads();
-  // class segment offsets: seg_off[b, c] = first sorted position whose class >= c
-  for (int c = threadIdx.x; c <= num_classes; c += blockDim.x) {
-    int lo = 0, hi = cnt;
-    while (lo < hi) {
-      const int mid = (lo + hi) >> 1;
-      if (odk_key1_class(g[mid]) >= c) hi = mid; else lo = mid + 1;
-    }
-    seg_off[(size_t)b * (num_classes + 1) + c] = lo;
+  int base = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < kCollectPiece / 32; ++w) {
+    const int v = s_wcnt[w];
+    base += (w < warp) ? v : 0;
+    total += v;
   }
+  const size_t piece = (size_t)b * gridDim.x + blockIdx.x;
+  if (is_cand) cand_keys[piece * kCollectPiece + base + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
+  if (threadIdx.x == 0) piece_count[piece] = total;
 }
 
-// ---- greedy sweep, one CTA (4 cooperating warps) per (image, class) ------------------------------------
-// Candidates are consumed 32 at a time in score order.  All four warps hold the same 32 candidates
-// (lane = candidate); the kept list and the intra-chunk pair tests are split 4 ways across the warps
-// and the partial suppression masks are OR-ed through shared memory.
-//
 // Pair test.  IoU >= thr  <=>  inter >= k*(area_a+area_b) with k = thr/(1+thr).  The hot loops use
 // that division-free form with a +-3e-5 relative guard band (two FFMAs against per-lane constants);
 // a pair that lands inside the band (or any pair when the fast form does not apply) is re-evaluated
@@ -92,304 +87,417 @@ struct FastThr {
   int enabled;
 };
 
-__device__ __forceinline__ void fast_pair(const float4 a, float a_hi, float a_lo, const float4 b, float area_b, const FastThr ft,
-                                          bool& yes, bool& maybe) {
-  const float w = fmaxf(fminf(a.z, b.z) - fmaxf(a.x, b.x), 0.0f);
-  const float h = fmaxf(fminf(a.w, b.w) - fmaxf(a.y, b.y), 0.0f);
-  const float inter = w * h;
-  yes = inter > fmaf(area_b, ft.k_hi, a_hi);
-  maybe = (inter >= fmaf(area_b, ft.k_lo, a_lo)) && !yes;
+template <bool GE>
+__device__ __forceinline__ bool pair_hit(const float4 a, float area_a, float a_hi, float a_lo, const float4 b, float area_b, float thr,
+                                         const FastThr ft, bool fast) {
+  if (fast) {
+    const float w = fmaxf(fminf(a.z, b.z) - fmaxf(a.x, b.x), 0.0f);
+    const float h = fmaxf(fminf(a.w, b.w) - fmaxf(a.y, b.y), 0.0f);
+    const float inter = w * h;
+    const bool yes = inter > fmaf(area_b, ft.k_hi, a_hi);
+    const bool maybe = (inter >= fmaf(area_b, ft.k_lo, a_lo)) && !yes;
+    return maybe ? odk_iou_passes<GE>(a, area_a, b, area_b, thr) : yes;
+  }
+  return odk_iou_passes<GE>(a, area_a, b, area_b, thr);
+}
+
+struct NmsArgs {
+  AnchorView av;
+  int n, piece, n_pieces;
+  const unsigned long long* cand_keys;  // [B, n_pieces*piece]
+  const int* piece_count;               // [B, n_pieces]
+  const float4* boxes;                  // [B, N] decoded boxes, or null ->
+  const float4* locs;                   // [B, N] head output, decoded lazily
+  float iou_thr;
+  FastThr ft;
+  int limit;       // sweep stops once this many boxes are kept
+  int top_k;       // rows of `out` per image
+  int skip_empty;  // ml.py:610-611
+  float* out;             // [B, top_k, 6] or null
+  int32_t* kept_index;    // [B, top_k] or null
+  int32_t* out_index;     // standalone: [limit] kept input indices ...
+  int32_t* out_count;     // ... and their number
+};
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int* s_warp /*[kNmsWarps + 1]*/, int& total) {
+  const int lane = (int)odk_lane(), warp = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    const int wv = (lane < kNmsWarps) ? s_warp[lane] : 0;
+    int winc = wv;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, winc, d);
+      if (lane >= d) winc += o;
+    }
+    if (lane < kNmsWarps) s_warp[lane] = winc - wv;
+    if (lane == kNmsWarps - 1) s_warp[kNmsWarps] = winc;
+  }
+  __syncthreads();
+  const int res = s_warp[warp] + inc - v;
+  total = s_warp[kNmsWarps];
+  __syncthreads();
+  return res;
 }
 
 template <bool GE>
-__global__ void __launch_bounds__(kSweepWarps * 32) nms_sweep_kernel(const unsigned long long* __restrict__ cand_keys, int cand_cap,
-                                                                    const int* __restrict__ seg_off, int num_classes, int n,
-                                                                    const float4* __restrict__ boxes, float iou_thr, FastThr ft, int limit,
-                                                                    int stride, int skip_empty, unsigned long long* __restrict__ kept_keys,
-                                                                    int* __restrict__ kept_count) {
-  extern __shared__ __align__(16) unsigned char sweep_smem[];
-  __shared__ unsigned s_dead[kSweepWarps];
-  __shared__ unsigned s_sup[32];
-  __shared__ int s_cnt;
-  const int warp = threadIdx.x >> 5;
-  const unsigned lane = odk_lane();
-  const int c = blockIdx.x;
-  const int b = blockIdx.y;
-  float4* kbox = reinterpret_cast<float4*>(sweep_smem);
-  float* karea = reinterpret_cast<float*>(sweep_smem + (size_t)stride * 16);
-  const bool fast = GE && ft.enabled;  // the fast form needs positive-extent boxes: guaranteed by the zero-area skip
+__global__ void __launch_bounds__(kNmsThreads) nms_image_kernel(const NmsArgs p) {
+  extern __shared__ __align__(16) unsigned char nms_smem[];
+  __shared__ int s_hist[kBins];
+  __shared__ __align__(16) unsigned long long s_band[kBand];   // key1 of the band, sorted
+  __shared__ __align__(16) unsigned long long s_order[kBand];  // survivors in global order
+  __shared__ float4 s_box[kBand];
+  __shared__ float s_area[kBand];
+  __shared__ unsigned char s_alive[kBand];
+  __shared__ unsigned char s_keep[kBand];
+  __shared__ int s_seg[kBand + 1];
+  __shared__ int s_scan[kNmsWarps + 1];
+  __shared__ int s_nb, s_nseg, s_nk, s_sel_r, s_sel_cnt;
 
-  const int s = seg_off[(size_t)b * (num_classes + 1) + c];
-  const int e = seg_off[(size_t)b * (num_classes + 1) + c + 1];
-  const unsigned long long* keys = cand_keys + (size_t)b * cand_cap;
-  const float4* bx = boxes + (size_t)b * n;
-  unsigned long long* out = kept_keys + ((size_t)b * num_classes + c) * stride;
-  int nkept = 0;  // identical in every thread of the CTA
-  if (threadIdx.x < 32) s_sup[threadIdx.x] = 0u;
-  __syncthreads();
-
-  for (int base = s; base < e && nkept < limit; base += 32) {
-    const int i = base + (int)lane;
-    const bool have = i < e;
-    const unsigned long long key = have ? keys[i] : 0ull;
-    float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (have) box = bx[(int)(key & ODK_IDX_MASK)];
-    const float w = __fsub_rn(box.z, box.x), h = __fsub_rn(box.w, box.y);
-    const float area = __fmul_rn(w, h);
-    const bool alive0 = have && !(skip_empty && (w <= 0.0f || h <= 0.0f));  // ml.py:610-611
-    const float a_hi = area * ft.k_hi, a_lo = area * ft.k_lo;
-    // (1) this warp's quarter of the kept list (uniform trip count, no divergent exits)
-    bool hit_kept = false;
-    if (fast) {
-      bool unsure = false;
-#pragma unroll 4
-      for (int k = warp; k < nkept; k += kSweepWarps) {
-        bool yes, maybe;
-        fast_pair(box, a_hi, a_lo, kbox[k], karea[k], ft, yes, maybe);
-        hit_kept |= yes;
-        unsure |= maybe;
-      }
-      if (__any_sync(0xffffffffu, unsure && !hit_kept && alive0)) {  // rare: some pair sits inside the guard band
-        for (int k = warp; k < nkept; k += kSweepWarps) hit_kept |= odk_iou_passes<GE>(box, area, kbox[k], karea[k], iou_thr);
-      }
-    } else {
-#pragma unroll 2
-      for (int k = warp; k < nkept; k += kSweepWarps) hit_kept |= odk_iou_passes<GE>(box, area, kbox[k], karea[k], iou_thr);
-    }
-    const unsigned dead = __ballot_sync(0xffffffffu, hit_kept);
-    if (lane == 0) s_dead[warp] = dead;
-    // (2) this warp's quarter of the intra-chunk pairs: sup bit j = "this lane's box suppresses lane j"
-    const unsigned am0 = __ballot_sync(0xffffffffu, alive0);
-    unsigned sup = 0;
-    for (unsigned rem = (am0 & (am0 - 1)) & (0x11111111u << warp); rem; rem &= rem - 1) {  // j = warp (mod 4), j != lowest alive
-      const int j = __ffs(rem) - 1;
-      float4 bj;
-      bj.x = __shfl_sync(0xffffffffu, box.x, j);
-      bj.y = __shfl_sync(0xffffffffu, box.y, j);
-      bj.z = __shfl_sync(0xffffffffu, box.z, j);
-      bj.w = __shfl_sync(0xffffffffu, box.w, j);
-      const float aj = __shfl_sync(0xffffffffu, area, j);
-      bool sj;
-      if (fast) {
-        bool maybe;
-        fast_pair(box, a_hi, a_lo, bj, aj, ft, sj, maybe);
-        if (maybe) sj = odk_iou_passes<GE>(bj, aj, box, area, iou_thr);
-      } else {
-        sj = odk_iou_passes<GE>(bj, aj, box, area, iou_thr);
-      }
-      if (alive0 && (int)lane < j && sj) sup |= 1u << j;
-    }
-    if (sup) atomicOr(&s_sup[lane], sup);
-    __syncthreads();
-    // (3) combine and resolve: warp 0 walks the alive lanes in score order
-    if (warp == 0) {
-      unsigned am = am0;
-#pragma unroll
-      for (int q = 0; q < kSweepWarps; ++q) am &= ~s_dead[q];
-      const unsigned sup_all = s_sup[lane];
-      unsigned removed = 0, keep = 0;
-      int cnt = nkept;
-      for (unsigned rem = am; rem; rem &= rem - 1) {
-        const int l = __ffs(rem) - 1;
-        const unsigned sup_l = __shfl_sync(0xffffffffu, sup_all, l);
-        if ((removed >> l) & 1u) continue;
-        if (cnt >= limit) break;  // ml.py:622-623
-        keep |= 1u << l;
-        ++cnt;
-        removed |= sup_l;
-      }
-      if ((keep >> lane) & 1u) {
-        const int pos = nkept + __popc(keep & ((1u << lane) - 1u));
-        kbox[pos] = box;
-        karea[pos] = area;
-        out[pos] = odk_key1_to_key2(key);
-      }
-      s_sup[lane] = 0u;
-      if (lane == 0) s_cnt = cnt;
-    }
-    __syncthreads();  // kept list, count and cleared masks visible
-    nkept = s_cnt;
-  }
-  if (threadIdx.x == 0) kept_count[(size_t)b * num_classes + c] = nkept;
-}
-
-// ---- cross-class top-k + output rows -------------------------------------------------------------------
-__global__ void __launch_bounds__(256) topk_merge_kernel(const unsigned long long* __restrict__ kept_keys,
-                                                        const int* __restrict__ kept_count, int num_classes, int limit, int n,
-                                                        const float4* __restrict__ boxes, int top_k, float* __restrict__ out,
-                                                        int32_t* __restrict__ kept_index) {
-  extern __shared__ __align__(16) unsigned long long s_keys[];
-  __shared__ int s_total;
-  __shared__ int s_scan[256];
-  __shared__ int s_off[ODK_MAX_CLASSES + 1];
-  const int b = blockIdx.x;
   const int tid = threadIdx.x;
-  // exclusive scan of kept_count over classes, 256 classes per round
-  int carry = 0;
-  for (int c0 = 0; c0 < num_classes; c0 += 256) {
-    const int c = c0 + tid;
-    const int v = (c < num_classes) ? kept_count[(size_t)b * num_classes + c] : 0;
-    s_scan[tid] = v;
-    __syncthreads();
-    for (int d = 1; d < 256; d <<= 1) {
-      const int add = (tid >= d) ? s_scan[tid - d] : 0;
-      __syncthreads();
-      s_scan[tid] += add;
-      __syncthreads();
-    }
-    if (c < num_classes) s_off[c] = carry + s_scan[tid] - v;
-    carry += s_scan[255];
-    __syncthreads();
-  }
-  if (tid == 0) { s_total = carry; s_off[num_classes] = carry; }
-  __syncthreads();
-  // coalesced gather of the per-class kept lists into one dense array
-  for (int i = tid; i < num_classes * limit; i += blockDim.x) {
-    const int c = i / limit, k = i - c * limit;
-    if (k < s_off[c + 1] - s_off[c]) s_keys[s_off[c] + k] = kept_keys[(size_t)b * num_classes * limit + i];
-  }
-  const int total = s_total;
-  int n_pad = 2;
-  while (n_pad < total) n_pad <<= 1;
-  for (int i = total + tid; i < n_pad; i += blockDim.x) s_keys[i] = 0ull;
-  __syncthreads();
-  if (total > 1) bitonic_sort_shared(s_keys, n_pad, 0, 2, n_pad);
-  const int rows = min(top_k, total);
-  for (int r = tid; r < top_k; r += blockDim.x) {
-    float* o = out + ((size_t)b * top_k + r) * 6;
-    if (r < rows) {
-      const unsigned long long k = s_keys[r];
-      const int idx = (int)(k & ODK_IDX_MASK);
-      const int cls = ODK_MAX_CLASSES - 1 - (int)((k >> ODK_IDX_BITS) & (ODK_MAX_CLASSES - 1));
-      const float4 bx = boxes[(size_t)b * n + idx];
-      o[0] = (float)cls; o[1] = odk_unflip_score((uint32_t)(k >> 32));
-      o[2] = bx.x; o[3] = bx.y; o[4] = bx.z; o[5] = bx.w;
-      kept_index[(size_t)b * top_k + r] = idx;
-    } else {
-      o[0] = o[1] = o[2] = o[3] = o[4] = o[5] = 0.0f;
-      kept_index[(size_t)b * top_k + r] = -1;
-    }
-  }
-}
+  const int lane = (int)odk_lane();
+  const int warp = tid >> 5;
+  const int b = blockIdx.x;
+  const int limit = p.limit;
+  float4* kbox = reinterpret_cast<float4*>(nms_smem);                                   // [limit]
+  float* karea = reinterpret_cast<float*>(nms_smem + (size_t)limit * 16);               // [limit]
+  int* kcls = reinterpret_cast<int*>(nms_smem + (size_t)limit * 20);                    // [limit]
+  int* s_pref = reinterpret_cast<int*>(nms_smem + odk_align_up((size_t)limit * 24, 16));  // [n_pieces + 1]
+  const bool fast = GE && p.ft.enabled;  // the fast form needs positive-extent boxes: guaranteed by the zero-area skip
 
-// ml.non_maximum_suppression result export: kept indices in NMS order.
-__global__ void export_kept_kernel(const unsigned long long* __restrict__ kept_keys, const int* __restrict__ kept_count,
-                                   int32_t* __restrict__ out_index, int32_t* __restrict__ out_count) {
-  const int cnt = kept_count[0];
-  for (int i = threadIdx.x; i < cnt; i += blockDim.x) out_index[i] = (int32_t)(kept_keys[i] & ODK_IDX_MASK);
-  if (threadIdx.x == 0) *out_count = cnt;
+  const unsigned long long* keys = p.cand_keys + (size_t)b * p.n_pieces * p.piece;
+  const int* pcount = p.piece_count + (size_t)b * p.n_pieces;
+
+  // ---- flat index space over the pieces ---------------------------------------------------------------
+  int total;
+  {
+    const int per = (p.n_pieces + kNmsThreads - 1) / kNmsThreads;
+    const int q0 = min(p.n_pieces, tid * per), q1 = min(p.n_pieces, q0 + per);
+    int local = 0;
+    for (int q = q0; q < q1; ++q) local += pcount[q];
+    int run = block_exclusive_scan(local, s_scan, total);
+    for (int q = q0; q < q1; ++q) {
+      s_pref[q] = run;
+      run += pcount[q];
+    }
+    if (tid == 0) s_pref[p.n_pieces] = total;
+    __syncthreads();
+  }
+  // candidate i of the image (any order): piece by binary search over the prefix sums
+  auto cand_key = [&](int i) {
+    int lo = 0, hi = p.n_pieces;  // largest q with s_pref[q] <= i
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (s_pref[mid] <= i) lo = mid; else hi = mid;
+    }
+    return keys[(size_t)lo * p.piece + (i - s_pref[lo])];
+  };
+
+  int nkept = 0, processed = 0;
+  unsigned long long hi_key = ~0ull;  // keys of earlier bands are >= hi_key (every real key is < ~0)
+
+  while (processed < total && nkept < limit) {
+    const int remaining = total - processed;
+    // ---- a. threshold of the next band --------------------------------------------------------------
+    unsigned long long lo_key = 0ull;
+    if (remaining > kBand) {
+      unsigned long long prefix = 0ull;  // digits fixed so far (the bucket that still overflows)
+      int above = 0;                     // keys < hi_key that lie above that bucket (all taken)
+      for (int shift = 64 - kDigitBits; ; shift = max(0, shift - kDigitBits)) {
+        const int width = (shift == 0) ? ((64 - 1) % kDigitBits + 1) : kDigitBits;  // last digit takes the leftover bits
+        const int top = shift + width;                                              // bits above the digit
+        for (int i = tid; i < kBins; i += kNmsThreads) s_hist[i] = 0;
+        __syncthreads();
+        for (int i = tid; i < total; i += kNmsThreads) {
+          const unsigned long long k = cand_key(i);
+          if (k < hi_key && (top >= 64 || (k >> top) == prefix)) atomicAdd(&s_hist[(int)((k >> shift) & (unsigned long long)((1 << width) - 1))], 1);
+        }
+        __syncthreads();
+        // walk the digits from the top: largest r such that above + S(r) <= kBand, S = inclusive sum over reversed bins
+        const int nb_bins = 1 << width;
+        const int per = kBins / kNmsThreads;
+        int loc[kBins / kNmsThreads];
+        int lsum = 0;
+#pragma unroll
+        for (int j = 0; j < per; ++j) {
+          const int r = tid * per + j;
+          loc[j] = (r < nb_bins) ? s_hist[nb_bins - 1 - r] : 0;
+          lsum += loc[j];
+        }
+        int tot_in_bucket;
+        int run = above + block_exclusive_scan(lsum, s_scan, tot_in_bucket);
+        int n_ok = 0, last_ok_sum = -1;
+#pragma unroll
+        for (int j = 0; j < per; ++j) {
+          run += loc[j];
+          const int r = tid * per + j;
+          if (r < nb_bins && run <= kBand) { ++n_ok; last_ok_sum = run; }
+        }
+        if (tid == 0) { s_sel_r = 0; s_sel_cnt = above; }
+        __syncthreads();
+        if (n_ok) {
+          atomicAdd(&s_sel_r, n_ok);
+          atomicMax(&s_sel_cnt, last_ok_sum);  // S is monotone: the largest accepted running sum
+        }
+        __syncthreads();
+        const int n_take_bins = s_sel_r;   // digits nb_bins-1 .. nb_bins-n_take_bins are taken whole
+        const int cnt_take = s_sel_cnt;
+        const int d_star = nb_bins - n_take_bins;
+        __syncthreads();
+        if (cnt_take >= min(kBandMin, remaining) || shift == 0) {
+          if (d_star < nb_bins) lo_key = ((top >= 64 ? 0ull : (prefix << width)) | (unsigned long long)d_star) << shift;
+          else lo_key = (prefix + 1ull) << top;  // nothing of this bucket: only the keys above it (top < 64 here)
+          break;
+        }
+        prefix = (top >= 64 ? 0ull : (prefix << width)) | (unsigned long long)(d_star - 1);  // refine inside the overflowing bin
+        above = cnt_take;
+      }
+    }
+    // ---- b. gather + sort the band -----------------------------------------------------------------------
+    if (tid == 0) { s_nb = 0; s_nk = 0; }
+    __syncthreads();
+    for (int i = tid; i < total; i += kNmsThreads) {
+      const unsigned long long k = cand_key(i);
+      if (k < hi_key && k >= lo_key) {
+        const int pos = atomicAdd(&s_nb, 1);
+        if (pos < kBand) s_band[pos] = odk_key2_to_key1(k);
+      }
+    }
+    __syncthreads();
+    const int nb = min(s_nb, kBand);
+    int n_pad = 2;
+    while (n_pad < nb) n_pad <<= 1;
+    for (int i = nb + tid; i < n_pad; i += kNmsThreads) s_band[i] = 0ull;
+    __syncthreads();
+    if (nb > 1) bitonic_sort_shared(s_band, n_pad, 0, 2, n_pad);
+    hi_key = lo_key;
+    processed += nb;
+
+    // ---- c. boxes of the band (lazy decode) + class segments ---------------------------------------------
+    int my_cls = -1;
+    bool seg_start = false;
+    if (tid < nb) {
+      const unsigned long long k1 = s_band[tid];
+      const int a = (int)(k1 & ODK_IDX_MASK);
+      my_cls = odk_key1_class(k1);
+      float4 box;
+      if (p.boxes != nullptr) box = p.boxes[(size_t)b * p.n + a];
+      else box = odk_decode_box(p.locs[(size_t)b * p.n + a], __ldg(p.av.locs + a), __ldg(p.av.scale + a));
+      const float w = __fsub_rn(box.z, box.x), h = __fsub_rn(box.w, box.y);
+      s_box[tid] = box;
+      s_area[tid] = __fmul_rn(w, h);
+      s_alive[tid] = !(p.skip_empty && (w <= 0.0f || h <= 0.0f));  // ml.py:610-611
+      s_keep[tid] = 0;
+      seg_start = (tid == 0) || (odk_key1_class(s_band[tid - 1]) != my_cls);
+    }
+    {
+      int nseg;
+      const int pos = block_exclusive_scan(seg_start ? 1 : 0, s_scan, nseg);
+      if (seg_start) s_seg[pos] = tid;
+      if (tid == 0) { s_seg[nseg] = nb; s_nseg = nseg; }
+    }
+    __syncthreads();
+    // ---- d. drop what earlier rounds' kept boxes suppress -------------------------------------------------
+    if (nkept > 0 && tid < nb && s_alive[tid]) {
+      const float4 box = s_box[tid];
+      const float area = s_area[tid];
+      const float a_hi = area * p.ft.k_hi, a_lo = area * p.ft.k_lo;
+      bool dead = false;
+      for (int k = 0; k < nkept; ++k)
+        if (kcls[k] == my_cls) dead |= pair_hit<GE>(box, area, a_hi, a_lo, kbox[k], karea[k], p.iou_thr, p.ft, fast);
+      if (dead) s_alive[tid] = 0;
+    }
+    __syncthreads();
+    // ---- e. one warp per class segment ---------------------------------------------------------------------
+    const int nseg = s_nseg;
+    for (int sg = warp; sg < nseg; sg += kNmsWarps) {
+      const int s0 = s_seg[sg], s1 = s_seg[sg + 1];
+      int seg_kept = 0;
+      for (int base = s0; base < s1; base += 32) {
+        const int i = base + lane;
+        const bool have = i < s1;
+        const float4 box = have ? s_box[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float area = have ? s_area[i] : 0.f;
+        const float a_hi = area * p.ft.k_hi, a_lo = area * p.ft.k_lo;
+        bool alive = have && s_alive[i];
+        // earlier chunks of this segment: only their kept entries matter (uniform trip count)
+        if (seg_kept > 0) {
+          bool dead = false;
+          for (int e = s0; e < base; ++e)
+            if (s_keep[e]) dead |= pair_hit<GE>(box, area, a_hi, a_lo, s_box[e], s_area[e], p.iou_thr, p.ft, fast);
+          alive = alive && !dead;
+        }
+        // intra-chunk: sup bit j of lane i = "i suppresses j" (i before j)
+        const unsigned am = __ballot_sync(0xffffffffu, alive);
+        unsigned sup = 0;
+        for (unsigned rem = am & (am - 1); rem; rem &= rem - 1) {  // every alive lane except the first
+          const int j = __ffs(rem) - 1;
+          float4 bj;
+          bj.x = __shfl_sync(0xffffffffu, box.x, j);
+          bj.y = __shfl_sync(0xffffffffu, box.y, j);
+          bj.z = __shfl_sync(0xffffffffu, box.z, j);
+          bj.w = __shfl_sync(0xffffffffu, box.w, j);
+          const float aj = __shfl_sync(0xffffffffu, area, j);
+          if (alive && lane < j && pair_hit<GE>(box, area, a_hi, a_lo, bj, aj, p.iou_thr, p.ft, fast)) sup |= 1u << j;
+        }
+        unsigned removed = 0, keep = 0;
+        for (unsigned rem = am; rem; rem &= rem - 1) {
+          const int l = __ffs(rem) - 1;
+          const unsigned sup_l = __shfl_sync(0xffffffffu, sup, l);
+          if (!((removed >> l) & 1u)) {
+            keep |= 1u << l;
+            removed |= sup_l;
+          }
+        }
+        if ((keep >> lane) & 1u) s_keep[i] = 1;
+        seg_kept += __popc(keep);
+        __syncwarp();
+      }
+      if (lane == 0 && seg_kept) atomicAdd(&s_nk, seg_kept);
+    }
+    __syncthreads();
+    // ---- f. survivors -> global order -> kept list + output ---------------------------------------------------
+    const int nk = s_nk;
+    if (nk > 0) {
+      // order key = [flip(score):32][4095-class:12][kBand-1-slot:9]: equal (score, class) -> lower slot = higher anchor first
+      for (int i = tid; i < n_pad; i += kNmsThreads) {
+        unsigned long long v = 0ull;
+        if (i < nb && s_keep[i]) {
+          const unsigned long long k1 = s_band[i];
+          v = (((k1 >> ODK_IDX_BITS) & 0xffffffffull) << 21) | ((k1 >> (32 + ODK_IDX_BITS)) << 9) | (unsigned long long)(kBand - 1 - i);
+          v |= 1ull << 63;  // survivors sort above the zero padding even for the smallest score
+        }
+        s_order[i] = v;
+      }
+      __syncthreads();
+      bitonic_sort_shared(s_order, n_pad, 0, 2, n_pad);
+      const int take = min(nk, limit - nkept);
+      if (tid < take) {
+        const unsigned long long v = s_order[tid];
+        const int slot = kBand - 1 - (int)(v & (unsigned long long)(kBand - 1));
+        const unsigned long long k1 = s_band[slot];
+        const int a = (int)(k1 & ODK_IDX_MASK);
+        const int cls = odk_key1_class(k1);
+        const float4 bx = s_box[slot];
+        const int r = nkept + tid;
+        kbox[r] = bx;
+        karea[r] = s_area[slot];
+        kcls[r] = cls;
+        if (p.out != nullptr && r < p.top_k) {
+          float* o = p.out + ((size_t)b * p.top_k + r) * 6;
+          o[0] = (float)cls;
+          o[1] = odk_unflip_score((uint32_t)((k1 >> ODK_IDX_BITS) & 0xffffffffull));
+          o[2] = bx.x; o[3] = bx.y; o[4] = bx.z; o[5] = bx.w;
+          p.kept_index[(size_t)b * p.top_k + r] = a;
+        }
+        if (p.out_index != nullptr) p.out_index[r] = a;
+      }
+      nkept += take;
+    }
+    __syncthreads();
+  }
+  // ---- zero padding (layers.py:969) / count ---------------------------------------------------------------------
+  if (p.out != nullptr) {
+    for (int r = nkept + tid; r < p.top_k; r += kNmsThreads) {
+      float* o = p.out + ((size_t)b * p.top_k + r) * 6;
+      o[0] = o[1] = o[2] = o[3] = o[4] = o[5] = 0.0f;
+      p.kept_index[(size_t)b * p.top_k + r] = -1;
+    }
+  }
+  if (p.out_count != nullptr && tid == 0) *p.out_count = nkept;
 }
 
 }  // namespace
 
 // ---- workspace layout ------------------------------------------------------------------------------------
 struct NmsWorkspace {
-  int* cand_count;              // [B]
-  int* seg_off;                 // [B, C+1]
-  int* kept_count;              // [B, C]
-  unsigned long long* cand_keys;  // [B, cap]
-  unsigned long long* kept_keys;  // [B, C, L]
-  float4* boxes;                // [B, N]  (fused mode)
-  int cap, limit;
+  int* piece_count;               // [B, ceil(N/32)]   (only n_pieces per image are used)
+  unsigned long long* cand_keys;  // [B, round_up(N, 256)]
   size_t bytes;
 };
 
-static NmsWorkspace nms_layout(void* base, int batch, int n, int num_classes, int top_k) {
+static NmsWorkspace nms_layout(void* base, int batch, int n) {
   NmsWorkspace w;
-  w.cap = odk_next_pow2(n < 2 ? 2 : n);
-  w.limit = top_k < 2 ? 2 : top_k;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = odk_align_up(off + bytes, 256); return o; };
-  const size_t o_cnt = take(sizeof(int) * (size_t)batch);
-  const size_t o_seg = take(sizeof(int) * (size_t)batch * (num_classes + 1));
-  const size_t o_kc = take(sizeof(int) * (size_t)batch * num_classes);
-  const size_t o_ck = take(8 * (size_t)batch * w.cap);
-  const size_t o_kk = take(8 * (size_t)batch * num_classes * w.limit);
-  const size_t o_bx = take(16 * (size_t)batch * n);
+  const size_t o_cnt = take(sizeof(int) * (size_t)batch * ((n + 31) / 32));
+  const size_t o_ck = take(8 * (size_t)batch * odk_align_up((size_t)n, 256));
   char* p = static_cast<char*>(base);
-  w.cand_count = reinterpret_cast<int*>(p + o_cnt);
-  w.seg_off = reinterpret_cast<int*>(p + o_seg);
-  w.kept_count = reinterpret_cast<int*>(p + o_kc);
+  w.piece_count = reinterpret_cast<int*>(p + o_cnt);
   w.cand_keys = reinterpret_cast<unsigned long long*>(p + o_ck);
-  w.kept_keys = reinterpret_cast<unsigned long long*>(p + o_kk);
-  w.boxes = reinterpret_cast<float4*>(p + o_bx);
   w.bytes = off;
   return w;
-}
-
-size_t odk_nms_workspace_bytes_impl(int batch, int n, int num_classes, int top_k) {
-  return nms_layout(nullptr, batch, n, num_classes, top_k).bytes;
 }
 
 static int nms_check(int batch, int n, int num_classes, int top_k, const void* ws, size_t ws_bytes) {
   ODK_REQUIRE(batch >= 1 && n >= 1 && num_classes >= 1 && top_k >= 0, ODK_ERR_INVALID_ARGUMENT,
               "nms: bad sizes batch=%d n=%d classes=%d top_k=%d", batch, n, num_classes, top_k);
-  ODK_REQUIRE(n <= (int)ODK_IDX_MASK, ODK_ERR_UNSUPPORTED, "nms: n=%d exceeds the 20-bit anchor field", n);
+  ODK_REQUIRE(n < (int)ODK_IDX_MASK, ODK_ERR_UNSUPPORTED, "nms: n=%d exceeds the 20-bit anchor field", n);
   ODK_REQUIRE(num_classes <= ODK_MAX_CLASSES, ODK_ERR_UNSUPPORTED, "nms: num_classes=%d > %d", num_classes, ODK_MAX_CLASSES);
-  const long long kept_cap = (long long)num_classes * (top_k < 2 ? 2 : top_k);
-  ODK_REQUIRE(kept_cap <= kSortChunk, ODK_ERR_UNSUPPORTED,
-              "nms: num_classes*max(top_k,2)=%lld exceeds the %d-key shared-memory merge", kept_cap, kSortChunk);
-  ODK_REQUIRE((size_t)(top_k < 2 ? 2 : top_k) * 20 <= 200 * 1024, ODK_ERR_UNSUPPORTED, "nms: top_k=%d too large", top_k);
-  ODK_REQUIRE(ws != nullptr && ws_bytes >= odk_nms_workspace_bytes_impl(batch, n, num_classes, top_k), ODK_ERR_WORKSPACE,
-              "nms: workspace of %zu bytes is smaller than the required %zu", ws_bytes,
-              odk_nms_workspace_bytes_impl(batch, n, num_classes, top_k));
+  ODK_REQUIRE(top_k <= 4096, ODK_ERR_UNSUPPORTED, "nms: top_k=%d > 4096 (kept list lives in shared memory)", top_k);
+  const size_t need = nms_layout(nullptr, batch, n).bytes;
+  ODK_REQUIRE(ws != nullptr && ws_bytes >= need, ODK_ERR_WORKSPACE, "nms: workspace of %zu bytes is smaller than the required %zu", ws_bytes,
+              need);
   ODK_REQUIRE(((uintptr_t)ws & 255) == 0, ODK_ERR_INVALID_ARGUMENT, "nms: workspace must be 256-byte aligned");
   return ODK_OK;
 }
 
-// sort -> sweep -> merge on an already filled candidate list
-static int nms_run(const NmsWorkspace& w, int batch, int n, int num_classes, const float4* boxes, float iou_thr, int top_k,
-                   int iou_ge, float* out, int32_t* kept_index, cudaStream_t stream) {
-  ODK_CUDA(cudaFuncSetAttribute(sort_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortChunk * 8));
-  ODK_CUDA(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortChunk * 8));
-  ODK_CUDA(cudaFuncSetAttribute(nms_sweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  ODK_CUDA(cudaFuncSetAttribute(nms_sweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+// select + sort + sweep + output on already emitted candidate pieces
+static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch, int n, int piece, const float4* boxes, const float4* locs,
+                   float iou_thr, int top_k, int limit, int iou_ge, float* out, int32_t* kept_index, int32_t* out_index, int32_t* out_count,
+                   cudaStream_t stream) {
+  NmsArgs a;
+  if (anchors != nullptr) a.av = odk_view(anchors);
+  else memset(&a.av, 0, sizeof(a.av));
+  a.n = n; a.piece = piece; a.n_pieces = (n + piece - 1) / piece;
+  ODK_REQUIRE(a.n_pieces <= kMaxPieces, ODK_ERR_UNSUPPORTED, "nms: %d candidate pieces per image > %d", a.n_pieces, kMaxPieces);
+  a.cand_keys = w.cand_keys; a.piece_count = w.piece_count;
+  a.boxes = boxes; a.locs = locs;
+  a.iou_thr = iou_thr;
+  a.ft.enabled = (iou_thr > 1e-3f && iou_thr < 0.999f) ? 1 : 0;
+  const double kk = a.ft.enabled ? (double)iou_thr / (1.0 + (double)iou_thr) : 0.0;
+  a.ft.k_hi = (float)(kk * (1.0 + 3e-5));
+  a.ft.k_lo = (float)(kk * (1.0 - 3e-5));
+  a.limit = limit; a.top_k = top_k; a.skip_empty = iou_ge ? 1 : 0;
+  a.out = out; a.kept_index = kept_index; a.out_index = out_index; a.out_count = out_count;
+  const size_t smem = odk_align_up((size_t)(limit < 1 ? 1 : limit) * 24, 16) + sizeof(int) * ((size_t)a.n_pieces + 1);
+  auto kern = iou_ge ? nms_image_kernel<true> : nms_image_kernel<false>;
+  ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
   {
-    OdkProfileScope prof_("sort_candidates_kernel", stream);
-    sort_candidates_kernel<<<batch, kSortThreads, kSortChunk * 8, stream>>>(w.cand_keys, w.cand_count, w.cap, num_classes, w.seg_off);
+    OdkProfileScope prof_("nms_image_kernel", stream);
+    kern<<<batch, kNmsThreads, smem, stream>>>(a);
   }
-  ODK_LAUNCH_CHECK("sort_candidates_kernel");
-  const int limit = iou_ge ? w.limit : top_k;
-  FastThr ft;
-  ft.enabled = (iou_thr > 1e-3f && iou_thr < 0.999f) ? 1 : 0;
-  const double kk = ft.enabled ? (double)iou_thr / (1.0 + (double)iou_thr) : 0.0;
-  ft.k_hi = (float)(kk * (1.0 + 3e-5));
-  ft.k_lo = (float)(kk * (1.0 - 3e-5));
-  dim3 grid(num_classes, batch);
-  const size_t sweep_smem = (size_t)w.limit * 20;
-  if (iou_ge)
-    {
-      OdkProfileScope prof_("nms_sweep_kernel", stream);
-      nms_sweep_kernel<true><<<grid, kSweepWarps * 32, sweep_smem, stream>>>(w.cand_keys, w.cap, w.seg_off, num_classes, n, boxes, iou_thr,
-                                                                             ft, limit, w.limit, 1, w.kept_keys, w.kept_count);
-    }
-  else
-    {
-      OdkProfileScope prof_("nms_sweep_kernel", stream);
-      nms_sweep_kernel<false><<<grid, kSweepWarps * 32, sweep_smem, stream>>>(w.cand_keys, w.cap, w.seg_off, num_classes, n, boxes, iou_thr,
-                                                                              ft, limit, w.limit, 0, w.kept_keys, w.kept_count);
-    }
-  ODK_LAUNCH_CHECK("nms_sweep_kernel");
-  if (out != nullptr) {
-    int pad = odk_next_pow2(num_classes * w.limit);
-    if (pad < 2) pad = 2;
-    {
-      OdkProfileScope prof_("topk_merge_kernel", stream);
-      topk_merge_kernel<<<batch, 256, (size_t)pad * 8, stream>>>(w.kept_keys, w.kept_count, num_classes, w.limit, n, boxes, top_k, out,
-                                                                 kept_index);
-    }
-    ODK_LAUNCH_CHECK("topk_merge_kernel");
-  }
+  ODK_LAUNCH_CHECK("nms_image_kernel");
   return ODK_OK;
 }
 
+int odk_piece_size(int num_classes);
 int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
                             int32_t* classes, float* confs, float* boxes, bool dense, float conf_thr,
-                            unsigned long long* cand_keys, int* cand_count, int cand_cap, cudaStream_t stream);
+                            unsigned long long* cand_keys, int* piece_count, cudaStream_t stream);
 
 extern "C" size_t odk_nms_workspace_bytes(int batch, int n, int num_classes, int top_k) {
   if (batch < 1 || n < 1 || num_classes < 1 || top_k < 0) return 0;
-  return odk_nms_workspace_bytes_impl(batch, n, num_classes, top_k);
+  return nms_layout(nullptr, batch, n).bytes;
+}
+
+static int collect(const NmsWorkspace& w, int batch, int n, int num_classes, const int32_t* classes, const float* confs, float conf_thr,
+                   int take_all, cudaStream_t stream) {
+  dim3 grid((n + kCollectPiece - 1) / kCollectPiece, batch);
+  ODK_REQUIRE(batch <= 65535, ODK_ERR_UNSUPPORTED, "nms: batch=%d > 65535", batch);
+  {
+    OdkProfileScope prof_("collect_pieces_kernel", stream);
+    collect_pieces_kernel<<<grid, kCollectPiece, 0, stream>>>(n, num_classes, classes, confs, conf_thr, take_all, w.cand_keys, w.piece_count);
+  }
+  ODK_LAUNCH_CHECK("collect_pieces_kernel");
+  return ODK_OK;
 }
 
 extern "C" int odk_nms_layer(int batch, int n, int num_classes, const int32_t* classes, const float* confs, const float* boxes,
@@ -399,15 +507,10 @@ extern "C" int odk_nms_layer(int batch, int n, int num_classes, const int32_t* c
   if (int rc = nms_check(batch, n, num_classes, top_k, workspace, workspace_bytes)) return rc;
   ODK_REQUIRE(classes && confs && boxes && out && kept_index, ODK_ERR_INVALID_ARGUMENT, "nms_layer: null pointer");
   ODK_REQUIRE(((uintptr_t)boxes & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "nms_layer: boxes must be 16-byte aligned");
-  NmsWorkspace w = nms_layout(workspace, batch, n, num_classes, top_k);
-  ODK_CUDA(cudaMemsetAsync(w.cand_count, 0, sizeof(int) * (size_t)batch, stream));
-  dim3 grid((n + 255) / 256, batch);
-  {
-    OdkProfileScope prof_("collect_candidates_kernel", stream);
-    collect_candidates_kernel<<<grid, 256, 0, stream>>>(n, num_classes, classes, confs, conf_thr, 0, w.cand_keys, w.cand_count, w.cap);
-  }
-  ODK_LAUNCH_CHECK("collect_candidates_kernel");
-  return nms_run(w, batch, n, num_classes, reinterpret_cast<const float4*>(boxes), iou_thr, top_k, iou_ge, out, kept_index, stream);
+  NmsWorkspace w = nms_layout(workspace, batch, n);
+  if (int rc = collect(w, batch, n, num_classes, classes, confs, conf_thr, 0, stream)) return rc;
+  return nms_run(w, nullptr, batch, n, kCollectPiece, reinterpret_cast<const float4*>(boxes), nullptr, iou_thr, top_k, top_k, iou_ge, out,
+                 kept_index, nullptr, nullptr, stream);
 }
 
 extern "C" int odk_decode_nms(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs, float conf_thr,
@@ -417,13 +520,14 @@ extern "C" int odk_decode_nms(const odk_anchors* a, int batch, const float* objs
   ODK_REQUIRE(a != nullptr, ODK_ERR_INVALID_ARGUMENT, "decode_nms: null anchors handle");
   if (int rc = nms_check(batch, a->n, a->num_classes, top_k, workspace, workspace_bytes)) return rc;
   ODK_REQUIRE(objs && clfs && locs && out && kept_index, ODK_ERR_INVALID_ARGUMENT, "decode_nms: null pointer");
-  ODK_REQUIRE((((uintptr_t)objs | (uintptr_t)clfs | (uintptr_t)locs) & 3) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_nms: inputs must be 4-byte aligned");
-  NmsWorkspace w = nms_layout(workspace, batch, a->n, a->num_classes, top_k);
-  ODK_CUDA(cudaMemsetAsync(w.cand_count, 0, sizeof(int) * (size_t)batch, stream));
-  if (int rc = odk_launch_decode_score(a, batch, objs, clfs, locs, nullptr, nullptr, reinterpret_cast<float*>(w.boxes), false, conf_thr,
-                                       w.cand_keys, w.cand_count, w.cap, stream))
+  ODK_REQUIRE((((uintptr_t)objs | (uintptr_t)clfs) & 3) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_nms: inputs must be 4-byte aligned");
+  ODK_REQUIRE(((uintptr_t)locs & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_nms: locs must be 16-byte aligned");
+  NmsWorkspace w = nms_layout(workspace, batch, a->n);
+  if (int rc = odk_launch_decode_score(a, batch, objs, clfs, locs, nullptr, nullptr, nullptr, false, conf_thr, w.cand_keys, w.piece_count,
+                                       stream))
     return rc;
-  return nms_run(w, batch, a->n, a->num_classes, w.boxes, iou_thr, top_k, iou_ge, out, kept_index, stream);
+  return nms_run(w, a, batch, a->n, odk_piece_size(a->num_classes), nullptr, reinterpret_cast<const float4*>(locs), iou_thr, top_k, top_k,
+                 iou_ge, out, kept_index, nullptr, nullptr, stream);
 }
 
 extern "C" int odk_nms(const float* boxes, const float* scores, int n, int top_k, float iou_thr, int iou_ge, int32_t* out_index,
@@ -434,22 +538,13 @@ extern "C" int odk_nms(const float* boxes, const float* scores, int n, int top_k
     ODK_CUDA(cudaMemsetAsync(out_count, 0, sizeof(int32_t), stream));
     return ODK_OK;
   }
-  if (int rc = nms_check(1, n, 1, top_k, workspace, workspace_bytes)) return rc;
+  if (int rc = nms_check(1, n, 1, top_k < 0 ? 0 : top_k, workspace, workspace_bytes)) return rc;
   ODK_REQUIRE(boxes && scores, ODK_ERR_INVALID_ARGUMENT, "nms: null input pointer");
   ODK_REQUIRE(((uintptr_t)boxes & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "nms: boxes must be 16-byte aligned");
-  NmsWorkspace w = nms_layout(workspace, 1, n, 1, top_k);
-  ODK_CUDA(cudaMemsetAsync(w.cand_count, 0, sizeof(int), stream));
-  dim3 grid((n + 255) / 256, 1);
-  {
-    OdkProfileScope prof_("collect_candidates_kernel", stream);
-    collect_candidates_kernel<<<grid, 256, 0, stream>>>(n, 1, nullptr, scores, 0.f, 1, w.cand_keys, w.cand_count, w.cap);
-  }
-  ODK_LAUNCH_CHECK("collect_candidates_kernel");
-  if (int rc = nms_run(w, 1, n, 1, reinterpret_cast<const float4*>(boxes), iou_thr, top_k, iou_ge, nullptr, nullptr, stream)) return rc;
-  {
-    OdkProfileScope prof_("export_kept_kernel", stream);
-    export_kept_kernel<<<1, 256, 0, stream>>>(w.kept_keys, w.kept_count, out_index, out_count);
-  }
-  ODK_LAUNCH_CHECK("export_kept_kernel");
-  return ODK_OK;
+  NmsWorkspace w = nms_layout(workspace, 1, n);
+  if (int rc = collect(w, 1, n, 1, nullptr, scores, 0.f, 1, stream)) return rc;
+  // ml.py:612-623: the length check sits only in the non-first branch -> at least two results (SURVEY A-7)
+  const int limit = iou_ge ? (top_k < 2 ? 2 : top_k) : (top_k < 0 ? 0 : top_k);
+  return nms_run(w, nullptr, 1, n, kCollectPiece, reinterpret_cast<const float4*>(boxes), nullptr, iou_thr, 0, limit, iou_ge, nullptr, nullptr,
+                 out_index, out_count, stream);
 }

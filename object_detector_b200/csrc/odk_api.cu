@@ -19,7 +19,7 @@ int odk_set_error(int code, const char* fmt, ...) {
 
 int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
                             int32_t* classes, float* confs, float* boxes, bool dense, float conf_thr,
-                            unsigned long long* cand_keys, int* cand_count, int cand_cap, cudaStream_t stream);
+                            unsigned long long* cand_keys, int* piece_count, cudaStream_t stream);
 int odk_launch_decode_locs(const odk_anchors* a, long long rows, const float* pred, float* out, cudaStream_t stream);
 
 // ---- per-launch event timing (used by bench.py for the roofline line) -------------------------------
@@ -170,6 +170,6 @@ extern "C" int odk_decode_score(const odk_anchors* a, int batch, const float* ob
   ODK_REQUIRE(a != nullptr && batch >= 1, ODK_ERR_INVALID_ARGUMENT, "decode_score: bad arguments");
   ODK_REQUIRE(objs && clfs && locs && classes && confs && boxes, ODK_ERR_INVALID_ARGUMENT, "decode_score: null pointer");
   ODK_REQUIRE(((uintptr_t)boxes & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_score: boxes must be 16-byte aligned");
-  return odk_launch_decode_score(a, batch, objs, clfs, locs, classes, confs, boxes, true, 0.f, nullptr, nullptr, 0,
+  return odk_launch_decode_score(a, batch, objs, clfs, locs, classes, confs, boxes, true, 0.f, nullptr, nullptr,
                                  static_cast<cudaStream_t>(stream));
 }

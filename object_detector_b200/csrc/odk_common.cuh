@@ -142,6 +142,30 @@ __device__ __forceinline__ unsigned long long odk_key1_to_key2(unsigned long lon
   return (score << 32) | (cls_field << ODK_IDX_BITS) | (k & ODK_IDX_MASK);
 }
 
+__device__ __forceinline__ unsigned long long odk_make_key2(int cls, float conf, int idx) {
+  return ((unsigned long long)odk_flip_score(conf) << 32) |
+         ((unsigned long long)(ODK_MAX_CLASSES - 1 - cls) << ODK_IDX_BITS) | (unsigned long long)idx;
+}
+__device__ __forceinline__ unsigned long long odk_key2_to_key1(unsigned long long k) {
+  const unsigned long long score = k >> 32;
+  const unsigned long long cls_field = (k >> ODK_IDX_BITS) & (ODK_MAX_CLASSES - 1);
+  return (cls_field << (32 + ODK_IDX_BITS)) | (score << ODK_IDX_BITS) | (k & ODK_IDX_MASK);
+}
+__device__ __forceinline__ int odk_key2_class(unsigned long long k) {
+  return ODK_MAX_CLASSES - 1 - (int)((k >> ODK_IDX_BITS) & (ODK_MAX_CLASSES - 1));
+}
+__device__ __forceinline__ float odk_key2_score(unsigned long long k) { return odk_unflip_score((uint32_t)(k >> 32)); }
+
+// The fp32 decode of od_pb.py:216-222 as the Keras Lambda evaluates it (od_net.py:189).
+__device__ __forceinline__ float4 odk_decode_box(const float4 pr, const float4 lc, const float2 sc) {
+  float4 box;
+  box.x = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.x, sc.x), lc.x), 0.0f), 1.0f);
+  box.y = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.y, sc.y), lc.y), 0.0f), 1.0f);
+  box.z = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.z, sc.x), lc.z), 0.0f), 1.0f);
+  box.w = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.w, sc.y), lc.w), 0.0f), 1.0f);
+  return box;
+}
+
 // ---- warp helpers ------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned odk_lane() { return threadIdx.x & 31u; }
 
