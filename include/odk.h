@@ -78,10 +78,12 @@ int odk_decode_locs(const odk_anchors* a, int64_t rows, const float* pred /*[dev
 /* PriorBoxes._assign_boxes (od_pb.py:315-363) for a padded batch.  Outputs per image b with
  * G = gt_count[b]: pb_indices[b, 0:G] ascending anchor ids, gt_indices[b, 0:G] the GT each one
  * owns (both -1 beyond G), status[b] one of ODK_IMG_*. */
+size_t odk_assign_workspace_bytes(const odk_anchors* a, int batch, int gmax); /* scratch for odk_assign / odk_assign_encode */
 int odk_assign(const odk_anchors* a, int batch, const float* gt_boxes /*[dev B,Gmax,4]*/,
                const int32_t* gt_count /*[dev B]*/, int gmax,
                int64_t* pb_indices /*[dev B,Gmax]*/, int64_t* gt_indices /*[dev B,Gmax]*/,
-               int32_t* status /*[dev B]*/, void* stream);
+               int32_t* status /*[dev B]*/, void* workspace /*[dev]*/, size_t workspace_bytes,
+               void* stream);
 
 /* PriorBoxes.encode_truth (od_pb.py:299-313) = odk_assign + the y_true writer.
  * y_true[b, n, :] = [mask, weight, obj, onehot(C), locs(4)] fp32, written in full (no pre-zeroing
@@ -91,7 +93,8 @@ int odk_assign_encode(const odk_anchors* a, int batch, const float* gt_boxes /*[
                       const int32_t* gt_count /*[dev B]*/, int gmax,
                       float* y_true /*[dev B,N,3+C+4]*/, int64_t* pb_indices /*[dev B,Gmax]*/,
                       int64_t* gt_indices /*[dev B,Gmax]*/, uint8_t* pb_valids /*[dev B,N] or NULL*/,
-                      int32_t* status /*[dev B]*/, void* stream);
+                      int32_t* status /*[dev B]*/, void* workspace /*[dev]*/, size_t workspace_bytes,
+                      void* stream);
 
 /* ChannelArgMax + ChannelMax + _objconf + decode_locs (layers.py:69-98, od_net.py:177-189):
  * classes = argmax_c clfs, confs = objs*max_c clfs*pb_mask, boxes = decode(locs). */

@@ -24,9 +24,11 @@ SIGNATURES = {
     'odk_compute_iou': (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     'odk_encode_locs': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     'odk_decode_locs': (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
-    'odk_assign': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    'odk_assign_workspace_bytes': (c_size_t, [c_void_p, c_int, c_int]),
+    'odk_assign': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                           c_void_p]),
     'odk_assign_encode': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
-                                  c_void_p, c_void_p, c_void_p, c_void_p]),
+                                  c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_decode_score': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                  c_void_p]),
     'odk_nms_workspace_bytes': (c_size_t, [c_int, c_int, c_int, c_int]),

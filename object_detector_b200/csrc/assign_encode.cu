@@ -1,16 +1,19 @@
 // K3 + K4 — training-target generation: PriorBoxes._assign_boxes + encode_truth
 // (dl/od_pb.py:299-363), plus the small drop-ins compute_iou / encode_locs.
 //
-// K3 assign_greedy_kernel — ONE WARP PER IMAGE.  The reference's loop over ground-truth boxes is
-//   inherently sequential (each GT removes one anchor), so parallelism is lanes-over-candidates and
-//   warps-over-images:
-//     * GT order = ascending fp32 area, ties by index (argsort, od_pb.py:327; SURVEY A-6);
-//     * primary rule (od_pb.py:336-346): the anchors whose pb_grid cell contains the GT centre are
-//       found through the anchor layout (floor(c*m) +-1 cells x patterns x maps — at most
-//       9*P*maps table probes, each decided by the exact fp32 in_range test on the pb_grid table),
-//       cost = sum |encode_locs| in fp64 in NumPy's order, warp-shuffle arg-min (lowest index wins);
-//     * fallback (od_pb.py:347-352): warp-wide arg-max of the exact fp32 IoU over free valid anchors;
-//     * "taken" state = an N-bit bitmap in shared memory.
+// K3 — the reference's loop over ground-truth boxes is inherently sequential (each GT removes one
+//   anchor), but everything that does not depend on the "taken" state is not:
+//   assign_candidates_kernel — ONE WARP PER (image, GT), grid-wide.  Primary rule (od_pb.py:336-346):
+//       the anchors whose pb_grid cell contains the GT centre are found through the anchor layout
+//       (floor(c*m) +-1 cells x patterns x maps — at most 9*P*maps table probes, each decided by the
+//       exact fp32 in_range test on the pb_grid table), cost = sum |encode_locs| in fp64 in NumPy's
+//       order; the in-cell anchors are ranked by (cost, index) and the first L ranks go to the workspace.
+//   assign_greedy_kernel — ONE CTA PER IMAGE: GT order = ascending fp32 area, ties by index (argsort,
+//       od_pb.py:327; SURVEY A-6); the ranked lists are staged in shared memory and one warp walks the
+//       GTs in that order taking the first free anchor of each list ("taken" = an N-bit bitmap in
+//       shared memory).  Exhausted prefix -> exact re-evaluation over the free in-cell anchors;
+//       no free in-cell anchor -> fallback (od_pb.py:347-352): CTA-wide arg-max of the exact fp32 IoU
+//       over free valid anchors, first maximum wins.
 //   Emits pb_indices (ascending anchor id) / gt_indices / status.
 // K4 encode_rows_kernel — one CTA per (image, 128-anchor tile): computes the order-independent
 //   ignore mask  pb_mask & any_g IoU(g, a) >= 0.5  (closed form of od_pb.py:355-361, SURVEY A-4)
@@ -24,7 +27,6 @@
 
 namespace {
 
-constexpr int kEncodeTile = 128;
 
 struct AssignArgs {
   AnchorView av;
@@ -37,6 +39,10 @@ struct AssignArgs {
   int32_t* status;
   int list_len;  // ranked candidates remembered per GT
   int bitmap_words;
+  int* ws_list;   // [B, Gmax, list_len] ranked in-cell anchors
+  int* ws_ncand;  // [B, Gmax] in-cell valid anchors of the GT
+  int* ws_nlist;  // [B, Gmax] entries stored in its ranked list
+  unsigned* ws_ignore;  // [B, bitmap_words] bit a = "pb_mask[a] and some GT has IoU >= 0.5 with anchor a" (pre-zeroed) or null
 };
 
 __device__ __forceinline__ double encode_cost(const float4 box, const float4 loc, const double2 sz) {
@@ -97,6 +103,91 @@ __device__ __forceinline__ bool cand_less(double c0, int a0, double c1, int a1) 
   return c0 < c1 || (c0 == c1 && a0 < a1);  // argmin -> first minimum = lowest anchor index (od_pb.py:343)
 }
 
+// Phase A: every in-cell anchor of one GT ranked by (fp64 cost, index), ignoring "taken".
+__global__ void __launch_bounds__(kGreedyThreads) assign_candidates_kernel(const AssignArgs p) {
+  __shared__ double s_cost[kGreedyWarps * kScratch];
+  __shared__ int s_idx[kGreedyWarps * kScratch];
+  const int warp = threadIdx.x >> 5;
+  const int lane = (int)odk_lane();
+  const long long task = (long long)blockIdx.x * kGreedyWarps + warp;
+  if (task >= (long long)p.batch * p.gmax) return;
+  const int b = (int)(task / p.gmax), g = (int)(task % p.gmax);
+  const int g_count = p.gt_count[b];
+  if (g_count < 0 || g_count > p.gmax || g >= g_count) return;
+  const int L = p.list_len;
+  double* wc = s_cost + (size_t)warp * kScratch;
+  int* wi = s_idx + (size_t)warp * kScratch;
+  int* list = p.ws_list + ((size_t)b * p.gmax + g) * L;
+
+  const float4 box = p.gt_boxes[(size_t)b * p.gmax + g];
+  const float cx = __fmul_rn(__fadd_rn(box.z, box.x), 0.5f);  // ml.py:485-488
+  const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
+  int filled = 0;
+  const int total = for_each_cell_candidate(p.av, cx, cy, lane, [&](int a, bool ok) {
+    const unsigned m = __ballot_sync(0xffffffffu, ok);
+    if (ok) {
+      const int pos = filled + __popc(m & ((1u << lane) - 1u));
+      if (pos < kScratch) {
+        wc[pos] = encode_cost(box, __ldg(p.av.locs + a), p.av.sizes[a]);
+        wi[pos] = a;
+      }
+    }
+    filled += __popc(m);
+  });
+  __syncwarp();
+  int stored = 0;
+  if (total <= kScratch) {  // ranks are global only if every candidate made it into the scratch
+    for (int e = lane; e < total; e += 32) {
+      const double ce = wc[e];
+      const int ae = wi[e];
+      int r = 0;
+      for (int q = 0; q < total; ++q) r += cand_less(wc[q], wi[q], ce, ae);
+      if (r < L) list[r] = ae;
+    }
+    stored = min(total, L);
+  }
+  if (lane == 0) {
+    p.ws_ncand[(size_t)b * p.gmax + g] = total;
+    p.ws_nlist[(size_t)b * p.gmax + g] = stored;
+  }
+  if (p.ws_ignore == nullptr) return;
+  // ---- ignore mask, scattered per GT: pb_valids[iou >= 0.5] = False (od_pb.py:355-357; order-independent
+  //      closed form, SURVEY A-4).  Only anchors that CAN reach IoU 0.5 are visited:
+  //        IoU >= 1/2  =>  I >= (A+B)/3 and min(A,B)/max(A,B) >= 1/2;  with I <= iw*min(hg,ha) and
+  //        iw <= (wg+wa)/2 - |dcx|  this gives |dcx| <= (wg+wa)/6 (same in y).
+  //      The cell ranges below are that bound with 2% + one cell of slack; every visited anchor is then
+  //      decided by the exact fp32 expression.
+  unsigned* ignore = p.ws_ignore + (size_t)b * p.bitmap_words;
+  const float wg = __fsub_rn(box.z, box.x), hg = __fsub_rn(box.w, box.y);
+  const float ga = __fmul_rn(wg, hg);
+  for (int mi = 0; mi < p.av.n_maps; ++mi) {
+    const int m = p.av.map_size[mi];
+    for (int pat = 0; pat < p.av.n_patterns; ++pat) {
+      const int base = p.av.map_off[mi] + pat * m * m;
+      const float4 l0 = __ldg(p.av.locs + base);  // anchor of cell (0,0): all cells of this (map, pattern) share its size
+      const float wa = l0.z - l0.x, ha = l0.w - l0.y;
+      const float aa = wa * ha;
+      if (!(ga >= 0.45f * aa && ga <= 2.2f * aa)) continue;
+      const float rx = (wg + wa) * 0.17f + 1e-4f, ry = (hg + ha) * 0.17f + 1e-4f;
+      const float c0x = 0.5f * (l0.x + l0.z), c0y = 0.5f * (l0.y + l0.w);
+      const int ix_lo = max(0, (int)floorf((cx - rx - c0x) * (float)m) - 1);
+      const int ix_hi = min(m - 1, (int)ceilf((cx + rx - c0x) * (float)m) + 1);
+      const int iy_lo = max(0, (int)floorf((cy - ry - c0y) * (float)m) - 1);
+      const int iy_hi = min(m - 1, (int)ceilf((cy + ry - c0y) * (float)m) + 1);
+      const int nx = ix_hi - ix_lo + 1, ny = iy_hi - iy_lo + 1;
+      if (nx <= 0 || ny <= 0) continue;
+      for (int t = lane; t < nx * ny; t += 32) {
+        const int iy = iy_lo + t / nx, ix = ix_lo + t % nx;
+        const int a = base + iy * m + ix;
+        if (!p.av.mask[a]) continue;
+        const float4 lc = __ldg(p.av.locs + a);
+        if (odk_iou_passes<true>(box, ga, lc, odk_area(lc), 0.5f)) atomicOr(ignore + (a >> 5), 1u << (a & 31));
+      }
+    }
+  }
+}
+
+// Phase B: the sequential greedy walk, one CTA per image.
 __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const AssignArgs p) {
   extern __shared__ __align__(16) unsigned char greedy_smem[];
   const int warp = threadIdx.x >> 5;
@@ -105,16 +196,17 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   const int L = p.list_len;
   unsigned char* sp = greedy_smem;
   float4* gbox = reinterpret_cast<float4*>(sp);            sp += (size_t)p.gmax * 16;
-  double* s_cost = reinterpret_cast<double*>(sp);          sp += (size_t)kGreedyWarps * kScratch * 8;
-  int* s_idx = reinterpret_cast<int*>(sp);                 sp += (size_t)kGreedyWarps * kScratch * 4;
+  int* list = reinterpret_cast<int*>(sp);                  sp += (size_t)p.gmax * L * 4;  // 16-byte aligned (L % 8 == 0)
   float* garea = reinterpret_cast<float*>(sp);             sp += (size_t)p.gmax * 4;
   int* order = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
   int* pick = reinterpret_cast<int*>(sp);                  sp += (size_t)p.gmax * 4;
-  int* ncand = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;  // in-cell valid anchors of the GT
-  int* nlist = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;  // entries stored in its ranked list
-  int* list = reinterpret_cast<int*>(sp);                  sp += (size_t)p.gmax * L * 4;
+  int* ncand = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
+  int* nlist = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
   unsigned* taken = reinterpret_cast<unsigned*>(sp);
   __shared__ int s_err;
+  __shared__ float s_best_v[kGreedyWarps];
+  __shared__ int s_best_a[kGreedyWarps];
+  __shared__ int s_state[2];  // [0] = GT needing the CTA-wide fallback (-1: none, -2: finished), [1] = its result
 
   long long* out_pb = p.pb_indices + (size_t)b * p.gmax;
   long long* out_gt = p.gt_indices + (size_t)b * p.gmax;
@@ -128,14 +220,21 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     const float4 bx = p.gt_boxes[(size_t)b * p.gmax + g];
     gbox[g] = bx;
     garea[g] = odk_area(bx);
+    ncand[g] = p.ws_ncand[(size_t)b * p.gmax + g];
+    nlist[g] = p.ws_nlist[(size_t)b * p.gmax + g];
     if (p.gt_classes != nullptr) {
       const int c = p.gt_classes[(size_t)b * p.gmax + g];
       if (c < 0 || c >= p.av.num_classes) atomicMax(&s_err, ODK_IMG_BAD_CLASS);  // od_pb.py:304
     }
   }
   for (int w = threadIdx.x; w < p.bitmap_words; w += kGreedyThreads) taken[w] = 0u;
+  {  // stage the ranked lists: 16-byte cp.async, all in flight at once (entries beyond nlist[g] are never read)
+    const int4* src = reinterpret_cast<const int4*>(p.ws_list + (size_t)b * p.gmax * L);
+    int4* dst = reinterpret_cast<int4*>(list);
+    for (int i = threadIdx.x; i < G * (L / 4); i += kGreedyThreads) odk_cp_async<16>(dst + i, src + i);
+    odk_cp_async_commit();
+  }
   __syncthreads();
-
   if (s_err == ODK_IMG_OK) {
     // ascending-area rank, ties by index (od_pb.py:327)
     for (int g = threadIdx.x; g < G; g += kGreedyThreads) {
@@ -147,109 +246,110 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
       }
       order[r] = g;
     }
-    // ---- phase A (parallel over GTs, one warp each): every in-cell anchor of the GT ranked by
-    //      (fp64 cost, index), ignoring "taken"; the first L ranks are kept.
-    double* wc = s_cost + (size_t)warp * kScratch;
-    int* wi = s_idx + (size_t)warp * kScratch;
-    for (int g = warp; g < G; g += kGreedyWarps) {
-      const float4 box = gbox[g];
-      const float cx = __fmul_rn(__fadd_rn(box.z, box.x), 0.5f);  // ml.py:485-488
-      const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
-      int filled = 0;
-      const int total = for_each_cell_candidate(p.av, cx, cy, lane, [&](int a, bool ok) {
-        const unsigned m = __ballot_sync(0xffffffffu, ok);
-        if (ok) {
-          const int pos = filled + __popc(m & ((1u << lane) - 1u));
-          if (pos < kScratch) {
-            wc[pos] = encode_cost(box, __ldg(p.av.locs + a), p.av.sizes[a]);
-            wi[pos] = a;
-          }
-        }
-        filled += __popc(m);
-      });
-      __syncwarp();
-      int stored = 0;
-      if (total <= kScratch) {  // ranks are global only if every candidate made it into the scratch
-        for (int e = lane; e < total; e += 32) {
-          const double ce = wc[e];
-          const int ae = wi[e];
-          int r = 0;
-          for (int q = 0; q < total; ++q) r += cand_less(wc[q], wi[q], ce, ae);
-          if (r < L) list[(size_t)g * L + r] = ae;
-        }
-        stored = min(total, L);
-      }
-      if (lane == 0) { ncand[g] = total; nlist[g] = stored; }
-      __syncwarp();
-    }
   }
+  odk_cp_async_wait<0>();
   __syncthreads();
-  if (warp != 0) return;
 
-  // ---- phase B (warp 0, sequential over GTs in area order): first free anchor of each GT's list
+  // Warp 0 walks the GTs; the other warps sleep at the barrier below and wake only to help with a
+  // CTA-wide IoU arg-max when some GT has no free in-cell anchor (the crowded / stress case).
   int err = s_err;
-  if (!err) {
-    for (int r = 0; r < G; ++r) {
-      const int g = order[r];
-      if (r >= p.av.n_valid) { err = ODK_IMG_ENCODE_ERROR; break; }  // od_pb.py:331-332
-      const int nc = ncand[g];
-      if (nc == 0) { err = ODK_IMG_ENCODE_ERROR; break; }             // od_pb.py:338
-      const int nl = nlist[g];
-      int best_a = -1;
-      for (int k0 = 0; k0 < nl && best_a < 0; k0 += 32) {
-        const int k = k0 + lane;
-        const int a = (k < nl) ? list[(size_t)g * L + k] : -1;
-        const bool is_free = a >= 0 && !((taken[a >> 5] >> (a & 31)) & 1u);
-        const unsigned fm = __ballot_sync(0xffffffffu, is_free);
-        if (fm) best_a = __shfl_sync(0xffffffffu, a, __ffs(fm) - 1);
-      }
-      const float4 box = gbox[g];
-      if (best_a < 0 && nc > nl) {
-        // the ranked prefix is exhausted but more in-cell anchors exist: exact re-evaluation over the free ones
-        const float cx = __fmul_rn(__fadd_rn(box.z, box.x), 0.5f);
-        const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
-        double mc = DBL_MAX;
-        int ma = INT_MAX;
-        for_each_cell_candidate(p.av, cx, cy, lane, [&](int a, bool ok) {
-          if (!ok || ((taken[a >> 5] >> (a & 31)) & 1u)) return;  // od_pb.py:339
-          const double c = encode_cost(box, __ldg(p.av.locs + a), p.av.sizes[a]);
-          if (cand_less(c, a, mc, ma)) { mc = c; ma = a; }
-        });
+  int r = 0;
+  while (true) {
+    int need = -2;
+    if (warp == 0) {
+      if (!err) {
+        // the first 32 ranks of the next GT are fetched while the current one is decided (they do not
+        // depend on `taken`), so the serial chain per GT is: bitmap probe -> ballot -> bitmap update
+        int g_next = (r < G) ? order[r] : 0;
+        int nl_next = (r < G) ? nlist[g_next] : 0;
+        int a_next = (r < G && lane < nl_next) ? list[(size_t)g_next * L + lane] : -1;
+        for (; r < G; ++r) {
+          const int g = g_next, nl = nl_next, a_first = a_next;
+          if (r + 1 < G) {
+            g_next = order[r + 1];
+            nl_next = nlist[g_next];
+            a_next = (lane < nl_next) ? list[(size_t)g_next * L + lane] : -1;
+          }
+          if (r >= p.av.n_valid) { err = ODK_IMG_ENCODE_ERROR; break; }  // od_pb.py:331-332
+          const int nc = ncand[g];
+          if (nc == 0) { err = ODK_IMG_ENCODE_ERROR; break; }             // od_pb.py:338
+          int best_a = -1;
+          for (int k0 = 0; k0 < nl && best_a < 0; k0 += 32) {
+            const int k = k0 + lane;
+            const int a = (k0 == 0) ? a_first : ((k < nl) ? list[(size_t)g * L + k] : -1);
+            const bool is_free = a >= 0 && !((taken[a >> 5] >> (a & 31)) & 1u);
+            const unsigned fm = __ballot_sync(0xffffffffu, is_free);
+            if (fm) best_a = __shfl_sync(0xffffffffu, a, __ffs(fm) - 1);
+          }
+          if (best_a < 0 && nc > nl) {
+            // the ranked prefix is exhausted but more in-cell anchors exist: exact re-evaluation over the free ones
+            const float4 box = gbox[g];
+            const float cx = __fmul_rn(__fadd_rn(box.z, box.x), 0.5f);
+            const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
+            double mc = DBL_MAX;
+            int ma = INT_MAX;
+            for_each_cell_candidate(p.av, cx, cy, lane, [&](int a, bool ok) {
+              if (!ok || ((taken[a >> 5] >> (a & 31)) & 1u)) return;  // od_pb.py:339
+              const double c = encode_cost(box, __ldg(p.av.locs + a), p.av.sizes[a]);
+              if (cand_less(c, a, mc, ma)) { mc = c; ma = a; }
+            });
 #pragma unroll
-        for (int d = 16; d > 0; d >>= 1) {
-          const double oc = __shfl_xor_sync(0xffffffffu, mc, d);
-          const int oa = __shfl_xor_sync(0xffffffffu, ma, d);
-          if (cand_less(oc, oa, mc, ma)) { mc = oc; ma = oa; }
+            for (int d = 16; d > 0; d >>= 1) {
+              const double oc = __shfl_xor_sync(0xffffffffu, mc, d);
+              const int oa = __shfl_xor_sync(0xffffffffu, ma, d);
+              if (cand_less(oc, oa, mc, ma)) { mc = oc; ma = oa; }
+            }
+            if (ma != INT_MAX) best_a = ma;
+          }
+          if (best_a < 0) { need = g; break; }  // -> CTA-wide fallback
+          if (lane == 0) {
+            taken[best_a >> 5] |= 1u << (best_a & 31);
+            pick[g] = best_a;
+          }
+          __syncwarp();
         }
-        if (ma != INT_MAX) best_a = ma;
       }
-      if (best_a < 0) {
-        // fallback: arg-max IoU over the free valid anchors, first maximum wins (od_pb.py:347-352)
-        float best_v = -1.0f;
-        int fa = INT_MAX;
-        const float ga = garea[g];
-        for (int a = lane; a < p.av.n; a += 32) {
-          if (!p.av.mask[a] || ((taken[a >> 5] >> (a & 31)) & 1u)) continue;
-          const float4 lc = __ldg(p.av.locs + a);
-          const float v = odk_iou_value(box, ga, lc, odk_area(lc));
-          if (v > best_v) { best_v = v; fa = a; }
-        }
+      if (lane == 0) s_state[0] = need;
+    }
+    __syncthreads();
+    need = s_state[0];
+    if (need == -2) break;
+    {
+      // fallback: arg-max IoU over the free valid anchors, first maximum wins (od_pb.py:347-352)
+      const float4 box = gbox[need];
+      const float ga = garea[need];
+      float best_v = -1.0f;
+      int fa = INT_MAX;
+      for (int a = threadIdx.x; a < p.av.n; a += kGreedyThreads) {
+        if (!p.av.mask[a] || ((taken[a >> 5] >> (a & 31)) & 1u)) continue;
+        const float4 lc = __ldg(p.av.locs + a);
+        const float v = odk_iou_value(box, ga, lc, odk_area(lc));
+        if (v > best_v) { best_v = v; fa = a; }  // ascending a per thread: the first maximum stays
+      }
 #pragma unroll
-        for (int d = 16; d > 0; d >>= 1) {
-          const float ov = __shfl_xor_sync(0xffffffffu, best_v, d);
-          const int oa = __shfl_xor_sync(0xffffffffu, fa, d);
-          if (ov > best_v || (ov == best_v && oa < fa)) { best_v = ov; fa = oa; }
+      for (int d = 16; d > 0; d >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best_v, d);
+        const int oa = __shfl_xor_sync(0xffffffffu, fa, d);
+        if (ov > best_v || (ov == best_v && oa < fa)) { best_v = ov; fa = oa; }
+      }
+      if (lane == 0) { s_best_v[warp] = best_v; s_best_a[warp] = fa; }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        for (int w = 1; w < kGreedyWarps; ++w)
+          if (s_best_v[w] > best_v || (s_best_v[w] == best_v && s_best_a[w] < fa)) { best_v = s_best_v[w]; fa = s_best_a[w]; }
+        s_state[1] = fa;
+        if (fa != INT_MAX) {
+          taken[fa >> 5] |= 1u << (fa & 31);
+          pick[need] = fa;
         }
-        if (fa == INT_MAX) { err = ODK_IMG_ENCODE_ERROR; break; }
-        best_a = fa;
       }
-      if (lane == 0) {
-        taken[best_a >> 5] |= 1u << (best_a & 31);
-        pick[g] = best_a;
-      }
-      __syncwarp();
+      __syncthreads();
+      if (s_state[1] == INT_MAX) err = ODK_IMG_ENCODE_ERROR;
+      ++r;  // warp 0 resumes with the next GT (other warps' r is unused)
     }
   }
+  if (warp != 0) return;
+  err = __shfl_sync(0xffffffffu, err, 0);
   if (err) {
     for (int g = lane; g < p.gmax; g += 32) { out_pb[g] = -1; out_gt[g] = -1; }
     if (lane == 0) p.status[b] = err;
@@ -258,10 +358,10 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   // np.where(pb_assigned_gt >= 0): ascending anchor index (od_pb.py:359); picks are unique
   for (int g = lane; g < G; g += 32) {
     const int mine = pick[g];
-    int r = 0;
-    for (int j = 0; j < G; ++j) r += pick[j] < mine;
-    out_pb[r] = mine;
-    out_gt[r] = g;
+    int rk = 0;
+    for (int j = 0; j < G; ++j) rk += pick[j] < mine;
+    out_pb[rk] = mine;
+    out_gt[rk] = g;
   }
   for (int g = G + lane; g < p.gmax; g += 32) { out_pb[g] = -1; out_gt[g] = -1; }
   if (lane == 0) p.status[b] = ODK_IMG_OK;
@@ -278,131 +378,153 @@ struct EncodeArgs {
   const int32_t* status;
   float* y_true;
   uint8_t* pb_valids;
+  const unsigned* ignore;  // [B, bitmap_words] from assign_candidates_kernel
+  int bitmap_words;
 };
 
-__global__ void __launch_bounds__(kEncodeTile) encode_rows_kernel(const EncodeArgs p) {
+// Per-item inputs, staged in shared memory by cp.async one item ahead.
+struct EncodeStage {
+  long long* pb;     // [gmax] assigned anchors (ascending)
+  long long* gi;     // [gmax] the GT each one owns
+  unsigned* ignore;  // [TILE/32] ignore-mask words of this tile
+  int* meta;         // [2] = gt_count, status
+};
+
+template <int TILE>
+__global__ void __launch_bounds__(TILE) encode_rows_kernel(const EncodeArgs p, int items_per_cta) {
   extern __shared__ __align__(128) unsigned char enc_smem[];
   const int C = p.av.num_classes;
   const int W = 3 + C + 4;
-  const int b = blockIdx.y;
-  const int a0 = blockIdx.x * kEncodeTile;
-  const int rows = min(kEncodeTile, p.av.n - a0);
   const int tid = threadIdx.x;
-  float* s_rows = reinterpret_cast<float*>(enc_smem);                       // [kEncodeTile * W]
-  const size_t rows_bytes = odk_align_up((size_t)kEncodeTile * W * 4, 16);
-  float4* s_gbox = reinterpret_cast<float4*>(enc_smem + rows_bytes);        // [gmax]
-  float* s_garea = reinterpret_cast<float*>(enc_smem + rows_bytes + (size_t)p.gmax * 16);
-  __shared__ unsigned char s_assigned[kEncodeTile];
+  const size_t rows_bytes = odk_align_up((size_t)TILE * W * 4, 128);
+  const size_t stage_bytes = odk_align_up((size_t)p.gmax * 16 + 32, 16);
+  auto stage = [&](int i) {  // pointers by arithmetic (no dynamically indexed local arrays)
+    unsigned char* q = enc_smem + 2 * rows_bytes + (size_t)i * stage_bytes;
+    EncodeStage e;
+    e.ignore = reinterpret_cast<unsigned*>(q);
+    e.meta = reinterpret_cast<int*>(q + 16);
+    e.pb = reinterpret_cast<long long*>(q + 32);
+    e.gi = reinterpret_cast<long long*>(q + 32 + (size_t)p.gmax * 8);
+    return e;
+  };
+  __shared__ int s_owner[TILE];
 
-  int* s_list = reinterpret_cast<int*>(enc_smem + rows_bytes + (size_t)p.gmax * 20);  // [gmax] GTs that can reach this tile
-  __shared__ float s_red[6][kEncodeTile / 32];
-  __shared__ int s_nlist;
+  const int n_tiles = (p.av.n + TILE - 1) / TILE;
+  const long long n_items = (long long)n_tiles * p.batch;  // tile-major: item = tile * B + b
+  const long long first = (long long)blockIdx.x * items_per_cta;
+  const int count = (int)(min(n_items, first + items_per_cta) - first);
+  if (count <= 0) return;
+  int tile = (int)(first / p.batch), b = (int)(first % p.batch);  // advanced incrementally
 
-  const bool ok = p.status[b] == ODK_IMG_OK;
-  const int G = ok ? p.gt_count[b] : 0;
-  for (int g = tid; g < G; g += kEncodeTile) {
-    const float4 bx = p.gt_boxes[(size_t)b * p.gmax + g];
-    s_gbox[g] = bx;
-    s_garea[g] = odk_area(bx);
-  }
-  {  // zero the tile
-    float4* z = reinterpret_cast<float4*>(s_rows);
-    const int n4 = (kEncodeTile * W * 4 + 15) / 16;
-    for (int i = tid; i < n4; i += kEncodeTile) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  s_assigned[tid] = 0;
-  if (tid == 0) s_nlist = 0;
-
-  // this thread's anchor, and the tile's bounding box / area range over its VALID anchors
-  const int a = a0 + tid;
-  const bool active = tid < rows && ok && G > 0 && p.av.mask[a];
-  float4 ab = make_float4(0.f, 0.f, 0.f, 0.f);
-  float aa = 0.f;
-  float r0 = FLT_MAX, r1 = FLT_MAX, r2 = -FLT_MAX, r3 = -FLT_MAX, r4 = FLT_MAX, r5 = -FLT_MAX;
-  if (active) {
-    ab = __ldg(p.av.locs + a);
-    aa = odk_area(ab);
-    r0 = ab.x; r1 = ab.y; r2 = ab.z; r3 = ab.w; r4 = aa; r5 = aa;
-  }
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) {
-    r0 = fminf(r0, __shfl_xor_sync(0xffffffffu, r0, d));
-    r1 = fminf(r1, __shfl_xor_sync(0xffffffffu, r1, d));
-    r2 = fmaxf(r2, __shfl_xor_sync(0xffffffffu, r2, d));
-    r3 = fmaxf(r3, __shfl_xor_sync(0xffffffffu, r3, d));
-    r4 = fminf(r4, __shfl_xor_sync(0xffffffffu, r4, d));
-    r5 = fmaxf(r5, __shfl_xor_sync(0xffffffffu, r5, d));
-  }
-  if ((tid & 31) == 0) {
-    const int w = tid >> 5;
-    s_red[0][w] = r0; s_red[1][w] = r1; s_red[2][w] = r2; s_red[3][w] = r3; s_red[4][w] = r4; s_red[5][w] = r5;
-  }
-  __syncthreads();
-#pragma unroll
-  for (int w = 0; w < kEncodeTile / 32; ++w) {
-    r0 = fminf(r0, s_red[0][w]); r1 = fminf(r1, s_red[1][w]); r2 = fmaxf(r2, s_red[2][w]);
-    r3 = fmaxf(r3, s_red[3][w]); r4 = fminf(r4, s_red[4][w]); r5 = fmaxf(r5, s_red[5][w]);
-  }
-  // Conservative cull: fl(IoU) >= 0.5 needs a positive-extent overlap with some anchor of the tile
-  // (=> with the tile's bounding box) and min(Ag,Aa)/max(Ag,Aa) >= IoU, i.e. Ag within [0.5,2]x the
-  // anchor area; 0.49 / 2.05 leave ~2% slack against the few-ulp rounding of the fp32 areas.
-  for (int g = tid; g < G; g += kEncodeTile) {
-    const float4 gb = s_gbox[g];
-    const float ga = s_garea[g];
-    const bool reach = gb.x < r2 && gb.z > r0 && gb.y < r3 && gb.w > r1 && ga >= 0.49f * r4 && ga <= 2.05f * r5;
-    if (reach) s_list[atomicAdd(&s_nlist, 1)] = g;
-  }
-  __syncthreads();
-
-  const float w0 = (float)(1.0 / (double)max(1, G));  // od_pb.py:306
-  bool valid = true;
-  {
-    const int nl = s_nlist;  // block-uniform trip count; the loop body has no divergent exits
-    bool ignored = false;
-    for (int k = 0; k < nl; ++k) {
-      const int g = s_list[k];
-      ignored |= odk_iou_passes<true>(s_gbox[g], s_garea[g], ab, aa, 0.5f);  // od_pb.py:355
+  auto prefetch = [&](int pt, int pb_, int buf) {  // all threads; one commit group per item
+    const size_t g0 = (size_t)pb_ * p.gmax;
+    const EncodeStage e = stage(buf);
+    for (int g = tid; g < p.gmax; g += TILE) {
+      odk_cp_async<8>(e.pb + g, p.pb_indices + g0 + g);
+      odk_cp_async<8>(e.gi + g, p.gt_indices + g0 + g);
     }
-    valid = !(active && ignored);
-    if (tid < rows && ok && valid) s_rows[tid * W] = w0;
+    if (tid < TILE / 32 && pt * (TILE / 32) + tid < p.bitmap_words)
+      odk_cp_async<4>(e.ignore + tid, p.ignore + (size_t)pb_ * p.bitmap_words + (size_t)pt * (TILE / 32) + tid);
+    if (tid == TILE / 32) odk_cp_async<4>(e.meta, p.gt_count + pb_);
+    if (tid == TILE / 32 + 1) odk_cp_async<4>(e.meta + 1, p.status + pb_);
+    odk_cp_async_commit();
+  };
+
+  prefetch(tile, b, 0);
+  {  // both row buffers start all-zero; afterwards every item only rewrites what it dirtied
+    float4* z = reinterpret_cast<float4*>(enc_smem);
+    const int n4 = (int)(2 * rows_bytes / 16);
+    for (int i = tid; i < n4; i += TILE) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  __syncthreads();
-  // positives (one per GT): od_pb.py:307-311
-  if (G > 0) {
-    const float w1 = (float)(1.0 / (double)G);
-    for (int k = tid; k < G; k += kEncodeTile) {
-      const int pa = (int)p.pb_indices[(size_t)b * p.gmax + k];
-      if (pa < a0 || pa >= a0 + rows) continue;
-      const int g = (int)p.gt_indices[(size_t)b * p.gmax + k];
-      float* row = s_rows + (size_t)(pa - a0) * W;
-      const float4 box = s_gbox[g];
-      const float4 loc = __ldg(p.av.locs + pa);
-      const double2 sz = p.av.sizes[pa];
-      row[0] = w0;  // pb_valids[pb_indices] = True (od_pb.py:361)
-      row[1] = w1;
-      row[2] = 1.0f;
-      row[3 + p.gt_classes[(size_t)b * p.gmax + g]] = 1.0f;
-      row[3 + C + 0] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.x, loc.x), sz.x), 0.10);
-      row[3 + C + 1] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.y, loc.y), sz.y), 0.10);
-      row[3 + C + 2] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.z, loc.z), sz.x), 0.10);
-      row[3 + C + 3] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.w, loc.w), sz.y), 0.10);
-      s_assigned[pa - a0] = 1;
+  s_owner[tid] = -1;
+
+  int cur_tile = -1, a0 = 0, rows = 0, a = 0;
+  bool anchor_ok = false;  // inside the table and pb_mask set
+  int dirty0 = -1, dirty1 = -1;  // class column this thread set in row buffer 0 / 1 (-1: its row is clean)
+  int n_stores = 0;
+  bool last_was_bulk = false;
+
+  for (int it = 0; it < count; ++it) {
+    const int buf = it & 1;
+    int nt = tile, nb = b + 1;  // the next item
+    if (nb == p.batch) { nb = 0; ++nt; }
+    if (it + 1 < count) prefetch(nt, nb, buf ^ 1);
+    else odk_cp_async_commit();  // keep the group count uniform
+    if (tile != cur_tile) {
+      cur_tile = tile;
+      a0 = tile * TILE;
+      rows = min(TILE, p.av.n - a0);
+      a = a0 + tid;
+      anchor_ok = tid < rows && p.av.mask[a];
     }
-  }
-  odk_fence_proxy_async();  // generic-proxy smem writes -> visible to the bulk (async-proxy) store
-  __syncthreads();
-  float* dst = p.y_true + ((size_t)b * p.av.n + a0) * W;
-  const uint32_t bytes = (uint32_t)rows * W * 4;
-  if (((uintptr_t)dst & 15) == 0 && (bytes & 15) == 0) {
-    if (tid == 0) {
-      odk_bulk_s2g(dst, s_rows, bytes);
-      odk_bulk_commit();
+    // ---- A: this item's inputs are staged, and row buffer `buf` (stored two items ago) has been read out ----
+    odk_cp_async_wait<1>();
+    if (tid == 0 && n_stores > 0) {
+      if (last_was_bulk) odk_bulk_wait_read<1>();  // only the previous item's store may still be reading
+      else odk_bulk_wait_read<0>();
     }
-  } else {
-    for (int i = tid; i < rows * W; i += kEncodeTile) dst[i] = s_rows[i];
+    __syncthreads();
+    const EncodeStage s = stage(buf);
+    float* rowbuf = reinterpret_cast<float*>(enc_smem + (size_t)buf * rows_bytes);
+    float* row = rowbuf + (size_t)tid * W;
+    const bool ok = s.meta[1] == ODK_IMG_OK;
+    const int G = ok ? s.meta[0] : 0;
+    {  // undo the positive this thread wrote into the buffer two items ago
+      const int dirty = buf ? dirty1 : dirty0;
+      if (dirty >= 0) {
+        row[1] = 0.f; row[2] = 0.f; row[3 + dirty] = 0.f;
+        row[3 + C] = 0.f; row[3 + C + 1] = 0.f; row[3 + C + 2] = 0.f; row[3 + C + 3] = 0.f;
+      }
+      if (buf) dirty1 = -1; else dirty0 = -1;
+    }
+    for (int g = tid; g < G; g += TILE) {  // assignment slot g: anchor pa owns GT gi[g]
+      const int pa = (int)s.pb[g];
+      if (pa >= a0 && pa < a0 + rows) s_owner[pa - a0] = g;
+    }
+    __syncthreads();  // B
+    const float w0 = __fdiv_rn(1.0f, (float)max(1, G));  // float32(1/max(1,G)), od_pb.py:306 (== the fp64 quotient rounded once)
+    const bool ignored = anchor_ok && ((s.ignore[tid >> 5] >> (tid & 31)) & 1u);  // od_pb.py:355-357
+    const int own = s_owner[tid];
+    if (tid < rows) {
+      const bool valid = ok && (!ignored || own >= 0);  // pb_valids[pb_indices] = True (od_pb.py:361)
+      row[0] = valid ? w0 : 0.0f;
+      if (own >= 0) {  // positives (one per GT): od_pb.py:307-311
+        const int g = (int)s.gi[own];
+        const float4 box = __ldg(p.gt_boxes + (size_t)b * p.gmax + g);
+        const int cls = __ldg(p.gt_classes + (size_t)b * p.gmax + g);
+        const float4 ab = __ldg(p.av.locs + a);
+        const double2 sz = p.av.sizes[a];
+        row[1] = __fdiv_rn(1.0f, (float)G);
+        row[2] = 1.0f;
+        row[3 + cls] = 1.0f;
+        row[3 + C + 0] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.x, ab.x), sz.x), 0.10);
+        row[3 + C + 1] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.y, ab.y), sz.y), 0.10);
+        row[3 + C + 2] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.z, ab.z), sz.x), 0.10);
+        row[3 + C + 3] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.w, ab.w), sz.y), 0.10);
+        if (buf) dirty1 = cls; else dirty0 = cls;
+        s_owner[tid] = -1;
+      }
+      if (p.pb_valids != nullptr) p.pb_valids[(size_t)b * p.av.n + a] = valid ? 1 : 0;
+    }
+    odk_fence_proxy_async();  // generic-proxy smem writes -> visible to the bulk (async-proxy) store
+    __syncthreads();          // C
+    float* dst = p.y_true + ((size_t)b * p.av.n + a0) * W;
+    const uint32_t bytes = (uint32_t)rows * W * 4;
+    if (((uintptr_t)dst & 15) == 0 && (bytes & 15) == 0) {
+      if (tid == 0) {
+        odk_bulk_s2g(dst, rowbuf, bytes);
+        odk_bulk_commit();
+      }
+      ++n_stores;
+      last_was_bulk = true;
+    } else {
+      for (int i = tid; i < rows * W; i += TILE) dst[i] = rowbuf[i];
+      last_was_bulk = false;
+    }
+    tile = nt;
+    b = nb;
   }
-  if (p.pb_valids != nullptr && tid < rows) p.pb_valids[(size_t)b * p.av.n + a] = (ok && (valid || s_assigned[tid])) ? 1 : 0;
-  if (tid == 0) odk_bulk_wait_read<0>();  // smem must outlive the bulk read
+  if (tid == 0) odk_bulk_wait_read<0>();  // shared memory must outlive the bulk reads
 }
 
 __global__ void compute_iou_kernel(const float4* __restrict__ a, int na, const float4* __restrict__ b, int nb, float* __restrict__ out) {
@@ -432,8 +554,24 @@ __global__ void encode_locs_kernel(AnchorView av, int k, const float4* __restric
   out[4 * i + 3] = __ddiv_rn(__ddiv_rn((double)__fsub_rn(box.w, loc.w), sz.y), 0.10);
 }
 
+int assign_list_len(int gmax) {
+  int list_len = (int)((96 * 1024) / (4 * (size_t)gmax)) & ~7;
+  return list_len > 128 ? 128 : (list_len < 8 ? 8 : list_len);
+}
+
+size_t assign_lists_bytes(int batch, int gmax) {
+  return odk_align_up(sizeof(int) * (size_t)batch * gmax * ((size_t)assign_list_len(gmax) + 2), 256);
+}
+size_t assign_workspace_bytes(int n, int batch, int gmax) {
+  return assign_lists_bytes(batch, gmax) + odk_align_up(sizeof(unsigned) * (size_t)batch * ((n + 31) / 32), 256);
+}
+
 int launch_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count, int gmax,
-                  int64_t* pb_indices, int64_t* gt_indices, int32_t* status, cudaStream_t stream) {
+                  int64_t* pb_indices, int64_t* gt_indices, int32_t* status, bool want_ignore, void* workspace, size_t workspace_bytes,
+                  cudaStream_t stream) {
+  ODK_REQUIRE(workspace != nullptr && workspace_bytes >= assign_workspace_bytes(a->n, batch, gmax), ODK_ERR_WORKSPACE,
+              "assign: workspace of %zu bytes is smaller than the required %zu", workspace_bytes, assign_workspace_bytes(a->n, batch, gmax));
+  ODK_REQUIRE(((uintptr_t)workspace & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "assign: workspace must be 16-byte aligned");
   AssignArgs args;
   args.av = odk_view(a);
   args.batch = batch; args.gmax = gmax;
@@ -443,18 +581,54 @@ int launch_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const 
   args.gt_indices = reinterpret_cast<long long*>(gt_indices);
   args.status = status;
   args.bitmap_words = (a->n + 31) / 32;
-  int list_len = (int)((96 * 1024) / (4 * (size_t)gmax)) & ~7;
-  list_len = list_len > 128 ? 128 : (list_len < 8 ? 8 : list_len);
-  args.list_len = list_len;
-  const size_t smem = odk_align_up((size_t)gmax * (16 + 20 + 4 * (size_t)list_len) + (size_t)kGreedyWarps * kScratch * 12 +
-                                   (size_t)args.bitmap_words * 4, 16);
+  args.list_len = assign_list_len(gmax);
+  args.ws_list = static_cast<int*>(workspace);
+  args.ws_ncand = args.ws_list + (size_t)batch * gmax * args.list_len;
+  args.ws_nlist = args.ws_ncand + (size_t)batch * gmax;
+  args.ws_ignore = nullptr;
+  if (want_ignore) {
+    args.ws_ignore = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + assign_lists_bytes(batch, gmax));
+    ODK_CUDA(cudaMemsetAsync(args.ws_ignore, 0, sizeof(unsigned) * (size_t)batch * args.bitmap_words, stream));
+  }
+  const size_t smem = odk_align_up((size_t)gmax * (16 + 20 + 4 * (size_t)args.list_len) + (size_t)args.bitmap_words * 4, 16);
   ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign: N=%d / Gmax=%d need %zu bytes of shared memory per image", a->n, gmax, smem);
   ODK_CUDA(cudaFuncSetAttribute(assign_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  const long long tasks = (long long)batch * gmax;
+  {
+    OdkProfileScope prof_("assign_candidates_kernel", stream);
+    assign_candidates_kernel<<<(unsigned)((tasks + kGreedyWarps - 1) / kGreedyWarps), kGreedyThreads, 0, stream>>>(args);
+  }
+  ODK_LAUNCH_CHECK("assign_candidates_kernel");
   {
     OdkProfileScope prof_("assign_greedy_kernel", stream);
     assign_greedy_kernel<<<batch, kGreedyThreads, smem, stream>>>(args);
   }
   ODK_LAUNCH_CHECK("assign_greedy_kernel");
+  return ODK_OK;
+}
+
+template <int TILE>
+int launch_encode(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
+  const size_t smem = 2 * odk_align_up((size_t)TILE * W * 4, 128) + 2 * odk_align_up((size_t)e.gmax * 16 + 32, 16);
+  ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign_encode: C=%d / Gmax=%d need %zu bytes of shared memory", W - 7, e.gmax, smem);
+  auto kern = encode_rows_kernel<TILE>;
+  ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  const long long n_items = (long long)((n + TILE - 1) / TILE) * e.batch;
+  int per_sm = (int)((220 * 1024) / (smem + 2048));
+  per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / TILE ? 2048 / TILE : per_sm);
+  int sms = 0, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (sms <= 0) sms = 148;
+  long long grid = (long long)sms * per_sm;
+  if (grid > n_items) grid = n_items;
+  const int per_cta = (int)((n_items + grid - 1) / grid);
+  grid = (n_items + per_cta - 1) / per_cta;
+  {
+    OdkProfileScope prof_("encode_rows_kernel", stream);
+    kern<<<(unsigned)grid, TILE, smem, stream>>>(e, per_cta);
+  }
+  ODK_LAUNCH_CHECK("encode_rows_kernel");
   return ODK_OK;
 }
 
@@ -469,20 +643,28 @@ int assign_check(const odk_anchors* a, int batch, const void* gt_boxes, const vo
 
 }  // namespace
 
+extern "C" size_t odk_assign_workspace_bytes(const odk_anchors* a, int batch, int gmax) {
+  if (a == nullptr || batch < 1 || gmax < 1) return 0;
+  return assign_workspace_bytes(a->n, batch, gmax);
+}
+
 extern "C" int odk_assign(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_count, int gmax, int64_t* pb_indices,
-                          int64_t* gt_indices, int32_t* status, void* stream) {
+                          int64_t* gt_indices, int32_t* status, void* workspace, size_t workspace_bytes, void* stream) {
   if (int rc = assign_check(a, batch, gt_boxes, gt_count, gmax, pb_indices, gt_indices, status)) return rc;
-  return launch_greedy(a, batch, gt_boxes, nullptr, gt_count, gmax, pb_indices, gt_indices, status, static_cast<cudaStream_t>(stream));
+  return launch_greedy(a, batch, gt_boxes, nullptr, gt_count, gmax, pb_indices, gt_indices, status, false, workspace, workspace_bytes,
+                       static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int odk_assign_encode(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count,
                                  int gmax, float* y_true, int64_t* pb_indices, int64_t* gt_indices, uint8_t* pb_valids, int32_t* status,
-                                 void* stream_) {
+                                 void* workspace, size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = assign_check(a, batch, gt_boxes, gt_count, gmax, pb_indices, gt_indices, status)) return rc;
   ODK_REQUIRE(gt_classes && y_true, ODK_ERR_INVALID_ARGUMENT, "assign_encode: null pointer");
   ODK_REQUIRE(((uintptr_t)y_true & 3) == 0, ODK_ERR_INVALID_ARGUMENT, "assign_encode: y_true must be 4-byte aligned");
-  if (int rc = launch_greedy(a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, stream)) return rc;
+  if (int rc = launch_greedy(a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, true, workspace, workspace_bytes,
+                             stream))
+    return rc;
   EncodeArgs e;
   e.av = odk_view(a);
   e.batch = batch; e.gmax = gmax;
@@ -491,18 +673,11 @@ extern "C" int odk_assign_encode(const odk_anchors* a, int batch, const float* g
   e.pb_indices = reinterpret_cast<const long long*>(pb_indices);
   e.gt_indices = reinterpret_cast<const long long*>(gt_indices);
   e.status = status; e.y_true = y_true; e.pb_valids = pb_valids;
+  e.bitmap_words = (a->n + 31) / 32;
+  e.ignore = reinterpret_cast<const unsigned*>(static_cast<const char*>(workspace) + assign_lists_bytes(batch, gmax));
   const int W = 3 + a->num_classes + 4;
-  const size_t smem = odk_align_up((size_t)kEncodeTile * W * 4, 16) + (size_t)gmax * 24;
-  ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign_encode: C=%d / Gmax=%d need %zu bytes of shared memory", a->num_classes, gmax, smem);
-  ODK_CUDA(cudaFuncSetAttribute(encode_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  dim3 grid((a->n + kEncodeTile - 1) / kEncodeTile, batch);
-  ODK_REQUIRE(batch <= 65535, ODK_ERR_UNSUPPORTED, "assign_encode: batch=%d > 65535", batch);
-  {
-    OdkProfileScope prof_("encode_rows_kernel", stream);
-    encode_rows_kernel<<<grid, kEncodeTile, smem, stream>>>(e);
-  }
-  ODK_LAUNCH_CHECK("encode_rows_kernel");
-  return ODK_OK;
+  if (W <= 100) return launch_encode<128>(e, a->n, W, stream);
+  return launch_encode<32>(e, a->n, W, stream);
 }
 
 extern "C" int odk_compute_iou(const float* a, int na, const float* b, int nb, float* out, void* stream) {

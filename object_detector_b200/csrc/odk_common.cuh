@@ -221,6 +221,17 @@ template <int N>
 __device__ __forceinline__ void odk_bulk_wait() {
   asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
+// Ampere-style per-thread async copies (SASS LDGSTS), sizes 4 / 8 / 16 bytes.
+template <int BYTES>
+__device__ __forceinline__ void odk_cp_async(void* dst, const void* src) {
+  static_assert(BYTES == 4 || BYTES == 8 || BYTES == 16, "cp.async size");
+  asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(odk_smem_u32(dst)), "l"(src), "n"(BYTES) : "memory");
+}
+__device__ __forceinline__ void odk_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void odk_cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
 __device__ __forceinline__ void odk_fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }

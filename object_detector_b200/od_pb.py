@@ -218,10 +218,12 @@ class PriorBoxes:
         gt_idx = torch.empty((b, gmax), dtype=torch.int64, device=dev)
         status = torch.empty((b,), dtype=torch.int32, device=dev)
         valids = torch.empty((b, n), dtype=torch.uint8, device=dev) if want_valids else None
+        ws_bytes = _lib.load().odk_assign_workspace_bytes(self._handle(dev), b, gmax)
+        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             _lib.call('odk_assign_encode', self._handle(dev), b, boxes.data_ptr(), classes.data_ptr(), count.data_ptr(), gmax,
                       y_true.data_ptr(), pb_idx.data_ptr(), gt_idx.data_ptr(), _dev.ptr(valids), status.data_ptr(),
-                      _dev.stream_ptr(dev))
+                      ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
         res = {'y_true': y_true, 'pb_indices': pb_idx, 'gt_indices': gt_idx, 'status': status}
         if want_valids:
             res['pb_valids'] = valids.view(torch.bool)

@@ -14,6 +14,6 @@ $CMD > $OUT/plain_$TAG.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_launches_$TAG.log 2>&1
 echo "ncu launches exit $?"
 $CMD > $OUT/plain2_$TAG.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'decode_score_kernel|encode_rows_kernel|nms_sweep_kernel|sort_candidates_kernel|assign_greedy_kernel|topk_merge_kernel' -s 36 -c 12 -o $OUT/prof_$TAG -f $CMD > $OUT/ncu_full_$TAG.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'score_emit|decode_score_kernel|encode_rows_kernel|nms_image_kernel|assign_greedy_kernel|assign_candidates_kernel' -s 30 -c 10 -o $OUT/prof_$TAG -f $CMD > $OUT/ncu_full_$TAG.log 2>&1
 echo "ncu full exit $?"
 ls -la $OUT
