@@ -160,14 +160,30 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_candidates_kernel(const
   unsigned* ignore = p.ws_ignore + (size_t)b * p.bitmap_words;
   const float wg = __fsub_rn(box.z, box.x), hg = __fsub_rn(box.w, box.y);
   const float ga = __fmul_rn(wg, hg);
-  for (int mi = 0; mi < p.av.n_maps; ++mi) {
-    const int m = p.av.map_size[mi];
-    for (int pat = 0; pat < p.av.n_patterns; ++pat) {
-      const int base = p.av.map_off[mi] + pat * m * m;
-      const float4 l0 = __ldg(p.av.locs + base);  // anchor of cell (0,0): all cells of this (map, pattern) share its size
+  const int n_combo = p.av.n_maps * p.av.n_patterns;
+  for (int c0 = 0; c0 < n_combo; c0 += 32) {
+    // lane i fetches the cell-(0,0) anchor of (map, pattern) combination c0+i: one round trip for 32 of them
+    int my_m = 1, my_base = 0;
+    float4 my_l0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c0 + lane < n_combo) {
+      const int mi = (c0 + lane) / p.av.n_patterns, pat = (c0 + lane) % p.av.n_patterns;
+      my_m = p.av.map_size[mi];
+      my_base = p.av.map_off[mi] + pat * my_m * my_m;
+      my_l0 = __ldg(p.av.locs + my_base);
+    }
+    // all cells of a (map, pattern) share the anchor size; its area decides whether IoU 0.5 is reachable at all
+    const float my_aa = (my_l0.z - my_l0.x) * (my_l0.w - my_l0.y);
+    unsigned todo = __ballot_sync(0xffffffffu, c0 + lane < n_combo && ga >= 0.45f * my_aa && ga <= 2.2f * my_aa);
+    for (; todo; todo &= todo - 1) {
+      const int src = __ffs(todo) - 1;
+      const int m = __shfl_sync(0xffffffffu, my_m, src);
+      const int base = __shfl_sync(0xffffffffu, my_base, src);
+      float4 l0;
+      l0.x = __shfl_sync(0xffffffffu, my_l0.x, src);
+      l0.y = __shfl_sync(0xffffffffu, my_l0.y, src);
+      l0.z = __shfl_sync(0xffffffffu, my_l0.z, src);
+      l0.w = __shfl_sync(0xffffffffu, my_l0.w, src);
       const float wa = l0.z - l0.x, ha = l0.w - l0.y;
-      const float aa = wa * ha;
-      if (!(ga >= 0.45f * aa && ga <= 2.2f * aa)) continue;
       const float rx = (wg + wa) * 0.17f + 1e-4f, ry = (hg + ha) * 0.17f + 1e-4f;
       const float c0x = 0.5f * (l0.x + l0.z), c0y = 0.5f * (l0.y + l0.w);
       const int ix_lo = max(0, (int)floorf((cx - rx - c0x) * (float)m) - 1);
@@ -220,8 +236,12 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     const float4 bx = p.gt_boxes[(size_t)b * p.gmax + g];
     gbox[g] = bx;
     garea[g] = odk_area(bx);
-    ncand[g] = p.ws_ncand[(size_t)b * p.gmax + g];
+    const int nc = p.ws_ncand[(size_t)b * p.gmax + g];
+    ncand[g] = nc;
     nlist[g] = p.ws_nlist[(size_t)b * p.gmax + g];
+    // od_pb.py:338 (a centre inside no valid cell) / od_pb.py:331-332 (more GTs than valid anchors): whichever GT
+    // trips first, the image fails as a whole, so both are decided up front
+    if (nc == 0 || g >= p.av.n_valid) atomicMax(&s_err, ODK_IMG_ENCODE_ERROR);
     if (p.gt_classes != nullptr) {
       const int c = p.gt_classes[(size_t)b * p.gmax + g];
       if (c < 0 || c >= p.av.num_classes) atomicMax(&s_err, ODK_IMG_BAD_CLASS);  // od_pb.py:304
@@ -270,16 +290,26 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
             nl_next = nlist[g_next];
             a_next = (lane < nl_next) ? list[(size_t)g_next * L + lane] : -1;
           }
-          if (r >= p.av.n_valid) { err = ODK_IMG_ENCODE_ERROR; break; }  // od_pb.py:331-332
+          // fast path: some anchor among the first 32 ranks is free (the owning lane records it)
+          const unsigned word = (a_first >= 0) ? taken[a_first >> 5] : 0xffffffffu;
+          const unsigned bit = 1u << (a_first & 31);
+          const unsigned fm = __ballot_sync(0xffffffffu, !(word & bit));
+          if (fm) {
+            if (lane == __ffs(fm) - 1) {
+              taken[a_first >> 5] = word | bit;
+              pick[g] = a_first;
+            }
+            __syncwarp();
+            continue;
+          }
           const int nc = ncand[g];
-          if (nc == 0) { err = ODK_IMG_ENCODE_ERROR; break; }             // od_pb.py:338
           int best_a = -1;
-          for (int k0 = 0; k0 < nl && best_a < 0; k0 += 32) {
+          for (int k0 = 32; k0 < nl && best_a < 0; k0 += 32) {
             const int k = k0 + lane;
-            const int a = (k0 == 0) ? a_first : ((k < nl) ? list[(size_t)g * L + k] : -1);
+            const int a = (k < nl) ? list[(size_t)g * L + k] : -1;
             const bool is_free = a >= 0 && !((taken[a >> 5] >> (a & 31)) & 1u);
-            const unsigned fm = __ballot_sync(0xffffffffu, is_free);
-            if (fm) best_a = __shfl_sync(0xffffffffu, a, __ffs(fm) - 1);
+            const unsigned fm2 = __ballot_sync(0xffffffffu, is_free);
+            if (fm2) best_a = __shfl_sync(0xffffffffu, a, __ffs(fm2) - 1);
           }
           if (best_a < 0 && nc > nl) {
             // the ranked prefix is exhausted but more in-cell anchors exist: exact re-evaluation over the free ones

@@ -110,6 +110,7 @@ struct NmsArgs {
   const float4* locs;                   // [B, N] head output, decoded lazily
   float iou_thr;
   FastThr ft;
+  int cache_cap;   // candidate keys that fit the shared-memory cache
   int limit;       // sweep stops once this many boxes are kept
   int top_k;       // rows of `out` per image
   int skip_empty;  // ml.py:610-611
@@ -147,29 +148,63 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* s_warp /*[kNmsWa
   return res;
 }
 
+// Bitonic sort (descending) of kNmsThreads keys, one per thread: strides below 32 are exchanged with warp
+// shuffles, the rest through a double-buffered shared-memory array (one barrier per such stage).
+__device__ __forceinline__ unsigned long long block_sort_desc_1(unsigned long long key, unsigned long long* s_x /*[2][kNmsThreads]*/) {
+  const int tid = threadIdx.x;
+  int pb = 0;
+  for (int k = 2; k <= kNmsThreads; k <<= 1) {
+    const bool desc = (tid & k) == 0;
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      unsigned long long other;
+      if (j >= 32) {
+        s_x[pb * kNmsThreads + tid] = key;
+        __syncthreads();
+        other = s_x[pb * kNmsThreads + (tid ^ j)];
+        pb ^= 1;
+      } else {
+        other = __shfl_xor_sync(0xffffffffu, key, j);
+      }
+      const bool lower = (tid & j) == 0;
+      key = (lower == desc) ? (key > other ? key : other) : (key < other ? key : other);
+    }
+  }
+  return key;
+}
+
 template <bool GE>
 __global__ void __launch_bounds__(kNmsThreads) nms_image_kernel(const NmsArgs p) {
+  static_assert(kBand == kNmsThreads, "one band slot per thread");
   extern __shared__ __align__(16) unsigned char nms_smem[];
   __shared__ int s_hist[kBins];
-  __shared__ __align__(16) unsigned long long s_band[kBand];   // key1 of the band, sorted
-  __shared__ __align__(16) unsigned long long s_order[kBand];  // survivors in global order
+  __shared__ __align__(16) unsigned long long s_band[kBand];            // key2 of the band, sorted descending (global order)
+  __shared__ __align__(16) unsigned long long s_x[2 * kNmsThreads];     // sort exchange buffers
   __shared__ float4 s_box[kBand];
   __shared__ float s_area[kBand];
+  __shared__ unsigned short s_cls[kBand];
   __shared__ unsigned char s_alive[kBand];
   __shared__ unsigned char s_keep[kBand];
-  __shared__ int s_seg[kBand + 1];
+  __shared__ unsigned s_clsbits[ODK_MAX_CLASSES / 32];
+  __shared__ unsigned short s_clslist[kBand];
   __shared__ int s_scan[kNmsWarps + 1];
-  __shared__ int s_nb, s_nseg, s_nk, s_sel_r, s_sel_cnt;
+  __shared__ unsigned long long s_mm[2 * kNmsWarps];
+  __shared__ int s_nb, s_sel_r, s_sel_cnt;
 
   const int tid = threadIdx.x;
   const int lane = (int)odk_lane();
   const int warp = tid >> 5;
   const int b = blockIdx.x;
   const int limit = p.limit;
-  float4* kbox = reinterpret_cast<float4*>(nms_smem);                                   // [limit]
-  float* karea = reinterpret_cast<float*>(nms_smem + (size_t)limit * 16);               // [limit]
-  int* kcls = reinterpret_cast<int*>(nms_smem + (size_t)limit * 20);                    // [limit]
-  int* s_pref = reinterpret_cast<int*>(nms_smem + odk_align_up((size_t)limit * 24, 16));  // [n_pieces + 1]
+  unsigned char* dyn = nms_smem;
+  float4* kbox = reinterpret_cast<float4*>(dyn);                          // [limit]
+  float* karea = reinterpret_cast<float*>(dyn + (size_t)limit * 16);      // [limit]
+  int* kcls = reinterpret_cast<int*>(dyn + (size_t)limit * 20);           // [limit]
+  dyn += odk_align_up((size_t)(limit < 1 ? 1 : limit) * 24, 16);
+  int* s_pref = reinterpret_cast<int*>(dyn);                              // [n_pieces + 1]
+  dyn += odk_align_up(sizeof(int) * ((size_t)p.n_pieces + 1), 16);
+  unsigned short* s_member = reinterpret_cast<unsigned short*>(dyn);      // [kNmsWarps][kBand]
+  dyn += (size_t)kNmsWarps * kBand * 2;
+  unsigned long long* s_cache = reinterpret_cast<unsigned long long*>(dyn);  // [cache_cap] all candidate keys of the image
   const bool fast = GE && p.ft.enabled;  // the fast form needs positive-extent boxes: guaranteed by the zero-area skip
 
   const unsigned long long* keys = p.cand_keys + (size_t)b * p.n_pieces * p.piece;
@@ -190,8 +225,20 @@ __global__ void __launch_bounds__(kNmsThreads) nms_image_kernel(const NmsArgs p)
     if (tid == 0) s_pref[p.n_pieces] = total;
     __syncthreads();
   }
-  // candidate i of the image (any order): piece by binary search over the prefix sums
-  auto cand_key = [&](int i) {
+  // The image's keys are pulled into shared memory once when they fit (every later pass is on-chip);
+  // otherwise each pass reads them from L2 through the piece prefix sums.
+  const bool cached = total <= p.cache_cap;
+  if (cached) {
+    const int slots = p.n_pieces * p.piece;
+    for (int i = tid; i < slots; i += kNmsThreads) {
+      const int q = i / p.piece, sl = i - q * p.piece;
+      const int q_lo = s_pref[q];
+      if (sl < s_pref[q + 1] - q_lo) s_cache[q_lo + sl] = keys[i];
+    }
+    __syncthreads();
+  }
+  auto cand_key = [&](int i) -> unsigned long long {
+    if (cached) return s_cache[i];
     int lo = 0, hi = p.n_pieces;  // largest q with s_pref[q] <= i
     while (hi - lo > 1) {
       const int mid = (lo + hi) >> 1;
@@ -205,14 +252,36 @@ __global__ void __launch_bounds__(kNmsThreads) nms_image_kernel(const NmsArgs p)
 
   while (processed < total && nkept < limit) {
     const int remaining = total - processed;
-    // ---- a. threshold of the next band --------------------------------------------------------------
+    // ---- a. threshold of the next band: MSB radix select starting at the first bit in which the
+    //         remaining keys differ (fp32 scores share their leading exponent bits) -------------------------
     unsigned long long lo_key = 0ull;
     if (remaining > kBand) {
-      unsigned long long prefix = 0ull;  // digits fixed so far (the bucket that still overflows)
-      int above = 0;                     // keys < hi_key that lie above that bucket (all taken)
-      for (int shift = 64 - kDigitBits; ; shift = max(0, shift - kDigitBits)) {
-        const int width = (shift == 0) ? ((64 - 1) % kDigitBits + 1) : kDigitBits;  // last digit takes the leftover bits
-        const int top = shift + width;                                              // bits above the digit
+      unsigned long long kmin = ~0ull, kmax = 0ull;
+      for (int i = tid; i < total; i += kNmsThreads) {
+        const unsigned long long k = cand_key(i);
+        if (k < hi_key) {
+          kmin = k < kmin ? k : kmin;
+          kmax = k > kmax ? k : kmax;
+        }
+      }
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+        const unsigned long long omin = __shfl_xor_sync(0xffffffffu, kmin, d), omax = __shfl_xor_sync(0xffffffffu, kmax, d);
+        kmin = omin < kmin ? omin : kmin;
+        kmax = omax > kmax ? omax : kmax;
+      }
+      if (lane == 0) { s_mm[warp] = kmin; s_mm[kNmsWarps + warp] = kmax; }
+      __syncthreads();
+      for (int w = 0; w < kNmsWarps; ++w) {
+        kmin = s_mm[w] < kmin ? s_mm[w] : kmin;
+        kmax = s_mm[kNmsWarps + w] > kmax ? s_mm[kNmsWarps + w] : kmax;
+      }
+      int top = 64 - __clzll((long long)(kmin ^ kmax));  // bits [top-1:0] vary (keys are distinct, so top >= 1)
+      unsigned long long prefix = (top >= 64) ? 0ull : (kmax >> top);  // common bits above them
+      int above = 0;                                                   // keys < hi_key above the current bucket (all taken)
+      while (true) {
+        const int shift = max(0, top - kDigitBits);
+        const int width = top - shift;
         for (int i = tid; i < kBins; i += kNmsThreads) s_hist[i] = 0;
         __syncthreads();
         for (int i = tid; i < total; i += kNmsThreads) {
@@ -222,8 +291,8 @@ __global__ void __launch_bounds__(kNmsThreads) nms_image_kernel(const NmsArgs p)
         __syncthreads();
         // walk the digits from the top: largest r such that above + S(r) <= kBand, S = inclusive sum over reversed bins
         const int nb_bins = 1 << width;
-        const int per = kBins / kNmsThreads;
-        int loc[kBins / kNmsThreads];
+        constexpr int per = kBins / kNmsThreads;
+        int loc[per];
         int lsum = 0;
 #pragma unroll
         for (int j = 0; j < per; ++j) {
@@ -251,89 +320,90 @@ __global__ void __launch_bounds__(kNmsThreads) nms_image_kernel(const NmsArgs p)
         const int cnt_take = s_sel_cnt;
         const int d_star = nb_bins - n_take_bins;
         __syncthreads();
-        if (cnt_take >= min(kBandMin, remaining) || shift == 0) {
-          if (d_star < nb_bins) lo_key = ((top >= 64 ? 0ull : (prefix << width)) | (unsigned long long)d_star) << shift;
+        if (cnt_take >= kBandMin || shift == 0) {
+          if (d_star < nb_bins) lo_key = ((prefix << width) | (unsigned long long)d_star) << shift;
           else lo_key = (prefix + 1ull) << top;  // nothing of this bucket: only the keys above it (top < 64 here)
           break;
         }
-        prefix = (top >= 64 ? 0ull : (prefix << width)) | (unsigned long long)(d_star - 1);  // refine inside the overflowing bin
+        prefix = (prefix << width) | (unsigned long long)(d_star - 1);  // refine inside the overflowing bin
+        top = shift;
         above = cnt_take;
       }
     }
-    // ---- b. gather + sort the band -----------------------------------------------------------------------
-    if (tid == 0) { s_nb = 0; s_nk = 0; }
+    // ---- b. gather the band, sort it into the global order (one key per thread) --------------------------
+    if (tid == 0) s_nb = 0;
+    for (int i = tid; i < ODK_MAX_CLASSES / 32; i += kNmsThreads) s_clsbits[i] = 0u;
     __syncthreads();
     for (int i = tid; i < total; i += kNmsThreads) {
       const unsigned long long k = cand_key(i);
       if (k < hi_key && k >= lo_key) {
         const int pos = atomicAdd(&s_nb, 1);
-        if (pos < kBand) s_band[pos] = odk_key2_to_key1(k);
+        if (pos < kBand) s_band[pos] = k;
       }
     }
     __syncthreads();
     const int nb = min(s_nb, kBand);
-    int n_pad = 2;
-    while (n_pad < nb) n_pad <<= 1;
-    for (int i = nb + tid; i < n_pad; i += kNmsThreads) s_band[i] = 0ull;
-    __syncthreads();
-    if (nb > 1) bitonic_sort_shared(s_band, n_pad, 0, 2, n_pad);
+    const unsigned long long my_key = block_sort_desc_1(tid < nb ? s_band[tid] : 0ull, s_x);
     hi_key = lo_key;
     processed += nb;
 
-    // ---- c. boxes of the band (lazy decode) + class segments ---------------------------------------------
-    int my_cls = -1;
-    bool seg_start = false;
+    // ---- c. boxes of the band (lazy decode), classes present in it -------------------------------------------
+    __syncthreads();  // every thread has read its unsorted s_band slot
     if (tid < nb) {
-      const unsigned long long k1 = s_band[tid];
-      const int a = (int)(k1 & ODK_IDX_MASK);
-      my_cls = odk_key1_class(k1);
+      const int a = (int)(my_key & ODK_IDX_MASK);
+      const int cls = odk_key2_class(my_key);
       float4 box;
       if (p.boxes != nullptr) box = p.boxes[(size_t)b * p.n + a];
       else box = odk_decode_box(p.locs[(size_t)b * p.n + a], __ldg(p.av.locs + a), __ldg(p.av.scale + a));
       const float w = __fsub_rn(box.z, box.x), h = __fsub_rn(box.w, box.y);
+      s_band[tid] = my_key;
       s_box[tid] = box;
       s_area[tid] = __fmul_rn(w, h);
+      s_cls[tid] = (unsigned short)cls;
       s_alive[tid] = !(p.skip_empty && (w <= 0.0f || h <= 0.0f));  // ml.py:610-611
       s_keep[tid] = 0;
-      seg_start = (tid == 0) || (odk_key1_class(s_band[tid - 1]) != my_cls);
+      atomicOr(&s_clsbits[cls >> 5], 1u << (cls & 31));
     }
+    __syncthreads();
+    int n_present;
     {
-      int nseg;
-      const int pos = block_exclusive_scan(seg_start ? 1 : 0, s_scan, nseg);
-      if (seg_start) s_seg[pos] = tid;
-      if (tid == 0) { s_seg[nseg] = nb; s_nseg = nseg; }
+      const unsigned wbits = (tid < ODK_MAX_CLASSES / 32) ? s_clsbits[tid] : 0u;
+      int pos = block_exclusive_scan(__popc(wbits), s_scan, n_present);
+      for (unsigned rem = wbits; rem; rem &= rem - 1) s_clslist[pos++] = (unsigned short)(tid * 32 + __ffs(rem) - 1);
     }
     __syncthreads();
-    // ---- d. drop what earlier rounds' kept boxes suppress -------------------------------------------------
-    if (nkept > 0 && tid < nb && s_alive[tid]) {
-      const float4 box = s_box[tid];
-      const float area = s_area[tid];
-      const float a_hi = area * p.ft.k_hi, a_lo = area * p.ft.k_lo;
-      bool dead = false;
-      for (int k = 0; k < nkept; ++k)
-        if (kcls[k] == my_cls) dead |= pair_hit<GE>(box, area, a_hi, a_lo, kbox[k], karea[k], p.iou_thr, p.ft, fast);
-      if (dead) s_alive[tid] = 0;
-    }
-    __syncthreads();
-    // ---- e. one warp per class segment ---------------------------------------------------------------------
-    const int nseg = s_nseg;
-    for (int sg = warp; sg < nseg; sg += kNmsWarps) {
-      const int s0 = s_seg[sg], s1 = s_seg[sg + 1];
-      int seg_kept = 0;
-      for (int base = s0; base < s1; base += 32) {
+    // ---- d/e. one warp per class present: its members in score order, 32 at a time ----------------------------
+    for (int ci = warp; ci < n_present; ci += kNmsWarps) {
+      const int c = s_clslist[ci];
+      unsigned short* mem = s_member + (size_t)warp * kBand;
+      int nm = 0;
+      for (int base = 0; base < nb; base += 32) {
         const int i = base + lane;
-        const bool have = i < s1;
+        const bool is = i < nb && s_cls[i] == c;
+        const unsigned m = __ballot_sync(0xffffffffu, is);
+        if (is) mem[nm + __popc(m & ((1u << lane) - 1u))] = (unsigned short)i;
+        nm += __popc(m);
+      }
+      __syncwarp();
+      int seg_kept = 0;
+      for (int mb = 0; mb < nm; mb += 32) {
+        const bool have = mb + lane < nm;
+        const int i = have ? mem[mb + lane] : 0;
         const float4 box = have ? s_box[i] : make_float4(0.f, 0.f, 0.f, 0.f);
         const float area = have ? s_area[i] : 0.f;
         const float a_hi = area * p.ft.k_hi, a_lo = area * p.ft.k_lo;
-        bool alive = have && s_alive[i];
-        // earlier chunks of this segment: only their kept entries matter (uniform trip count)
+        bool dead = false;
+        // boxes of this class kept in earlier rounds (warp-uniform class test)
+        for (int k = 0; k < nkept; ++k)
+          if (kcls[k] == c) dead |= pair_hit<GE>(box, area, a_hi, a_lo, kbox[k], karea[k], p.iou_thr, p.ft, fast);
+        // ... and in earlier chunks of this round
         if (seg_kept > 0) {
-          bool dead = false;
-          for (int e = s0; e < base; ++e)
-            if (s_keep[e]) dead |= pair_hit<GE>(box, area, a_hi, a_lo, s_box[e], s_area[e], p.iou_thr, p.ft, fast);
-          alive = alive && !dead;
+          for (int e = 0; e < mb; ++e) {
+            const int ie = mem[e];
+            if (s_keep[ie]) dead |= pair_hit<GE>(box, area, a_hi, a_lo, s_box[ie], s_area[ie], p.iou_thr, p.ft, fast);
+          }
         }
+        const bool alive = have && s_alive[i] && !dead;
         // intra-chunk: sup bit j of lane i = "i suppresses j" (i before j)
         const unsigned am = __ballot_sync(0xffffffffu, alive);
         unsigned sup = 0;
@@ -360,40 +430,26 @@ __global__ void __launch_bounds__(kNmsThreads) nms_image_kernel(const NmsArgs p)
         seg_kept += __popc(keep);
         __syncwarp();
       }
-      if (lane == 0 && seg_kept) atomicAdd(&s_nk, seg_kept);
     }
     __syncthreads();
-    // ---- f. survivors -> global order -> kept list + output ---------------------------------------------------
-    const int nk = s_nk;
-    if (nk > 0) {
-      // order key = [flip(score):32][4095-class:12][kBand-1-slot:9]: equal (score, class) -> lower slot = higher anchor first
-      for (int i = tid; i < n_pad; i += kNmsThreads) {
-        unsigned long long v = 0ull;
-        if (i < nb && s_keep[i]) {
-          const unsigned long long k1 = s_band[i];
-          v = (((k1 >> ODK_IDX_BITS) & 0xffffffffull) << 21) | ((k1 >> (32 + ODK_IDX_BITS)) << 9) | (unsigned long long)(kBand - 1 - i);
-          v |= 1ull << 63;  // survivors sort above the zero padding even for the smallest score
-        }
-        s_order[i] = v;
-      }
-      __syncthreads();
-      bitonic_sort_shared(s_order, n_pad, 0, 2, n_pad);
+    // ---- f. survivors are already in global order: compact, cut at the limit, emit ------------------------------
+    {
+      const bool kept = tid < nb && s_keep[tid];
+      int nk;
+      const int pos = block_exclusive_scan(kept ? 1 : 0, s_scan, nk);
       const int take = min(nk, limit - nkept);
-      if (tid < take) {
-        const unsigned long long v = s_order[tid];
-        const int slot = kBand - 1 - (int)(v & (unsigned long long)(kBand - 1));
-        const unsigned long long k1 = s_band[slot];
-        const int a = (int)(k1 & ODK_IDX_MASK);
-        const int cls = odk_key1_class(k1);
-        const float4 bx = s_box[slot];
-        const int r = nkept + tid;
+      if (kept && pos < take) {
+        const int a = (int)(my_key & ODK_IDX_MASK);
+        const int cls = odk_key2_class(my_key);
+        const float4 bx = s_box[tid];
+        const int r = nkept + pos;
         kbox[r] = bx;
-        karea[r] = s_area[slot];
+        karea[r] = s_area[tid];
         kcls[r] = cls;
         if (p.out != nullptr && r < p.top_k) {
           float* o = p.out + ((size_t)b * p.top_k + r) * 6;
           o[0] = (float)cls;
-          o[1] = odk_unflip_score((uint32_t)((k1 >> ODK_IDX_BITS) & 0xffffffffull));
+          o[1] = odk_key2_score(my_key);
           o[2] = bx.x; o[3] = bx.y; o[4] = bx.z; o[5] = bx.w;
           p.kept_index[(size_t)b * p.top_k + r] = a;
         }
@@ -467,9 +523,14 @@ static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch,
   a.ft.k_lo = (float)(kk * (1.0 - 3e-5));
   a.limit = limit; a.top_k = top_k; a.skip_empty = iou_ge ? 1 : 0;
   a.out = out; a.kept_index = kept_index; a.out_index = out_index; a.out_count = out_count;
-  const size_t smem = odk_align_up((size_t)(limit < 1 ? 1 : limit) * 24, 16) + sizeof(int) * ((size_t)a.n_pieces + 1);
+  const size_t fixed = odk_align_up((size_t)(limit < 1 ? 1 : limit) * 24, 16) + odk_align_up(sizeof(int) * ((size_t)a.n_pieces + 1), 16) +
+                       (size_t)kNmsWarps * kBand * 2;
+  a.cache_cap = n < 8192 ? n : 8192;
+  if (fixed + (size_t)a.cache_cap * 8 > 180 * 1024) a.cache_cap = 0;
+  const size_t smem = fixed + (size_t)a.cache_cap * 8;
+  ODK_REQUIRE(smem <= 180 * 1024, ODK_ERR_UNSUPPORTED, "nms: top_k=%d / %d pieces need %zu bytes of shared memory", top_k, a.n_pieces, smem);
   auto kern = iou_ge ? nms_image_kernel<true> : nms_image_kernel<false>;
-  ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+  ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 180 * 1024));
   {
     OdkProfileScope prof_("nms_image_kernel", stream);
     kern<<<batch, kNmsThreads, smem, stream>>>(a);
