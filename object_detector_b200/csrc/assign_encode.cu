@@ -104,7 +104,7 @@ __device__ __forceinline__ bool cand_less(double c0, int a0, double c1, int a1) 
 }
 
 // Phase A: every in-cell anchor of one GT ranked by (fp64 cost, index), ignoring "taken".
-__global__ void __launch_bounds__(kGreedyThreads) assign_candidates_kernel(const AssignArgs p) {
+__global__ void __launch_bounds__(kGreedyThreads, 2) assign_candidates_kernel(const AssignArgs p) {
   __shared__ double s_cost[kGreedyWarps * kScratch];
   __shared__ int s_idx[kGreedyWarps * kScratch];
   const int warp = threadIdx.x >> 5;
@@ -192,12 +192,13 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_candidates_kernel(const
       const int iy_hi = min(m - 1, (int)ceilf((cy + ry - c0y) * (float)m) + 1);
       const int nx = ix_hi - ix_lo + 1, ny = iy_hi - iy_lo + 1;
       if (nx <= 0 || ny <= 0) continue;
+#pragma unroll 4
       for (int t = lane; t < nx * ny; t += 32) {
         const int iy = iy_lo + t / nx, ix = ix_lo + t % nx;
         const int a = base + iy * m + ix;
-        if (!p.av.mask[a]) continue;
+        const unsigned char mk = __ldg(p.av.mask + a);  // mask and box travel together: one round trip per batch
         const float4 lc = __ldg(p.av.locs + a);
-        if (odk_iou_passes<true>(box, ga, lc, odk_area(lc), 0.5f)) atomicOr(ignore + (a >> 5), 1u << (a & 31));
+        if (mk && odk_iou_passes<true>(box, ga, lc, odk_area(lc), 0.5f)) atomicOr(ignore + (a >> 5), 1u << (a & 31));
       }
     }
   }

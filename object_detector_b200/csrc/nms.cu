@@ -33,7 +33,7 @@
 
 namespace {
 
-constexpr int kNmsThreads = 512;
+constexpr int kNmsThreads = 1024;
 constexpr int kNmsWarps = kNmsThreads / 32;
 constexpr int kBand = 512;
 constexpr int kBandMin = 256;   // a select level is accepted once it yields at least this many keys
@@ -148,12 +148,14 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* s_warp /*[kNmsWa
   return res;
 }
 
-// Bitonic sort (descending) of kNmsThreads keys, one per thread: strides below 32 are exchanged with warp
-// shuffles, the rest through a double-buffered shared-memory array (one barrier per such stage).
+// Bitonic sort (descending) of kBand keys, one per thread of the first kBand threads (the others run the
+// same network among themselves on dummy keys so that the barriers stay uniform): strides below 32 are
+// exchanged with warp shuffles, the rest through a double-buffered shared-memory array (one barrier per
+// such stage).
 __device__ __forceinline__ unsigned long long block_sort_desc_1(unsigned long long key, unsigned long long* s_x /*[2][kNmsThreads]*/) {
   const int tid = threadIdx.x;
   int pb = 0;
-  for (int k = 2; k <= kNmsThreads; k <<= 1) {
+  for (int k = 2; k <= kBand; k <<= 1) {
     const bool desc = (tid & k) == 0;
     for (int j = k >> 1; j > 0; j >>= 1) {
       unsigned long long other;
@@ -173,8 +175,8 @@ __device__ __forceinline__ unsigned long long block_sort_desc_1(unsigned long lo
 }
 
 template <bool GE>
-__global__ void __launch_bounds__(kNmsThreads) nms_image_kernel(const NmsArgs p) {
-  static_assert(kBand == kNmsThreads, "one band slot per thread");
+__global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs p) {
+  static_assert(kBand <= kNmsThreads && ODK_MAX_CLASSES / 32 <= kNmsThreads, "one band slot / class word per thread");
   extern __shared__ __align__(16) unsigned char nms_smem[];
   __shared__ int s_hist[kBins];
   __shared__ __align__(16) unsigned long long s_band[kBand];            // key2 of the band, sorted descending (global order)
@@ -229,12 +231,16 @@ __global__ void __launch_bounds__(kNmsThreads) nms_image_kernel(const NmsArgs p)
   // otherwise each pass reads them from L2 through the piece prefix sums.
   const bool cached = total <= p.cache_cap;
   if (cached) {
+    // fire-and-forget 8-byte async copies: every key of the image is in flight at once
     const int slots = p.n_pieces * p.piece;
+    const int shift = 31 - __clz(p.piece);  // piece heights are powers of two
     for (int i = tid; i < slots; i += kNmsThreads) {
-      const int q = i / p.piece, sl = i - q * p.piece;
+      const int q = i >> shift, sl = i & (p.piece - 1);
       const int q_lo = s_pref[q];
-      if (sl < s_pref[q + 1] - q_lo) s_cache[q_lo + sl] = keys[i];
+      if (sl < s_pref[q + 1] - q_lo) odk_cp_async<8>(s_cache + q_lo + sl, keys + i);
     }
+    odk_cp_async_commit();
+    odk_cp_async_wait<0>();
     __syncthreads();
   }
   auto cand_key = [&](int i) -> unsigned long long {
@@ -291,7 +297,7 @@ __global__ void __launch_bounds__(kNmsThreads) nms_image_kernel(const NmsArgs p)
         __syncthreads();
         // walk the digits from the top: largest r such that above + S(r) <= kBand, S = inclusive sum over reversed bins
         const int nb_bins = 1 << width;
-        constexpr int per = kBins / kNmsThreads;
+        constexpr int per = (kBins + kNmsThreads - 1) / kNmsThreads;
         int loc[per];
         int lsum = 0;
 #pragma unroll
@@ -404,27 +410,20 @@ __global__ void __launch_bounds__(kNmsThreads) nms_image_kernel(const NmsArgs p)
           }
         }
         const bool alive = have && s_alive[i] && !dead;
-        // intra-chunk: sup bit j of lane i = "i suppresses j" (i before j)
-        const unsigned am = __ballot_sync(0xffffffffu, alive);
-        unsigned sup = 0;
-        for (unsigned rem = am & (am - 1); rem; rem &= rem - 1) {  // every alive lane except the first
-          const int j = __ffs(rem) - 1;
-          float4 bj;
-          bj.x = __shfl_sync(0xffffffffu, box.x, j);
-          bj.y = __shfl_sync(0xffffffffu, box.y, j);
-          bj.z = __shfl_sync(0xffffffffu, box.z, j);
-          bj.w = __shfl_sync(0xffffffffu, box.w, j);
-          const float aj = __shfl_sync(0xffffffffu, area, j);
-          if (alive && lane < j && pair_hit<GE>(box, area, a_hi, a_lo, bj, aj, p.iou_thr, p.ft, fast)) sup |= 1u << j;
-        }
-        unsigned removed = 0, keep = 0;
-        for (unsigned rem = am; rem; rem &= rem - 1) {
+        // intra-chunk greedy in score order: the first remaining lane is kept and knocks out what it suppresses
+        unsigned keep = 0;
+        for (unsigned rem = __ballot_sync(0xffffffffu, alive); rem;) {
           const int l = __ffs(rem) - 1;
-          const unsigned sup_l = __shfl_sync(0xffffffffu, sup, l);
-          if (!((removed >> l) & 1u)) {
-            keep |= 1u << l;
-            removed |= sup_l;
-          }
+          keep |= 1u << l;
+          rem &= rem - 1;
+          float4 bl;
+          bl.x = __shfl_sync(0xffffffffu, box.x, l);
+          bl.y = __shfl_sync(0xffffffffu, box.y, l);
+          bl.z = __shfl_sync(0xffffffffu, box.z, l);
+          bl.w = __shfl_sync(0xffffffffu, box.w, l);
+          const float al = __shfl_sync(0xffffffffu, area, l);
+          const bool hit = ((rem >> lane) & 1u) && pair_hit<GE>(box, area, a_hi, a_lo, bl, al, p.iou_thr, p.ft, fast);
+          rem &= ~__ballot_sync(0xffffffffu, hit);
         }
         if ((keep >> lane) & 1u) s_keep[i] = 1;
         seg_kept += __popc(keep);
