@@ -186,10 +186,11 @@ __global__ void __launch_bounds__(kGreedyThreads, 2) assign_candidates_kernel(co
       const float wa = l0.z - l0.x, ha = l0.w - l0.y;
       const float rx = (wg + wa) * 0.17f + 1e-4f, ry = (hg + ha) * 0.17f + 1e-4f;
       const float c0x = 0.5f * (l0.x + l0.z), c0y = 0.5f * (l0.y + l0.w);
-      const int ix_lo = max(0, (int)floorf((cx - rx - c0x) * (float)m) - 1);
-      const int ix_hi = min(m - 1, (int)ceilf((cx + rx - c0x) * (float)m) + 1);
-      const int iy_lo = max(0, (int)floorf((cy - ry - c0y) * (float)m) - 1);
-      const int iy_hi = min(m - 1, (int)ceilf((cy + ry - c0y) * (float)m) + 1);
+      // anchor centres sit at c0 + i/m (to fp32 rounding); 0.02 of a cell on top of the 2% absorbs that rounding
+      const int ix_lo = max(0, (int)ceilf((cx - rx - c0x) * (float)m - 0.02f));
+      const int ix_hi = min(m - 1, (int)floorf((cx + rx - c0x) * (float)m + 0.02f));
+      const int iy_lo = max(0, (int)ceilf((cy - ry - c0y) * (float)m - 0.02f));
+      const int iy_hi = min(m - 1, (int)floorf((cy + ry - c0y) * (float)m + 0.02f));
       const int nx = ix_hi - ix_lo + 1, ny = iy_hi - iy_lo + 1;
       if (nx <= 0 || ny <= 0) continue;
 #pragma unroll 4

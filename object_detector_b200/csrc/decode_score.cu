@@ -48,7 +48,7 @@ struct StageLayout {
   static constexpr size_t kOffObj = 0, kOffAMask = (size_t)TILE * 4, kOffLoc = kOffAMask + (size_t)((TILE + 15) / 16 * 16),
                           kOffALoc = kOffLoc + (DENSE ? (size_t)TILE * 16 : 0), kOffAScale = kOffALoc + (DENSE ? (size_t)TILE * 16 : 0),
                           kTail = kOffAScale + (DENSE ? (size_t)TILE * 8 : 0);
-  static constexpr int kStages = DENSE ? 3 : 4;
+  static constexpr int kStages = 3;
   static size_t stage_bytes(int c) { return (size_t)TILE * c * 4 + kTail; }
 };
 
@@ -150,19 +150,25 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
       const float* row = s_clf + (size_t)tid * c;
       float best;
       if ((c & 3) == 0) {
+        // four independent running maxima (one per float4 lane) keep the dependency chains short; each is a
+        // first-maximum scan of its own residue class, and the merge prefers the lower index on equal values,
+        // which together is np.argmax's "first maximum wins"
         const float4* row4 = reinterpret_cast<const float4*>(row);
         float4 v = row4[0];
-        best = v.x;
-        if (v.y > best) { best = v.y; cls = 1; }
-        if (v.z > best) { best = v.z; cls = 2; }
-        if (v.w > best) { best = v.w; cls = 3; }
+        float b0 = v.x, b1 = v.y, b2 = v.z, b3 = v.w;
+        int i0 = 0, i1 = 1, i2 = 2, i3 = 3;
         for (int j = 1; j < (c >> 2); ++j) {
           v = row4[j];
-          if (v.x > best) { best = v.x; cls = 4 * j; }
-          if (v.y > best) { best = v.y; cls = 4 * j + 1; }
-          if (v.z > best) { best = v.z; cls = 4 * j + 2; }
-          if (v.w > best) { best = v.w; cls = 4 * j + 3; }
+          if (v.x > b0) { b0 = v.x; i0 = 4 * j; }
+          if (v.y > b1) { b1 = v.y; i1 = 4 * j + 1; }
+          if (v.z > b2) { b2 = v.z; i2 = 4 * j + 2; }
+          if (v.w > b3) { b3 = v.w; i3 = 4 * j + 3; }
         }
+        if (b1 > b0 || (b1 == b0 && i1 < i0)) { b0 = b1; i0 = i1; }
+        if (b3 > b2 || (b3 == b2 && i3 < i2)) { b2 = b3; i2 = i3; }
+        if (b2 > b0 || (b2 == b0 && i2 < i0)) { b0 = b2; i0 = i2; }
+        best = b0;
+        cls = i0;
       } else {
         best = row[0];
         for (int j = 1; j < c; ++j) {

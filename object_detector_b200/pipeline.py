@@ -1,0 +1,124 @@
+"""Stream / graph plumbing around the two halves of the hot path (no arithmetic here).
+
+The train side (``odk_assign_encode``) and the predict side (``odk_decode_nms``) of one batch are
+independent, their latency-bound kernels (greedy walk, per-image NMS) occupy a fraction of the SMs, and
+all launches are tiny — so a step is captured once into a CUDA graph with the two sides on parallel
+branches and replayed (``capture_step``).  ``HostPipeline`` adds what a caller with HOST buffers needs:
+pinned staging, separate copy-in / compute / copy-out streams and double buffering, so that the
+host->device copy of batch i+1, the kernels of batch i and the device->host copy of batch i-1 overlap
+(PCIe is full duplex).  The reference has no counterpart: its generator threads call ``encode_truth`` per
+sample on the CPU (pytoolkit/generator.py:160-166) and ``predict`` runs the whole graph per batch.
+"""
+import torch
+
+from . import _dev
+
+
+def capture_step(pb, gt, head, y_true, dets, top_k=200, conf_threshold=0.01, nms_threshold=0.45, two_streams=True):
+    """Captures ``encode_truth_batch(*gt, y_true=y_true)`` and ``decode_nms(*head, out=dets)`` into one CUDA
+    graph (parallel branches when ``two_streams``).  All tensors must be CUDA tensors that stay alive and
+    keep their addresses; replay with ``graph.replay()`` on any stream.  The first call for a PriorBoxes
+    must happen after its tables were uploaded (call either method once eagerly before capturing)."""
+    dev = y_true.device
+    side = torch.cuda.Stream(device=dev) if two_streams else None
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.device(dev), torch.cuda.graph(graph):
+        main = torch.cuda.current_stream(dev)
+        if side is not None:
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                pb.decode_nms(*head, top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold, out=dets)
+            pb.encode_truth_batch(*gt, y_true=y_true)
+            main.wait_stream(side)
+        else:
+            pb.encode_truth_batch(*gt, y_true=y_true)
+            pb.decode_nms(*head, top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold, out=dets)
+    return graph
+
+
+class HostPipeline:
+    """Host-buffer front end for fixed batch shapes.
+
+    ``submit(gt_boxes, gt_classes, gt_count, objs, clfs, locs)`` takes pinned host tensors (or NumPy
+    arrays, which are staged through an internal pinned buffer), returns a slot id immediately;
+    ``result(slot)`` waits for that batch only and returns pinned host views ``(y_true, dets)`` that stay
+    valid until the slot is submitted again (``depth`` batches later).
+    """
+
+    def __init__(self, pb, batch, gmax, top_k=200, conf_threshold=0.01, nms_threshold=0.45, depth=2, device=None,
+                 use_graph=True):
+        self.pb, self.batch, self.gmax, self.top_k, self.depth = pb, batch, gmax, top_k, depth
+        self.dev = _dev.device(device)
+        n, c = len(pb.pb_locs), pb.num_classes
+        f32, i32 = torch.float32, torch.int32
+        shapes = [((batch, gmax, 4), f32), ((batch, gmax), i32), ((batch,), i32),
+                  ((batch, n, 1), f32), ((batch, n, c), f32), ((batch, n, 4), f32)]
+        with torch.cuda.device(self.dev):
+            self.s_in, self.s_run, self.s_out = (torch.cuda.Stream(device=self.dev) for _ in range(3))
+            self.d_in = [[torch.empty(s, dtype=t, device=self.dev) for s, t in shapes] for _ in range(depth)]
+            self.h_in = [[torch.empty(s, dtype=t).pin_memory() for s, t in shapes] for _ in range(depth)]
+            self.d_y = [torch.empty((batch, n, 3 + c + 4), dtype=f32, device=self.dev) for _ in range(depth)]
+            self.d_det = [torch.empty((batch, top_k, 6), dtype=f32, device=self.dev) for _ in range(depth)]
+            self.h_y = [torch.empty((batch, n, 3 + c + 4), dtype=f32).pin_memory() for _ in range(depth)]
+            self.h_det = [torch.empty((batch, top_k, 6), dtype=f32).pin_memory() for _ in range(depth)]
+            self.ev_in = [torch.cuda.Event() for _ in range(depth)]
+            self.ev_run = [torch.cuda.Event() for _ in range(depth)]
+            self.ev_out = [torch.cuda.Event() for _ in range(depth)]
+        self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.d_in[0])
+        self.d2h_bytes = self.h_y[0].numel() * 4 + self.h_det[0].numel() * 4
+        self._kw = dict(top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold)
+        self._count = 0
+        self.graphs = None
+        if use_graph:
+            with torch.cuda.device(self.dev):
+                for t in self.d_in[0]:
+                    t.zero_()
+                self.d_in[0][2].fill_(0)  # gt_count = 0: a valid empty batch for the eager warm-up call
+                self._eager(0)            # uploads the anchor tables, sets kernel attributes
+                torch.cuda.synchronize(self.dev)
+                self.graphs = [capture_step(pb, self.d_in[k][:3], self.d_in[k][3:], self.d_y[k], self.d_det[k], **self._kw)
+                               for k in range(depth)]
+
+    def _eager(self, k):
+        self.pb.encode_truth_batch(*self.d_in[k][:3], y_true=self.d_y[k])
+        self.pb.decode_nms(*self.d_in[k][3:], out=self.d_det[k], **self._kw)
+
+    def submit(self, *host_inputs):
+        k = self._count % self.depth
+        self._count += 1
+        src = []
+        for i, x in enumerate(host_inputs):
+            if isinstance(x, torch.Tensor) and x.is_pinned():
+                src.append(x)
+            else:  # pageable memory: stage through the slot's pinned buffer (safe: the slot's last H2D has completed)
+                self.ev_in[k].synchronize()
+                self.h_in[k][i].copy_(torch.as_tensor(x).reshape(self.h_in[k][i].shape))
+                src.append(self.h_in[k][i])
+        with torch.cuda.device(self.dev):
+            self.s_in.wait_event(self.ev_run[k])   # the kernels that last read this slot's inputs are done
+            with torch.cuda.stream(self.s_in):
+                for d, h in zip(self.d_in[k], src):
+                    d.copy_(h.reshape(d.shape), non_blocking=True)
+                self.ev_in[k].record(self.s_in)
+            self.s_run.wait_event(self.ev_in[k])
+            self.s_run.wait_event(self.ev_out[k])  # the slot's previous outputs have left the device
+            with torch.cuda.stream(self.s_run):
+                if self.graphs is not None:
+                    self.graphs[k].replay()
+                else:
+                    self._eager(k)
+                self.ev_run[k].record(self.s_run)
+            self.s_out.wait_event(self.ev_run[k])
+            with torch.cuda.stream(self.s_out):
+                self.h_y[k].copy_(self.d_y[k], non_blocking=True)
+                self.h_det[k].copy_(self.d_det[k], non_blocking=True)
+                self.ev_out[k].record(self.s_out)
+        return k
+
+    def result(self, slot):
+        self.ev_out[slot].synchronize()
+        return self.h_y[slot], self.h_det[slot]
+
+    def synchronize(self):
+        for s in (self.s_in, self.s_run, self.s_out):
+            s.synchronize()
