@@ -169,6 +169,10 @@ def run_cuda(args):
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
     local = int(os.environ.get('LOCAL_RANK', '0'))
+    # native libraries (NCCL's version banner) write to fd 1: keep stdout clean for the single JSON line
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     assert world == args.gpus or world == 1, f'WORLD_SIZE={world} but --gpus {args.gpus}'
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
@@ -313,7 +317,10 @@ def run_cuda(args):
             'gpu_launches': launches_per_step * args.steps, 'gpu_launches_per_step': launches_per_step,
             'roofline': roofline, 'cpu_baseline': cpu,
         }
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
         print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
     if world > 1:
         dist.destroy_process_group()
 
