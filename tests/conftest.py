@@ -25,6 +25,9 @@ ANCHOR_SETS = {
     'voc640': ((640, 640), [40, 20, 10], 20),
     'tiny128': ((128, 128), [8], 2),
     'stress1120': ((1120, 1120), [140, 70, 35], 80),
+    'mid80': ((256, 256), [16, 8], 80),    # C=80  -> 64-row candidate pieces / W=87 encode rows
+    'mid100': ((192, 192), [12, 6], 100),  # C=100 -> 32-row candidate pieces / 32-row encode tiles, C % 4 == 0
+    'odd7': ((160, 160), [10, 5], 7),      # C=7   -> scalar argmax path, unaligned row widths
 }
 
 

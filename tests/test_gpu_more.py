@@ -1,0 +1,174 @@
+"""More GPU parity cases: class counts that select the other kernel templates, ties, extreme ground-truth
+sizes for the scattered ignore mask, multi-round / uncached NMS, CUDA-graph replay and the host pipeline."""
+import numpy as np
+import pytest
+import torch
+
+import object_detector_b200 as odk
+from object_detector_b200 import pipeline, synth
+from oracle import restated as R
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize('name', ['mid80', 'mid100', 'odd7'])
+def test_other_class_counts_full_path(prior_boxes, oracle_tables, name):
+    """C=80 (64-row pieces), C=100 (32-row pieces and encode tiles), C=7 (scalar arg-max, odd row width)."""
+    pb, t = prior_boxes(name), oracle_tables(name)
+    c, n = pb.num_classes, len(pb)
+    objs, clfs, locs = synth.predictions(31, 3, n, c)
+    classes, confs, boxes = pb.decode_score(objs, clfs, locs)
+    rc, rs = R.score_anchors(t, objs, clfs)
+    assert np.array_equal(classes.cpu().numpy(), rc) and np.array_equal(confs.cpu().numpy(), rs)
+    assert np.array_equal(boxes.cpu().numpy(), R.decode_locs_f32(t, locs))
+    out, kept = pb.decode_nms(objs, clfs, locs, return_index=True)
+    ro, rk = R.predict_tail(t, objs, clfs, locs)
+    assert np.array_equal(kept.cpu().numpy(), rk) and np.array_equal(out.cpu().numpy(), ro)
+    gtb, gtc, gtn = synth.gt_batch(5, 4, 9, c, size=(0.1, 0.5))
+    res = pb.encode_truth_batch(gtb, gtc, gtn)
+    ref = R.encode_truth(t, [(gtc[i, :gtn[i]], gtb[i, :gtn[i]]) for i in range(4)])
+    assert (res['status'].cpu().numpy() == 0).all()
+    assert np.array_equal(res['y_true'].cpu().numpy(), ref)
+
+
+def test_argmax_ties_first_maximum_wins(prior_boxes, oracle_tables):
+    """Quantised class scores produce many exact ties: np.argmax semantics (layers.py:80) in both kernels."""
+    pb, t = prior_boxes('voc640'), oracle_tables('voc640')
+    rng = np.random.RandomState(3)
+    objs, clfs, locs = synth.predictions(9, 2, len(pb), 20)
+    clfs = (rng.randint(0, 4, size=clfs.shape) / 4.0).astype(np.float32)
+    objs = rng.uniform(0.05, 1.0, size=objs.shape).astype(np.float32)
+    classes, confs, _ = pb.decode_score(objs, clfs, locs)
+    rc, rs = R.score_anchors(t, objs, clfs)
+    assert np.array_equal(classes.cpu().numpy(), rc) and np.array_equal(confs.cpu().numpy(), rs)
+    # fused path on the same tied data: compare with the unfused layer fed by the dense kernel
+    out, kept = pb.decode_nms(objs, clfs, locs, return_index=True)
+    out2, kept2 = odk.layers.nms()(20, len(pb))(list(pb.decode_score(objs, clfs, locs)), return_index=True)
+    assert torch.equal(out, out2) and torch.equal(kept, kept2)
+
+
+def _closed_form_valids(t, boxes, assigned):
+    """SURVEY A-4: pb_valids = not(pb_mask and any_g IoU(g, a) >= 0.5) or assigned[a]."""
+    iou = R.pairwise_iou(boxes, t.pb_locs)
+    v = ~(t.pb_mask & (iou >= np.float32(0.5)).any(axis=0))
+    v[assigned] = True
+    return v
+
+
+@pytest.mark.parametrize('name,seed', [('voc640', 1), ('voc320', 2), ('mid80', 3), ('stress1120', 4)])
+def test_ignore_mask_scatter_extreme_sizes(prior_boxes, oracle_tables, name, seed):
+    """The ignore mask is scattered per GT over a cell range derived from a necessary condition for
+    IoU >= 0.5; it must equal the dense closed form for boxes from a few pixels up to the whole image,
+    including boxes that match an anchor exactly."""
+    pb, t = prior_boxes(name), oracle_tables(name)
+    rng = np.random.RandomState(seed)
+    batch, g = 6, 48
+    gtb = np.zeros((batch, g, 4), np.float32)
+    for i in range(batch):
+        lo, hi = [(0.004, 0.05), (0.02, 0.3), (0.2, 1.0)][i % 3]
+        # anchors themselves (clipped), jittered by up to ~1%: IoU close to 1 and around the cell borders
+        pick = rng.choice(np.flatnonzero(t.pb_mask), 8, replace=False)
+        a = np.clip(t.pb_locs[pick] + rng.uniform(-0.003, 0.003, size=(8, 4)).astype(np.float32), 0, 1)
+        a = a[(a[:, 2] - a[:, 0] > 1e-3) & (a[:, 3] - a[:, 1] > 1e-3)]
+        gtb[i] = np.concatenate([synth.gt_boxes(rng, g - len(a), size=(lo, hi)), a]).astype(np.float32)
+    gtn = np.full((batch,), g, np.int32)
+    gtc = rng.randint(0, pb.num_classes, size=(batch, g)).astype(np.int32)
+    res = pb.encode_truth_batch(gtb, gtc, gtn, want_valids=True)
+    status = res['status'].cpu().numpy()
+    valids = res['pb_valids'].cpu().numpy()
+    pbi = res['pb_indices'].cpu().numpy()
+    checked = 0
+    for i in range(batch):
+        if status[i] != 0:  # a centre inside no valid cell: the reference raises as well
+            with pytest.raises(AssertionError):
+                R.assign_boxes(t, gtb[i])
+            continue
+        assert np.array_equal(valids[i], _closed_form_valids(t, gtb[i], pbi[i])), i
+        checked += 1
+    assert checked >= 3
+
+
+def test_nms_many_rounds_and_large_top_k():
+    """Heavy suppression with top_k above the band size: several select/sort/sweep rounds per image."""
+    rng = np.random.RandomState(21)
+    n = 6000
+    c = 0.5 + rng.uniform(-0.08, 0.08, size=(n, 2))
+    s = rng.uniform(0.05, 0.25, size=(n, 2))
+    boxes = np.clip(np.concatenate([c - s / 2, c + s / 2], 1), 0, 1).astype(np.float32)
+    scores = (rng.permutation(n).astype(np.float32) + 1) / (n + 1)
+    for top_k, thr in [(200, 0.45), (700, 0.6), (1, 0.45), (2, 0.3)]:
+        out = odk.ml.non_maximum_suppression(boxes, scores, top_k, thr)
+        assert np.array_equal(out, R.numpy_nms_policy(boxes, scores, top_k, thr)), (top_k, thr)
+
+
+def test_nms_equal_scores_need_low_key_bits():
+    """All scores equal: the radix select has to descend into the class / anchor bits of the keys."""
+    rng = np.random.RandomState(5)
+    n = 3000
+    c = rng.uniform(0.05, 0.95, size=(n, 2))
+    boxes = np.clip(np.concatenate([c - 0.01, c + 0.01], 1), 0, 1).astype(np.float32)
+    scores = np.full((n,), 0.5, np.float32)
+    out = odk.ml.non_maximum_suppression(boxes, scores, 300, 0.45)
+    assert np.array_equal(out, R.numpy_nms_policy(boxes, scores, 300, 0.45))
+
+
+def test_nms_layer_single_class_flood(prior_boxes, oracle_tables):
+    """Every candidate in ONE class (the worst case for the per-class warps) and > 8192 candidates per image
+    (keys do not fit the shared-memory cache)."""
+    pb, t = prior_boxes('voc640'), oracle_tables('voc640')
+    objs, clfs, locs = synth.predictions(13, 1, len(pb), 20)
+    clfs[:] = 0.01
+    clfs[:, :, 7] = 0.81
+    objs[:] = np.random.RandomState(1).uniform(0.2, 1.0, size=objs.shape).astype(np.float32)
+    locs *= 0.3
+    out, kept = pb.decode_nms(objs, clfs, locs, return_index=True)
+    ro, rk = R.predict_tail(t, objs, clfs, locs)
+    assert (rk >= 0).sum() > 50
+    assert np.array_equal(kept.cpu().numpy(), rk) and np.array_equal(out.cpu().numpy(), ro)
+
+
+def test_graph_replay_equals_eager(prior_boxes):
+    pb = prior_boxes('voc640')
+    gt = [torch.from_numpy(x).cuda() for x in synth.gt_batch(3, 8, 16, 20)]
+    head = [torch.from_numpy(x).cuda() for x in synth.predictions(4, 8, len(pb), 20)]
+    y_ref = pb.encode_truth_batch(*gt)['y_true']
+    d_ref = pb.decode_nms(*head)
+    y, d = torch.zeros_like(y_ref), torch.zeros_like(d_ref)
+    for two in (True, False):
+        g = pipeline.capture_step(pb, gt, head, y, d, two_streams=two)
+        for _ in range(3):
+            y.fill_(-1)
+            d.fill_(-1)
+            g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(y, y_ref) and torch.equal(d, d_ref)
+    # new inputs in the same buffers: the graph reads them
+    gt2 = synth.gt_batch(33, 8, 16, 20)
+    for dst, src in zip(gt, gt2):
+        dst.copy_(torch.from_numpy(src))
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(y, pb.encode_truth_batch(*gt)['y_true'])
+
+
+@pytest.mark.parametrize('use_graph', [True, False])
+def test_host_pipeline_results_in_order(prior_boxes, use_graph):
+    pb = prior_boxes('voc320')
+    batch, gmax = 4, 8
+    pipe = pipeline.HostPipeline(pb, batch, gmax, use_graph=use_graph)
+    sets = [synth.gt_batch(100 + i, batch, gmax, 20) + synth.predictions(200 + i, batch, len(pb), 20) for i in range(5)]
+    got = []
+    prev = None
+    for i, s in enumerate(sets):
+        src = [torch.from_numpy(x).pin_memory() for x in s] if i % 2 == 0 else list(s)  # pinned and pageable inputs
+        slot = pipe.submit(*src)
+        if prev is not None:
+            y, d = pipe.result(prev)
+            got.append((y.clone(), d.clone()))
+        prev = slot
+    y, d = pipe.result(prev)
+    got.append((y.clone(), d.clone()))
+    for s, (y, d) in zip(sets, got):
+        assert torch.equal(y, pb.encode_truth_batch(*s[:3])['y_true'].cpu())
+        assert torch.equal(d, pb.decode_nms(*s[3:]).cpu())
+    assert pipe.h2d_bytes == sum(x.nbytes for x in sets[0])
