@@ -36,7 +36,6 @@ namespace {
 constexpr int kNmsThreads = 1024;
 constexpr int kNmsWarps = kNmsThreads / 32;
 constexpr int kBand = 512;
-constexpr int kBandMin = 256;   // a select level is accepted once it yields at least this many keys
 constexpr int kDigitBits = 11;
 constexpr int kBins = 1 << kDigitBits;
 constexpr int kCollectPiece = 256;
@@ -152,10 +151,11 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* s_warp /*[kNmsWa
 // same network among themselves on dummy keys so that the barriers stay uniform): strides below 32 are
 // exchanged with warp shuffles, the rest through a double-buffered shared-memory array (one barrier per
 // such stage).
-__device__ __forceinline__ unsigned long long block_sort_desc_1(unsigned long long key, unsigned long long* s_x /*[2][kNmsThreads]*/) {
+__device__ __forceinline__ unsigned long long block_sort_desc_1(unsigned long long key, unsigned long long* s_x /*[2][kNmsThreads]*/,
+                                                                int n_sort /* power of two >= the number of real keys */) {
   const int tid = threadIdx.x;
   int pb = 0;
-  for (int k = 2; k <= kBand; k <<= 1) {
+  for (int k = 2; k <= n_sort; k <<= 1) {
     const bool desc = (tid & k) == 0;
     for (int j = k >> 1; j > 0; j >>= 1) {
       unsigned long long other;
@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
   __shared__ unsigned short s_clslist[kBand];
   __shared__ int s_scan[kNmsWarps + 1];
   __shared__ unsigned long long s_mm[2 * kNmsWarps];
-  __shared__ int s_nb, s_sel_r, s_sel_cnt;
+  __shared__ int s_nb, s_sel[4];
 
   const int tid = threadIdx.x;
   const int lane = (int)odk_lane();
@@ -261,6 +261,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     // ---- a. threshold of the next band: MSB radix select starting at the first bit in which the
     //         remaining keys differ (fp32 scores share their leading exponent bits) -------------------------
     unsigned long long lo_key = 0ull;
+    const int want = min(kBand, (limit - nkept) + ((limit - nkept) >> 2) + 32);  // band size aimed at: 1.25x what is still needed
     if (remaining > kBand) {
       unsigned long long kmin = ~0ull, kmax = 0ull;
       for (int i = tid; i < total; i += kNmsThreads) {
@@ -308,25 +309,33 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
         }
         int tot_in_bucket;
         int run = above + block_exclusive_scan(lsum, s_scan, tot_in_bucket);
-        int n_ok = 0, last_ok_sum = -1;
+        // S is monotone over r, so "S < want" and "S <= kBand" each hold on a prefix of the bins
+        int n_ok = 0, last_ok_sum = -1, n_lt = 0, first_ge_sum = INT_MAX;
 #pragma unroll
         for (int j = 0; j < per; ++j) {
           run += loc[j];
           const int r = tid * per + j;
-          if (r < nb_bins && run <= kBand) { ++n_ok; last_ok_sum = run; }
+          if (r < nb_bins) {
+            if (run <= kBand) { ++n_ok; last_ok_sum = run; }
+            if (run < want) ++n_lt;
+            else first_ge_sum = min(first_ge_sum, run);
+          }
         }
-        if (tid == 0) { s_sel_r = 0; s_sel_cnt = above; }
+        if (tid == 0) { s_sel[0] = 0; s_sel[1] = above; s_sel[2] = 0; s_sel[3] = INT_MAX; }
         __syncthreads();
-        if (n_ok) {
-          atomicAdd(&s_sel_r, n_ok);
-          atomicMax(&s_sel_cnt, last_ok_sum);  // S is monotone: the largest accepted running sum
-        }
+        if (n_ok) { atomicAdd(&s_sel[0], n_ok); atomicMax(&s_sel[1], last_ok_sum); }
+        if (n_lt) atomicAdd(&s_sel[2], n_lt);
+        if (first_ge_sum != INT_MAX) atomicMin(&s_sel[3], first_ge_sum);
         __syncthreads();
-        const int n_take_bins = s_sel_r;   // digits nb_bins-1 .. nb_bins-n_take_bins are taken whole
-        const int cnt_take = s_sel_cnt;
-        const int d_star = nb_bins - n_take_bins;
+        // Prefer the shortest run of top digits that reaches `want` keys (the sweep rarely needs more); if the
+        // bin that crosses `want` would overflow the band, take the bins before it and, when that is too few,
+        // refine inside the crossing bin.
+        int n_take_bins, cnt_take;
+        if (s_sel[2] < s_sel[0]) { n_take_bins = s_sel[2] + 1; cnt_take = s_sel[3]; }
+        else { n_take_bins = s_sel[0]; cnt_take = s_sel[1]; }
+        const int d_star = nb_bins - n_take_bins;  // digits >= d_star are taken whole
         __syncthreads();
-        if (cnt_take >= kBandMin || shift == 0) {
+        if (cnt_take >= max(32, want / 2) || shift == 0) {
           if (d_star < nb_bins) lo_key = ((prefix << width) | (unsigned long long)d_star) << shift;
           else lo_key = (prefix + 1ull) << top;  // nothing of this bucket: only the keys above it (top < 64 here)
           break;
@@ -349,7 +358,9 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     }
     __syncthreads();
     const int nb = min(s_nb, kBand);
-    const unsigned long long my_key = block_sort_desc_1(tid < nb ? s_band[tid] : 0ull, s_x);
+    int n_sort = 32;
+    while (n_sort < nb) n_sort <<= 1;
+    const unsigned long long my_key = block_sort_desc_1(tid < nb ? s_band[tid] : 0ull, s_x, n_sort);
     hi_key = lo_key;
     processed += nb;
 
