@@ -1,5 +1,6 @@
-// K3 + K4 — training-target generation: PriorBoxes._assign_boxes + encode_truth
-// (dl/od_pb.py:299-363), plus the small drop-ins compute_iou / encode_locs.
+// K3 — anchor assignment: PriorBoxes._assign_boxes (dl/od_pb.py:315-363), plus the small drop-ins
+// compute_iou / encode_locs.  The y_true writer that consumes the assignment (encode_truth) lives in
+// encode_rows.cu.
 //
 // K3 — the reference's loop over ground-truth boxes is inherently sequential (each GT removes one
 //   anchor), but everything that does not depend on the "taken" state is not:
@@ -15,12 +16,6 @@
 //       no free in-cell anchor -> fallback (od_pb.py:347-352): CTA-wide arg-max of the exact fp32 IoU
 //       over free valid anchors, first maximum wins.
 //   Emits pb_indices (ascending anchor id) / gt_indices / status.
-// K4 encode_rows_kernel — one CTA per (image, 128-anchor tile): computes the order-independent
-//   ignore mask  pb_mask & any_g IoU(g, a) >= 0.5  (closed form of od_pb.py:355-361, SURVEY A-4)
-//   with GT boxes staged in shared memory, builds the tile's y_true rows [mask, weight, obj,
-//   onehot(C), locs(4)] in shared memory, patches the <= G positives, and writes the tile — a
-//   contiguous 128*(3+C+4)*4-byte span of HBM — with one bulk TMA store (cp.async.bulk.global).
-//   Algorithmic bytes: 4*N*(3+C+4) written per image; GT/assignment lists are a few KB.
 #include <float.h>
 
 #include "odk_common.cuh"
@@ -399,166 +394,6 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   if (lane == 0) p.status[b] = ODK_IMG_OK;
 }
 
-struct EncodeArgs {
-  AnchorView av;
-  int batch, gmax;
-  const float4* gt_boxes;
-  const int32_t* gt_classes;
-  const int32_t* gt_count;
-  const long long* pb_indices;
-  const long long* gt_indices;
-  const int32_t* status;
-  float* y_true;
-  uint8_t* pb_valids;
-  const unsigned* ignore;  // [B, bitmap_words] from assign_candidates_kernel
-  int bitmap_words;
-};
-
-// Per-item inputs, staged in shared memory by cp.async one item ahead.
-struct EncodeStage {
-  long long* pb;     // [gmax] assigned anchors (ascending)
-  long long* gi;     // [gmax] the GT each one owns
-  unsigned* ignore;  // [TILE/32] ignore-mask words of this tile
-  int* meta;         // [2] = gt_count, status
-};
-
-template <int TILE>
-__global__ void __launch_bounds__(TILE) encode_rows_kernel(const EncodeArgs p, int items_per_cta) {
-  extern __shared__ __align__(128) unsigned char enc_smem[];
-  const int C = p.av.num_classes;
-  const int W = 3 + C + 4;
-  const int tid = threadIdx.x;
-  const size_t rows_bytes = odk_align_up((size_t)TILE * W * 4, 128);
-  const size_t stage_bytes = odk_align_up((size_t)p.gmax * 16 + 32, 16);
-  auto stage = [&](int i) {  // pointers by arithmetic (no dynamically indexed local arrays)
-    unsigned char* q = enc_smem + 2 * rows_bytes + (size_t)i * stage_bytes;
-    EncodeStage e;
-    e.ignore = reinterpret_cast<unsigned*>(q);
-    e.meta = reinterpret_cast<int*>(q + 16);
-    e.pb = reinterpret_cast<long long*>(q + 32);
-    e.gi = reinterpret_cast<long long*>(q + 32 + (size_t)p.gmax * 8);
-    return e;
-  };
-  __shared__ int s_owner[TILE];
-
-  const int n_tiles = (p.av.n + TILE - 1) / TILE;
-  const long long n_items = (long long)n_tiles * p.batch;  // tile-major: item = tile * B + b
-  const long long first = (long long)blockIdx.x * items_per_cta;
-  const int count = (int)(min(n_items, first + items_per_cta) - first);
-  if (count <= 0) return;
-  int tile = (int)(first / p.batch), b = (int)(first % p.batch);  // advanced incrementally
-
-  auto prefetch = [&](int pt, int pb_, int buf) {  // all threads; one commit group per item
-    const size_t g0 = (size_t)pb_ * p.gmax;
-    const EncodeStage e = stage(buf);
-    for (int g = tid; g < p.gmax; g += TILE) {
-      odk_cp_async<8>(e.pb + g, p.pb_indices + g0 + g);
-      odk_cp_async<8>(e.gi + g, p.gt_indices + g0 + g);
-    }
-    if (tid < TILE / 32 && pt * (TILE / 32) + tid < p.bitmap_words)
-      odk_cp_async<4>(e.ignore + tid, p.ignore + (size_t)pb_ * p.bitmap_words + (size_t)pt * (TILE / 32) + tid);
-    if (tid == TILE / 32) odk_cp_async<4>(e.meta, p.gt_count + pb_);
-    if (tid == TILE / 32 + 1) odk_cp_async<4>(e.meta + 1, p.status + pb_);
-    odk_cp_async_commit();
-  };
-
-  prefetch(tile, b, 0);
-  {  // both row buffers start all-zero; afterwards every item only rewrites what it dirtied
-    float4* z = reinterpret_cast<float4*>(enc_smem);
-    const int n4 = (int)(2 * rows_bytes / 16);
-    for (int i = tid; i < n4; i += TILE) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  s_owner[tid] = -1;
-
-  int cur_tile = -1, a0 = 0, rows = 0, a = 0;
-  bool anchor_ok = false;  // inside the table and pb_mask set
-  int dirty0 = -1, dirty1 = -1;  // class column this thread set in row buffer 0 / 1 (-1: its row is clean)
-  int n_stores = 0;
-  bool last_was_bulk = false;
-
-  for (int it = 0; it < count; ++it) {
-    const int buf = it & 1;
-    int nt = tile, nb = b + 1;  // the next item
-    if (nb == p.batch) { nb = 0; ++nt; }
-    if (it + 1 < count) prefetch(nt, nb, buf ^ 1);
-    else odk_cp_async_commit();  // keep the group count uniform
-    if (tile != cur_tile) {
-      cur_tile = tile;
-      a0 = tile * TILE;
-      rows = min(TILE, p.av.n - a0);
-      a = a0 + tid;
-      anchor_ok = tid < rows && p.av.mask[a];
-    }
-    // ---- A: this item's inputs are staged, and row buffer `buf` (stored two items ago) has been read out ----
-    odk_cp_async_wait<1>();
-    if (tid == 0 && n_stores > 0) {
-      if (last_was_bulk) odk_bulk_wait_read<1>();  // only the previous item's store may still be reading
-      else odk_bulk_wait_read<0>();
-    }
-    __syncthreads();
-    const EncodeStage s = stage(buf);
-    float* rowbuf = reinterpret_cast<float*>(enc_smem + (size_t)buf * rows_bytes);
-    float* row = rowbuf + (size_t)tid * W;
-    const bool ok = s.meta[1] == ODK_IMG_OK;
-    const int G = ok ? s.meta[0] : 0;
-    {  // undo the positive this thread wrote into the buffer two items ago
-      const int dirty = buf ? dirty1 : dirty0;
-      if (dirty >= 0) {
-        row[1] = 0.f; row[2] = 0.f; row[3 + dirty] = 0.f;
-        row[3 + C] = 0.f; row[3 + C + 1] = 0.f; row[3 + C + 2] = 0.f; row[3 + C + 3] = 0.f;
-      }
-      if (buf) dirty1 = -1; else dirty0 = -1;
-    }
-    for (int g = tid; g < G; g += TILE) {  // assignment slot g: anchor pa owns GT gi[g]
-      const int pa = (int)s.pb[g];
-      if (pa >= a0 && pa < a0 + rows) s_owner[pa - a0] = g;
-    }
-    __syncthreads();  // B
-    const float w0 = __fdiv_rn(1.0f, (float)max(1, G));  // float32(1/max(1,G)), od_pb.py:306 (== the fp64 quotient rounded once)
-    const bool ignored = anchor_ok && ((s.ignore[tid >> 5] >> (tid & 31)) & 1u);  // od_pb.py:355-357
-    const int own = s_owner[tid];
-    if (tid < rows) {
-      const bool valid = ok && (!ignored || own >= 0);  // pb_valids[pb_indices] = True (od_pb.py:361)
-      row[0] = valid ? w0 : 0.0f;
-      if (own >= 0) {  // positives (one per GT): od_pb.py:307-311
-        const int g = (int)s.gi[own];
-        const float4 box = __ldg(p.gt_boxes + (size_t)b * p.gmax + g);
-        const int cls = __ldg(p.gt_classes + (size_t)b * p.gmax + g);
-        const float4 ab = __ldg(p.av.locs + a);
-        const double2 sz = p.av.sizes[a];
-        row[1] = __fdiv_rn(1.0f, (float)G);
-        row[2] = 1.0f;
-        row[3 + cls] = 1.0f;
-        row[3 + C + 0] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.x, ab.x), sz.x), 0.10);
-        row[3 + C + 1] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.y, ab.y), sz.y), 0.10);
-        row[3 + C + 2] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.z, ab.z), sz.x), 0.10);
-        row[3 + C + 3] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.w, ab.w), sz.y), 0.10);
-        if (buf) dirty1 = cls; else dirty0 = cls;
-        s_owner[tid] = -1;
-      }
-      if (p.pb_valids != nullptr) p.pb_valids[(size_t)b * p.av.n + a] = valid ? 1 : 0;
-    }
-    odk_fence_proxy_async();  // generic-proxy smem writes -> visible to the bulk (async-proxy) store
-    __syncthreads();          // C
-    float* dst = p.y_true + ((size_t)b * p.av.n + a0) * W;
-    const uint32_t bytes = (uint32_t)rows * W * 4;
-    if (((uintptr_t)dst & 15) == 0 && (bytes & 15) == 0) {
-      if (tid == 0) {
-        odk_bulk_s2g(dst, rowbuf, bytes);
-        odk_bulk_commit();
-      }
-      ++n_stores;
-      last_was_bulk = true;
-    } else {
-      for (int i = tid; i < rows * W; i += TILE) dst[i] = rowbuf[i];
-      last_was_bulk = false;
-    }
-    tile = nt;
-    b = nb;
-  }
-  if (tid == 0) odk_bulk_wait_read<0>();  // shared memory must outlive the bulk reads
-}
-
 __global__ void compute_iou_kernel(const float4* __restrict__ a, int na, const float4* __restrict__ b, int nb, float* __restrict__ out) {
   const long long total = (long long)na * nb;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -591,20 +426,19 @@ int assign_list_len(int gmax) {
   return list_len > 128 ? 128 : (list_len < 8 ? 8 : list_len);
 }
 
-size_t assign_lists_bytes(int batch, int gmax) {
+}  // namespace
+
+// ---- internal interface shared with encode_rows.cu ----------------------------------------------------------
+size_t odk_assign_lists_bytes(int batch, int gmax) {
   return odk_align_up(sizeof(int) * (size_t)batch * gmax * ((size_t)assign_list_len(gmax) + 2), 256);
 }
-size_t assign_workspace_bytes(int n, int batch, int gmax) {
-  return assign_lists_bytes(batch, gmax) + odk_align_up(sizeof(unsigned) * (size_t)batch * ((n + 31) / 32), 256);
-}
 
-int launch_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count, int gmax,
-                  int64_t* pb_indices, int64_t* gt_indices, int32_t* status, bool want_ignore, void* workspace, size_t workspace_bytes,
-                  cudaStream_t stream) {
-  ODK_REQUIRE(workspace != nullptr && workspace_bytes >= assign_workspace_bytes(a->n, batch, gmax), ODK_ERR_WORKSPACE,
-              "assign: workspace of %zu bytes is smaller than the required %zu", workspace_bytes, assign_workspace_bytes(a->n, batch, gmax));
-  ODK_REQUIRE(((uintptr_t)workspace & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "assign: workspace must be 16-byte aligned");
-  AssignArgs args;
+// Candidate ranking (+ the ignore-mask scatter when `ignore` is given: [B, ceil(N/32)] words, pre-zeroed), then
+// the greedy walk; `lists_ws` holds odk_assign_lists_bytes() bytes.  Two launches so that a caller can fork other
+// work between them.
+static int fill_args(AssignArgs& args, const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes,
+                     const int32_t* gt_count, int gmax, int64_t* pb_indices, int64_t* gt_indices, int32_t* status, void* lists_ws,
+                     unsigned* ignore) {
   args.av = odk_view(a);
   args.batch = batch; args.gmax = gmax;
   args.gt_boxes = reinterpret_cast<const float4*>(gt_boxes);
@@ -614,23 +448,33 @@ int launch_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const 
   args.status = status;
   args.bitmap_words = (a->n + 31) / 32;
   args.list_len = assign_list_len(gmax);
-  args.ws_list = static_cast<int*>(workspace);
+  args.ws_list = static_cast<int*>(lists_ws);
   args.ws_ncand = args.ws_list + (size_t)batch * gmax * args.list_len;
   args.ws_nlist = args.ws_ncand + (size_t)batch * gmax;
-  args.ws_ignore = nullptr;
-  if (want_ignore) {
-    args.ws_ignore = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + assign_lists_bytes(batch, gmax));
-    ODK_CUDA(cudaMemsetAsync(args.ws_ignore, 0, sizeof(unsigned) * (size_t)batch * args.bitmap_words, stream));
-  }
-  const size_t smem = odk_align_up((size_t)gmax * (16 + 20 + 4 * (size_t)args.list_len) + (size_t)args.bitmap_words * 4, 16);
-  ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign: N=%d / Gmax=%d need %zu bytes of shared memory per image", a->n, gmax, smem);
-  ODK_CUDA(cudaFuncSetAttribute(assign_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  args.ws_ignore = ignore;
+  return ODK_OK;
+}
+
+int odk_launch_assign_candidates(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_count, int gmax, void* lists_ws,
+                                 unsigned* ignore, cudaStream_t stream) {
+  AssignArgs args;
+  fill_args(args, a, batch, gt_boxes, nullptr, gt_count, gmax, nullptr, nullptr, nullptr, lists_ws, ignore);
   const long long tasks = (long long)batch * gmax;
   {
     OdkProfileScope prof_("assign_candidates_kernel", stream);
     assign_candidates_kernel<<<(unsigned)((tasks + kGreedyWarps - 1) / kGreedyWarps), kGreedyThreads, 0, stream>>>(args);
   }
   ODK_LAUNCH_CHECK("assign_candidates_kernel");
+  return ODK_OK;
+}
+
+int odk_launch_assign_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count,
+                             int gmax, int64_t* pb_indices, int64_t* gt_indices, int32_t* status, void* lists_ws, cudaStream_t stream) {
+  AssignArgs args;
+  fill_args(args, a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, lists_ws, nullptr);
+  const size_t smem = odk_align_up((size_t)gmax * (16 + 20 + 4 * (size_t)args.list_len) + (size_t)args.bitmap_words * 4, 16);
+  ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign: N=%d / Gmax=%d need %zu bytes of shared memory per image", a->n, gmax, smem);
+  ODK_CUDA(cudaFuncSetAttribute(assign_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   {
     OdkProfileScope prof_("assign_greedy_kernel", stream);
     assign_greedy_kernel<<<batch, kGreedyThreads, smem, stream>>>(args);
@@ -639,33 +483,8 @@ int launch_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const 
   return ODK_OK;
 }
 
-template <int TILE>
-int launch_encode(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
-  const size_t smem = 2 * odk_align_up((size_t)TILE * W * 4, 128) + 2 * odk_align_up((size_t)e.gmax * 16 + 32, 16);
-  ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign_encode: C=%d / Gmax=%d need %zu bytes of shared memory", W - 7, e.gmax, smem);
-  auto kern = encode_rows_kernel<TILE>;
-  ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  const long long n_items = (long long)((n + TILE - 1) / TILE) * e.batch;
-  int per_sm = (int)((220 * 1024) / (smem + 2048));
-  per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / TILE ? 2048 / TILE : per_sm);
-  int sms = 0, dev = 0;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (sms <= 0) sms = 148;
-  long long grid = (long long)sms * per_sm;
-  if (grid > n_items) grid = n_items;
-  const int per_cta = (int)((n_items + grid - 1) / grid);
-  grid = (n_items + per_cta - 1) / per_cta;
-  {
-    OdkProfileScope prof_("encode_rows_kernel", stream);
-    kern<<<(unsigned)grid, TILE, smem, stream>>>(e, per_cta);
-  }
-  ODK_LAUNCH_CHECK("encode_rows_kernel");
-  return ODK_OK;
-}
-
-int assign_check(const odk_anchors* a, int batch, const void* gt_boxes, const void* gt_count, int gmax, const void* pb, const void* gt,
-                 const void* status) {
+int odk_assign_check(const odk_anchors* a, int batch, const void* gt_boxes, const void* gt_count, int gmax, const void* pb, const void* gt,
+                     const void* status) {
   ODK_REQUIRE(a != nullptr, ODK_ERR_INVALID_ARGUMENT, "assign: null anchors handle");
   ODK_REQUIRE(batch >= 1 && gmax >= 1, ODK_ERR_INVALID_ARGUMENT, "assign: batch=%d gmax=%d must be >= 1", batch, gmax);
   ODK_REQUIRE(gt_boxes && gt_count && pb && gt && status, ODK_ERR_INVALID_ARGUMENT, "assign: null pointer");
@@ -673,43 +492,30 @@ int assign_check(const odk_anchors* a, int batch, const void* gt_boxes, const vo
   return ODK_OK;
 }
 
-}  // namespace
+size_t odk_assign_workspace_bytes_impl(int n, int batch, int gmax) {
+  return odk_assign_lists_bytes(batch, gmax) + odk_align_up(sizeof(unsigned) * (size_t)batch * ((n + 31) / 32), 256);
+}
+
+int odk_assign_workspace_check(const odk_anchors* a, int batch, int gmax, const void* workspace, size_t workspace_bytes) {
+  const size_t need = odk_assign_workspace_bytes_impl(a->n, batch, gmax);
+  ODK_REQUIRE(workspace != nullptr && workspace_bytes >= need, ODK_ERR_WORKSPACE, "assign: workspace of %zu bytes is smaller than the required %zu",
+              workspace_bytes, need);
+  ODK_REQUIRE(((uintptr_t)workspace & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "assign: workspace must be 16-byte aligned");
+  return ODK_OK;
+}
 
 extern "C" size_t odk_assign_workspace_bytes(const odk_anchors* a, int batch, int gmax) {
   if (a == nullptr || batch < 1 || gmax < 1) return 0;
-  return assign_workspace_bytes(a->n, batch, gmax);
+  return odk_assign_workspace_bytes_impl(a->n, batch, gmax);
 }
 
 extern "C" int odk_assign(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_count, int gmax, int64_t* pb_indices,
                           int64_t* gt_indices, int32_t* status, void* workspace, size_t workspace_bytes, void* stream) {
-  if (int rc = assign_check(a, batch, gt_boxes, gt_count, gmax, pb_indices, gt_indices, status)) return rc;
-  return launch_greedy(a, batch, gt_boxes, nullptr, gt_count, gmax, pb_indices, gt_indices, status, false, workspace, workspace_bytes,
-                       static_cast<cudaStream_t>(stream));
-}
-
-extern "C" int odk_assign_encode(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count,
-                                 int gmax, float* y_true, int64_t* pb_indices, int64_t* gt_indices, uint8_t* pb_valids, int32_t* status,
-                                 void* workspace, size_t workspace_bytes, void* stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (int rc = assign_check(a, batch, gt_boxes, gt_count, gmax, pb_indices, gt_indices, status)) return rc;
-  ODK_REQUIRE(gt_classes && y_true, ODK_ERR_INVALID_ARGUMENT, "assign_encode: null pointer");
-  ODK_REQUIRE(((uintptr_t)y_true & 3) == 0, ODK_ERR_INVALID_ARGUMENT, "assign_encode: y_true must be 4-byte aligned");
-  if (int rc = launch_greedy(a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, true, workspace, workspace_bytes,
-                             stream))
-    return rc;
-  EncodeArgs e;
-  e.av = odk_view(a);
-  e.batch = batch; e.gmax = gmax;
-  e.gt_boxes = reinterpret_cast<const float4*>(gt_boxes);
-  e.gt_classes = gt_classes; e.gt_count = gt_count;
-  e.pb_indices = reinterpret_cast<const long long*>(pb_indices);
-  e.gt_indices = reinterpret_cast<const long long*>(gt_indices);
-  e.status = status; e.y_true = y_true; e.pb_valids = pb_valids;
-  e.bitmap_words = (a->n + 31) / 32;
-  e.ignore = reinterpret_cast<const unsigned*>(static_cast<const char*>(workspace) + assign_lists_bytes(batch, gmax));
-  const int W = 3 + a->num_classes + 4;
-  if (W <= 100) return launch_encode<128>(e, a->n, W, stream);
-  return launch_encode<32>(e, a->n, W, stream);
+  if (int rc = odk_assign_check(a, batch, gt_boxes, gt_count, gmax, pb_indices, gt_indices, status)) return rc;
+  if (int rc = odk_assign_workspace_check(a, batch, gmax, workspace, workspace_bytes)) return rc;
+  if (int rc = odk_launch_assign_candidates(a, batch, gt_boxes, gt_count, gmax, workspace, nullptr, static_cast<cudaStream_t>(stream))) return rc;
+  return odk_launch_assign_greedy(a, batch, gt_boxes, nullptr, gt_count, gmax, pb_indices, gt_indices, status, workspace,
+                                  static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int odk_compute_iou(const float* a, int na, const float* b, int nb, float* out, void* stream) {

@@ -250,6 +250,8 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   const long long total = (long long)args.batch * args.tiles_per_image;
   int per_sm = (int)((220 * 1024) / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / TILE ? 2048 / TILE : per_sm);
+  // EMIT runs beside the train-side kernels of the same step (other graph branch): leave them shared memory
+  if (!DENSE && per_sm > 2) per_sm = 2;
   long long grid = (long long)sm_count_cached() * per_sm;
   if (grid > total) grid = total;
   if (grid < 1) grid = 1;

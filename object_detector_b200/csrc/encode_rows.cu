@@ -1,0 +1,259 @@
+// K4 — the y_true writer: PriorBoxes.encode_truth (dl/od_pb.py:299-313) on top of the assignment of
+// assign_encode.cu (whose candidate kernel also scatters the ignore mask into a per-image bitmap).  Two
+// kernels, arranged so that the HBM-bound stream does not wait for the latency-bound greedy walk:
+//
+//   encode_rows_kernel     HBM-write-bound: every row of y_true with column 0 = 1/max(1,G) where the anchor is
+//                          not ignored, zeros elsewhere — produced 16 bytes at a time in registers from the
+//                          packed pb_mask and ignore bitmaps and written with coalesced st.global.v4.  No shared
+//                          memory, so it co-resides with the latency-bound kernels running beside it.
+//                          Algorithmic bytes: 4*N*(3+C+4) written per image.
+//   encode_patch_kernel    the <= G positive rows per image [w0, 1/G, 1, onehot(C), encode_locs] (od_pb.py:
+//                          307-311; they are valid whatever the ignore mask says, od_pb.py:359-361), and the
+//                          all-zero result of images whose assignment failed.
+//
+// Stream layout inside odk_assign_encode: the caller's stream runs memset -> candidates (+ ignore mask) -> greedy;
+// a per-thread side stream, forked after the candidates and joined with events (capturable into a CUDA graph),
+// runs the rows kernel next to the greedy walk; the patch kernel runs on the caller's stream after the join.
+#include <stdlib.h>
+
+#include "odk_common.cuh"
+
+// from assign_encode.cu
+size_t odk_assign_lists_bytes(int batch, int gmax);
+int odk_launch_assign_candidates(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_count, int gmax, void* lists_ws,
+                                 unsigned* ignore, cudaStream_t stream);
+int odk_launch_assign_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count,
+                             int gmax, int64_t* pb_indices, int64_t* gt_indices, int32_t* status, void* lists_ws, cudaStream_t stream);
+int odk_assign_check(const odk_anchors* a, int batch, const void* gt_boxes, const void* gt_count, int gmax, const void* pb, const void* gt,
+                     const void* status);
+int odk_assign_workspace_check(const odk_anchors* a, int batch, int gmax, const void* workspace, size_t workspace_bytes);
+
+namespace {
+
+struct EncodeArgs {
+  AnchorView av;
+  int batch, gmax;
+  const int32_t* gt_count;
+  const unsigned* ignore;  // [B, bitmap_words] from assign_ignore_kernel
+  int bitmap_words;
+  float* y_true;
+  uint8_t* pb_valids;      // optional
+};
+
+constexpr int kRowsThreads = 256;
+constexpr int kRowsPerThread = 8;  // 16-byte stores per thread
+
+// y_true of one image is a contiguous array of N*W floats, all zero except column 0.  Each thread produces whole
+// 16-byte pieces of it in registers — a piece holds at most one column-0 element because W >= 8 — and stores them
+// with coalesced st.global.v4: no shared memory (the kernel co-resides with anything), nothing to wait for.
+// A thread's pieces are kRowsThreads*VEC floats apart; (row, column) of the first comes from one division, the
+// others by adding the constant step; the bitmap words of all pieces are loaded before the first store.
+template <int VEC>
+__global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeArgs p, unsigned step_rows, unsigned step_cols) {
+  const int b = blockIdx.y;
+  const unsigned W = 3 + p.av.num_classes + 4;
+  const unsigned n = (unsigned)p.av.n;
+  const int g_count = p.gt_count[b];
+  const bool count_ok = g_count >= 0 && g_count <= p.gmax;   // otherwise the image fails (patch kernel zeroes it)
+  const float w0 = count_ok ? __fdiv_rn(1.0f, (float)max(1, g_count)) : 0.0f;  // float32(1/max(1,G)), od_pb.py:306
+  const unsigned* ign = p.ignore + (size_t)b * p.bitmap_words;
+  const unsigned* mb = p.av.maskbits;
+  const unsigned total = n * W;  // floats per image (< 2^31, checked by the launcher)
+  float* y = p.y_true + (size_t)b * total;
+  const unsigned pieces = (total + VEC - 1) / VEC;
+  const unsigned i0 = blockIdx.x * (kRowsThreads * kRowsPerThread) + threadIdx.x;
+  unsigned row = (i0 * VEC) / W, col = (i0 * VEC) - row * W;
+  float w[kRowsPerThread];
+  int j[kRowsPerThread];
+#pragma unroll
+  for (int u = 0; u < kRowsPerThread; ++u) {
+    // the next column-0 element at or after this piece: offset jj within the piece, row r
+    const unsigned jj = (col == 0) ? 0u : W - col;
+    const unsigned r = (col == 0) ? row : row + 1;
+    const bool has = jj < (unsigned)VEC && r < n && (i0 + u * kRowsThreads) < pieces;
+    const unsigned rw = has ? (r >> 5) : 0u;
+    const unsigned bits = __ldg(mb + rw) & ign[rw];  // pb_mask and IoU >= 0.5 with some GT (od_pb.py:355-357)
+    w[u] = (has && !((bits >> (r & 31)) & 1u)) ? w0 : 0.0f;
+    j[u] = (int)jj;
+    row += step_rows;
+    col += step_cols;
+    if (col >= W) { col -= W; ++row; }
+  }
+#pragma unroll
+  for (int u = 0; u < kRowsPerThread; ++u) {
+    const unsigned i = i0 + u * kRowsThreads;
+    if (i < pieces) {
+      if (VEC == 4)
+        reinterpret_cast<float4*>(y)[i] =
+            make_float4(j[u] == 0 ? w[u] : 0.f, j[u] == 1 ? w[u] : 0.f, j[u] == 2 ? w[u] : 0.f, j[u] == 3 ? w[u] : 0.f);
+      else
+        y[i] = w[u];
+    }
+  }
+  if (p.pb_valids != nullptr) {
+#pragma unroll
+    for (int u = 0; u < kRowsPerThread; ++u) {
+      const unsigned a = i0 + u * kRowsThreads;
+      if (a < n) {
+        const unsigned bits = __ldg(mb + (a >> 5)) & ign[a >> 5];
+        p.pb_valids[(size_t)b * n + a] = (count_ok && !((bits >> (a & 31)) & 1u)) ? 1 : 0;
+      }
+    }
+  }
+}
+
+struct PatchArgs {
+  AnchorView av;
+  int batch, gmax;
+  const float4* gt_boxes;
+  const int32_t* gt_classes;
+  const int32_t* gt_count;
+  const long long* pb_indices;
+  const long long* gt_indices;
+  const int32_t* status;
+  float* y_true;
+  uint8_t* pb_valids;
+};
+
+// One CTA per image: the positives (od_pb.py:307-311), or an all-zero image when the assignment failed.
+__global__ void __launch_bounds__(128) encode_patch_kernel(const PatchArgs p) {
+  const int b = blockIdx.x;
+  const int C = p.av.num_classes;
+  const int W = 3 + C + 4;
+  float* y = p.y_true + (size_t)b * p.av.n * W;
+  if (p.status[b] != ODK_IMG_OK) {
+    for (int a = threadIdx.x; a < p.av.n; a += blockDim.x) {
+      y[(size_t)a * W] = 0.0f;
+      if (p.pb_valids != nullptr) p.pb_valids[(size_t)b * p.av.n + a] = 0;
+    }
+    return;
+  }
+  const int G = p.gt_count[b];
+  const float w0 = __fdiv_rn(1.0f, (float)max(1, G));
+  for (int k = threadIdx.x; k < G; k += blockDim.x) {  // assignment slot k: anchor pa owns GT g
+    const int pa = (int)p.pb_indices[(size_t)b * p.gmax + k];
+    const int g = (int)p.gt_indices[(size_t)b * p.gmax + k];
+    const float4 box = p.gt_boxes[(size_t)b * p.gmax + g];
+    const int cls = p.gt_classes[(size_t)b * p.gmax + g];
+    const float4 ab = __ldg(p.av.locs + pa);
+    const double2 sz = p.av.sizes[pa];
+    float* row = y + (size_t)pa * W;
+    row[0] = w0;  // pb_valids[pb_indices] = True (od_pb.py:361)
+    row[1] = __fdiv_rn(1.0f, (float)G);
+    row[2] = 1.0f;
+    row[3 + cls] = 1.0f;
+    row[3 + C + 0] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.x, ab.x), sz.x), 0.10);
+    row[3 + C + 1] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.y, ab.y), sz.y), 0.10);
+    row[3 + C + 2] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.z, ab.z), sz.x), 0.10);
+    row[3 + C + 3] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.w, ab.w), sz.y), 0.10);
+    if (p.pb_valids != nullptr) p.pb_valids[(size_t)b * p.av.n + pa] = 1;
+  }
+}
+
+// ---- per-host-thread side stream (fork/join with events; works under stream capture) ---------------------------
+struct SideLane {
+  cudaStream_t stream;
+  cudaEvent_t fork, join;
+  bool ready;
+};
+
+int side_lane(SideLane** out) {
+  constexpr int kMaxDevices = 64;
+  static thread_local SideLane lanes[kMaxDevices] = {};
+  int dev = 0;
+  ODK_CUDA(cudaGetDevice(&dev));
+  ODK_REQUIRE(dev >= 0 && dev < kMaxDevices, ODK_ERR_UNSUPPORTED, "device index %d out of range", dev);
+  SideLane& l = lanes[dev];
+  if (!l.ready) {
+    ODK_CUDA(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
+    ODK_CUDA(cudaEventCreateWithFlags(&l.fork, cudaEventDisableTiming));
+    ODK_CUDA(cudaEventCreateWithFlags(&l.join, cudaEventDisableTiming));
+    l.ready = true;
+  }
+  *out = &l;
+  return ODK_OK;
+}
+
+int launch_rows(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
+  const long long total = (long long)n * W;
+  ODK_REQUIRE(total < 0x7fffffffLL, ODK_ERR_UNSUPPORTED, "assign_encode: image of %lld floats too large", total);
+  const bool vec = (total % 4 == 0) && (((uintptr_t)e.y_true & 15) == 0);
+  const int v = vec ? 4 : 1;
+  const long long pieces = total / v;
+  const long long per_cta = (long long)kRowsThreads * kRowsPerThread;
+  const long long gx = (pieces + per_cta - 1) / per_cta;  // >= ceil(n / per_cta): the pb_valids loop is covered too
+  const unsigned step = (unsigned)(kRowsThreads * v);     // floats between a thread's consecutive pieces
+  dim3 grid((unsigned)gx, (unsigned)e.batch);
+  {
+    OdkProfileScope prof_("encode_rows_kernel", stream);
+    if (vec) encode_rows_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W);
+    else encode_rows_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W);
+  }
+  ODK_LAUNCH_CHECK("encode_rows_kernel");
+  return ODK_OK;
+}
+
+}  // namespace
+
+extern "C" int odk_assign_encode(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count,
+                                 int gmax, float* y_true, int64_t* pb_indices, int64_t* gt_indices, uint8_t* pb_valids, int32_t* status,
+                                 void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = odk_assign_check(a, batch, gt_boxes, gt_count, gmax, pb_indices, gt_indices, status)) return rc;
+  if (int rc = odk_assign_workspace_check(a, batch, gmax, workspace, workspace_bytes)) return rc;
+  ODK_REQUIRE(gt_classes && y_true, ODK_ERR_INVALID_ARGUMENT, "assign_encode: null pointer");
+  ODK_REQUIRE(((uintptr_t)y_true & 3) == 0, ODK_ERR_INVALID_ARGUMENT, "assign_encode: y_true must be 4-byte aligned");
+  ODK_REQUIRE(batch <= 65535, ODK_ERR_UNSUPPORTED, "assign_encode: batch=%d > 65535", batch);
+  const int words = (a->n + 31) / 32;
+  unsigned* ignore = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + odk_assign_lists_bytes(batch, gmax));
+  SideLane* lane = nullptr;
+  if (int rc = side_lane(&lane)) return rc;
+  static const bool single_stream = getenv("ODK_SINGLE_STREAM") != nullptr;  // debugging aid: no fork/join
+  SideLane same = {stream, lane->fork, lane->join, true};
+  if (single_stream) lane = &same;
+
+  // caller's stream: ignore mask (scattered per GT) + ranked candidate lists
+  ODK_CUDA(cudaMemsetAsync(ignore, 0, sizeof(unsigned) * (size_t)batch * words, stream));
+  if (int rc = odk_launch_assign_candidates(a, batch, gt_boxes, gt_count, gmax, workspace, ignore, stream)) return rc;
+  // fork: the side stream streams out the rows (HBM-bound) ...
+  ODK_CUDA(cudaEventRecord(lane->fork, stream));
+  ODK_CUDA(cudaStreamWaitEvent(lane->stream, lane->fork, 0));
+  {
+    EncodeArgs e;
+    e.av = odk_view(a);
+    e.batch = batch; e.gmax = gmax;
+    e.gt_count = gt_count; e.ignore = ignore; e.bitmap_words = words;
+    e.y_true = y_true; e.pb_valids = pb_valids;
+    const int W = 3 + a->num_classes + 4;
+    const int rc = launch_rows(e, a->n, W, lane->stream);
+    ODK_CUDA(cudaEventRecord(lane->join, lane->stream));
+    if (rc) {
+      cudaStreamWaitEvent(stream, lane->join, 0);  // never leave the side stream un-joined (stream capture)
+      return rc;
+    }
+  }
+  // ... while the caller's stream walks the GTs (latency-bound, one CTA per image)
+  {
+    const int rc = odk_launch_assign_greedy(a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, workspace, stream);
+    if (rc) {
+      cudaStreamWaitEvent(stream, lane->join, 0);
+      return rc;
+    }
+  }
+  // join, then the positives
+  ODK_CUDA(cudaStreamWaitEvent(stream, lane->join, 0));
+  PatchArgs q;
+  q.av = odk_view(a);
+  q.batch = batch; q.gmax = gmax;
+  q.gt_boxes = reinterpret_cast<const float4*>(gt_boxes);
+  q.gt_classes = gt_classes; q.gt_count = gt_count;
+  q.pb_indices = reinterpret_cast<const long long*>(pb_indices);
+  q.gt_indices = reinterpret_cast<const long long*>(gt_indices);
+  q.status = status; q.y_true = y_true; q.pb_valids = pb_valids;
+  {
+    OdkProfileScope prof_("encode_patch_kernel", stream);
+    encode_patch_kernel<<<batch, 128, 0, stream>>>(q);
+  }
+  ODK_LAUNCH_CHECK("encode_patch_kernel");
+  return ODK_OK;
+}

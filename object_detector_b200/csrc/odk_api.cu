@@ -90,7 +90,7 @@ static int upload(T** dst, const void* src, size_t count) {
 
 extern "C" int odk_anchors_destroy(odk_anchors* a) {
   if (a == nullptr) return ODK_OK;
-  cudaFree(a->d_locs); cudaFree(a->d_grid); cudaFree(a->d_sizes); cudaFree(a->d_scale); cudaFree(a->d_mask);
+  cudaFree(a->d_locs); cudaFree(a->d_grid); cudaFree(a->d_sizes); cudaFree(a->d_scale); cudaFree(a->d_mask); cudaFree(a->d_maskbits);
   free(a);
   return ODK_OK;
 }
@@ -147,6 +147,16 @@ extern "C" int odk_anchors_create(odk_anchors** out, int n, int num_classes, int
   if (!rc) rc = upload(&a->d_sizes, pb_sizes, n);
   if (!rc) rc = upload(&a->d_scale, scale, n);
   if (!rc) rc = upload(&a->d_mask, pb_mask, n);
+  if (!rc) {
+    const size_t words = ((size_t)n + 31) / 32;
+    uint32_t* bits = static_cast<uint32_t*>(calloc(words, sizeof(uint32_t)));
+    if (bits == nullptr) rc = odk_set_error(ODK_ERR_CUDA, "anchors_create: out of host memory");
+    else {
+      for (int i = 0; i < n; ++i) if (pb_mask[i]) bits[i >> 5] |= 1u << (i & 31);
+      rc = upload(&a->d_maskbits, bits, words);
+      free(bits);
+    }
+  }
   free(scale);
   if (rc) { odk_anchors_destroy(a); return rc; }
   *out = a;

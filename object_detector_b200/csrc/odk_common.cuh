@@ -24,6 +24,7 @@ struct odk_anchors {
   double2* d_sizes;  // pb_sizes (w,h) fp64
   float2* d_scale;   // float32(0.10 * pb_sizes)
   uint8_t* d_mask;   // pb_mask
+  uint32_t* d_maskbits;  // pb_mask packed, bit (a & 31) of word a >> 5
 };
 
 // By-value kernel argument (pointers + layout); no device-side handle dereference.
@@ -36,6 +37,7 @@ struct AnchorView {
   const double2* sizes;
   const float2* scale;
   const uint8_t* mask;
+  const uint32_t* maskbits;
 };
 
 inline AnchorView odk_view(const odk_anchors* a) {
@@ -44,7 +46,7 @@ inline AnchorView odk_view(const odk_anchors* a) {
   v.n_valid = a->n_valid;
   for (int i = 0; i < ODK_MAX_MAPS; ++i) v.map_size[i] = a->map_size[i];
   for (int i = 0; i <= ODK_MAX_MAPS; ++i) v.map_off[i] = a->map_off[i];
-  v.locs = a->d_locs; v.grid = a->d_grid; v.sizes = a->d_sizes; v.scale = a->d_scale; v.mask = a->d_mask;
+  v.locs = a->d_locs; v.grid = a->d_grid; v.sizes = a->d_sizes; v.scale = a->d_scale; v.mask = a->d_mask; v.maskbits = a->d_maskbits;
   return v;
 }
 
