@@ -144,6 +144,15 @@ int odk_voc_ap(int n_img, int top_k, int num_classes, const float* dets /*[dev n
                int gt_max_per_image, double* ap_area /*[dev C]*/, double* ap07 /*[dev C]*/,
                void* workspace, size_t workspace_bytes, void* stream);
 
+/* ml.compute_scores (ml.py:352-394) for n_thr confidence thresholds at once (ml.search_conf_threshold,
+ * ml.py:328-340, sweeps 50 of them): counts[t, 0/1/2, c] = TP / FP / FN of class c at conf_thr[t].
+ * dets / GT arrays as in odk_voc_ap (boxes normalised fp32, IoU in fp32 like ml.compute_iou). */
+int odk_match_counts(int n_img, int top_k, int num_classes, const float* dets /*[dev n_img,top_k,6]*/,
+                     const float* gt_boxes /*[dev n_gt,4]*/, const int32_t* gt_classes /*[dev n_gt]*/,
+                     const uint8_t* gt_difficult /*[dev n_gt]*/, const int32_t* gt_offsets /*[dev n_img+1]*/,
+                     int n_thr, const float* conf_thr /*[dev n_thr]*/, float iou_thr,
+                     int32_t* counts /*[dev n_thr,3,C]*/, void* stream);
+
 /* Measurement aid (bench.py): when enabled for the calling host thread every kernel launch of the
  * library is bracketed by CUDA events on its stream; odk_profile_read synchronises them and returns,
  * per kernel name, the summed device time and the launch count, then clears the log. */

@@ -41,6 +41,8 @@ SIGNATURES = {
     'odk_voc_ap_workspace_bytes': (c_size_t, [c_int, c_int, c_int, c_int]),
     'odk_voc_ap': (c_int, [c_int, c_int, c_int, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p,
                            c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    'odk_match_counts': (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
+                                 c_float, c_void_p, c_void_p]),
     'odk_profile_enable': (c_int, [c_int]),
     'odk_profile_read': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
 }

@@ -112,3 +112,53 @@ def non_maximum_suppression(boxes, scores, top_k=200, iou_threshold=0.45):
     k = int(cnt.item())
     res = out[:k].to(torch.int64)
     return res.cpu().numpy() if is_np else res
+
+
+def _match_counts(gt, pred, conf_thresholds, iou_threshold, num_classes):
+    """(n_thr, 3, C) int64 TP / FP / FN counts through odk_match_counts (one launch for all thresholds)."""
+    from . import voc  # packing helpers shared with the VOC evaluation
+    dev = _dev.device()
+    g = voc.pack_ground_truth(gt, dev)
+    dets = voc.pack_predictions(pred, dev)
+    thr = _dev.to_device(np.asarray(conf_thresholds, dtype=np.float32), torch.float32, dev)
+    counts = torch.empty((len(thr), 3, num_classes), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call('odk_match_counts', len(gt), dets.shape[1], int(num_classes), dets.data_ptr(), g['boxes'].data_ptr(),
+                  g['classes'].data_ptr(), g['difficult'].data_ptr(), g['offsets'].data_ptr(), len(thr), thr.data_ptr(),
+                  float(iou_threshold), counts.data_ptr(), _dev.stream_ptr(dev))
+    return counts.cpu().numpy().astype(np.int64)
+
+
+def _scores_from_counts(tp, fp, fn):
+    supports = tp + fn
+    precisions = tp.astype(float) / (tp + fp + 1e-7)
+    recalls = tp.astype(float) / (supports + 1e-7)
+    fscores = 2 / (1 / (precisions + 1e-7) + 1 / (recalls + 1e-7))
+    return precisions, recalls, fscores, supports
+
+
+def compute_scores(gt, pred, conf_threshold=0, iou_threshold=0.5, num_classes=None):
+    """ml.py:352-394 -> (precisions, recalls, fscores, supports) per class."""
+    assert len(gt) == len(pred)
+    assert 0 < iou_threshold < 1
+    assert 0 <= conf_threshold < 1
+    if num_classes is None:
+        num_classes = np.max(np.concatenate([y.classes for y in gt])) + 1
+    c = _match_counts(gt, pred, [conf_threshold], iou_threshold, int(num_classes))[0]
+    return _scores_from_counts(c[0], c[1], c[2])
+
+
+def search_conf_threshold(gt, pred, iou_threshold=0.5):
+    """ml.py:328-340: the conf_threshold maximising the support-weighted F1 — all 50 thresholds in one launch."""
+    conf_threshold_list = np.linspace(0.01, 0.99, 50)
+    num_classes = int(np.max(np.concatenate([y.classes for y in gt])) + 1)
+    counts = _match_counts(gt, pred, conf_threshold_list, iou_threshold, num_classes)
+    scores = []
+    for c in counts:
+        _, _, fscores, supports = _scores_from_counts(c[0], c[1], c[2])
+        scores.append(np.average(fscores, weights=supports))
+    scores = np.array(scores)
+    max_scores = scores >= 1
+    if max_scores.any():
+        return np.mean(conf_threshold_list[max_scores])
+    return conf_threshold_list[scores.argmax()]

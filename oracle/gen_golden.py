@@ -160,10 +160,26 @@ def gen_iou_nms_decode():
     np.savez_compressed(OUT / 'iou_nms_decode.npz', **d)
 
 
+def gen_scores():
+    """ml.compute_scores / search_conf_threshold (ml.py:328-394) of the unmodified reference on a seeded set."""
+    d = {}
+    gts, preds = synth.eval_set(77, 60, 5, max_gt=5, n_fp=6)
+    y_true = [Ann('.', w, h, c, b, dif) for (w, h, c, b, dif) in gts]
+    y_pred = [tk.ml.ObjectsPrediction(c, s, b) for (c, s, b) in preds]
+    d['seed'] = np.array([77, 60, 5, 5, 6])
+    for i, th in enumerate([0.0, 0.25, 0.6]):
+        p, r, f, s = tk.ml.compute_scores(y_true, y_pred, th, 0.5, num_classes=5)
+        d[f'scores_{i}/conf_threshold'] = np.array(th)
+        d[f'scores_{i}/precisions'], d[f'scores_{i}/recalls'], d[f'scores_{i}/fscores'], d[f'scores_{i}/supports'] = p, r, f, s
+    d['search_conf_threshold'] = np.array(tk.ml.search_conf_threshold(y_true, y_pred, 0.5))
+    np.savez_compressed(OUT / 'scores.npz', **d)
+
+
 if __name__ == '__main__':
     OUT.mkdir(parents=True, exist_ok=True)
     gen_anchors()
     gen_iou_nms_decode()
     gen_assign()
+    gen_scores()
     for p in sorted(OUT.glob('*.npz')):
         print(p.name, p.stat().st_size)

@@ -413,3 +413,53 @@ def voc_evaluate(gt_list, pred_list, num_classes):
     ap07 = voc_ap(n_pos, score, match, True)
     with np.errstate(invalid='ignore'):
         return {'AP': ap, 'mAP': np.nanmean(ap), 'AP_VOC': ap07, 'mAP_VOC': np.nanmean(ap07)}
+
+
+# --------------------------------------------------------------------------------------
+def match_counts(gt_list, pred_list, conf_threshold, iou_threshold, num_classes):
+    """Counting part of ml.compute_scores (ml.py:352-389).  gt_list = [(classes, bboxes f32, difficults)],
+    pred_list = [(classes, confs f32, bboxes f32)].  Returns int arrays tp, fp, fn."""
+    tp = np.zeros((num_classes,), dtype=int)
+    fp = np.zeros((num_classes,), dtype=int)
+    fn = np.zeros((num_classes,), dtype=int)
+    for (gc, gb, gd), (pc, ps, pb) in zip(gt_list, pred_list):
+        enabled = ps >= conf_threshold  # f32 array vs Python float: compared in f32 (NEP 50)
+        for cls, box, difficult in zip(gc, gb, gd):
+            sel = np.logical_and(enabled, pc == cls)
+            hit = False
+            if sel.any():
+                iou = pairwise_iou(box[None, :], pb[sel])[0, :]
+                k = iou.argmax()
+                hit = iou[k] >= iou_threshold
+            if hit:
+                if not difficult:
+                    tp[cls] += 1
+                enabled[np.flatnonzero(sel)[k]] = False
+            elif not difficult:
+                fn[cls] += 1
+        for cls in pc[enabled]:
+            fp[cls] += 1
+    return tp, fp, fn
+
+
+def scores_from_counts(tp, fp, fn):
+    """ml.py:390-394."""
+    supports = tp + fn
+    precisions = tp.astype(float) / (tp + fp + 1e-7)
+    recalls = tp.astype(float) / (supports + 1e-7)
+    fscores = 2 / (1 / (precisions + 1e-7) + 1 / (recalls + 1e-7))
+    return precisions, recalls, fscores, supports
+
+
+def search_conf_threshold(gt_list, pred_list, num_classes, iou_threshold=0.5):
+    """ml.py:328-340."""
+    grid = np.linspace(0.01, 0.99, 50)
+    scores = []
+    for th in grid:
+        _, _, f, s = scores_from_counts(*match_counts(gt_list, pred_list, th, iou_threshold, num_classes))
+        scores.append(np.average(f, weights=s))
+    scores = np.array(scores)
+    full = scores >= 1
+    if full.any():
+        return np.mean(grid[full])
+    return grid[scores.argmax()]

@@ -172,3 +172,32 @@ def test_host_pipeline_results_in_order(prior_boxes, use_graph):
         assert torch.equal(y, pb.encode_truth_batch(*s[:3])['y_true'].cpu())
         assert torch.equal(d, pb.decode_nms(*s[3:]).cpu())
     assert pipe.h2d_bytes == sum(x.nbytes for x in sets[0])
+
+
+def _score_objects(seed, n_img, classes, **kw):
+    gts, preds = synth.eval_set(seed, n_img, classes, **kw)
+    y_true = [odk.ml.ObjectsAnnotation('.', w, h, c, b, d) for (w, h, c, b, d) in gts]
+    y_pred = [odk.ml.ObjectsPrediction(c, s, b) for (c, s, b) in preds]
+    return y_true, y_pred, [(c, b, d) for (_, _, c, b, d) in gts], preds
+
+
+def test_compute_scores_golden_from_reference(golden):
+    g = golden['scores']
+    y_true, y_pred, _, _ = _score_objects(77, 60, 5, max_gt=5, n_fp=6)
+    for i in range(3):
+        p, r, f, s = odk.ml.compute_scores(y_true, y_pred, float(g[f'scores_{i}/conf_threshold']), 0.5, num_classes=5)
+        assert np.array_equal(s, g[f'scores_{i}/supports'])
+        assert np.array_equal(p, g[f'scores_{i}/precisions']) and np.array_equal(r, g[f'scores_{i}/recalls'])
+        assert np.array_equal(f, g[f'scores_{i}/fscores'])
+    assert odk.ml.search_conf_threshold(y_true, y_pred) == float(g['search_conf_threshold'])
+
+
+def test_compute_scores_vs_oracle_voc_sized():
+    """4952 images x 50 thresholds in one launch; counts are integers -> bit-exact scores."""
+    y_true, y_pred, gt, pred = _score_objects(2007, 4952, 20)
+    for th in (0.0, 0.31, 0.9):
+        res = odk.ml.compute_scores(y_true, y_pred, th, 0.5)
+        ref = R.scores_from_counts(*R.match_counts(gt, pred, th, 0.5, 20))
+        for a, b in zip(res, ref):
+            assert np.array_equal(a, b), th
+    assert odk.ml.search_conf_threshold(y_true[:400], y_pred[:400]) == R.search_conf_threshold(gt[:400], pred[:400], 20)

@@ -155,3 +155,22 @@ def test_restatement_against_live_reference(oracle_tables):
     b = synth.gt_boxes(rng, 300, size=(0.05, 0.3))
     s = rng.permutation(300).astype(np.float32) / 300
     assert np.array_equal(tk.ml.non_maximum_suppression(b, s, 50, 0.45), R.numpy_nms_policy(b, s, 50, 0.45))
+
+
+def _score_sets():
+    from object_detector_b200 import synth
+    gts, preds = synth.eval_set(77, 60, 5, max_gt=5, n_fp=6)
+    return [(c, b, d) for (_, _, c, b, d) in gts], preds
+
+
+def test_compute_scores_golden(golden):
+    """ml.compute_scores / search_conf_threshold (ml.py:328-394) vs outputs of the unmodified reference."""
+    g = golden['scores']
+    gt, pred = _score_sets()
+    for i in range(3):
+        th = float(g[f'scores_{i}/conf_threshold'])
+        p, r, f, s = R.scores_from_counts(*R.match_counts(gt, pred, th, 0.5, 5))
+        assert np.array_equal(s, g[f'scores_{i}/supports'])
+        assert np.array_equal(p, g[f'scores_{i}/precisions']) and np.array_equal(r, g[f'scores_{i}/recalls'])
+        assert np.array_equal(f, g[f'scores_{i}/fscores'])
+    assert R.search_conf_threshold(gt, pred, 5) == float(g['search_conf_threshold'])
