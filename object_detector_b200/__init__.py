@@ -2,7 +2,7 @@
 anchor<->GT assignment + target encoding, and decode + score + per-class NMS (+ VOC AP), behind the
 reference's own Python call signatures.  All arithmetic runs in libodk.so (hand-written CUDA, reached
 through ctypes); there is no CPU or PyTorch fallback."""
-from . import _lib, dist, layers, ml, od, od_pb, voc  # noqa: F401
+from . import _lib, dist, generator, layers, ml, od, od_pb, voc  # noqa: F401
 from .od import ObjectDetector  # noqa: F401
 from .od_pb import PriorBoxes  # noqa: F401
 

@@ -201,3 +201,28 @@ def test_compute_scores_vs_oracle_voc_sized():
         for a, b in zip(res, ref):
             assert np.array_equal(a, b), th
     assert odk.ml.search_conf_threshold(y_true[:400], y_pred[:400]) == R.search_conf_threshold(gt[:400], pred[:400], 20)
+
+
+def test_encode_truth_hook_coalesces_threads(prior_boxes):
+    """The per-sample hook of the data pipeline (dl/od.py:169) called from worker threads like the reference's
+    generator does (generator.py:160-166): same rows as the batched call, few launches."""
+    import threading
+    from object_detector_b200 import generator
+    od = odk.ObjectDetector.load_voc((320, 320))
+    boxes, classes, counts = synth.gt_batch(5, 24, 6, 20, crowded_every=0)
+    anns = [odk.ml.ObjectsAnnotation('.', 100, 100, classes[i, :counts[i]], boxes[i, :counts[i]]) for i in range(24)]
+    ref = od.pb.encode_truth(anns)
+    hook = generator.encode_truth_hook(od, max_batch=16, max_wait_ms=100.0)
+    out = [None] * 24
+
+    def work(i):
+        out[i] = hook(anns[i])
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(24)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert all(np.array_equal(out[i], ref[i]) for i in range(24))
+    assert hook.coalescer.batches < 24 and hook.coalescer.items == 24
+    assert np.array_equal(generator.collate_truth(od.pb, anns), ref)
+    hook.coalescer.close()

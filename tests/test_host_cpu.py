@@ -103,3 +103,33 @@ def test_no_cpu_fallback():
 def test_product_never_imports_oracle():
     for p in (ROOT / 'object_detector_b200').rglob('*.py'):
         assert 'oracle' not in re.sub(r'#.*', '', p.read_text()), f'{p} mentions the oracle'
+
+
+def test_batch_coalescer_groups_concurrent_calls():
+    """generator.BatchCoalescer: per-item calls from many threads are served by few batched calls, each caller
+    gets its own result, and an exception of the batched function reaches every caller of that batch."""
+    import threading
+    from object_detector_b200.generator import BatchCoalescer
+    seen = []
+
+    def fn(items):
+        seen.append(len(items))
+        if any(i < 0 for i in items):
+            raise ValueError('bad item')
+        return [i * i for i in items]
+    co = BatchCoalescer(fn, max_batch=16, max_wait_ms=50.0)
+    out = {}
+
+    def work(i):
+        out[i] = co(i)
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(40)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert out == {i: i * i for i in range(40)}
+    assert sum(seen) == 40 and max(seen) <= 16 and len(seen) < 40
+    with pytest.raises(ValueError):
+        co(-1)
+    assert co(3) == 9  # still alive after an error
+    co.close()
