@@ -126,6 +126,24 @@ int odk_decode_nms(const odk_anchors* a, int batch, const float* objs, const flo
                    float* out /*[dev B,top_k,6]*/, int32_t* kept_index /*[dev B,top_k]*/,
                    void* workspace /*[dev]*/, size_t workspace_bytes, void* stream);
 
+/* strict_nms=True (od_net.py:175 -> layers.py:890 nms_all_threshold=0.5): the per-class limit doubles
+ * to 2*top_k (layers.py:940) and a second, class-agnostic greedy NMS at nms_all_thr runs over the
+ * class-concatenated survivors in descending score (layers.py:953-957), cut at top_k.  Both stages
+ * run inside the same per-image sweep.  Equal scores are visited lower class first in the second
+ * stage (tie policy of this build; identical to the reference for distinct scores).  Needs the
+ * larger workspace below. */
+size_t odk_nms_strict_workspace_bytes(int batch, int n, int num_classes, int top_k);
+int odk_nms_layer_strict(int batch, int n, int num_classes, const int32_t* classes /*[dev B,N]*/,
+                         const float* confs /*[dev B,N]*/, const float* boxes /*[dev B,N,4]*/,
+                         float conf_thr, float iou_thr, float nms_all_thr, int top_k, int iou_ge,
+                         float* out /*[dev B,top_k,6]*/, int32_t* kept_index /*[dev B,top_k]*/,
+                         void* workspace /*[dev]*/, size_t workspace_bytes, void* stream);
+int odk_decode_nms_strict(const odk_anchors* a, int batch, const float* objs, const float* clfs,
+                          const float* locs, float conf_thr, float iou_thr, float nms_all_thr,
+                          int top_k, int iou_ge, float* out /*[dev B,top_k,6]*/,
+                          int32_t* kept_index /*[dev B,top_k]*/, void* workspace /*[dev]*/,
+                          size_t workspace_bytes, void* stream);
+
 /* ml.non_maximum_suppression (ml.py:589-625) on one fp32 box set: writes the kept input indices
  * in descending-score order to out_index[0:*out_count] (capacity max(top_k,2)). */
 int odk_nms(const float* boxes /*[dev n,4]*/, const float* scores /*[dev n]*/, int n, int top_k,

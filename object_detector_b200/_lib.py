@@ -36,6 +36,11 @@ SIGNATURES = {
                               c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_decode_nms': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_float, c_float, c_int, c_int,
                                c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    'odk_nms_strict_workspace_bytes': (c_size_t, [c_int, c_int, c_int, c_int]),
+    'odk_nms_layer_strict': (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_float, c_float, c_float, c_int, c_int,
+                                     c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    'odk_decode_nms_strict': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_float, c_float, c_float, c_int, c_int,
+                                      c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_nms': (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p, c_void_p, c_size_t,
                         c_void_p]),
     'odk_voc_ap_workspace_bytes': (c_size_t, [c_int, c_int, c_int, c_int]),

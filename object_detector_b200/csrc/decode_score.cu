@@ -40,6 +40,7 @@ struct DecodeArgs {
   unsigned long long* cand_keys;  // [B, tiles_per_image * TILE]
   int* piece_count;               // [B, tiles_per_image]
   int tiles_per_image;
+  int stages;  // depth of the shared-memory ring
 };
 
 template <int TILE, bool DENSE>
@@ -48,20 +49,20 @@ struct StageLayout {
   static constexpr size_t kOffObj = 0, kOffAMask = (size_t)TILE * 4, kOffLoc = kOffAMask + (size_t)((TILE + 15) / 16 * 16),
                           kOffALoc = kOffLoc + (DENSE ? (size_t)TILE * 16 : 0), kOffAScale = kOffALoc + (DENSE ? (size_t)TILE * 16 : 0),
                           kTail = kOffAScale + (DENSE ? (size_t)TILE * 8 : 0);
-  static constexpr int kStages = 3;
+  static constexpr int kMaxStages = 8;
   static size_t stage_bytes(int c) { return (size_t)TILE * c * 4 + kTail; }
 };
 
 template <int TILE, bool DENSE>
 __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) {
   using L = StageLayout<TILE, DENSE>;
-  constexpr int kStages = L::kStages;
+  const int kStages = p.stages;
   constexpr int kWarps = TILE / 32;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int c = p.c;
   const size_t clf_bytes = (size_t)TILE * c * 4;
   const size_t stage_bytes = clf_bytes + L::kTail;
-  __shared__ uint64_t full_bar[kStages];
+  __shared__ uint64_t full_bar[L::kMaxStages];
   __shared__ int s_wcnt[2][kWarps];
 
   const long long total_tiles = (long long)p.batch * p.tiles_per_image;
@@ -243,7 +244,10 @@ int sm_count_cached() {
 template <int TILE, bool DENSE>
 int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   using L = StageLayout<TILE, DENSE>;
-  const size_t smem = L::stage_bytes(args.c) * L::kStages;
+  static const int env_stages = getenv("ODK_EMIT_STAGES") ? atoi(getenv("ODK_EMIT_STAGES")) : 0;
+  static const int env_per_sm = getenv("ODK_EMIT_PER_SM") ? atoi(getenv("ODK_EMIT_PER_SM")) : 0;
+  args.stages = (!DENSE && env_stages >= 2 && env_stages <= L::kMaxStages) ? env_stages : 3;
+  const size_t smem = L::stage_bytes(args.c) * args.stages;
   auto kern = decode_score_kernel<TILE, DENSE>;
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   args.tiles_per_image = (args.n + TILE - 1) / TILE;
@@ -252,6 +256,7 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / TILE ? 2048 / TILE : per_sm);
   // EMIT runs beside the train-side kernels of the same step (other graph branch): leave them shared memory
   if (!DENSE && per_sm > 2) per_sm = 2;
+  if (!DENSE && env_per_sm > 0) per_sm = env_per_sm;
   long long grid = (long long)sm_count_cached() * per_sm;
   if (grid > total) grid = total;
   if (grid < 1) grid = 1;
@@ -267,7 +272,11 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
 
 // Candidate piece (= tile) height used for `num_classes` channels: chosen so that the shared-memory ring
 // stays under ~100 KB (2+ CTAs per SM).  The NMS workspace layout depends on it.
-int odk_piece_size(int num_classes) { return num_classes <= 32 ? 256 : (num_classes <= 96 ? 64 : 32); }
+int odk_piece_size(int num_classes) {
+  static const int env_tile = getenv("ODK_EMIT_TILE") ? atoi(getenv("ODK_EMIT_TILE")) : 0;
+  if (num_classes <= 32 && env_tile == 128) return 128;
+  return num_classes <= 32 ? 256 : (num_classes <= 96 ? 64 : 32);
+}
 
 // Internal entry used by odk_decode_score (dense) and odk_decode_nms (emit).
 int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
@@ -284,6 +293,7 @@ int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, 
   ODK_REQUIRE(c <= 512, ODK_ERR_UNSUPPORTED, "num_classes=%d > 512 not supported by decode_score", c);
   switch (odk_piece_size(c)) {
     case 256: return dense ? launch_tile<256, true>(args, stream) : launch_tile<256, false>(args, stream);
+    case 128: return dense ? launch_tile<128, true>(args, stream) : launch_tile<128, false>(args, stream);
     case 64: return dense ? launch_tile<64, true>(args, stream) : launch_tile<64, false>(args, stream);
     default: return dense ? launch_tile<32, true>(args, stream) : launch_tile<32, false>(args, stream);
   }

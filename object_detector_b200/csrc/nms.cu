@@ -117,6 +117,12 @@ struct NmsArgs {
   int32_t* kept_index;    // [B, top_k] or null
   int32_t* out_index;     // standalone: [limit] kept input indices ...
   int32_t* out_count;     // ... and their number
+  // strict mode (layers.py:940,953-957): `limit` is the shared-memory capacity of the class-stage kept list
+  float iou_thr2;         // nms_all_threshold
+  FastThr ft2;
+  int class_cap;          // per-class limit of the class stage (2*top_k)
+  float4* spill_box;      // [B, n] class-stage kept entries beyond `limit` (L2-resident workspace)
+  int2* spill_meta;       // [B, n] {area bits, class}
 };
 
 __device__ __forceinline__ int block_exclusive_scan(int v, int* s_warp /*[kNmsWarps + 1]*/, int& total) {
@@ -174,7 +180,7 @@ __device__ __forceinline__ unsigned long long block_sort_desc_1(unsigned long lo
   return key;
 }
 
-template <bool GE>
+template <bool GE, bool STRICT>
 __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs p) {
   static_assert(kBand <= kNmsThreads && ODK_MAX_CLASSES / 32 <= kNmsThreads, "one band slot / class word per thread");
   extern __shared__ __align__(16) unsigned char nms_smem[];
@@ -202,6 +208,14 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
   float* karea = reinterpret_cast<float*>(dyn + (size_t)limit * 16);      // [limit]
   int* kcls = reinterpret_cast<int*>(dyn + (size_t)limit * 20);           // [limit]
   dyn += odk_align_up((size_t)(limit < 1 ? 1 : limit) * 24, 16);
+  // strict mode: the final (all-class stage) kept list
+  float4* k2box = reinterpret_cast<float4*>(dyn);                                              // [top_k]
+  float* k2area = reinterpret_cast<float*>(dyn + (size_t)(STRICT ? p.top_k : 0) * 16);         // [top_k]
+  if (STRICT) dyn += odk_align_up((size_t)(p.top_k < 1 ? 1 : p.top_k) * 20, 16);
+  float4* spill_box = STRICT ? p.spill_box + (size_t)blockIdx.x * p.n : nullptr;
+  int2* spill_meta = STRICT ? p.spill_meta + (size_t)blockIdx.x * p.n : nullptr;
+  const bool fast2 = GE && p.ft2.enabled;
+  int nkept2 = 0;
   int* s_pref = reinterpret_cast<int*>(dyn);                              // [n_pieces + 1]
   dyn += odk_align_up(sizeof(int) * ((size_t)p.n_pieces + 1), 16);
   unsigned short* s_member = reinterpret_cast<unsigned short*>(dyn);      // [kNmsWarps][kBand]
@@ -256,12 +270,13 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
   int nkept = 0, processed = 0;
   unsigned long long hi_key = ~0ull;  // keys of earlier bands are >= hi_key (every real key is < ~0)
 
-  while (processed < total && nkept < limit) {
+  while (processed < total && (STRICT ? nkept2 < p.top_k : nkept < limit)) {
     const int remaining = total - processed;
     // ---- a. threshold of the next band: MSB radix select starting at the first bit in which the
     //         remaining keys differ (fp32 scores share their leading exponent bits) -------------------------
     unsigned long long lo_key = 0ull;
-    const int want = min(kBand, (limit - nkept) + ((limit - nkept) >> 2) + 32);  // band size aimed at: 1.25x what is still needed
+    const int need = STRICT ? p.top_k - nkept2 : limit - nkept;
+    const int want = min(kBand, need + (need >> 2) + 32);  // band size aimed at: 1.25x what is still needed
     if (remaining > kBand) {
       unsigned long long kmin = ~0ull, kmax = 0ull;
       for (int i = tid; i < total; i += kNmsThreads) {
@@ -403,6 +418,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
       }
       __syncwarp();
       int seg_kept = 0;
+      int cls_before = 0;  // STRICT: boxes of this class kept by the class stage in earlier rounds
       for (int mb = 0; mb < nm; mb += 32) {
         const bool have = mb + lane < nm;
         const int i = have ? mem[mb + lane] : 0;
@@ -411,8 +427,23 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
         const float a_hi = area * p.ft.k_hi, a_lo = area * p.ft.k_lo;
         bool dead = false;
         // boxes of this class kept in earlier rounds (warp-uniform class test)
-        for (int k = 0; k < nkept; ++k)
-          if (kcls[k] == c) dead |= pair_hit<GE>(box, area, a_hi, a_lo, kbox[k], karea[k], p.iou_thr, p.ft, fast);
+        const int nk_s = STRICT ? min(nkept, limit) : nkept;
+        int cnt = 0;
+        for (int k = 0; k < nk_s; ++k)
+          if (kcls[k] == c) {
+            ++cnt;
+            dead |= pair_hit<GE>(box, area, a_hi, a_lo, kbox[k], karea[k], p.iou_thr, p.ft, fast);
+          }
+        if (STRICT) {
+          for (int k = limit; k < nkept; ++k) {  // spilled part of the class-stage list
+            const int2 m = spill_meta[k];
+            if (m.y == c) {
+              ++cnt;
+              dead |= pair_hit<GE>(box, area, a_hi, a_lo, spill_box[k], __int_as_float(m.x), p.iou_thr, p.ft, fast);
+            }
+          }
+          cls_before = cnt;
+        }
         // ... and in earlier chunks of this round
         if (seg_kept > 0) {
           for (int e = 0; e < mb; ++e) {
@@ -424,6 +455,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
         // intra-chunk greedy in score order: the first remaining lane is kept and knocks out what it suppresses
         unsigned keep = 0;
         for (unsigned rem = __ballot_sync(0xffffffffu, alive); rem;) {
+          if (STRICT && cls_before + seg_kept + __popc(keep) >= p.class_cap) break;  // layers.py:940-941 (warp-uniform)
           const int l = __ffs(rem) - 1;
           keep |= 1u << l;
           rem &= rem - 1;
@@ -443,7 +475,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     }
     __syncthreads();
     // ---- f. survivors are already in global order: compact, cut at the limit, emit ------------------------------
-    {
+    if (!STRICT) {
       const bool kept = tid < nb && s_keep[tid];
       int nk;
       const int pos = block_exclusive_scan(kept ? 1 : 0, s_scan, nk);
@@ -466,9 +498,92 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
         if (p.out_index != nullptr) p.out_index[r] = a;
       }
       nkept += take;
+    } else {
+      // ---- f'. strict mode.  The class-stage survivors (global order) all join the class-stage kept list;
+      //      then the all-class greedy pass (layers.py:953-957) visits them in the same order against the
+      //      final kept list at nms_all_threshold, stopping at top_k. ---------------------------------------
+      const bool kept1 = tid < nb && s_keep[tid];
+      int nk1;
+      const int pos = block_exclusive_scan(kept1 ? 1 : 0, s_scan, nk1);
+      bool dead2 = false;
+      if (kept1) {
+        const float4 bx = s_box[tid];
+        const float ar = s_area[tid];
+        const int r1 = nkept + pos;
+        if (r1 < limit) {
+          kbox[r1] = bx;
+          karea[r1] = ar;
+          kcls[r1] = (int)s_cls[tid];
+        } else {
+          spill_box[r1] = bx;
+          spill_meta[r1] = make_int2(__float_as_int(ar), (int)s_cls[tid]);
+        }
+        s_clslist[pos] = (unsigned short)tid;  // survivors in global order (the class list is no longer needed)
+        const float a_hi = ar * p.ft2.k_hi, a_lo = ar * p.ft2.k_lo;
+        for (int k = 0; k < nkept2; ++k) dead2 |= pair_hit<GE>(bx, ar, a_hi, a_lo, k2box[k], k2area[k], p.iou_thr2, p.ft2, fast2);
+        s_alive[tid] = dead2 ? 0 : 1;
+      }
+      __syncthreads();
+      if (warp == 0) {
+        unsigned short* mem = s_member;  // this round's final keeps (band slots, global order)
+        int rk = 0;
+        const int room = p.top_k - nkept2;
+        for (int mb = 0; mb < nk1 && rk < room; mb += 32) {
+          const bool have = mb + lane < nk1;
+          const int i = have ? s_clslist[mb + lane] : 0;
+          const float4 box = have ? s_box[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+          const float area = have ? s_area[i] : 0.f;
+          const float a_hi = area * p.ft2.k_hi, a_lo = area * p.ft2.k_lo;
+          bool dead = false;
+          for (int e = 0; e < rk; ++e) {
+            const int ie = mem[e];
+            dead |= pair_hit<GE>(box, area, a_hi, a_lo, s_box[ie], s_area[ie], p.iou_thr2, p.ft2, fast2);
+          }
+          const bool alive = have && s_alive[i] && !dead;
+          unsigned keep = 0;
+          for (unsigned rem = __ballot_sync(0xffffffffu, alive); rem;) {
+            if (rk + __popc(keep) >= room) break;
+            const int l = __ffs(rem) - 1;
+            keep |= 1u << l;
+            rem &= rem - 1;
+            float4 bl;
+            bl.x = __shfl_sync(0xffffffffu, box.x, l);
+            bl.y = __shfl_sync(0xffffffffu, box.y, l);
+            bl.z = __shfl_sync(0xffffffffu, box.z, l);
+            bl.w = __shfl_sync(0xffffffffu, box.w, l);
+            const float al = __shfl_sync(0xffffffffu, area, l);
+            const bool hit = ((rem >> lane) & 1u) && pair_hit<GE>(box, area, a_hi, a_lo, bl, al, p.iou_thr2, p.ft2, fast2);
+            rem &= ~__ballot_sync(0xffffffffu, hit);
+          }
+          if ((keep >> lane) & 1u) mem[rk + __popc(keep & ((1u << lane) - 1u))] = (unsigned short)i;
+          rk += __popc(keep);
+          __syncwarp();
+        }
+        if (lane == 0) s_nb = rk;
+      }
+      __syncthreads();
+      const int rk = s_nb;
+      if (tid < rk) {
+        const int i = s_member[tid];
+        const unsigned long long key = s_band[i];
+        const float4 bx = s_box[i];
+        const int r = nkept2 + tid;
+        k2box[r] = bx;
+        k2area[r] = s_area[i];
+        if (p.out != nullptr) {
+          float* o = p.out + ((size_t)b * p.top_k + r) * 6;
+          o[0] = (float)odk_key2_class(key);
+          o[1] = odk_key2_score(key);
+          o[2] = bx.x; o[3] = bx.y; o[4] = bx.z; o[5] = bx.w;
+          p.kept_index[(size_t)b * p.top_k + r] = (int)(key & ODK_IDX_MASK);
+        }
+      }
+      nkept += nk1;
+      nkept2 += rk;
     }
     __syncthreads();
   }
+  if (STRICT) nkept = nkept2;  // rows written
   // ---- zero padding (layers.py:969) / count ---------------------------------------------------------------------
   if (p.out != nullptr) {
     for (int r = nkept + tid; r < p.top_k; r += kNmsThreads) {
@@ -486,29 +601,35 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
 struct NmsWorkspace {
   int* piece_count;               // [B, ceil(N/32)]   (only n_pieces per image are used)
   unsigned long long* cand_keys;  // [B, round_up(N, 256)]
+  float4* spill_box;              // strict only: [B, N]
+  int2* spill_meta;               // strict only: [B, N]
   size_t bytes;
 };
 
-static NmsWorkspace nms_layout(void* base, int batch, int n) {
+static NmsWorkspace nms_layout(void* base, int batch, int n, bool strict = false) {
   NmsWorkspace w;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = odk_align_up(off + bytes, 256); return o; };
   const size_t o_cnt = take(sizeof(int) * (size_t)batch * ((n + 31) / 32));
   const size_t o_ck = take(8 * (size_t)batch * odk_align_up((size_t)n, 256));
+  const size_t o_sb = strict ? take(16 * (size_t)batch * n) : 0;
+  const size_t o_sm = strict ? take(8 * (size_t)batch * n) : 0;
   char* p = static_cast<char*>(base);
   w.piece_count = reinterpret_cast<int*>(p + o_cnt);
   w.cand_keys = reinterpret_cast<unsigned long long*>(p + o_ck);
+  w.spill_box = strict ? reinterpret_cast<float4*>(p + o_sb) : nullptr;
+  w.spill_meta = strict ? reinterpret_cast<int2*>(p + o_sm) : nullptr;
   w.bytes = off;
   return w;
 }
 
-static int nms_check(int batch, int n, int num_classes, int top_k, const void* ws, size_t ws_bytes) {
+static int nms_check(int batch, int n, int num_classes, int top_k, const void* ws, size_t ws_bytes, bool strict = false) {
   ODK_REQUIRE(batch >= 1 && n >= 1 && num_classes >= 1 && top_k >= 0, ODK_ERR_INVALID_ARGUMENT,
               "nms: bad sizes batch=%d n=%d classes=%d top_k=%d", batch, n, num_classes, top_k);
   ODK_REQUIRE(n < (int)ODK_IDX_MASK, ODK_ERR_UNSUPPORTED, "nms: n=%d exceeds the 20-bit anchor field", n);
   ODK_REQUIRE(num_classes <= ODK_MAX_CLASSES, ODK_ERR_UNSUPPORTED, "nms: num_classes=%d > %d", num_classes, ODK_MAX_CLASSES);
   ODK_REQUIRE(top_k <= 4096, ODK_ERR_UNSUPPORTED, "nms: top_k=%d > 4096 (kept list lives in shared memory)", top_k);
-  const size_t need = nms_layout(nullptr, batch, n).bytes;
+  const size_t need = nms_layout(nullptr, batch, n, strict).bytes;
   ODK_REQUIRE(ws != nullptr && ws_bytes >= need, ODK_ERR_WORKSPACE, "nms: workspace of %zu bytes is smaller than the required %zu", ws_bytes,
               need);
   ODK_REQUIRE(((uintptr_t)ws & 255) == 0, ODK_ERR_INVALID_ARGUMENT, "nms: workspace must be 256-byte aligned");
@@ -518,7 +639,7 @@ static int nms_check(int batch, int n, int num_classes, int top_k, const void* w
 // select + sort + sweep + output on already emitted candidate pieces
 static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch, int n, int piece, const float4* boxes, const float4* locs,
                    float iou_thr, int top_k, int limit, int iou_ge, float* out, int32_t* kept_index, int32_t* out_index, int32_t* out_count,
-                   cudaStream_t stream) {
+                   cudaStream_t stream, bool strict = false, float iou_thr2 = 0.f) {
   NmsArgs a;
   if (anchors != nullptr) a.av = odk_view(anchors);
   else memset(&a.av, 0, sizeof(a.av));
@@ -531,18 +652,27 @@ static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch,
   const double kk = a.ft.enabled ? (double)iou_thr / (1.0 + (double)iou_thr) : 0.0;
   a.ft.k_hi = (float)(kk * (1.0 + 3e-5));
   a.ft.k_lo = (float)(kk * (1.0 - 3e-5));
+  a.iou_thr2 = iou_thr2;
+  a.ft2.enabled = (strict && iou_thr2 > 1e-3f && iou_thr2 < 0.999f) ? 1 : 0;
+  const double kk2 = a.ft2.enabled ? (double)iou_thr2 / (1.0 + (double)iou_thr2) : 0.0;
+  a.ft2.k_hi = (float)(kk2 * (1.0 + 3e-5));
+  a.ft2.k_lo = (float)(kk2 * (1.0 - 3e-5));
+  a.class_cap = 2 * top_k;  // layers.py:940
+  a.spill_box = w.spill_box; a.spill_meta = w.spill_meta;
+  if (strict) limit = 1024;  // shared-memory part of the class-stage kept list; the rest spills to the workspace
   a.limit = limit; a.top_k = top_k; a.skip_empty = iou_ge ? 1 : 0;
   a.out = out; a.kept_index = kept_index; a.out_index = out_index; a.out_count = out_count;
   const size_t fixed = odk_align_up((size_t)(limit < 1 ? 1 : limit) * 24, 16) + odk_align_up(sizeof(int) * ((size_t)a.n_pieces + 1), 16) +
-                       (size_t)kNmsWarps * kBand * 2;
+                       (size_t)kNmsWarps * kBand * 2 + (strict ? odk_align_up((size_t)(top_k < 1 ? 1 : top_k) * 20, 16) : 0);
   a.cache_cap = n < 8192 ? n : 8192;
   if (fixed + (size_t)a.cache_cap * 8 > 180 * 1024) a.cache_cap = 0;
   const size_t smem = fixed + (size_t)a.cache_cap * 8;
   ODK_REQUIRE(smem <= 180 * 1024, ODK_ERR_UNSUPPORTED, "nms: top_k=%d / %d pieces need %zu bytes of shared memory", top_k, a.n_pieces, smem);
-  auto kern = iou_ge ? nms_image_kernel<true> : nms_image_kernel<false>;
+  auto kern = strict ? (iou_ge ? nms_image_kernel<true, true> : nms_image_kernel<false, true>)
+                     : (iou_ge ? nms_image_kernel<true, false> : nms_image_kernel<false, false>);
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 180 * 1024));
   {
-    OdkProfileScope prof_("nms_image_kernel", stream);
+    OdkProfileScope prof_(strict ? "nms_image_kernel_strict" : "nms_image_kernel", stream);
     kern<<<batch, kNmsThreads, smem, stream>>>(a);
   }
   ODK_LAUNCH_CHECK("nms_image_kernel");
@@ -571,34 +701,70 @@ static int collect(const NmsWorkspace& w, int batch, int n, int num_classes, con
   return ODK_OK;
 }
 
-extern "C" int odk_nms_layer(int batch, int n, int num_classes, const int32_t* classes, const float* confs, const float* boxes,
-                             float conf_thr, float iou_thr, int top_k, int iou_ge, float* out, int32_t* kept_index, void* workspace,
-                             size_t workspace_bytes, void* stream_) {
+static int nms_layer_impl(int batch, int n, int num_classes, const int32_t* classes, const float* confs, const float* boxes, float conf_thr,
+                          float iou_thr, bool strict, float nms_all_thr, int top_k, int iou_ge, float* out, int32_t* kept_index,
+                          void* workspace, size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (int rc = nms_check(batch, n, num_classes, top_k, workspace, workspace_bytes)) return rc;
+  if (int rc = nms_check(batch, n, num_classes, top_k, workspace, workspace_bytes, strict)) return rc;
   ODK_REQUIRE(classes && confs && boxes && out && kept_index, ODK_ERR_INVALID_ARGUMENT, "nms_layer: null pointer");
   ODK_REQUIRE(((uintptr_t)boxes & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "nms_layer: boxes must be 16-byte aligned");
-  NmsWorkspace w = nms_layout(workspace, batch, n);
+  NmsWorkspace w = nms_layout(workspace, batch, n, strict);
   if (int rc = collect(w, batch, n, num_classes, classes, confs, conf_thr, 0, stream)) return rc;
   return nms_run(w, nullptr, batch, n, kCollectPiece, reinterpret_cast<const float4*>(boxes), nullptr, iou_thr, top_k, top_k, iou_ge, out,
-                 kept_index, nullptr, nullptr, stream);
+                 kept_index, nullptr, nullptr, stream, strict, nms_all_thr);
 }
 
-extern "C" int odk_decode_nms(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs, float conf_thr,
-                              float iou_thr, int top_k, int iou_ge, float* out, int32_t* kept_index, void* workspace,
-                              size_t workspace_bytes, void* stream_) {
+static int decode_nms_impl(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs, float conf_thr,
+                           float iou_thr, bool strict, float nms_all_thr, int top_k, int iou_ge, float* out, int32_t* kept_index,
+                           void* workspace, size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   ODK_REQUIRE(a != nullptr, ODK_ERR_INVALID_ARGUMENT, "decode_nms: null anchors handle");
-  if (int rc = nms_check(batch, a->n, a->num_classes, top_k, workspace, workspace_bytes)) return rc;
+  if (int rc = nms_check(batch, a->n, a->num_classes, top_k, workspace, workspace_bytes, strict)) return rc;
   ODK_REQUIRE(objs && clfs && locs && out && kept_index, ODK_ERR_INVALID_ARGUMENT, "decode_nms: null pointer");
   ODK_REQUIRE((((uintptr_t)objs | (uintptr_t)clfs) & 3) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_nms: inputs must be 4-byte aligned");
   ODK_REQUIRE(((uintptr_t)locs & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_nms: locs must be 16-byte aligned");
-  NmsWorkspace w = nms_layout(workspace, batch, a->n);
+  NmsWorkspace w = nms_layout(workspace, batch, a->n, strict);
   if (int rc = odk_launch_decode_score(a, batch, objs, clfs, locs, nullptr, nullptr, nullptr, false, conf_thr, w.cand_keys, w.piece_count,
                                        stream))
     return rc;
   return nms_run(w, a, batch, a->n, odk_piece_size(a->num_classes), nullptr, reinterpret_cast<const float4*>(locs), iou_thr, top_k, top_k,
-                 iou_ge, out, kept_index, nullptr, nullptr, stream);
+                 iou_ge, out, kept_index, nullptr, nullptr, stream, strict, nms_all_thr);
+}
+
+extern "C" int odk_nms_layer(int batch, int n, int num_classes, const int32_t* classes, const float* confs, const float* boxes,
+                             float conf_thr, float iou_thr, int top_k, int iou_ge, float* out, int32_t* kept_index, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+  return nms_layer_impl(batch, n, num_classes, classes, confs, boxes, conf_thr, iou_thr, false, 0.f, top_k, iou_ge, out, kept_index, workspace,
+                        workspace_bytes, stream);
+}
+
+extern "C" int odk_decode_nms(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs, float conf_thr,
+                              float iou_thr, int top_k, int iou_ge, float* out, int32_t* kept_index, void* workspace,
+                              size_t workspace_bytes, void* stream) {
+  return decode_nms_impl(a, batch, objs, clfs, locs, conf_thr, iou_thr, false, 0.f, top_k, iou_ge, out, kept_index, workspace, workspace_bytes,
+                         stream);
+}
+
+// strict_nms (od_net.py:175, layers.py:940,953-957): nms_all_threshold given
+extern "C" size_t odk_nms_strict_workspace_bytes(int batch, int n, int num_classes, int top_k) {
+  if (batch < 1 || n < 1 || num_classes < 1 || top_k < 0) return 0;
+  return nms_layout(nullptr, batch, n, true).bytes;
+}
+
+extern "C" int odk_nms_layer_strict(int batch, int n, int num_classes, const int32_t* classes, const float* confs, const float* boxes,
+                                    float conf_thr, float iou_thr, float nms_all_thr, int top_k, int iou_ge, float* out,
+                                    int32_t* kept_index, void* workspace, size_t workspace_bytes, void* stream) {
+  ODK_REQUIRE(nms_all_thr > 0.f, ODK_ERR_INVALID_ARGUMENT, "nms_layer_strict: nms_all_threshold must be > 0 (falsy means non-strict)");
+  return nms_layer_impl(batch, n, num_classes, classes, confs, boxes, conf_thr, iou_thr, true, nms_all_thr, top_k, iou_ge, out, kept_index,
+                        workspace, workspace_bytes, stream);
+}
+
+extern "C" int odk_decode_nms_strict(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
+                                     float conf_thr, float iou_thr, float nms_all_thr, int top_k, int iou_ge, float* out,
+                                     int32_t* kept_index, void* workspace, size_t workspace_bytes, void* stream) {
+  ODK_REQUIRE(nms_all_thr > 0.f, ODK_ERR_INVALID_ARGUMENT, "decode_nms_strict: nms_all_threshold must be > 0 (falsy means non-strict)");
+  return decode_nms_impl(a, batch, objs, clfs, locs, conf_thr, iou_thr, true, nms_all_thr, top_k, iou_ge, out, kept_index, workspace,
+                         workspace_bytes, stream);
 }
 
 extern "C" int odk_nms(const float* boxes, const float* scores, int n, int top_k, float iou_thr, int iou_ge, int32_t* out_index,

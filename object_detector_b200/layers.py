@@ -12,7 +12,8 @@ def nms():
     class NMS:
         """layers.py:890-970.  ``NMS(num_classes, prior_boxes, ...)([classes, confs, locs]) -> (B, top_k, 6)``
         rows [class, conf, x1, y1, x2, y2], zero padded.  ``nms_all_threshold`` (strict all-class NMS,
-        od_net.py:175) is SURVEY §8 row f4 and not built yet."""
+        od_net.py:175, layers.py:940,953-957) runs both stages in the same per-image sweep
+        (``odk_nms_layer_strict``)."""
 
         def __init__(self, num_classes, prior_boxes, top_k=200, conf_threshold=0.01, nms_threshold=0.45,
                      nms_all_threshold=None, iou_ge=True, **kwargs):
@@ -24,8 +25,6 @@ def nms():
             self.nms_threshold = nms_threshold
             self.nms_all_threshold = nms_all_threshold
             self.iou_ge = iou_ge  # True: reference NumPy-NMS semantics (pinned); False: TF-1.10 style (unpinned)
-            if nms_all_threshold:
-                raise NotImplementedError('nms_all_threshold (strict_nms) is not built yet (SURVEY §8 f4)')
 
         def compute_output_shape(self, input_shape):
             assert input_shape and len(input_shape) >= 2
@@ -50,12 +49,15 @@ def nms():
             b = confs.shape[0]
             out = torch.empty((b, self.top_k, 6), dtype=torch.float32, device=dev)
             kept = torch.empty((b, self.top_k), dtype=torch.int32, device=dev)
-            ws_bytes = _lib.load().odk_nms_workspace_bytes(b, n, self.num_classes, self.top_k)
+            strict = bool(self.nms_all_threshold)  # layers.py:940,953: truthiness decides
+            ws_fn = 'odk_nms_strict_workspace_bytes' if strict else 'odk_nms_workspace_bytes'
+            ws_bytes = getattr(_lib.load(), ws_fn)(b, n, self.num_classes, self.top_k)
             ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+            thr = (float(self.nms_threshold), float(self.nms_all_threshold)) if strict else (float(self.nms_threshold),)
             with torch.cuda.device(dev):
-                _lib.call('odk_nms_layer', b, n, self.num_classes, classes.data_ptr(), confs.data_ptr(), locs.data_ptr(),
-                          float(self.conf_threshold), float(self.nms_threshold), int(self.top_k), 1 if self.iou_ge else 0,
-                          out.data_ptr(), kept.data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
+                _lib.call('odk_nms_layer_strict' if strict else 'odk_nms_layer', b, n, self.num_classes, classes.data_ptr(),
+                          confs.data_ptr(), locs.data_ptr(), float(self.conf_threshold), *thr, int(self.top_k),
+                          1 if self.iou_ge else 0, out.data_ptr(), kept.data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
             if is_np:
                 out, kept = out.cpu().numpy(), kept.cpu().numpy()
             return (out, kept) if return_index else out

@@ -49,22 +49,30 @@ class ObjectDetector:
         return od
 
     @staticmethod
-    def load_voc(input_size=(320, 320)):
-        """Anchor set of the published VOC models (od.py:80-97); weights are not loaded."""
+    def load_voc(input_size=(320, 320), strict_nms=True):
+        """Anchor set of the published VOC models (od.py:80-97); weights are not loaded.  ``strict_nms``
+        as in the reference signature (od.py:81): it selects nms_all_threshold=0.5 in the prediction tail
+        (od_net.py:175) when ``predict_from_head`` is called without an explicit value."""
         input_size = tuple(input_size)
         assert input_size in ((320, 320), (640, 640))
         data = _VOC_JSON_DATA.copy()
         data['input_size'] = input_size
-        return ObjectDetector.load_from_dict(data)
+        od = ObjectDetector.load_from_dict(data)
+        od.strict_nms = bool(strict_nms)
+        return od
 
     def encode_truth(self, y):
         """The ProcessOutput hook of the training pipeline (od.py:169): one annotation -> (N, 3+C+4)."""
         return self.pb.encode_truth([y])[0]
 
-    def predict_from_head(self, objs, clfs, locs, conf_threshold=0.01, top_k=200, nms_threshold=0.45):
+    def predict_from_head(self, objs, clfs, locs, conf_threshold=0.01, top_k=200, nms_threshold=0.45, strict_nms=False):
         """What ``predict`` does after the CNN (od_net.py:186-190 + od.py:258-266, keep_aspect=False):
-        head outputs -> list of ObjectsPrediction with confs >= conf_threshold."""
-        out = self.pb.decode_nms(objs, clfs, locs, top_k=top_k, nms_threshold=nms_threshold)
+        head outputs -> list of ObjectsPrediction with confs >= conf_threshold.  ``strict_nms=True`` adds the
+        all-class pass at 0.5 (od_net.py:175); ``None`` uses what ``load_voc`` was given."""
+        if strict_nms is None:
+            strict_nms = getattr(self, 'strict_nms', False)
+        out = self.pb.decode_nms(objs, clfs, locs, top_k=top_k, nms_threshold=nms_threshold,
+                                 nms_all_threshold=0.5 if strict_nms else None)
         return unpack_predictions(out, conf_threshold)
 
 

@@ -289,22 +289,25 @@ class PriorBoxes:
         return classes, confs, boxes
 
     def decode_nms(self, objs, clfs, locs, top_k=200, conf_threshold=0.01, nms_threshold=0.45, iou_ge=True,
-                   out=None, return_index=False):
+                   out=None, return_index=False, nms_all_threshold=None):
         """The whole prediction tail (od_net.py:186-190) fused: head outputs -> (B, top_k, 6)
         [class, conf, x1, y1, x2, y2], zero padded (layers.py:963-970).  ``out`` may be a slice of a
-        larger (e.g. all-gather) buffer."""
+        larger (e.g. all-gather) buffer.  ``nms_all_threshold`` = the strict_nms second pass
+        (od_net.py:175: 0.5 when ``strict_nms``)."""
         dev, b, objs, clfs, locs = self._head_inputs(objs, clfs, locs)
         n, c = len(self.pb_locs), self.num_classes
         if out is None:
             out = torch.empty((b, top_k, 6), dtype=torch.float32, device=dev)
         assert out.shape == (b, top_k, 6) and out.dtype == torch.float32 and out.is_contiguous()
         kept = torch.empty((b, top_k), dtype=torch.int32, device=dev)
-        ws_bytes = _lib.load().odk_nms_workspace_bytes(b, n, c, top_k)
+        strict = bool(nms_all_threshold)
+        ws_bytes = getattr(_lib.load(), 'odk_nms_strict_workspace_bytes' if strict else 'odk_nms_workspace_bytes')(b, n, c, top_k)
         ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        thr = (float(nms_threshold), float(nms_all_threshold)) if strict else (float(nms_threshold),)
         with torch.cuda.device(dev):
-            _lib.call('odk_decode_nms', self._handle(dev), b, objs.data_ptr(), clfs.data_ptr(), locs.data_ptr(),
-                      float(conf_threshold), float(nms_threshold), int(top_k), 1 if iou_ge else 0, out.data_ptr(),
-                      kept.data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
+            _lib.call('odk_decode_nms_strict' if strict else 'odk_decode_nms', self._handle(dev), b, objs.data_ptr(),
+                      clfs.data_ptr(), locs.data_ptr(), float(conf_threshold), *thr, int(top_k), 1 if iou_ge else 0,
+                      out.data_ptr(), kept.data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
         return (out, kept) if return_index else out
 
 

@@ -252,16 +252,44 @@ def score_anchors(t: AnchorTables, objs, clfs):
     return classes, conf * t.pb_mask[None, :].astype(np.float32)
 
 
+def greedy_nms_in_order(boxes, iou_threshold, top_k):
+    """Body of ml.non_maximum_suppression (ml.py:605-624) over boxes ALREADY in visiting order:
+    returns the kept positions.  Same zero-area skip, ``>=`` test and length-check placement."""
+    area = np.prod(boxes[:, 2:] - boxes[:, :2], axis=1)
+    thr = boxes.dtype.type(iou_threshold) if boxes.dtype.kind == 'f' else iou_threshold
+    keep = []
+    for i in range(len(boxes)):
+        if (boxes[i, 2:] - boxes[i, :2] <= 0).any():
+            continue
+        if keep:
+            lo = np.maximum(boxes[i, :2], boxes[keep, :2])
+            hi = np.minimum(boxes[i, 2:], boxes[keep, 2:])
+            inter = np.prod(hi - lo, axis=1) * (lo < hi).all(axis=1)
+            if (inter / (area[i] + area[keep] - inter) >= thr).any():
+                continue
+            keep.append(i)
+            if len(keep) >= top_k:
+                break
+        else:
+            keep.append(i)
+    return np.asarray(keep, dtype=np.int64)
+
+
 def nms_layer_image(classes, confs, locs, num_classes, top_k=200, conf_threshold=0.01,
-                    nms_threshold=0.45, inner=numpy_nms_policy):
-    """layers.py:925-970 for one image, nms_all_threshold=None branch.
+                    nms_threshold=0.45, inner=numpy_nms_policy, nms_all_threshold=None):
+    """layers.py:925-970 for one image.  ``nms_all_threshold=None``: per-class NMS then global
+    top_k (:958-961).  With a threshold (strict_nms, od_net.py:175): the per-class limit doubles
+    (:940) and a second, class-agnostic greedy NMS runs over the class-concatenated survivors
+    (:953-957).  Tie policy of this build for that second pass: equal scores are visited in
+    concatenation order (lower class first) — identical to the reference when scores are distinct.
     Returns (out (top_k,6) f32, kept anchor index (top_k,) i64 with -1 padding)."""
     cat_cls, cat_conf, cat_loc, cat_idx = [], [], [], []
+    class_limit = top_k * 2 if nms_all_threshold else top_k  # :940
     for c in range(num_classes):
         sel = np.flatnonzero((classes == c) & (confs > np.float32(conf_threshold)))  # :935 strict
         if len(sel) == 0:
             continue
-        k = min(top_k, len(sel))  # :940-941
+        k = min(class_limit, len(sel))  # :941
         kept = inner(locs[sel], confs[sel], k, nms_threshold)  # :942
         cat_cls.append(np.full(len(kept), c, dtype=np.int64))
         cat_conf.append(confs[sel][kept])
@@ -275,7 +303,12 @@ def nms_layer_image(classes, confs, locs, num_classes, top_k=200, conf_threshold
         loc = np.concatenate(cat_loc)
         idx = np.concatenate(cat_idx)
         k = min(top_k, len(conf))  # :952
-        top = np.argsort(-conf, kind='stable')[:k]  # tf.nn.top_k(sorted=True): lower position first on ties
+        order = np.argsort(-conf, kind='stable')  # lower position first on ties
+        if nms_all_threshold:
+            top = order[greedy_nms_in_order(loc[order], nms_all_threshold, k)]  # :954
+            k = len(top)
+        else:
+            top = order[:k]  # tf.nn.top_k(sorted=True)
         out[:k, 0] = cls[top]
         out[:k, 1] = conf[top]
         out[:k, 2:] = loc[top]
@@ -284,7 +317,7 @@ def nms_layer_image(classes, confs, locs, num_classes, top_k=200, conf_threshold
 
 
 def predict_tail(t: AnchorTables, objs, clfs, locs, top_k=200, conf_threshold=0.01,
-                 nms_threshold=0.45, inner=numpy_nms_policy):
+                 nms_threshold=0.45, inner=numpy_nms_policy, nms_all_threshold=None):
     """od_net.py:172-192: score -> decode (f32) -> NMS layer, whole batch.
     Returns (B,top_k,6) f32 and (B,top_k) i64 kept anchor ids."""
     classes, confs = score_anchors(t, objs, clfs)
@@ -292,7 +325,7 @@ def predict_tail(t: AnchorTables, objs, clfs, locs, top_k=200, conf_threshold=0.
     outs, idxs = [], []
     for b in range(len(objs)):
         o, k = nms_layer_image(classes[b], confs[b], boxes[b], t.num_classes, top_k,
-                               conf_threshold, nms_threshold, inner)
+                               conf_threshold, nms_threshold, inner, nms_all_threshold)
         outs.append(o)
         idxs.append(k)
     return np.stack(outs), np.stack(idxs)
@@ -463,3 +496,55 @@ def search_conf_threshold(gt_list, pred_list, num_classes, iou_threshold=0.5):
     if full.any():
         return np.mean(grid[full])
     return grid[scores.argmax()]
+
+
+# --------------------------------------------------------------------------------------
+# SURVEY §8 f3 — loss-side consumption of y_true (od_pb.py:365-431, losses.py:22-30).  The reference builds these
+# as TensorFlow-1.10 graph ops (tf.keras.losses.*, tf.keras.backend.*; tensorflow is absent here) -> PARITY
+# UNPINNED; the Keras formulas restated below are the published ones (epsilon 1e-7; categorical_crossentropy
+# renormalises the prediction, clips to [eps, 1-eps]; mean_squared_error averages the last axis).  Elementwise
+# arithmetic in float32 like the graph, sums in float64 (the graph's float32 reduction order is unspecified;
+# tolerance 1e-5 relative, BASELINE north_star).
+_K_EPS = np.float32(1e-7)
+
+
+def binary_focal_loss(y_true, y_pred, alpha=0.25, gamma=2.0):
+    """losses.py:22-30 (gamma=2 -> a square)."""
+    one = np.float32(1)
+    a_t = y_true * np.float32(alpha) + (one - y_true) * np.float32(1 - alpha)
+    p_t = y_true * y_pred + (one - y_true) * (one - y_pred)
+    p_t = np.clip(p_t, _K_EPS, one - _K_EPS)
+    assert gamma == 2.0
+    return -a_t * ((one - p_t) * (one - p_t)) * np.log(p_t)
+
+
+def od_losses(t: AnchorTables, y_true, y_pred):
+    """od_pb.py:365-431: the three loss terms and the three metrics, each (B,) float64.
+    y_true / y_pred: (B, N, 3+C+4) float32 in the layout of encode_truth (od_pb.py:301-311)."""
+    y_true = np.asarray(y_true, np.float32)
+    y_pred = np.asarray(y_pred, np.float32)
+    gt_mask, gt_w, gt_obj = y_true[:, :, 0], y_true[:, :, 1], y_true[:, :, 2]
+    pred_obj = y_pred[:, :, 2]
+    f64 = np.float64
+    # loss_obj :403-411
+    mask = t.pb_mask[None].astype(np.float32) * gt_mask
+    loss_obj = (binary_focal_loss(gt_obj, pred_obj) * mask).astype(np.float32).sum(axis=-1, dtype=f64) * 3
+    # loss_clf :413-421
+    gt_cls, pred_cls = y_true[:, :, 3:-4], y_pred[:, :, 3:-4]
+    norm = pred_cls / pred_cls.sum(axis=-1, keepdims=True, dtype=np.float32)
+    norm = np.clip(norm, _K_EPS, np.float32(1) - _K_EPS)
+    cce = -(gt_cls * np.log(norm)).sum(axis=-1, dtype=np.float32)
+    loss_clf = (cce * gt_w).sum(axis=-1, dtype=f64)
+    # loss_loc :423-431
+    diff = y_pred[:, :, -4:] - y_true[:, :, -4:]
+    mse = (diff * diff).mean(axis=-1, dtype=np.float32)
+    loss_loc = (mse * gt_w).sum(axis=-1, dtype=f64) * 2
+    # metrics :380-401 (tf round = half to even = np.round)
+    acc = (np.round(gt_obj) == np.round(pred_obj)).astype(np.float32)
+    gt_bg = (np.float32(1) - gt_obj) * gt_mask
+    rec_bg = (acc * gt_bg).sum(axis=-1, dtype=f64) / np.maximum(gt_bg.sum(axis=-1, dtype=f64), 1)
+    rec_obj = (acc * gt_obj).sum(axis=-1, dtype=f64) / np.maximum(gt_obj.sum(axis=-1, dtype=f64), 1)
+    acc_c = (np.argmax(gt_cls, axis=-1) == np.argmax(pred_cls, axis=-1)).astype(np.float32)
+    acc_clf = (acc_c * gt_obj).sum(axis=-1, dtype=f64) / np.maximum(gt_obj.sum(axis=-1, dtype=f64), 1)
+    return {'loss_obj': loss_obj, 'loss_clf': loss_clf, 'loss_loc': loss_loc, 'loss': loss_obj + loss_clf + loss_loc,
+            'rec_bg': rec_bg, 'rec_obj': rec_obj, 'acc_clf': acc_clf}

@@ -58,3 +58,16 @@ def prior_boxes():
             cache[name] = pb
         return cache[name]
     return get
+
+
+@pytest.fixture
+def strict_cap_case():
+    """top_k=2 case for layers.py:940: (boxes, classes, confs) — a class-1 box with four class-0 boxes shifted
+    by 0.3 of its width around it (IoU 0.538 with it, < 0.45 among themselves) and a far, weak class-0 box."""
+    b = np.array([0.3, 0.3, 0.6, 0.6], np.float32)
+    d = np.float32(0.09)
+    boxes = np.stack([b, b + [d, 0, d, 0], b - [d, 0, d, 0], b + [0, d, 0, d], b - [0, d, 0, d],
+                      np.array([0.8, 0.8, 0.95, 0.95], np.float32)]).astype(np.float32)
+    classes = np.array([1, 0, 0, 0, 0, 0])
+    confs = np.array([0.9, 0.8, 0.7, 0.6, 0.5, 0.4], np.float32)
+    return boxes, classes, confs

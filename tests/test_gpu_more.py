@@ -226,3 +226,55 @@ def test_encode_truth_hook_coalesces_threads(prior_boxes):
     assert hook.coalescer.batches < 24 and hook.coalescer.items == 24
     assert np.array_equal(generator.collate_truth(od.pb, anns), ref)
     hook.coalescer.close()
+
+
+# ----------------------------------------------------------------------------------------- strict_nms
+@pytest.mark.parametrize('name,batch,top_k,clustered', [('voc640', 3, 200, False), ('voc640', 2, 200, True),
+                                                        ('voc320', 2, 20, True), ('tiny128', 4, 5, False),
+                                                        ('mid80', 2, 200, False)])
+def test_strict_nms_fused_vs_oracle(prior_boxes, oracle_tables, name, batch, top_k, clustered):
+    """layers.py:940,953-957 (nms_all_threshold=0.5 as od_net.py:175 sets it): kept anchors and rows bit-exact."""
+    pb, t = prior_boxes(name), oracle_tables(name)
+    objs, clfs, locs = synth.predictions(99, batch, len(pb), pb.num_classes, clustered=clustered)
+    out, kept = pb.decode_nms(objs, clfs, locs, top_k=top_k, nms_all_threshold=0.5, return_index=True)
+    ro, rk = R.predict_tail(t, objs, clfs, locs, top_k=top_k, nms_all_threshold=0.5)
+    assert np.array_equal(kept.cpu().numpy(), rk)
+    assert np.array_equal(out.cpu().numpy(), ro)
+    # and it differs from the non-strict result where suppression across classes happens at all
+    loose = pb.decode_nms(objs, clfs, locs, top_k=top_k)
+    if clustered:
+        assert not torch.equal(loose, out)
+
+
+def test_strict_nms_layer_class_limit_and_spill(strict_cap_case):
+    """(1) the per-class limit 2*top_k cuts before the all-class pass; (2) > 1024 class-stage survivors (the
+    shared-memory part of that list) with heavy cross-class suppression: 1500 classes x 4 places."""
+    boxes, classes, confs = strict_cap_case
+    layer = odk.layers.nms()(2, len(boxes), top_k=2, nms_all_threshold=0.5)
+    out, kept = layer([classes[None].astype(np.int32), confs[None], boxes[None]], return_index=True)
+    ro, rk = R.nms_layer_image(classes, confs, boxes, 2, top_k=2, nms_all_threshold=0.5)
+    assert kept[0].tolist() == rk.tolist() == [0, -1] and np.array_equal(out[0], ro)
+
+    rng = np.random.RandomState(8)
+    c, places = 1500, 4
+    n = c * places
+    base = np.array([[0.05, 0.05, 0.3, 0.3], [0.6, 0.1, 0.9, 0.35], [0.1, 0.6, 0.4, 0.9], [0.55, 0.55, 0.95, 0.95]], np.float32)
+    boxes = (np.repeat(base, c, axis=0) + rng.normal(0, 0.004, size=(n, 4))).astype(np.float32)
+    classes = np.tile(np.arange(c), places).astype(np.int32)
+    confs = (rng.permutation(n).astype(np.float32) + 100) / np.float32(n + 200)
+    layer = odk.layers.nms()(c, n, top_k=200, nms_all_threshold=0.5)
+    out, kept = layer([classes[None], confs[None], boxes[None]], return_index=True)
+    ro, rk = R.nms_layer_image(classes, confs, boxes, c, top_k=200, nms_all_threshold=0.5)
+    assert np.array_equal(kept[0], rk) and np.array_equal(out[0], ro)
+    assert 1 <= int((rk >= 0).sum()) <= 40  # a handful per place survive the class-agnostic pass
+
+
+def test_predict_from_head_strict_flag(prior_boxes, oracle_tables):
+    od = odk.ObjectDetector.load_voc((320, 320))
+    assert od.strict_nms is True  # od.py:81 default
+    t = oracle_tables('voc320')
+    objs, clfs, locs = synth.predictions(4, 2, len(od.pb), 20, clustered=True)
+    preds = od.predict_from_head(objs, clfs, locs, conf_threshold=0.25, strict_nms=None)
+    ro, _ = R.predict_tail(t, objs, clfs, locs, nms_all_threshold=0.5)
+    for p, (rc, rs, rb) in zip(preds, R.unpack_predictions(ro, 0.25)):
+        assert np.array_equal(p.classes, rc) and np.array_equal(p.confs, rs) and np.array_equal(p.bboxes, rb)

@@ -174,3 +174,49 @@ def test_compute_scores_golden(golden):
         assert np.array_equal(p, g[f'scores_{i}/precisions']) and np.array_equal(r, g[f'scores_{i}/recalls'])
         assert np.array_equal(f, g[f'scores_{i}/fscores'])
     assert R.search_conf_threshold(gt, pred, 5) == float(g['search_conf_threshold'])
+
+
+# ----------------------------------------------------------------------------------------- strict_nms (layers.py:940,953-957)
+def _strict_two_pass(classes, confs, boxes, num_classes, top_k, thr, thr_all):
+    """Independent statement of the strict branch: per-class NumPy NMS with limit 2*top_k, concat, then one
+    more NumPy NMS over everything (scores distinct, so the reference's own argsort order is unambiguous)."""
+    cat = []
+    for c in range(num_classes):
+        sel = np.flatnonzero((classes == c) & (confs > np.float32(0.01)))
+        if len(sel):
+            cat.append(sel[R.numpy_nms(boxes[sel], confs[sel], min(2 * top_k, len(sel)), thr)])
+    if not cat:
+        return np.zeros(0, np.int64)
+    cat = np.concatenate(cat)
+    return cat[R.numpy_nms(boxes[cat], confs[cat], min(top_k, len(cat)), thr_all)]
+
+
+def test_strict_layer_equals_two_independent_passes():
+    rng = np.random.RandomState(5)
+    for trial in range(6):
+        n, c = 400, 5
+        ctr = rng.uniform(0.2, 0.8, size=(12, 2))[rng.randint(0, 12, size=n)] + rng.normal(0, 0.03, size=(n, 2))
+        wh = rng.uniform(0.1, 0.3, size=(n, 2))
+        boxes = np.clip(np.concatenate([ctr - wh / 2, ctr + wh / 2], axis=1), 0, 1).astype(np.float32)
+        confs = rng.permutation(n).astype(np.float32) / np.float32(n) * np.float32(0.9) + np.float32(0.02)
+        classes = rng.randint(0, c, size=n)
+        top_k = [200, 10, 3][trial % 3]
+        out, kept = R.nms_layer_image(classes, confs, boxes, c, top_k=top_k, nms_all_threshold=0.5)
+        ref = _strict_two_pass(classes, confs, boxes, c, top_k, 0.45, 0.5)
+        k = int((kept >= 0).sum())
+        assert np.array_equal(kept[:k], ref)
+        assert np.array_equal(out[:k, 1], confs[ref]) and np.array_equal(out[:k, 0], classes[ref].astype(np.float32))
+        assert (out[k:] == 0).all()
+        # the second pass can only remove boxes relative to the doubled-limit class stage
+        loose, lk = R.nms_layer_image(classes, confs, boxes, c, top_k=2 * top_k * c)
+        assert set(kept[:k]) <= set(lk[lk >= 0])
+
+
+def test_strict_class_limit_cuts_before_all_class_pass(strict_cap_case):
+    """top_k=2 -> per-class limit 4 (layers.py:940): four mutually compatible class-0 boxes around a stronger
+    class-1 box use the limit up and are then all removed by the class-agnostic pass; the fifth class-0 box
+    was already cut by the limit, so only the class-1 box survives."""
+    boxes, classes, confs = strict_cap_case
+    out, kept = R.nms_layer_image(classes, confs, boxes, 2, top_k=2, nms_all_threshold=0.5)
+    assert kept.tolist() == [0, -1]
+    assert np.array_equal(kept[:1], _strict_two_pass(classes, confs, boxes, 2, 2, 0.45, 0.5))
