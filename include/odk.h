@@ -96,6 +96,29 @@ int odk_assign_encode(const odk_anchors* a, int batch, const float* gt_boxes /*[
                       int32_t* status /*[dev B]*/, void* workspace /*[dev]*/, size_t workspace_bytes,
                       void* stream);
 
+/* PriorBoxes.loss / loss_obj / loss_clf / loss_loc and the rec_bg / rec_obj / acc_clf metrics
+ * (od_pb.py:365-431; binary focal loss losses.py:22-30, Keras categorical_crossentropy and
+ * mean_squared_error) — forward values per image.  y_true, y_pred: [dev B,N,3+C+4] fp32 in the
+ * encode_truth layout.  out[b, :] = {loss, loss_obj, loss_clf, loss_loc, rec_bg, rec_obj, acc_clf,
+ * number of positive anchors} as fp64 (per-row arithmetic fp32 like the TF graph, sums fp64).
+ * PARITY UNPINNED (TensorFlow absent from the reference tree); 1e-5 relative against the oracle. */
+size_t odk_loss_workspace_bytes(const odk_anchors* a, int batch);
+int odk_loss(const odk_anchors* a, int batch, const float* y_true /*[dev B,N,3+C+4]*/,
+             const float* y_pred /*[dev B,N,3+C+4]*/, double* out /*[dev B,8]*/,
+             void* workspace /*[dev]*/, size_t workspace_bytes, void* stream);
+
+/* encode_truth (od_pb.py:299-313) followed by loss (od_pb.py:365-431) with y_true never written:
+ * odk_assign, then a pass that reads one float per negative anchor row of y_pred and whole rows
+ * only for the positives.  Same outputs as odk_loss; pb_indices / gt_indices / status as odk_assign.
+ * Images whose status is not ODK_IMG_OK contribute an all-zero y_true (as odk_assign_encode). */
+size_t odk_assign_loss_workspace_bytes(const odk_anchors* a, int batch, int gmax);
+int odk_assign_loss(const odk_anchors* a, int batch, const float* gt_boxes /*[dev B,Gmax,4]*/,
+                    const int32_t* gt_classes /*[dev B,Gmax]*/, const int32_t* gt_count /*[dev B]*/,
+                    int gmax, const float* y_pred /*[dev B,N,3+C+4]*/, double* out /*[dev B,8]*/,
+                    int64_t* pb_indices /*[dev B,Gmax]*/, int64_t* gt_indices /*[dev B,Gmax]*/,
+                    int32_t* status /*[dev B]*/, void* workspace /*[dev, 256-byte aligned]*/,
+                    size_t workspace_bytes, void* stream);
+
 /* ChannelArgMax + ChannelMax + _objconf + decode_locs (layers.py:69-98, od_net.py:177-189):
  * classes = argmax_c clfs, confs = objs*max_c clfs*pb_mask, boxes = decode(locs). */
 int odk_decode_score(const odk_anchors* a, int batch, const float* objs /*[dev B,N,1]*/,

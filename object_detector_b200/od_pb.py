@@ -229,6 +229,79 @@ class PriorBoxes:
             res['pb_valids'] = valids.view(torch.bool)
         return res
 
+    # ---- loss side (od_pb.py:365-431) --------------------------------------------------------------------
+    LOSS_COLUMNS = ('loss', 'loss_obj', 'loss_clf', 'loss_loc', 'rec_bg', 'rec_obj', 'acc_clf', 'n_positive')
+
+    def loss_terms(self, y_true, y_pred):
+        """All of od_pb.py:365-431 in one pass over (B,N,3+C+4) ``y_true`` / ``y_pred``: a (B,8) float64 CUDA
+        tensor with the columns ``LOSS_COLUMNS`` (forward values; ``odk_loss``)."""
+        dev = _dev.device(y_pred.device if isinstance(y_pred, torch.Tensor) and y_pred.is_cuda else None)
+        yt = _dev.to_device(y_true, torch.float32, dev)
+        yp = _dev.to_device(y_pred, torch.float32, dev)
+        n, w = len(self.pb_locs), 3 + self.num_classes + 4
+        assert yt.dim() == 3 and yt.shape[1:] == (n, w) and yp.shape == yt.shape
+        b = yt.shape[0]
+        out = torch.empty((b, 8), dtype=torch.float64, device=dev)
+        ws_bytes = _lib.load().odk_loss_workspace_bytes(self._handle(dev), b)
+        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _lib.call('odk_loss', self._handle(dev), b, yt.data_ptr(), yp.data_ptr(), out.data_ptr(), ws.data_ptr(), ws_bytes,
+                      _dev.stream_ptr(dev))
+        return out
+
+    def assign_loss_batch(self, gt_boxes, gt_classes, gt_count, y_pred):
+        """``encode_truth`` followed by ``loss`` without ever writing y_true (``odk_assign_loss``): padded GT as in
+        ``encode_truth_batch`` + the network output (B,N,3+C+4) -> dict with ``terms`` (B,8) float64 (columns
+        ``LOSS_COLUMNS``), ``pb_indices``, ``gt_indices``, ``status``."""
+        dev = _dev.device(y_pred.device if isinstance(y_pred, torch.Tensor) and y_pred.is_cuda else None)
+        boxes = _dev.to_device(gt_boxes, torch.float32, dev)
+        classes = _dev.to_device(gt_classes, torch.int32, dev)
+        count = _dev.to_device(gt_count, torch.int32, dev)
+        yp = _dev.to_device(y_pred, torch.float32, dev)
+        b, gmax = boxes.shape[0], boxes.shape[1]
+        n, w = len(self.pb_locs), 3 + self.num_classes + 4
+        assert boxes.shape == (b, gmax, 4) and classes.shape == (b, gmax) and count.shape == (b,) and yp.shape == (b, n, w)
+        out = torch.empty((b, 8), dtype=torch.float64, device=dev)
+        pb_idx = torch.empty((b, gmax), dtype=torch.int64, device=dev)
+        gt_idx = torch.empty((b, gmax), dtype=torch.int64, device=dev)
+        status = torch.empty((b,), dtype=torch.int32, device=dev)
+        ws_bytes = _lib.load().odk_assign_loss_workspace_bytes(self._handle(dev), b, gmax)
+        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _lib.call('odk_assign_loss', self._handle(dev), b, boxes.data_ptr(), classes.data_ptr(), count.data_ptr(), gmax,
+                      yp.data_ptr(), out.data_ptr(), pb_idx.data_ptr(), gt_idx.data_ptr(), status.data_ptr(), ws.data_ptr(),
+                      ws_bytes, _dev.stream_ptr(dev))
+        return {'terms': out, 'pb_indices': pb_idx, 'gt_indices': gt_idx, 'status': status}
+
+    def _loss_column(self, y_true, y_pred, k):
+        return self.loss_terms(y_true, y_pred)[:, k].to(torch.float32)
+
+    def loss(self, y_true, y_pred):
+        """od_pb.py:365-373: (B,) float32 = loss_obj + loss_clf + loss_loc."""
+        return self._loss_column(y_true, y_pred, 0)
+
+    def loss_obj(self, y_true, y_pred):
+        """od_pb.py:403-411 (binary focal loss over pb_mask * gt_mask, times 3)."""
+        return self._loss_column(y_true, y_pred, 1)
+
+    def loss_clf(self, y_true, y_pred):
+        """od_pb.py:413-421 (categorical cross-entropy weighted by channel 1)."""
+        return self._loss_column(y_true, y_pred, 2)
+
+    def loss_loc(self, y_true, y_pred):
+        """od_pb.py:423-431 (mean squared box error weighted by channel 1, times 2)."""
+        return self._loss_column(y_true, y_pred, 3)
+
+    @property
+    def metrics(self):
+        """od_pb.py:375-401: [loss_obj, loss_clf, loss_loc, rec_bg, rec_obj, acc_clf] as callables (y_true, y_pred)."""
+        def column(k, name):
+            def fn(y_true, y_pred):
+                return self._loss_column(y_true, y_pred, k)
+            fn.__name__ = name
+            return fn
+        return [self.loss_obj, self.loss_clf, self.loss_loc, column(4, 'rec_bg'), column(5, 'rec_obj'), column(6, 'acc_clf')]
+
     @staticmethod
     def _raise_for_status(status, y_gt):
         """Maps device status words to the reference's AssertionErrors (od_pb.py:304,332,338)."""

@@ -278,3 +278,63 @@ def test_predict_from_head_strict_flag(prior_boxes, oracle_tables):
     ro, _ = R.predict_tail(t, objs, clfs, locs, nms_all_threshold=0.5)
     for p, (rc, rs, rb) in zip(preds, R.unpack_predictions(ro, 0.25)):
         assert np.array_equal(p.classes, rc) and np.array_equal(p.confs, rs) and np.array_equal(p.bboxes, rb)
+
+
+# ----------------------------------------------------------------------------------------- losses
+def _head_like(rng, shape, c):
+    """A y_pred in the network's output layout: sigmoid objectness, softmax classes, free box offsets."""
+    y = rng.normal(size=shape).astype(np.float32)
+    y[..., :3] = 1 / (1 + np.exp(-y[..., :3] * 2))
+    e = np.exp(y[..., 3:3 + c] * 2)
+    y[..., 3:3 + c] = e / e.sum(axis=-1, keepdims=True)
+    return y.astype(np.float32)
+
+
+@pytest.mark.parametrize('name,batch,gmax', [('voc640', 4, 64), ('voc320', 3, 7), ('mid80', 2, 9), ('odd7', 3, 5), ('tiny128', 5, 3)])
+def test_loss_terms_dense_and_fused_vs_oracle(prior_boxes, oracle_tables, name, batch, gmax):
+    """od_pb.py:365-431.  Floating point: 1e-5 relative (BASELINE north_star) against the float32/float64 oracle;
+    the fused assign+loss path (no y_true) must agree with the dense one to the same bar, its indices exactly."""
+    pb, t = prior_boxes(name), oracle_tables(name)
+    c = pb.num_classes
+    gtb, gtc, gtn = synth.gt_batch(11, batch, gmax, c, size=(0.1, 0.5))
+    gtn[0] = 0  # an image without ground truth: weights 1/max(1,0)
+    enc = pb.encode_truth_batch(gtb, gtc, gtn)
+    assert (enc['status'].cpu().numpy() == 0).all()
+    y_true = enc['y_true']
+    rng = np.random.RandomState(2)
+    y_pred = _head_like(rng, tuple(y_true.shape), c)
+    ref = R.od_losses(t, y_true.cpu().numpy(), y_pred)
+    terms = pb.loss_terms(y_true, y_pred).cpu().numpy()
+    fused = pb.assign_loss_batch(gtb, gtc, gtn, y_pred)
+    assert torch.equal(fused['pb_indices'], enc['pb_indices']) and torch.equal(fused['gt_indices'], enc['gt_indices'])
+    ft = fused['terms'].cpu().numpy()
+    for k, col in enumerate(pb.LOSS_COLUMNS[:7]):
+        np.testing.assert_allclose(terms[:, k], ref[col], rtol=1e-5, atol=1e-7, err_msg=col)
+        np.testing.assert_allclose(ft[:, k], ref[col], rtol=1e-5, atol=1e-7, err_msg='fused ' + col)
+    assert np.array_equal(terms[:, 7], gtn.astype(np.float64)) and np.array_equal(ft[:, 7], terms[:, 7])
+    # the reference's call signatures
+    np.testing.assert_allclose(pb.loss(y_true, y_pred).cpu().numpy(), ref['loss'], rtol=2e-5)
+    got = [m(y_true, y_pred).cpu().numpy() for m in pb.metrics]
+    for g, col in zip(got, ('loss_obj', 'loss_clf', 'loss_loc', 'rec_bg', 'rec_obj', 'acc_clf')):
+        np.testing.assert_allclose(g, ref[col], rtol=2e-5, atol=1e-7, err_msg=col)
+
+
+def test_loss_full_batch_properties(prior_boxes):
+    """BASELINE config 3 at full size (B=256, <= 64 GT): perfect prediction -> ~0 loss and unit metrics; linear in
+    the weights (scaling a term's inputs); deterministic across runs."""
+    pb = prior_boxes('voc640')
+    gtb, gtc, gtn = synth.gt_batch(7, 256, 64, 20)
+    enc = pb.encode_truth_batch(gtb, gtc, gtn)
+    ok = (enc['status'] == 0)
+    y_true = enc['y_true']
+    y_perfect = y_true.clone()
+    y_perfect[:, :, 3:-4] += (y_true[:, :, 2:3] == 0) * 0.05  # negatives: a uniform softmax row instead of all-zero
+    perfect = pb.loss_terms(y_true, y_perfect)
+    assert bool((perfect[ok][:, 0] < 1e-3).all()) and bool((perfect[ok][:, 4:7] == 1).all())
+    rng = np.random.RandomState(5)
+    y_pred = torch.from_numpy(_head_like(rng, (256, len(pb), 27), 20)).cuda()
+    a = pb.loss_terms(y_true, y_pred)
+    assert torch.equal(a, pb.loss_terms(y_true, y_pred))  # fixed reduction order
+    f = pb.assign_loss_batch(gtb, gtc, gtn, y_pred)['terms']
+    assert torch.allclose(f[ok], a[ok], rtol=1e-9, atol=1e-12)
+    assert bool(torch.isfinite(a).all()) and bool((a[:, 0] > 0).all())

@@ -220,3 +220,32 @@ def test_strict_class_limit_cuts_before_all_class_pass(strict_cap_case):
     out, kept = R.nms_layer_image(classes, confs, boxes, 2, top_k=2, nms_all_threshold=0.5)
     assert kept.tolist() == [0, -1]
     assert np.array_equal(kept[:1], _strict_two_pass(classes, confs, boxes, 2, 2, 0.45, 0.5))
+
+
+# ----------------------------------------------------------------------------------------- losses (od_pb.py:365-431; parity unpinned: TF absent)
+def test_od_losses_closed_form_cases(oracle_tables):
+    """Hand-checkable cases of the restated loss: a perfect prediction gives ~0 loss and metric 1; the focal term of
+    a single negative row equals -0.75 * p^2 * log(1-p) * mask; the weights sum to 1 over the positives."""
+    t = oracle_tables('tiny128')
+    rng = np.random.RandomState(0)
+    boxes = np.array([[0.1, 0.1, 0.5, 0.6], [0.55, 0.3, 0.9, 0.8]], np.float32)
+    classes = np.array([0, 1], np.int32)
+    y_true = R.encode_truth(t, [(classes, boxes)])
+    assert np.isclose(y_true[0, :, 1].sum(), 1.0)
+    perfect = y_true.copy()
+    perfect[0, y_true[0, :, 2] == 0, 3:-4] = 0.5  # a softmax output is never all-zero (0/0 would be NaN, as in TF)
+    res = R.od_losses(t, y_true, perfect)
+    assert res['loss'][0] < 1e-4 and res['rec_bg'][0] == 1 and res['rec_obj'][0] == 1 and res['acc_clf'][0] == 1
+    # one negative valid row predicts objectness p, everything else perfect
+    neg = np.flatnonzero((y_true[0, :, 2] == 0) & (y_true[0, :, 0] > 0) & t.pb_mask)[3]
+    pred = perfect.copy()
+    p = np.float32(0.7)
+    pred[0, neg, 2] = p
+    res2 = R.od_losses(t, y_true, pred)
+    want = 3 * (-0.75 * float(p) ** 2 * np.log(1 - float(p))) * float(y_true[0, neg, 0])
+    assert np.isclose(res2['loss_obj'][0] - res['loss_obj'][0], want, rtol=1e-5)
+    assert res2['rec_bg'][0] < 1
+    # random predictions: finite, positive
+    pred = rng.uniform(0.01, 0.99, size=y_true.shape).astype(np.float32)
+    r3 = R.od_losses(t, y_true, pred)
+    assert all(np.isfinite(v).all() for v in r3.values()) and r3['loss'][0] > 0
