@@ -38,6 +38,7 @@ struct AssignArgs {
   int* ws_ncand;  // [B, Gmax] in-cell valid anchors of the GT
   int* ws_nlist;  // [B, Gmax] entries stored in its ranked list
   unsigned* ws_ignore;  // [B, bitmap_words] bit a = "pb_mask[a] and some GT has IoU >= 0.5 with anchor a" (pre-zeroed) or null
+  int debug_skip;       // timing experiments only (ODK_DEBUG_SKIP): wrong results when non-zero
 };
 
 __device__ __forceinline__ double encode_cost(const float4 box, const float4 loc, const double2 sz) {
@@ -99,12 +100,16 @@ __device__ __forceinline__ bool cand_less(double c0, int a0, double c1, int a1) 
 }
 
 // Phase A: every in-cell anchor of one GT ranked by (fp64 cost, index), ignoring "taken".
-__global__ void __launch_bounds__(kGreedyThreads, 2) assign_candidates_kernel(const AssignArgs p) {
-  __shared__ double s_cost[kGreedyWarps * kScratch];
-  __shared__ int s_idx[kGreedyWarps * kScratch];
+// 4 warps per CTA and <= 64 registers: all (image, GT) warps of a batch-64 x 64-GT launch are resident at once (16 CTAs
+// per SM), so the kernel lasts one warp's dependent-load chain instead of two waves of it.
+constexpr int kCandThreads = 128;
+constexpr int kCandWarps = kCandThreads / 32;
+__global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(const AssignArgs p) {
+  __shared__ double s_cost[kCandWarps * kScratch];
+  __shared__ int s_idx[kCandWarps * kScratch];
   const int warp = threadIdx.x >> 5;
   const int lane = (int)odk_lane();
-  const long long task = (long long)blockIdx.x * kGreedyWarps + warp;
+  const long long task = (long long)blockIdx.x * kCandWarps + warp;
   if (task >= (long long)p.batch * p.gmax) return;
   const int b = (int)(task / p.gmax), g = (int)(task % p.gmax);
   const int g_count = p.gt_count[b];
@@ -117,6 +122,7 @@ __global__ void __launch_bounds__(kGreedyThreads, 2) assign_candidates_kernel(co
   const float4 box = p.gt_boxes[(size_t)b * p.gmax + g];
   const float cx = __fmul_rn(__fadd_rn(box.z, box.x), 0.5f);  // ml.py:485-488
   const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
+  if (p.debug_skip & 4) return;
   int filled = 0;
   const int total = for_each_cell_candidate(p.av, cx, cy, lane, [&](int a, bool ok) {
     const unsigned m = __ballot_sync(0xffffffffu, ok);
@@ -131,13 +137,32 @@ __global__ void __launch_bounds__(kGreedyThreads, 2) assign_candidates_kernel(co
   });
   __syncwarp();
   int stored = 0;
-  if (total <= kScratch) {  // ranks are global only if every candidate made it into the scratch
-    for (int e = lane; e < total; e += 32) {
-      const double ce = wc[e];
-      const int ae = wi[e];
-      int r = 0;
-      for (int q = 0; q < total; ++q) r += cand_less(wc[q], wi[q], ce, ae);
-      if (r < L) list[r] = ae;
+  if (total <= kScratch && !(p.debug_skip & 1)) {  // ranks are global only if every candidate made it into the scratch
+    // rank = number of candidates that order before this one.  A lane ranks up to four entries in one pass over the
+    // scratch (shared broadcast reads, unrolled), instead of one pass per entry.
+    for (int e0 = 0; e0 < total; e0 += 128) {
+      // costs are sums of absolute values (>= +0.0, finite for finite boxes): their bit patterns order like the values,
+      // so the comparisons run on the integer pipe
+      const long long* wk = reinterpret_cast<const long long*>(wc);
+      long long ce[4];
+      int ae[4], rk[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int e = e0 + u * 32 + lane;
+        ce[u] = e < total ? wk[e] : 0ll;
+        ae[u] = e < total ? wi[e] : 0;
+        rk[u] = 0;
+      }
+#pragma unroll 4
+      for (int q = 0; q < total; ++q) {
+        const long long cq = wk[q];
+        const int aq = wi[q];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) rk[u] += (cq < ce[u]) || (cq == ce[u] && aq < ae[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (e0 + u * 32 + lane < total && rk[u] < L) list[rk[u]] = ae[u];
     }
     stored = min(total, L);
   }
@@ -145,57 +170,73 @@ __global__ void __launch_bounds__(kGreedyThreads, 2) assign_candidates_kernel(co
     p.ws_ncand[(size_t)b * p.gmax + g] = total;
     p.ws_nlist[(size_t)b * p.gmax + g] = stored;
   }
-  if (p.ws_ignore == nullptr) return;
+  if (p.ws_ignore == nullptr || (p.debug_skip & 2)) return;
   // ---- ignore mask, scattered per GT: pb_valids[iou >= 0.5] = False (od_pb.py:355-357; order-independent
   //      closed form, SURVEY A-4).  Only anchors that CAN reach IoU 0.5 are visited:
   //        IoU >= 1/2  =>  I >= (A+B)/3 and min(A,B)/max(A,B) >= 1/2;  with I <= iw*min(hg,ha) and
   //        iw <= (wg+wa)/2 - |dcx|  this gives |dcx| <= (wg+wa)/6 (same in y).
   //      The cell ranges below are that bound with 2% + one cell of slack; every visited anchor is then
   //      decided by the exact fp32 expression.
+  //      All (map, pattern) combinations that can reach IoU 0.5 are flattened into ONE cell index space (descriptors in
+  //      the warp's scratch, offsets by a warp scan), so the anchor loads of different combinations are independent
+  //      and overlap instead of costing one L2 round trip per combination.
   unsigned* ignore = p.ws_ignore + (size_t)b * p.bitmap_words;
   const float wg = __fsub_rn(box.z, box.x), hg = __fsub_rn(box.w, box.y);
   const float ga = __fmul_rn(wg, hg);
   const int n_combo = p.av.n_maps * p.av.n_patterns;
+  int* d_end = wi;                               // [32] inclusive cell-count scan
+  int4* d_geo = reinterpret_cast<int4*>(wc);     // [32] {base, m, ix_lo, iy_lo}
+  int* d_nx = wi + 32;                           // [32]
   for (int c0 = 0; c0 < n_combo; c0 += 32) {
-    // lane i fetches the cell-(0,0) anchor of (map, pattern) combination c0+i: one round trip for 32 of them
+    // lane i owns (map, pattern) combination c0+i: its cell-(0,0) anchor gives the size shared by all its cells
     int my_m = 1, my_base = 0;
-    float4 my_l0 = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (c0 + lane < n_combo) {
+    float4 l0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool have = c0 + lane < n_combo;
+    if (have) {
       const int mi = (c0 + lane) / p.av.n_patterns, pat = (c0 + lane) % p.av.n_patterns;
       my_m = p.av.map_size[mi];
       my_base = p.av.map_off[mi] + pat * my_m * my_m;
-      my_l0 = __ldg(p.av.locs + my_base);
+      l0 = __ldg(p.av.locs + my_base);
     }
-    // all cells of a (map, pattern) share the anchor size; its area decides whether IoU 0.5 is reachable at all
-    const float my_aa = (my_l0.z - my_l0.x) * (my_l0.w - my_l0.y);
-    unsigned todo = __ballot_sync(0xffffffffu, c0 + lane < n_combo && ga >= 0.45f * my_aa && ga <= 2.2f * my_aa);
-    for (; todo; todo &= todo - 1) {
-      const int src = __ffs(todo) - 1;
-      const int m = __shfl_sync(0xffffffffu, my_m, src);
-      const int base = __shfl_sync(0xffffffffu, my_base, src);
-      float4 l0;
-      l0.x = __shfl_sync(0xffffffffu, my_l0.x, src);
-      l0.y = __shfl_sync(0xffffffffu, my_l0.y, src);
-      l0.z = __shfl_sync(0xffffffffu, my_l0.z, src);
-      l0.w = __shfl_sync(0xffffffffu, my_l0.w, src);
-      const float wa = l0.z - l0.x, ha = l0.w - l0.y;
-      const float rx = (wg + wa) * 0.17f + 1e-4f, ry = (hg + ha) * 0.17f + 1e-4f;
-      const float c0x = 0.5f * (l0.x + l0.z), c0y = 0.5f * (l0.y + l0.w);
-      // anchor centres sit at c0 + i/m (to fp32 rounding); 0.02 of a cell on top of the 2% absorbs that rounding
-      const int ix_lo = max(0, (int)ceilf((cx - rx - c0x) * (float)m - 0.02f));
-      const int ix_hi = min(m - 1, (int)floorf((cx + rx - c0x) * (float)m + 0.02f));
-      const int iy_lo = max(0, (int)ceilf((cy - ry - c0y) * (float)m - 0.02f));
-      const int iy_hi = min(m - 1, (int)floorf((cy + ry - c0y) * (float)m + 0.02f));
-      const int nx = ix_hi - ix_lo + 1, ny = iy_hi - iy_lo + 1;
-      if (nx <= 0 || ny <= 0) continue;
+    const float wa = l0.z - l0.x, ha = l0.w - l0.y;
+    const float aa = wa * ha;  // its area decides whether IoU 0.5 is reachable at all
+    const float rx = (wg + wa) * 0.17f + 1e-4f, ry = (hg + ha) * 0.17f + 1e-4f;
+    const float c0x = 0.5f * (l0.x + l0.z), c0y = 0.5f * (l0.y + l0.w);
+    const float m = (float)my_m;
+    // anchor centres sit at c0 + i/m (to fp32 rounding); 0.02 of a cell on top of the 2% absorbs that rounding
+    const int ix_lo = max(0, (int)ceilf((cx - rx - c0x) * m - 0.02f));
+    const int ix_hi = min(my_m - 1, (int)floorf((cx + rx - c0x) * m + 0.02f));
+    const int iy_lo = max(0, (int)ceilf((cy - ry - c0y) * m - 0.02f));
+    const int iy_hi = min(my_m - 1, (int)floorf((cy + ry - c0y) * m + 0.02f));
+    const int nx = ix_hi - ix_lo + 1, ny = iy_hi - iy_lo + 1;
+    const bool todo = have && ga >= 0.45f * aa && ga <= 2.2f * aa && nx > 0 && ny > 0;
+    const int cnt = todo ? nx * ny : 0;
+    int end = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, end, d);
+      if (lane >= d) end += o;
+    }
+    const int n_cells = __shfl_sync(0xffffffffu, end, 31);
+    __syncwarp();  // earlier readers of the scratch are done
+    d_end[lane] = end;
+    d_geo[lane] = make_int4(my_base, my_m, ix_lo, iy_lo);
+    d_nx[lane] = nx > 0 ? nx : 1;
+    __syncwarp();
 #pragma unroll 4
-      for (int t = lane; t < nx * ny; t += 32) {
-        const int iy = iy_lo + t / nx, ix = ix_lo + t % nx;
-        const int a = base + iy * m + ix;
-        const unsigned char mk = __ldg(p.av.mask + a);  // mask and box travel together: one round trip per batch
-        const float4 lc = __ldg(p.av.locs + a);
-        if (mk && odk_iou_passes<true>(box, ga, lc, odk_area(lc), 0.5f)) atomicOr(ignore + (a >> 5), 1u << (a & 31));
-      }
+    for (int t = lane; t < n_cells; t += 32) {
+      int j = 0;  // first combination whose inclusive end exceeds t (ends are non-decreasing)
+#pragma unroll
+      for (int step = 16; step > 0; step >>= 1)
+        if (d_end[j + step - 1] <= t) j += step;
+      const int4 geo = d_geo[j];
+      const int w = d_nx[j];
+      const int cell = t - (j > 0 ? d_end[j - 1] : 0);
+      const int iy = geo.w + cell / w, ix = geo.z + cell % w;
+      const int a = geo.x + iy * geo.y + ix;
+      const unsigned char mk = __ldg(p.av.mask + a);
+      const float4 lc = __ldg(p.av.locs + a);
+      if (mk && odk_iou_passes<true>(box, ga, lc, odk_area(lc), 0.5f)) atomicOr(ignore + (a >> 5), 1u << (a & 31));
     }
   }
 }
@@ -452,6 +493,8 @@ static int fill_args(AssignArgs& args, const odk_anchors* a, int batch, const fl
   args.ws_ncand = args.ws_list + (size_t)batch * gmax * args.list_len;
   args.ws_nlist = args.ws_ncand + (size_t)batch * gmax;
   args.ws_ignore = ignore;
+  static const int dbg = getenv("ODK_DEBUG_SKIP") ? atoi(getenv("ODK_DEBUG_SKIP")) : 0;
+  args.debug_skip = dbg;
   return ODK_OK;
 }
 
@@ -462,7 +505,7 @@ int odk_launch_assign_candidates(const odk_anchors* a, int batch, const float* g
   const long long tasks = (long long)batch * gmax;
   {
     OdkProfileScope prof_("assign_candidates_kernel", stream);
-    assign_candidates_kernel<<<(unsigned)((tasks + kGreedyWarps - 1) / kGreedyWarps), kGreedyThreads, 0, stream>>>(args);
+    assign_candidates_kernel<<<(unsigned)((tasks + kCandWarps - 1) / kCandWarps), kCandThreads, 0, stream>>>(args);
   }
   ODK_LAUNCH_CHECK("assign_candidates_kernel");
   return ODK_OK;
