@@ -194,6 +194,15 @@ int odk_match_counts(int n_img, int top_k, int num_classes, const float* dets /*
                      int n_thr, const float* conf_thr /*[dev n_thr]*/, float iou_thr,
                      int32_t* counts /*[dev n_thr,3,C]*/, void* stream);
 
+/* ml.od_confusion_matrix (ml.py:397-451): cm[(C+1),(C+1)] int32, rows = ground-truth class (last row:
+ * nothing there), columns = predicted class (last column: missed).  dets as for odk_match_counts
+ * ([n_img, top_k, 6] rows [class, conf, x1,y1,x2,y2], real rows first, class < 0 = padding).  The
+ * reference's positional use of the mask at ml.py:421 is reproduced (see csrc/scores.cu). */
+int odk_confusion_matrix(int n_img, int top_k, int num_classes, const float* dets /*[dev n_img,top_k,6]*/,
+                         const float* gt_boxes /*[dev n_gt,4]*/, const int32_t* gt_classes /*[dev n_gt]*/,
+                         const int32_t* gt_offsets /*[dev n_img+1]*/, float conf_thr, float iou_thr,
+                         int32_t* cm /*[dev (C+1)*(C+1)]*/, void* stream);
+
 /* Measurement aid (bench.py): when enabled for the calling host thread every kernel launch of the
  * library is bracketed by CUDA events on its stream; odk_profile_read synchronises them and returns,
  * per kernel name, the summed device time and the launch count, then clears the log. */

@@ -53,6 +53,8 @@ SIGNATURES = {
                            c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_match_counts': (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
                                  c_float, c_void_p, c_void_p]),
+    'odk_confusion_matrix': (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p,
+                                     c_void_p]),
     'odk_profile_enable': (c_int, [c_int]),
     'odk_profile_read': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
 }

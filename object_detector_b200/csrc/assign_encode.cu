@@ -141,24 +141,21 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(cons
     // rank = number of candidates that order before this one.  A lane ranks up to four entries in one pass over the
     // scratch (shared broadcast reads, unrolled), instead of one pass per entry.
     for (int e0 = 0; e0 < total; e0 += 128) {
-      // costs are sums of absolute values (>= +0.0, finite for finite boxes): their bit patterns order like the values,
-      // so the comparisons run on the integer pipe
-      const long long* wk = reinterpret_cast<const long long*>(wc);
-      long long ce[4];
+      double ce[4];
       int ae[4], rk[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const int e = e0 + u * 32 + lane;
-        ce[u] = e < total ? wk[e] : 0ll;
+        ce[u] = e < total ? wc[e] : 0.0;
         ae[u] = e < total ? wi[e] : 0;
         rk[u] = 0;
       }
 #pragma unroll 4
       for (int q = 0; q < total; ++q) {
-        const long long cq = wk[q];
+        const double cq = wc[q];
         const int aq = wi[q];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) rk[u] += (cq < ce[u]) || (cq == ce[u] && aq < ae[u]);
+        for (int u = 0; u < 4; ++u) rk[u] += cand_less(cq, aq, ce[u], ae[u]);
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u)

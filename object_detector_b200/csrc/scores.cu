@@ -114,3 +114,141 @@ extern "C" int odk_match_counts(int n_img, int top_k, int num_classes, const flo
   ODK_LAUNCH_CHECK("match_counts_kernel");
   return ODK_OK;
 }
+
+// ---- ml.od_confusion_matrix (ml.py:397-451) ---------------------------------------------------------------------------
+// One warp per image; detections live in shared memory.  Per image: (1) descending-confidence order of the
+// detections (rank by counting; equal confidences: higher index first); (2) per detection the GT of its largest
+// fp32 IoU (first maximum) and whether that IoU reaches the threshold; (3) the reference's sequential loop over the
+// GTs.  Step 3 reproduces ml.py:421 literally: the per-detection mask m is applied to the POSITIONS of the sorted index
+// array, so position j contributes detection order[j] when detection j passes the mask.  For one GT the visited set T
+// splits into A = {class == gt class} and B = {still enabled, other class}; pass 1 (:424-431) books the first of A as
+// the hit and the rest of A as duplicates, pass 2 (:433-442) books the first of B as a class confusion if A was empty
+// and everything else as duplicates; all of T is disabled afterwards.  Leftover enabled detections are false
+// positives (:446-447).
+namespace {
+
+struct CmArgs {
+  int n_img, top_k, num_classes;
+  const float* dets;           // [n_img, K, 6]; the real rows (class >= 0) come first
+  const float4* gt_boxes;      // [n_gt]
+  const int32_t* gt_classes;   // [n_gt]
+  const int32_t* gt_offsets;   // [n_img + 1]
+  float conf_thr, iou_thr;
+  int32_t* cm;                 // [(C+1), (C+1)] pre-zeroed
+};
+
+__global__ void __launch_bounds__(kScoreWarps * 32) confusion_kernel(const CmArgs p) {
+  extern __shared__ __align__(16) unsigned char cm_smem[];
+  const int warp = threadIdx.x >> 5;
+  const int lane = (int)odk_lane();
+  const int img = blockIdx.x * kScoreWarps + warp;
+  if (img >= p.n_img) return;
+  const int K = p.top_k, C = p.num_classes, C1 = p.num_classes + 1;
+  unsigned char* base = cm_smem + (size_t)warp * odk_align_up((size_t)K * 32, 16);
+  float4* dbox = reinterpret_cast<float4*>(base);                        // [K]
+  float* dconf = reinterpret_cast<float*>(base + (size_t)K * 16);        // [K]
+  short* dcls = reinterpret_cast<short*>(base + (size_t)K * 20);         // [K]
+  short* order = reinterpret_cast<short*>(base + (size_t)K * 22);        // [K] detection at sorted position j
+  short* dgt = reinterpret_cast<short*>(base + (size_t)K * 24);          // [K] GT of the largest IoU, -1 if below threshold
+  short* tlist = reinterpret_cast<short*>(base + (size_t)K * 26);        // [K] detections visited for the current GT
+  unsigned char* dlive = base + (size_t)K * 28;                          // [K] pred_enabled
+  const float* rows = p.dets + (size_t)img * K * 6;
+  int n_local = 0;
+  for (int d = lane; d < K; d += 32) {
+    const float* r = rows + d * 6;
+    const bool real = r[0] >= 0.0f;
+    dbox[d] = make_float4(r[2], r[3], r[4], r[5]);
+    dconf[d] = r[1];
+    dcls[d] = real ? (short)min((int)r[0], C) : (short)-1;
+    dlive[d] = (real && r[1] >= p.conf_thr) ? 1 : 0;  // ml.py:410
+    n_local += real ? 1 : 0;
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) n_local += __shfl_xor_sync(0xffffffffu, n_local, s);
+  const int n = n_local;  // number of detections of this image
+  __syncwarp();
+  const int g0 = p.gt_offsets[img], G = p.gt_offsets[img + 1] - g0;
+  if (G > 0) {
+    for (int d = lane; d < n; d += 32) {
+      // (1) sorted position of detection d
+      const float cd = dconf[d];
+      int rk = 0;
+      for (int q = 0; q < n; ++q) {
+        const float cq = dconf[q];
+        rk += (cq > cd) || (cq == cd && q > d);
+      }
+      order[rk] = (short)d;
+      // (2) nearest GT (ml.py:413-415)
+      const float4 db = dbox[d];
+      const float da = odk_area(db);
+      float best = -1.0f;
+      int bg = 0;
+      for (int g = 0; g < G; ++g) {
+        const float4 gb = p.gt_boxes[g0 + g];
+        const float v = odk_iou_value(gb, odk_area(gb), db, da);
+        if (v > best) { best = v; bg = g; }
+      }
+      dgt[d] = (best >= p.iou_thr) ? (short)bg : (short)-1;
+    }
+    __syncwarp();
+    // (3) the loop over the GTs (ml.py:418-444)
+    for (int g = 0; g < G; ++g) {
+      const int gc = p.gt_classes[g0 + g];
+      int nA = 0, nT = 0, firstA = 0x7fffffff, firstB = 0x7fffffff;
+      for (int j0 = 0; j0 < n; j0 += 32) {
+        const int j = j0 + lane;
+        const bool mj = j < n && dlive[j] && dgt[j] == g;
+        const int t = mj ? order[j] : 0;
+        const bool inA = mj && dcls[t] == gc;
+        const bool inB = mj && dlive[t] && dcls[t] != gc;
+        const unsigned bm = __ballot_sync(0xffffffffu, mj), ba = __ballot_sync(0xffffffffu, inA), bb = __ballot_sync(0xffffffffu, inB);
+        if (mj) tlist[nT + __popc(bm & ((1u << lane) - 1u))] = (short)t;
+        nT += __popc(bm);
+        nA += __popc(ba);
+        if (ba && firstA == 0x7fffffff) firstA = j0 + __ffs(ba) - 1;
+        if (bb && firstB == 0x7fffffff) firstB = j0 + __ffs(bb) - 1;
+        if (inA) atomicAdd(p.cm + (size_t)((j == firstA) ? gc : C) * C1 + gc, 1);
+        // pass 2 needs to know whether A is empty: decided after the scan (below) for the first of B only
+        if (inB && j != firstB) atomicAdd(p.cm + (size_t)C * C1 + dcls[t], 1);
+      }
+      if (lane == 0) {
+        if (firstB != 0x7fffffff) {
+          const int t = order[firstB];
+          atomicAdd(p.cm + (size_t)((nA == 0) ? gc : C) * C1 + dcls[t], 1);
+        }
+        if (nA == 0 && firstB == 0x7fffffff) atomicAdd(p.cm + (size_t)gc * C1 + C, 1);  // missed (:443-444)
+      }
+      __syncwarp();
+      for (int i = lane; i < nT; i += 32) dlive[tlist[i]] = 0;
+      __syncwarp();
+    }
+  }
+  for (int d = lane; d < n; d += 32)
+    if (dlive[d]) atomicAdd(p.cm + (size_t)C * C1 + dcls[d], 1);
+}
+
+}  // namespace
+
+extern "C" int odk_confusion_matrix(int n_img, int top_k, int num_classes, const float* dets, const float* gt_boxes, const int32_t* gt_classes,
+                                    const int32_t* gt_offsets, float conf_thr, float iou_thr, int32_t* cm, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  ODK_REQUIRE(n_img >= 1 && top_k >= 1 && num_classes >= 1, ODK_ERR_INVALID_ARGUMENT, "confusion_matrix: bad sizes n_img=%d top_k=%d classes=%d",
+              n_img, top_k, num_classes);
+  ODK_REQUIRE(dets && gt_offsets && cm, ODK_ERR_INVALID_ARGUMENT, "confusion_matrix: null pointer");
+  ODK_REQUIRE(((uintptr_t)gt_boxes & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "confusion_matrix: gt_boxes must be 16-byte aligned");
+  ODK_REQUIRE(top_k <= 32767 && num_classes <= 32766, ODK_ERR_UNSUPPORTED, "confusion_matrix: top_k / num_classes exceed 16-bit indices");
+  const size_t smem = odk_align_up((size_t)top_k * 32, 16) * kScoreWarps;
+  ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "confusion_matrix: top_k=%d needs too much shared memory", top_k);
+  ODK_CUDA(cudaFuncSetAttribute(confusion_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  ODK_CUDA(cudaMemsetAsync(cm, 0, sizeof(int32_t) * (size_t)(num_classes + 1) * (num_classes + 1), stream));
+  CmArgs a;
+  a.n_img = n_img; a.top_k = top_k; a.num_classes = num_classes;
+  a.dets = dets; a.gt_boxes = reinterpret_cast<const float4*>(gt_boxes); a.gt_classes = gt_classes; a.gt_offsets = gt_offsets;
+  a.conf_thr = conf_thr; a.iou_thr = iou_thr; a.cm = cm;
+  {
+    OdkProfileScope prof_("confusion_kernel", stream);
+    confusion_kernel<<<(n_img + kScoreWarps - 1) / kScoreWarps, kScoreWarps * 32, smem, stream>>>(a);
+  }
+  ODK_LAUNCH_CHECK("confusion_kernel");
+  return ODK_OK;
+}

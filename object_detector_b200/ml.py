@@ -162,3 +162,27 @@ def search_conf_threshold(gt, pred, iou_threshold=0.5):
     if max_scores.any():
         return np.mean(conf_threshold_list[max_scores])
     return conf_threshold_list[scores.argmax()]
+
+
+def od_confusion_matrix(gt, pred, conf_threshold=0, iou_threshold=0.5, num_classes=None):
+    """ml.py:397-451 -> (C+1, C+1) int matrix (last row: false detections, last column: missed objects)."""
+    assert len(gt) == len(pred)
+    assert 0 < iou_threshold < 1
+    assert 0 <= conf_threshold < 1
+    if num_classes is None:
+        num_classes = np.max(np.concatenate([y.classes for y in gt])) + 1
+    num_classes = int(num_classes)
+    for y_true, y_pred in zip(gt, pred):
+        if y_true.num_objects > 0:
+            assert len(y_pred.bboxes) > 0  # ml.compute_iou (ml.py:507-508) refuses an empty detection set
+        assert all(0 <= c < num_classes for c in y_true.classes) and all(0 <= c < num_classes for c in y_pred.classes)
+    from . import voc
+    dev = _dev.device()
+    g = voc.pack_ground_truth(gt, dev)
+    dets = voc.pack_predictions(pred, dev)
+    cm = torch.empty((num_classes + 1, num_classes + 1), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call('odk_confusion_matrix', len(gt), dets.shape[1], num_classes, dets.data_ptr(), g['boxes'].data_ptr(),
+                  g['classes'].data_ptr(), g['offsets'].data_ptr(), float(conf_threshold), float(iou_threshold), cm.data_ptr(),
+                  _dev.stream_ptr(dev))
+    return cm.cpu().numpy().astype(int)

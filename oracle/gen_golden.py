@@ -172,6 +172,15 @@ def gen_scores():
         d[f'scores_{i}/conf_threshold'] = np.array(th)
         d[f'scores_{i}/precisions'], d[f'scores_{i}/recalls'], d[f'scores_{i}/fscores'], d[f'scores_{i}/supports'] = p, r, f, s
     d['search_conf_threshold'] = np.array(tk.ml.search_conf_threshold(y_true, y_pred, 0.5))
+    # ml.od_confusion_matrix (ml.py:397-451); the eval set has several detections per GT and class confusions
+    for i, th in enumerate([0.0, 0.25, 0.6]):
+        d[f'cm_{i}/conf_threshold'] = np.array(th)
+        d[f'cm_{i}/out'] = tk.ml.od_confusion_matrix(y_true, y_pred, th, 0.5, num_classes=5)
+    gts2, preds2 = synth.eval_set(78, 40, 3, max_gt=6, n_fp=12)
+    y_true2 = [Ann('.', w, h, c, b, dif) for (w, h, c, b, dif) in gts2]
+    y_pred2 = [tk.ml.ObjectsPrediction(c, s, b) for (c, s, b) in preds2]
+    d['cm_dense/seed'] = np.array([78, 40, 3, 6, 12])
+    d['cm_dense/out'] = tk.ml.od_confusion_matrix(y_true2, y_pred2, 0.1, 0.3, num_classes=3)
     np.savez_compressed(OUT / 'scores.npz', **d)
 
 

@@ -548,3 +548,49 @@ def od_losses(t: AnchorTables, y_true, y_pred):
     acc_clf = (acc_c * gt_obj).sum(axis=-1, dtype=f64) / np.maximum(gt_obj.sum(axis=-1, dtype=f64), 1)
     return {'loss_obj': loss_obj, 'loss_clf': loss_clf, 'loss_loc': loss_loc, 'loss': loss_obj + loss_clf + loss_loc,
             'rec_bg': rec_bg, 'rec_obj': rec_obj, 'acc_clf': acc_clf}
+
+
+# --------------------------------------------------------------------------------------
+def od_confusion_matrix(gt_list, pred_list, conf_threshold, iou_threshold, num_classes):
+    """ml.od_confusion_matrix (ml.py:397-451).  gt_list = [(classes, bboxes f32, ...)], pred_list = [(classes,
+    confs f32, bboxes f32)].  Returns the (C+1, C+1) int matrix: rows = truth (+ "nothing there"), columns =
+    prediction (+ "missed").  Every detection is attached to the GT of its largest IoU (:414, first maximum) if
+    that IoU reaches the threshold (:415).  NOTE the reference's indexing at :421,
+    ``confs.argsort()[::-1][m]``: the boolean mask ``m`` (one flag per detection) is applied to the POSITIONS
+    of the sorted index array, so the detections visited for a GT are ``order[j]`` for the positions j whose
+    own detection j passes the mask — reproduced as is, it decides the reference's numbers.  Tie policy of this
+    build for equal confidences: stable order reversed (the higher index first)."""
+    cm = np.zeros((num_classes + 1, num_classes + 1), dtype=int)
+    for g, (pc, ps, pb) in zip(gt_list, pred_list):
+        gc, gb = np.asarray(g[0]), np.asarray(g[1])
+        enabled = ps >= conf_threshold  # :410
+        if len(gc) > 0:
+            iou = pairwise_iou(gb, pb)  # asserts a non-empty detection set, like ml.compute_iou (:507-508)
+            pred_gt = iou.argmax(axis=0)
+            near = iou.max(axis=0) >= iou_threshold
+            order = stable_desc_order(ps)
+            for gt_ix, gt_class in enumerate(gc):
+                m = enabled & near & (pred_gt == gt_ix)  # :419-420
+                targets = order[m]                       # :421 (positional, see above)
+                found = False
+                for k in targets:  # :424-431
+                    if pc[k] == gt_class:
+                        if found:
+                            cm[-1, pc[k]] += 1
+                        else:
+                            found = True
+                            cm[gt_class, pc[k]] += 1
+                        enabled[k] = False
+                for k in targets:  # :433-442
+                    if enabled[k] and pc[k] != gt_class:
+                        if found:
+                            cm[-1, pc[k]] += 1
+                        else:
+                            found = True
+                            cm[gt_class, pc[k]] += 1
+                    enabled[k] = False
+                if not found:
+                    cm[gt_class, -1] += 1  # :443-444
+        for c in pc[enabled]:  # :446-447
+            cm[-1, c] += 1
+    return cm

@@ -228,6 +228,30 @@ def test_encode_truth_hook_coalesces_threads(prior_boxes):
     hook.coalescer.close()
 
 
+
+def test_confusion_matrix_golden_and_oracle(golden):
+    """ml.od_confusion_matrix (ml.py:397-451): golden matrices of the unmodified reference, then a VOC-sized set and
+    equal-confidence ties against the oracle; an image with ground truth but no detection raises like ml.compute_iou."""
+    g = golden['scores']
+    y_true, y_pred, _, _ = _score_objects(77, 60, 5, max_gt=5, n_fp=6)
+    for i in range(3):
+        cm = odk.ml.od_confusion_matrix(y_true, y_pred, float(g[f'cm_{i}/conf_threshold']), 0.5, num_classes=5)
+        assert cm.dtype == int and np.array_equal(cm, g[f'cm_{i}/out'])
+    y_true, y_pred, _, _ = _score_objects(78, 40, 3, max_gt=6, n_fp=12)
+    assert np.array_equal(odk.ml.od_confusion_matrix(y_true, y_pred, 0.1, 0.3, num_classes=3), g['cm_dense/out'])
+    y_true, y_pred, gt, pred = _score_objects(2007, 1500, 20)
+    for th, iou in ((0.0, 0.5), (0.31, 0.5), (0.2, 0.25)):
+        assert np.array_equal(odk.ml.od_confusion_matrix(y_true, y_pred, th, iou), R.od_confusion_matrix(gt, pred, th, iou, 20))
+    # quantised confidences -> many ties
+    y_true, y_pred, gt, pred = _score_objects(5, 200, 4, max_gt=6, n_fp=10)
+    pred = [(c, np.round(s * 8) / np.float32(8), b) for (c, s, b) in pred]
+    y_pred = [odk.ml.ObjectsPrediction(c, s, b) for (c, s, b) in pred]
+    assert np.array_equal(odk.ml.od_confusion_matrix(y_true, y_pred, 0.2, 0.4, 4), R.od_confusion_matrix(gt, pred, 0.2, 0.4, 4))
+    empty = odk.ml.ObjectsPrediction(np.zeros(0, np.int32), np.zeros(0, np.float32), np.zeros((0, 4), np.float32))
+    with pytest.raises(AssertionError):
+        odk.ml.od_confusion_matrix(y_true[:1], [empty], 0.0, 0.5, 4)
+
+
 # ----------------------------------------------------------------------------------------- strict_nms (SURVEY §8 f4)
 @pytest.mark.parametrize('name,batch,top_k,clustered', [('voc640', 3, 200, False), ('voc640', 2, 200, True),
                                                         ('voc320', 2, 20, True), ('tiny128', 4, 5, False),

@@ -249,3 +249,20 @@ def test_od_losses_closed_form_cases(oracle_tables):
     pred = rng.uniform(0.01, 0.99, size=y_true.shape).astype(np.float32)
     r3 = R.od_losses(t, y_true, pred)
     assert all(np.isfinite(v).all() for v in r3.values()) and r3['loss'][0] > 0
+
+
+def test_confusion_matrix_golden(golden):
+    """ml.od_confusion_matrix (ml.py:397-451) vs outputs of the unmodified reference, incl. its positional use of the
+    per-detection mask on the sorted index array (ml.py:421)."""
+    from object_detector_b200 import synth
+    g = golden['scores']
+    gts, preds = synth.eval_set(77, 60, 5, max_gt=5, n_fp=6)
+    gt = [(c, b, d) for (_, _, c, b, d) in gts]
+    for i in range(3):
+        th = float(g[f'cm_{i}/conf_threshold'])
+        cm = R.od_confusion_matrix(gt, preds, th, 0.5, 5)
+        assert np.array_equal(cm, g[f'cm_{i}/out'])
+        assert cm[:-1].sum() == sum(len(x[0]) for x in gt)  # every GT lands in exactly one cell of its row
+    gts, preds = synth.eval_set(78, 40, 3, max_gt=6, n_fp=12)
+    gt = [(c, b, d) for (_, _, c, b, d) in gts]
+    assert np.array_equal(R.od_confusion_matrix(gt, preds, 0.1, 0.3, 3), g['cm_dense/out'])
