@@ -36,10 +36,24 @@ def main(rep, out):
     hdr, units, body = rows[0], rows[1], rows[2:]
     lines = [f'# ncu --set full summary of {rep}', '']
     names = []
+    traffic = {}
+
+    def to_bytes(v, unit):
+        return float(v) * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}.get(unit, 1)
+
     for r in body:
         name = r[hdr.index('Kernel Name')].split('(')[0].replace('<unnamed>::', '').replace('void ', '')
         names.append(name)
         lines.append(name)
+        try:
+            ir, iw, it = hdr.index('dram__bytes_read.sum'), hdr.index('dram__bytes_write.sum'), hdr.index('gpu__time_duration.sum')
+            t = traffic.setdefault(name, {'launches': 0, 'dram_read_bytes': 0.0, 'dram_write_bytes': 0.0, 'duration_us': 0.0})
+            t['launches'] += 1
+            t['dram_read_bytes'] += to_bytes(r[ir], units[ir])
+            t['dram_write_bytes'] += to_bytes(r[iw], units[iw])
+            t['duration_us'] += float(r[it]) * {'ns': 1e-3, 'us': 1, 'ms': 1e3}.get(units[it], 1)
+        except ValueError:
+            pass
         for key, label in RAW:
             if key in hdr:
                 i = hdr.index(key)
@@ -73,6 +87,13 @@ def main(rep, out):
         lines.append('')
     open(out, 'w').write('\n'.join(lines) + '\n')
     print('wrote', out)
+    if len(sys.argv) > 3:  # per-launch averages, read by bench.py for roofline.traffic
+        import json
+        for t in traffic.values():
+            for k in ('dram_read_bytes', 'dram_write_bytes', 'duration_us'):
+                t[k] /= t['launches']
+        json.dump({'source': rep, 'kernels': traffic}, open(sys.argv[3], 'w'), indent=1)
+        print('wrote', sys.argv[3])
 
 
 if __name__ == '__main__':

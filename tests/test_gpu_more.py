@@ -362,3 +362,32 @@ def test_loss_full_batch_properties(prior_boxes):
     f = pb.assign_loss_batch(gtb, gtc, gtn, y_pred)['terms']
     assert torch.allclose(f[ok], a[ok], rtol=1e-9, atol=1e-12)
     assert bool(torch.isfinite(a).all()) and bool((a[:, 0] > 0).all())
+
+
+# ----------------------------------------------------------------------------------------- BASELINE config 5 (dense-anchor stress)
+def test_stress_config5_predict_side(prior_boxes, oracle_tables):
+    """200k anchors x 80 classes, NMS IoU 0.45, top-k 200: two images against the oracle (kept anchors and rows
+    bit-exact, candidate lists beyond the shared-memory key cache), then B=8 through size-independent properties."""
+    pb, t = prior_boxes('stress1120'), oracle_tables('stress1120')
+    n, c = len(pb), 80
+    assert n == 205800
+    objs, clfs, locs = synth.predictions(55, 2, n, c)
+    out, kept = pb.decode_nms(objs, clfs, locs, return_index=True)
+    ro, rk = R.predict_tail(t, objs, clfs, locs)
+    assert np.array_equal(kept.cpu().numpy(), rk) and np.array_equal(out.cpu().numpy(), ro)
+    so, sk = pb.decode_nms(objs, clfs, locs, nms_all_threshold=0.5, return_index=True)
+    ro2, rk2 = R.predict_tail(t, objs, clfs, locs, nms_all_threshold=0.5)
+    assert np.array_equal(sk.cpu().numpy(), rk2) and np.array_equal(so.cpu().numpy(), ro2)
+    objs, clfs, locs = (torch.from_numpy(x).cuda() for x in synth.predictions(56, 8, n, c))
+    out, kept = pb.decode_nms(objs, clfs, locs, return_index=True)
+    classes, confs, boxes = pb.decode_score(objs, clfs, locs)
+    out2, kept2 = odk.layers.nms()(c, n)([classes, confs, boxes], return_index=True)
+    assert torch.equal(out, out2) and torch.equal(kept, kept2)            # fused == dense decode + layer
+    conf = out[:, :, 1]
+    assert bool((conf[:, 1:] <= conf[:, :-1]).all()) and bool((kept >= 0).all())  # sorted, 200 kept everywhere
+    for b in range(8):
+        k = kept[b].long()
+        assert k.unique().numel() == 200
+        assert torch.equal(confs[b][k], conf[b]) and torch.equal(classes[b][k].float(), out[b, :, 0])
+        assert torch.equal(boxes[b][k], out[b, :, 2:])
+    assert torch.equal(pb.decode_nms(objs, clfs, locs), out)               # deterministic
