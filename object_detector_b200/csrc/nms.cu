@@ -276,7 +276,11 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     //         remaining keys differ (fp32 scores share their leading exponent bits) -------------------------
     unsigned long long lo_key = 0ull;
     const int need = STRICT ? p.top_k - nkept2 : limit - nkept;
-    const int want = min(kBand, need + (need >> 2) + 32);  // band size aimed at: 1.25x what is still needed
+    // band size aimed at: 1.25x what is still needed; after its first round strict mode scales that by the survival
+    // ratio of the all-class pass seen so far
+    int want = need + (need >> 2) + 32;
+    if (STRICT && nkept2 > 0) want = (int)min((long long)kBand, (long long)need * processed / nkept2 * 5 / 4 + 32);
+    want = min(kBand, want);
     if (remaining > kBand) {
       unsigned long long kmin = ~0ull, kmax = 0ull;
       for (int i = tid; i < total; i += kNmsThreads) {
@@ -524,47 +528,62 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
         s_alive[tid] = dead2 ? 0 : 1;
       }
       __syncthreads();
-      if (warp == 0) {
-        unsigned short* mem = s_member;  // this round's final keeps (band slots, global order)
-        int rk = 0;
-        const int room = p.top_k - nkept2;
-        for (int mb = 0; mb < nk1 && rk < room; mb += 32) {
-          const bool have = mb + lane < nk1;
-          const int i = have ? s_clslist[mb + lane] : 0;
-          const float4 box = have ? s_box[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-          const float area = have ? s_area[i] : 0.f;
-          const float a_hi = area * p.ft2.k_hi, a_lo = area * p.ft2.k_lo;
-          bool dead = false;
-          for (int e = 0; e < rk; ++e) {
-            const int ie = mem[e];
-            dead |= pair_hit<GE>(box, area, a_hi, a_lo, s_box[ie], s_area[ie], p.iou_thr2, p.ft2, fast2);
+      // in-band greedy order, bitmask form: every thread fills words of the suppression matrix M[i][w] (bit j of word
+      // w: survivor 32w+j, later than i, is suppressed by survivor i), then one warp resolves the order serially with
+      // a 512-bit "removed" set spread over its lanes — one shared-memory row OR per kept box.
+      const int nw = (nk1 + 31) >> 5;
+      unsigned* M = reinterpret_cast<unsigned*>(s_member);                  // [nk1][nw] <= 512 x 16 words = 32 KB
+      unsigned short* rlist = reinterpret_cast<unsigned short*>(s_x);       // this round's final keeps (band slots)
+      // a warp owns row i; its lanes test the 32 survivors of one word at a time and the ballot IS the word
+      for (int i = warp; i < nk1; i += kNmsWarps) {
+        const int si = s_clslist[i];
+        const bool row_alive = s_alive[si] != 0;
+        const float4 bi = s_box[si];
+        const float ai = s_area[si];
+        for (int w = i >> 5; w < nw; ++w) {
+          const int j = w * 32 + lane;
+          bool hit = false;
+          if (row_alive && j > i && j < nk1) {
+            const int sj = s_clslist[j];
+            const float aj = s_area[sj];
+            hit = pair_hit<GE>(s_box[sj], aj, aj * p.ft2.k_hi, aj * p.ft2.k_lo, bi, ai, p.iou_thr2, p.ft2, fast2);
           }
-          const bool alive = have && s_alive[i] && !dead;
-          unsigned keep = 0;
-          for (unsigned rem = __ballot_sync(0xffffffffu, alive); rem;) {
-            if (rk + __popc(keep) >= room) break;
+          const unsigned bits = __ballot_sync(0xffffffffu, hit);
+          if (lane == 0) M[i * nw + w] = bits;
+        }
+      }
+      __syncthreads();
+      if (warp == 0) {
+        // serial resolve, 32 survivors at a time: the block's own order needs only the diagonal words (registers +
+        // shuffles); the rows of the boxes it keeps are then OR-ed into the later words of `removed` in one go
+        const int room = p.top_k - nkept2;
+        unsigned removed = 0u;  // lane l: removed flags of survivors 32l .. 32l+31
+        int rk = 0;
+        for (int w = 0; w < nw && rk < room; ++w) {
+          const int j = w * 32 + lane;
+          const bool in = j < nk1;
+          const unsigned alive = __ballot_sync(0xffffffffu, in && s_alive[s_clslist[in ? j : 0]]);
+          const unsigned diag = in ? M[j * nw + w] : 0u;
+          unsigned rem = alive & ~__shfl_sync(0xffffffffu, removed, w);
+          unsigned keep = 0u;
+          while (rem) {
             const int l = __ffs(rem) - 1;
             keep |= 1u << l;
-            rem &= rem - 1;
-            float4 bl;
-            bl.x = __shfl_sync(0xffffffffu, box.x, l);
-            bl.y = __shfl_sync(0xffffffffu, box.y, l);
-            bl.z = __shfl_sync(0xffffffffu, box.z, l);
-            bl.w = __shfl_sync(0xffffffffu, box.w, l);
-            const float al = __shfl_sync(0xffffffffu, area, l);
-            const bool hit = ((rem >> lane) & 1u) && pair_hit<GE>(box, area, a_hi, a_lo, bl, al, p.iou_thr2, p.ft2, fast2);
-            rem &= ~__ballot_sync(0xffffffffu, hit);
+            rem &= ~(__shfl_sync(0xffffffffu, diag, l) | (1u << l));
           }
-          if ((keep >> lane) & 1u) mem[rk + __popc(keep & ((1u << lane) - 1u))] = (unsigned short)i;
-          rk += __popc(keep);
-          __syncwarp();
+          const int take = min(__popc(keep), room - rk);
+          if (take < __popc(keep)) keep &= (1u << (__fns(keep, 0, take + 1) & 31)) - 1u;  // cut at top_k: drop from the (take+1)-th on
+          if ((keep >> lane) & 1u) rlist[rk + __popc(keep & ((1u << lane) - 1u))] = s_clslist[j];
+          rk += take;
+          if (lane > w && lane < nw)
+            for (unsigned kk = keep; kk; kk &= kk - 1) removed |= M[(w * 32 + __ffs(kk) - 1) * nw + lane];
         }
         if (lane == 0) s_nb = rk;
       }
       __syncthreads();
       const int rk = s_nb;
       if (tid < rk) {
-        const int i = s_member[tid];
+        const int i = reinterpret_cast<const unsigned short*>(s_x)[tid];
         const unsigned long long key = s_band[i];
         const float4 bx = s_box[i];
         const int r = nkept2 + tid;

@@ -391,3 +391,43 @@ def test_stress_config5_predict_side(prior_boxes, oracle_tables):
         assert torch.equal(confs[b][k], conf[b]) and torch.equal(classes[b][k].float(), out[b, :, 0])
         assert torch.equal(boxes[b][k], out[b, :, 2:])
     assert torch.equal(pb.decode_nms(objs, clfs, locs), out)               # deterministic
+
+
+# ----------------------------------------------------------------------------------------- empty and ragged inputs
+def test_empty_and_ragged_inputs(prior_boxes, oracle_tables):
+    """No ground truth, no candidate above the confidence threshold, an empty box set, one-element sets, a batch mixing
+    G = 0 / 1 / Gmax: the reference's results for the degenerate shapes (od_pb.py:306 weight 1/max(1,0); layers.py:969
+    all-zero rows; ml.py:589-625 on empty / single inputs)."""
+    pb, t = prior_boxes('voc320'), oracle_tables('voc320')
+    n = len(pb)
+    # train side: ragged counts incl. zero
+    gtb, gtc, gtn = synth.gt_batch(3, 5, 16, 20, crowded_every=0, fixed_g=16)
+    gtn[:] = [0, 1, 16, 0, 7]
+    res = pb.encode_truth_batch(gtb, gtc, gtn, want_valids=True)
+    ref = R.encode_truth(t, [(gtc[i, :gtn[i]], gtb[i, :gtn[i]]) for i in range(5)])
+    assert (res['status'].cpu().numpy() == 0).all() and np.array_equal(res['y_true'].cpu().numpy(), ref)
+    y0 = res['y_true'][0].cpu().numpy()
+    assert (y0[:, 0] == 1).all() and (y0[:, 1:] == 0).all() and bool(res['pb_valids'][0].all())  # G = 0: everything valid, weight 1
+    assert (res['pb_indices'][0] == -1).all() and (res['pb_indices'][1, 1:] == -1).all()
+    idx, gts, valid = pb._assign_boxes(np.zeros((0, 4), np.float32))
+    assert idx.shape == (0,) and gts.shape == (0,) and valid.all() and idx.dtype == np.int64
+    assert pb.encode_truth([]).shape == (0, n, 27)
+    # predict side: nothing above the threshold
+    objs, clfs, locs = synth.predictions(8, 2, n, 20)
+    objs[:] = 0.001
+    out, kept = pb.decode_nms(objs, clfs, locs, return_index=True)
+    assert bool((out == 0).all()) and bool((kept == -1).all())
+    so = pb.decode_nms(objs, clfs, locs, nms_all_threshold=0.5)
+    assert bool((so == 0).all())
+    # exactly one candidate in one image
+    objs[1, 777, 0] = 0.9
+    out, kept = pb.decode_nms(objs, clfs, locs, return_index=True)
+    ro, rk = R.predict_tail(t, objs, clfs, locs)
+    assert np.array_equal(out.cpu().numpy(), ro) and np.array_equal(kept.cpu().numpy(), rk) and int((rk >= 0).sum()) in (0, 1)
+    # NumPy NMS mirror on empty / single / all-degenerate sets
+    assert odk.ml.non_maximum_suppression(np.zeros((0, 4), np.float32), np.zeros(0, np.float32)).shape == (0,)
+    one = np.array([[0.1, 0.1, 0.4, 0.5]], np.float32)
+    assert odk.ml.non_maximum_suppression(one, np.array([0.3], np.float32)).tolist() == [0]
+    flat = np.array([[0.1, 0.1, 0.1, 0.5], [0.2, 0.3, 0.6, 0.3]], np.float32)  # zero width / zero height: skipped (ml.py:610)
+    assert odk.ml.non_maximum_suppression(flat, np.array([0.3, 0.2], np.float32)).shape == (0,)
+    assert R.numpy_nms(flat, np.array([0.3, 0.2], np.float32)).shape == (0,)
