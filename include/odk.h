@@ -203,6 +203,11 @@ int odk_confusion_matrix(int n_img, int top_k, int num_classes, const float* det
                          const int32_t* gt_offsets /*[dev n_img+1]*/, float conf_thr, float iou_thr,
                          int32_t* cm /*[dev (C+1)*(C+1)]*/, void* stream);
 
+/* Diagnostics: in-kernel timeline of the six kernels of a step (candidates, greedy, rows, patch, emit, nms).
+ * buf = 12 device words, word 2*id = earliest CTA entry (initialise to UINT64_MAX), word 2*id+1 = latest CTA exit
+ * (initialise to 0), in %globaltimer nanoseconds; NULL switches it off.  Works inside CUDA-graph replays. */
+int odk_timeline_set(unsigned long long* buf /*[dev 12] or NULL*/);
+
 /* Measurement aid (bench.py): when enabled for the calling host thread every kernel launch of the
  * library is bracketed by CUDA events on its stream; odk_profile_read synchronises them and returns,
  * per kernel name, the summed device time and the launch count, then clears the log. */

@@ -105,6 +105,7 @@ __device__ __forceinline__ bool cand_less(double c0, int a0, double c1, int a1) 
 constexpr int kCandThreads = 128;
 constexpr int kCandWarps = kCandThreads / 32;
 __global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(const AssignArgs p) {
+  OdkTimeline tl_(ODK_TL_CANDIDATES);
   __shared__ double s_cost[kCandWarps * kScratch];
   __shared__ int s_idx[kCandWarps * kScratch];
   const int warp = threadIdx.x >> 5;
@@ -240,6 +241,7 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(cons
 
 // Phase B: the sequential greedy walk, one CTA per image.
 __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const AssignArgs p) {
+  OdkTimeline tl_(ODK_TL_GREEDY);
   extern __shared__ __align__(16) unsigned char greedy_smem[];
   const int warp = threadIdx.x >> 5;
   const int lane = (int)odk_lane();
@@ -502,7 +504,7 @@ int odk_launch_assign_candidates(const odk_anchors* a, int batch, const float* g
   const long long tasks = (long long)batch * gmax;
   {
     OdkProfileScope prof_("assign_candidates_kernel", stream);
-    assign_candidates_kernel<<<(unsigned)((tasks + kCandWarps - 1) / kCandWarps), kCandThreads, 0, stream>>>(args);
+    odk_launch_high(assign_candidates_kernel, dim3((unsigned)((tasks + kCandWarps - 1) / kCandWarps)), dim3(kCandThreads), 0, stream, args);
   }
   ODK_LAUNCH_CHECK("assign_candidates_kernel");
   return ODK_OK;
@@ -517,7 +519,7 @@ int odk_launch_assign_greedy(const odk_anchors* a, int batch, const float* gt_bo
   ODK_CUDA(cudaFuncSetAttribute(assign_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   {
     OdkProfileScope prof_("assign_greedy_kernel", stream);
-    assign_greedy_kernel<<<batch, kGreedyThreads, smem, stream>>>(args);
+    odk_launch_high(assign_greedy_kernel, dim3(batch), dim3(kGreedyThreads), smem, stream, args);
   }
   ODK_LAUNCH_CHECK("assign_greedy_kernel");
   return ODK_OK;
@@ -586,3 +588,5 @@ extern "C" int odk_encode_locs(const odk_anchors* a, int k, const float* boxes, 
   ODK_LAUNCH_CHECK("encode_locs_kernel");
   return ODK_OK;
 }
+
+ODK_TIMELINE_SETTER(odk_timeline_set_assign)

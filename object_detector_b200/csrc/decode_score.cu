@@ -55,6 +55,7 @@ struct StageLayout {
 
 template <int TILE, bool DENSE>
 __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) {
+  OdkTimeline tl_(ODK_TL_EMIT);
   using L = StageLayout<TILE, DENSE>;
   const int kStages = p.stages;
   constexpr int kWarps = TILE / 32;
@@ -312,3 +313,5 @@ int odk_launch_decode_locs(const odk_anchors* a, long long rows, const float* pr
   ODK_LAUNCH_CHECK("decode_locs_kernel");
   return ODK_OK;
 }
+
+ODK_TIMELINE_SETTER(odk_timeline_set_decode)

@@ -50,6 +50,7 @@ constexpr int kRowsPerThread = 8;  // 16-byte stores per thread
 // others by adding the constant step; the bitmap words of all pieces are loaded before the first store.
 template <int VEC>
 __global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeArgs p, unsigned step_rows, unsigned step_cols) {
+  OdkTimeline tl_(ODK_TL_ROWS);
   const int b = blockIdx.y;
   const unsigned W = 3 + p.av.num_classes + 4;
   const unsigned n = (unsigned)p.av.n;
@@ -117,6 +118,7 @@ struct PatchArgs {
 
 // One CTA per image: the positives (od_pb.py:307-311), or an all-zero image when the assignment failed.
 __global__ void __launch_bounds__(128) encode_patch_kernel(const PatchArgs p) {
+  OdkTimeline tl_(ODK_TL_PATCH);
   const int b = blockIdx.x;
   const int C = p.av.num_classes;
   const int W = 3 + C + 4;
@@ -252,8 +254,10 @@ extern "C" int odk_assign_encode(const odk_anchors* a, int batch, const float* g
   q.status = status; q.y_true = y_true; q.pb_valids = pb_valids;
   {
     OdkProfileScope prof_("encode_patch_kernel", stream);
-    encode_patch_kernel<<<batch, 128, 0, stream>>>(q);
+    odk_launch_high(encode_patch_kernel, dim3(batch), dim3(128), 0, stream, q);
   }
   ODK_LAUNCH_CHECK("encode_patch_kernel");
   return ODK_OK;
 }
+
+ODK_TIMELINE_SETTER(odk_timeline_set_rows)

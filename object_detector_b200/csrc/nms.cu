@@ -182,6 +182,7 @@ __device__ __forceinline__ unsigned long long block_sort_desc_1(unsigned long lo
 
 template <bool GE, bool STRICT>
 __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs p) {
+  OdkTimeline tl_(ODK_TL_NMS);
   static_assert(kBand <= kNmsThreads && ODK_MAX_CLASSES / 32 <= kNmsThreads, "one band slot / class word per thread");
   extern __shared__ __align__(16) unsigned char nms_smem[];
   __shared__ int s_hist[kBins];
@@ -692,7 +693,7 @@ static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch,
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 180 * 1024));
   {
     OdkProfileScope prof_(strict ? "nms_image_kernel_strict" : "nms_image_kernel", stream);
-    kern<<<batch, kNmsThreads, smem, stream>>>(a);
+    odk_launch_high(kern, dim3(batch), dim3(kNmsThreads), smem, stream, a);
   }
   ODK_LAUNCH_CHECK("nms_image_kernel");
   return ODK_OK;
@@ -804,3 +805,5 @@ extern "C" int odk_nms(const float* boxes, const float* scores, int n, int top_k
   return nms_run(w, nullptr, 1, n, kCollectPiece, reinterpret_cast<const float4*>(boxes), nullptr, iou_thr, 0, limit, iou_ge, nullptr, nullptr,
                  out_index, out_count, stream);
 }
+
+ODK_TIMELINE_SETTER(odk_timeline_set_nms)

@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/odk.h"
 
@@ -167,6 +168,56 @@ __device__ __forceinline__ float4 odk_decode_box(const float4 pr, const float4 l
   box.w = fminf(fmaxf(__fadd_rn(__fmul_rn(pr.w, sc.y), lc.w), 0.0f), 1.0f);
   return box;
 }
+
+// ---- priority launches ------------------------------------------------------------------------------------------
+// The step mixes HBM-streaming kernels with large grids (encode_rows, score_emit) and short latency-bound kernels of
+// 64..1024 small CTAs (candidates, greedy walk, patch, NMS).  Launched at equal priority, the CTAs of a latency-bound
+// kernel queue behind every not-yet-dispatched CTA of a streaming kernel that was issued earlier, so "concurrent"
+// branches serialise.  The latency-bound kernels are therefore launched with the highest kernel priority
+// (cudaLaunchAttributePriority; honoured for stream launches and captured into graph kernel nodes).
+inline int odk_high_priority() {
+  static int greatest = 1;
+  if (greatest == 1) {
+    int least = 0, g = 0;
+    if (cudaDeviceGetStreamPriorityRange(&least, &g) != cudaSuccess) g = 0;
+    greatest = g;
+  }
+  return greatest;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t odk_launch_high(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  static const bool off = getenv("ODK_NO_PRIORITY") != nullptr;  // diagnostics
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributePriority;
+  attr[0].val.priority = odk_high_priority();
+  cfg.attrs = attr;
+  cfg.numAttrs = off ? 0 : 1;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
+// ---- optional in-kernel timeline (odk_timeline_set; diagnostics for overlapping launches inside a CUDA graph) --------
+// When a buffer is installed, thread 0 of every CTA of an instrumented kernel records %globaltimer (ns) at entry
+// (atomicMin into slot 2*id) and at exit (atomicMax into slot 2*id+1).  One copy of the pointer per translation unit.
+static __device__ unsigned long long* odk_tl_buf = nullptr;
+#define ODK_TIMELINE_SETTER(fn) \
+  int fn(unsigned long long* buf) { ODK_CUDA(cudaMemcpyToSymbol(odk_tl_buf, &buf, sizeof(buf))); return ODK_OK; }
+struct OdkTimeline {
+  int id_;
+  __device__ __forceinline__ static unsigned long long now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+  }
+  __device__ __forceinline__ explicit OdkTimeline(int id) : id_(id) {
+    if (threadIdx.x == 0 && odk_tl_buf != nullptr) atomicMin(odk_tl_buf + 2 * id_, now());
+  }
+  __device__ __forceinline__ ~OdkTimeline() {
+    if (threadIdx.x == 0 && odk_tl_buf != nullptr) atomicMax(odk_tl_buf + 2 * id_ + 1, now());
+  }
+};
+enum { ODK_TL_CANDIDATES = 0, ODK_TL_GREEDY = 1, ODK_TL_ROWS = 2, ODK_TL_PATCH = 3, ODK_TL_EMIT = 4, ODK_TL_NMS = 5 };
 
 // ---- warp helpers ------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned odk_lane() { return threadIdx.x & 31u; }

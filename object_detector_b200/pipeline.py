@@ -17,9 +17,10 @@ from . import _dev
 def capture_step(pb, gt, head, y_true, dets, top_k=200, conf_threshold=0.01, nms_threshold=0.45, two_streams=True):
     """Captures ``encode_truth_batch(*gt, y_true=y_true)`` and ``decode_nms(*head, out=dets)`` into one CUDA
     graph (parallel branches when ``two_streams``).  All tensors must be CUDA tensors that stay alive and
-    keep their addresses; replay with ``graph.replay()`` on any stream.  The first call for a PriorBoxes
-    must happen after its tables were uploaded (call either method once eagerly before capturing)."""
+    keep their addresses; replay with ``graph.replay()`` on any stream."""
     dev = y_true.device
+    with torch.cuda.device(dev):
+        pb._handle(dev)  # the anchor tables are uploaded (cudaMalloc) on first use: not allowed while capturing
     side = torch.cuda.Stream(device=dev) if two_streams else None
     graph = torch.cuda.CUDAGraph()
     with torch.cuda.device(dev), torch.cuda.graph(graph):
