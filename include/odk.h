@@ -85,6 +85,12 @@ int odk_assign(const odk_anchors* a, int batch, const float* gt_boxes /*[dev B,G
                int32_t* status /*[dev B]*/, void* workspace /*[dev]*/, size_t workspace_bytes,
                void* stream);
 
+/* PriorBoxes.check_prior_boxes (od_pb.py:224-297), device part: for k assigned (GT box, anchor) pairs the initial
+ * offsets encode_locs(box, ix) (fp64, :243) and the fp32 IoU of the box with its anchor (:252). */
+int odk_assignment_quality(const odk_anchors* a, int k, const float* boxes /*[dev k,4]*/,
+                           const int32_t* ix /*[dev k]*/, double* delta /*[dev k,4]*/,
+                           float* iou /*[dev k]*/, void* stream);
+
 /* PriorBoxes.encode_truth (od_pb.py:299-313) = odk_assign + the y_true writer.
  * y_true[b, n, :] = [mask, weight, obj, onehot(C), locs(4)] fp32, written in full (no pre-zeroing
  * needed).  pb_valids (optional, may be NULL) receives _assign_boxes' third result. */

@@ -27,6 +27,7 @@ SIGNATURES = {
     'odk_assign_workspace_bytes': (c_size_t, [c_void_p, c_int, c_int]),
     'odk_assign': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                            c_void_p]),
+    'odk_assignment_quality': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     'odk_assign_encode': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_loss_workspace_bytes': (c_size_t, [c_void_p, c_int]),

@@ -336,6 +336,109 @@ class PriorBoxes:
         return (res['pb_indices'][0, :g].cpu().numpy(), res['gt_indices'][0, :g].cpu().numpy(),
                 res['pb_valids'][0].cpu().numpy())
 
+    def assign_batch(self, gt_boxes, gt_count):
+        """``_assign_boxes`` for a padded batch without building y_true (``odk_assign``): -> ``pb_indices``,
+        ``gt_indices`` (B,Gmax) i64 (-1 padded) and ``status`` (B,) i32 CUDA tensors."""
+        dev = _dev.device(gt_boxes.device if isinstance(gt_boxes, torch.Tensor) and gt_boxes.is_cuda else None)
+        boxes = _dev.to_device(gt_boxes, torch.float32, dev)
+        count = _dev.to_device(gt_count, torch.int32, dev)
+        b, gmax = boxes.shape[0], boxes.shape[1]
+        assert boxes.shape == (b, gmax, 4) and count.shape == (b,)
+        pb_idx = torch.empty((b, gmax), dtype=torch.int64, device=dev)
+        gt_idx = torch.empty((b, gmax), dtype=torch.int64, device=dev)
+        status = torch.empty((b,), dtype=torch.int32, device=dev)
+        ws_bytes = _lib.load().odk_assign_workspace_bytes(self._handle(dev), b, gmax)
+        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _lib.call('odk_assign', self._handle(dev), b, boxes.data_ptr(), count.data_ptr(), gmax, pb_idx.data_ptr(),
+                      gt_idx.data_ptr(), status.data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
+        return {'pb_indices': pb_idx, 'gt_indices': gt_idx, 'status': status}
+
+    def check_prior_boxes(self, y_test, batch=256, print_fn=None):
+        """od_pb.py:224-297: how well the prior boxes fit a dataset.  The whole dataset is assigned in batches
+        (``odk_assign``), the initial offsets and GT-anchor IoUs of all assigned pairs come from one more launch
+        (``odk_assignment_quality``); the statistics and the log lines are then formed on the host exactly as the
+        reference prints them.  Logs through ``logging`` (or ``print_fn``) and also returns the numbers."""
+        import logging
+        from . import textstats
+        emit = print_fn or logging.getLogger(__name__).info
+        dev = _dev.device()
+        for y in y_test:
+            for class_id in y.classes:
+                assert 0 <= class_id < self.num_classes  # od_pb.py:246
+        total_gt_boxes = sum([np.sum(np.logical_not(y.difficults)) for y in y_test])
+        pair_boxes, pair_pb, pair_img, pair_gt, assigned_count_list = [], [], [], [], []
+        for s0 in range(0, len(y_test), batch):
+            chunk = y_test[s0:s0 + batch]
+            boxes, _, counts = self._pad_gt(chunk)
+            res = self.assign_batch(boxes, counts)
+            self._raise_for_status(res['status'].cpu().numpy(), chunk)
+            pb_idx, gt_idx = res['pb_indices'].cpu().numpy(), res['gt_indices'].cpu().numpy()
+            for i, g in enumerate(counts):
+                assigned_count_list.append(int(g))  # one prior box per GT (od_pb.py:239)
+                pair_pb.append(pb_idx[i, :g])
+                pair_gt.append(gt_idx[i, :g])
+                pair_img.append(np.full(g, s0 + i, dtype=np.int64))
+                pair_boxes.append(boxes[i][gt_idx[i, :g]])
+        pair_pb = np.concatenate(pair_pb) if pair_pb else np.zeros(0, np.int64)
+        pair_gt = np.concatenate(pair_gt) if pair_gt else np.zeros(0, np.int64)
+        pair_img = np.concatenate(pair_img) if pair_img else np.zeros(0, np.int64)
+        pair_boxes = np.concatenate(pair_boxes).astype(np.float32) if pair_boxes else np.zeros((0, 4), np.float32)
+        k = len(pair_pb)
+        delta = torch.empty((k, 4), dtype=torch.float64, device=dev)
+        iou = torch.empty((k,), dtype=torch.float32, device=dev)
+        if k:
+            d_boxes = _dev.to_device(pair_boxes, torch.float32, dev)
+            d_ix = _dev.to_device(pair_pb.astype(np.int32), torch.int32, dev)
+            with torch.cuda.device(dev):
+                _lib.call('odk_assignment_quality', self._handle(dev), k, d_boxes.data_ptr(), d_ix.data_ptr(), delta.data_ptr(),
+                          iou.data_ptr(), _dev.stream_ptr(dev))
+        delta, iou = delta.cpu().numpy(), iou.cpu().numpy()
+        # per object (od_pb.py:245-267): every GT owns exactly one prior box, so the "not assigned" branch stays empty
+        assigned_counts = np.zeros((len(self.pb_info),))
+        y_true, y_pred, iou_list = [], [], []
+        total_errors = 0
+        slot_of = {(int(i), int(g)): j for j, (i, g) in enumerate(zip(pair_img, pair_gt))}
+        for img, y in enumerate(y_test):
+            for gt_ix, (class_id, difficult) in enumerate(zip(y.classes, y.difficults)):
+                if difficult:
+                    continue
+                j = slot_of.get((img, gt_ix))
+                if j is not None:
+                    max_iou = iou[j]
+                    assigned_counts[self.pb_info_indices[pair_pb[j]]] += 1
+                else:
+                    max_iou = 0
+                    total_errors += 1
+                y_true.append(class_id)
+                y_pred.append(class_id if max_iou >= 0.5 else None)
+                iou_list.append(max_iou)
+        lines = ['assigned counts:']
+        for i, c in enumerate(assigned_counts):
+            lines.append('  prior boxes{m=%d, size=%.2f ar=%.2f} = %d (%.02f%%)' % (
+                self.pb_info[i]['map_size'], self.pb_info[i]['size'], self.pb_info[i]['aspect_ratio'], c,
+                100 * c / self.pb_info[i]['count'] / total_gt_boxes))
+        lines.append('recall (prior box iou >= 0.5):')
+        y_true, y_pred = np.array(y_true), np.array(y_pred)
+        recall = {}
+        with np.errstate(invalid='ignore', divide='ignore'):
+            for class_id in range(self.num_classes):
+                y_mask = y_true == class_id
+                class_ok, class_all = (y_pred[y_mask] == class_id).sum(), y_mask.sum()
+                recall[class_id] = (int(class_ok), int(class_all))
+                lines.append(f'  class{class_id:02d} : {class_ok:5d} / {class_all:5d} = {100 * class_ok / class_all:5.1f}%')
+        lines.append('total errors: %d / %d (%.02f%%)' % (total_errors, total_gt_boxes, 100 * total_errors / total_gt_boxes))
+        lines.append('Avg IOU: %.1f' % (np.mean(iou_list) * 100))
+        lines.extend(textstats.histogram_lines(assigned_count_list, title='assigned_count'))
+        lines.append('assigned count per image: median=%d min=%d max=%d' % (
+            np.median(assigned_count_list), min(assigned_count_list), max(assigned_count_list)))
+        lines.extend(textstats.histogram_lines([np.mean(np.abs(dl)) for dl in delta], title='mean_abs_delta'))
+        lines.append('delta loc: mean=%.2f std=%.2f min=%.2f max=%.2f' % (delta.mean(), delta.std(), delta.min(), delta.max()))
+        for line in lines:
+            emit(line)
+        return {'lines': lines, 'assigned_counts': assigned_counts, 'recall': recall, 'total_errors': total_errors,
+                'iou': np.asarray(iou_list), 'delta_locs': delta, 'assigned_count_per_image': assigned_count_list}
+
     # ------------------------------------------------------------------ prediction side (od_net.py:172-192)
     def _head_inputs(self, objs, clfs, locs):
         dev = _dev.device(objs.device if isinstance(objs, torch.Tensor) and objs.is_cuda else None)

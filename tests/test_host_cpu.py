@@ -133,3 +133,17 @@ def test_batch_coalescer_groups_concurrent_calls():
         co(-1)
     assert co(3) == 9  # still alive after an error
     co.close()
+
+
+def test_text_histogram_lines_match_golden_log():
+    """textstats.histogram_lines reproduces the histogram blocks the reference logged (math.py:26-78) — checked on
+    the 'assigned_count' block of tests/golden/check_prior_boxes.txt, whose samples are the GT counts per image."""
+    import pathlib
+    from object_detector_b200 import synth, textstats
+    want = (pathlib.Path(__file__).parent / 'golden' / 'check_prior_boxes.txt').read_text(encoding='utf-8').splitlines()
+    start = next(i for i, line in enumerate(want) if 'assigned_count' in line and line.startswith('-'))
+    gts, _ = synth.eval_set(11, 40, 20, max_gt=6)
+    counts = [len(g[2]) for g in gts]
+    assert textstats.histogram_lines(counts, title='assigned_count') == want[start:start + 13]
+    assert textstats.number_column(np.array([1, 20, 300])) == ['  1', ' 20', '300']
+    assert textstats.number_column(np.array([-0.5, 0.25])) == ['-0.500', ' 0.250']
