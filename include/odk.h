@@ -209,6 +209,14 @@ int odk_confusion_matrix(int n_img, int top_k, int num_classes, const float* det
                          const int32_t* gt_offsets /*[dev n_img+1]*/, float conf_thr, float iou_thr,
                          int32_t* cm /*[dev (C+1)*(C+1)]*/, void* stream);
 
+/* ObjectsPrediction.is_match (ml.py:159-182) per image -> match[n_img] (1 = the detections with
+ * conf >= conf_thr pair off one-to-one with the ground truth, IoU >= iou_thr, same classes);
+ * ml.od_accuracy (ml.py:343-349) is the mean of it. */
+int odk_exact_match(int n_img, int top_k, const float* dets /*[dev n_img,top_k,6]*/,
+                    const float* gt_boxes /*[dev n_gt,4]*/, const int32_t* gt_classes /*[dev n_gt]*/,
+                    const int32_t* gt_offsets /*[dev n_img+1]*/, float conf_thr, float iou_thr,
+                    uint8_t* match /*[dev n_img]*/, void* stream);
+
 /* Diagnostics: in-kernel timeline of the six kernels of a step (candidates, greedy, rows, patch, emit, nms).
  * buf = 12 device words, word 2*id = earliest CTA entry (initialise to UINT64_MAX), word 2*id+1 = latest CTA exit
  * (initialise to 0), in %globaltimer nanoseconds; NULL switches it off.  Works inside CUDA-graph replays. */

@@ -56,6 +56,7 @@ SIGNATURES = {
                                  c_float, c_void_p, c_void_p]),
     'odk_confusion_matrix': (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p,
                                      c_void_p]),
+    'odk_exact_match': (c_int, [c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p]),
     'odk_timeline_set': (c_int, [c_void_p]),
     'odk_profile_enable': (c_int, [c_int]),
     'odk_profile_read': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),

@@ -252,3 +252,86 @@ extern "C" int odk_confusion_matrix(int n_img, int top_k, int num_classes, const
   ODK_LAUNCH_CHECK("confusion_kernel");
   return ODK_OK;
 }
+
+// ---- ObjectsPrediction.is_match / ml.od_accuracy (ml.py:159-182, 343-349) -----------------------------------------------
+// One warp per image: the detections with conf >= conf_thr must pair off one-to-one with the ground truth — as many as
+// there are GTs, each attached (largest fp32 IoU, first maximum) to a different GT with IoU >= iou_thr and of that GT's
+// class.
+namespace {
+
+__global__ void __launch_bounds__(kScoreWarps * 32) exact_match_kernel(const CmArgs p, uint8_t* __restrict__ match) {
+  extern __shared__ __align__(16) unsigned char em_smem[];
+  const int warp = threadIdx.x >> 5;
+  const int lane = (int)odk_lane();
+  const int img = blockIdx.x * kScoreWarps + warp;
+  if (img >= p.n_img) return;
+  const int K = p.top_k;
+  short* dgt = reinterpret_cast<short*>(em_smem + (size_t)warp * odk_align_up((size_t)K * 4, 16));  // [K] GT of an enabled detection
+  short* dcls = dgt + K;                                                                              // [K]
+  const float* rows = p.dets + (size_t)img * K * 6;
+  const int g0 = p.gt_offsets[img], G = p.gt_offsets[img + 1] - g0;
+  int cnt = 0;
+  bool ok = true;
+  for (int d = lane; d < K; d += 32) {
+    const float* r = rows + d * 6;
+    const bool on = r[0] >= 0.0f && r[1] >= p.conf_thr;  // mask = confs >= conf_threshold (ml.py:163)
+    short tgt = -1;
+    if (on) {
+      ++cnt;
+      const float4 db = make_float4(r[2], r[3], r[4], r[5]);
+      const float da = odk_area(db);
+      float best = -1.0f;
+      int bg = 0;
+      for (int g = 0; g < G; ++g) {
+        const float4 gb = p.gt_boxes[g0 + g];
+        const float v = odk_iou_value(gb, odk_area(gb), db, da);
+        if (v > best) { best = v; bg = g; }
+      }
+      if (G > 0 && best < p.iou_thr) ok = false;  // ml.py:171-172
+      tgt = (short)bg;
+    }
+    dgt[d] = tgt;
+    dcls[d] = (short)(int)r[0];
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, s);
+  __syncwarp();
+  if (cnt != G) ok = false;  // ml.py:164-165
+  if (cnt == G && G > 0) {
+    for (int g = lane; g < G; g += 32) {  // ml.py:175-181: one detection per GT, of its class
+      int seen = 0, cls = -1;
+      for (int d = 0; d < K; ++d)
+        if (dgt[d] == g) {
+          if (seen == 0) cls = dcls[d];
+          ++seen;
+        }
+      if (seen != 1 || cls != p.gt_classes[g0 + g]) ok = false;
+    }
+  }
+  const bool all_ok = __all_sync(0xffffffffu, ok);
+  if (lane == 0) match[img] = all_ok ? 1 : 0;
+}
+
+}  // namespace
+
+extern "C" int odk_exact_match(int n_img, int top_k, const float* dets, const float* gt_boxes, const int32_t* gt_classes,
+                               const int32_t* gt_offsets, float conf_thr, float iou_thr, uint8_t* match, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  ODK_REQUIRE(n_img >= 1 && top_k >= 1, ODK_ERR_INVALID_ARGUMENT, "exact_match: bad sizes n_img=%d top_k=%d", n_img, top_k);
+  ODK_REQUIRE(dets && gt_offsets && match, ODK_ERR_INVALID_ARGUMENT, "exact_match: null pointer");
+  ODK_REQUIRE(((uintptr_t)gt_boxes & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "exact_match: gt_boxes must be 16-byte aligned");
+  ODK_REQUIRE(top_k <= 32767, ODK_ERR_UNSUPPORTED, "exact_match: top_k=%d exceeds 16-bit indices", top_k);
+  const size_t smem = odk_align_up((size_t)top_k * 4, 16) * kScoreWarps;
+  ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "exact_match: top_k=%d needs too much shared memory", top_k);
+  ODK_CUDA(cudaFuncSetAttribute(exact_match_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  CmArgs a;
+  a.n_img = n_img; a.top_k = top_k; a.num_classes = 0;
+  a.dets = dets; a.gt_boxes = reinterpret_cast<const float4*>(gt_boxes); a.gt_classes = gt_classes; a.gt_offsets = gt_offsets;
+  a.conf_thr = conf_thr; a.iou_thr = iou_thr; a.cm = nullptr;
+  {
+    OdkProfileScope prof_("exact_match_kernel", stream);
+    exact_match_kernel<<<(n_img + kScoreWarps - 1) / kScoreWarps, kScoreWarps * 32, smem, stream>>>(a, match);
+  }
+  ODK_LAUNCH_CHECK("exact_match_kernel");
+  return ODK_OK;
+}

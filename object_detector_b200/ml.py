@@ -38,6 +38,33 @@ class ObjectsAnnotation:
         """Pixel boxes: round-half-even of the f64 product (ml.py:62-65)."""
         return np.round(self.bboxes * [self.width, self.height, self.width, self.height]).astype(np.int32)
 
+    @property
+    def bboxes_ar_fixed(self):
+        """Boxes rescaled as if the image were padded to a square (ml.py:67-78; used for anchor fitting)."""
+        assert self.width > 0 and self.height > 0
+        out = np.copy(self.bboxes)
+        if self.width > self.height:
+            out[:, [1, 3]] *= self.height / self.width
+        elif self.width < self.height:
+            out[:, [0, 2]] *= self.width / self.height
+        return out
+
+    def to_str(self, class_names):
+        """ml.py:90-95: one line per object, ordered by (y, x) of the pixel box."""
+        items = sorted(zip(self.real_bboxes, self.classes), key=lambda t: _pixel_box_order(t[0]))
+        return '\n'.join(f'({x1}, {y1}) [{x2 - x1} x {y2 - y1}]: {class_names[c]}' for (x1, y1, x2, y2), c in items)
+
+    def rot90(self, k):
+        """Quarter turns of the normalised boxes (ml.py:102-112)."""
+        assert 0 <= k <= 3
+        b = self.bboxes
+        if k == 1:
+            self.bboxes = np.stack([b[:, 1], 1 - b[:, 2], b[:, 3], 1 - b[:, 0]], axis=1)
+        elif k == 2:
+            self.bboxes = 1 - b[:, [2, 3, 0, 1]]
+        elif k == 3:
+            self.bboxes = np.stack([1 - b[:, 3], b[:, 0], 1 - b[:, 1], b[:, 2]], axis=1)
+
 
 class ObjectsPrediction:
     """Detections of one image (ml.py:115-197)."""
@@ -56,6 +83,19 @@ class ObjectsPrediction:
 
     def get_real_bboxes(self, width, height):
         return np.round(self.bboxes * [width, height, width, height]).astype(np.int32)  # ml.py:184-186
+
+    def to_str(self, width, height, class_names, conf_threshold=0):
+        """ml.py:146-152."""
+        items = sorted(zip(self.get_real_bboxes(width, height), self.classes, self.confs), key=lambda t: _pixel_box_order(t[0]))
+        return '\n'.join(f'({x1}, {y1}) [{x2 - x1} x {y2 - y1}]: {class_names[c]}'
+                         for (x1, y1, x2, y2), c, cf in items if cf >= conf_threshold)
+
+    def is_match(self, classes, bboxes, conf_threshold=0, iou_threshold=0.5):
+        """ml.py:159-182: True when the detections with conf >= conf_threshold match the given objects one-to-one
+        (IoU >= iou_threshold, same classes).  Evaluated by ``odk_exact_match``."""
+        bboxes = np.asarray(bboxes, dtype=np.float32).reshape(-1, 4)
+        assert bboxes.shape == (len(classes), 4)
+        return bool(_exact_matches([(np.asarray(classes), bboxes)], [self], conf_threshold, iou_threshold)[0])
 
     def __repr__(self):
         return (f'{type(self).__module__}.{type(self).__name__}(classes={self.classes!r}, '
@@ -112,6 +152,41 @@ def non_maximum_suppression(boxes, scores, top_k=200, iou_threshold=0.45):
     k = int(cnt.item())
     res = out[:k].to(torch.int64)
     return res.cpu().numpy() if is_np else res
+
+
+def _pixel_box_order(box):
+    """Sort key of the reference's listings (``_rbb_sortkey``, ml.py:783-786): top-to-bottom, then left-to-right."""
+    return box[1], box[0], box[3], box[2]
+
+
+def _exact_matches(gt, pred, conf_threshold, iou_threshold):
+    """uint8 (n_img,) through odk_exact_match; gt = [(classes, bboxes f32)], pred = [ObjectsPrediction]."""
+    from . import voc
+    dev = _dev.device()
+    counts = np.array([len(c) for c, _ in gt], dtype=np.int64)
+    offsets = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+    n_gt = int(offsets[-1])
+    boxes = np.concatenate([np.asarray(b, np.float32).reshape(-1, 4) for _, b in gt]) if n_gt else np.zeros((1, 4), np.float32)
+    classes = np.concatenate([np.asarray(c, np.int32) for c, _ in gt]) if n_gt else np.zeros((1,), np.int32)
+    d_boxes = _dev.to_device(boxes, torch.float32, dev)
+    d_classes = _dev.to_device(classes, torch.int32, dev)
+    d_off = _dev.to_device(offsets, torch.int32, dev)
+    dets = voc.pack_predictions(pred, dev)
+    out = torch.empty((len(gt),), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call('odk_exact_match', len(gt), dets.shape[1], dets.data_ptr(), d_boxes.data_ptr(), d_classes.data_ptr(),
+                  d_off.data_ptr(), float(conf_threshold), float(iou_threshold), out.data_ptr(), _dev.stream_ptr(dev))
+    return out.cpu().numpy()
+
+
+def od_accuracy(gt, pred, conf_threshold=0, iou_threshold=0.5):
+    """ml.py:343-349: share of images whose detections match the ground truth exactly (``is_match``)."""
+    assert len(gt) == len(pred)
+    assert 0 < iou_threshold < 1
+    assert 0 <= conf_threshold < 1
+    if len(gt) == 0:
+        return np.mean([])
+    return np.mean(_exact_matches([(y.classes, y.bboxes) for y in gt], list(pred), conf_threshold, iou_threshold).astype(bool))
 
 
 def _match_counts(gt, pred, conf_thresholds, iou_threshold, num_classes):
@@ -172,6 +247,8 @@ def od_confusion_matrix(gt, pred, conf_threshold=0, iou_threshold=0.5, num_class
     if num_classes is None:
         num_classes = np.max(np.concatenate([y.classes for y in gt])) + 1
     num_classes = int(num_classes)
+    if len(gt) == 0:
+        return np.zeros((num_classes + 1, num_classes + 1), dtype=int)
     for y_true, y_pred in zip(gt, pred):
         if y_true.num_objects > 0:
             assert len(y_pred.bboxes) > 0  # ml.compute_iou (ml.py:507-508) refuses an empty detection set

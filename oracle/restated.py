@@ -594,3 +594,23 @@ def od_confusion_matrix(gt_list, pred_list, conf_threshold, iou_threshold, num_c
         for c in pc[enabled]:  # :446-447
             cm[-1, c] += 1
     return cm
+
+
+def exact_match(gt_classes, gt_boxes, pred, conf_threshold=0, iou_threshold=0.5):
+    """ObjectsPrediction.is_match (ml.py:159-182); pred = (classes, confs f32, bboxes f32)."""
+    pc, ps, pb = pred
+    mask = ps >= conf_threshold
+    if np.sum(mask) != len(gt_classes):
+        return False
+    if len(gt_classes) == 0:
+        return True
+    iou = pairwise_iou(np.asarray(gt_boxes), pb[mask])
+    if (iou.max(axis=0) < iou_threshold).any():
+        return False
+    pred_gt = iou.argmax(axis=0)
+    if len(np.unique(pred_gt)) != len(gt_classes):
+        return False
+    for gt_ix, gt_class in enumerate(gt_classes):
+        if gt_class != pc[mask][pred_gt == gt_ix][0]:
+            return False
+    return True

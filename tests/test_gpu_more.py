@@ -446,3 +446,38 @@ def test_check_prior_boxes_log_lines_equal_reference(prior_boxes):
     res = prior_boxes('voc320').check_prior_boxes(y, batch=16, print_fn=got.append)
     assert got == want
     assert res['total_errors'] == 0 and len(res['delta_locs']) == sum(len(g[2]) for g in gts)
+
+
+# ----------------------------------------------------------------------------------------- is_match / od_accuracy (ml.py:159-182, 343-349)
+def test_od_accuracy_reference_kat_and_oracle():
+    """The reference's own test (pytoolkit/tests/ml_test.py:116-155) verbatim, then random sets against the oracle."""
+    gt = [odk.ml.ObjectsAnnotation('.', 100, 100, [0, 1], [[0.00, 0.00, 0.05, 0.05], [0.25, 0.25, 0.75, 0.75]])] * 6
+    P = odk.ml.ObjectsPrediction
+    pred = [
+        P([1, 0], [1, 1], [[0.25, 0.25, 0.75, 0.75], [0.00, 0.00, 0.05, 0.05]]),
+        P([1, 0, 0], [1, 0, 1], [[0.25, 0.25, 0.75, 0.75], [0.00, 0.00, 0.05, 0.05], [0.00, 0.00, 0.05, 0.05]]),
+        P([1, 1], [1, 1], [[0.25, 0.25, 0.75, 0.75], [0.00, 0.00, 0.05, 0.05]]),
+        P([1, 0, 0], [1, 1, 1], [[0.25, 0.25, 0.75, 0.75], [0.00, 0.00, 0.05, 0.05], [0.00, 0.00, 0.05, 0.05]]),
+        P([1], [1], [[0.25, 0.25, 0.75, 0.75]]),
+        P([1, 0], [1, 1], [[0.25, 0.25, 0.75, 0.75], [0.90, 0.90, 0.95, 0.95]]),
+    ]
+    for yt, yp, m in zip(gt, pred, [True, True, False, False, False, False]):
+        assert yp.is_match(yt.classes, yt.bboxes, conf_threshold=0.5) == m
+    assert odk.ml.od_accuracy(gt, pred, conf_threshold=0.5) == pytest.approx(2 / 6)
+    # the reference's confusion-matrix KAT (ml_test.py:158-193)
+    assert (odk.ml.od_confusion_matrix(np.array([]), np.array([]), num_classes=3) == np.zeros((4, 4), dtype=int)).all()
+    cm = odk.ml.od_confusion_matrix(
+        [odk.ml.ObjectsAnnotation('.', 100, 100, [1], [[0.25, 0.25, 0.75, 0.75]])],
+        [P([0, 2, 1, 1, 2], [0, 1, 1, 1, 1], [[0.25, 0.25, 0.75, 0.75]] * 4 + [[0.95, 0.95, 0.99, 0.99]])],
+        conf_threshold=0.5, num_classes=3)
+    assert (cm == np.array([[0, 0, 0, 0], [0, 1, 0, 0], [0, 0, 0, 0], [0, 1, 2, 0]])).all()
+    # random sets: mostly mismatches plus exact copies of the ground truth
+    y_true, y_pred, gt_l, pred_l = _score_objects(9, 300, 6, max_gt=4, n_fp=2)
+    for i in range(0, 300, 3):
+        c, b, _ = gt_l[i]
+        pred_l[i] = (c.copy(), np.full(len(c), 0.9, np.float32), b.copy())
+        y_pred[i] = P(*pred_l[i])
+    for thr in (0.0, 0.4):
+        want = [R.exact_match(c, b, p, thr, 0.5) for (c, b, _), p in zip(gt_l, pred_l)]
+        assert 0.2 < np.mean(want) < 0.9
+        assert odk.ml.od_accuracy(y_true, y_pred, thr, 0.5) == np.mean(want)
