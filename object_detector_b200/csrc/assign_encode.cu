@@ -38,7 +38,6 @@ struct AssignArgs {
   int* ws_ncand;  // [B, Gmax] in-cell valid anchors of the GT
   int* ws_nlist;  // [B, Gmax] entries stored in its ranked list
   unsigned* ws_ignore;  // [B, bitmap_words] bit a = "pb_mask[a] and some GT has IoU >= 0.5 with anchor a" (pre-zeroed) or null
-  int debug_skip;       // timing experiments only (ODK_DEBUG_SKIP): wrong results when non-zero
 };
 
 __device__ __forceinline__ double encode_cost(const float4 box, const float4 loc, const double2 sz) {
@@ -123,7 +122,6 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(cons
   const float4 box = p.gt_boxes[(size_t)b * p.gmax + g];
   const float cx = __fmul_rn(__fadd_rn(box.z, box.x), 0.5f);  // ml.py:485-488
   const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
-  if (p.debug_skip & 4) return;
   int filled = 0;
   const int total = for_each_cell_candidate(p.av, cx, cy, lane, [&](int a, bool ok) {
     const unsigned m = __ballot_sync(0xffffffffu, ok);
@@ -138,7 +136,7 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(cons
   });
   __syncwarp();
   int stored = 0;
-  if (total <= kScratch && !(p.debug_skip & 1)) {  // ranks are global only if every candidate made it into the scratch
+  if (total <= kScratch) {  // ranks are global only if every candidate made it into the scratch
     // rank = number of candidates that order before this one.  A lane ranks up to four entries in one pass over the
     // scratch (shared broadcast reads, unrolled), instead of one pass per entry.
     for (int e0 = 0; e0 < total; e0 += 128) {
@@ -168,7 +166,7 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(cons
     p.ws_ncand[(size_t)b * p.gmax + g] = total;
     p.ws_nlist[(size_t)b * p.gmax + g] = stored;
   }
-  if (p.ws_ignore == nullptr || (p.debug_skip & 2)) return;
+  if (p.ws_ignore == nullptr) return;
   // ---- ignore mask, scattered per GT: pb_valids[iou >= 0.5] = False (od_pb.py:355-357; order-independent
   //      closed form, SURVEY A-4).  Only anchors that CAN reach IoU 0.5 are visited:
   //        IoU >= 1/2  =>  I >= (A+B)/3 and min(A,B)/max(A,B) >= 1/2;  with I <= iw*min(hg,ha) and
@@ -514,8 +512,6 @@ static int fill_args(AssignArgs& args, const odk_anchors* a, int batch, const fl
   args.ws_ncand = args.ws_list + (size_t)batch * gmax * args.list_len;
   args.ws_nlist = args.ws_ncand + (size_t)batch * gmax;
   args.ws_ignore = ignore;
-  static const int dbg = getenv("ODK_DEBUG_SKIP") ? atoi(getenv("ODK_DEBUG_SKIP")) : 0;
-  args.debug_skip = dbg;
   return ODK_OK;
 }
 

@@ -41,6 +41,7 @@ struct DecodeArgs {
   int* piece_count;               // [B, tiles_per_image]
   int tiles_per_image;
   int stages;  // depth of the shared-memory ring
+  int stream_hint;  // 1: head outputs are fetched with an L2 evict-first policy
 };
 
 template <int TILE, bool DENSE>
@@ -94,8 +95,14 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
       if (tid == 0) {
         const uint32_t r = (uint32_t)rows;
         odk_mbar_expect_tx(&full_bar[s], r * c * 4 + r * 4 + r + (DENSE ? r * 16 + r * 16 + r * 8 : 0));
-        odk_bulk_g2s(dst, src_clf, r * c * 4, &full_bar[s]);
-        odk_bulk_g2s(tail + L::kOffObj, src_obj, r * 4, &full_bar[s]);
+        if (p.stream_hint) {
+          const uint64_t pol = odk_policy_evict_first();
+          odk_bulk_g2s_stream(dst, src_clf, r * c * 4, &full_bar[s], pol);
+          odk_bulk_g2s_stream(tail + L::kOffObj, src_obj, r * 4, &full_bar[s], pol);
+        } else {
+          odk_bulk_g2s(dst, src_clf, r * c * 4, &full_bar[s]);
+          odk_bulk_g2s(tail + L::kOffObj, src_obj, r * 4, &full_bar[s]);
+        }
         odk_bulk_g2s(tail + L::kOffAMask, p.av.mask + a0, r, &full_bar[s]);  // anchor tables are L2-resident
         if (DENSE) {
           odk_bulk_g2s(tail + L::kOffLoc, src_loc, r * 16, &full_bar[s]);
@@ -247,6 +254,8 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   using L = StageLayout<TILE, DENSE>;
   static const int env_stages = getenv("ODK_EMIT_STAGES") ? atoi(getenv("ODK_EMIT_STAGES")) : 0;
   static const int env_per_sm = getenv("ODK_EMIT_PER_SM") ? atoi(getenv("ODK_EMIT_PER_SM")) : 0;
+  static const int env_hint = getenv("ODK_EMIT_HINT") ? atoi(getenv("ODK_EMIT_HINT")) : 1;
+  args.stream_hint = env_hint;
   args.stages = (!DENSE && env_stages >= 2 && env_stages <= L::kMaxStages) ? env_stages : 3;
   const size_t smem = L::stage_bytes(args.c) * args.stages;
   auto kern = decode_score_kernel<TILE, DENSE>;

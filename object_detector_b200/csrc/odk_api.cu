@@ -92,16 +92,9 @@ extern "C" int odk_timeline_set(unsigned long long* buf) {
 extern "C" const char* odk_version(void) { return "odk 0.1.0 (sm_100a)"; }
 extern "C" const char* odk_last_error(void) { return g_last_error; }
 
-template <typename T>
-static int upload(T** dst, const void* src, size_t count) {
-  ODK_CUDA(cudaMalloc(reinterpret_cast<void**>(dst), sizeof(T) * count));
-  ODK_CUDA(cudaMemcpy(*dst, src, sizeof(T) * count, cudaMemcpyHostToDevice));
-  return ODK_OK;
-}
-
 extern "C" int odk_anchors_destroy(odk_anchors* a) {
   if (a == nullptr) return ODK_OK;
-  cudaFree(a->d_locs); cudaFree(a->d_grid); cudaFree(a->d_sizes); cudaFree(a->d_scale); cudaFree(a->d_mask); cudaFree(a->d_maskbits);
+  cudaFree(a->d_slab);
   free(a);
   return ODK_OK;
 }
@@ -153,21 +146,30 @@ extern "C" int odk_anchors_create(odk_anchors** out, int n, int num_classes, int
   if (scale == nullptr) { free(a); return odk_set_error(ODK_ERR_CUDA, "anchors_create: out of host memory"); }
   for (size_t i = 0; i < 2 * (size_t)n; ++i) scale[i] = (float)(0.10 * pb_sizes[i]);  // float32(_VAR_LOC * pb_sizes), od_pb.py:221
   cudaGetDevice(&a->device);
-  int rc = upload(&a->d_locs, pb_locs, n);
-  if (!rc) rc = upload(&a->d_grid, pb_grid, n);
-  if (!rc) rc = upload(&a->d_sizes, pb_sizes, n);
-  if (!rc) rc = upload(&a->d_scale, scale, n);
-  if (!rc) rc = upload(&a->d_mask, pb_mask, n);
+  // one device slab for all tables
+  const size_t words = ((size_t)n + 31) / 32;
+  uint32_t* bits = static_cast<uint32_t*>(calloc(words, sizeof(uint32_t)));
+  if (bits == nullptr) { free(scale); free(a); return odk_set_error(ODK_ERR_CUDA, "anchors_create: out of host memory"); }
+  for (int i = 0; i < n; ++i) if (pb_mask[i]) bits[i >> 5] |= 1u << (i & 31);
+  const size_t sz[6] = {16 * (size_t)n, 16 * (size_t)n, 16 * (size_t)n, 8 * (size_t)n, (size_t)n, 4 * words};
+  const void* src[6] = {pb_locs, pb_grid, pb_sizes, scale, pb_mask, bits};
+  size_t off[6], total_bytes = 0;
+  for (int i = 0; i < 6; ++i) { off[i] = total_bytes; total_bytes = odk_align_up(total_bytes + sz[i], 256); }
+  int rc = ODK_OK;
+  if (cudaMalloc(&a->d_slab, total_bytes) != cudaSuccess) rc = odk_set_error(ODK_ERR_CUDA, "anchors_create: cudaMalloc of %zu bytes failed", total_bytes);
+  for (int i = 0; i < 6 && !rc; ++i)
+    if (cudaMemcpy(static_cast<char*>(a->d_slab) + off[i], src[i], sz[i], cudaMemcpyHostToDevice) != cudaSuccess)
+      rc = odk_set_error(ODK_ERR_CUDA, "anchors_create: upload of table %d failed", i);
   if (!rc) {
-    const size_t words = ((size_t)n + 31) / 32;
-    uint32_t* bits = static_cast<uint32_t*>(calloc(words, sizeof(uint32_t)));
-    if (bits == nullptr) rc = odk_set_error(ODK_ERR_CUDA, "anchors_create: out of host memory");
-    else {
-      for (int i = 0; i < n; ++i) if (pb_mask[i]) bits[i >> 5] |= 1u << (i & 31);
-      rc = upload(&a->d_maskbits, bits, words);
-      free(bits);
-    }
+    char* base = static_cast<char*>(a->d_slab);
+    a->d_locs = reinterpret_cast<float4*>(base + off[0]);
+    a->d_grid = reinterpret_cast<float4*>(base + off[1]);
+    a->d_sizes = reinterpret_cast<double2*>(base + off[2]);
+    a->d_scale = reinterpret_cast<float2*>(base + off[3]);
+    a->d_mask = reinterpret_cast<uint8_t*>(base + off[4]);
+    a->d_maskbits = reinterpret_cast<uint32_t*>(base + off[5]);
   }
+  free(bits);
   free(scale);
   if (rc) { odk_anchors_destroy(a); return rc; }
   *out = a;
