@@ -33,6 +33,7 @@ struct AssignArgs {
   long long* gt_indices;
   int32_t* status;
   int list_len;  // ranked candidates remembered per GT
+  int use_walk;  // greedy kernel: the first 32 ranks of every GT are regrouped in walk order (shared memory permitting)
   int bitmap_words;
   int* ws_list;   // [B, Gmax, list_len] ranked in-cell anchors
   int* ws_ncand;  // [B, Gmax] in-cell valid anchors of the GT
@@ -253,7 +254,8 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   int* pick = reinterpret_cast<int*>(sp);                  sp += (size_t)p.gmax * 4;
   int* ncand = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
   int* nlist = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
-  unsigned* taken = reinterpret_cast<unsigned*>(sp);
+  unsigned* taken = reinterpret_cast<unsigned*>(sp);                sp += (size_t)p.bitmap_words * 4;
+  int* walk_a = reinterpret_cast<int*>(sp);  // [gmax][32] (use_walk): rank-0..31 anchors of the r-th GT of the walk, -1 padded
   __shared__ int s_err;
   __shared__ float s_best_v[kGreedyWarps];
   __shared__ int s_best_a[kGreedyWarps];
@@ -304,6 +306,14 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   }
   odk_cp_async_wait<0>();
   __syncthreads();
+  if (p.use_walk && s_err == ODK_IMG_OK) {
+    // regroup what the walk reads: one independent shared-memory load per step instead of order -> nlist -> list
+    for (int i = threadIdx.x; i < G * 32; i += kGreedyThreads) {
+      const int g = order[i >> 5], k = i & 31;
+      walk_a[i] = (k < nlist[g]) ? list[(size_t)g * L + k] : -1;
+    }
+    __syncthreads();
+  }
 
   // Warp 0 walks the GTs; the other warps sleep at the barrier below and wake only to help with a
   // CTA-wide IoU arg-max when some GT has no free in-cell anchor (the crowded / stress case).
@@ -313,18 +323,21 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     int need = -2;
     if (warp == 0) {
       if (!err) {
-        // the first 32 ranks of the next GT are fetched while the current one is decided (they do not
-        // depend on `taken`), so the serial chain per GT is: bitmap probe -> ballot -> bitmap update
-        int g_next = (r < G) ? order[r] : 0;
-        int nl_next = (r < G) ? nlist[g_next] : 0;
-        int a_next = (r < G && lane < nl_next) ? list[(size_t)g_next * L + lane] : -1;
+        // the first 32 ranks of the next two GTs are fetched while the current one is decided (they do not depend on
+        // `taken`), so the serial chain per GT is: bitmap probe -> ballot -> bitmap update
+        auto fetch = [&](int rr) -> int {
+          if (rr >= G) return -1;
+          if (p.use_walk) return walk_a[rr * 32 + lane];
+          const int gg = order[rr];
+          return (lane < nlist[gg]) ? list[(size_t)gg * L + lane] : -1;
+        };
+        int a0 = fetch(r), a1 = fetch(r + 1);
         for (; r < G; ++r) {
-          const int g = g_next, nl = nl_next, a_first = a_next;
-          if (r + 1 < G) {
-            g_next = order[r + 1];
-            nl_next = nlist[g_next];
-            a_next = (lane < nl_next) ? list[(size_t)g_next * L + lane] : -1;
-          }
+          const int a_first = a0;
+          a0 = a1;
+          a1 = fetch(r + 2);
+          const int g = order[r];
+          const int nl = nlist[g];
           // fast path: some anchor among the first 32 ranks is free (the owning lane records it)
           const unsigned word = (a_first >= 0) ? taken[a_first >> 5] : 0xffffffffu;
           const unsigned bit = 1u << (a_first & 31);
@@ -512,6 +525,7 @@ static int fill_args(AssignArgs& args, const odk_anchors* a, int batch, const fl
   args.ws_ncand = args.ws_list + (size_t)batch * gmax * args.list_len;
   args.ws_nlist = args.ws_ncand + (size_t)batch * gmax;
   args.ws_ignore = ignore;
+  args.use_walk = 0;
   return ODK_OK;
 }
 
@@ -532,8 +546,10 @@ int odk_launch_assign_greedy(const odk_anchors* a, int batch, const float* gt_bo
                              int gmax, int64_t* pb_indices, int64_t* gt_indices, int32_t* status, void* lists_ws, cudaStream_t stream) {
   AssignArgs args;
   fill_args(args, a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, lists_ws, nullptr);
-  const size_t smem = odk_align_up((size_t)gmax * (16 + 20 + 4 * (size_t)args.list_len) + (size_t)args.bitmap_words * 4, 16);
+  size_t smem = odk_align_up((size_t)gmax * (16 + 20 + 4 * (size_t)args.list_len) + (size_t)args.bitmap_words * 4, 16);
   ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign: N=%d / Gmax=%d need %zu bytes of shared memory per image", a->n, gmax, smem);
+  args.use_walk = (smem + (size_t)gmax * 128 <= 200 * 1024) ? 1 : 0;
+  if (args.use_walk) smem += (size_t)gmax * 128;
   ODK_CUDA(cudaFuncSetAttribute(assign_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   {
     OdkProfileScope prof_("assign_greedy_kernel", stream);
