@@ -113,6 +113,13 @@ int odk_loss(const odk_anchors* a, int batch, const float* y_true /*[dev B,N,3+C
              const float* y_pred /*[dev B,N,3+C+4]*/, double* out /*[dev B,8]*/,
              void* workspace /*[dev]*/, size_t workspace_bytes, void* stream);
 
+/* Gradient of PriorBoxes.loss (od_pb.py:365-373: loss_obj + loss_clf + loss_loc) with respect to y_pred — what
+ * TensorFlow's autodiff derives from the reference's graph ops (tf.clip_by_value passes gradients only inside the
+ * clip range).  grad[b, n, :] = upstream[b] * dloss[b]/dy_pred[b, n, :]; upstream may be NULL (= 1). */
+int odk_loss_grad(const odk_anchors* a, int batch, const float* y_true /*[dev B,N,3+C+4]*/,
+                  const float* y_pred /*[dev B,N,3+C+4]*/, const float* upstream /*[dev B] or NULL*/,
+                  float* grad /*[dev B,N,3+C+4]*/, void* stream);
+
 /* encode_truth (od_pb.py:299-313) followed by loss (od_pb.py:365-431) with y_true never written:
  * odk_assign, then a pass that reads one float per negative anchor row of y_pred and whole rows
  * only for the positives.  Same outputs as odk_loss; pb_indices / gt_indices / status as odk_assign.

@@ -32,6 +32,7 @@ SIGNATURES = {
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_loss_workspace_bytes': (c_size_t, [c_void_p, c_int]),
     'odk_loss': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    'odk_loss_grad': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     'odk_assign_loss_workspace_bytes': (c_size_t, [c_void_p, c_int, c_int]),
     'odk_assign_loss': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -232,6 +232,107 @@ __global__ void __launch_bounds__(kLossTile) loss_sparse_kernel(const LossArgs p
   block_reduce_store(acc, p.partial + ((size_t)b * p.tiles_per_image + tile) * kAcc);
 }
 
+// ---- gradient of loss = loss_obj + loss_clf + loss_loc (od_pb.py:365-373) w.r.t. y_pred --------------------------------
+// Same tiling as the dense forward kernel: the y_true / y_pred tiles arrive by bulk TMA, a thread differentiates its row
+// in place of the y_true row in shared memory, and the finished tile leaves with one bulk TMA store.  Per row
+//   d/dobj   = 3 * pb_mask * mask * (2y-1) * a_t * [2(1-p_t) log p_t - (1-p_t)^2 / p_t]      (0 where p_t was clipped)
+//   d/dcls_k = -w/s * [t_k/n_k * in_k - sum_j t_j * q_j/(s*n_j) * in_j],  n = clip(q/s), in = "not clipped"
+//   d/dloc_j = w * (q_j - t_j)
+// (columns 0 and 1 of y_pred carry no gradient), times the upstream gradient of the image's loss when given —
+// tf.clip_by_value passes the gradient only inside [eps, 1-eps], like here.
+__global__ void __launch_bounds__(kLossTile) loss_grad_kernel(const LossArgs p, const float* __restrict__ upstream, float* __restrict__ grad) {
+  extern __shared__ __align__(128) unsigned char lg_smem[];
+  __shared__ uint64_t bar;
+  const int tid = threadIdx.x;
+  const int b = blockIdx.y, tile = blockIdx.x;
+  const int a0 = tile * kLossTile;
+  const int rows = min(kLossTile, p.n - a0);
+  const int W = p.W, C = p.c;
+  float* s_true = reinterpret_cast<float*>(lg_smem);
+  float* s_pred = s_true + (size_t)kLossTile * W;
+  const size_t row0 = (size_t)b * p.n + a0;
+  const float* g_true = p.y_true + row0 * W;
+  const float* g_pred = p.y_pred + row0 * W;
+  float* g_out = grad + row0 * W;
+  const uint32_t bytes = (uint32_t)rows * W * 4;
+  const bool tma_ok = ((bytes & 15) == 0) && ((((uintptr_t)g_true | (uintptr_t)g_pred | (uintptr_t)g_out) & 15) == 0);
+  if (tma_ok) {
+    if (tid == 0) {
+      odk_mbar_init(&bar, 1);
+      odk_mbar_fence_init();
+      odk_mbar_expect_tx(&bar, 2 * bytes);
+      odk_bulk_g2s(s_true, g_true, bytes, &bar);
+      odk_bulk_g2s(s_pred, g_pred, bytes, &bar);
+    }
+    __syncthreads();
+    odk_mbar_wait(&bar, 0);
+  } else {
+    for (int i = tid; i < rows * W; i += kLossTile) {
+      s_true[i] = __ldg(g_true + i);
+      s_pred[i] = __ldg(g_pred + i);
+    }
+    __syncthreads();
+  }
+  const float up = upstream ? upstream[b] : 1.0f;
+  if (tid < rows) {
+    float* t = s_true + (size_t)tid * W;  // becomes the gradient row
+    const float* q = s_pred + (size_t)tid * W;
+    const float gt_mask = t[0], w = t[1], y = t[2], pr = q[2];
+    // objectness
+    const float om_y = 1.0f - y;
+    const float a_t = y * 0.25f + om_y * 0.75f;
+    const float p_raw = y * pr + om_y * (1.0f - pr);
+    const bool inside = p_raw >= kEps && p_raw <= 1.0f - kEps;
+    const float p_t = fminf(fmaxf(p_raw, kEps), 1.0f - kEps);
+    const float om = 1.0f - p_t;
+    const float dfdpt = a_t * (2.0f * om * logf(p_t) - om * om / p_t);
+    const float m = (p.av.mask[a0 + tid] ? 1.0f : 0.0f) * gt_mask;
+    const float g_obj = inside ? 3.0f * m * (y - om_y) * dfdpt * up : 0.0f;
+    // classes
+    float s = 0.0f;
+    for (int j = 0; j < C; ++j) s += q[3 + j];
+    float cross = 0.0f;  // sum_j t_j * in_j * n_j / nclip_j
+    if (w != 0.0f) {
+      for (int j = 0; j < C; ++j) {
+        const float tj = t[3 + j];
+        if (tj != 0.0f) {
+          const float nj = q[3 + j] / s;
+          if (nj >= kEps && nj <= 1.0f - kEps) cross += tj;  // n_j / clip(n_j) = 1 inside the range
+        }
+      }
+    }
+    for (int j = 0; j < C; ++j) {
+      float g = 0.0f;
+      if (w != 0.0f) {
+        const float tj = t[3 + j];
+        const float nj = q[3 + j] / s;
+        const bool in = nj >= kEps && nj <= 1.0f - kEps;
+        const float direct = (tj != 0.0f && in) ? tj / nj : 0.0f;
+        g = -(w / s) * (direct - cross) * up;
+      }
+      t[3 + j] = g;
+    }
+    // box offsets
+#pragma unroll
+    for (int j = 0; j < 4; ++j) t[3 + C + j] = w * (q[3 + C + j] - t[3 + C + j]) * up;
+    t[0] = 0.0f;
+    t[1] = 0.0f;
+    t[2] = g_obj;
+  }
+  if (tma_ok) {
+    odk_fence_proxy_async();  // the generic-proxy writes above must be visible to the bulk store
+    __syncthreads();
+    if (tid == 0) {
+      odk_bulk_s2g(g_out, s_true, bytes);
+      odk_bulk_commit();
+      odk_bulk_wait_read<0>();  // shared memory may be released once it has been read
+    }
+  } else {
+    __syncthreads();
+    for (int i = tid; i < rows * W; i += kLossTile) g_out[i] = s_true[i];
+  }
+}
+
 // ---- per image: tile partials in a fixed order -> the seven reported values ---------------------------------------
 __global__ void __launch_bounds__(32) loss_finish_kernel(const LossArgs p) {
   const int b = blockIdx.x, lane = threadIdx.x;
@@ -359,4 +460,27 @@ extern "C" int odk_assign_loss(const odk_anchors* a, int batch, const float* gt_
   }
   ODK_LAUNCH_CHECK("loss_sparse_kernel");
   return loss_finish(p, stream);
+}
+
+extern "C" int odk_loss_grad(const odk_anchors* a, int batch, const float* y_true, const float* y_pred, const float* upstream, float* grad,
+                             void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  ODK_REQUIRE(a != nullptr && batch >= 1 && batch <= 65535, ODK_ERR_INVALID_ARGUMENT, "loss_grad: bad arguments");
+  ODK_REQUIRE(y_true && y_pred && grad, ODK_ERR_INVALID_ARGUMENT, "loss_grad: null pointer");
+  ODK_REQUIRE((((uintptr_t)y_true | (uintptr_t)y_pred | (uintptr_t)grad) & 3) == 0, ODK_ERR_INVALID_ARGUMENT, "loss_grad: misaligned buffer");
+  LossArgs p;
+  memset(&p, 0, sizeof(p));
+  p.av = odk_view(a);
+  p.batch = batch; p.n = a->n; p.c = a->num_classes; p.W = 3 + a->num_classes + 4;
+  p.tiles_per_image = (a->n + kLossTile - 1) / kLossTile;
+  p.y_true = y_true; p.y_pred = y_pred;
+  const size_t smem = 2 * (size_t)kLossTile * p.W * 4;
+  ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "loss_grad: row width %d floats needs %zu bytes of shared memory per tile", p.W, smem);
+  ODK_CUDA(cudaFuncSetAttribute(loss_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  {
+    OdkProfileScope prof_("loss_grad_kernel", stream);
+    loss_grad_kernel<<<dim3(p.tiles_per_image, batch), kLossTile, smem, stream>>>(p, upstream, grad);
+  }
+  ODK_LAUNCH_CHECK("loss_grad_kernel");
+  return ODK_OK;
 }

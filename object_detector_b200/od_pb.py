@@ -273,6 +273,40 @@ class PriorBoxes:
                       ws_bytes, _dev.stream_ptr(dev))
         return {'terms': out, 'pb_indices': pb_idx, 'gt_indices': gt_idx, 'status': status}
 
+    def loss_grad(self, y_true, y_pred, upstream=None):
+        """d ``loss`` / d ``y_pred`` (B,N,3+C+4) float32 — the gradient TensorFlow derives from od_pb.py:365-431
+        (``odk_loss_grad``).  ``upstream`` (B,) scales each image's gradient (the incoming dL/dloss)."""
+        dev = _dev.device(y_pred.device if isinstance(y_pred, torch.Tensor) and y_pred.is_cuda else None)
+        yt = _dev.to_device(y_true, torch.float32, dev)
+        yp = _dev.to_device(y_pred, torch.float32, dev)
+        n, w = len(self.pb_locs), 3 + self.num_classes + 4
+        assert yt.dim() == 3 and yt.shape[1:] == (n, w) and yp.shape == yt.shape
+        up = _dev.to_device(upstream, torch.float32, dev) if upstream is not None else None
+        assert up is None or up.shape == (yt.shape[0],)
+        grad = torch.empty_like(yp)
+        with torch.cuda.device(dev):
+            _lib.call('odk_loss_grad', self._handle(dev), yt.shape[0], yt.data_ptr(), yp.data_ptr(), _dev.ptr(up), grad.data_ptr(),
+                      _dev.stream_ptr(dev))
+        return grad
+
+    def loss_with_grad(self, y_true, y_pred):
+        """``loss`` as a differentiable torch op: forward ``odk_loss``, backward ``odk_loss_grad`` — for training
+        loops whose network lives in torch (the reference relies on TensorFlow's autodiff here)."""
+        pb = self
+
+        class _Loss(torch.autograd.Function):
+            @staticmethod
+            def forward(ctx, yt, yp):
+                ctx.save_for_backward(yt, yp)
+                return pb.loss_terms(yt, yp)[:, 0].to(torch.float32)
+
+            @staticmethod
+            def backward(ctx, grad_out):
+                yt, yp = ctx.saved_tensors
+                return None, pb.loss_grad(yt, yp, grad_out.contiguous())
+
+        return _Loss.apply(y_true, y_pred)
+
     def _loss_column(self, y_true, y_pred, k):
         return self.loss_terms(y_true, y_pred)[:, k].to(torch.float32)
 

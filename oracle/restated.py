@@ -614,3 +614,34 @@ def exact_match(gt_classes, gt_boxes, pred, conf_threshold=0, iou_threshold=0.5)
         if gt_class != pc[mask][pred_gt == gt_ix][0]:
             return False
     return True
+
+
+def od_loss_grad(t: AnchorTables, y_true, y_pred, upstream=None):
+    """d(loss_obj + loss_clf + loss_loc)/d y_pred (od_pb.py:365-373), float64, analytic — what autodiff yields for
+    the graph of ``od_losses``: clip_by_value passes the gradient only inside [eps, 1-eps].  Checked against
+    torch.autograd in tests/test_oracle_cpu.py.  Returns (B, N, 3+C+4) float64."""
+    yt = np.asarray(y_true, np.float64)
+    yp = np.asarray(y_pred, np.float64)
+    eps = float(_K_EPS)
+    g = np.zeros_like(yp)
+    mask = t.pb_mask[None].astype(np.float64) * yt[:, :, 0]
+    w, y, p = yt[:, :, 1], yt[:, :, 2], yp[:, :, 2]
+    a_t = y * 0.25 + (1 - y) * 0.75
+    p_raw = y * p + (1 - y) * (1 - p)
+    inside = (p_raw >= eps) & (p_raw <= 1 - eps)
+    p_t = np.clip(p_raw, eps, 1 - eps)
+    dfdpt = a_t * (2 * (1 - p_t) * np.log(p_t) - (1 - p_t) ** 2 / p_t)
+    g[:, :, 2] = np.where(inside, 3 * mask * (2 * y - 1) * dfdpt, 0.0)
+    q, tt = yp[:, :, 3:-4], yt[:, :, 3:-4]
+    s = q.sum(axis=-1, keepdims=True)
+    with np.errstate(invalid='ignore', divide='ignore'):
+        n = q / s
+        ok = (n >= eps) & (n <= 1 - eps)
+        direct = np.where(ok & (tt != 0), tt / n, 0.0)
+        cross = np.where(ok, tt, 0.0).sum(axis=-1, keepdims=True)
+        gc = -(w[:, :, None] / s) * (direct - cross)
+    g[:, :, 3:-4] = np.where(w[:, :, None] != 0, gc, 0.0)
+    g[:, :, -4:] = w[:, :, None] * (yp[:, :, -4:] - yt[:, :, -4:])
+    if upstream is not None:
+        g *= np.asarray(upstream, np.float64)[:, None, None]
+    return g

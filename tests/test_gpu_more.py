@@ -481,3 +481,32 @@ def test_od_accuracy_reference_kat_and_oracle():
         want = [R.exact_match(c, b, p, thr, 0.5) for (c, b, _), p in zip(gt_l, pred_l)]
         assert 0.2 < np.mean(want) < 0.9
         assert odk.ml.od_accuracy(y_true, y_pred, thr, 0.5) == np.mean(want)
+
+
+@pytest.mark.parametrize('name,batch,gmax', [('voc640', 3, 24), ('mid80', 2, 9), ('odd7', 3, 5), ('tiny128', 4, 3)])
+def test_loss_gradient_vs_oracle_and_autograd(prior_boxes, oracle_tables, name, batch, gmax):
+    """odk_loss_grad against the float64 analytic oracle (itself checked against torch.autograd on the CPU): fp32
+    kernel arithmetic -> 2e-5 relative to the largest gradient magnitude of each column group; clipped entries give an
+    exact zero; the autograd wrapper hands the same tensor to backward()."""
+    pb, t = prior_boxes(name), oracle_tables(name)
+    c = pb.num_classes
+    gtb, gtc, gtn = synth.gt_batch(13, batch, gmax, c, size=(0.1, 0.5))
+    enc = pb.encode_truth_batch(gtb, gtc, gtn)
+    y_true = enc['y_true']
+    rng = np.random.RandomState(6)
+    y_pred = _head_like(rng, tuple(y_true.shape), c)
+    y_pred[0, 3, 2] = 1.0  # negative row with p_t clipped to eps: no gradient
+    up = rng.uniform(0.5, 2.0, size=batch).astype(np.float32)
+    ref = R.od_loss_grad(t, y_true.cpu().numpy(), y_pred, up)
+    got = pb.loss_grad(y_true, y_pred, up).cpu().numpy()
+    assert got.dtype == np.float32 and got.shape == ref.shape
+    assert (got[:, :, :2] == 0).all() and got[0, 3, 2] == 0
+    for sl in (slice(2, 3), slice(3, 3 + c), slice(3 + c, None)):
+        scale = np.abs(ref[:, :, sl]).max()
+        assert scale > 0
+        np.testing.assert_allclose(got[:, :, sl], ref[:, :, sl], rtol=2e-5, atol=2e-5 * scale)
+    yp = torch.from_numpy(y_pred).cuda().requires_grad_(True)
+    loss = pb.loss_with_grad(y_true, yp)
+    (loss * torch.from_numpy(up).cuda()).sum().backward()
+    assert torch.equal(yp.grad, torch.from_numpy(got).cuda())
+    np.testing.assert_allclose(loss.detach().cpu().numpy(), R.od_losses(t, y_true.cpu().numpy(), y_pred)['loss'], rtol=2e-5)

@@ -294,3 +294,35 @@ def test_annotation_helpers_match_reference():
         keep = ps >= 0.3  # a prediction set that does match: the jittered GT copies only
         sub = (pc[keep][:len(c)], ps[keep][:len(c)], pb[keep][:len(c)])
         assert R.exact_match(c, b, sub, 0.0, 0.5) == tk.ml.ObjectsPrediction(*sub).is_match(c, b, 0.0, 0.5)
+
+
+def test_loss_gradient_oracle_vs_torch_autograd(oracle_tables):
+    """The analytic gradient of the oracle equals torch.autograd of the Keras formulas written in float64 torch
+    (clamp passes gradients only inside its range, like tf.clip_by_value)."""
+    import torch
+    t = oracle_tables('tiny128')
+    rng = np.random.RandomState(4)
+    boxes = np.array([[0.1, 0.1, 0.5, 0.6], [0.55, 0.3, 0.9, 0.8], [0.2, 0.5, 0.45, 0.95]], np.float32)
+    y_true = R.encode_truth(t, [(np.array([0, 1, 1], np.int32), boxes), (np.array([1], np.int32), boxes[:1])])
+    y_pred = rng.uniform(0.02, 0.98, size=y_true.shape).astype(np.float32)
+    y_pred[0, 5, 2] = 1.0          # p_t = 0 for a negative row -> clipped -> no gradient
+    y_pred[0, 7, 2] = 0.0          # p_t = 1 -> clipped
+    up = np.array([1.0, 0.37])
+    yt, yp = torch.tensor(y_true, dtype=torch.float64), torch.tensor(y_pred, dtype=torch.float64, requires_grad=True)
+    eps = 1e-7
+    y, p = yt[:, :, 2], yp[:, :, 2]
+    a_t = y * 0.25 + (1 - y) * 0.75
+    p_t = torch.clamp(y * p + (1 - y) * (1 - p), float(np.float32(eps)), 1 - float(np.float32(eps)))
+    mask = torch.tensor(t.pb_mask.astype(np.float64))[None] * yt[:, :, 0]
+    loss_obj = 3 * ((-a_t * (1 - p_t) ** 2 * torch.log(p_t)) * mask).sum(-1)
+    q = yp[:, :, 3:-4]
+    n = torch.clamp(q / q.sum(-1, keepdim=True), float(np.float32(eps)), 1 - float(np.float32(eps)))
+    loss_clf = (-(yt[:, :, 3:-4] * torch.log(n)).sum(-1) * yt[:, :, 1]).sum(-1)
+    loss_loc = 2 * (((yp[:, :, -4:] - yt[:, :, -4:]) ** 2).mean(-1) * yt[:, :, 1]).sum(-1)
+    loss = loss_obj + loss_clf + loss_loc
+    (loss * torch.tensor(up)).sum().backward()
+    got = R.od_loss_grad(t, y_true, y_pred, up)
+    np.testing.assert_allclose(got, yp.grad.numpy(), rtol=1e-9, atol=1e-12)
+    assert got[0, 5, 2] == 0 and got[0, 7, 2] == 0 and np.abs(got[:, :, 2]).max() > 0
+    ref = R.od_losses(t, y_true, y_pred)
+    np.testing.assert_allclose(ref['loss'], loss.detach().numpy(), rtol=1e-5)
