@@ -132,6 +132,17 @@ int odk_assign_loss(const odk_anchors* a, int batch, const float* gt_boxes /*[de
                     int32_t* status /*[dev B]*/, void* workspace /*[dev, 256-byte aligned]*/,
                     size_t workspace_bytes, void* stream);
 
+/* odk_assign_loss plus the gradient of the loss w.r.t. y_pred in the same pass (what a training step needs from
+ * encode_truth + loss + autodiff), still without y_true: grad[b, n, :] = upstream[b] * dloss[b]/dy_pred[b, n, :],
+ * all zero except the objectness column and the positive rows; upstream may be NULL (= 1). */
+int odk_assign_loss_grad(const odk_anchors* a, int batch, const float* gt_boxes /*[dev B,Gmax,4]*/,
+                         const int32_t* gt_classes /*[dev B,Gmax]*/, const int32_t* gt_count /*[dev B]*/,
+                         int gmax, const float* y_pred /*[dev B,N,3+C+4]*/, const float* upstream /*[dev B] or NULL*/,
+                         double* out /*[dev B,8]*/, float* grad /*[dev B,N,3+C+4]*/,
+                         int64_t* pb_indices /*[dev B,Gmax]*/, int64_t* gt_indices /*[dev B,Gmax]*/,
+                         int32_t* status /*[dev B]*/, void* workspace /*[dev, 256-byte aligned]*/,
+                         size_t workspace_bytes, void* stream);
+
 /* ChannelArgMax + ChannelMax + _objconf + decode_locs (layers.py:69-98, od_net.py:177-189):
  * classes = argmax_c clfs, confs = objs*max_c clfs*pb_mask, boxes = decode(locs). */
 int odk_decode_score(const odk_anchors* a, int batch, const float* objs /*[dev B,N,1]*/,

@@ -36,6 +36,8 @@ SIGNATURES = {
     'odk_assign_loss_workspace_bytes': (c_size_t, [c_void_p, c_int, c_int]),
     'odk_assign_loss': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_void_p, c_void_p, c_size_t, c_void_p]),
+    'odk_assign_loss_grad': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_decode_score': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                  c_void_p]),
     'odk_nms_workspace_bytes': (c_size_t, [c_int, c_int, c_int, c_int]),

@@ -42,6 +42,8 @@ struct LossArgs {
   int gmax;
   double* partial;  // [B, tiles_per_image, kAcc]
   double* out;      // [B, 8]
+  float* grad;            // SPARSE + gradient: [B, N, W] or null
+  const float* upstream;  // [B] or null (= 1)
 };
 
 // losses.py:22-30 with alpha=0.25, gamma=2
@@ -52,6 +54,16 @@ __device__ __forceinline__ float focal(float y, float p) {
   p_t = fminf(fmaxf(p_t, kEps), __fsub_rn(1.0f, kEps));
   const float om = __fsub_rn(1.0f, p_t);
   return __fmul_rn(__fmul_rn(-a_t, __fmul_rn(om, om)), logf(p_t));
+}
+
+// d(3 * mask * focal(y, p)) / dp  (tf.clip_by_value: no gradient where p_t was clipped)
+__device__ __forceinline__ float obj_grad(float y, float p, float mask) {
+  const float om_y = 1.0f - y;
+  const float a_t = y * 0.25f + om_y * 0.75f;
+  const float p_raw = y * p + om_y * (1.0f - p);
+  if (!(p_raw >= kEps && p_raw <= 1.0f - kEps)) return 0.0f;
+  const float om = 1.0f - p_raw;
+  return 3.0f * mask * (y - om_y) * a_t * (2.0f * om * logf(p_raw) - om * om / p_raw);
 }
 
 // Adds one anchor row's terms.  cce / mse / cls_match are that row's categorical cross-entropy (od_pb.py:419),
@@ -169,7 +181,11 @@ __global__ void __launch_bounds__(kLossTile) loss_dense_kernel(const LossArgs p)
 }
 
 // ---- SPARSE: the assignment stands in for y_true ---------------------------------------------------------------------
+// GRAD: the gradient tile (all zero except column 2 and the positive rows) is built in shared memory and leaves with one
+// bulk TMA store, so forward values and d loss / d y_pred come out of the same pass over the objectness column.
+template <bool GRAD>
 __global__ void __launch_bounds__(kLossTile) loss_sparse_kernel(const LossArgs p) {
+  extern __shared__ __align__(128) unsigned char ls_smem[];
   __shared__ int s_pos[kLossTile];  // assignment slot + 1 of the positive anchors of this tile
   const int tid = threadIdx.x;
   const int b = blockIdx.y, tile = blockIdx.x;
@@ -185,6 +201,12 @@ __global__ void __launch_bounds__(kLossTile) loss_sparse_kernel(const LossArgs p
     if (pa >= 0 && pa < rows) s_pos[pa] = k + 1;
   }
   __syncthreads();
+  float* s_g = reinterpret_cast<float*>(ls_smem);  // GRAD: [rows][W]
+  const float up = (GRAD && p.upstream) ? p.upstream[b] : 1.0f;
+  if (GRAD) {
+    for (int i = tid; i < rows * W; i += kLossTile) s_g[i] = 0.0f;
+    __syncthreads();
+  }
   double acc[kAcc];
 #pragma unroll
   for (int k = 0; k < kAcc; ++k) acc[k] = 0.0;
@@ -198,7 +220,9 @@ __global__ void __launch_bounds__(kLossTile) loss_sparse_kernel(const LossArgs p
     if (slot == 0) {
       // negative (or ignored) row: y_true = [mask, 0, 0, 0.., 0,0,0,0]; cce = 0 (all-zero target), weight 0
       const float gt_mask = (ok && !(mbit & ibit)) ? w0 : 0.0f;
-      add_row(acc, gt_mask, 0.0f, 0.0f, q[2], mbit ? 1.0f : 0.0f, 0.0f, 0.0f, false);
+      const float pr = q[2];
+      add_row(acc, gt_mask, 0.0f, 0.0f, pr, mbit ? 1.0f : 0.0f, 0.0f, 0.0f, false);
+      if (GRAD) s_g[tid * W + 2] = obj_grad(0.0f, pr, (mbit ? 1.0f : 0.0f) * gt_mask) * up;
     } else {
       const int g = (int)p.gt_indices[(size_t)b * p.gmax + slot - 1];
       const float4 box = p.gt_boxes[(size_t)b * p.gmax + g];
@@ -226,10 +250,37 @@ __global__ void __launch_bounds__(kLossTile) loss_sparse_kernel(const LossArgs p
         const float d = __fsub_rn(q[3 + p.c + j], tl[j]);
         se = __fadd_rn(se, __fmul_rn(d, d));
       }
-      add_row(acc, w0, __fdiv_rn(1.0f, (float)G), 1.0f, q[2], mbit ? 1.0f : 0.0f, cce, __fmul_rn(se, 0.25f), ap == cls);
+      const float wgt = __fdiv_rn(1.0f, (float)G);
+      add_row(acc, w0, wgt, 1.0f, q[2], mbit ? 1.0f : 0.0f, cce, __fmul_rn(se, 0.25f), ap == cls);
+      if (GRAD) {
+        float* gr = s_g + tid * W;
+        gr[2] = obj_grad(1.0f, q[2], (mbit ? 1.0f : 0.0f) * w0) * up;
+        const float ncls = qc[cls] / s;
+        const bool in = ncls >= kEps && ncls <= 1.0f - kEps;
+        const float cross = in ? 1.0f : 0.0f;
+        for (int j = 0; j < p.c; ++j) gr[3 + j] = -(wgt / s) * (((j == cls && in) ? 1.0f / ncls : 0.0f) - cross) * up;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) gr[3 + p.c + j] = wgt * (q[3 + p.c + j] - tl[j]) * up;
+      }
+    }
+  }
+  if (GRAD) {
+    float* g_out = p.grad + ((size_t)b * p.n + a0) * W;
+    const uint32_t bytes = (uint32_t)rows * W * 4;
+    if (((bytes & 15) == 0) && (((uintptr_t)g_out & 15) == 0)) {
+      odk_fence_proxy_async();
+      __syncthreads();
+      if (tid == 0) {
+        odk_bulk_s2g(g_out, s_g, bytes);
+        odk_bulk_commit();
+      }
+    } else {
+      __syncthreads();
+      for (int i = tid; i < rows * W; i += kLossTile) g_out[i] = s_g[i];
     }
   }
   block_reduce_store(acc, p.partial + ((size_t)b * p.tiles_per_image + tile) * kAcc);
+  if (GRAD && tid == 0) odk_bulk_wait_read<0>();  // the tile must stay in shared memory until the bulk store has read it
 }
 
 // ---- gradient of loss = loss_obj + loss_clf + loss_loc (od_pb.py:365-373) w.r.t. y_pred --------------------------------
@@ -431,9 +482,9 @@ extern "C" size_t odk_assign_loss_workspace_bytes(const odk_anchors* a, int batc
   return odk_align_up(odk_assign_workspace_bytes_impl(a->n, batch, gmax), 256) + loss_partial_bytes(a->n, batch);
 }
 
-extern "C" int odk_assign_loss(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count,
-                               int gmax, const float* y_pred, double* out, int64_t* pb_indices, int64_t* gt_indices, int32_t* status,
-                               void* workspace, size_t workspace_bytes, void* stream_) {
+static int assign_loss_impl(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count,
+                            int gmax, const float* y_pred, const float* upstream, double* out, float* grad, int64_t* pb_indices,
+                            int64_t* gt_indices, int32_t* status, void* workspace, size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = odk_assign_check(a, batch, gt_boxes, gt_count, gmax, pb_indices, gt_indices, status)) return rc;
   ODK_REQUIRE(gt_classes != nullptr, ODK_ERR_INVALID_ARGUMENT, "assign_loss: null gt_classes");
@@ -454,12 +505,35 @@ extern "C" int odk_assign_loss(const odk_anchors* a, int batch, const float* gt_
   p.gt_indices = reinterpret_cast<const long long*>(gt_indices);
   p.gt_boxes = reinterpret_cast<const float4*>(gt_boxes);
   p.gt_classes = gt_classes; p.gt_count = gt_count; p.status = status; p.gmax = gmax;
-  {
+  p.grad = grad; p.upstream = upstream;
+  if (grad != nullptr) {
+    const size_t smem = (size_t)kLossTile * p.W * 4;
+    ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign_loss_grad: row width %d floats needs %zu bytes of shared memory", p.W, smem);
+    ODK_CUDA(cudaFuncSetAttribute(loss_sparse_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    OdkProfileScope prof_("loss_sparse_grad_kernel", stream);
+    loss_sparse_kernel<true><<<dim3(p.tiles_per_image, batch), kLossTile, smem, stream>>>(p);
+  } else {
     OdkProfileScope prof_("loss_sparse_kernel", stream);
-    loss_sparse_kernel<<<dim3(p.tiles_per_image, batch), kLossTile, 0, stream>>>(p);
+    loss_sparse_kernel<false><<<dim3(p.tiles_per_image, batch), kLossTile, 0, stream>>>(p);
   }
   ODK_LAUNCH_CHECK("loss_sparse_kernel");
   return loss_finish(p, stream);
+}
+
+extern "C" int odk_assign_loss(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count,
+                               int gmax, const float* y_pred, double* out, int64_t* pb_indices, int64_t* gt_indices, int32_t* status,
+                               void* workspace, size_t workspace_bytes, void* stream) {
+  return assign_loss_impl(a, batch, gt_boxes, gt_classes, gt_count, gmax, y_pred, nullptr, out, nullptr, pb_indices, gt_indices, status,
+                          workspace, workspace_bytes, stream);
+}
+
+extern "C" int odk_assign_loss_grad(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes,
+                                    const int32_t* gt_count, int gmax, const float* y_pred, const float* upstream, double* out, float* grad,
+                                    int64_t* pb_indices, int64_t* gt_indices, int32_t* status, void* workspace, size_t workspace_bytes,
+                                    void* stream) {
+  ODK_REQUIRE(grad != nullptr && (((uintptr_t)grad) & 3) == 0, ODK_ERR_INVALID_ARGUMENT, "assign_loss_grad: grad null or misaligned");
+  return assign_loss_impl(a, batch, gt_boxes, gt_classes, gt_count, gmax, y_pred, upstream, out, grad, pb_indices, gt_indices, status,
+                          workspace, workspace_bytes, stream);
 }
 
 extern "C" int odk_loss_grad(const odk_anchors* a, int batch, const float* y_true, const float* y_pred, const float* upstream, float* grad,

@@ -249,10 +249,11 @@ class PriorBoxes:
                       _dev.stream_ptr(dev))
         return out
 
-    def assign_loss_batch(self, gt_boxes, gt_classes, gt_count, y_pred):
+    def assign_loss_batch(self, gt_boxes, gt_classes, gt_count, y_pred, with_grad=False, upstream=None):
         """``encode_truth`` followed by ``loss`` without ever writing y_true (``odk_assign_loss``): padded GT as in
         ``encode_truth_batch`` + the network output (B,N,3+C+4) -> dict with ``terms`` (B,8) float64 (columns
-        ``LOSS_COLUMNS``), ``pb_indices``, ``gt_indices``, ``status``."""
+        ``LOSS_COLUMNS``), ``pb_indices``, ``gt_indices``, ``status``; ``with_grad`` adds ``grad`` (B,N,3+C+4) float32 =
+        ``upstream[b]`` * d loss / d y_pred from the same pass (``odk_assign_loss_grad``)."""
         dev = _dev.device(y_pred.device if isinstance(y_pred, torch.Tensor) and y_pred.is_cuda else None)
         boxes = _dev.to_device(gt_boxes, torch.float32, dev)
         classes = _dev.to_device(gt_classes, torch.int32, dev)
@@ -267,11 +268,20 @@ class PriorBoxes:
         status = torch.empty((b,), dtype=torch.int32, device=dev)
         ws_bytes = _lib.load().odk_assign_loss_workspace_bytes(self._handle(dev), b, gmax)
         ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        res = {'terms': out, 'pb_indices': pb_idx, 'gt_indices': gt_idx, 'status': status}
         with torch.cuda.device(dev):
-            _lib.call('odk_assign_loss', self._handle(dev), b, boxes.data_ptr(), classes.data_ptr(), count.data_ptr(), gmax,
-                      yp.data_ptr(), out.data_ptr(), pb_idx.data_ptr(), gt_idx.data_ptr(), status.data_ptr(), ws.data_ptr(),
-                      ws_bytes, _dev.stream_ptr(dev))
-        return {'terms': out, 'pb_indices': pb_idx, 'gt_indices': gt_idx, 'status': status}
+            if with_grad:
+                up = _dev.to_device(upstream, torch.float32, dev) if upstream is not None else None
+                assert up is None or up.shape == (b,)
+                res['grad'] = torch.empty_like(yp)
+                _lib.call('odk_assign_loss_grad', self._handle(dev), b, boxes.data_ptr(), classes.data_ptr(), count.data_ptr(), gmax,
+                          yp.data_ptr(), _dev.ptr(up), out.data_ptr(), res['grad'].data_ptr(), pb_idx.data_ptr(), gt_idx.data_ptr(),
+                          status.data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
+            else:
+                _lib.call('odk_assign_loss', self._handle(dev), b, boxes.data_ptr(), classes.data_ptr(), count.data_ptr(), gmax,
+                          yp.data_ptr(), out.data_ptr(), pb_idx.data_ptr(), gt_idx.data_ptr(), status.data_ptr(), ws.data_ptr(),
+                          ws_bytes, _dev.stream_ptr(dev))
+        return res
 
     def loss_grad(self, y_true, y_pred, upstream=None):
         """d ``loss`` / d ``y_pred`` (B,N,3+C+4) float32 — the gradient TensorFlow derives from od_pb.py:365-431

@@ -40,6 +40,11 @@ for B in (64, 256):
     res['encode_then_loss_us'] = timed([cap(lambda g=g, y=y, p=p: (pb.encode_truth_batch(*g, y_true=y), pb.loss_terms(y, p)))
                                         for g, y, p in zip(gts, ys, preds)])
     res['assign_loss_fused_us'] = timed([cap(lambda g=g, p=p: pb.assign_loss_batch(*g, p)) for g, p in zip(gts, preds)])
+    res['loss_grad_dense_us'] = timed([cap(lambda y=y, p=p: pb.loss_grad(y, p)) for y, p in zip(ys, preds)])
+    res['loss_grad_dense_gbs'] = round(3 * B * N * W * 4 / (res['loss_grad_dense_us'] * 1e-6) / 1e9)
+    res['train_step_dense_us'] = timed([cap(lambda g=g, y=y, p=p: (pb.encode_truth_batch(*g, y_true=y), pb.loss_terms(y, p), pb.loss_grad(y, p)))
+                                        for g, y, p in zip(gts, ys, preds)])
+    res['train_step_fused_us'] = timed([cap(lambda g=g, p=p: pb.assign_loss_batch(*g, p, with_grad=True)) for g, p in zip(gts, preds)])
     a = pb.loss_terms(ys[0], preds[0]); f = pb.assign_loss_batch(*gts[0], preds[0])['terms']
     res['fused_vs_dense_max_rel'] = float(((a - f).abs() / a.abs().clamp_min(1e-12)).max())
     print(json.dumps({k: (round(v, 2) if isinstance(v, float) and v > 1e-3 else v) for k, v in res.items()}), flush=True)

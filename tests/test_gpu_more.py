@@ -505,6 +505,14 @@ def test_loss_gradient_vs_oracle_and_autograd(prior_boxes, oracle_tables, name, 
         scale = np.abs(ref[:, :, sl]).max()
         assert scale > 0
         np.testing.assert_allclose(got[:, :, sl], ref[:, :, sl], rtol=2e-5, atol=2e-5 * scale)
+    # fused: assignment + forward + gradient without y_true
+    fused = pb.assign_loss_batch(gtb, gtc, gtn, y_pred, with_grad=True, upstream=up)
+    fg = fused['grad'].cpu().numpy()
+    for sl in (slice(2, 3), slice(3, 3 + c), slice(3 + c, None)):
+        scale = np.abs(ref[:, :, sl]).max()
+        np.testing.assert_allclose(fg[:, :, sl], ref[:, :, sl], rtol=2e-5, atol=2e-5 * scale)
+    assert (fg[:, :, :2] == 0).all()
+    assert torch.equal(fused['terms'], pb.assign_loss_batch(gtb, gtc, gtn, y_pred)['terms'])
     yp = torch.from_numpy(y_pred).cuda().requires_grad_(True)
     loss = pb.loss_with_grad(y_true, yp)
     (loss * torch.from_numpy(up).cuda()).sum().backward()
