@@ -43,7 +43,7 @@ def load_peaks():
         return 6650.0, 'fallback'
 
 
-NCU_NAMES = {'score_emit_kernel': 'decode_score_kernel<256, 0>', 'encode_rows_kernel': 'encode_rows_kernel<4>'}
+NCU_NAMES = {'score_emit_kernel': 'decode_score_kernel<256, 0', 'encode_rows_kernel': 'encode_rows_kernel<4'}  # ncu name prefixes
 
 
 def load_traffic(kernel):
@@ -51,7 +51,9 @@ def load_traffic(kernel):
     (profiles/ncu_traffic.json, written by scripts/ncu_summary.py), or None."""
     try:
         with open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')) as f:
-            k = json.load(f)['kernels'][NCU_NAMES.get(kernel, kernel)]
+            kernels = json.load(f)['kernels']
+        prefix = NCU_NAMES.get(kernel, kernel)
+        k = next(v for name, v in kernels.items() if name.startswith(prefix))
         return k['dram_read_bytes'] + k['dram_write_bytes']
     except Exception:  # noqa: BLE001
         return None

@@ -54,12 +54,15 @@ struct StageLayout {
   static size_t stage_bytes(int c) { return (size_t)TILE * c * 4 + kTail; }
 };
 
-template <int TILE, bool DENSE>
-__global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) {
+// SPLIT threads share one anchor row (wide class vectors: each scans 1/SPLIT of the classes, the group merges by
+// shuffles), so that a tile of few, long rows still fills the CTA with 256 threads.
+template <int TILE, bool DENSE, int SPLIT>
+__global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const DecodeArgs p) {
   OdkTimeline tl_(ODK_TL_EMIT);
   using L = StageLayout<TILE, DENSE>;
+  constexpr int kThreads = TILE * SPLIT;
   const int kStages = p.stages;
-  constexpr int kWarps = TILE / 32;
+  constexpr int kWarps = kThreads / 32;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int c = p.c;
   const size_t clf_bytes = (size_t)TILE * c * 4;
@@ -69,6 +72,7 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
 
   const long long total_tiles = (long long)p.batch * p.tiles_per_image;
   const int tid = threadIdx.x;
+  const int row_id = tid / SPLIT, part = tid % SPLIT;  // SPLIT consecutive lanes own one anchor row
 
   if (tid == 0) {
     for (int s = 0; s < kStages; ++s) odk_mbar_init(&full_bar[s], 1);
@@ -114,8 +118,8 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
       float* d0 = reinterpret_cast<float*>(dst);
       float* d2 = reinterpret_cast<float*>(tail + L::kOffObj);
       unsigned char* d5 = tail + L::kOffAMask;
-      for (int i = tid; i < rows * c; i += TILE) d0[i] = __ldg(src_clf + i);
-      for (int i = tid; i < rows; i += TILE) {
+      for (int i = tid; i < rows * c; i += kThreads) d0[i] = __ldg(src_clf + i);
+      for (int i = tid; i < rows; i += kThreads) {
         d2[i] = __ldg(src_obj + i);
         d5[i] = p.av.mask[a0 + i];
       }
@@ -123,8 +127,8 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
         float* d1 = reinterpret_cast<float*>(tail + L::kOffLoc);
         float4* d3 = reinterpret_cast<float4*>(tail + L::kOffALoc);
         float2* d4 = reinterpret_cast<float2*>(tail + L::kOffAScale);
-        for (int i = tid; i < rows * 4; i += TILE) d1[i] = __ldg(src_loc + i);
-        for (int i = tid; i < rows; i += TILE) {
+        for (int i = tid; i < rows * 4; i += kThreads) d1[i] = __ldg(src_loc + i);
+        for (int i = tid; i < rows; i += kThreads) {
           d3[i] = __ldg(p.av.locs + a0 + i);
           d4[i] = __ldg(p.av.scale + a0 + i);
         }
@@ -154,46 +158,69 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
 
     int cls = 0;
     float conf = 0.0f;
-    const int a = a0 + tid;
-    if (tid < rows) {
-      const float* row = s_clf + (size_t)tid * c;
-      float best;
-      if ((c & 3) == 0) {
-        // four independent running maxima (one per float4 lane) keep the dependency chains short; each is a
-        // first-maximum scan of its own residue class, and the merge prefers the lower index on equal values,
-        // which together is np.argmax's "first maximum wins"
-        const float4* row4 = reinterpret_cast<const float4*>(row);
-        float4 v = row4[0];
-        float b0 = v.x, b1 = v.y, b2 = v.z, b3 = v.w;
-        int i0 = 0, i1 = 1, i2 = 2, i3 = 3;
-        for (int j = 1; j < (c >> 2); ++j) {
-          v = row4[j];
-          if (v.x > b0) { b0 = v.x; i0 = 4 * j; }
-          if (v.y > b1) { b1 = v.y; i1 = 4 * j + 1; }
-          if (v.z > b2) { b2 = v.z; i2 = 4 * j + 2; }
-          if (v.w > b3) { b3 = v.w; i3 = 4 * j + 3; }
-        }
-        if (b1 > b0 || (b1 == b0 && i1 < i0)) { b0 = b1; i0 = i1; }
-        if (b3 > b2 || (b3 == b2 && i3 < i2)) { b2 = b3; i2 = i3; }
-        if (b2 > b0 || (b2 == b0 && i2 < i0)) { b0 = b2; i0 = i2; }
-        best = b0;
-        cls = i0;
-      } else {
-        best = row[0];
-        for (int j = 1; j < c; ++j) {
-          const float v = row[j];
-          if (v > best) { best = v; cls = j; }
+    const int a = a0 + row_id;
+    const bool owner = part == 0 && row_id < rows;
+    {
+      const float* row = s_clf + (size_t)row_id * c;
+      float best = -INFINITY;
+      cls = 0x7fffffff;
+      if (row_id < rows) {
+        if ((c & 3) == 0) {
+          // four independent running maxima (one per float4 lane) keep the dependency chains short; each is a
+          // first-maximum scan of its own residue class, and the merge prefers the lower index on equal values,
+          // which together is np.argmax's "first maximum wins"
+          const int nchunk = c >> 2, per = (nchunk + SPLIT - 1) / SPLIT;
+          const int j0 = part * per, j1 = min(nchunk, j0 + per);
+          if (j0 < j1) {
+            const float4* row4 = reinterpret_cast<const float4*>(row);
+            float4 v = row4[j0];
+            float b0 = v.x, b1 = v.y, b2 = v.z, b3 = v.w;
+            int i0 = 4 * j0, i1 = 4 * j0 + 1, i2 = 4 * j0 + 2, i3 = 4 * j0 + 3;
+            for (int j = j0 + 1; j < j1; ++j) {
+              v = row4[j];
+              if (v.x > b0) { b0 = v.x; i0 = 4 * j; }
+              if (v.y > b1) { b1 = v.y; i1 = 4 * j + 1; }
+              if (v.z > b2) { b2 = v.z; i2 = 4 * j + 2; }
+              if (v.w > b3) { b3 = v.w; i3 = 4 * j + 3; }
+            }
+            if (b1 > b0 || (b1 == b0 && i1 < i0)) { b0 = b1; i0 = i1; }
+            if (b3 > b2 || (b3 == b2 && i3 < i2)) { b2 = b3; i2 = i3; }
+            if (b2 > b0 || (b2 == b0 && i2 < i0)) { b0 = b2; i0 = i2; }
+            best = b0;
+            cls = i0;
+          }
+        } else {
+          const int per = (c + SPLIT - 1) / SPLIT;
+          const int j0 = part * per, j1 = min(c, j0 + per);
+          if (j0 < j1) {
+            best = row[j0];
+            cls = j0;
+            for (int j = j0 + 1; j < j1; ++j) {
+              const float v = row[j];
+              if (v > best) { best = v; cls = j; }
+            }
+          }
         }
       }
-      const float maskf = s_amask[tid] ? 1.0f : 0.0f;
-      conf = __fmul_rn(__fmul_rn(s_obj[tid], best), maskf);  // (objs*confs)*pb_mask, od_net.py:183-184
+#pragma unroll
+      for (int d = 1; d < SPLIT; d <<= 1) {  // merge the parts of a row: larger value, then lower class index
+        const float ob = __shfl_xor_sync(0xffffffffu, best, d);
+        const int oc = __shfl_xor_sync(0xffffffffu, cls, d);
+        if (ob > best || (ob == best && oc < cls)) { best = ob; cls = oc; }
+      }
+      if (owner) {
+        // a row of NaNs leaves best = -inf in every part: np.argmax returns 0 there
+        if (cls == 0x7fffffff) { cls = 0; best = row[0]; }
+        const float maskf = s_amask[row_id] ? 1.0f : 0.0f;
+        conf = __fmul_rn(__fmul_rn(s_obj[row_id], best), maskf);  // (objs*confs)*pb_mask, od_net.py:183-184
+      }
     }
     if (DENSE) {
-      if (tid < rows) {
+      if (owner) {
         const float4* s_loc = reinterpret_cast<const float4*>(st + clf_bytes + L::kOffLoc);
         const float4* s_aloc = reinterpret_cast<const float4*>(st + clf_bytes + L::kOffALoc);
         const float2* s_ascale = reinterpret_cast<const float2*>(st + clf_bytes + L::kOffAScale);
-        const float4 box = odk_decode_box(s_loc[tid], s_aloc[tid], s_ascale[tid]);
+        const float4 box = odk_decode_box(s_loc[row_id], s_aloc[row_id], s_ascale[row_id]);
         const size_t r = (size_t)b * p.n + a;
         p.classes[r] = cls;
         p.confs[r] = conf;
@@ -202,7 +229,7 @@ __global__ void __launch_bounds__(TILE) decode_score_kernel(const DecodeArgs p) 
       __syncthreads();  // every thread is done with ring slot `slot`
       if (t_issue < total_tiles) issue(t_issue, slot);
     } else {
-      const bool is_cand = (tid < rows) && (conf > p.conf_thr);
+      const bool is_cand = owner && (conf > p.conf_thr);
       const unsigned m = __ballot_sync(0xffffffffu, is_cand);
       const unsigned lane = odk_lane();
       const int warp = tid >> 5;
@@ -249,7 +276,7 @@ int sm_count_cached() {
   return sms;
 }
 
-template <int TILE, bool DENSE>
+template <int TILE, bool DENSE, int SPLIT>
 int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   using L = StageLayout<TILE, DENSE>;
   static const int env_stages = getenv("ODK_EMIT_STAGES") ? atoi(getenv("ODK_EMIT_STAGES")) : 0;
@@ -258,12 +285,12 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   args.stream_hint = env_hint;
   args.stages = (!DENSE && env_stages >= 2 && env_stages <= L::kMaxStages) ? env_stages : 3;
   const size_t smem = L::stage_bytes(args.c) * args.stages;
-  auto kern = decode_score_kernel<TILE, DENSE>;
+  auto kern = decode_score_kernel<TILE, DENSE, SPLIT>;
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   args.tiles_per_image = (args.n + TILE - 1) / TILE;
   const long long total = (long long)args.batch * args.tiles_per_image;
   int per_sm = (int)((220 * 1024) / (smem + 1024));
-  per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / TILE ? 2048 / TILE : per_sm);
+  per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / (TILE * SPLIT) ? 2048 / (TILE * SPLIT) : per_sm);
   // EMIT runs beside the train-side kernels of the same step (other graph branch): leave them shared memory
   if (!DENSE && per_sm > 2) per_sm = 2;
   if (!DENSE && env_per_sm > 0) per_sm = env_per_sm;
@@ -272,7 +299,7 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   if (grid < 1) grid = 1;
   {
     OdkProfileScope prof_(DENSE ? "decode_score_kernel" : "score_emit_kernel", stream);
-    kern<<<(unsigned)grid, TILE, smem, stream>>>(args);
+    kern<<<(unsigned)grid, TILE * SPLIT, smem, stream>>>(args);
   }
   ODK_LAUNCH_CHECK(DENSE ? "decode_score_kernel" : "score_emit_kernel");
   return ODK_OK;
@@ -302,10 +329,10 @@ int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, 
   const int c = a->num_classes;
   ODK_REQUIRE(c <= 512, ODK_ERR_UNSUPPORTED, "num_classes=%d > 512 not supported by decode_score", c);
   switch (odk_piece_size(c)) {
-    case 256: return dense ? launch_tile<256, true>(args, stream) : launch_tile<256, false>(args, stream);
-    case 128: return dense ? launch_tile<128, true>(args, stream) : launch_tile<128, false>(args, stream);
-    case 64: return dense ? launch_tile<64, true>(args, stream) : launch_tile<64, false>(args, stream);
-    default: return dense ? launch_tile<32, true>(args, stream) : launch_tile<32, false>(args, stream);
+    case 256: return dense ? launch_tile<256, true, 1>(args, stream) : launch_tile<256, false, 1>(args, stream);
+    case 128: return dense ? launch_tile<128, true, 1>(args, stream) : launch_tile<128, false, 1>(args, stream);
+    case 64: return dense ? launch_tile<64, true, 4>(args, stream) : launch_tile<64, false, 4>(args, stream);
+    default: return dense ? launch_tile<32, true, 8>(args, stream) : launch_tile<32, false, 8>(args, stream);
   }
 }
 

@@ -258,14 +258,32 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     odk_cp_async_wait<0>();
     __syncthreads();
   }
-  auto cand_key = [&](int i) -> unsigned long long {
-    if (cached) return s_cache[i];
-    int lo = 0, hi = p.n_pieces;  // largest q with s_pref[q] <= i
-    while (hi - lo > 1) {
-      const int mid = (lo + hi) >> 1;
-      if (s_pref[mid] <= i) lo = mid; else hi = mid;
+  // Visits every candidate key of the image once (any thread, any order).  Cached: a strided walk over shared memory.
+  // Not cached (more candidates than the cache holds, e.g. 57 k per image in the dense-anchor stress shape): a warp takes
+  // four pieces at a time and its lanes the pieces' entries — coalesced 8-byte loads from L2, no index search.
+  auto for_each_key = [&](auto&& f) {
+    if (cached) {
+      for (int i = tid; i < total; i += kNmsThreads) f(s_cache[i]);
+    } else {
+      constexpr int kU = 4;  // pieces in flight per warp: their loads are independent, the L2 round trips overlap
+      for (int q0 = warp * kU; q0 < p.n_pieces; q0 += kNmsWarps * kU) {
+        int cnt[kU], maxc = 0;
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+          cnt[u] = (q0 + u < p.n_pieces) ? s_pref[q0 + u + 1] - s_pref[q0 + u] : 0;
+          maxc = max(maxc, cnt[u]);
+        }
+        const unsigned long long* src = keys + (size_t)q0 * p.piece;
+        for (int sl = lane; sl < maxc; sl += 32) {
+          unsigned long long k[kU];
+#pragma unroll
+          for (int u = 0; u < kU; ++u) k[u] = (sl < cnt[u]) ? src[(size_t)u * p.piece + sl] : 0ull;
+#pragma unroll
+          for (int u = 0; u < kU; ++u)
+            if (sl < cnt[u]) f(k[u]);
+        }
+      }
     }
-    return keys[(size_t)lo * p.piece + (i - s_pref[lo])];
   };
 
   int nkept = 0, processed = 0;
@@ -284,13 +302,12 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     want = min(kBand, want);
     if (remaining > kBand) {
       unsigned long long kmin = ~0ull, kmax = 0ull;
-      for (int i = tid; i < total; i += kNmsThreads) {
-        const unsigned long long k = cand_key(i);
+      for_each_key([&](unsigned long long k) {
         if (k < hi_key) {
           kmin = k < kmin ? k : kmin;
           kmax = k > kmax ? k : kmax;
         }
-      }
+      });
 #pragma unroll
       for (int d = 16; d > 0; d >>= 1) {
         const unsigned long long omin = __shfl_xor_sync(0xffffffffu, kmin, d), omax = __shfl_xor_sync(0xffffffffu, kmax, d);
@@ -311,10 +328,9 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
         const int width = top - shift;
         for (int i = tid; i < kBins; i += kNmsThreads) s_hist[i] = 0;
         __syncthreads();
-        for (int i = tid; i < total; i += kNmsThreads) {
-          const unsigned long long k = cand_key(i);
+        for_each_key([&](unsigned long long k) {
           if (k < hi_key && (top >= 64 || (k >> top) == prefix)) atomicAdd(&s_hist[(int)((k >> shift) & (unsigned long long)((1 << width) - 1))], 1);
-        }
+        });
         __syncthreads();
         // walk the digits from the top: largest r such that above + S(r) <= kBand, S = inclusive sum over reversed bins
         const int nb_bins = 1 << width;
@@ -369,13 +385,12 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     if (tid == 0) s_nb = 0;
     for (int i = tid; i < ODK_MAX_CLASSES / 32; i += kNmsThreads) s_clsbits[i] = 0u;
     __syncthreads();
-    for (int i = tid; i < total; i += kNmsThreads) {
-      const unsigned long long k = cand_key(i);
+    for_each_key([&](unsigned long long k) {
       if (k < hi_key && k >= lo_key) {
         const int pos = atomicAdd(&s_nb, 1);
         if (pos < kBand) s_band[pos] = k;
       }
-    }
+    });
     __syncthreads();
     const int nb = min(s_nb, kBand);
     int n_sort = 32;
