@@ -426,23 +426,24 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
       ++r;  // warp 0 resumes with the next GT (other warps' r is unused)
     }
   }
-  if (warp != 0) return;
-  err = __shfl_sync(0xffffffffu, err, 0);
+  // every thread holds the same `err` (it changes only in the CTA-wide fallback); pick[] is complete and visible (the
+  // loop's last barrier).  The output order needs each pick's rank among all picks: O(G^2), shared by the whole CTA.
   if (err) {
-    for (int g = lane; g < p.gmax; g += 32) { out_pb[g] = -1; out_gt[g] = -1; }
-    if (lane == 0) p.status[b] = err;
+    for (int g = threadIdx.x; g < p.gmax; g += kGreedyThreads) { out_pb[g] = -1; out_gt[g] = -1; }
+    if (threadIdx.x == 0) p.status[b] = err;
     return;
   }
   // np.where(pb_assigned_gt >= 0): ascending anchor index (od_pb.py:359); picks are unique
-  for (int g = lane; g < G; g += 32) {
+  for (int g = threadIdx.x; g < G; g += kGreedyThreads) {
     const int mine = pick[g];
     int rk = 0;
+#pragma unroll 4
     for (int j = 0; j < G; ++j) rk += pick[j] < mine;
     out_pb[rk] = mine;
     out_gt[rk] = g;
   }
-  for (int g = G + lane; g < p.gmax; g += 32) { out_pb[g] = -1; out_gt[g] = -1; }
-  if (lane == 0) p.status[b] = ODK_IMG_OK;
+  for (int g = G + threadIdx.x; g < p.gmax; g += kGreedyThreads) { out_pb[g] = -1; out_gt[g] = -1; }
+  if (threadIdx.x == 0) p.status[b] = ODK_IMG_OK;
 }
 
 __global__ void compute_iou_kernel(const float4* __restrict__ a, int na, const float4* __restrict__ b, int nb, float* __restrict__ out) {
