@@ -518,3 +518,84 @@ def test_loss_gradient_vs_oracle_and_autograd(prior_boxes, oracle_tables, name, 
     (loss * torch.from_numpy(up).cuda()).sum().backward()
     assert torch.equal(yp.grad, torch.from_numpy(got).cuda())
     np.testing.assert_allclose(loss.detach().cpu().numpy(), R.od_losses(t, y_true.cpu().numpy(), y_pred)['loss'], rtol=2e-5)
+
+
+# ----------------------------------------------------------------------------------------- concurrency and randomised sweeps
+def test_concurrent_host_threads_on_own_streams(prior_boxes, oracle_tables):
+    """The reference calls encode_truth from a pool of host threads (generator.py:160-166).  Eight threads, each on its
+    own CUDA stream, hammer both sides of the path with different inputs; every result must equal the serial one
+    (no global mutable state in the library, per-thread side stream and error slot)."""
+    import threading
+    pb = prior_boxes('voc320')
+    n = len(pb)
+    jobs = []
+    for k in range(8):
+        gt = synth.gt_batch(100 + k, 6, 12, 20, crowded_every=3)
+        head = synth.predictions(200 + k, 3, n, 20, clustered=bool(k % 2))
+        jobs.append((gt, head))
+    want = [(pb.encode_truth_batch(*gt)['y_true'].clone(), pb.decode_nms(*head).clone()) for gt, head in jobs]
+    torch.cuda.synchronize()
+    got, errors = [None] * len(jobs), []
+
+    def work(k):
+        try:
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                for _ in range(5):
+                    y = pb.encode_truth_batch(*jobs[k][0])['y_true']
+                    d = pb.decode_nms(*jobs[k][1], nms_all_threshold=0.5 if k == 3 else None)
+                    d = pb.decode_nms(*jobs[k][1])
+                st.synchronize()
+            got[k] = (y, d)
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=work, args=(k,)) for k in range(len(jobs))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for (wy, wd), (gy, gd) in zip(want, got):
+        assert torch.equal(wy, gy) and torch.equal(wd, gd)
+
+
+def test_randomised_small_cases_vs_oracle(prior_boxes, oracle_tables):
+    """A few hundred small random problems per side: odd ground-truth counts, tiny and border-touching boxes, random
+    thresholds and top_k, equal boxes — every assignment and every kept set equals the oracle's."""
+    rng = np.random.RandomState(20261104)
+    pb, t = prior_boxes('tiny128'), oracle_tables('tiny128')
+    checked = 0
+    for trial in range(120):
+        g = int(rng.randint(1, 9))
+        size = [(0.02, 0.1), (0.05, 0.5), (0.3, 0.95)][trial % 3]
+        boxes = synth.gt_boxes(rng, g, size=size)
+        if trial % 5 == 0:
+            boxes[0, :2] = 0.0      # touches the top-left border
+        if trial % 7 == 0:
+            boxes[-1, 2:] = 1.0     # touches the bottom-right border
+        boxes = boxes.astype(np.float32)
+        try:
+            ri, rg, rv = R.assign_boxes(t, boxes)
+        except AssertionError:
+            with pytest.raises(AssertionError):
+                pb._assign_boxes(boxes)
+            continue
+        gi, gg, gv = pb._assign_boxes(boxes)
+        assert np.array_equal(gi, ri) and np.array_equal(gg, rg) and np.array_equal(gv, rv), trial
+        checked += 1
+    assert checked >= 60
+    for trial in range(120):
+        n = int(rng.randint(1, 400))
+        hubs = rng.uniform(0.2, 0.8, size=(int(rng.randint(1, 6)), 2))
+        ctr = hubs[rng.randint(0, len(hubs), size=n)]
+        ctr = ctr + rng.normal(0, [0.01, 0.05, 0.2][trial % 3], size=(n, 2))
+        wh = rng.uniform(0.02, 0.4, size=(n, 2))
+        b = np.clip(np.concatenate([ctr - wh / 2, ctr + wh / 2], 1), 0, 1).astype(np.float32)
+        if n > 3:
+            b[1] = b[0]             # identical boxes
+            b[2, 2] = b[2, 0]       # zero width
+        s = (rng.permutation(n).astype(np.float32) + 1) / np.float32(n + 1)
+        top_k = int(rng.choice([1, 2, 5, 50, 200]))
+        thr = float(rng.choice([0.3, 0.45, 0.5, 0.7]))
+        assert np.array_equal(odk.ml.non_maximum_suppression(b, s, top_k, thr), R.numpy_nms_policy(b, s, top_k, thr)), trial
