@@ -235,6 +235,34 @@ int odk_exact_match(int n_img, int top_k, const float* dets /*[dev n_img,top_k,6
                     const int32_t* gt_offsets /*[dev n_img+1]*/, float conf_thr, float iou_thr,
                     uint8_t* match /*[dev n_img]*/, void* stream);
 
+/* Bounding-box side of the augmentation upstream of encode_truth, for a padded batch of ground truth:
+ * RandomZoom._padding / _crop (image.py:321-388) and the letterbox of a failed zoom (image.py:298-314).
+ * kind[b]: 0 leave alone, 1 zoom-out (paste at try_xy inside a try_size canvas), 2 zoom-in (crop window
+ * try_xy..try_xy+try_size), 3 letterbox (in_size = resized image, try_size = output, try_xy = origin; always
+ * accepted).  Each image walks its `tries` attempts in order, as the reference's retry loop does, and takes the
+ * first acceptable one: chosen[b] = its index or -1 (boxes then pass through unchanged).  boxes are fp64 holding
+ * either fp32 values straight from ObjectsAnnotation (src_f32 = 1: centre and area are then taken in fp32, as NumPy
+ * does) or the fp64 result of an earlier step.  keep[b,g] = 0 for boxes the crop drops (image.py:355-363);
+ * wide[b] = 1 once the boxes of image b are fp64 values in the reference. */
+int odk_bbox_zoom(int batch, int gmax, int tries, const double* boxes /*[dev B,Gmax,4]*/, int src_f32,
+                  const int32_t* gt_count /*[dev B]*/, const int32_t* kind /*[dev B]*/,
+                  const int64_t* in_size /*[dev B,2] w,h*/, const int64_t* try_size /*[dev B,tries,2]*/,
+                  const int64_t* try_xy /*[dev B,tries,2]*/, int out_w, int out_h, double min_object_px,
+                  double* boxes_out /*[dev B,Gmax,4]*/, uint8_t* keep /*[dev B,Gmax]*/,
+                  int32_t* chosen /*[dev B]*/, uint8_t* wide /*[dev B]*/, void* stream);
+
+/* RandomFlipLR / RandomFlipTB (image.py:433-465) then ObjectsAnnotation.rot90 (ml.py:102-112), in that order
+ * (od.py:160-165), followed by the order-preserving removal of boxes with keep = 0.  ops[b]: bit 0 flip
+ * left-right, bit 1 flip top-bottom, bits 2-3 the number of quarter turns.  1-x is taken in fp32 for images whose
+ * wide flag is 0 (NULL: all).  Outputs feed odk_assign_encode directly: boxes_out fp32 [B,Gmax,4], classes_out,
+ * count_out (rows beyond the count are zero); boxes64_out (optional) keeps the unrounded values. */
+int odk_bbox_flip_rot(int batch, int gmax, const double* boxes /*[dev B,Gmax,4]*/,
+                      const uint8_t* keep /*[dev B,Gmax] or NULL*/, const int32_t* gt_classes /*[dev B,Gmax]*/,
+                      const int32_t* gt_count /*[dev B]*/, const uint8_t* wide /*[dev B] or NULL*/,
+                      const int32_t* ops /*[dev B]*/, double* boxes64_out /*[dev B,Gmax,4] or NULL*/,
+                      float* boxes_out /*[dev B,Gmax,4]*/, int32_t* classes_out /*[dev B,Gmax]*/,
+                      int32_t* count_out /*[dev B]*/, void* stream);
+
 /* Diagnostics: in-kernel timeline of the six kernels of a step (candidates, greedy, rows, patch, emit, nms).
  * buf = 12 device words, word 2*id = earliest CTA entry (initialise to UINT64_MAX), word 2*id+1 = latest CTA exit
  * (initialise to 0), in %globaltimer nanoseconds; NULL switches it off.  Works inside CUDA-graph replays. */

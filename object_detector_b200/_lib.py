@@ -11,6 +11,7 @@ _PKG = pathlib.Path(__file__).resolve().parent
 LIB_PATH = _PKG / 'libodk.so'
 
 c_int, c_float, c_size_t, c_void_p, c_int64 = ctypes.c_int, ctypes.c_float, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_int64
+c_double = ctypes.c_double
 
 # name -> (restype, argtypes); kept in one table so tests can check it against include/odk.h
 SIGNATURES = {
@@ -60,6 +61,10 @@ SIGNATURES = {
     'odk_confusion_matrix': (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p,
                                      c_void_p]),
     'odk_exact_match': (c_int, [c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p]),
+    'odk_bbox_zoom': (c_int, [c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                             c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    'odk_bbox_flip_rot': (c_int, [c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                 c_void_p, c_void_p, c_void_p]),
     'odk_timeline_set': (c_int, [c_void_p]),
     'odk_profile_enable': (c_int, [c_int]),
     'odk_profile_read': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),

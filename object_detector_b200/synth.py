@@ -90,3 +90,24 @@ def eval_set(seed, n_img, num_classes, max_gt=6, difficult_frac=0.1, n_fp=20):
                       np.concatenate([ps, fs])[ok].astype(np.float32), boxes[ok]))
         gts.append((w, h, gc, gb, gd))
     return gts, preds
+
+
+AUGMENT_CONFIGS = {
+    # name: (output_size, keep_aspect, RandomZoom keyword arguments) — od.py:156-165 defaults first
+    'default': (320, False, {}),
+    'keep_aspect': (320, True, {}),
+    'pad_only': (300, False, {'crop_rate': None}),
+    'crop_only': (512, True, {'padding_rate': None, 'min_object_px': 24}),
+}
+
+
+def augment_inputs(seed, count):
+    """Seeded annotations for the augmentation vectors: image size, f32 boxes, classes, per-sample RNG seed."""
+    rng = np.random.RandomState(seed)
+    out = []
+    for i in range(count):
+        w, h = int(rng.randint(120, 640)), int(rng.randint(120, 640))
+        g = int(rng.randint(1, 9))
+        boxes = gt_boxes(rng, g, size=[(0.03, 0.2), (0.1, 0.6), (0.3, 0.9)][i % 3])
+        out.append((w, h, boxes, rng.randint(0, 20, size=g).astype(np.int32), int(rng.randint(0, 2 ** 31))))
+    return out

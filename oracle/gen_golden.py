@@ -204,6 +204,38 @@ def gen_check_prior_boxes():
     (OUT / 'check_prior_boxes.txt').write_text(buf.getvalue(), encoding='utf-8')
 
 
+def gen_augment():
+    """Bounding-box side of RandomZoom -> RandomFlipLR -> RandomFlipTB -> RandomRotate90 (image.py:233-485,
+    ml.py:102-112) of the unmodified reference, per-sample RandomState(seed) as generator.py:172 makes it."""
+    import types
+    tk = ref_loader.load_augment()
+    ctx = types.SimpleNamespace(do_augmentation=lambda rand, probability=1: probability >= 1 or rand.rand() <= probability)
+    d = {}
+    for name, (size, keep_aspect, kw) in synth.AUGMENT_CONFIGS.items():
+        ops = [tk.image.RandomZoom(probability=1, output_size=(size, size), keep_aspect=keep_aspect, **kw),
+               tk.image.RandomFlipLR(probability=0.5), tk.image.RandomFlipTB(probability=0.5),
+               tk.image.RandomRotate90(probability=1)]
+        boxes, classes, counts, nxt = [], [], [], []
+        for w, h, b, c, seed in synth.augment_inputs(911, 160):
+            ann = tk.ml.ObjectsAnnotation('.', w, h, c, b)
+            rand = np.random.RandomState(seed)
+            x, y = np.zeros((h, w, 3), np.float32), ann
+            for op in ops:
+                x, y, _ = op.execute(x, y, None, rand, ctx)
+            assert x.shape[:2] == (size, size)
+            boxes.append(np.asarray(y.bboxes, dtype=np.float64).reshape(-1, 4))
+            classes.append(np.asarray(y.classes, dtype=np.int32))
+            counts.append(len(y.classes))
+            nxt.append(rand.rand())
+        d[name + '_boxes'] = np.concatenate(boxes)
+        d[name + '_classes'] = np.concatenate(classes)
+        d[name + '_counts'] = np.asarray(counts, np.int32)
+        d[name + '_next_draw'] = np.asarray(nxt, np.float64)
+    np.savez_compressed(OUT / 'augment.npz', **d)
+    print('augment.npz', {k: v.shape for k, v in d.items() if k.endswith('_counts')},
+          'dropped', {n: int(sum(len(i[3]) for i in synth.augment_inputs(911, 160)) - d[n + '_counts'].sum()) for n in synth.AUGMENT_CONFIGS})
+
+
 if __name__ == '__main__':
     OUT.mkdir(parents=True, exist_ok=True)
     gen_check_prior_boxes()
@@ -211,5 +243,6 @@ if __name__ == '__main__':
     gen_iou_nms_decode()
     gen_assign()
     gen_scores()
+    gen_augment()
     for p in sorted(OUT.glob('*.npz')):
         print(p.name, p.stat().st_size)

@@ -65,3 +65,25 @@ def load():
         parent, _, leaf = name.rpartition('.')
         setattr(dl if parent == 'dl' else pkg, leaf, mod)
     return pkg
+
+
+def load_augment():
+    """``load()`` plus the reference's generator / image modules (image.py:233-485), for the bounding-box side of the
+    augmentation pipeline.  OpenCV is absent here, so the three PIXEL functions RandomZoom calls (ndimage.resize /
+    pad_ltrb / crop) are replaced by shape-only stand-ins; every line of box arithmetic and every RNG draw is the
+    reference's own."""
+    pkg = load()
+    if hasattr(pkg, 'image'):
+        return pkg
+    for name in ('data_utils', 'generator', 'image'):
+        full = 'pytoolkit.' + name
+        spec = importlib.util.spec_from_file_location(full, REFERENCE_ROOT / (name + '.py'))
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[full] = mod
+        spec.loader.exec_module(mod)
+        setattr(pkg, name, mod)
+    nd = pkg.ndimage
+    nd.resize = lambda rgb, width, height, padding=None, interp='lanczos': np.zeros((int(height), int(width), rgb.shape[2]), np.float32)
+    nd.pad_ltrb = lambda rgb, x1, y1, x2, y2, padding='edge': np.zeros((rgb.shape[0] + int(y1) + int(y2), rgb.shape[1] + int(x1) + int(x2), rgb.shape[2]), np.float32)
+    nd.crop = lambda rgb, x, y, width, height: rgb[int(y):int(y) + int(height), int(x):int(x) + int(width), :]
+    return pkg

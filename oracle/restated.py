@@ -645,3 +645,110 @@ def od_loss_grad(t: AnchorTables, y_true, y_pred, upstream=None):
     if upstream is not None:
         g *= np.asarray(upstream, np.float64)[:, None, None]
     return g
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Bounding-box side of the augmentation pipeline: RandomZoom -> RandomFlipLR -> RandomFlipTB -> RandomRotate90
+# (image.py:233-388, 433-485; ml.py:102-112; per-sample RandomState, generator.py:172).  Pixel work is not restated.
+AUGMENT_DEFAULTS = dict(keep_aspect=False, padding_rate=16, crop_rate=0.1, aspect_prob=0.5, max_aspect_ratio=1.5,
+                        min_object_px=8, flip_lr=True, flip_tb=True, rotate90=True, tries=30)
+
+
+def zoom_try_pad(boxes, in_size, padded, xy, out_size, min_px):
+    """One zoom-out attempt (image.py:328-333): boxes pasted at ``xy`` inside a ``padded`` canvas; rejected when any
+    box side, in output pixels, drops below ``min_px``.  Integer sizes widen the product to fp64."""
+    s2, p2, x2, o2 = (np.concatenate([np.asarray(v, np.int64)] * 2) for v in (in_size, padded, xy, out_size))
+    moved = (x2 + boxes * s2) / p2
+    px = moved * o2
+    return not bool((px[:, 2:] - px[:, :2] < min_px).any()), moved
+
+
+def zoom_try_crop(boxes, in_size, wh, xy, out_size, min_px):
+    """One zoom-in attempt (image.py:350-375).  Returns (accepted, boxes, keep): a box survives when its centre lies
+    in the window (low <= c < high, math.py:14-17) and at least 30 % of its area does; no survivor, or any box (kept
+    or not) narrower than ``min_px`` output pixels after clipping, rejects the attempt.  Centre and area are taken in
+    the dtype the boxes arrive in (fp32 straight from ObjectsAnnotation), the rest in fp64."""
+    in_size, wh, xy = (np.asarray(v, np.int64) for v in (in_size, wh, xy))
+    window = np.concatenate([xy, xy + wh]) / np.concatenate([in_size, in_size])
+    centre = (boxes[:, 2:] + boxes[:, :2]) / 2
+    area = (boxes[:, 2:] - boxes[:, :2]).prod(axis=-1)
+    keep = np.logical_and(window[:2] <= centre, centre < window[2:]).all(axis=-1)
+    if not keep.any():
+        return False, None, None
+    lo = np.maximum(window[None, :2], boxes[:, :2])
+    hi = np.minimum(window[None, 2:], boxes[:, 2:])
+    visible = (hi - lo).prod(axis=-1) * (lo < hi).all(axis=-1)
+    keep = np.logical_and(keep, visible >= area * 0.3)
+    moved = np.clip((boxes * np.concatenate([in_size, in_size]) - np.concatenate([xy, xy])) / np.concatenate([wh, wh]), 0, 1)
+    px = moved * np.concatenate([np.asarray(out_size, np.int64)] * 2)
+    if (px[:, 2:] - px[:, :2] < min_px).any():
+        return False, None, None
+    return True, moved, keep
+
+
+def flip_rot_boxes(boxes, flip_lr, flip_tb, k):
+    """RandomFlipLR / RandomFlipTB / ObjectsAnnotation.rot90 on (G,4) boxes, in the dtype they arrive in
+    (image.py:445,462; ml.py:102-112)."""
+    b = boxes.copy()
+    one = b.dtype.type(1)
+    if flip_lr:
+        b[:, [0, 2]] = one - b[:, [2, 0]]
+    if flip_tb:
+        b[:, [1, 3]] = one - b[:, [3, 1]]
+    x1, y1, x2, y2 = (b[:, i].copy() for i in range(4))
+    if k == 1:
+        b = np.stack([y1, one - x2, y2, one - x1], axis=1)
+    elif k == 2:
+        b = np.stack([one - x2, one - y2, one - x1, one - y1], axis=1)
+    elif k == 3:
+        b = np.stack([one - y2, x1, one - y1, x2], axis=1)
+    return b
+
+
+def augment_boxes_sample(rand, width, height, boxes, classes, output_size, **cfg):
+    """The whole box pipeline for one sample, drawing from ``rand`` in the reference's order (image.py:283-319, then
+    :441-479).  Returns (boxes, classes, info); boxes are fp64 once a zoom or letterbox touched them, else fp32."""
+    c = dict(AUGMENT_DEFAULTS, **cfg)
+    out = np.array([output_size, output_size] if np.isscalar(output_size) else output_size, np.int64)
+    in_size = np.array([width, height], np.int64)
+    boxes = np.asarray(boxes, np.float32).reshape(-1, 4)
+    classes = np.asarray(classes)
+    base_ar = width / height if c['keep_aspect'] else out[0] / out[1]
+    lo_ar, hi_ar = np.log(1 / c['max_aspect_ratio']), np.log(c['max_aspect_ratio'])
+    rand_ar = np.exp(rand.uniform(lo_ar, hi_ar)) if rand.rand() <= c['aspect_prob'] else 1
+    root = np.sqrt(base_ar * rand_ar)
+    ar = np.array([root, 1 / root])
+    pad = c['padding_rate'] is not None and (c['crop_rate'] is None or rand.rand() <= 0.5)
+    info = {'kind': 'pad' if pad else 'crop', 'chosen': -1}
+    for t in range(c['tries']):
+        if pad:
+            rate = rand.uniform(1, np.sqrt(c['padding_rate']))
+            size = np.maximum(np.ceil(in_size * rate * ar).astype(int), in_size)
+            slack = size - in_size
+        else:
+            rate = rand.uniform(np.sqrt(c['crop_rate']), 1)
+            size = np.minimum(np.floor(in_size * rate * ar).astype(int), in_size)
+            slack = in_size - size
+        xy = np.array([rand.randint(0, slack[0] + 1), rand.randint(0, slack[1] + 1)])
+        if pad:
+            ok, moved = zoom_try_pad(boxes, in_size, size, xy, out, c['min_object_px'])
+            keep = None
+        else:
+            ok, moved, keep = zoom_try_crop(boxes, in_size, size, xy, out, c['min_object_px'])
+        if ok:
+            boxes = moved if keep is None else moved[keep]
+            classes = classes if keep is None else classes[keep]
+            info['chosen'] = t
+            break
+    if info['chosen'] < 0 and c['keep_aspect'] and not (in_size == out).all():
+        # every attempt failed: letterbox into the output (image.py:298-314)
+        scale = (out / in_size).min()
+        resized = np.floor(in_size * scale + 0.1).astype(np.int32)
+        origin = (out - resized) // 2
+        boxes = (np.concatenate([origin, origin]) + boxes * np.concatenate([resized, resized])) / np.concatenate([out, out])
+        info['letterbox'] = (origin, resized)
+    lr = c['flip_lr'] and rand.rand() <= 0.5
+    tb = c['flip_tb'] and rand.rand() <= 0.5
+    k = int(rand.randint(0, 4)) if c['rotate90'] else 0
+    info.update(flip_lr=bool(lr), flip_tb=bool(tb), k=k)
+    return flip_rot_boxes(boxes, lr, tb, k), classes, info

@@ -599,3 +599,72 @@ def test_randomised_small_cases_vs_oracle(prior_boxes, oracle_tables):
         top_k = int(rng.choice([1, 2, 5, 50, 200]))
         thr = float(rng.choice([0.3, 0.45, 0.5, 0.7]))
         assert np.array_equal(odk.ml.non_maximum_suppression(b, s, top_k, thr), R.numpy_nms_policy(b, s, top_k, thr)), trial
+
+
+# ----------------------------------------------------------------------------------------- box side of the augmentation (f2)
+def _augment_batch(samples):
+    gmax = max(len(s[3]) for s in samples)
+    boxes = np.zeros((len(samples), gmax, 4), np.float32)
+    classes = np.zeros((len(samples), gmax), np.int32)
+    count = np.zeros(len(samples), np.int32)
+    for i, (_, _, b, c, _) in enumerate(samples):
+        boxes[i, :len(c)], classes[i, :len(c)], count[i] = b, c, len(c)
+    sizes = np.array([[s[0], s[1]] for s in samples], np.int64)
+    return boxes, classes, count, sizes
+
+
+@pytest.mark.parametrize('name', sorted(synth.AUGMENT_CONFIGS))
+def test_box_augmenter_matches_reference_vectors(golden, name):
+    """odk_bbox_zoom + odk_bbox_flip_rot over a whole batch against the vectors of the unmodified reference
+    (tests/golden/augment.npz): surviving boxes bit-exact in fp64, classes, counts, and every sample's RandomState left
+    where the reference leaves it."""
+    from object_detector_b200.bbox_augment import BoxAugmenter
+    size, keep_aspect, kw = synth.AUGMENT_CONFIGS[name]
+    samples = synth.augment_inputs(911, 160)
+    boxes, classes, count, sizes = _augment_batch(samples)
+    rands = [np.random.RandomState(s[4]) for s in samples]
+    out = BoxAugmenter(size, keep_aspect=keep_aspect, **kw)(boxes, classes, count, sizes, rands)
+    g = golden['augment']
+    assert np.array_equal(out['gt_count'].cpu().numpy(), g[name + '_counts'])
+    b64, b32, cls = out['boxes64'].cpu().numpy(), out['gt_boxes'].cpu().numpy(), out['gt_classes'].cpu().numpy()
+    at = 0
+    for i, n in enumerate(g[name + '_counts']):
+        assert np.array_equal(b64[i, :n], g[name + '_boxes'][at:at + n]), (name, i)
+        assert np.array_equal(cls[i, :n], g[name + '_classes'][at:at + n])
+        assert np.array_equal(b32[i, :n], g[name + '_boxes'][at:at + n].astype(np.float32))
+        assert not b64[i, n:].any() and not cls[i, n:].any()
+        assert rands[i].rand() == g[name + '_next_draw'][i]
+        at += n
+
+
+def test_box_augmenter_vs_oracle_and_feeds_encode_truth(prior_boxes, oracle_tables):
+    """Fresh seeds (not in the vectors), larger ground-truth counts (more than one warp pass), then straight into
+    encode_truth_batch on the device: every augmented image still encodes without an error status."""
+    from object_detector_b200.bbox_augment import BoxAugmenter
+    rng = np.random.RandomState(31)
+    samples = []
+    for i in range(96):
+        g = int(rng.randint(1, 70))
+        samples.append((int(rng.randint(200, 700)), int(rng.randint(200, 700)), synth.gt_boxes(rng, g, size=(0.05, 0.3)),
+                        rng.randint(0, 20, size=g).astype(np.int32), int(rng.randint(0, 2 ** 31))))
+    boxes, classes, count, sizes = _augment_batch(samples)
+    rands = [np.random.RandomState(s[4]) for s in samples]
+    aug = BoxAugmenter(320, keep_aspect=True, min_object_px=4)
+    out = aug(boxes, classes, count, sizes, rands)
+    cnt, b64, cls = out['gt_count'].cpu().numpy(), out['boxes64'].cpu().numpy(), out['gt_classes'].cpu().numpy()
+    for i, (w, h, b, c, seed) in enumerate(samples):
+        rand = np.random.RandomState(seed)
+        ob, oc, info = R.augment_boxes_sample(rand, w, h, b, c, 320, keep_aspect=True, min_object_px=4)
+        assert cnt[i] == len(oc) and np.array_equal(b64[i, :cnt[i]], ob.astype(np.float64)) and np.array_equal(cls[i, :cnt[i]], oc)
+        assert info['chosen'] == out['plan']['chosen'][i] and info['k'] == out['plan']['k'][i]
+        assert rand.rand() == rands[i].rand()
+    pb = prior_boxes('voc320')
+    res = pb.encode_truth_batch(out['gt_boxes'], out['gt_classes'], out['gt_count'])
+    status = res['status'].cpu().numpy()
+    live = cnt > 0
+    assert (status[live] == 0).mean() > 0.9     # a zoom can push a centre out of every cell; the reference raises there too
+    ok = np.nonzero(live & (status == 0))[0][:8]
+    t = oracle_tables('voc320')
+    for i in ok:
+        want = R.encode_truth(t, [(cls[i, :cnt[i]], out['gt_boxes'][i, :cnt[i]].cpu().numpy())])[0]
+        assert np.array_equal(res['y_true'][i].cpu().numpy(), want)
