@@ -26,7 +26,8 @@ if ROOT not in sys.path:
 
 METRIC = 'images/sec assign+decode+NMS @640x640'
 B, N, C, GMAX, TOPK = 64, 16800, 20, 64, 200
-ROT = 3  # distinct input sets rotated through so every step reads data that is not L2-resident
+ROT = 4  # distinct input sets rotated through so every step reads data that is not L2-resident
+LANES = 4  # batches in flight (pipeline.StepRing): a slot (= input set + its outputs) always runs on lane slot % LANES
 WORKLOAD = 'cfg2+cfg3: Darknet53 640x640 VOC anchors (N=16800, C=20), batch 64: assign+encode (<=64 GT/img) + decode + per-class NMS (top-k 200)'
 
 # algorithmic HBM bytes per image
@@ -210,8 +211,9 @@ def run_cuda(args):
         objs, clfs, locs = synth.predictions(1234 + 100 * rank + r, B, N, C)
         host_sets.append((gtb, gtc, gtn, objs, clfs, locs))
     dev_sets = [tuple(torch.from_numpy(x).to(dev) for x in s) for s in host_sets]
-    y_true = torch.empty((B, N, 3 + C + 4), dtype=torch.float32, device=dev)
-    dets = torch.empty((B, TOPK, 6), dtype=torch.float32, device=dev)
+    y_trues = [torch.empty((B, N, 3 + C + 4), dtype=torch.float32, device=dev) for _ in range(ROT)]
+    detss = [torch.empty((B, TOPK, 6), dtype=torch.float32, device=dev) for _ in range(ROT)]
+    y_true, dets = y_trues[0], detss[0]
 
     def step_eager(i):
         gtb, gtc, gtn, objs, clfs, locs = dev_sets[i % ROT]
@@ -236,23 +238,41 @@ def run_cuda(args):
     torch.cuda.synchronize()
     # one CUDA graph per input set: the train side and the predict side of a step are independent and run on
     # parallel branches; replaying removes the per-launch host cost of the five small kernels
-    graphs = None
-    if not args.no_graph:
-        graphs = [pipeline.capture_step(pb, s[:3], s[3:], y_true, dets, top_k=TOPK) for s in dev_sets]
+    # and `lanes` batches in flight: the latency-bound tail of one batch runs beside the HBM-bound head of the next
+    lanes = max(1, min(args.lanes, ROT))
+    while ROT % lanes:
+        lanes -= 1
+    slots = [(s[:3], s[3:], y_trues[k], detss[k]) for k, s in enumerate(dev_sets)]
+    ring = pipeline.StepRing(pb, slots, lanes=lanes, top_k=TOPK, use_graph=not args.no_graph)
+    graphs = ring.graphs
 
-    def step(i):
-        if graphs is not None:
-            graphs[i % ROT].replay()
-        else:
-            step_eager(i)
+    def timed_ring(steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ring.fork()
+        for i in range(steps):
+            ring.submit(i)
+        ring.join()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
 
-    for i in range(max(args.warmup, 3)):
-        step(i)
+    timed_ring(max(args.warmup, 3))
     sampler = ClockSampler(local)
     sampler.start()
-    ms_total = timed(step, args.steps)
+    ms_total = timed_ring(args.steps)
     clocks = sampler.stop()
     value = B * world * args.steps / (ms_total * 1e-3)
+    # the same K steps with one batch in flight (latency of a step, and the figure earlier rounds reported)
+    one = pipeline.StepRing(pb, slots, lanes=1, top_k=TOPK, use_graph=not args.no_graph) if lanes > 1 else ring
+    ring_saved, ring = ring, one
+    timed_ring(3)
+    ms_serial = timed_ring(args.steps)
+    ring = ring_saved
 
     # ---- per-kernel device time over the same K steps (second pass, library event hooks on)
     _lib.profile_enable(True)
@@ -333,7 +353,9 @@ def run_cuda(args):
             'dtype': 'f32', 'data': 'synthetic',
             'config': {'workload': WORKLOAD, 'batch_per_gpu': B, 'anchors': N, 'classes': C, 'gt_max': GMAX, 'top_k': TOPK,
                        'l2': f'inputs rotate over {ROT} distinct sets ({ROT * (h2d + B * N * 27 * 4) >> 20} MB touched) > 126 MB L2',
-                       'launch': 'eager' if graphs is None else 'CUDA graph per input set, train and predict sides on parallel branches',
+                       'launch': ('eager' if graphs is None else 'CUDA graph per input set, train and predict sides on parallel branches')
+                       + f'; {lanes} batches in flight on {lanes} streams (each slot has its own inputs, y_true, detections, workspaces)',
+                       'batches_in_flight': lanes, 'ms_per_step_one_in_flight': ms_serial / args.steps,
                        'parallelism': f'images sharded over {world} GPU(s), no data-path collective'},
             'clocks': clocks, 'e2e': {'value': e2e_value, 'unit': 'images/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                                       'steps': e2e_steps},
@@ -356,6 +378,7 @@ def main():
     ap.add_argument('--impl', default='cuda', choices=['cuda', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-graph', action='store_true', help='eager launches instead of CUDA-graph replay')
+    ap.add_argument('--lanes', type=int, default=LANES, help='batches in flight (1 = one step at a time)')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

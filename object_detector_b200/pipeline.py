@@ -37,6 +37,55 @@ def capture_step(pb, gt, head, y_true, dets, top_k=200, conf_threshold=0.01, nms
     return graph
 
 
+class StepRing:
+    """Device-resident batches, several in flight.
+
+    The six kernels of a step leave most of the GPU idle most of the time (two of them are HBM-bound for ~20 us each,
+    the other four are latency-bound chains on 64-128 SMs), and consecutive batches are independent — so the graphs of
+    consecutive steps are replayed round-robin on ``lanes`` streams and the tail of batch i (per-image NMS, greedy walk,
+    positives) runs beside the head of batch i+1 (score/emit, candidates).  Every slot owns its inputs, outputs and
+    workspaces; a slot is always replayed on the same lane, so reuse of a slot is ordered by that stream.
+
+    ``slots``: list of ``(gt, head, y_true, dets)`` with ``gt = (boxes, classes, count)``, ``head = (objs, clfs, locs)``
+    CUDA tensors that keep their addresses; ``len(slots)`` must be a multiple of ``lanes``.
+    """
+
+    def __init__(self, pb, slots, lanes=4, top_k=200, conf_threshold=0.01, nms_threshold=0.45, use_graph=True):
+        assert len(slots) >= 1 and lanes >= 1 and len(slots) % lanes == 0, 'len(slots) must be a multiple of lanes'
+        self.pb, self.slots, self.lanes = pb, slots, lanes
+        self.dev = slots[0][2].device
+        self._kw = dict(top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold)
+        with torch.cuda.device(self.dev):
+            self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(lanes)]
+            self._ev = torch.cuda.Event()
+            self.graphs = [capture_step(pb, gt, head, y, d, **self._kw) for gt, head, y, d in slots] if use_graph else None
+
+    def fork(self):
+        """Orders every lane after the work already queued on the current stream."""
+        cur = torch.cuda.current_stream(self.dev)
+        self._ev.record(cur)
+        for st in self.streams:
+            st.wait_event(self._ev)
+
+    def submit(self, i):
+        """Queues step ``i`` (slot ``i % len(slots)``) on its lane; returns the slot index."""
+        k = i % len(self.slots)
+        with torch.cuda.device(self.dev), torch.cuda.stream(self.streams[k % self.lanes]):
+            if self.graphs is not None:
+                self.graphs[k].replay()
+            else:
+                gt, head, y, d = self.slots[k]
+                self.pb.encode_truth_batch(*gt, y_true=y)
+                self.pb.decode_nms(*head, out=d, **self._kw)
+        return k
+
+    def join(self):
+        """Orders the current stream after everything queued on the lanes."""
+        cur = torch.cuda.current_stream(self.dev)
+        for st in self.streams:
+            cur.wait_stream(st)
+
+
 class HostPipeline:
     """Host-buffer front end for fixed batch shapes.
 

@@ -668,3 +668,31 @@ def test_box_augmenter_vs_oracle_and_feeds_encode_truth(prior_boxes, oracle_tabl
     for i in ok:
         want = R.encode_truth(t, [(cls[i, :cnt[i]], out['gt_boxes'][i, :cnt[i]].cpu().numpy())])[0]
         assert np.array_equal(res['y_true'][i].cpu().numpy(), want)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('use_graph', [True, False])
+def test_step_ring_batches_in_flight(use_graph):
+    """pipeline.StepRing: four batches in flight on four streams give, slot by slot, exactly the results of the two
+    separate calls (every slot owns its outputs and workspaces; reuse of a slot is ordered by its lane)."""
+    import torch
+    import object_detector_b200 as odk
+    from object_detector_b200 import pipeline, synth
+    B, GMAX, TOPK, SLOTS = 8, 32, 200, 4
+    pb = odk.ObjectDetector.load_voc((640, 640)).pb
+    n, c = len(pb.pb_locs), pb.num_classes
+    dev = torch.device('cuda', 0)
+    slots, want = [], []
+    for k in range(SLOTS):
+        gt = tuple(torch.from_numpy(x).to(dev) for x in synth.gt_batch(500 + k, B, GMAX, c))
+        head = tuple(torch.from_numpy(x).to(dev) for x in synth.predictions(600 + k, B, n, c))
+        want.append((pb.encode_truth_batch(*gt)['y_true'].clone(), pb.decode_nms(*head, top_k=TOPK).clone()))
+        slots.append((gt, head, torch.full((B, n, 3 + c + 4), 7.0, device=dev), torch.full((B, TOPK, 6), 7.0, device=dev)))
+    ring = pipeline.StepRing(pb, slots, lanes=4, top_k=TOPK, use_graph=use_graph)
+    ring.fork()
+    for i in range(3 * SLOTS):
+        ring.submit(i)
+    ring.join()
+    torch.cuda.synchronize()
+    for (gt, head, y, d), (wy, wd) in zip(slots, want):
+        assert torch.equal(y, wy) and torch.equal(d, wd)
