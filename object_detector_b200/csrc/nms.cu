@@ -33,7 +33,7 @@
 
 namespace {
 
-constexpr int kNmsThreads = 1024;
+constexpr int kNmsThreads = 512;
 constexpr int kNmsWarps = kNmsThreads / 32;
 constexpr int kBand = 512;
 constexpr int kDigitBits = 11;
