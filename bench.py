@@ -178,6 +178,8 @@ def run_reference(args):
 
 # ------------------------------------------------------------------------------------------ CUDA arm
 def run_cuda(args):
+    global ROT
+    ROT = max(1, args.slots)
     import torch
     import torch.distributed as dist
     import object_detector_b200 as odk
@@ -378,6 +380,7 @@ def main():
     ap.add_argument('--impl', default='cuda', choices=['cuda', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-graph', action='store_true', help='eager launches instead of CUDA-graph replay')
+    ap.add_argument('--slots', type=int, default=ROT, help='distinct resident batches (inputs + outputs) rotated through')
     ap.add_argument('--lanes', type=int, default=LANES, help='batches in flight (1 = one step at a time)')
     args = ap.parse_args()
     if args.impl == 'reference':
