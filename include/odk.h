@@ -209,6 +209,23 @@ int odk_voc_ap(int n_img, int top_k, int num_classes, const float* dets /*[dev n
                int gt_max_per_image, double* ap_area /*[dev C]*/, double* ap07 /*[dev C]*/,
                void* workspace, size_t workspace_bytes, void* stream);
 
+/* data.coco.evaluate (data/coco.py:75-99 -> chainercv eval_detection_coco -> pycocotools COCOeval 'bbox';
+ * PARITY UNPINNED: neither package is vendored or pinned by the reference).  dets / img_wh / gt_boxes / gt_classes /
+ * gt_offsets as in odk_voc_ap; gt_areas = ObjectsAnnotation.areas (the annotation's area, used for the area ranges),
+ * gt_crowd = crowdeds.  iou_thrs[10], rec_thrs[101], area_ranges[4][2] are HOST arrays (pycocotools Params: the
+ * caller passes np.linspace's values so that threshold comparisons are bit-identical).  Outputs are COCOeval.eval's
+ * arrays over ALL class ids 0..C-1: precision[T=10,R=101,C,A=4,M=3], recall[T,C,A,M], -1 where undefined
+ * (maxDets = 1, 10, 100; at most 256 GT boxes per image). */
+size_t odk_coco_ap_workspace_bytes(int n_img, int top_k, int num_classes);
+int odk_coco_ap(int n_img, int top_k, int num_classes, const float* dets /*[dev n_img,top_k,6]*/, float conf_thr,
+                const int32_t* img_wh /*[dev n_img,2]*/, const float* gt_boxes /*[dev n_gt,4] normalised*/,
+                const int32_t* gt_classes /*[dev n_gt]*/, const double* gt_areas /*[dev n_gt] pixels^2*/,
+                const uint8_t* gt_crowd /*[dev n_gt]*/, const int32_t* gt_offsets /*[dev n_img+1]*/,
+                int gt_max_per_image, const double* iou_thrs /*[host 10]*/, const double* rec_thrs /*[host 101]*/,
+                const double* area_ranges /*[host 4,2]*/, double* precision /*[dev 10,101,C,4,3]*/,
+                double* recall /*[dev 10,C,4,3]*/, void* workspace /*[dev, 256-byte aligned]*/,
+                size_t workspace_bytes, void* stream);
+
 /* ml.compute_scores (ml.py:352-394) for n_thr confidence thresholds at once (ml.search_conf_threshold,
  * ml.py:328-340, sweeps 50 of them): counts[t, 0/1/2, c] = TP / FP / FN of class c at conf_thr[t].
  * dets / GT arrays as in odk_voc_ap (boxes normalised fp32, IoU in fp32 like ml.compute_iou). */

@@ -56,6 +56,9 @@ SIGNATURES = {
     'odk_voc_ap_workspace_bytes': (c_size_t, [c_int, c_int, c_int, c_int]),
     'odk_voc_ap': (c_int, [c_int, c_int, c_int, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p,
                            c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    'odk_coco_ap_workspace_bytes': (c_size_t, [c_int, c_int, c_int]),
+    'odk_coco_ap': (c_int, [c_int, c_int, c_int, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                            c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_match_counts': (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
                                  c_float, c_void_p, c_void_p]),
     'odk_confusion_matrix': (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p,

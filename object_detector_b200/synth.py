@@ -111,3 +111,20 @@ def augment_inputs(seed, count):
         boxes = gt_boxes(rng, g, size=[(0.03, 0.2), (0.1, 0.6), (0.3, 0.9)][i % 3])
         out.append((w, h, boxes, rng.randint(0, 20, size=g).astype(np.int32), int(rng.randint(0, 2 ** 31))))
     return out
+
+
+def coco_eval_set(seed, n_img, num_classes, max_gt=8, crowd_frac=0.1, n_fp=20, tie_frac=0.2):
+    """COCO-style evaluation set on top of ``eval_set``: annotation areas (a fraction of the box area, as a
+    segmentation area would be), crowd flags, and a share of quantised (tied) scores.
+    gts: (w, h, classes, boxes f32, areas f32, crowdeds); preds as ``eval_set``."""
+    rng = np.random.RandomState(seed + 77)
+    gts, preds = eval_set(seed, n_img, num_classes, max_gt=max_gt, n_fp=n_fp)
+    out = []
+    for (w, h, gc, gb, _), (pc, ps, pbx) in zip(gts, preds):
+        px = np.round(gb.astype(np.float32) * [w, h, w, h])
+        areas = ((px[:, 2] - px[:, 0]) * (px[:, 3] - px[:, 1]) * rng.uniform(0.4, 1.0, size=len(gb))).astype(np.float32)
+        crowd = rng.uniform(size=len(gb)) < crowd_frac
+        out.append((w, h, gc, gb, areas, crowd))
+        tied = rng.uniform(size=len(ps)) < tie_frac
+        ps[tied] = np.round(ps[tied] * 8) / 8
+    return out, preds

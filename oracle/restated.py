@@ -752,3 +752,177 @@ def augment_boxes_sample(rand, width, height, boxes, classes, output_size, **cfg
     k = int(rand.randint(0, 4)) if c['rotate90'] else 0
     info.update(flip_lr=bool(lr), flip_tb=bool(tb), k=k)
     return flip_rot_boxes(boxes, lr, tb, k), classes, info
+
+
+# --------------------------------------------------------------------------------------
+# MS COCO detection metrics: data/coco.py:75-99 -> chainercv.evaluations.eval_detection_coco ->
+# pycocotools.cocoeval.COCOeval(iouType='bbox').  Neither package is vendored or pinned by the reference
+# (README.md:20 lists chainercv without a version; pycocotools is its optional dependency), so this follows
+# the published algorithm (COCOeval.evaluate / evaluateImg / accumulate, chainercv _create_ann / _summarize)
+# — PARITY UNPINNED against the real packages.
+COCO_IOU_THRS = np.linspace(.5, 0.95, int(np.round((0.95 - .5) / .05)) + 1, endpoint=True)
+COCO_REC_THRS = np.linspace(.0, 1.00, int(np.round((1.00 - .0) / .01)) + 1, endpoint=True)
+COCO_MAX_DETS = (1, 10, 100)
+COCO_AREA_RNG = ((0 ** 2, 1e5 ** 2), (0 ** 2, 32 ** 2), (32 ** 2, 96 ** 2), (96 ** 2, 1e5 ** 2))
+COCO_AREA_LBL = ('all', 'small', 'medium', 'large')
+COCO_KEYS = (
+    ('ap/iou=0.50:0.95/area=all/max_dets=100', True, None, 'all', 100),
+    ('ap/iou=0.50/area=all/max_dets=100', True, 0, 'all', 100),
+    ('ap/iou=0.75/area=all/max_dets=100', True, 5, 'all', 100),
+    ('ap/iou=0.50:0.95/area=small/max_dets=100', True, None, 'small', 100),
+    ('ap/iou=0.50:0.95/area=medium/max_dets=100', True, None, 'medium', 100),
+    ('ap/iou=0.50:0.95/area=large/max_dets=100', True, None, 'large', 100),
+    ('ar/iou=0.50:0.95/area=all/max_dets=1', False, None, 'all', 1),
+    ('ar/iou=0.50:0.95/area=all/max_dets=10', False, None, 'all', 10),
+    ('ar/iou=0.50:0.95/area=all/max_dets=100', False, None, 'all', 100),
+    ('ar/iou=0.50:0.95/area=small/max_dets=100', False, None, 'small', 100),
+    ('ar/iou=0.50:0.95/area=medium/max_dets=100', False, None, 'medium', 100),
+    ('ar/iou=0.50:0.95/area=large/max_dets=100', False, None, 'large', 100),
+)
+
+
+def _coco_box_iou(d, g, crowd):
+    """maskApi bbIou on [x, y, w, h] doubles: crowd GT -> union = area of the detection."""
+    out = np.zeros((len(d), len(g)))
+    for i, a in enumerate(d):
+        for j, b in enumerate(g):
+            w = min(a[0] + a[2], b[0] + b[2]) - max(a[0], b[0])
+            h = min(a[1] + a[3], b[1] + b[3]) - max(a[1], b[1])
+            if w <= 0 or h <= 0:
+                continue
+            inter = w * h
+            u = a[2] * a[3] if crowd[j] else a[2] * a[3] + b[2] * b[3] - inter
+            out[i, j] = inter / u
+    return out
+
+
+def coco_evaluate_image(dt_xywh, dt_score, gt_xywh, gt_area, gt_crowd, area_rng, max_det=100):
+    """COCOeval.computeIoU + evaluateImg for one (image, category, area range).  Returns (scores sorted desc,
+    dtMatched (T,D) bool, dtIgnore (T,D) bool, gtIgnore (G,) bool) for the first ``max_det`` detections."""
+    order = np.argsort(-np.asarray(dt_score, dtype=np.float64), kind='mergesort')[:max_det]
+    dt = np.asarray(dt_xywh, dtype=np.float64).reshape(-1, 4)[order]
+    sc = np.asarray(dt_score, dtype=np.float64)[order]
+    gt_xywh = np.asarray(gt_xywh, dtype=np.float64).reshape(-1, 4)
+    g_ign = np.array([bool(c) or a < area_rng[0] or a > area_rng[1] for a, c in zip(gt_area, gt_crowd)], dtype=bool)
+    gtind = np.argsort(g_ign.astype(np.int64), kind='mergesort')
+    gt = gt_xywh[gtind]
+    crowd = np.asarray(gt_crowd, dtype=bool)[gtind] if len(gtind) else np.zeros(0, dtype=bool)
+    g_ign = g_ign[gtind]
+    ious = _coco_box_iou(dt, gt, crowd)
+    T, D, G = len(COCO_IOU_THRS), len(dt), len(gt)
+    gtm = np.zeros((T, G), dtype=bool)
+    dtm = np.zeros((T, D), dtype=bool)
+    dt_ig = np.zeros((T, D), dtype=bool)
+    for ti, t in enumerate(COCO_IOU_THRS):
+        for di in range(D):
+            iou = min(t, 1 - 1e-10)
+            m = -1
+            for gi in range(G):
+                if gtm[ti, gi] and not crowd[gi]:
+                    continue
+                if m > -1 and not g_ign[m] and g_ign[gi]:
+                    break
+                if ious[di, gi] < iou:
+                    continue
+                iou = ious[di, gi]
+                m = gi
+            if m == -1:
+                continue
+            dt_ig[ti, di] = g_ign[m]
+            dtm[ti, di] = True
+            gtm[ti, m] = True
+    d_area = dt[:, 2] * dt[:, 3]
+    out_of_range = np.logical_or(d_area < area_rng[0], d_area > area_rng[1])
+    dt_ig = np.logical_or(dt_ig, np.logical_and(~dtm, out_of_range[None, :]))
+    return sc, dtm, dt_ig, g_ign
+
+
+def coco_accumulate(per_image, max_det):
+    """COCOeval.accumulate for one (category, area range, max_det): ``per_image`` = list of coco_evaluate_image
+    results.  Returns (precision (T,R), recall (T,)), all -1 when there is no non-ignored GT."""
+    T, R = len(COCO_IOU_THRS), len(COCO_REC_THRS)
+    precision, recall = -np.ones((T, R)), -np.ones(T)
+    if not per_image:
+        return precision, recall
+    scores = np.concatenate([e[0][:max_det] for e in per_image])
+    inds = np.argsort(-scores, kind='mergesort')
+    dtm = np.concatenate([e[1][:, :max_det] for e in per_image], axis=1)[:, inds]
+    dt_ig = np.concatenate([e[2][:, :max_det] for e in per_image], axis=1)[:, inds]
+    npig = int(np.count_nonzero(~np.concatenate([e[3] for e in per_image])))
+    if npig == 0:
+        return precision, recall
+    tp_sum = np.cumsum(np.logical_and(dtm, ~dt_ig), axis=1).astype(np.float64)
+    fp_sum = np.cumsum(np.logical_and(~dtm, ~dt_ig), axis=1).astype(np.float64)
+    for t in range(T):
+        tp, fp = tp_sum[t], fp_sum[t]
+        nd = len(tp)
+        rc = tp / npig
+        pr = tp / (fp + tp + np.spacing(1))
+        q = np.zeros(R)
+        recall[t] = rc[-1] if nd else 0
+        pr = pr.tolist()
+        for i in range(nd - 1, 0, -1):
+            if pr[i] > pr[i - 1]:
+                pr[i - 1] = pr[i]
+        for ri, pi in enumerate(np.searchsorted(rc, COCO_REC_THRS, side='left')):
+            if pi >= nd:
+                break
+            q[ri] = pr[pi]
+        precision[t] = q
+    return precision, recall
+
+
+def coco_summarize(precision, recall, existent_labels):
+    """chainercv eval_detection_coco's result dict from precision (T,R,K,A,M) / recall (T,K,A,M) over the
+    ``existent_labels`` (K of them, sorted)."""
+    res = {}
+    n = int(np.max(existent_labels)) + 1 if len(existent_labels) else 0
+    for key, is_ap, iou_ix, area, max_det in COCO_KEYS:
+        a, m = COCO_AREA_LBL.index(area), COCO_MAX_DETS.index(max_det)
+        v = (precision if is_ap else recall).copy()
+        if iou_ix is not None:
+            v = v[iou_ix:iou_ix + 1]
+        v = v[:, :, :, a, m] if is_ap else v[:, :, a, m]
+        v[v == -1] = np.nan
+        v = v.reshape((-1, v.shape[-1]))
+        valid = np.any(~np.isnan(v), axis=0)
+        per_class = np.full(len(valid), np.nan)
+        if valid.any():
+            per_class[valid] = np.nanmean(v[:, valid], axis=0)
+        full = np.full(n, np.nan)
+        full[existent_labels] = per_class
+        res[key] = full
+        res['m' + key] = np.nanmean(per_class) if valid.any() else np.nan
+    res['existent_labels'] = np.asarray(existent_labels)
+    return res
+
+
+def coco_evaluate(gt_list, pred_list):
+    """data/coco.py:75-99.  gt_list = [(width, height, classes, bboxes f32, areas, crowdeds)], pred_list =
+    [(classes, confs, bboxes f32)].  Boxes go through real_bboxes / get_real_bboxes (ml.py:62-65,184-186) to int32
+    pixels; chainercv reads them as (y_min, x_min, y_max, x_max), which only swaps the axes consistently."""
+    labels = sorted(set(int(c) for g in gt_list for c in g[2]) | set(int(c) for p in pred_list for c in p[0]))
+    T, R, K, A, M = len(COCO_IOU_THRS), len(COCO_REC_THRS), len(labels), len(COCO_AREA_RNG), len(COCO_MAX_DETS)
+    precision, recall = -np.ones((T, R, K, A, M)), -np.ones((T, K, A, M))
+
+    def xywh(px):
+        px = np.asarray(px, dtype=np.float64).reshape(-1, 4)
+        return np.stack([px[:, 0], px[:, 1], px[:, 2] - px[:, 0], px[:, 3] - px[:, 1]], axis=1)
+
+    gts = [(np.asarray(g[2]).astype(int), xywh(to_pixels(np.asarray(g[3], dtype=np.float32).reshape(-1, 4), g[0], g[1])),
+            np.asarray(g[4], dtype=np.float64), np.asarray(g[5], dtype=bool)) for g in gt_list]
+    dts = [(np.asarray(p[0]).astype(int), np.asarray(p[1]), xywh(to_pixels(np.asarray(p[2], dtype=np.float32).reshape(-1, 4), g[0], g[1])))
+           for p, g in zip(pred_list, gt_list)]
+    for k, c in enumerate(labels):
+        for a, rng in enumerate(COCO_AREA_RNG):
+            per_image = []
+            for (gc, gb, ga, gw), (dc, ds, db) in zip(gts, dts):
+                gm, dm = gc == c, dc == c
+                if not gm.any() and not dm.any():
+                    continue  # COCOeval.evaluateImg returns None
+                per_image.append(coco_evaluate_image(db[dm], ds[dm], gb[gm], ga[gm], gw[gm], rng))
+            for m, max_det in enumerate(COCO_MAX_DETS):
+                precision[:, :, k, a, m], recall[:, k, a, m] = coco_accumulate(per_image, max_det)
+    res = coco_summarize(precision, recall, labels)
+    res['precision'], res['recall'] = precision, recall
+    return res

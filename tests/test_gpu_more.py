@@ -696,3 +696,64 @@ def test_step_ring_batches_in_flight(use_graph):
     torch.cuda.synchronize()
     for (gt, head, y, d), (wy, wd) in zip(slots, want):
         assert torch.equal(y, wy) and torch.equal(d, wd)
+
+
+# ----------------------------------------------------------------------------------------- COCO metrics (parity unpinned)
+def _coco_objects(gts, preds):
+    y_true = [odk.ml.ObjectsAnnotation('.', w, h, c, b, areas=a, crowdeds=cr) for (w, h, c, b, a, cr) in gts]
+    y_pred = [odk.ml.ObjectsPrediction(c, s, b) for (c, s, b) in preds]
+    return y_true, y_pred
+
+
+def _assert_coco_equal(res, ref):
+    from object_detector_b200 import coco
+    assert res['existent_labels'].tolist() == list(ref['existent_labels'])
+    for key, *_ in coco.KEYS:
+        assert np.array_equal(np.isnan(res[key]), np.isnan(ref[key])), key
+        np.testing.assert_allclose(res[key], ref[key], rtol=1e-5, atol=1e-12, equal_nan=True)  # north_star: AP within 1e-5 relative
+        np.testing.assert_allclose(res['m' + key], ref['m' + key], rtol=1e-5, equal_nan=True)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('n_img,classes,seed,n_fp', [(60, 5, 1, 20), (400, 20, 2017, 20), (40, 2, 3, 150)])
+def test_coco_ap_vs_oracle(n_img, classes, seed, n_fp):
+    """odk_coco_ap (matching per image x class x area range x IoU threshold, per-class sort, precision / recall
+    arrays) vs the pycocotools restatement, incl. crowd GT, annotation areas, tied scores and — n_fp=150 with two
+    classes — more than maxDets = 100 detections of one class in an image."""
+    import torch
+    from object_detector_b200 import coco, voc
+    R = pytest.importorskip('oracle.restated')
+    gts, preds = synth.coco_eval_set(seed, n_img, classes, n_fp=n_fp)
+    y_true, y_pred = _coco_objects(gts, preds)
+    ref = R.coco_evaluate(gts, preds)
+    res = coco.evaluate(y_true, y_pred)
+    _assert_coco_equal(res, ref)
+    assert 0.02 < res['map/iou=0.50:0.95/area=all/max_dets=100'] < 1.0
+    # the raw COCOeval arrays, bit for bit (same fp64 operations in the same order)
+    dev = torch.device('cuda', 0)
+    labels = [int(x) for x in ref['existent_labels']]
+    prec, rec = coco.evaluate_detections(voc.pack_predictions(y_pred, dev), coco.pack_ground_truth(y_true, dev), labels[-1] + 1)
+    assert np.array_equal(prec.cpu().numpy()[:, :, labels], ref['precision'])
+    assert np.array_equal(rec.cpu().numpy()[:, labels], ref['recall'])
+
+
+@pytest.mark.gpu
+def test_coco_ap_micro_cases_on_gpu():
+    from object_detector_b200 import coco
+    R = pytest.importorskip('oracle.restated')
+    f = np.float32
+    gts = [(100, 100, np.array([0, 0]), np.array([[.1, .1, .5, .5], [.6, .6, .9, .9]], f), np.array([1600, 900], f), np.array([True, False]))]
+    cases = [
+        [(np.array([0, 0, 0, 0]), np.array([.9, .8, .7, .6], f), np.array([[.1, .1, .5, .5], [.1, .1, .5, .5], [.6, .6, .9, .9], [.6, .6, .9, .9]], f))],
+        [(np.array([0]), np.array([.9], f), np.array([[.6, .6, .9, .8]], f))],
+        [(np.zeros((0,), np.int32), np.zeros((0,), f), np.zeros((0, 4), f))],
+        [(np.array([3]), np.array([.9], f), np.array([[.6, .6, .9, .9]], f))],
+    ]
+    for preds in cases:
+        y_true, y_pred = _coco_objects(gts, preds)
+        _assert_coco_equal(coco.evaluate(y_true, y_pred), R.coco_evaluate(gts, preds))
+    # areas / crowdeds absent (VOC-style annotations): box area, no crowd
+    y_true = [odk.ml.ObjectsAnnotation('.', 100, 100, gts[0][2], gts[0][3])]
+    y_pred = [odk.ml.ObjectsPrediction(*cases[0][0])]
+    ref = R.coco_evaluate([(100, 100, gts[0][2], gts[0][3], np.array([1600., 900.]), np.array([False, False]))], cases[0])
+    _assert_coco_equal(coco.evaluate(y_true, y_pred), ref)

@@ -367,3 +367,47 @@ def test_flip_rot_boxes_keeps_fp32_rounding():
     for k in range(4):   # four quarter turns compose to the identity up to rounding; areas are preserved
         r = R.flip_rot_boxes(b.astype(np.float64), False, False, k)
         assert np.allclose((r[:, 2] - r[:, 0]) * (r[:, 3] - r[:, 1]), (b[:, 2] - b[:, 0]).astype(np.float64) * (b[:, 3] - b[:, 1]), rtol=1e-6)
+
+
+def test_coco_ap_micro_cases():
+    """Hand-computed cases for the pycocotools / chainercv restatement (PARITY UNPINNED: both packages absent)."""
+    f = np.float32
+    key = 'ap/iou=0.50:0.95/area=all/max_dets=100'
+
+    def gt(boxes, crowd=None, areas=None, classes=None):
+        boxes = np.array(boxes, f)
+        n = len(boxes)
+        px = boxes * 100
+        a = np.array(areas, np.float64) if areas is not None else (px[:, 2] - px[:, 0]) * (px[:, 3] - px[:, 1])
+        return [(100, 100, np.zeros(n, int) if classes is None else np.array(classes), boxes, a,
+                 np.zeros(n, bool) if crowd is None else np.array(crowd))]
+
+    def pred(boxes, scores, classes=None):
+        n = len(boxes)
+        return [(np.zeros(n, int) if classes is None else np.array(classes), np.array(scores, f), np.array(boxes, f).reshape(-1, 4))]
+
+    one = gt([[.1, .1, .5, .5]])  # 40x40 px = 1600 px^2: "medium"
+    r = R.coco_evaluate(one, pred([[.1, .1, .5, .5]], [.9]))
+    assert r['m' + key] == pytest.approx(1.0, abs=1e-12) and r['mar/iou=0.50:0.95/area=all/max_dets=1'] == pytest.approx(1.0, abs=1e-12)
+    assert r['map/iou=0.50:0.95/area=medium/max_dets=100'] == pytest.approx(1.0, abs=1e-12)
+    assert np.isnan(r['map/iou=0.50:0.95/area=small/max_dets=100']) and np.isnan(r['map/iou=0.50:0.95/area=large/max_dets=100'])
+    r = R.coco_evaluate(one, pred([[.6, .6, .9, .9]], [.9]))
+    assert r['m' + key] == 0.0 and r['mar/iou=0.50:0.95/area=all/max_dets=100'] == 0.0
+    # FP (higher score) then TP: precision 0.5 at recall 1, and the envelope carries it to every recall threshold
+    r = R.coco_evaluate(one, pred([[.6, .6, .9, .9], [.1, .1, .5, .5]], [.9, .8]))
+    assert r['m' + key] == pytest.approx(0.5) and r['mar/iou=0.50:0.95/area=all/max_dets=1'] == 0.0
+    assert r['mar/iou=0.50:0.95/area=all/max_dets=10'] == pytest.approx(1.0, abs=1e-12)
+    # IoU 0.625 with the GT: a true positive at thresholds 0.50 .. 0.60 only -> 3 of 10
+    r = R.coco_evaluate(one, pred([[.1, .1, .5, .35]], [.9]))
+    assert r['m' + key] == pytest.approx(0.3) and r['map/iou=0.50/area=all/max_dets=100'] == pytest.approx(1.0, abs=1e-12)
+    assert r['map/iou=0.75/area=all/max_dets=100'] == 0.0
+    # the only GT is a crowd: it is ignored, the detection matching it is ignored too -> nothing to score
+    r = R.coco_evaluate(gt([[.1, .1, .5, .5]], crowd=[True]), pred([[.1, .1, .5, .5]], [.9]))
+    assert np.isnan(r['m' + key])
+    # a crowd GT absorbs any number of detections; the plain GT is matched once, the duplicate is a false positive
+    r = R.coco_evaluate(gt([[.1, .1, .5, .5], [.6, .6, .9, .9]], crowd=[True, False]),
+                        pred([[.1, .1, .5, .5], [.1, .1, .5, .5], [.6, .6, .9, .9], [.6, .6, .9, .9]], [.9, .8, .7, .6]))
+    assert r['m' + key] == pytest.approx(1.0, abs=1e-12)  # TP at rank 3 (ranks 1-2 ignored), FP after it does not lower the envelope at recall 1
+    # labels absent between 0 and the maximum get nan, existent_labels lists the rest
+    r = R.coco_evaluate(gt([[.1, .1, .5, .5]], classes=[2]), pred([[.1, .1, .5, .5]], [.9], classes=[2]))
+    assert r['existent_labels'].tolist() == [2] and np.isnan(r[key][:2]).all() and r[key][2] == pytest.approx(1.0, abs=1e-12)
