@@ -26,8 +26,8 @@ if ROOT not in sys.path:
 
 METRIC = 'images/sec assign+decode+NMS @640x640'
 B, N, C, GMAX, TOPK = 64, 16800, 20, 64, 200
-ROT = 4  # distinct input sets rotated through so every step reads data that is not L2-resident
-LANES = 4  # batches in flight (pipeline.StepRing): a slot (= input set + its outputs) always runs on lane slot % LANES
+ROT = 8  # distinct input sets rotated through so every step reads data that is not L2-resident
+LANES, GROUP = 2, 4  # pipeline.StepRing: GROUP consecutive slots per CUDA graph (a branch each), graphs alternating on LANES streams
 WORKLOAD = 'cfg2+cfg3: Darknet53 640x640 VOC anchors (N=16800, C=20), batch 64: assign+encode (<=64 GT/img) + decode + per-class NMS (top-k 200)'
 
 # algorithmic HBM bytes per image
@@ -241,20 +241,22 @@ def run_cuda(args):
     # one CUDA graph per input set: the train side and the predict side of a step are independent and run on
     # parallel branches; replaying removes the per-launch host cost of the five small kernels
     # and `lanes` batches in flight: the latency-bound tail of one batch runs beside the HBM-bound head of the next
-    lanes = max(1, min(args.lanes, ROT))
-    while ROT % lanes:
+    group = max(1, min(args.group, ROT))
+    while ROT % group:
+        group -= 1
+    lanes = max(1, min(args.lanes, ROT // group))
+    while (ROT // group) % lanes:
         lanes -= 1
     slots = [(s[:3], s[3:], y_trues[k], detss[k]) for k, s in enumerate(dev_sets)]
-    ring = pipeline.StepRing(pb, slots, lanes=lanes, top_k=TOPK, use_graph=not args.no_graph)
-    graphs = ring.graphs
+    ring = pipeline.StepRing(pb, slots, lanes=lanes, group=group, top_k=TOPK, use_graph=not args.no_graph)
+    graphs = ring.group_graphs
 
     def timed_ring(steps):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         ring.fork()
-        for i in range(steps):
-            ring.submit(i)
+        ring.run(steps)
         ring.join()
         e1.record()
         barrier()
@@ -270,7 +272,7 @@ def run_cuda(args):
     clocks = sampler.stop()
     value = B * world * args.steps / (ms_total * 1e-3)
     # the same K steps with one batch in flight (latency of a step, and the figure earlier rounds reported)
-    one = pipeline.StepRing(pb, slots, lanes=1, top_k=TOPK, use_graph=not args.no_graph) if lanes > 1 else ring
+    one = pipeline.StepRing(pb, slots, lanes=1, group=1, top_k=TOPK, use_graph=not args.no_graph) if lanes * group > 1 else ring
     ring_saved, ring = ring, one
     timed_ring(3)
     ms_serial = timed_ring(args.steps)
@@ -356,8 +358,9 @@ def run_cuda(args):
             'config': {'workload': WORKLOAD, 'batch_per_gpu': B, 'anchors': N, 'classes': C, 'gt_max': GMAX, 'top_k': TOPK,
                        'l2': f'inputs rotate over {ROT} distinct sets ({ROT * (h2d + B * N * 27 * 4) >> 20} MB touched) > 126 MB L2',
                        'launch': ('eager' if graphs is None else 'CUDA graph per input set, train and predict sides on parallel branches')
-                       + f'; {lanes} batches in flight on {lanes} streams (each slot has its own inputs, y_true, detections, workspaces)',
-                       'batches_in_flight': lanes, 'ms_per_step_one_in_flight': ms_serial / args.steps,
+                       + f'; {group} consecutive batches per graph (a branch each), graphs alternating on {lanes} streams'
+                       f' = up to {lanes * group} batches in flight (each slot has its own inputs, y_true, detections, workspaces)',
+                       'batches_in_flight': lanes * group, 'batches_per_graph': group, 'lanes': lanes, 'ms_per_step_one_in_flight': ms_serial / args.steps,
                        'parallelism': f'images sharded over {world} GPU(s), no data-path collective'},
             'clocks': clocks, 'e2e': {'value': e2e_value, 'unit': 'images/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                                       'steps': e2e_steps},
@@ -381,7 +384,8 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-graph', action='store_true', help='eager launches instead of CUDA-graph replay')
     ap.add_argument('--slots', type=int, default=ROT, help='distinct resident batches (inputs + outputs) rotated through')
-    ap.add_argument('--lanes', type=int, default=LANES, help='batches in flight (1 = one step at a time)')
+    ap.add_argument('--lanes', type=int, default=LANES, help='streams the step graphs alternate on')
+    ap.add_argument('--group', type=int, default=GROUP, help='consecutive batches captured into one CUDA graph (a branch each)')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

@@ -14,51 +14,82 @@ import torch
 from . import _dev
 
 
+def _enqueue_step(pb, gt, head, y_true, dets, side, kw):
+    """Both sides of one batch on the current stream; the predict side on ``side`` (forked / joined) if given."""
+    main = torch.cuda.current_stream(y_true.device)
+    if side is not None:
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            pb.decode_nms(*head, out=dets, **kw)
+        pb.encode_truth_batch(*gt, y_true=y_true)
+        main.wait_stream(side)
+    else:
+        pb.encode_truth_batch(*gt, y_true=y_true)
+        pb.decode_nms(*head, out=dets, **kw)
+
+
+def capture_steps(pb, slots, top_k=200, conf_threshold=0.01, nms_threshold=0.45, two_streams=True):
+    """Captures the steps of all ``slots`` = [(gt, head, y_true, dets)] into ONE CUDA graph, every slot on its own
+    branch (and within a slot the train and the predict side on parallel branches when ``two_streams``): one host
+    launch per ``len(slots)`` batches.  All tensors must be CUDA tensors that stay alive and keep their addresses."""
+    dev = slots[0][2].device
+    kw = dict(top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold)
+    with torch.cuda.device(dev):
+        pb._handle(dev)  # the anchor tables are uploaded (cudaMalloc) on first use: not allowed while capturing
+        branch = [torch.cuda.Stream(device=dev) for _ in slots[1:]]
+        side = [torch.cuda.Stream(device=dev) if two_streams else None for _ in slots]
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.device(dev), torch.cuda.graph(graph):
+        main = torch.cuda.current_stream(dev)
+        for k, (gt, head, y, d) in enumerate(slots):
+            if k == 0:
+                continue
+            branch[k - 1].wait_stream(main)
+            with torch.cuda.stream(branch[k - 1]):
+                _enqueue_step(pb, gt, head, y, d, side[k], kw)
+        _enqueue_step(pb, *slots[0], side[0], kw)
+        for st in branch:
+            main.wait_stream(st)
+    return graph
+
+
 def capture_step(pb, gt, head, y_true, dets, top_k=200, conf_threshold=0.01, nms_threshold=0.45, two_streams=True):
     """Captures ``encode_truth_batch(*gt, y_true=y_true)`` and ``decode_nms(*head, out=dets)`` into one CUDA
     graph (parallel branches when ``two_streams``).  All tensors must be CUDA tensors that stay alive and
     keep their addresses; replay with ``graph.replay()`` on any stream."""
-    dev = y_true.device
-    with torch.cuda.device(dev):
-        pb._handle(dev)  # the anchor tables are uploaded (cudaMalloc) on first use: not allowed while capturing
-    side = torch.cuda.Stream(device=dev) if two_streams else None
-    graph = torch.cuda.CUDAGraph()
-    with torch.cuda.device(dev), torch.cuda.graph(graph):
-        main = torch.cuda.current_stream(dev)
-        if side is not None:
-            side.wait_stream(main)
-            with torch.cuda.stream(side):
-                pb.decode_nms(*head, top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold, out=dets)
-            pb.encode_truth_batch(*gt, y_true=y_true)
-            main.wait_stream(side)
-        else:
-            pb.encode_truth_batch(*gt, y_true=y_true)
-            pb.decode_nms(*head, top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold, out=dets)
-    return graph
+    return capture_steps(pb, [(gt, head, y_true, dets)], top_k, conf_threshold, nms_threshold, two_streams)
 
 
 class StepRing:
     """Device-resident batches, several in flight.
 
     The six kernels of a step leave most of the GPU idle most of the time (two of them are HBM-bound for ~20 us each,
-    the other four are latency-bound chains on 64-128 SMs), and consecutive batches are independent — so the graphs of
-    consecutive steps are replayed round-robin on ``lanes`` streams and the tail of batch i (per-image NMS, greedy walk,
-    positives) runs beside the head of batch i+1 (score/emit, candidates).  Every slot owns its inputs, outputs and
-    workspaces; a slot is always replayed on the same lane, so reuse of a slot is ordered by that stream.
+    the other four are latency-bound chains on 64-128 SMs), and consecutive batches are independent — so consecutive
+    steps run concurrently: the tail of batch i (per-image NMS, greedy walk, positives) beside the head of batch i+1
+    (score/emit, candidates).  Slots (= inputs + outputs + workspaces of one batch) are tied into groups of ``group``
+    consecutive slots; a group is ONE CUDA graph with a branch per slot (one host launch per ``group`` batches — with
+    8 ranks on one host the launch rate of single-step graphs is what limits), and groups are replayed round-robin on
+    ``lanes`` streams.  A slot is only ever touched by work queued on its group's lane, so reuse is ordered by that
+    stream.
 
     ``slots``: list of ``(gt, head, y_true, dets)`` with ``gt = (boxes, classes, count)``, ``head = (objs, clfs, locs)``
-    CUDA tensors that keep their addresses; ``len(slots)`` must be a multiple of ``lanes``.
+    CUDA tensors that keep their addresses; ``len(slots)`` must be a multiple of ``lanes * group``.
     """
 
-    def __init__(self, pb, slots, lanes=4, top_k=200, conf_threshold=0.01, nms_threshold=0.45, use_graph=True):
-        assert len(slots) >= 1 and lanes >= 1 and len(slots) % lanes == 0, 'len(slots) must be a multiple of lanes'
-        self.pb, self.slots, self.lanes = pb, slots, lanes
+    def __init__(self, pb, slots, lanes=2, group=4, top_k=200, conf_threshold=0.01, nms_threshold=0.45, use_graph=True):
+        assert len(slots) >= 1 and lanes >= 1 and group >= 1 and len(slots) % (lanes * group) == 0, \
+            'len(slots) must be a multiple of lanes * group'
+        self.pb, self.slots, self.lanes, self.group = pb, slots, lanes, group
         self.dev = slots[0][2].device
         self._kw = dict(top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold)
+        self.n_groups = len(slots) // group
         with torch.cuda.device(self.dev):
             self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(lanes)]
             self._ev = torch.cuda.Event()
-            self.graphs = [capture_step(pb, gt, head, y, d, **self._kw) for gt, head, y, d in slots] if use_graph else None
+        self.use_graph = use_graph
+        self.group_graphs = ([capture_steps(pb, slots[j * group:(j + 1) * group], **self._kw) for j in range(self.n_groups)]
+                             if use_graph else None)
+        self._slot_graphs = {}  # single-step graphs, captured on first use (steps outside whole groups)
 
     def fork(self):
         """Orders every lane after the work already queued on the current stream."""
@@ -67,17 +98,34 @@ class StepRing:
         for st in self.streams:
             st.wait_event(self._ev)
 
+    def _lane_of_slot(self, k):
+        return self.streams[(k // self.group) % self.lanes]
+
     def submit(self, i):
-        """Queues step ``i`` (slot ``i % len(slots)``) on its lane; returns the slot index."""
+        """Queues the single step ``i`` (slot ``i % len(slots)``) on its lane; returns the slot index."""
         k = i % len(self.slots)
-        with torch.cuda.device(self.dev), torch.cuda.stream(self.streams[k % self.lanes]):
-            if self.graphs is not None:
-                self.graphs[k].replay()
+        gt, head, y, d = self.slots[k]
+        if self.use_graph and k not in self._slot_graphs:
+            self._slot_graphs[k] = capture_step(self.pb, gt, head, y, d, **self._kw)
+        with torch.cuda.device(self.dev), torch.cuda.stream(self._lane_of_slot(k)):
+            if self.use_graph:
+                self._slot_graphs[k].replay()
             else:
-                gt, head, y, d = self.slots[k]
-                self.pb.encode_truth_batch(*gt, y_true=y)
-                self.pb.decode_nms(*head, out=d, **self._kw)
+                _enqueue_step(self.pb, gt, head, y, d, None, self._kw)
         return k
+
+    def run(self, steps, start=0):
+        """Queues steps ``start .. start+steps-1``: whole groups as one graph launch each, the rest step by step."""
+        i, end = start, start + steps
+        while i < end:
+            if self.use_graph and i % self.group == 0 and i + self.group <= end:
+                j = (i // self.group) % self.n_groups
+                with torch.cuda.device(self.dev), torch.cuda.stream(self.streams[j % self.lanes]):
+                    self.group_graphs[j].replay()
+                i += self.group
+            else:
+                self.submit(i)
+                i += 1
 
     def join(self):
         """Orders the current stream after everything queued on the lanes."""

@@ -671,10 +671,11 @@ def test_box_augmenter_vs_oracle_and_feeds_encode_truth(prior_boxes, oracle_tabl
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize('use_graph', [True, False])
-def test_step_ring_batches_in_flight(use_graph):
-    """pipeline.StepRing: four batches in flight on four streams give, slot by slot, exactly the results of the two
-    separate calls (every slot owns its outputs and workspaces; reuse of a slot is ordered by its lane)."""
+@pytest.mark.parametrize('use_graph,lanes,group', [(True, 4, 1), (True, 2, 2), (True, 1, 4), (False, 2, 2)])
+def test_step_ring_batches_in_flight(use_graph, lanes, group):
+    """pipeline.StepRing: several batches in flight (groups of slots captured into one graph with a branch per slot,
+    groups alternating on streams) give, slot by slot, exactly the results of the two separate calls (every slot
+    owns its outputs and workspaces; reuse of a slot is ordered by its lane).  13 steps: whole groups + a remainder."""
     import torch
     import object_detector_b200 as odk
     from object_detector_b200 import pipeline, synth
@@ -688,10 +689,9 @@ def test_step_ring_batches_in_flight(use_graph):
         head = tuple(torch.from_numpy(x).to(dev) for x in synth.predictions(600 + k, B, n, c))
         want.append((pb.encode_truth_batch(*gt)['y_true'].clone(), pb.decode_nms(*head, top_k=TOPK).clone()))
         slots.append((gt, head, torch.full((B, n, 3 + c + 4), 7.0, device=dev), torch.full((B, TOPK, 6), 7.0, device=dev)))
-    ring = pipeline.StepRing(pb, slots, lanes=4, top_k=TOPK, use_graph=use_graph)
+    ring = pipeline.StepRing(pb, slots, lanes=lanes, group=group, top_k=TOPK, use_graph=use_graph)
     ring.fork()
-    for i in range(3 * SLOTS):
-        ring.submit(i)
+    ring.run(3 * SLOTS + 1)
     ring.join()
     torch.cuda.synchronize()
     for (gt, head, y, d), (wy, wd) in zip(slots, want):
