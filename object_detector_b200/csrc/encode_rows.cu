@@ -159,13 +159,17 @@ struct SideLane {
   bool ready;
 };
 
+// A small pool of lanes per host thread and device, used round-robin: consecutive calls (e.g. the steps of several
+// batches captured into one CUDA graph, or issued on different caller streams) must not be chained to each other
+// through a shared side stream.
 int side_lane(SideLane** out) {
-  constexpr int kMaxDevices = 64;
-  static thread_local SideLane lanes[kMaxDevices] = {};
+  constexpr int kMaxDevices = 64, kLanes = 8;
+  static thread_local SideLane lanes[kMaxDevices][kLanes] = {};
+  static thread_local unsigned next[kMaxDevices] = {};
   int dev = 0;
   ODK_CUDA(cudaGetDevice(&dev));
   ODK_REQUIRE(dev >= 0 && dev < kMaxDevices, ODK_ERR_UNSUPPORTED, "device index %d out of range", dev);
-  SideLane& l = lanes[dev];
+  SideLane& l = lanes[dev][next[dev]++ % kLanes];
   if (!l.ready) {
     ODK_CUDA(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
     ODK_CUDA(cudaEventCreateWithFlags(&l.fork, cudaEventDisableTiming));
