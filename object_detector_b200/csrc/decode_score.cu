@@ -283,7 +283,10 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   static const int env_per_sm = getenv("ODK_EMIT_PER_SM") ? atoi(getenv("ODK_EMIT_PER_SM")) : 0;
   static const int env_hint = getenv("ODK_EMIT_HINT") ? atoi(getenv("ODK_EMIT_HINT")) : 1;
   args.stream_hint = env_hint;
-  args.stages = (!DENSE && env_stages >= 2 && env_stages <= L::kMaxStages) ? env_stages : 3;
+  // EMIT: a 2-deep ring at 3 CTAs per SM (3 x 43 KB at C = 20).  Same shared memory per SM as 2 CTAs x 3 stages, but the
+  // smaller CTAs still fit two at a time beside a per-image NMS CTA (~120 KB) of another batch in flight
+  // (profiles/emit_sweep_r01i.log: step 46.3 -> 45.5 us, the kernel 26.3 -> 24.1 us).
+  args.stages = (!DENSE && env_stages >= 2 && env_stages <= L::kMaxStages) ? env_stages : (DENSE ? 3 : 2);
   const size_t smem = L::stage_bytes(args.c) * args.stages;
   auto kern = decode_score_kernel<TILE, DENSE, SPLIT>;
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -292,7 +295,7 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   int per_sm = (int)((220 * 1024) / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / (TILE * SPLIT) ? 2048 / (TILE * SPLIT) : per_sm);
   // EMIT runs beside the train-side kernels of the same step (other graph branch): leave them shared memory
-  if (!DENSE && per_sm > 2) per_sm = 2;
+  if (!DENSE && per_sm > 3) per_sm = 3;
   if (!DENSE && env_per_sm > 0) per_sm = env_per_sm;
   long long grid = (long long)sm_count_cached() * per_sm;
   if (grid > total) grid = total;
