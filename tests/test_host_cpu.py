@@ -147,3 +147,25 @@ def test_text_histogram_lines_match_golden_log():
     assert textstats.histogram_lines(counts, title='assigned_count') == want[start:start + 13]
     assert textstats.number_column(np.array([1, 20, 300])) == ['  1', ' 20', '300']
     assert textstats.number_column(np.array([-0.5, 0.25])) == ['-0.500', ' 0.250']
+
+
+def test_coco_summarize_host_logic_matches_oracle():
+    """coco.summarize (the host part of the COCO mirror: chainercv _summarize over COCOeval's arrays) against the
+    oracle's summary of the same arrays, incl. absent labels and undefined (-1) entries; and the pycocotools
+    parameter tables the mirror hands to odk_coco_ap equal the oracle's."""
+    import numpy as np
+    from object_detector_b200 import coco, synth
+    from oracle import restated as R
+    assert np.array_equal(coco.IOU_THRS, R.COCO_IOU_THRS) and np.array_equal(coco.REC_THRS, R.COCO_REC_THRS)
+    assert np.array_equal(coco.AREA_RNG, np.array(R.COCO_AREA_RNG, dtype=np.float64)) and coco.MAX_DETS == R.COCO_MAX_DETS
+    assert [k[0] for k in coco.KEYS] == [k[0] for k in R.COCO_KEYS]
+    gts, preds = synth.coco_eval_set(5, 40, 6)
+    gts = [(w, h, c + 2 * (c >= 3), b, a, cr) for (w, h, c, b, a, cr) in gts]      # labels 3, 4 never occur
+    preds = [(c + 2 * (c >= 3), s, b) for (c, s, b) in preds]
+    ref = R.coco_evaluate(gts, preds)
+    res = coco.summarize(ref['precision'], ref['recall'], ref['existent_labels'])
+    assert res['existent_labels'].tolist() == list(ref['existent_labels']) and 3 not in res['existent_labels']
+    for key, *_ in coco.KEYS:
+        np.testing.assert_array_equal(res[key], ref[key])
+        np.testing.assert_array_equal(res['m' + key], ref['m' + key])
+    assert np.isnan(res['ap/iou=0.50:0.95/area=all/max_dets=100'][3:5]).all()
