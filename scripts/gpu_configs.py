@@ -66,3 +66,26 @@ us_t = timed([cap(lambda g=g: sp.encode_truth_batch(*g, y_true=y)) for g in gts]
 print(json.dumps({'config': 'cfg5 stress N=205800 C=80 G=512 B=8', 'predict_us': round(us_p, 1), 'predict_img_per_s': round(8 / us_p * 1e6),
                   'predict_read_gbs': round(8 * NS * 4 * (1 + CS + 4) / us_p / 1e3), 'train_us': round(us_t, 1),
                   'train_img_per_s': round(8 / us_t * 1e6), 'train_write_gbs': round(8 * NS * 87 * 4 / us_t / 1e3), 'status': st}), flush=True)
+# evaluation kernels at dataset size: VOC07-test (4952 images, 20 classes) and COCO-val-sized (5000 images, 80 classes)
+del heads, gts, y
+torch.cuda.empty_cache()
+from object_detector_b200 import coco, voc  # noqa: E402
+for name, n_img, ncls in (('voc07-test-sized', 4952, 20), ('coco-val-sized', 5000, 80)):
+    g_list, p_list = synth.coco_eval_set(2017, n_img, ncls, n_fp=60)
+    y_true = [odk.ml.ObjectsAnnotation('.', w, h, c, b, areas=a, crowdeds=cr) for (w, h, c, b, a, cr) in g_list]
+    y_pred = [odk.ml.ObjectsPrediction(c, s, b) for (c, s, b) in p_list]
+    dets = voc.pack_predictions(y_pred, dev)
+    gv, gc = voc.pack_ground_truth(y_true, dev), coco.pack_ground_truth(y_true, dev)
+    out = {'config': f'eval {name}: {n_img} images x {dets.shape[1]} detections, {ncls} classes'}
+    for label, fn in (('voc_ap_us', lambda: voc.evaluate_detections(dets, gv, ncls)), ('coco_ap_us', lambda: coco.evaluate_detections(dets, gc, ncls))):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        out[label] = round(e0.elapsed_time(e1) / 10 * 1e3, 1)
+    print(json.dumps(out), flush=True)
