@@ -190,19 +190,10 @@ int launch_rows(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
   const long long gx = (pieces + per_cta - 1) / per_cta;  // >= ceil(n / per_cta): the pb_valids loop is covered too
   const unsigned step = (unsigned)(kRowsThreads * v);     // floats between a thread's consecutive pieces
   dim3 grid((unsigned)gx, (unsigned)e.batch);
-  // Residency cap: the kernel uses no shared memory, but an (unused) dynamic request of `cap_kb` KB per CTA bounds how
-  // many of its 256-thread CTAs an SM holds, so that they never take every register of an SM away from the
-  // latency-bound kernels of the batches in flight beside it.  0 = no cap.
-  static const int cap_kb = getenv("ODK_ROWS_SMEM_KB") ? atoi(getenv("ODK_ROWS_SMEM_KB")) : 0;
-  const size_t cap = cap_kb > 0 ? (size_t)(cap_kb > 200 ? 200 : cap_kb) * 1024 : 0;
-  if (cap > 48 * 1024) {
-    ODK_CUDA(cudaFuncSetAttribute(encode_rows_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap));
-    ODK_CUDA(cudaFuncSetAttribute(encode_rows_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap));
-  }
   {
     OdkProfileScope prof_("encode_rows_kernel", stream);
-    if (vec) encode_rows_kernel<4><<<grid, kRowsThreads, cap, stream>>>(e, step / W, step % W);
-    else encode_rows_kernel<1><<<grid, kRowsThreads, cap, stream>>>(e, step / W, step % W);
+    if (vec) encode_rows_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W);
+    else encode_rows_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W);
   }
   ODK_LAUNCH_CHECK("encode_rows_kernel");
   return ODK_OK;
