@@ -89,7 +89,10 @@ class StepRing:
         self.use_graph = use_graph
         self.group_graphs = ([capture_steps(pb, slots[j * group:(j + 1) * group], **self._kw) for j in range(self.n_groups)]
                              if use_graph else None)
-        self._slot_graphs = {}  # single-step graphs, captured on first use (steps outside whole groups)
+        # single-step graphs for steps outside whole groups; captured up front so that no capture (milliseconds) ever
+        # happens between a caller's timing events
+        self._slot_graphs = ({k: capture_step(pb, *slots[k], **self._kw) for k in range(len(slots))}
+                             if (use_graph and group > 1) else {})
 
     def fork(self):
         """Orders every lane after the work already queued on the current stream."""
@@ -105,11 +108,9 @@ class StepRing:
         """Queues the single step ``i`` (slot ``i % len(slots)``) on its lane; returns the slot index."""
         k = i % len(self.slots)
         gt, head, y, d = self.slots[k]
-        if self.use_graph and k not in self._slot_graphs:
-            self._slot_graphs[k] = capture_step(self.pb, gt, head, y, d, **self._kw)
         with torch.cuda.device(self.dev), torch.cuda.stream(self._lane_of_slot(k)):
             if self.use_graph:
-                self._slot_graphs[k].replay()
+                (self.group_graphs[k] if self.group == 1 else self._slot_graphs[k]).replay()
             else:
                 _enqueue_step(self.pb, gt, head, y, d, None, self._kw)
         return k
