@@ -12,9 +12,19 @@
  *  - `stream` is a cudaStream_t passed as void* (0 = legacy default stream).  Launches are
  *    asynchronous: no entry point synchronises the stream;
  *  - every function returns 0 on success or a negative odk_status; the message is retrievable
- *    per host thread with odk_last_error().  No global mutable state: safe to call from many
- *    host threads on distinct streams (generator.py:160-166 calls encode_truth from a thread
- *    pool);
+ *    per host thread with odk_last_error().  Safe to call from many host threads on distinct
+ *    streams (generator.py:160-166 calls encode_truth from a thread pool).  State the library
+ *    keeps besides the anchors handles, all of it per host thread or diagnostic:
+ *      * odk_assign_encode / odk_assign_encode_compact fork part of their work onto LIBRARY-OWNED
+ *        side streams (a small per-host-thread, per-device pool of non-blocking streams + events,
+ *        created on first use, never destroyed) and join them back with events before returning
+ *        to the caller's stream order; the fork/join is capturable into a CUDA graph.  Work is
+ *        therefore ordered with respect to `stream`, but not every kernel runs ON `stream`;
+ *      * odk_profile_enable() switches on per-host-thread CUDA-event timing of every launch;
+ *      * odk_timeline_set() installs a PROCESS-WIDE device pointer (one per device context) that
+ *        instrumented kernels write %globaltimer stamps to — a diagnostic for overlap studies,
+ *        never set on the product path;
+ *      * kernel tuning knobs are read once from ODK_* environment variables (diagnostics);
  *  - the library allocates device memory only inside odk_anchors_create (freed by
  *    odk_anchors_destroy).  Scratch memory is passed in by the caller (odk_*_workspace_bytes).
  */
@@ -75,6 +85,17 @@ int odk_encode_locs(const odk_anchors* a, int k, const float* boxes /*[dev k,4]*
 int odk_decode_locs(const odk_anchors* a, int64_t rows, const float* pred /*[dev rows,4]*/,
                     float* out /*[dev rows,4]*/, void* stream);
 
+/* PriorBoxes.decode_locs with xp=np (od_pb.py:216-222 as NumPy evaluates it; the call check_assign.py:27 makes):
+ * pb_sizes is fp64 there, so out = clip(pred * (0.10 * tile(pb_sizes,2)) + pb_locs, 0, 1) entirely in fp64. */
+int odk_decode_locs_f64(const odk_anchors* a, int64_t rows, const double* pred /*[dev rows,4]*/,
+                        double* out /*[dev rows,4]*/, void* stream);
+
+/* ChannelArgMax / ChannelMax as stand-alone layers (layers.py:69-98): per row of `channels` values the index of the
+ * first maximum (int64, like K.argmax) and/or the maximum.  Either output may be NULL.  (odk_decode_score and
+ * odk_decode_nms fuse the same scan; these tensors never exist on the hot path.) */
+int odk_channel_argmax_max(int64_t rows, int channels, const float* x /*[dev rows,channels]*/,
+                           int64_t* arg /*[dev rows] or NULL*/, float* mx /*[dev rows] or NULL*/, void* stream);
+
 /* PriorBoxes._assign_boxes (od_pb.py:315-363) for a padded batch.  Outputs per image b with
  * G = gt_count[b]: pb_indices[b, 0:G] ascending anchor ids, gt_indices[b, 0:G] the GT each one
  * owns (both -1 beyond G), status[b] one of ODK_IMG_*. */
@@ -84,12 +105,6 @@ int odk_assign(const odk_anchors* a, int batch, const float* gt_boxes /*[dev B,G
                int64_t* pb_indices /*[dev B,Gmax]*/, int64_t* gt_indices /*[dev B,Gmax]*/,
                int32_t* status /*[dev B]*/, void* workspace /*[dev]*/, size_t workspace_bytes,
                void* stream);
-
-/* PriorBoxes.check_prior_boxes (od_pb.py:224-297), device part: for k assigned (GT box, anchor) pairs the initial
- * offsets encode_locs(box, ix) (fp64, :243) and the fp32 IoU of the box with its anchor (:252). */
-int odk_assignment_quality(const odk_anchors* a, int k, const float* boxes /*[dev k,4]*/,
-                           const int32_t* ix /*[dev k]*/, double* delta /*[dev k,4]*/,
-                           float* iou /*[dev k]*/, void* stream);
 
 /* PriorBoxes.encode_truth (od_pb.py:299-313) = odk_assign + the y_true writer.
  * y_true[b, n, :] = [mask, weight, obj, onehot(C), locs(4)] fp32, written in full (no pre-zeroing

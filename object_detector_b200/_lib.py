@@ -25,10 +25,11 @@ SIGNATURES = {
     'odk_compute_iou': (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     'odk_encode_locs': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     'odk_decode_locs': (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
+    'odk_decode_locs_f64': (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
+    'odk_channel_argmax_max': (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     'odk_assign_workspace_bytes': (c_size_t, [c_void_p, c_int, c_int]),
     'odk_assign': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                            c_void_p]),
-    'odk_assignment_quality': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     'odk_assign_encode': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_loss_workspace_bytes': (c_size_t, [c_void_p, c_int]),

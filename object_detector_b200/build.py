@@ -28,15 +28,35 @@ def needs_build() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> pathlib.Path:
+    """One nvcc -c per source file, in parallel (objects under csrc/.obj/, git-ignored), then one link."""
     if not force and not needs_build():
         return LIB
+    import concurrent.futures as cf
     nvcc = shutil.which('nvcc') or '/usr/local/cuda/bin/nvcc'
-    cmd = [nvcc] + NVCC_FLAGS + (['-Xptxas', '-v'] if verbose else []) + ['-o', str(LIB)] + [str(s) for s in SRC]
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError('nvcc failed:\n' + res.stdout + res.stderr)
+    obj_dir = PKG / 'csrc' / '.obj'
+    obj_dir.mkdir(exist_ok=True)
+    hdr_time = max(p.stat().st_mtime for p in HDR + [pathlib.Path(__file__)])
+    compile_flags = [f for f in NVCC_FLAGS if f != '-shared']
+
+    def compile_one(src):
+        obj = obj_dir / (src.stem + '.o')
+        if not force and obj.exists() and obj.stat().st_mtime > max(src.stat().st_mtime, hdr_time):
+            return obj, ''
+        cmd = [nvcc] + compile_flags + (['-Xptxas', '-v'] if verbose else []) + ['-c', '-o', str(obj), str(src)]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError(f'nvcc failed on {src.name}:\n' + res.stdout + res.stderr)
+        return obj, res.stderr
+
+    with cf.ThreadPoolExecutor(max_workers=len(SRC)) as pool:
+        results = list(pool.map(compile_one, SRC))
     if verbose:
-        print(res.stderr)
+        for _, log in results:
+            print(log)
+    res = subprocess.run([nvcc, '-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-Xcompiler', '-fPIC', '-o', str(LIB)]
+                         + [str(o) for o, _ in results], capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError('nvcc link failed:\n' + res.stdout + res.stderr)
     return LIB
 
 

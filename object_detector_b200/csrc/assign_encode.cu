@@ -473,28 +473,6 @@ __global__ void encode_locs_kernel(AnchorView av, int k, const float4* __restric
   out[4 * i + 3] = __ddiv_rn(__ddiv_rn((double)__fsub_rn(box.w, loc.w), sz.y), 0.10);
 }
 
-// check_prior_boxes (od_pb.py:224-297): per assigned (GT box, anchor) pair the initial offsets encode_locs (:243) and the
-// IoU of the GT with its anchor, ml.compute_iou(bbox, pb_locs[pb]) (:252), fp32.
-__global__ void assignment_quality_kernel(AnchorView av, int k, const float4* __restrict__ boxes, const int32_t* __restrict__ ix,
-                                          double* __restrict__ delta, float* __restrict__ iou) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= k) return;
-  const int a = ix[i];
-  if (a < 0 || a >= av.n) {
-    delta[4 * i] = delta[4 * i + 1] = delta[4 * i + 2] = delta[4 * i + 3] = __longlong_as_double(0x7ff8000000000000ll);
-    iou[i] = __int_as_float(0x7fc00000);
-    return;
-  }
-  const float4 box = boxes[i];
-  const float4 loc = av.locs[a];
-  const double2 sz = av.sizes[a];
-  delta[4 * i + 0] = __ddiv_rn(__ddiv_rn((double)__fsub_rn(box.x, loc.x), sz.x), 0.10);
-  delta[4 * i + 1] = __ddiv_rn(__ddiv_rn((double)__fsub_rn(box.y, loc.y), sz.y), 0.10);
-  delta[4 * i + 2] = __ddiv_rn(__ddiv_rn((double)__fsub_rn(box.z, loc.z), sz.x), 0.10);
-  delta[4 * i + 3] = __ddiv_rn(__ddiv_rn((double)__fsub_rn(box.w, loc.w), sz.y), 0.10);
-  iou[i] = odk_iou_value(box, odk_area(box), loc, odk_area(loc));
-}
-
 int assign_list_len(int gmax) {
   int list_len = (int)((96 * 1024) / (4 * (size_t)gmax)) & ~7;
   return list_len > 128 ? 128 : (list_len < 8 ? 8 : list_len);
@@ -626,17 +604,3 @@ extern "C" int odk_encode_locs(const odk_anchors* a, int k, const float* boxes, 
 
 ODK_TIMELINE_SETTER(odk_timeline_set_assign)
 
-extern "C" int odk_assignment_quality(const odk_anchors* a, int k, const float* boxes, const int32_t* ix, double* delta, float* iou,
-                                      void* stream) {
-  ODK_REQUIRE(a != nullptr && k >= 0, ODK_ERR_INVALID_ARGUMENT, "assignment_quality: bad arguments");
-  if (k == 0) return ODK_OK;
-  ODK_REQUIRE(boxes && ix && delta && iou, ODK_ERR_INVALID_ARGUMENT, "assignment_quality: null pointer");
-  ODK_REQUIRE(((uintptr_t)boxes & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "assignment_quality: boxes must be 16-byte aligned");
-  {
-    OdkProfileScope prof_("assignment_quality_kernel", static_cast<cudaStream_t>(stream));
-    assignment_quality_kernel<<<(k + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(odk_view(a), k, reinterpret_cast<const float4*>(boxes),
-                                                                                              ix, delta, iou);
-  }
-  ODK_LAUNCH_CHECK("assignment_quality_kernel");
-  return ODK_OK;
-}

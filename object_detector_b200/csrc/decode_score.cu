@@ -265,6 +265,43 @@ __global__ void __launch_bounds__(256) decode_locs_kernel(AnchorView av, long lo
   }
 }
 
+// decode_locs as NumPy evaluates it (od_pb.py:216-222 with xp=np, the path check_assign.py:27 takes): pb_sizes is fp64,
+// so the whole expression is fp64 — clip(pred * (0.10 * tile(pb_sizes, 2)) + pb_locs, 0, 1), one rounding per operation.
+__global__ void __launch_bounds__(256) decode_locs_f64_kernel(AnchorView av, long long rows, const double* __restrict__ pred,
+                                                              double* __restrict__ out) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += (long long)gridDim.x * blockDim.x) {
+    const int a = (int)(r % av.n);
+    const float4 lc = __ldg(av.locs + a);
+    const double2 sz = av.sizes[a];
+    const double sx = __dmul_rn(0.10, sz.x), sy = __dmul_rn(0.10, sz.y);
+    const double loc[4] = {(double)lc.x, (double)lc.y, (double)lc.z, (double)lc.w};
+    const double sc[4] = {sx, sy, sx, sy};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const double v = __dadd_rn(__dmul_rn(pred[4 * r + k], sc[k]), loc[k]);
+      out[4 * r + k] = (v != v) ? v : fmin(fmax(v, 0.0), 1.0);  // np.clip keeps NaN
+    }
+  }
+}
+
+// ChannelArgMax / ChannelMax (layers.py:69-98) on their own: one thread per row of `c` channels, first maximum wins
+// (the same scan the fused kernel above performs; the hot path never materialises these tensors).
+__global__ void __launch_bounds__(256) channel_reduce_kernel(long long rows, int c, const float* __restrict__ x,
+                                                             long long* __restrict__ arg, float* __restrict__ mx) {
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += (long long)gridDim.x * blockDim.x) {
+    const float* row = x + r * c;
+    float best = -INFINITY;
+    int cls = -1;
+    for (int j = 0; j < c; ++j) {
+      const float v = __ldg(row + j);
+      if (v > best || (cls < 0 && v == best)) { best = v; cls = j; }
+    }
+    if (cls < 0) { cls = 0; best = __ldg(row); }  // a row of NaNs: np.argmax returns 0, np.max NaN
+    if (arg != nullptr) arg[r] = cls;
+    if (mx != nullptr) mx[r] = best;
+  }
+}
+
 int sm_count_cached() {
   static int sms = 0;
   if (sms == 0) {
@@ -350,6 +387,32 @@ int odk_launch_decode_locs(const odk_anchors* a, long long rows, const float* pr
                                                               reinterpret_cast<float4*>(out));
   }
   ODK_LAUNCH_CHECK("decode_locs_kernel");
+  return ODK_OK;
+}
+
+int odk_launch_decode_locs_f64(const odk_anchors* a, long long rows, const double* pred, double* out, cudaStream_t stream) {
+  long long blocks = (rows + 255) / 256;
+  const long long cap = (long long)sm_count_cached() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  {
+    OdkProfileScope prof_("decode_locs_f64_kernel", stream);
+    decode_locs_f64_kernel<<<(unsigned)blocks, 256, 0, stream>>>(odk_view(a), rows, pred, out);
+  }
+  ODK_LAUNCH_CHECK("decode_locs_f64_kernel");
+  return ODK_OK;
+}
+
+int odk_launch_channel_reduce(long long rows, int c, const float* x, long long* arg, float* mx, cudaStream_t stream) {
+  long long blocks = (rows + 255) / 256;
+  const long long cap = (long long)sm_count_cached() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  {
+    OdkProfileScope prof_("channel_reduce_kernel", stream);
+    channel_reduce_kernel<<<(unsigned)blocks, 256, 0, stream>>>(rows, c, x, arg, mx);
+  }
+  ODK_LAUNCH_CHECK("channel_reduce_kernel");
   return ODK_OK;
 }
 

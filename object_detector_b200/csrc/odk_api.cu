@@ -21,6 +21,8 @@ int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, 
                             int32_t* classes, float* confs, float* boxes, bool dense, float conf_thr,
                             unsigned long long* cand_keys, int* piece_count, cudaStream_t stream);
 int odk_launch_decode_locs(const odk_anchors* a, long long rows, const float* pred, float* out, cudaStream_t stream);
+int odk_launch_decode_locs_f64(const odk_anchors* a, long long rows, const double* pred, double* out, cudaStream_t stream);
+int odk_launch_channel_reduce(long long rows, int c, const float* x, long long* arg, float* mx, cudaStream_t stream);
 
 // ---- per-launch event timing (used by bench.py for the roofline line) -------------------------------
 #include <string>
@@ -186,6 +188,21 @@ extern "C" int odk_decode_locs(const odk_anchors* a, int64_t rows, const float* 
   ODK_REQUIRE(pred && out, ODK_ERR_INVALID_ARGUMENT, "decode_locs: null pointer");
   ODK_REQUIRE((((uintptr_t)pred | (uintptr_t)out) & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_locs: buffers must be 16-byte aligned");
   return odk_launch_decode_locs(a, rows, pred, out, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int odk_decode_locs_f64(const odk_anchors* a, int64_t rows, const double* pred, double* out, void* stream) {
+  ODK_REQUIRE(a != nullptr && rows >= 0, ODK_ERR_INVALID_ARGUMENT, "decode_locs_f64: bad arguments");
+  ODK_REQUIRE(rows % a->n == 0, ODK_ERR_INVALID_ARGUMENT, "decode_locs_f64: rows=%lld is not a multiple of N=%d", (long long)rows, a->n);
+  if (rows == 0) return ODK_OK;
+  ODK_REQUIRE(pred && out, ODK_ERR_INVALID_ARGUMENT, "decode_locs_f64: null pointer");
+  return odk_launch_decode_locs_f64(a, rows, pred, out, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int odk_channel_argmax_max(int64_t rows, int channels, const float* x, int64_t* arg, float* mx, void* stream) {
+  ODK_REQUIRE(rows >= 0 && channels >= 1, ODK_ERR_INVALID_ARGUMENT, "channel_argmax_max: rows=%lld channels=%d", (long long)rows, channels);
+  if (rows == 0) return ODK_OK;
+  ODK_REQUIRE(x && (arg || mx), ODK_ERR_INVALID_ARGUMENT, "channel_argmax_max: null pointer");
+  return odk_launch_channel_reduce(rows, channels, x, reinterpret_cast<long long*>(arg), mx, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int odk_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs, int32_t* classes,

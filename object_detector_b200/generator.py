@@ -15,12 +15,18 @@ import threading
 import time
 
 
+class _Failed:
+    """Per-item failure marker a batched function may return in place of a result: only that caller raises."""
+
+    def __init__(self, error):
+        self.error = error
+
+
 class BatchCoalescer:
     """Turns a batched function ``fn_batch(list_of_items) -> sequence_of_results`` into a thread-safe
     per-item callable.  Items submitted by different threads within ``max_wait_ms`` of the first one (at most
     ``max_batch``) are served by one ``fn_batch`` call.  An exception raised by ``fn_batch`` is re-raised in
-    every caller of that batch (per-image data errors therefore fail the whole micro-batch; callers that need
-    isolation can retry singly)."""
+    every caller of that batch; a ``_Failed`` entry in its result fails only the caller of that item."""
 
     _STOP = object()
 
@@ -66,7 +72,10 @@ class BatchCoalescer:
                 if len(results) != len(batch):
                     raise RuntimeError(f'batched function returned {len(results)} results for {len(batch)} items')
                 for s, r in zip(batch, results):
-                    s['result'] = r
+                    if isinstance(r, _Failed):
+                        s['error'] = r.error
+                    else:
+                        s['result'] = r
             except BaseException as e:  # noqa: BLE001 - delivered to the callers
                 for s in batch:
                     s['error'] = e
@@ -83,11 +92,31 @@ def collate_truth(pb, annotations):
     return pb.encode_truth(list(annotations))
 
 
-def encode_truth_hook(od, max_batch=64, max_wait_ms=2.0):
+def encode_truth_hook(od, max_batch=64, max_wait_ms=2.0, device=None):
     """Replacement for the reference's ``lambda y: pb.encode_truth([y])[0]`` (dl/od.py:169): same per-sample
     call shape, but concurrent calls from the generator's worker threads share one ``odk_assign_encode``
     launch.  Returns the callable; ``hook.coalescer.close()`` stops the worker thread."""
-    co = BatchCoalescer(lambda ys: list(od.pb.encode_truth(ys)), max_batch=max_batch, max_wait_ms=max_wait_ms)
+    import torch
+    # the worker thread has its own "current device" (device 0 by default): pin it to the device that is current
+    # where the hook is built — in a one-process-per-GPU job that is the rank's GPU
+    dev = torch.cuda.current_device() if device is None else torch.device(device).index
+
+    def run(ys):
+        with torch.cuda.device(dev):
+            try:
+                return list(od.pb.encode_truth(ys))
+            except AssertionError:
+                if len(ys) == 1:
+                    raise
+            # a bad sample fails only its own call, as in the reference (od_pb.py:304,332,338 raise per sample)
+            out = []
+            for y in ys:
+                try:
+                    out.append(od.pb.encode_truth([y])[0])
+                except AssertionError as e:
+                    out.append(_Failed(e))
+            return out
+    co = BatchCoalescer(run, max_batch=max_batch, max_wait_ms=max_wait_ms)
 
     def hook(y):
         return co(y)

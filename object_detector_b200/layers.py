@@ -67,21 +67,39 @@ def nms():
     return NMS
 
 
+def _channel_reduce(inputs, want_arg):
+    is_np = not isinstance(inputs, torch.Tensor)
+    dev = _dev.device(None if is_np or not inputs.is_cuda else inputs.device)
+    x = _dev.to_device(inputs, torch.float32, dev)
+    rows, c = x.numel() // x.shape[-1], x.shape[-1]
+    out = torch.empty(x.shape[:-1], dtype=torch.int64 if want_arg else torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call('odk_channel_argmax_max', rows, c, x.data_ptr(), out.data_ptr() if want_arg else 0,
+                  0 if want_arg else out.data_ptr(), _dev.stream_ptr(dev))
+    return out.cpu().numpy() if is_np else out
+
+
 def channel_argmax():
-    """layers.py:69-82."""
+    """layers.py:69-82: argmax over the last axis, int64, first maximum wins (``odk_channel_argmax_max``)."""
 
     class ChannelArgMax:
+        def compute_output_shape(self, input_shape):
+            return input_shape[:-1]
+
         def __call__(self, inputs):
-            return torch.argmax(inputs, dim=-1)
+            return _channel_reduce(inputs, True)
 
     return ChannelArgMax
 
 
 def channel_max():
-    """layers.py:85-98."""
+    """layers.py:85-98: max over the last axis (``odk_channel_argmax_max``)."""
 
     class ChannelMax:
+        def compute_output_shape(self, input_shape):
+            return input_shape[:-1]
+
         def __call__(self, inputs):
-            return torch.max(inputs, dim=-1).values
+            return _channel_reduce(inputs, False)
 
     return ChannelMax

@@ -38,22 +38,6 @@ class ObjectsAnnotation:
         """Pixel boxes: round-half-even of the f64 product (ml.py:62-65)."""
         return np.round(self.bboxes * [self.width, self.height, self.width, self.height]).astype(np.int32)
 
-    @property
-    def bboxes_ar_fixed(self):
-        """Boxes rescaled as if the image were padded to a square (ml.py:67-78; used for anchor fitting)."""
-        assert self.width > 0 and self.height > 0
-        out = np.copy(self.bboxes)
-        if self.width > self.height:
-            out[:, [1, 3]] *= self.height / self.width
-        elif self.width < self.height:
-            out[:, [0, 2]] *= self.width / self.height
-        return out
-
-    def to_str(self, class_names):
-        """ml.py:90-95: one line per object, ordered by (y, x) of the pixel box."""
-        items = sorted(zip(self.real_bboxes, self.classes), key=lambda t: _pixel_box_order(t[0]))
-        return '\n'.join(f'({x1}, {y1}) [{x2 - x1} x {y2 - y1}]: {class_names[c]}' for (x1, y1, x2, y2), c in items)
-
     def rot90(self, k):
         """Quarter turns of the normalised boxes (ml.py:102-112)."""
         assert 0 <= k <= 3
@@ -84,12 +68,6 @@ class ObjectsPrediction:
     def get_real_bboxes(self, width, height):
         return np.round(self.bboxes * [width, height, width, height]).astype(np.int32)  # ml.py:184-186
 
-    def to_str(self, width, height, class_names, conf_threshold=0):
-        """ml.py:146-152."""
-        items = sorted(zip(self.get_real_bboxes(width, height), self.classes, self.confs), key=lambda t: _pixel_box_order(t[0]))
-        return '\n'.join(f'({x1}, {y1}) [{x2 - x1} x {y2 - y1}]: {class_names[c]}'
-                         for (x1, y1, x2, y2), c, cf in items if cf >= conf_threshold)
-
     def is_match(self, classes, bboxes, conf_threshold=0, iou_threshold=0.5):
         """ml.py:159-182: True when the detections with conf >= conf_threshold match the given objects one-to-one
         (IoU >= iou_threshold, same classes).  Evaluated by ``odk_exact_match``."""
@@ -97,9 +75,6 @@ class ObjectsPrediction:
         assert bboxes.shape == (len(classes), 4)
         return bool(_exact_matches([(np.asarray(classes), bboxes)], [self], conf_threshold, iou_threshold)[0])
 
-    def __repr__(self):
-        return (f'{type(self).__module__}.{type(self).__name__}(classes={self.classes!r}, '
-                f'confs={self.confs!r}, bboxes={self.bboxes!r})')
 
 
 def bboxes_center(bboxes):
@@ -152,11 +127,6 @@ def non_maximum_suppression(boxes, scores, top_k=200, iou_threshold=0.45):
     k = int(cnt.item())
     res = out[:k].to(torch.int64)
     return res.cpu().numpy() if is_np else res
-
-
-def _pixel_box_order(box):
-    """Sort key of the reference's listings (``_rbb_sortkey``, ml.py:783-786): top-to-bottom, then left-to-right."""
-    return box[1], box[0], box[3], box[2]
 
 
 def _exact_matches(gt, pred, conf_threshold, iou_threshold):

@@ -31,6 +31,7 @@ class ObjectDetector:
 
     def __init__(self, input_size, map_sizes, num_classes):
         self.pb = od_pb.PriorBoxes(input_size, map_sizes, num_classes)
+        self.strict_nms = True  # the reference builds the strict graph by default (od.py:80,207 -> od_net.py:175)
 
     def to_dict(self):
         data = {'version': _JSON_VERSION, 'input_size': self.pb.input_size, 'map_sizes': self.pb.map_sizes,
@@ -65,12 +66,13 @@ class ObjectDetector:
         """The ProcessOutput hook of the training pipeline (od.py:169): one annotation -> (N, 3+C+4)."""
         return self.pb.encode_truth([y])[0]
 
-    def predict_from_head(self, objs, clfs, locs, conf_threshold=0.01, top_k=200, nms_threshold=0.45, strict_nms=False):
+    def predict_from_head(self, objs, clfs, locs, conf_threshold=0.01, top_k=200, nms_threshold=0.45, strict_nms=None):
         """What ``predict`` does after the CNN (od_net.py:186-190 + od.py:258-266, keep_aspect=False):
         head outputs -> list of ObjectsPrediction with confs >= conf_threshold.  ``strict_nms=True`` adds the
-        all-class pass at 0.5 (od_net.py:175); ``None`` uses what ``load_voc`` was given."""
+        all-class pass at 0.5 (od_net.py:175); the default ``None`` uses what ``load_voc`` was given, which itself
+        defaults to True like the reference (od.py:80-97)."""
         if strict_nms is None:
-            strict_nms = getattr(self, 'strict_nms', False)
+            strict_nms = self.strict_nms
         out = self.pb.decode_nms(objs, clfs, locs, top_k=top_k, nms_threshold=nms_threshold,
                                  nms_all_threshold=0.5 if strict_nms else None)
         return unpack_predictions(out, conf_threshold)

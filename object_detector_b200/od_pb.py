@@ -6,8 +6,9 @@ class (od_pb.py:13-363); the arithmetic runs in libodk's sm_100a kernels.  Ancho
 on the host exactly as ``_create_pb`` does (od_pb.py:125-184) because the kernels compare against
 them bit for bit, then uploaded once per device.
 
-Out of scope here: ``fit`` (offline KMeans), ``check_prior_boxes``, the Keras
-``loss*`` / ``metrics`` graph functions.
+Out of scope here: ``fit`` (offline KMeans anchor fitting, od_pb.py:63-123) and
+``check_prior_boxes`` (a logging diagnostic, od_pb.py:224-297).  The ``loss*`` / ``metrics`` functions
+(od_pb.py:365-431) are mirrored as device calls (``loss_terms`` and friends).
 
 Besides the reference's host-array API there is a batched device API (``encode_truth_batch``,
 ``decode_score``, ``decode_nms``) that takes / returns torch CUDA tensors and never synchronises.
@@ -37,7 +38,6 @@ class PriorBoxes:
         self.pb_centers = np.empty((0,))
         self.pb_sizes = np.empty((0,))
         self.pb_mask = np.empty((0,))
-        self.pb_info = []
         assert np.array(self.input_size).shape == (2,)
         assert len(self.map_sizes.shape) == 1 and len(self.map_sizes) >= 1
         assert self.num_classes >= 1
@@ -58,60 +58,48 @@ class PriorBoxes:
 
     # ------------------------------------------------------------------ tables (od_pb.py:125-198)
     def _create_pb(self):
-        """Host-side table construction; every rounding step follows od_pb.py:133-177 (f32 linspace,
-        f64 offsets added in place into f32 arrays, closed-interval validity test)."""
+        """Host-side table construction.  The kernels compare GT centres against these tables bit for bit, so every
+        rounding step of od_pb.py:133-177 is kept: f32 ``linspace`` ticks, f64 offsets added in place into f32 arrays
+        (``+=`` keeps the array dtype), f64 ``pb_sizes``, closed-interval validity test on the clipped box centre.
+        The per-(map, pattern) ``pb_info`` dicts of the reference only feed ``check_prior_boxes`` (out of scope);
+        ``pb_info_indices`` — which (map, pattern) plane an anchor belongs to — is kept as an output table."""
         self._release()
         inv_px = 1 / np.array(self.input_size)
-        n_pat = len(self.pb_size_patterns)
-        parts = {k: [] for k in ('grid', 'locs', 'centers', 'sizes', 'mask', 'info')}
-        self.pb_info = []
+        planes = []  # one entry per (map, pattern): grid, locs, centres, sizes, mask
         for map_size in self.map_sizes:
             cell = 1.0 / map_size
             ticks = np.linspace(0.5 * cell, 1 - 0.5 * cell, map_size, dtype=np.float32)
             xs, ys = np.meshgrid(ticks, ticks)
-            xy = np.concatenate((xs.reshape(-1, 1), ys.reshape(-1, 1)), axis=1)
-            centre4 = np.tile(xy, (1, 2))
-            grid = np.copy(centre4)
+            centre4 = np.tile(np.stack([xs.ravel(), ys.ravel()], axis=1), (1, 2))
+            grid = centre4.copy()
             grid[:, :2] -= cell / 2
             grid[:, 2:] += cell / 2 + inv_px
             for pattern in self.pb_size_patterns:
                 size = cell * pattern
-                box = np.copy(centre4)
+                box = centre4.copy()
                 box[:, :2] -= size / 2
                 box[:, 2:] += size / 2 + inv_px
                 clipped = np.clip(box, 0, 1)
                 cc = (clipped[:, :2] + clipped[:, 2:]) / 2
-                inside = np.all((grid[:, :2] <= cc) & (cc <= grid[:, 2:]), axis=-1)  # math.between
-                parts['grid'].append(grid)
-                parts['locs'].append(box)
-                parts['centers'].append(centre4[:, :2])
-                parts['sizes'].append(np.tile(size, (len(box), 1)))
-                parts['mask'].append(inside)
-                parts['info'].append(np.full(len(box), len(self.pb_info), dtype=np.int64))
-                self.pb_info.append({
-                    'map_size': map_size,
-                    'size': np.sqrt(size.prod()),
-                    'aspect_ratio': size[0] / size[1],
-                    'count': len(box),
-                })
-        self.pb_grid = np.concatenate(parts['grid'])
-        self.pb_locs = np.concatenate(parts['locs'])
-        self.pb_info_indices = np.concatenate(parts['info'])
-        self.pb_centers = np.concatenate(parts['centers'])
-        self.pb_sizes = np.concatenate(parts['sizes'])
-        self.pb_mask = np.concatenate(parts['mask'])
-        assert len(self.pb_info) == len(self.map_sizes) * n_pat
+                inside = ((grid[:, :2] <= cc) & (cc <= grid[:, 2:])).all(axis=-1)  # math.between (closed)
+                planes.append((grid, box, centre4[:, :2], np.tile(size, (len(box), 1)), inside))
+        self.pb_grid, self.pb_locs, self.pb_centers, self.pb_sizes, self.pb_mask = (
+            np.concatenate([pl[k] for pl in planes]) for k in range(5))
+        self.pb_info_indices = np.repeat(np.arange(len(planes), dtype=np.int64), [len(pl[1]) for pl in planes])
         self._check_state()
 
     def _check_state(self):
+        """Consistency of the tables (the reference's od_pb.py:186-198 checks): one row per anchor in every table, and
+        every unclipped anchor centre lies in its own half-open grid cell — the property ``for_each_cell_candidate``
+        in csrc/assign_encode.cu relies on."""
         n = len(self.pb_locs)
-        assert self.pb_locs.shape == (n, 4), f'shape error: {self.pb_locs.shape}'
-        assert self.pb_info_indices.shape == (n,), f'shape error: {self.pb_info_indices.shape}'
-        assert self.pb_centers.shape == (n, 2), f'shape error: {self.pb_centers.shape}'
-        assert self.pb_sizes.shape == (n, 2), f'shape error: {self.pb_sizes.shape}'
-        assert self.pb_mask.shape == (n,), f'shape error: {self.pb_mask.shape}'
-        ct = np.mean([self.pb_locs[:, 2:], self.pb_locs[:, :2]], axis=0)
-        assert ((self.pb_grid[:, :2] <= ct) & (ct < self.pb_grid[:, 2:])).all()  # math.in_range
+        expect = {'pb_locs': (n, 4), 'pb_grid': (n, 4), 'pb_info_indices': (n,), 'pb_centers': (n, 2),
+                  'pb_sizes': (n, 2), 'pb_mask': (n,)}
+        for name, shape in expect.items():
+            got = getattr(self, name).shape
+            assert got == shape, f'{name}: expected {shape}, got {got}'
+        mid = np.mean([self.pb_locs[:, 2:], self.pb_locs[:, :2]], axis=0)
+        assert ((self.pb_grid[:, :2] <= mid) & (mid < self.pb_grid[:, 2:])).all(), 'anchor centre outside its grid cell'
 
     def __len__(self):
         return len(self.pb_locs)
@@ -170,19 +158,20 @@ class PriorBoxes:
         return res[0] if scalar else res
 
     def decode_locs(self, pred, xp=None):
-        """od_pb.py:216-222 evaluated as the fp32 Keras Lambda (od_net.py:189):
-        clip(pred * float32(0.10*tile(pb_sizes,2)) + pb_locs, 0, 1).  NumPy in -> NumPy fp32 out,
-        torch CUDA tensor in -> torch tensor out (no sync).  ``xp`` is accepted for signature
-        compatibility and ignored (the reference's xp=np path computes the same expression in fp64)."""
-        del xp
+        """od_pb.py:216-222.  ``xp=None`` is the in-graph use (od_net.py:189): the fp32 Keras Lambda
+        clip(pred * float32(0.10*tile(pb_sizes,2)) + pb_locs, 0, 1); NumPy in -> NumPy fp32 out, torch CUDA tensor
+        in -> torch tensor out (no sync).  ``xp=np`` is the NumPy use (check_assign.py:27): pb_sizes is fp64 there,
+        so the expression is evaluated in fp64 and a float64 array comes back (``odk_decode_locs_f64``)."""
         is_np = not isinstance(pred, torch.Tensor)
         dev = _dev.device(None if is_np or not pred.is_cuda else pred.device)
-        t = _dev.to_device(pred, torch.float32, dev)
+        f64 = xp is np
+        t = _dev.to_device(pred, torch.float64 if f64 else torch.float32, dev)
         if t.shape[-1] != 4 or t.shape[-2] != len(self.pb_locs):
             raise ValueError(f'decode_locs: expected (..., {len(self.pb_locs)}, 4), got {tuple(t.shape)}')
         out = torch.empty_like(t)
         with torch.cuda.device(dev):
-            _lib.call('odk_decode_locs', self._handle(dev), t.numel() // 4, t.data_ptr(), out.data_ptr(), _dev.stream_ptr(dev))
+            _lib.call('odk_decode_locs_f64' if f64 else 'odk_decode_locs', self._handle(dev), t.numel() // 4, t.data_ptr(),
+                      out.data_ptr(), _dev.stream_ptr(dev))
         return out.cpu().numpy() if is_np else out
 
     # ------------------------------------------------------------------ training targets (od_pb.py:299-363)
@@ -397,91 +386,6 @@ class PriorBoxes:
             _lib.call('odk_assign', self._handle(dev), b, boxes.data_ptr(), count.data_ptr(), gmax, pb_idx.data_ptr(),
                       gt_idx.data_ptr(), status.data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
         return {'pb_indices': pb_idx, 'gt_indices': gt_idx, 'status': status}
-
-    def check_prior_boxes(self, y_test, batch=256, print_fn=None):
-        """od_pb.py:224-297: how well the prior boxes fit a dataset.  The whole dataset is assigned in batches
-        (``odk_assign``), the initial offsets and GT-anchor IoUs of all assigned pairs come from one more launch
-        (``odk_assignment_quality``); the statistics and the log lines are then formed on the host exactly as the
-        reference prints them.  Logs through ``logging`` (or ``print_fn``) and also returns the numbers."""
-        import logging
-        from . import textstats
-        emit = print_fn or logging.getLogger(__name__).info
-        dev = _dev.device()
-        for y in y_test:
-            for class_id in y.classes:
-                assert 0 <= class_id < self.num_classes  # od_pb.py:246
-        total_gt_boxes = sum([np.sum(np.logical_not(y.difficults)) for y in y_test])
-        pair_boxes, pair_pb, pair_img, pair_gt, assigned_count_list = [], [], [], [], []
-        for s0 in range(0, len(y_test), batch):
-            chunk = y_test[s0:s0 + batch]
-            boxes, _, counts = self._pad_gt(chunk)
-            res = self.assign_batch(boxes, counts)
-            self._raise_for_status(res['status'].cpu().numpy(), chunk)
-            pb_idx, gt_idx = res['pb_indices'].cpu().numpy(), res['gt_indices'].cpu().numpy()
-            for i, g in enumerate(counts):
-                assigned_count_list.append(int(g))  # one prior box per GT (od_pb.py:239)
-                pair_pb.append(pb_idx[i, :g])
-                pair_gt.append(gt_idx[i, :g])
-                pair_img.append(np.full(g, s0 + i, dtype=np.int64))
-                pair_boxes.append(boxes[i][gt_idx[i, :g]])
-        pair_pb = np.concatenate(pair_pb) if pair_pb else np.zeros(0, np.int64)
-        pair_gt = np.concatenate(pair_gt) if pair_gt else np.zeros(0, np.int64)
-        pair_img = np.concatenate(pair_img) if pair_img else np.zeros(0, np.int64)
-        pair_boxes = np.concatenate(pair_boxes).astype(np.float32) if pair_boxes else np.zeros((0, 4), np.float32)
-        k = len(pair_pb)
-        delta = torch.empty((k, 4), dtype=torch.float64, device=dev)
-        iou = torch.empty((k,), dtype=torch.float32, device=dev)
-        if k:
-            d_boxes = _dev.to_device(pair_boxes, torch.float32, dev)
-            d_ix = _dev.to_device(pair_pb.astype(np.int32), torch.int32, dev)
-            with torch.cuda.device(dev):
-                _lib.call('odk_assignment_quality', self._handle(dev), k, d_boxes.data_ptr(), d_ix.data_ptr(), delta.data_ptr(),
-                          iou.data_ptr(), _dev.stream_ptr(dev))
-        delta, iou = delta.cpu().numpy(), iou.cpu().numpy()
-        # per object (od_pb.py:245-267): every GT owns exactly one prior box, so the "not assigned" branch stays empty
-        assigned_counts = np.zeros((len(self.pb_info),))
-        y_true, y_pred, iou_list = [], [], []
-        total_errors = 0
-        slot_of = {(int(i), int(g)): j for j, (i, g) in enumerate(zip(pair_img, pair_gt))}
-        for img, y in enumerate(y_test):
-            for gt_ix, (class_id, difficult) in enumerate(zip(y.classes, y.difficults)):
-                if difficult:
-                    continue
-                j = slot_of.get((img, gt_ix))
-                if j is not None:
-                    max_iou = iou[j]
-                    assigned_counts[self.pb_info_indices[pair_pb[j]]] += 1
-                else:
-                    max_iou = 0
-                    total_errors += 1
-                y_true.append(class_id)
-                y_pred.append(class_id if max_iou >= 0.5 else None)
-                iou_list.append(max_iou)
-        lines = ['assigned counts:']
-        for i, c in enumerate(assigned_counts):
-            lines.append('  prior boxes{m=%d, size=%.2f ar=%.2f} = %d (%.02f%%)' % (
-                self.pb_info[i]['map_size'], self.pb_info[i]['size'], self.pb_info[i]['aspect_ratio'], c,
-                100 * c / self.pb_info[i]['count'] / total_gt_boxes))
-        lines.append('recall (prior box iou >= 0.5):')
-        y_true, y_pred = np.array(y_true), np.array(y_pred)
-        recall = {}
-        with np.errstate(invalid='ignore', divide='ignore'):
-            for class_id in range(self.num_classes):
-                y_mask = y_true == class_id
-                class_ok, class_all = (y_pred[y_mask] == class_id).sum(), y_mask.sum()
-                recall[class_id] = (int(class_ok), int(class_all))
-                lines.append(f'  class{class_id:02d} : {class_ok:5d} / {class_all:5d} = {100 * class_ok / class_all:5.1f}%')
-        lines.append('total errors: %d / %d (%.02f%%)' % (total_errors, total_gt_boxes, 100 * total_errors / total_gt_boxes))
-        lines.append('Avg IOU: %.1f' % (np.mean(iou_list) * 100))
-        lines.extend(textstats.histogram_lines(assigned_count_list, title='assigned_count'))
-        lines.append('assigned count per image: median=%d min=%d max=%d' % (
-            np.median(assigned_count_list), min(assigned_count_list), max(assigned_count_list)))
-        lines.extend(textstats.histogram_lines([np.mean(np.abs(dl)) for dl in delta], title='mean_abs_delta'))
-        lines.append('delta loc: mean=%.2f std=%.2f min=%.2f max=%.2f' % (delta.mean(), delta.std(), delta.min(), delta.max()))
-        for line in lines:
-            emit(line)
-        return {'lines': lines, 'assigned_counts': assigned_counts, 'recall': recall, 'total_errors': total_errors,
-                'iou': np.asarray(iou_list), 'delta_locs': delta, 'assigned_count_per_image': assigned_count_list}
 
     # ------------------------------------------------------------------ prediction side (od_net.py:172-192)
     def _head_inputs(self, objs, clfs, locs):

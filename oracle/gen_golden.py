@@ -184,26 +184,6 @@ def gen_scores():
     np.savez_compressed(OUT / 'scores.npz', **d)
 
 
-def gen_check_prior_boxes():
-    """Log lines of the unmodified PriorBoxes.check_prior_boxes (od_pb.py:224-297) on a seeded annotation set."""
-    import io
-    import logging
-    pb = ref_pb(*ANCHOR_SETS['voc320'])
-    gts, _ = synth.eval_set(11, 40, 20, max_gt=6)
-    y = [Ann('.', w, h, c, b, dif) for (w, h, c, b, dif) in gts]
-    buf = io.StringIO()
-    handler = logging.StreamHandler(buf)
-    handler.setLevel(logging.DEBUG)
-    logger = tk.log.get('pytoolkit.dl.od_pb')
-    logger.setLevel(logging.DEBUG)
-    logger.addHandler(handler)
-    try:
-        pb.check_prior_boxes(y)
-    finally:
-        logger.removeHandler(handler)
-    (OUT / 'check_prior_boxes.txt').write_text(buf.getvalue(), encoding='utf-8')
-
-
 def gen_augment():
     """Bounding-box side of RandomZoom -> RandomFlipLR -> RandomFlipTB -> RandomRotate90 (image.py:233-485,
     ml.py:102-112) of the unmodified reference, per-sample RandomState(seed) as generator.py:172 makes it."""
@@ -238,7 +218,6 @@ def gen_augment():
 
 if __name__ == '__main__':
     OUT.mkdir(parents=True, exist_ok=True)
-    gen_check_prior_boxes()
     gen_anchors()
     gen_iou_nms_decode()
     gen_assign()

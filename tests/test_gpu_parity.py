@@ -50,16 +50,43 @@ def test_encode_locs_bit_exact(golden, prior_boxes):
 def test_decode_locs(golden, prior_boxes, oracle_tables):
     g = golden['iou_nms_decode']
     pb, t = prior_boxes('tiny128'), oracle_tables('tiny128')
-    out = pb.decode_locs(g['decode_tiny/pred'], xp=np)
+    out = pb.decode_locs(g['decode_tiny/pred'])
     assert out.dtype == np.float32
     assert np.array_equal(out, R.decode_locs_f32(t, g['decode_tiny/pred']))  # fp32 graph semantics: bit-exact
     # the reference's xp=np path is fp64: agree within 1e-5 relative (north_star) -> abs 2e-7 on [0,1] values
     np.testing.assert_allclose(out, g['decode_tiny/out_f64'], rtol=1e-5, atol=2e-7)
+    # xp=np (check_assign.py:27): float64, bit-for-bit the unmodified reference's output
+    out64 = pb.decode_locs(g['decode_tiny/pred'], xp=np)
+    assert out64.dtype == np.float64 and np.array_equal(out64, g['decode_tiny/out_f64'])
     pb, t = prior_boxes('voc640'), oracle_tables('voc640')
     pred = np.random.RandomState(int(g['decode_voc640/seed'])).normal(size=(1, len(pb), 4)).astype(np.float32)
     out = pb.decode_locs(pred)
     assert np.array_equal(out, R.decode_locs_f32(t, pred))
     np.testing.assert_allclose(out[0, ::997], g['decode_voc640/out_f64_rows'], rtol=1e-5, atol=2e-7)
+    out64 = pb.decode_locs(pred, xp=np)
+    assert out64.dtype == np.float64 and np.array_equal(out64[0, ::997], g['decode_voc640/out_f64_rows'])
+    assert hashlib.sha256(np.ascontiguousarray(out64).tobytes()).hexdigest() == str(g['decode_voc640/out_f64_sha256'])
+    # the exact call of check_assign.py:27: zeros in -> the clipped prior boxes themselves, float64
+    zero = pb.decode_locs(np.zeros((len(pb), 4)), xp=np)
+    assert zero.dtype == np.float64 and np.array_equal(zero, np.clip(pb.pb_locs.astype(np.float64), 0, 1))
+
+
+def test_channel_argmax_max_layers(prior_boxes):
+    """layers.channel_argmax / channel_max (layers.py:69-98) run through odk_channel_argmax_max: NumPy argmax / max
+    semantics (first maximum wins), int64 indices, ties and an all-NaN row included."""
+    rng = np.random.RandomState(8)
+    x = rng.normal(size=(3, 1000, 20)).astype(np.float32)
+    x[0, 5, :] = 0.25            # all equal: index 0
+    x[1, 7, 3] = x[1, 7, 11] = 9.0  # tie: the lower index
+    x[2, 9, :] = np.nan
+    arg = odk.layers.channel_argmax()()(x)
+    mx = odk.layers.channel_max()()(x)
+    assert arg.dtype == np.int64 and arg.shape == (3, 1000) and mx.dtype == np.float32
+    ok = ~np.isnan(x).any(axis=-1)
+    assert np.array_equal(arg[ok], x.argmax(axis=-1)[ok]) and np.array_equal(mx[ok], x.max(axis=-1)[ok])
+    assert arg[2, 9] == 0 and np.isnan(mx[2, 9]) and arg[0, 5] == 0 and arg[1, 7] == 3
+    t = torch.from_numpy(x).cuda()
+    assert torch.equal(odk.layers.channel_argmax()()(t).cpu(), torch.from_numpy(arg))
 
 
 # ----------------------------------------------------------------------------------------- assign / encode
@@ -283,7 +310,7 @@ def test_predict_from_head_matches_oracle_unpack(prior_boxes, oracle_tables):
     od = odk.ObjectDetector.load_voc((640, 640))
     t = oracle_tables('voc640')
     objs, clfs, locs = synth.predictions(3, 2, len(od.pb), 20)
-    preds = od.predict_from_head(objs, clfs, locs, conf_threshold=0.25)
+    preds = od.predict_from_head(objs, clfs, locs, conf_threshold=0.25, strict_nms=False)
     ro, _ = R.predict_tail(t, objs, clfs, locs)
     ref = R.unpack_predictions(ro, 0.25)
     for p, (rc, rs, rb) in zip(preds, ref):

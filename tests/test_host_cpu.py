@@ -135,18 +135,30 @@ def test_batch_coalescer_groups_concurrent_calls():
     co.close()
 
 
-def test_text_histogram_lines_match_golden_log():
-    """textstats.histogram_lines reproduces the histogram blocks the reference logged (math.py:26-78) — checked on
-    the 'assigned_count' block of tests/golden/check_prior_boxes.txt, whose samples are the GT counts per image."""
-    import pathlib
-    from object_detector_b200 import synth, textstats
-    want = (pathlib.Path(__file__).parent / 'golden' / 'check_prior_boxes.txt').read_text(encoding='utf-8').splitlines()
-    start = next(i for i, line in enumerate(want) if 'assigned_count' in line and line.startswith('-'))
-    gts, _ = synth.eval_set(11, 40, 20, max_gt=6)
-    counts = [len(g[2]) for g in gts]
-    assert textstats.histogram_lines(counts, title='assigned_count') == want[start:start + 13]
-    assert textstats.number_column(np.array([1, 20, 300])) == ['  1', ' 20', '300']
-    assert textstats.number_column(np.array([-0.5, 0.25])) == ['-0.500', ' 0.250']
+def test_batch_coalescer_per_item_failure_reaches_only_its_caller():
+    """A ``_Failed`` entry in the batched result (what encode_truth_hook produces for a bad sample after retrying the
+    micro-batch singly) raises in the caller of that item only — like the reference, where only the bad sample's
+    encode_truth call asserts (od_pb.py:304,332,338)."""
+    import threading
+    from object_detector_b200.generator import BatchCoalescer, _Failed
+
+    def fn(items):
+        return [_Failed(AssertionError(f'bad {i}')) if i % 5 == 0 else i + 1 for i in items]
+    co = BatchCoalescer(fn, max_batch=16, max_wait_ms=50.0)
+    out, err = {}, {}
+
+    def work(i):
+        try:
+            out[i] = co(i)
+        except AssertionError as e:
+            err[i] = str(e)
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(20)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    co.close()
+    assert err == {i: f'bad {i}' for i in range(0, 20, 5)} and out == {i: i + 1 for i in range(20) if i % 5}
 
 
 def test_coco_summarize_host_logic_matches_oracle():
