@@ -70,6 +70,10 @@ int odk_anchors_create(odk_anchors** out, int n, int num_classes, int n_maps,
 int odk_anchors_destroy(odk_anchors* a);
 int odk_anchors_count(const odk_anchors* a);
 int odk_anchors_num_classes(const odk_anchors* a);
+/* Statistics of the valid-anchor span table the fused predict path reads through (anchors with pb_mask = 0 are
+ * never fetched there: conf = x * pb_mask = 0 can not pass conf_thr >= 0, od_net.py:183-184):
+ * out4 = {tile height, spans in the table, anchor rows covered by the spans, anchors with pb_mask = 1}. */
+int odk_anchors_span_stats(const odk_anchors* a, int32_t* out4 /*[host 4]*/);
 
 /* ml.compute_iou (ml.py:502-519) on fp32 boxes: out[i*nb+j] = IoU(a[i], b[j]). */
 int odk_compute_iou(const float* a /*[dev na,4]*/, int na, const float* b /*[dev nb,4]*/, int nb,
@@ -116,6 +120,22 @@ int odk_assign_encode(const odk_anchors* a, int batch, const float* gt_boxes /*[
                       int64_t* gt_indices /*[dev B,Gmax]*/, uint8_t* pb_valids /*[dev B,N] or NULL*/,
                       int32_t* status /*[dev B]*/, void* workspace /*[dev]*/, size_t workspace_bytes,
                       void* stream);
+
+/* PriorBoxes.encode_truth (od_pb.py:299-313) with a COMPACT result, for callers whose consumer sits on the host side
+ * of PCIe (the reference's generator hands y_true to Keras through host memory, generator.py:227-240): the dense
+ * (N, 3+C+4) tensor is > 99.7 % zeros plus one repeated constant, so only what defines it leaves the kernel:
+ *   valid_bits[b, w]  bit a of word a>>5 = pb_valids[a] (third result of _assign_boxes, od_pb.py:355-361); bits >= N are 0
+ *   pos_rows[b, k, :] the y_true row of anchor pb_indices[b, k] for k < G (zeros beyond G): [w0, 1/G, 1, onehot, locs]
+ * With w0 = float32(1/max(1,G)):  y_true[b] = zeros; y_true[b, a, 0] = w0 where valid_bits says so;
+ * y_true[b, pb_indices[b, k], :] = pos_rows[b, k, :]   — bit-identical to odk_assign_encode's output
+ * (object_detector_b200.od_pb.expand_truth does exactly this).  Failed images: all bits and rows zero.
+ * Same workspace as odk_assign_encode. */
+int odk_assign_encode_compact(const odk_anchors* a, int batch, const float* gt_boxes /*[dev B,Gmax,4]*/,
+                              const int32_t* gt_classes /*[dev B,Gmax]*/, const int32_t* gt_count /*[dev B]*/,
+                              int gmax, float* pos_rows /*[dev B,Gmax,3+C+4]*/,
+                              uint32_t* valid_bits /*[dev B,ceil(N/32)]*/, int64_t* pb_indices /*[dev B,Gmax]*/,
+                              int64_t* gt_indices /*[dev B,Gmax]*/, int32_t* status /*[dev B]*/,
+                              void* workspace /*[dev]*/, size_t workspace_bytes, void* stream);
 
 /* PriorBoxes.loss / loss_obj / loss_clf / loss_loc and the rec_bg / rec_obj / acc_clf metrics
  * (od_pb.py:365-431; binary focal loss losses.py:22-30, Keras categorical_crossentropy and
@@ -295,10 +315,10 @@ int odk_bbox_flip_rot(int batch, int gmax, const double* boxes /*[dev B,Gmax,4]*
                       float* boxes_out /*[dev B,Gmax,4]*/, int32_t* classes_out /*[dev B,Gmax]*/,
                       int32_t* count_out /*[dev B]*/, void* stream);
 
-/* Diagnostics: in-kernel timeline of the six kernels of a step (candidates, greedy, rows, patch, emit, nms).
+/* Diagnostics: in-kernel timeline of the seven kernels of a step (candidates, greedy, rows, patch, emit, nms, ignore).
  * buf = 12 device words, word 2*id = earliest CTA entry (initialise to UINT64_MAX), word 2*id+1 = latest CTA exit
  * (initialise to 0), in %globaltimer nanoseconds; NULL switches it off.  Works inside CUDA-graph replays. */
-int odk_timeline_set(unsigned long long* buf /*[dev 12] or NULL*/);
+int odk_timeline_set(unsigned long long* buf /*[dev 14] or NULL*/);
 
 /* Measurement aid (bench.py): when enabled for the calling host thread every kernel launch of the
  * library is bracketed by CUDA events on its stream; odk_profile_read synchronises them and returns,

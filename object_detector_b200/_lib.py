@@ -22,6 +22,7 @@ SIGNATURES = {
     'odk_anchors_destroy': (c_int, [c_void_p]),
     'odk_anchors_count': (c_int, [c_void_p]),
     'odk_anchors_num_classes': (c_int, [c_void_p]),
+    'odk_anchors_span_stats': (c_int, [c_void_p, c_void_p]),
     'odk_compute_iou': (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     'odk_encode_locs': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     'odk_decode_locs': (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
@@ -32,6 +33,8 @@ SIGNATURES = {
                            c_void_p]),
     'odk_assign_encode': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    'odk_assign_encode_compact': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                          c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_loss_workspace_bytes': (c_size_t, [c_void_p, c_int]),
     'odk_loss': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_loss_grad': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -167,8 +167,27 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(cons
     p.ws_ncand[(size_t)b * p.gmax + g] = total;
     p.ws_nlist[(size_t)b * p.gmax + g] = stored;
   }
-  if (p.ws_ignore == nullptr) return;
-  // ---- ignore mask, scattered per GT: pb_valids[iou >= 0.5] = False (od_pb.py:355-357; order-independent
+}
+
+// Phase A': the ignore mask, scattered per GT — its own kernel (one warp per (image, GT) again) because nothing in it
+// depends on the ranking above and only encode_rows consumes it: the two chains rank -> greedy walk and
+// ignore -> rows run side by side (odk_assign_encode forks at entry) instead of one after the other inside one warp.
+__global__ void __launch_bounds__(kCandThreads, 8) assign_ignore_kernel(const AssignArgs p) {
+  OdkTimeline tl_(ODK_TL_IGNORE);
+  __shared__ int4 s_geo[kCandWarps * 32];
+  __shared__ int s_end[kCandWarps * 32];
+  __shared__ int s_nx[kCandWarps * 32];
+  const int warp = threadIdx.x >> 5;
+  const int lane = (int)odk_lane();
+  const long long task = (long long)blockIdx.x * kCandWarps + warp;
+  if (task >= (long long)p.batch * p.gmax) return;
+  const int b = (int)(task / p.gmax), g = (int)(task % p.gmax);
+  const int g_count = p.gt_count[b];
+  if (g_count < 0 || g_count > p.gmax || g >= g_count) return;
+  const float4 box = p.gt_boxes[(size_t)b * p.gmax + g];
+  const float cx = __fmul_rn(__fadd_rn(box.z, box.x), 0.5f);  // ml.py:485-488
+  const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
+  // ---- pb_valids[iou >= 0.5] = False (od_pb.py:355-357; order-independent
   //      closed form, SURVEY A-4).  Only anchors that CAN reach IoU 0.5 are visited:
   //        IoU >= 1/2  =>  I >= (A+B)/3 and min(A,B)/max(A,B) >= 1/2;  with I <= iw*min(hg,ha) and
   //        iw <= (wg+wa)/2 - |dcx|  this gives |dcx| <= (wg+wa)/6 (same in y).
@@ -181,9 +200,9 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(cons
   const float wg = __fsub_rn(box.z, box.x), hg = __fsub_rn(box.w, box.y);
   const float ga = __fmul_rn(wg, hg);
   const int n_combo = p.av.n_maps * p.av.n_patterns;
-  int* d_end = wi;                               // [32] inclusive cell-count scan
-  int4* d_geo = reinterpret_cast<int4*>(wc);     // [32] {base, m, ix_lo, iy_lo}
-  int* d_nx = wi + 32;                           // [32]
+  int* d_end = s_end + warp * 32;                // [32] inclusive cell-count scan
+  int4* d_geo = s_geo + warp * 32;               // [32] {base, m, ix_lo, iy_lo}
+  int* d_nx = s_nx + warp * 32;                  // [32]
   for (int c0 = 0; c0 < n_combo; c0 += 32) {
     // lane i owns (map, pattern) combination c0+i: its cell-(0,0) anchor gives the size shared by all its cells
     int my_m = 1, my_base = 0;
@@ -508,10 +527,10 @@ static int fill_args(AssignArgs& args, const odk_anchors* a, int batch, const fl
   return ODK_OK;
 }
 
-int odk_launch_assign_candidates(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_count, int gmax, void* lists_ws,
-                                 unsigned* ignore, cudaStream_t stream) {
+int odk_launch_assign_rank(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_count, int gmax, void* lists_ws,
+                           cudaStream_t stream) {
   AssignArgs args;
-  fill_args(args, a, batch, gt_boxes, nullptr, gt_count, gmax, nullptr, nullptr, nullptr, lists_ws, ignore);
+  fill_args(args, a, batch, gt_boxes, nullptr, gt_count, gmax, nullptr, nullptr, nullptr, lists_ws, nullptr);
   const long long tasks = (long long)batch * gmax;
   {
     OdkProfileScope prof_("assign_candidates_kernel", stream);
@@ -519,6 +538,29 @@ int odk_launch_assign_candidates(const odk_anchors* a, int batch, const float* g
   }
   ODK_LAUNCH_CHECK("assign_candidates_kernel");
   return ODK_OK;
+}
+
+// `ignore`: [B, ceil(N/32)] words, zeroed here (a memset node in front of the scatter kernel).
+int odk_launch_assign_ignore(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_count, int gmax, unsigned* ignore,
+                             cudaStream_t stream) {
+  AssignArgs args;
+  fill_args(args, a, batch, gt_boxes, nullptr, gt_count, gmax, nullptr, nullptr, nullptr, nullptr, ignore);
+  ODK_CUDA(cudaMemsetAsync(ignore, 0, sizeof(unsigned) * (size_t)batch * args.bitmap_words, stream));
+  const long long tasks = (long long)batch * gmax;
+  {
+    OdkProfileScope prof_("assign_ignore_kernel", stream);
+    odk_launch_high(assign_ignore_kernel, dim3((unsigned)((tasks + kCandWarps - 1) / kCandWarps)), dim3(kCandThreads), 0, stream, args);
+  }
+  ODK_LAUNCH_CHECK("assign_ignore_kernel");
+  return ODK_OK;
+}
+
+// Both on one stream (the fused loss entries): ranked lists, and the ignore bitmap when `ignore` is given.
+int odk_launch_assign_candidates(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_count, int gmax, void* lists_ws,
+                                 unsigned* ignore, cudaStream_t stream) {
+  if (int rc = odk_launch_assign_rank(a, batch, gt_boxes, gt_count, gmax, lists_ws, stream)) return rc;
+  if (ignore == nullptr) return ODK_OK;
+  return odk_launch_assign_ignore(a, batch, gt_boxes, gt_count, gmax, ignore, stream);
 }
 
 int odk_launch_assign_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count,

@@ -42,6 +42,7 @@ struct DecodeArgs {
   int tiles_per_image;
   int stages;  // depth of the shared-memory ring
   int stream_hint;  // 1: head outputs are fetched with an L2 evict-first policy
+  int use_spans;    // EMIT: fetch only the runs of valid anchors of a tile (av.spans); rows outside them have pb_mask = 0
 };
 
 template <int TILE, bool DENSE>
@@ -96,7 +97,25 @@ __global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const Decode
     bool tma_ok = ((rows & 15) == 0) && ((((uintptr_t)src_clf | (uintptr_t)src_obj) & 15) == 0);
     if (DENSE) tma_ok = tma_ok && (((uintptr_t)src_loc & 15) == 0);
     if (tma_ok) {
-      if (tid == 0) {
+      if (!DENSE && p.use_spans) {
+        // warp 0: lane k < ODK_MAX_SPANS fetches the k-th run of valid rows of the tile, lanes 8 / 9 the objectness and
+        // pb_mask slabs of the whole tile.  Rows between the runs are never read from HBM (their pb_mask is 0, so
+        // conf = x * 0 cannot pass conf_thr >= 0) and never looked at below.
+        if (tid < 32) {
+          const uint32_t sp = (tid < ODK_MAX_SPANS) ? __ldg(p.av.spans + (size_t)(a0 / TILE) * ODK_MAX_SPANS + tid) : 0u;
+          const uint32_t first = sp >> 16, len = sp & 0xffffu;
+          uint32_t bytes = len * (uint32_t)c * 4u, tot = bytes;
+#pragma unroll
+          for (int d = 1; d < ODK_MAX_SPANS; d <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, d);  // lanes 0..7 hold the sum
+          const uint32_t r = (uint32_t)rows;
+          if (tid == 0) odk_mbar_expect_tx(&full_bar[s], tot + r * 4 + r);
+          __syncwarp();
+          const uint64_t pol = odk_policy_evict_first();
+          if (len) odk_bulk_g2s_stream(dst + (size_t)first * c * 4, src_clf + (size_t)first * c, bytes, &full_bar[s], pol);
+          if (tid == 8) odk_bulk_g2s_stream(tail + L::kOffObj, src_obj, r * 4, &full_bar[s], pol);
+          if (tid == 9) odk_bulk_g2s(tail + L::kOffAMask, p.av.mask + a0, r, &full_bar[s]);
+        }
+      } else if (tid == 0) {
         const uint32_t r = (uint32_t)rows;
         odk_mbar_expect_tx(&full_bar[s], r * c * 4 + r * 4 + r + (DENSE ? r * 16 + r * 16 + r * 8 : 0));
         if (p.stream_hint) {
@@ -164,7 +183,9 @@ __global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const Decode
       const float* row = s_clf + (size_t)row_id * c;
       float best = -INFINITY;
       cls = 0x7fffffff;
-      if (row_id < rows) {
+      // with spans, a row with pb_mask = 0 may hold stale shared memory: it is never scanned (conf = 0, never a candidate)
+      const bool scan = row_id < rows && (DENSE || !p.use_spans || s_amask[row_id] != 0);
+      if (scan) {
         if ((c & 3) == 0) {
           // four independent running maxima (one per float4 lane) keep the dependency chains short; each is a
           // first-maximum scan of its own residue class, and the merge prefers the lower index on equal values,
@@ -208,7 +229,7 @@ __global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const Decode
         const int oc = __shfl_xor_sync(0xffffffffu, cls, d);
         if (ob > best || (ob == best && oc < cls)) { best = ob; cls = oc; }
       }
-      if (owner) {
+      if (owner && scan) {
         // a row of NaNs leaves best = -inf in every part: np.argmax returns 0 there
         if (cls == 0x7fffffff) { cls = 0; best = row[0]; }
         const float maskf = s_amask[row_id] ? 1.0f : 0.0f;
@@ -320,6 +341,11 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   static const int env_per_sm = getenv("ODK_EMIT_PER_SM") ? atoi(getenv("ODK_EMIT_PER_SM")) : 0;
   static const int env_hint = getenv("ODK_EMIT_HINT") ? atoi(getenv("ODK_EMIT_HINT")) : 1;
   args.stream_hint = env_hint;
+  // spans need 16-byte aligned row starts (C % 4 == 0), a table built for this tile height, conf_thr >= 0 (a masked
+  // anchor's conf is 0 or NaN: it can only be a candidate for a negative threshold) — else the whole tile is fetched
+  static const int env_spans = getenv("ODK_EMIT_SPANS") ? atoi(getenv("ODK_EMIT_SPANS")) : 1;
+  args.use_spans = (!DENSE && env_spans && (args.c & 3) == 0 && args.av.spans != nullptr && args.av.span_tile == TILE &&
+                    args.conf_thr >= 0.0f) ? 1 : 0;
   // EMIT: a 2-deep ring at 3 CTAs per SM (3 x 43 KB at C = 20).  Same shared memory per SM as 2 CTAs x 3 stages, but the
   // smaller CTAs still fit two at a time beside a per-image NMS CTA (~120 KB) of another batch in flight
   // (profiles/emit_sweep_r01i.log: step 46.3 -> 45.5 us, the kernel 26.3 -> 24.1 us).

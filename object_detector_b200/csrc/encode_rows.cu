@@ -11,17 +11,27 @@
 //                          307-311; they are valid whatever the ignore mask says, od_pb.py:359-361), and the
 //                          all-zero result of images whose assignment failed.
 //
-// Stream layout inside odk_assign_encode: the caller's stream runs memset -> candidates (+ ignore mask) -> greedy;
-// a per-thread side stream, forked after the candidates and joined with events (capturable into a CUDA graph),
-// runs the rows kernel next to the greedy walk; the patch kernel runs on the caller's stream after the join.
+// Stream layout inside odk_assign_encode — two independent chains, forked at entry and joined with events (capturable
+// into a CUDA graph):
+//     caller's stream            ranked candidate lists -> greedy walk          (latency-bound, a few SMs)
+//     library-owned side stream  memset -> ignore mask  -> rows kernel          (the HBM-bound write)
+// then the patch kernel on the caller's stream after the join.  The rows kernel needs only the ignore bitmap and the
+// walk only the ranked lists, so neither chain waits for the other's first kernel.
+//
+// odk_assign_encode_compact is the same assignment with a COMPACT result for callers whose consumer is on the host:
+// instead of the dense (N, 3+C+4) tensor — 1.8 MB per image of which > 99.7 % is zeros and one repeated constant — it
+// writes the packed pb_valids bits, the <= G positive rows and the index lists (~10 KB per image); the dense tensor is
+// a trivial host-side expansion of those (object_detector_b200.od_pb.expand_truth).
 #include <stdlib.h>
 
 #include "odk_common.cuh"
 
 // from assign_encode.cu
 size_t odk_assign_lists_bytes(int batch, int gmax);
-int odk_launch_assign_candidates(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_count, int gmax, void* lists_ws,
-                                 unsigned* ignore, cudaStream_t stream);
+int odk_launch_assign_rank(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_count, int gmax, void* lists_ws,
+                           cudaStream_t stream);
+int odk_launch_assign_ignore(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_count, int gmax, unsigned* ignore,
+                             cudaStream_t stream);
 int odk_launch_assign_greedy(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count,
                              int gmax, int64_t* pb_indices, int64_t* gt_indices, int32_t* status, void* lists_ws, cudaStream_t stream);
 int odk_assign_check(const odk_anchors* a, int batch, const void* gt_boxes, const void* gt_count, int gmax, const void* pb, const void* gt,
@@ -42,6 +52,9 @@ struct EncodeArgs {
 
 constexpr int kRowsThreads = 256;
 constexpr int kRowsPerThread = 8;  // 16-byte stores per thread
+#ifndef ODK_ROWS_PER_SM_DEFAULT
+#define ODK_ROWS_PER_SM_DEFAULT 0
+#endif
 
 // y_true of one image is a contiguous array of N*W floats, all zero except column 0.  Each thread produces whole
 // 16-byte pieces of it in registers — a piece holds at most one column-0 element because W >= 8 — and stores them
@@ -49,9 +62,7 @@ constexpr int kRowsPerThread = 8;  // 16-byte stores per thread
 // A thread's pieces are kRowsThreads*VEC floats apart; (row, column) of the first comes from one division, the
 // others by adding the constant step; the bitmap words of all pieces are loaded before the first store.
 template <int VEC>
-__global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeArgs p, unsigned step_rows, unsigned step_cols) {
-  OdkTimeline tl_(ODK_TL_ROWS);
-  const int b = blockIdx.y;
+__device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, unsigned chunk, unsigned step_rows, unsigned step_cols) {
   const unsigned W = 3 + p.av.num_classes + 4;
   const unsigned n = (unsigned)p.av.n;
   const int g_count = p.gt_count[b];
@@ -62,7 +73,7 @@ __global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeA
   const unsigned total = n * W;  // floats per image (< 2^31, checked by the launcher)
   float* y = p.y_true + (size_t)b * total;
   const unsigned pieces = (total + VEC - 1) / VEC;
-  const unsigned i0 = blockIdx.x * (kRowsThreads * kRowsPerThread) + threadIdx.x;
+  const unsigned i0 = chunk * (kRowsThreads * kRowsPerThread) + threadIdx.x;
   unsigned row = (i0 * VEC) / W, col = (i0 * VEC) - row * W;
   float w[kRowsPerThread];
   int j[kRowsPerThread];
@@ -103,6 +114,27 @@ __global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeA
   }
 }
 
+// One CTA per chunk of kRowsThreads * kRowsPerThread pieces: grid (chunks per image, batch).
+template <int VEC>
+__global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeArgs p, unsigned step_rows, unsigned step_cols) {
+  OdkTimeline tl_(ODK_TL_ROWS);
+  encode_rows_chunk<VEC>(p, blockIdx.y, blockIdx.x, step_rows, step_cols);
+}
+
+// The same chunks walked by a bounded, persistent grid (a few CTAs per SM): the kernel then occupies a fixed share of
+// every SM's thread slots and registers for its whole duration instead of queueing thousands of CTAs in front of every
+// kernel launched after it, so the read-streaming kernel of the predict side and the latency-bound kernels of other
+// batches in flight find room beside it.
+template <int VEC>
+__global__ void __launch_bounds__(kRowsThreads) encode_rows_persistent_kernel(const EncodeArgs p, unsigned step_rows, unsigned step_cols,
+                                                                             unsigned chunks_per_image, unsigned total_chunks) {
+  OdkTimeline tl_(ODK_TL_ROWS);
+  for (unsigned item = blockIdx.x; item < total_chunks; item += gridDim.x) {
+    const unsigned b = item / chunks_per_image;
+    encode_rows_chunk<VEC>(p, (int)b, item - b * chunks_per_image, step_rows, step_cols);
+  }
+}
+
 struct PatchArgs {
   AnchorView av;
   int batch, gmax;
@@ -116,12 +148,26 @@ struct PatchArgs {
   uint8_t* pb_valids;
 };
 
+// The y_true row of a positive: [w0, 1/G, 1, onehot(C), encode_locs] (od_pb.py:307-311); `row` is pre-zeroed.
+__device__ __forceinline__ void write_positive_row(float* row, const AnchorView& av, int pa, const float4 box, int cls, int G) {
+  const int C = av.num_classes;
+  const float4 ab = __ldg(av.locs + pa);
+  const double2 sz = av.sizes[pa];
+  row[0] = __fdiv_rn(1.0f, (float)max(1, G));  // pb_valids[pb_indices] = True (od_pb.py:361)
+  row[1] = __fdiv_rn(1.0f, (float)G);
+  row[2] = 1.0f;
+  row[3 + cls] = 1.0f;
+  row[3 + C + 0] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.x, ab.x), sz.x), 0.10);
+  row[3 + C + 1] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.y, ab.y), sz.y), 0.10);
+  row[3 + C + 2] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.z, ab.z), sz.x), 0.10);
+  row[3 + C + 3] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.w, ab.w), sz.y), 0.10);
+}
+
 // One CTA per image: the positives (od_pb.py:307-311), or an all-zero image when the assignment failed.
 __global__ void __launch_bounds__(128) encode_patch_kernel(const PatchArgs p) {
   OdkTimeline tl_(ODK_TL_PATCH);
   const int b = blockIdx.x;
-  const int C = p.av.num_classes;
-  const int W = 3 + C + 4;
+  const int W = 3 + p.av.num_classes + 4;
   float* y = p.y_true + (size_t)b * p.av.n * W;
   if (p.status[b] != ODK_IMG_OK) {
     for (int a = threadIdx.x; a < p.av.n; a += blockDim.x) {
@@ -131,24 +177,45 @@ __global__ void __launch_bounds__(128) encode_patch_kernel(const PatchArgs p) {
     return;
   }
   const int G = p.gt_count[b];
-  const float w0 = __fdiv_rn(1.0f, (float)max(1, G));
   for (int k = threadIdx.x; k < G; k += blockDim.x) {  // assignment slot k: anchor pa owns GT g
     const int pa = (int)p.pb_indices[(size_t)b * p.gmax + k];
     const int g = (int)p.gt_indices[(size_t)b * p.gmax + k];
-    const float4 box = p.gt_boxes[(size_t)b * p.gmax + g];
-    const int cls = p.gt_classes[(size_t)b * p.gmax + g];
-    const float4 ab = __ldg(p.av.locs + pa);
-    const double2 sz = p.av.sizes[pa];
-    float* row = y + (size_t)pa * W;
-    row[0] = w0;  // pb_valids[pb_indices] = True (od_pb.py:361)
-    row[1] = __fdiv_rn(1.0f, (float)G);
-    row[2] = 1.0f;
-    row[3 + cls] = 1.0f;
-    row[3 + C + 0] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.x, ab.x), sz.x), 0.10);
-    row[3 + C + 1] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.y, ab.y), sz.y), 0.10);
-    row[3 + C + 2] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.z, ab.z), sz.x), 0.10);
-    row[3 + C + 3] = (float)__ddiv_rn(__ddiv_rn((double)__fsub_rn(box.w, ab.w), sz.y), 0.10);
+    write_positive_row(y + (size_t)pa * W, p.av, pa, p.gt_boxes[(size_t)b * p.gmax + g], p.gt_classes[(size_t)b * p.gmax + g], G);
     if (p.pb_valids != nullptr) p.pb_valids[(size_t)b * p.av.n + pa] = 1;
+  }
+}
+
+struct CompactArgs {
+  PatchArgs q;               // y_true / pb_valids unused
+  const unsigned* ignore;    // [B, bitmap_words]
+  int bitmap_words;
+  float* pos_rows;           // [B, Gmax, W]
+  unsigned* valid_bits;      // [B, bitmap_words]: bit a = pb_valids[a]
+};
+
+// One CTA per image: the compact form of encode_truth's result.
+__global__ void __launch_bounds__(128) encode_compact_kernel(const CompactArgs c) {
+  const PatchArgs& p = c.q;
+  const int b = blockIdx.x;
+  const int W = 3 + p.av.num_classes + 4;
+  const int n = p.av.n;
+  float* rows = c.pos_rows + (size_t)b * p.gmax * W;
+  unsigned* vb = c.valid_bits + (size_t)b * c.bitmap_words;
+  const bool ok = p.status[b] == ODK_IMG_OK;
+  const int G = ok ? p.gt_count[b] : 0;
+  for (int i = threadIdx.x; i < p.gmax * W; i += blockDim.x) rows[i] = 0.0f;
+  const unsigned* ign = c.ignore + (size_t)b * c.bitmap_words;
+  for (int w = threadIdx.x; w < c.bitmap_words; w += blockDim.x) {
+    unsigned v = ok ? ~(__ldg(p.av.maskbits + w) & ign[w]) : 0u;  // od_pb.py:355-357
+    if (w == c.bitmap_words - 1 && (n & 31)) v &= (1u << (n & 31)) - 1u;
+    vb[w] = v;
+  }
+  __syncthreads();  // zeroed rows / plain bitmap words are in place before the positives touch them
+  for (int k = threadIdx.x; k < G; k += blockDim.x) {
+    const int pa = (int)p.pb_indices[(size_t)b * p.gmax + k];
+    const int g = (int)p.gt_indices[(size_t)b * p.gmax + k];
+    write_positive_row(rows + (size_t)k * W, p.av, pa, p.gt_boxes[(size_t)b * p.gmax + g], p.gt_classes[(size_t)b * p.gmax + g], G);
+    atomicOr(vb + (pa >> 5), 1u << (pa & 31));  // od_pb.py:361
   }
 }
 
@@ -180,6 +247,17 @@ int side_lane(SideLane** out) {
   return ODK_OK;
 }
 
+int rows_sm_count() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+  }
+  return sms;
+}
+
 int launch_rows(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
   const long long total = (long long)n * W;
   ODK_REQUIRE(total < 0x7fffffffLL, ODK_ERR_UNSUPPORTED, "assign_encode: image of %lld floats too large", total);
@@ -189,14 +267,35 @@ int launch_rows(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
   const long long per_cta = (long long)kRowsThreads * kRowsPerThread;
   const long long gx = (pieces + per_cta - 1) / per_cta;  // >= ceil(n / per_cta): the pb_valids loop is covered too
   const unsigned step = (unsigned)(kRowsThreads * v);     // floats between a thread's consecutive pieces
-  dim3 grid((unsigned)gx, (unsigned)e.batch);
+  // ODK_ROWS_PER_SM = k > 0: persistent grid of k CTAs per SM; 0: one CTA per chunk
+  static const int per_sm = getenv("ODK_ROWS_PER_SM") ? atoi(getenv("ODK_ROWS_PER_SM")) : ODK_ROWS_PER_SM_DEFAULT;
+  const long long chunks = gx * e.batch;
+  ODK_REQUIRE(chunks < 0x7fffffffLL, ODK_ERR_UNSUPPORTED, "assign_encode: %lld row chunks", chunks);
   {
     OdkProfileScope prof_("encode_rows_kernel", stream);
-    if (vec) encode_rows_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W);
-    else encode_rows_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W);
+    if (per_sm > 0 && chunks > (long long)rows_sm_count() * per_sm) {
+      const unsigned grid = (unsigned)(rows_sm_count() * per_sm);
+      if (vec) encode_rows_persistent_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W, (unsigned)gx, (unsigned)chunks);
+      else encode_rows_persistent_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W, (unsigned)gx, (unsigned)chunks);
+    } else {
+      dim3 grid((unsigned)gx, (unsigned)e.batch);
+      if (vec) encode_rows_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W);
+      else encode_rows_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W);
+    }
   }
   ODK_LAUNCH_CHECK("encode_rows_kernel");
   return ODK_OK;
+}
+
+void fill_patch(PatchArgs& q, const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes, const int32_t* gt_count,
+                int gmax, const int64_t* pb_indices, const int64_t* gt_indices, const int32_t* status, float* y_true, uint8_t* pb_valids) {
+  q.av = odk_view(a);
+  q.batch = batch; q.gmax = gmax;
+  q.gt_boxes = reinterpret_cast<const float4*>(gt_boxes);
+  q.gt_classes = gt_classes; q.gt_count = gt_count;
+  q.pb_indices = reinterpret_cast<const long long*>(pb_indices);
+  q.gt_indices = reinterpret_cast<const long long*>(gt_indices);
+  q.status = status; q.y_true = y_true; q.pb_valids = pb_valids;
 }
 
 }  // namespace
@@ -218,49 +317,63 @@ extern "C" int odk_assign_encode(const odk_anchors* a, int batch, const float* g
   SideLane same = {stream, lane->fork, lane->join, true};
   if (single_stream) lane = &same;
 
-  // caller's stream: ignore mask (scattered per GT) + ranked candidate lists
-  ODK_CUDA(cudaMemsetAsync(ignore, 0, sizeof(unsigned) * (size_t)batch * words, stream));
-  if (int rc = odk_launch_assign_candidates(a, batch, gt_boxes, gt_count, gmax, workspace, ignore, stream)) return rc;
-  // fork: the side stream streams out the rows (HBM-bound) ...
+  // fork at entry: the side stream builds the ignore mask (scattered per GT) and streams out the rows (HBM-bound) ...
   ODK_CUDA(cudaEventRecord(lane->fork, stream));
   ODK_CUDA(cudaStreamWaitEvent(lane->stream, lane->fork, 0));
-  {
+  int rc_side = odk_launch_assign_ignore(a, batch, gt_boxes, gt_count, gmax, ignore, lane->stream);
+  if (!rc_side) {
     EncodeArgs e;
     e.av = odk_view(a);
     e.batch = batch; e.gmax = gmax;
     e.gt_count = gt_count; e.ignore = ignore; e.bitmap_words = words;
     e.y_true = y_true; e.pb_valids = pb_valids;
-    const int W = 3 + a->num_classes + 4;
-    const int rc = launch_rows(e, a->n, W, lane->stream);
-    ODK_CUDA(cudaEventRecord(lane->join, lane->stream));
-    if (rc) {
-      cudaStreamWaitEvent(stream, lane->join, 0);  // never leave the side stream un-joined (stream capture)
-      return rc;
-    }
+    rc_side = launch_rows(e, a->n, 3 + a->num_classes + 4, lane->stream);
   }
-  // ... while the caller's stream walks the GTs (latency-bound, one CTA per image)
-  {
-    const int rc = odk_launch_assign_greedy(a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, workspace, stream);
-    if (rc) {
-      cudaStreamWaitEvent(stream, lane->join, 0);
-      return rc;
-    }
-  }
-  // join, then the positives
+  ODK_CUDA(cudaEventRecord(lane->join, lane->stream));
+  // ... while the caller's stream ranks the in-cell anchors of every GT and walks the GTs (latency-bound, one CTA per image)
+  int rc_main = rc_side;
+  if (!rc_main) rc_main = odk_launch_assign_rank(a, batch, gt_boxes, gt_count, gmax, workspace, stream);
+  if (!rc_main) rc_main = odk_launch_assign_greedy(a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, workspace, stream);
+  // join (never leave the side stream un-joined: stream capture), then the positives
   ODK_CUDA(cudaStreamWaitEvent(stream, lane->join, 0));
+  if (rc_main) return rc_main;
   PatchArgs q;
-  q.av = odk_view(a);
-  q.batch = batch; q.gmax = gmax;
-  q.gt_boxes = reinterpret_cast<const float4*>(gt_boxes);
-  q.gt_classes = gt_classes; q.gt_count = gt_count;
-  q.pb_indices = reinterpret_cast<const long long*>(pb_indices);
-  q.gt_indices = reinterpret_cast<const long long*>(gt_indices);
-  q.status = status; q.y_true = y_true; q.pb_valids = pb_valids;
+  fill_patch(q, a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, y_true, pb_valids);
   {
     OdkProfileScope prof_("encode_patch_kernel", stream);
     odk_launch_high(encode_patch_kernel, dim3(batch), dim3(128), 0, stream, q);
   }
   ODK_LAUNCH_CHECK("encode_patch_kernel");
+  return ODK_OK;
+}
+
+extern "C" int odk_assign_encode_compact(const odk_anchors* a, int batch, const float* gt_boxes, const int32_t* gt_classes,
+                                         const int32_t* gt_count, int gmax, float* pos_rows, uint32_t* valid_bits, int64_t* pb_indices,
+                                         int64_t* gt_indices, int32_t* status, void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = odk_assign_check(a, batch, gt_boxes, gt_count, gmax, pb_indices, gt_indices, status)) return rc;
+  if (int rc = odk_assign_workspace_check(a, batch, gmax, workspace, workspace_bytes)) return rc;
+  ODK_REQUIRE(gt_classes && pos_rows && valid_bits, ODK_ERR_INVALID_ARGUMENT, "assign_encode_compact: null pointer");
+  const int words = (a->n + 31) / 32;
+  unsigned* ignore = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + odk_assign_lists_bytes(batch, gmax));
+  SideLane* lane = nullptr;
+  if (int rc = side_lane(&lane)) return rc;
+  ODK_CUDA(cudaEventRecord(lane->fork, stream));
+  ODK_CUDA(cudaStreamWaitEvent(lane->stream, lane->fork, 0));
+  int rc = odk_launch_assign_ignore(a, batch, gt_boxes, gt_count, gmax, ignore, lane->stream);
+  ODK_CUDA(cudaEventRecord(lane->join, lane->stream));
+  if (!rc) rc = odk_launch_assign_rank(a, batch, gt_boxes, gt_count, gmax, workspace, stream);
+  if (!rc) rc = odk_launch_assign_greedy(a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, workspace, stream);
+  ODK_CUDA(cudaStreamWaitEvent(stream, lane->join, 0));
+  if (rc) return rc;
+  CompactArgs c;
+  fill_patch(c.q, a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, nullptr, nullptr);
+  c.ignore = ignore; c.bitmap_words = words; c.pos_rows = pos_rows; c.valid_bits = valid_bits;
+  {
+    OdkProfileScope prof_("encode_compact_kernel", stream);
+    odk_launch_high(encode_compact_kernel, dim3(batch), dim3(128), 0, stream, c);
+  }
+  ODK_LAUNCH_CHECK("encode_compact_kernel");
   return ODK_OK;
 }
 

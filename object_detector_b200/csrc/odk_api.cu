@@ -21,6 +21,7 @@ int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, 
                             int32_t* classes, float* confs, float* boxes, bool dense, float conf_thr,
                             unsigned long long* cand_keys, int* piece_count, cudaStream_t stream);
 int odk_launch_decode_locs(const odk_anchors* a, long long rows, const float* pred, float* out, cudaStream_t stream);
+int odk_piece_size(int num_classes);
 int odk_launch_decode_locs_f64(const odk_anchors* a, long long rows, const double* pred, double* out, cudaStream_t stream);
 int odk_launch_channel_reduce(long long rows, int c, const float* x, long long* arg, float* mx, cudaStream_t stream);
 
@@ -153,13 +154,42 @@ extern "C" int odk_anchors_create(odk_anchors** out, int n, int num_classes, int
   uint32_t* bits = static_cast<uint32_t*>(calloc(words, sizeof(uint32_t)));
   if (bits == nullptr) { free(scale); free(a); return odk_set_error(ODK_ERR_CUDA, "anchors_create: out of host memory"); }
   for (int i = 0; i < n; ++i) if (pb_mask[i]) bits[i >> 5] |= 1u << (i & 31);
-  const size_t sz[6] = {16 * (size_t)n, 16 * (size_t)n, 16 * (size_t)n, 8 * (size_t)n, (size_t)n, 4 * words};
-  const void* src[6] = {pb_locs, pb_grid, pb_sizes, scale, pb_mask, bits};
-  size_t off[6], total_bytes = 0;
-  for (int i = 0; i < 6; ++i) { off[i] = total_bytes; total_bytes = odk_align_up(total_bytes + sz[i], 256); }
+  // Valid-anchor spans per score/emit tile: anchors with pb_mask = 0 can never become candidates (conf = x * 0,
+  // od_net.py:183-184), so the fused predict path fetches only the runs of valid rows of a tile.  Runs separated by at
+  // most two masked rows are merged (a separate bulk copy costs more than the five sectors it saves); a tile keeps at
+  // most ODK_MAX_SPANS runs (the narrowest gaps are merged first).
+  a->span_tile = odk_piece_size(num_classes);
+  const int n_tiles = (n + a->span_tile - 1) / a->span_tile;
+  std::vector<uint32_t> spans((size_t)n_tiles * ODK_MAX_SPANS, 0u);
+  a->span_rows = 0; a->span_count = 0;
+  for (int t = 0; t < n_tiles; ++t) {
+    const int a0 = t * a->span_tile, rows = (n - a0 < a->span_tile) ? n - a0 : a->span_tile;
+    std::vector<std::pair<int, int>> run;  // [first, end)
+    for (int i = 0; i < rows; ++i) {
+      if (!pb_mask[a0 + i]) continue;
+      if (!run.empty() && i - run.back().second <= 2) run.back().second = i + 1;
+      else run.push_back({i, i + 1});
+    }
+    while ((int)run.size() > ODK_MAX_SPANS) {
+      size_t best = 0;
+      for (size_t k = 1; k + 1 < run.size(); ++k)
+        if (run[k + 1].first - run[k].second < run[best + 1].first - run[best].second) best = k;
+      run[best].second = run[best + 1].second;
+      run.erase(run.begin() + best + 1);
+    }
+    for (size_t k = 0; k < run.size(); ++k) {
+      spans[(size_t)t * ODK_MAX_SPANS + k] = ((uint32_t)run[k].first << 16) | (uint32_t)(run[k].second - run[k].first);
+      a->span_rows += run[k].second - run[k].first;
+    }
+    a->span_count += (int)run.size();
+  }
+  const size_t sz[7] = {16 * (size_t)n, 16 * (size_t)n, 16 * (size_t)n, 8 * (size_t)n, (size_t)n, 4 * words, 4 * spans.size()};
+  const void* src[7] = {pb_locs, pb_grid, pb_sizes, scale, pb_mask, bits, spans.data()};
+  size_t off[7], total_bytes = 0;
+  for (int i = 0; i < 7; ++i) { off[i] = total_bytes; total_bytes = odk_align_up(total_bytes + sz[i], 256); }
   int rc = ODK_OK;
   if (cudaMalloc(&a->d_slab, total_bytes) != cudaSuccess) rc = odk_set_error(ODK_ERR_CUDA, "anchors_create: cudaMalloc of %zu bytes failed", total_bytes);
-  for (int i = 0; i < 6 && !rc; ++i)
+  for (int i = 0; i < 7 && !rc; ++i)
     if (cudaMemcpy(static_cast<char*>(a->d_slab) + off[i], src[i], sz[i], cudaMemcpyHostToDevice) != cudaSuccess)
       rc = odk_set_error(ODK_ERR_CUDA, "anchors_create: upload of table %d failed", i);
   if (!rc) {
@@ -170,6 +200,7 @@ extern "C" int odk_anchors_create(odk_anchors** out, int n, int num_classes, int
     a->d_scale = reinterpret_cast<float2*>(base + off[3]);
     a->d_mask = reinterpret_cast<uint8_t*>(base + off[4]);
     a->d_maskbits = reinterpret_cast<uint32_t*>(base + off[5]);
+    a->d_spans = reinterpret_cast<uint32_t*>(base + off[6]);
   }
   free(bits);
   free(scale);
@@ -179,6 +210,11 @@ extern "C" int odk_anchors_create(odk_anchors** out, int n, int num_classes, int
 }
 
 extern "C" int odk_anchors_count(const odk_anchors* a) { return a ? a->n : 0; }
+extern "C" int odk_anchors_span_stats(const odk_anchors* a, int32_t* out4) {
+  ODK_REQUIRE(a && out4, ODK_ERR_INVALID_ARGUMENT, "anchors_span_stats: null pointer");
+  out4[0] = a->span_tile; out4[1] = a->span_count; out4[2] = a->span_rows; out4[3] = a->n_valid;
+  return ODK_OK;
+}
 extern "C" int odk_anchors_num_classes(const odk_anchors* a) { return a ? a->num_classes : 0; }
 
 extern "C" int odk_decode_locs(const odk_anchors* a, int64_t rows, const float* pred, float* out, void* stream) {

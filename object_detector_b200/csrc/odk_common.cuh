@@ -15,6 +15,7 @@
 #define ODK_IDX_BITS 20                 // anchor index field of the sort keys (N < 2^20)
 #define ODK_IDX_MASK ((1u << ODK_IDX_BITS) - 1u)
 #define ODK_MAX_CLASSES 4096            // class field of the sort keys (12 bits)
+#define ODK_MAX_SPANS 8                 // valid-anchor runs per tile in the span table (shorter gaps are merged)
 
 struct odk_anchors {
   int n, num_classes, n_maps, n_patterns, n_valid, device;
@@ -26,6 +27,10 @@ struct odk_anchors {
   float2* d_scale;   // float32(0.10 * pb_sizes)
   uint8_t* d_mask;   // pb_mask
   uint32_t* d_maskbits;  // pb_mask packed, bit (a & 31) of word a >> 5
+  uint32_t* d_spans;     // [ceil(n / span_tile)][ODK_MAX_SPANS]: (first row << 16 | rows) of the runs of valid anchors in a tile
+  int span_tile;         // tile height the span table was built for (= odk_piece_size(num_classes))
+  int span_rows;         // anchors covered by all spans (statistics)
+  int span_count;        // spans in the table (statistics)
   void* d_slab;          // the one allocation holding all of the above
 };
 
@@ -40,6 +45,8 @@ struct AnchorView {
   const float2* scale;
   const uint8_t* mask;
   const uint32_t* maskbits;
+  const uint32_t* spans;
+  int span_tile;
 };
 
 inline AnchorView odk_view(const odk_anchors* a) {
@@ -49,6 +56,7 @@ inline AnchorView odk_view(const odk_anchors* a) {
   for (int i = 0; i < ODK_MAX_MAPS; ++i) v.map_size[i] = a->map_size[i];
   for (int i = 0; i <= ODK_MAX_MAPS; ++i) v.map_off[i] = a->map_off[i];
   v.locs = a->d_locs; v.grid = a->d_grid; v.sizes = a->d_sizes; v.scale = a->d_scale; v.mask = a->d_mask; v.maskbits = a->d_maskbits;
+  v.spans = a->d_spans; v.span_tile = a->span_tile;
   return v;
 }
 
@@ -220,7 +228,8 @@ struct OdkTimeline {
     if (threadIdx.x == 0 && odk_tl_buf != nullptr) atomicMax(odk_tl_buf + 2 * id_ + 1, now());
   }
 };
-enum { ODK_TL_CANDIDATES = 0, ODK_TL_GREEDY = 1, ODK_TL_ROWS = 2, ODK_TL_PATCH = 3, ODK_TL_EMIT = 4, ODK_TL_NMS = 5 };
+enum { ODK_TL_CANDIDATES = 0, ODK_TL_GREEDY = 1, ODK_TL_ROWS = 2, ODK_TL_PATCH = 3, ODK_TL_EMIT = 4, ODK_TL_NMS = 5, ODK_TL_IGNORE = 6,
+       ODK_TL_SLOTS = 7 };
 
 // ---- warp helpers ------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned odk_lane() { return threadIdx.x & 31u; }

@@ -1,8 +1,9 @@
 """Multi-GPU plumbing for the evaluation path: images are sharded contiguously over the
 ranks (one process per GPU), every rank runs decode+NMS on its shard straight into its slice of one
-(R*per_rank, top_k, 6) buffer, a single in-place ``all_gather_into_tensor`` (NCCL over NVLink) completes
-the buffer on every rank, and AP is computed from it.  Padding slabs are all-zero with class -1 so they
-can never count as detections.  The reference has no eval-time collective (rank-0 only,
+(R*per_rank, top_k, 6) buffer, a single IN-PLACE ``all_gather_into_tensor`` (NCCL over NVLink: the send
+buffer of rank r is ``recv + r*per`` of the same allocation, which is NCCL's in-place all-gather)
+completes the buffer on every rank, and AP is computed from it.  Padding slabs are all-zero with class -1
+so they can never count as detections.  The reference has no eval-time collective (rank-0 only,
 pytoolkit/od_voc.py:35-39); assign/encode/decode/NMS need none.
 """
 import torch
@@ -30,11 +31,22 @@ def local_slab(buf: torch.Tensor, rank: int, world: int):
 
 
 def all_gather_detections(buf: torch.Tensor, rank: int, world: int, group=None):
-    """In-place all-gather: rank r contributes buf[r*per:(r+1)*per]; afterwards buf is identical on all ranks."""
+    """In-place all-gather: rank r contributes buf[r*per:(r+1)*per] — the slab its NMS kernel wrote, no staging
+    copy; afterwards buf is identical on all ranks."""
     if world == 1:
         return buf
-    dist.all_gather_into_tensor(buf, local_slab(buf, rank, world).clone(), group=group)
+    dist.all_gather_into_tensor(buf, local_slab(buf, rank, world), group=group)
     return buf
+
+
+def decode_nms_shard(pb, objs, clfs, locs, out, batch=256, top_k=200, **kw):
+    """decode + per-class NMS of this rank's resident head outputs (n_local, N, ...) in batches of ``batch`` images,
+    written straight into ``out`` (n_local, top_k, 6) — normally a prefix of ``local_slab(buf, rank, world)``."""
+    n_local = objs.shape[0]
+    for s in range(0, n_local, batch):
+        e = min(n_local, s + batch)
+        pb.decode_nms(objs[s:e], clfs[s:e], locs[s:e], top_k=top_k, out=out[s:e], **kw)
+    return out
 
 
 def sharded_decode_nms_eval(pb, head_fn, y_true, num_classes, rank, world, batch=64, top_k=200, conf_threshold=0.01, group=None):
@@ -54,7 +66,7 @@ def sharded_decode_nms_eval(pb, head_fn, y_true, num_classes, rank, world, batch
     all_gather_detections(buf, rank, world, group)
     # slabs are rank-major with `per` slots each: image i lives at slot (i // per) * per + i % per == i
     gt = voc.pack_ground_truth(y_true, dev)
-    ap, ap07 = (t.cpu().numpy() for t in voc.evaluate_detections(buf[:n].contiguous(), gt, num_classes, conf_threshold))
+    ap, ap07 = (t.cpu().numpy() for t in voc.evaluate_detections(buf[:n], gt, num_classes, conf_threshold))
     with np.errstate(invalid='ignore'):
         import warnings
         with warnings.catch_warnings():

@@ -218,6 +218,41 @@ class PriorBoxes:
             res['pb_valids'] = valids.view(torch.bool)
         return res
 
+    def encode_truth_compact(self, gt_boxes, gt_classes, gt_count, out=None):
+        """``encode_truth_batch`` with the compact result of ``odk_assign_encode_compact`` (no host sync): dict of CUDA
+        tensors ``pos_rows`` (B,Gmax,3+C+4) f32, ``valid_bits`` (B,ceil(N/32)) i32 (bit a of word a>>5 = pb_valids[a]),
+        ``pb_indices`` / ``gt_indices`` (B,Gmax) i64, ``status`` (B,) i32 — ~10 KB per image instead of the 1.8 MB dense
+        tensor.  ``expand_truth`` turns the host copies of these into the dense array.  ``out``: a dict of preallocated
+        tensors with those keys (fixed addresses for CUDA-graph capture)."""
+        dev = _dev.device(gt_boxes.device if isinstance(gt_boxes, torch.Tensor) and gt_boxes.is_cuda else None)
+        boxes = _dev.to_device(gt_boxes, torch.float32, dev)
+        classes = _dev.to_device(gt_classes, torch.int32, dev)
+        count = _dev.to_device(gt_count, torch.int32, dev)
+        b, gmax = boxes.shape[0], boxes.shape[1]
+        assert boxes.shape == (b, gmax, 4) and classes.shape == (b, gmax) and count.shape == (b,)
+        n, w = len(self.pb_locs), 3 + self.num_classes + 4
+        res = out if out is not None else {
+            'pos_rows': torch.empty((b, gmax, w), dtype=torch.float32, device=dev),
+            'valid_bits': torch.empty((b, (n + 31) // 32), dtype=torch.int32, device=dev),
+            'pb_indices': torch.empty((b, gmax), dtype=torch.int64, device=dev),
+            'gt_indices': torch.empty((b, gmax), dtype=torch.int64, device=dev),
+            'status': torch.empty((b,), dtype=torch.int32, device=dev)}
+        assert res['pos_rows'].shape == (b, gmax, w) and res['valid_bits'].shape == (b, (n + 31) // 32)
+        ws_bytes = _lib.load().odk_assign_workspace_bytes(self._handle(dev), b, gmax)
+        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _lib.call('odk_assign_encode_compact', self._handle(dev), b, boxes.data_ptr(), classes.data_ptr(), count.data_ptr(), gmax,
+                      res['pos_rows'].data_ptr(), res['valid_bits'].data_ptr(), res['pb_indices'].data_ptr(),
+                      res['gt_indices'].data_ptr(), res['status'].data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
+        return res
+
+    def span_stats(self, dev=None):
+        """{tile, spans, rows_covered, valid} of the valid-anchor span table the fused predict path fetches through."""
+        dev = _dev.device(dev)
+        out = (ctypes.c_int32 * 4)()
+        _lib.call('odk_anchors_span_stats', self._handle(dev), ctypes.cast(out, ctypes.c_void_p))
+        return {'tile': int(out[0]), 'spans': int(out[1]), 'rows_covered': int(out[2]), 'valid': int(out[3]), 'anchors': len(self.pb_locs)}
+
     # ---- loss side (od_pb.py:365-431) --------------------------------------------------------------------
     LOSS_COLUMNS = ('loss', 'loss_obj', 'loss_clf', 'loss_loc', 'rec_bg', 'rec_obj', 'acc_clf', 'n_positive')
 
@@ -433,6 +468,25 @@ class PriorBoxes:
                       clfs.data_ptr(), locs.data_ptr(), float(conf_threshold), *thr, int(top_k), 1 if iou_ge else 0,
                       out.data_ptr(), kept.data_ptr(), ws.data_ptr(), ws_bytes, _dev.stream_ptr(dev))
         return (out, kept) if return_index else out
+
+
+def expand_truth(pos_rows, valid_bits, pb_indices, gt_count, n_anchors, out=None):
+    """Host-side expansion of ``encode_truth_compact``'s result (NumPy arrays) into the dense ``encode_truth`` array
+    (B, N, 3+C+4) float32 of od_pb.py:299-313: zeros, column 0 = float32(1/max(1,G)) where ``valid_bits`` is set, and the
+    G positive rows at ``pb_indices``.  A memset and two scatters — no arithmetic beyond the reference's own 1/G."""
+    pos_rows, valid_bits = np.asarray(pos_rows), np.asarray(valid_bits)
+    pb_indices, gt_count = np.asarray(pb_indices), np.asarray(gt_count)
+    b, gmax, w = pos_rows.shape
+    y = np.zeros((b, n_anchors, w), dtype=np.float32) if out is None else out
+    if out is not None:
+        y[...] = 0
+    bits = np.unpackbits(valid_bits.view(np.uint8).reshape(b, -1), axis=1, bitorder='little')[:, :n_anchors].astype(bool)
+    for i in range(b):
+        g = int(gt_count[i])
+        y[i, bits[i], 0] = np.float32(1 / max(1, g))  # od_pb.py:306
+        if bits[i].any() and g:
+            y[i, pb_indices[i, :g]] = pos_rows[i, :g]
+    return y
 
 
 def _centres(bboxes):

@@ -28,12 +28,14 @@ def _enqueue_step(pb, gt, head, y_true, dets, side, kw):
         pb.decode_nms(*head, out=dets, **kw)
 
 
-def capture_steps(pb, slots, top_k=200, conf_threshold=0.01, nms_threshold=0.45, two_streams=True):
+def capture_steps(pb, slots, top_k=200, conf_threshold=0.01, nms_threshold=0.45, two_streams=True, nms_all_threshold=None):
     """Captures the steps of all ``slots`` = [(gt, head, y_true, dets)] into ONE CUDA graph, every slot on its own
     branch (and within a slot the train and the predict side on parallel branches when ``two_streams``): one host
     launch per ``len(slots)`` batches.  All tensors must be CUDA tensors that stay alive and keep their addresses."""
     dev = slots[0][2].device
     kw = dict(top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold)
+    if nms_all_threshold:
+        kw['nms_all_threshold'] = nms_all_threshold  # strict_nms (od_net.py:175)
     with torch.cuda.device(dev):
         pb._handle(dev)  # the anchor tables are uploaded (cudaMalloc) on first use: not allowed while capturing
         branch = [torch.cuda.Stream(device=dev) for _ in slots[1:]]
@@ -53,11 +55,12 @@ def capture_steps(pb, slots, top_k=200, conf_threshold=0.01, nms_threshold=0.45,
     return graph
 
 
-def capture_step(pb, gt, head, y_true, dets, top_k=200, conf_threshold=0.01, nms_threshold=0.45, two_streams=True):
+def capture_step(pb, gt, head, y_true, dets, top_k=200, conf_threshold=0.01, nms_threshold=0.45, two_streams=True,
+                 nms_all_threshold=None):
     """Captures ``encode_truth_batch(*gt, y_true=y_true)`` and ``decode_nms(*head, out=dets)`` into one CUDA
     graph (parallel branches when ``two_streams``).  All tensors must be CUDA tensors that stay alive and
     keep their addresses; replay with ``graph.replay()`` on any stream."""
-    return capture_steps(pb, [(gt, head, y_true, dets)], top_k, conf_threshold, nms_threshold, two_streams)
+    return capture_steps(pb, [(gt, head, y_true, dets)], top_k, conf_threshold, nms_threshold, two_streams, nms_all_threshold)
 
 
 class StepRing:
@@ -76,12 +79,13 @@ class StepRing:
     CUDA tensors that keep their addresses; ``len(slots)`` must be a multiple of ``lanes * group``.
     """
 
-    def __init__(self, pb, slots, lanes=2, group=4, top_k=200, conf_threshold=0.01, nms_threshold=0.45, use_graph=True):
+    def __init__(self, pb, slots, lanes=2, group=4, top_k=200, conf_threshold=0.01, nms_threshold=0.45, use_graph=True,
+                 nms_all_threshold=None):
         assert len(slots) >= 1 and lanes >= 1 and group >= 1 and len(slots) % (lanes * group) == 0, \
             'len(slots) must be a multiple of lanes * group'
         self.pb, self.slots, self.lanes, self.group = pb, slots, lanes, group
         self.dev = slots[0][2].device
-        self._kw = dict(top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold)
+        self._kw = dict(top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold, nms_all_threshold=nms_all_threshold)
         self.n_groups = len(slots) // group
         with torch.cuda.device(self.dev):
             self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(lanes)]
@@ -138,53 +142,111 @@ class StepRing:
 class HostPipeline:
     """Host-buffer front end for fixed batch shapes.
 
-    ``submit(gt_boxes, gt_classes, gt_count, objs, clfs, locs)`` takes pinned host tensors (or NumPy
-    arrays, which are staged through an internal pinned buffer), returns a slot id immediately;
-    ``result(slot)`` waits for that batch only and returns pinned host views ``(y_true, dets)`` that stay
-    valid until the slot is submitted again (``depth`` batches later).
+    ``submit(*host_inputs)`` takes pinned host tensors (or NumPy arrays, which are staged through an internal pinned
+    buffer), returns a slot id immediately; ``result(slot)`` waits for that batch only and returns pinned host views
+    that stay valid until the slot is submitted again (``depth`` batches later).  Three result contracts:
+
+    ``mode='dense'``    inputs (gt_boxes, gt_classes, gt_count, objs, clfs, locs); result ``(y_true, dets)`` — the
+                        reference's own contract: the dense (B,N,3+C+4) array of ``encode_truth`` (od_pb.py:299-313)
+                        and the (B,top_k,6) array of the NMS layer.  1.8 MB per image cross PCIe in each direction.
+    ``mode='compact'``  same inputs; result ``(compact, dets)`` with ``compact`` = dict of ``pos_rows``, ``valid_bits``,
+                        ``pb_indices``, ``gt_indices``, ``status`` (``odk_assign_encode_compact``, ~10 KB per image);
+                        ``od_pb.expand_truth`` rebuilds the dense array on the host for callers that need it.
+    ``mode='fused'``    the network lives on the same GPU (``resident`` = dict with its outputs ``y_pred`` (B,N,3+C+4)
+                        and ``head`` = (objs, clfs, locs)): inputs are only the ground truth; the consumer of the
+                        assignment is the loss + gradient (``odk_assign_loss_grad``, y_true never exists) and only
+                        ``(terms (B,8) float64, dets)`` leave the device (generator.py:227-240 is where the
+                        reference hands y_true to the loss).
+    ``kernels=False`` queues the same copies on the same streams with no kernels in between: the copy-only ceiling
+    of the chosen contract on this host.
     """
 
     def __init__(self, pb, batch, gmax, top_k=200, conf_threshold=0.01, nms_threshold=0.45, depth=2, device=None,
-                 use_graph=True):
-        self.pb, self.batch, self.gmax, self.top_k, self.depth = pb, batch, gmax, top_k, depth
+                 use_graph=True, mode='dense', resident=None, kernels=True, nms_all_threshold=None):
+        assert mode in ('dense', 'compact', 'fused')
+        self.pb, self.batch, self.gmax, self.top_k, self.depth, self.mode = pb, batch, gmax, top_k, depth, mode
         self.dev = _dev.device(device)
+        self.resident = resident
         n, c = len(pb.pb_locs), pb.num_classes
-        f32, i32 = torch.float32, torch.int32
-        shapes = [((batch, gmax, 4), f32), ((batch, gmax), i32), ((batch,), i32),
-                  ((batch, n, 1), f32), ((batch, n, c), f32), ((batch, n, 4), f32)]
+        w = 3 + c + 4
+        f32, i32, i64, f64 = torch.float32, torch.int32, torch.int64, torch.float64
+        shapes = [((batch, gmax, 4), f32), ((batch, gmax), i32), ((batch,), i32)]
+        if mode != 'fused':
+            shapes += [((batch, n, 1), f32), ((batch, n, c), f32), ((batch, n, 4), f32)]
+        else:
+            assert resident is not None and 'y_pred' in resident and 'head' in resident
+        out_shapes = {'dets': ((batch, top_k, 6), f32)}
+        if mode == 'dense':
+            out_shapes['y_true'] = ((batch, n, w), f32)
+        elif mode == 'compact':
+            out_shapes.update({'pos_rows': ((batch, gmax, w), f32), 'valid_bits': ((batch, (n + 31) // 32), i32),
+                               'pb_indices': ((batch, gmax), i64), 'gt_indices': ((batch, gmax), i64), 'status': ((batch,), i32)})
+        else:
+            out_shapes['terms'] = ((batch, 8), f64)
         with torch.cuda.device(self.dev):
             self.s_in, self.s_run, self.s_out = (torch.cuda.Stream(device=self.dev) for _ in range(3))
+            self._sides = [torch.cuda.Stream(device=self.dev) for _ in range(depth)]  # predict-side branch of each slot
             self.d_in = [[torch.empty(s, dtype=t, device=self.dev) for s, t in shapes] for _ in range(depth)]
             self.h_in = [[torch.empty(s, dtype=t).pin_memory() for s, t in shapes] for _ in range(depth)]
-            self.d_y = [torch.empty((batch, n, 3 + c + 4), dtype=f32, device=self.dev) for _ in range(depth)]
-            self.d_det = [torch.empty((batch, top_k, 6), dtype=f32, device=self.dev) for _ in range(depth)]
-            self.h_y = [torch.empty((batch, n, 3 + c + 4), dtype=f32).pin_memory() for _ in range(depth)]
-            self.h_det = [torch.empty((batch, top_k, 6), dtype=f32).pin_memory() for _ in range(depth)]
+            self.d_out = [{k: torch.zeros(s, dtype=t, device=self.dev) for k, (s, t) in out_shapes.items()} for _ in range(depth)]
+            self.h_out = [{k: torch.empty(s, dtype=t).pin_memory() for k, (s, t) in out_shapes.items()} for _ in range(depth)]
             self.ev_in = [torch.cuda.Event() for _ in range(depth)]
             self.ev_run = [torch.cuda.Event() for _ in range(depth)]
             self.ev_out = [torch.cuda.Event() for _ in range(depth)]
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.d_in[0])
-        self.d2h_bytes = self.h_y[0].numel() * 4 + self.h_det[0].numel() * 4
+        self.d2h_bytes = sum(t.numel() * t.element_size() for t in self.h_out[0].values())
         self._kw = dict(top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold)
+        if nms_all_threshold:
+            self._kw['nms_all_threshold'] = nms_all_threshold
         self._count = 0
+        self.kernels = kernels
         self.graphs = None
-        if use_graph:
+        self._keep = []  # tensors allocated while capturing (the fused entry's gradient / index outputs)
+        if use_graph and kernels:
             with torch.cuda.device(self.dev):
                 for t in self.d_in[0]:
                     t.zero_()
-                self.d_in[0][2].fill_(0)  # gt_count = 0: a valid empty batch for the eager warm-up call
-                self._eager(0)            # uploads the anchor tables, sets kernel attributes
+                self._compute(0)            # eager warm-up on a valid empty batch (gt_count = 0): uploads the anchor tables
                 torch.cuda.synchronize(self.dev)
-                self.graphs = [capture_step(pb, self.d_in[k][:3], self.d_in[k][3:], self.d_y[k], self.d_det[k], **self._kw)
-                               for k in range(depth)]
+                self.graphs = []
+                for k in range(depth):
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g):
+                        self._compute(k)
+                    self.graphs.append(g)
 
-    def _eager(self, k):
-        self.pb.encode_truth_batch(*self.d_in[k][:3], y_true=self.d_y[k])
-        self.pb.decode_nms(*self.d_in[k][3:], out=self.d_det[k], **self._kw)
+    # compatibility with the dense-only interface of earlier rounds
+    @property
+    def d_y(self):
+        return [o['y_true'] for o in self.d_out]
+
+    @property
+    def d_det(self):
+        return [o['dets'] for o in self.d_out]
+
+    def _compute(self, k):
+        """Both sides of slot ``k`` on the current stream, the predict side forked onto a parallel branch."""
+        main = torch.cuda.current_stream(self.dev)
+        side = self._sides[k]
+        gt = self.d_in[k][:3]
+        head = self.d_in[k][3:] if self.mode != 'fused' else self.resident['head']
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            self.pb.decode_nms(*head, out=self.d_out[k]['dets'], **self._kw)
+        if self.mode == 'dense':
+            self.pb.encode_truth_batch(*gt, y_true=self.d_out[k]['y_true'])
+        elif self.mode == 'compact':
+            self.pb.encode_truth_compact(*gt, out=self.d_out[k])
+        else:
+            res = self.pb.assign_loss_batch(*gt, self.resident['y_pred'], with_grad=True)
+            self.d_out[k]['terms'].copy_(res['terms'])  # 4 KB, device to device, into the slot's fixed result buffer
+            self._keep.append(res)
+        main.wait_stream(side)
 
     def submit(self, *host_inputs):
         k = self._count % self.depth
         self._count += 1
+        assert len(host_inputs) == len(self.d_in[k]), f'mode {self.mode!r} takes {len(self.d_in[k])} host inputs'
         src = []
         for i, x in enumerate(host_inputs):
             if isinstance(x, torch.Tensor) and x.is_pinned():
@@ -202,21 +264,27 @@ class HostPipeline:
             self.s_run.wait_event(self.ev_in[k])
             self.s_run.wait_event(self.ev_out[k])  # the slot's previous outputs have left the device
             with torch.cuda.stream(self.s_run):
-                if self.graphs is not None:
-                    self.graphs[k].replay()
-                else:
-                    self._eager(k)
+                if self.kernels:
+                    if self.graphs is not None:
+                        self.graphs[k].replay()
+                    else:
+                        self._compute(k)
                 self.ev_run[k].record(self.s_run)
             self.s_out.wait_event(self.ev_run[k])
             with torch.cuda.stream(self.s_out):
-                self.h_y[k].copy_(self.d_y[k], non_blocking=True)
-                self.h_det[k].copy_(self.d_det[k], non_blocking=True)
+                for key, h in self.h_out[k].items():
+                    h.copy_(self.d_out[k][key], non_blocking=True)
                 self.ev_out[k].record(self.s_out)
         return k
 
     def result(self, slot):
         self.ev_out[slot].synchronize()
-        return self.h_y[slot], self.h_det[slot]
+        h = self.h_out[slot]
+        if self.mode == 'dense':
+            return h['y_true'], h['dets']
+        if self.mode == 'compact':
+            return {k: v for k, v in h.items() if k != 'dets'}, h['dets']
+        return h['terms'], h['dets']
 
     def synchronize(self):
         for s in (self.s_in, self.s_run, self.s_out):

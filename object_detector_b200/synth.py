@@ -1,6 +1,7 @@
 """Seeded synthetic workloads for the tests and ``bench.py``.
 
-NumPy only; produces HOST arrays.  Not part of the compute path.
+NumPy only and HOST arrays, except ``eval_head_outputs`` (config 4), which fills device tensors with torch's
+generator because 4 952 images of head outputs are 8 GB.  Not part of the compute path.
 """
 import numpy as np
 
@@ -90,6 +91,73 @@ def eval_set(seed, n_img, num_classes, max_gt=6, difficult_frac=0.1, n_fp=20):
                       np.concatenate([ps, fs])[ok].astype(np.float32), boxes[ok]))
         gts.append((w, h, gc, gb, gd))
     return gts, preds
+
+
+def plan_eval_head(pb, preds):
+    """Config 4: for every planned detection of ``eval_set`` (class, conf, box) the anchor that will carry it and the
+    ``locs`` head value that decodes to its box (od_pb.py:216-222 inverted in fp32).  Anchors are taken from the cell
+    that holds the box centre, finest map first, distinct within an image, ``pb_mask`` = 1 only.
+    Returns per-image tuples (anchor i64 (D,), class i32 (D,), conf f32 (D,), locs f32 (D,4))."""
+    maps = [int(m) for m in pb.map_sizes]
+    n_pat = len(pb.pb_size_patterns)
+    off = np.concatenate([[0], np.cumsum([m * m * n_pat for m in maps])])
+    mask = np.asarray(pb.pb_mask, dtype=bool)
+    locs_tab = np.asarray(pb.pb_locs, dtype=np.float32)
+    scale = np.tile((0.10 * np.asarray(pb.pb_sizes, dtype=np.float64)).astype(np.float32), 2)
+    plan = []
+    for pc, ps, pbx in preds:
+        used, anchors = set(), []
+        cx, cy = (pbx[:, 0] + pbx[:, 2]) / 2, (pbx[:, 1] + pbx[:, 3]) / 2
+        for j in range(len(pc)):
+            pick = -1
+            for mi, m in enumerate(maps):
+                ix, iy = min(m - 1, int(cx[j] * m)), min(m - 1, int(cy[j] * m))
+                for t in range(n_pat):
+                    a = int(off[mi] + ((j + t) % n_pat) * m * m + iy * m + ix)
+                    if mask[a] and a not in used:
+                        pick = a
+                        break
+                if pick >= 0:
+                    break
+            if pick < 0:  # every in-cell anchor taken or masked: any free valid anchor will do
+                pick = next(a for a in np.flatnonzero(mask) if a not in used)
+            used.add(pick)
+            anchors.append(pick)
+        anchors = np.asarray(anchors, dtype=np.int64)
+        head = ((pbx.astype(np.float32) - locs_tab[anchors]) / scale[anchors]).astype(np.float32)
+        plan.append((anchors, pc.astype(np.int32), ps.astype(np.float32), head))
+    return plan
+
+
+def eval_head_outputs(pb, plan, lo, hi, device, seed=2007, chunk=64):
+    """Config 4: resident head outputs (objs, clfs, locs) of images [lo, hi) as CUDA tensors.  Background = the
+    config-2 distributions at a lower objectness level (sigmoid(N(-8, 2^2)): a few hundred low-confidence candidates per
+    image, so the NMS has work) drawn per global 64-image chunk from a generator seeded by the chunk id — any rank
+    produces identical values for the same image — with the planned detections of ``plan_eval_head`` written on top."""
+    import torch
+    n, c = len(pb.pb_locs), pb.num_classes
+    cnt = hi - lo
+    objs = torch.empty((cnt, n, 1), dtype=torch.float32, device=device)
+    clfs = torch.empty((cnt, n, c), dtype=torch.float32, device=device)
+    locs = torch.empty((cnt, n, 4), dtype=torch.float32, device=device)
+    gen = torch.Generator(device=device)
+    for q in range(lo // chunk, (hi + chunk - 1) // chunk):
+        gen.manual_seed(seed * 1000003 + q)
+        o = torch.sigmoid(torch.randn((chunk, n, 1), generator=gen, device=device) * 2.0 - 8.0)
+        z = torch.softmax(3.0 * torch.randn((chunk, n, c), generator=gen, device=device), dim=-1)
+        ll = torch.randn((chunk, n, 4), generator=gen, device=device)
+        a, b = max(lo, q * chunk), min(hi, (q + 1) * chunk)
+        objs[a - lo:b - lo], clfs[a - lo:b - lo], locs[a - lo:b - lo] = o[a - q * chunk:b - q * chunk], z[a - q * chunk:b - q * chunk], ll[a - q * chunk:b - q * chunk]
+    flat = np.concatenate([(i - lo) * n + plan[i][0] for i in range(lo, hi)]) if cnt else np.zeros(0, np.int64)
+    if len(flat):
+        idx = torch.from_numpy(flat).to(device)
+        cls = torch.from_numpy(np.concatenate([plan[i][1] for i in range(lo, hi)]).astype(np.int64)).to(device)
+        objs.view(-1)[idx] = torch.from_numpy(np.concatenate([plan[i][2] for i in range(lo, hi)])).to(device)
+        onehot = torch.zeros((len(flat), c), dtype=torch.float32, device=device)
+        onehot[torch.arange(len(flat), device=device), cls] = 1.0
+        clfs.view(-1, c)[idx] = onehot
+        locs.view(-1, 4)[idx] = torch.from_numpy(np.concatenate([plan[i][3] for i in range(lo, hi)])).to(device)
+    return objs, clfs, locs
 
 
 AUGMENT_CONFIGS = {

@@ -1,9 +1,11 @@
-"""TEST INFRASTRUCTURE ONLY — loads the UNMODIFIED reference modules from /root/reference.
+"""TEST INFRASTRUCTURE ONLY — loads the UNMODIFIED reference modules, from /root/reference where it is
+mounted (the build container), else from the sourceless bytecode ``oracle/make_ref.py`` compiled from those
+files into ``oracle/_ref/`` (git-ignored; it travels to the GPU box with the snapshot).
 
-Used only by ``oracle/gen_golden.py`` (golden-vector generation) and by the
-``not gpu`` tests that cross-check ``oracle/restated.py`` against the real
-reference when ``/root/reference`` is mounted (it is absent on the GPU box, so
-nothing under ``-m gpu``, ``smoke()`` or ``bench.py`` imports this file).
+Used by ``oracle/gen_golden.py`` (golden-vector generation), by the ``not gpu`` tests that cross-check
+``oracle/restated.py`` against the real reference, and by the ``--impl reference`` arm of ``bench.py``
+(the reference's own CPU code as the timed baseline).  Nothing under ``object_detector_b200/`` and
+nothing under ``-m gpu`` or ``smoke()`` imports this file.
 
 The reference package cannot be imported whole (``pytoolkit/__init__.py`` pulls
 in TensorFlow etc.), so the eight files the detection path needs are loaded by
@@ -18,12 +20,32 @@ import types
 
 import numpy as np
 
-REFERENCE_ROOT = pathlib.Path('/root/reference/pytoolkit/pytoolkit')
+_MOUNTED = pathlib.Path('/root/reference/pytoolkit/pytoolkit')
+_COPIED = pathlib.Path(__file__).resolve().parent / '_ref' / 'pytoolkit'
+REFERENCE_ROOT = _MOUNTED if (_MOUNTED / 'dl' / 'od_pb.py').is_file() else _COPIED
 _FILES = ['utils', 'log', 'math', 'draw', 'ndimage', 'ml', 'dl.losses', 'dl.od_pb']
 
 
+def _suffix() -> str:
+    return '.py' if REFERENCE_ROOT == _MOUNTED else '.pyc'
+
+
 def available() -> bool:
-    return (REFERENCE_ROOT / 'dl' / 'od_pb.py').is_file()
+    if not (REFERENCE_ROOT / 'dl' / ('od_pb' + _suffix())).is_file():
+        return False
+    if REFERENCE_ROOT == _COPIED:  # bytecode is tied to the interpreter that compiled it
+        import json
+        try:
+            made_by = json.loads((_COPIED.parent / 'MANIFEST.json').read_text())['python']
+        except Exception:  # noqa: BLE001
+            return False
+        return list(sys.version_info[:2]) == list(made_by)
+    return True
+
+
+def source() -> str:
+    """'mounted' (/root/reference), 'compiled' (oracle/_ref) or 'absent'."""
+    return 'absent' if not available() else ('mounted' if REFERENCE_ROOT == _MOUNTED else 'compiled')
 
 
 def load():
@@ -57,8 +79,8 @@ def load():
     pkg.dl = dl
     for name in _FILES:
         full = 'pytoolkit.' + name
-        path = REFERENCE_ROOT / (name.replace('.', '/') + '.py')
-        spec = importlib.util.spec_from_file_location(full, path)
+        path = REFERENCE_ROOT / (name.replace('.', '/') + _suffix())
+        spec = importlib.util.spec_from_file_location(full, path)  # a SourcelessFileLoader for .pyc
         mod = importlib.util.module_from_spec(spec)
         sys.modules[full] = mod
         spec.loader.exec_module(mod)
@@ -77,7 +99,7 @@ def load_augment():
         return pkg
     for name in ('data_utils', 'generator', 'image'):
         full = 'pytoolkit.' + name
-        spec = importlib.util.spec_from_file_location(full, REFERENCE_ROOT / (name + '.py'))
+        spec = importlib.util.spec_from_file_location(full, _MOUNTED / (name + '.py'))  # golden generation only: build container
         mod = importlib.util.module_from_spec(spec)
         sys.modules[full] = mod
         spec.loader.exec_module(mod)

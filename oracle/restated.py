@@ -243,6 +243,36 @@ def numpy_nms_policy(boxes, scores, top_k=200, iou_threshold=0.45):
     return order[keep]
 
 
+def tf_nms_policy(boxes, scores, top_k=200, iou_threshold=0.45):
+    """Restatement of ``tf.image.non_max_suppression`` as TensorFlow 1.10 (the version the reference pins,
+    .travis.requirements.txt:13; call sites layers.py:942,954) implements it in non_max_suppression_op.cc —
+    PARITY UNPINNED (TensorFlow is not in the tree; no reference test checks the op's output):
+    candidates in descending score; a candidate is suppressed iff its IoU with an already selected box is
+    strictly GREATER than the threshold, where the IoU of a pair is 0 when either box has area <= 0 (such boxes
+    are therefore never suppressed, never suppress, and can be selected); selection stops at exactly
+    ``max_output_size``.  fp32 arithmetic: inter / (area_i + area_j - inter).  Tie order among equal scores is
+    unspecified in TF (a priority queue); this build's policy (``stable_desc_order``) is used."""
+    order = stable_desc_order(scores)
+    b = boxes[order].astype(np.float32)
+    area = ((b[:, 2] - b[:, 0]) * (b[:, 3] - b[:, 1])).astype(np.float32)
+    thr = np.float32(iou_threshold)
+    keep = []
+    for i in range(len(b)):
+        if len(keep) >= top_k:
+            break
+        if keep and area[i] > 0:
+            k = np.asarray(keep)
+            w = np.maximum(np.minimum(b[i, 2], b[k, 2]) - np.maximum(b[i, 0], b[k, 0]), np.float32(0))
+            h = np.maximum(np.minimum(b[i, 3], b[k, 3]) - np.maximum(b[i, 1], b[k, 1]), np.float32(0))
+            inter = (w * h).astype(np.float32)
+            with np.errstate(invalid='ignore', divide='ignore'):
+                iou = np.where(area[k] > 0, inter / (area[i] + area[k] - inter), np.float32(0))
+            if (iou > thr).any():
+                continue
+        keep.append(i)
+    return order[np.asarray(keep, dtype=np.int64)]
+
+
 def score_anchors(t: AnchorTables, objs, clfs):
     """layers.py:69-98 (ChannelArgMax / ChannelMax) + od_net.py:177-184 (_objconf).
     objs (B,N,1) f32, clfs (B,N,C) f32 -> classes (B,N) i64, objconfs (B,N) f32."""

@@ -174,6 +174,57 @@ def test_host_pipeline_results_in_order(prior_boxes, use_graph):
     assert pipe.h2d_bytes == sum(x.nbytes for x in sets[0])
 
 
+def test_encode_truth_compact_expands_to_dense(prior_boxes):
+    """odk_assign_encode_compact: valid bits + positive rows + indices, expanded on the host by od_pb.expand_truth, give
+    the dense y_true of odk_assign_encode bit for bit — incl. crowded images, G = 0, a failed image and the bits beyond N."""
+    from object_detector_b200.od_pb import expand_truth
+    for name, batch, gmax in (('voc640', 12, 24), ('odd7', 5, 6), ('tiny128', 3, 3)):
+        pb = prior_boxes(name)
+        boxes, classes, counts = synth.gt_batch(61, batch, gmax, pb.num_classes)
+        counts[1] = 0
+        classes[2, 0] = pb.num_classes + 3  # bad class: the image fails as a whole (od_pb.py:304)
+        dense = pb.encode_truth_batch(boxes, classes, counts, want_valids=True)
+        comp = pb.encode_truth_compact(boxes, classes, counts)
+        assert torch.equal(comp['status'], dense['status']) and int(dense['status'][2]) == 2
+        assert torch.equal(comp['pb_indices'], dense['pb_indices']) and torch.equal(comp['gt_indices'], dense['gt_indices'])
+        h = {k: v.cpu().numpy() for k, v in comp.items()}
+        y = expand_truth(h['pos_rows'], h['valid_bits'], h['pb_indices'], counts, len(pb))
+        assert np.array_equal(y, dense['y_true'].cpu().numpy())
+        n = len(pb)
+        bits = np.unpackbits(h['valid_bits'].view(np.uint8).reshape(batch, -1), axis=1, bitorder='little')
+        assert np.array_equal(bits[:, :n].astype(bool), dense['pb_valids'].cpu().numpy()) and not bits[:, n:].any()
+        assert not h['pos_rows'][2].any() and not bits[2].any()
+
+
+@pytest.mark.parametrize('mode', ['compact', 'fused'])
+def test_host_pipeline_compact_and_fused_modes(prior_boxes, mode):
+    """HostPipeline's other two result contracts against the direct calls: 'compact' (valid bits + positive rows ->
+    expand_truth == dense y_true) and 'fused' (GT in, loss terms + detections out, the network's outputs resident)."""
+    from object_detector_b200.od_pb import expand_truth
+    pb = prior_boxes('voc320')
+    batch, gmax, n = 4, 8, len(pb)
+    sets = [synth.gt_batch(300 + i, batch, gmax, 20) + synth.predictions(400 + i, batch, n, 20) for i in range(3)]
+    resident = None
+    if mode == 'fused':
+        rng = np.random.RandomState(5)
+        y_pred = torch.from_numpy(_head_like(rng, (batch, n, 27), 20)).cuda()
+        resident = {'y_pred': y_pred, 'head': tuple(torch.from_numpy(x).cuda() for x in sets[0][3:])}
+    pipe = pipeline.HostPipeline(pb, batch, gmax, mode=mode, resident=resident)
+    assert pipe.d2h_bytes < 0.02 * batch * n * 27 * 4
+    for s in sets:
+        slot = pipe.submit(*(s if mode == 'compact' else s[:3]))
+        a, d = pipe.result(slot)
+        if mode == 'compact':
+            y = expand_truth(a['pos_rows'].numpy(), a['valid_bits'].numpy(), a['pb_indices'].numpy(), s[2], n)
+            assert np.array_equal(y, pb.encode_truth_batch(*s[:3])['y_true'].cpu().numpy())
+            assert torch.equal(d, pb.decode_nms(*s[3:]).cpu())
+        else:
+            ref = pb.assign_loss_batch(*s[:3], resident['y_pred'])
+            assert torch.equal(a, ref['terms'].cpu()) and torch.equal(d, pb.decode_nms(*resident['head']).cpu())
+    ceiling = pipeline.HostPipeline(pb, batch, gmax, mode=mode, resident=resident, kernels=False)
+    ceiling.result(ceiling.submit(*(sets[0] if mode == 'compact' else sets[0][:3])))  # copies only: runs, returns buffers
+
+
 def _score_objects(seed, n_img, classes, **kw):
     gts, preds = synth.eval_set(seed, n_img, classes, **kw)
     y_true = [odk.ml.ObjectsAnnotation('.', w, h, c, b, d) for (w, h, c, b, d) in gts]

@@ -295,6 +295,68 @@ def test_fused_equals_unfused_full_batch(prior_boxes):
     assert torch.equal(again, out)
 
 
+def test_full_batch_config2_sampled_vs_oracle(prior_boxes, oracle_tables):
+    """BASELINE config 2 at full size (B=64, the bench's own first input set): 16 seeded images of the batch — most of
+    them with batch index >= 32 — against the oracle: kept anchor ids and output rows bit-exact.  Plus four images of
+    the clustered variant of the same batch."""
+    pb, t = prior_boxes('voc640'), oracle_tables('voc640')
+    for seed, clustered, picks in ((1234, False, [0, 7, 21, 31, 32, 33, 38, 40, 45, 47, 48, 52, 55, 59, 62, 63]),
+                                   (4321, True, [5, 33, 50, 63])):
+        objs, clfs, locs = synth.predictions(seed, 64, len(pb), 20, clustered=clustered)
+        out, kept = pb.decode_nms(objs, clfs, locs, return_index=True)
+        out, kept = out.cpu().numpy(), kept.cpu().numpy()
+        ro, rk = R.predict_tail(t, objs[picks], clfs[picks], locs[picks])
+        for j, b in enumerate(picks):
+            assert np.array_equal(kept[b], rk[j]), (clustered, b)
+            assert np.array_equal(out[b], ro[j]), (clustered, b)
+
+
+def test_full_batch_config3_sampled_vs_oracle(prior_boxes, oracle_tables):
+    """BASELINE config 3 at full size (B=256, <=64 GT, every 4th image crowded): 16 seeded images — batch indices up to
+    255, crowded ones included — against the oracle: the whole y_true slab of each image, the index lists and the
+    valid mask, bit for bit."""
+    pb, t = prior_boxes('voc640'), oracle_tables('voc640')
+    boxes, classes, counts = synth.gt_batch(7, 256, 64, 20)
+    res = pb.encode_truth_batch(boxes, classes, counts, want_valids=True)
+    picks = [0, 3, 31, 32, 35, 63, 64, 100, 127, 128, 131, 190, 199, 223, 254, 255]
+    assert sum(1 for b in picks if b % 4 == 3) >= 6 and int(res['status'].abs().sum()) == 0
+    idx = torch.tensor(picks, device='cuda')
+    y = res['y_true'][idx].cpu().numpy()
+    pi, gi, pv = (res[k][idx].cpu().numpy() for k in ('pb_indices', 'gt_indices', 'pb_valids'))
+    for j, b in enumerate(picks):
+        g = int(counts[b])
+        ref = R.encode_truth(t, [(classes[b, :g], boxes[b, :g])])[0]
+        assert np.array_equal(y[j], ref), b
+        ri, rg, rv = R.assign_boxes(t, boxes[b, :g])
+        assert np.array_equal(pi[j, :g], ri) and np.array_equal(gi[j, :g], rg) and np.array_equal(pv[j], rv), b
+        assert (pi[j, g:] == -1).all()
+
+
+def test_tf_style_layer_vs_restated_tf_nms(prior_boxes, oracle_tables):
+    """iou_ge=0 against the restatement of TF-1.10's NonMaxSuppression (PARITY UNPINNED: TensorFlow absent): the whole
+    layer on random and clustered head outputs, then the cases where the two rules differ — an IoU exactly at the
+    threshold (kept by '>', dropped by '>='), zero-area boxes (selectable, never suppressing), and the exact
+    max_output_size cut."""
+    pb, t = prior_boxes('voc320'), oracle_tables('voc320')
+    for clustered in (False, True):
+        objs, clfs, locs = synth.predictions(91, 2, len(pb), 20, clustered=clustered)
+        classes, confs = R.score_anchors(t, objs, clfs)
+        boxes = R.decode_locs_f32(t, locs)
+        out, kept = odk.layers.nms()(20, len(pb), iou_ge=False)([classes, confs, boxes], return_index=True)
+        for b in range(2):
+            ro, rk = R.nms_layer_image(classes[b], confs[b], boxes[b], 20, inner=R.tf_nms_policy)
+            assert np.array_equal(kept[b], rk) and np.array_equal(out[b], ro), (clustered, b)
+    boxes = np.array([[0, 0, 1, 1], [0, 0, 1, 0.5], [0.3, 0.3, 0.3, 0.8], [0.3, 0.3, 0.3, 0.8], [0, 0, 0.9, 1]], np.float32)
+    confs = np.array([[0.9, 0.8, 0.7, 0.6, 0.5]], np.float32)
+    classes = np.zeros((1, 5), np.int32)
+    for top_k in (5, 3, 1):
+        tf_kept = odk.layers.nms()(1, 5, top_k=top_k, nms_threshold=0.5, iou_ge=False)([classes, confs, boxes[None]], return_index=True)[1][0]
+        want = R.tf_nms_policy(boxes, confs[0], top_k, 0.5)
+        assert tf_kept[tf_kept >= 0].tolist() == want.tolist()
+    assert R.tf_nms_policy(boxes, confs[0], 5, 0.5).tolist() == [0, 1, 2, 3]       # IoU(0,1) == 0.5 is not > 0.5; both zero-area boxes selected
+    assert R.numpy_nms_policy(boxes, confs[0], 5, 0.5).tolist() == [0]              # the NumPy rule drops all four others
+
+
 def test_tf_style_mode_runs_and_differs_only_by_rule(prior_boxes):
     """iou_ge=0 (TF-1.10 style, PARITY UNPINNED): strict '>' and no zero-area skip."""
     boxes = np.array([[0, 0, 1, 1], [0, 0, 1, 0.45], [0.2, 0.2, 0.2, 0.9]], np.float32)  # IoU(0,1)=0.45 exactly? no: fp

@@ -269,6 +269,23 @@ def test_confusion_matrix_golden(golden):
     assert np.array_equal(R.od_confusion_matrix(gt, preds, 0.1, 0.3, 3), g['cm_dense/out'])
 
 
+def test_tf_nms_restatement_micro_cases():
+    """The TF-1.10 NonMaxSuppression restatement (PARITY UNPINNED) on hand-computed cases: '>' instead of '>=', zero-area
+    boxes selectable and inert, exact max_output_size; equals the NumPy rule when no pair sits at the threshold and no
+    box is degenerate."""
+    boxes = np.array([[0, 0, 1, 1], [0, 0, 1, 0.5], [0.3, 0.3, 0.3, 0.8], [0.3, 0.3, 0.3, 0.8], [0, 0, 0.9, 1]], np.float32)
+    confs = np.array([0.9, 0.8, 0.7, 0.6, 0.5], np.float32)
+    assert R.tf_nms_policy(boxes, confs, 5, 0.5).tolist() == [0, 1, 2, 3]
+    assert R.tf_nms_policy(boxes, confs, 3, 0.5).tolist() == [0, 1, 2] and R.tf_nms_policy(boxes, confs, 1, 0.5).tolist() == [0]
+    assert R.numpy_nms_policy(boxes, confs, 5, 0.5).tolist() == [0]
+    rng = np.random.RandomState(3)
+    c = rng.uniform(0.2, 0.8, size=(300, 2))
+    s = rng.uniform(0.05, 0.3, size=(300, 2))
+    b = np.concatenate([c - s / 2, c + s / 2], axis=1).astype(np.float32)
+    sc = rng.permutation(300).astype(np.float32) / 300
+    assert R.tf_nms_policy(b, sc, 200, 0.45).tolist() == R.numpy_nms_policy(b, sc, 200, 0.45).tolist()
+
+
 def test_annotation_helpers_match_reference():
     """rot90 / real_bboxes of the mirror datatypes against the unmodified reference classes
     (ml.py:62-65, 102-112), and the oracle's is_match against the reference's own (ml.py:159-182) on random cases."""
