@@ -530,7 +530,13 @@ def run_cuda(args):
         y = torch.empty((b3, N, 27), dtype=torch.float32, device=dev)
         us = time_graph(lambda: pb.encode_truth_batch(*gt, y_true=y), 10)
         st = pb.encode_truth_batch(*gt, y_true=y)['status']
-        return dict(entry(us, b3, b3 * BYTES_ASSIGN_ENCODE), workload='cfg3: assign+encode 640x640, batch 256, <=64 GT/img (every 4th image crowded)',
+        _lib.profile_enable(True)
+        for _ in range(3):
+            pb.encode_truth_batch(*gt, y_true=y)
+        torch.cuda.synchronize()
+        _lib.profile_enable(False)
+        per_kernel = {k: round(ms / c * 1e3, 1) for k, (ms, c) in _lib.profile_read().items()}
+        return dict(entry(us, b3, b3 * BYTES_ASSIGN_ENCODE), kernel_us_eager=per_kernel, workload='cfg3: assign+encode 640x640, batch 256, <=64 GT/img (every 4th image crowded)',
                     status_ok=bool((st == 0).all().item()))
 
     def cfg5():
@@ -547,9 +553,17 @@ def run_cuda(args):
         st = pb5.encode_truth_batch(*gt, y_true=y)['status']
         kept = int((d[:, :, 1] > 0).sum().item())
         w5 = 3 + c5 + 4
+        _lib.profile_enable(True)
+        for _ in range(3):
+            pb5.encode_truth_batch(*gt, y_true=y)
+            pb5.decode_nms(*head, top_k=TOPK, out=d)
+        torch.cuda.synchronize()
+        _lib.profile_enable(False)
+        per_kernel = {k: round(ms / c * 1e3, 1) for k, (ms, c) in _lib.profile_read().items()}
         return {'workload': 'cfg5: dense-anchor stress, N=205800 anchors x 512 GT, C=80, batch 8, NMS IoU 0.45, top-k 200 (head outputs generated on the device)',
                 'assign_encode': dict(entry(us_t, b5, b5 * (20 * g5 + 4 * n5 * w5)), status_ok=bool((st == 0).all().item())),
-                'decode_nms': dict(entry(us_p, b5, b5 * (4 * n5 * (1 + c5 + 4) + 4800)), kept=kept)}
+                'decode_nms': dict(entry(us_p, b5, b5 * (4 * n5 * (1 + c5 + 4) + 4800)), kept=kept),
+                'kernel_us_eager': per_kernel}
 
     def configs():
         out = {}

@@ -39,6 +39,7 @@ struct DecodeArgs {
   float conf_thr;                 // EMIT
   unsigned long long* cand_keys;  // [B, tiles_per_image * TILE]
   int* piece_count;               // [B, tiles_per_image]
+  int* score_hist;                // [B, ODK_HIST_BINS] (pre-zeroed) or null
   int tiles_per_image;
   int stages;  // depth of the shared-memory ring
   int stream_hint;  // 1: head outputs are fetched with an L2 evict-first policy
@@ -58,7 +59,7 @@ struct StageLayout {
 // SPLIT threads share one anchor row (wide class vectors: each scans 1/SPLIT of the classes, the group merges by
 // shuffles), so that a tile of few, long rows still fills the CTA with 256 threads.
 template <int TILE, bool DENSE, int SPLIT>
-__global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const DecodeArgs p) {
+__global__ void __launch_bounds__(TILE * SPLIT, DENSE ? 1 : (SPLIT > 1 ? 1024 : 1280) / (TILE * SPLIT)) decode_score_kernel(const DecodeArgs p) {
   OdkTimeline tl_(ODK_TL_EMIT);
   using L = StageLayout<TILE, DENSE>;
   constexpr int kThreads = TILE * SPLIT;
@@ -71,7 +72,7 @@ __global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const Decode
   __shared__ uint64_t full_bar[L::kMaxStages];
   __shared__ int s_wcnt[2][kWarps];
 
-  const long long total_tiles = (long long)p.batch * p.tiles_per_image;
+  const int total_tiles = p.batch * p.tiles_per_image;  // < 2^31 (checked by the launcher): 32-bit tile arithmetic
   const int tid = threadIdx.x;
   const int row_id = tid / SPLIT, part = tid % SPLIT;  // SPLIT consecutive lanes own one anchor row
 
@@ -84,9 +85,11 @@ __global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const Decode
   auto stage_ptr = [&](int s) { return smem_raw + (size_t)s * stage_bytes; };
 
   // Issue the loads of tile `t` into ring slot `s`.  Completion is signalled on the mbarrier in both paths.
-  auto issue = [&](long long t, int s) {
-    const int b = (int)(t / p.tiles_per_image);
-    const int a0 = (int)(t % p.tiles_per_image) * TILE;
+  // `sp`: lanes 0..ODK_MAX_SPANS-1 of warp 0 hold the tile's span words (use_spans only; fetched ahead of time so that no
+  // global load sits between a ring slot becoming free and its refill)
+  auto issue = [&](int t, int s, uint32_t sp) {
+    const int b = t / p.tiles_per_image;
+    const int a0 = (t - b * p.tiles_per_image) * TILE;
     const int rows = min(TILE, p.n - a0);
     const size_t row0 = (size_t)b * p.n + a0;
     const float* src_clf = p.clfs + row0 * c;
@@ -102,7 +105,6 @@ __global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const Decode
         // pb_mask slabs of the whole tile.  Rows between the runs are never read from HBM (their pb_mask is 0, so
         // conf = x * 0 cannot pass conf_thr >= 0) and never looked at below.
         if (tid < 32) {
-          const uint32_t sp = (tid < ODK_MAX_SPANS) ? __ldg(p.av.spans + (size_t)(a0 / TILE) * ODK_MAX_SPANS + tid) : 0u;
           const uint32_t first = sp >> 16, len = sp & 0xffffu;
           uint32_t bytes = len * (uint32_t)c * 4u, tot = bytes;
 #pragma unroll
@@ -158,16 +160,34 @@ __global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const Decode
   };
 
   // prologue: fill the ring
-  long long t_issue = blockIdx.x;
-  for (int s = 0; s < kStages; ++s, t_issue += gridDim.x)
-    if (t_issue < total_tiles) issue(t_issue, s);
+  const bool span_lane = !DENSE && p.use_spans && tid < ODK_MAX_SPANS;
+  auto span_word = [&](int t) -> uint32_t {
+    return (span_lane && t < total_tiles) ? __ldg(p.av.spans + (size_t)(t % p.tiles_per_image) * ODK_MAX_SPANS + tid) : 0u;
+  };
+  // (tile indices stay below total_tiles + (stages + 1) * gridDim.x < 2^31: checked by the launcher)
+  int t_issue = (int)blockIdx.x;
+  {
+    constexpr int kPre = 3;  // ring slots whose span words are fetched together before the first copy is issued
+    uint32_t sp0[kPre];
+#pragma unroll
+    for (int s = 0; s < kPre; ++s) sp0[s] = (s < kStages) ? span_word(t_issue + s * (int)gridDim.x) : 0u;
+#pragma unroll
+    for (int s = 0; s < kPre; ++s)
+      if (s < kStages) {
+        if (t_issue < total_tiles) issue(t_issue, s, sp0[s]);
+        t_issue += (int)gridDim.x;
+      }
+    for (int s = kPre; s < kStages; ++s, t_issue += (int)gridDim.x)
+      if (t_issue < total_tiles) issue(t_issue, s, span_word(t_issue));
+  }
 
   int slot = 0, buf = 0;
   uint32_t phase = 0;
-  for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+  for (int t = (int)blockIdx.x; t < total_tiles; t += (int)gridDim.x) {  // t + gridDim.x <= total_tiles + grid < 2^31
+    const uint32_t sp_next = span_word(t_issue);  // for the refill of this slot further down; lands while the tile is processed
     odk_mbar_wait(&full_bar[slot], phase);
-    const int b = (int)(t / p.tiles_per_image);
-    const int tile = (int)(t % p.tiles_per_image);
+    const int b = t / p.tiles_per_image;
+    const int tile = t - b * p.tiles_per_image;
     const int a0 = tile * TILE;
     const int rows = min(TILE, p.n - a0);
     const unsigned char* st = stage_ptr(slot);
@@ -248,7 +268,7 @@ __global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const Decode
         p.boxes[r] = box;
       }
       __syncthreads();  // every thread is done with ring slot `slot`
-      if (t_issue < total_tiles) issue(t_issue, slot);
+      if (t_issue < total_tiles) issue(t_issue, slot, 0u);
     } else {
       const bool is_cand = owner && (conf > p.conf_thr);
       const unsigned m = __ballot_sync(0xffffffffu, is_cand);
@@ -256,7 +276,7 @@ __global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const Decode
       const int warp = tid >> 5;
       if (lane == 0) s_wcnt[buf][warp] = __popc(m);
       __syncthreads();  // ring slot free (all rows are in registers) + warp counts visible
-      if (t_issue < total_tiles) issue(t_issue, slot);
+      if (t_issue < total_tiles) issue(t_issue, slot, sp_next);
       int base = 0, total = 0;
 #pragma unroll
       for (int w = 0; w < kWarps; ++w) {
@@ -265,11 +285,14 @@ __global__ void __launch_bounds__(TILE * SPLIT) decode_score_kernel(const Decode
         total += v;
       }
       const size_t piece = (size_t)b * p.tiles_per_image + tile;
-      if (is_cand) p.cand_keys[piece * TILE + base + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
+      if (is_cand) {
+        p.cand_keys[piece * TILE + base + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
+        if (p.score_hist != nullptr) atomicAdd(p.score_hist + (size_t)b * ODK_HIST_BINS + odk_score_bin(conf), 1);
+      }
       if (tid == 0) p.piece_count[piece] = total;
       buf ^= 1;  // the next tile's counts go to the other buffer; this one is rewritten two barriers later
     }
-    t_issue += gridDim.x;
+    t_issue += (int)gridDim.x;
     if (++slot == kStages) { slot = 0; phase ^= 1u; }
   }
 }
@@ -355,6 +378,7 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   args.tiles_per_image = (args.n + TILE - 1) / TILE;
   const long long total = (long long)args.batch * args.tiles_per_image;
+  ODK_REQUIRE(total + 16 * 2048 * 10 < 0x7fffffffLL, ODK_ERR_UNSUPPORTED, "decode_score: %lld tiles", total);
   int per_sm = (int)((220 * 1024) / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / (TILE * SPLIT) ? 2048 / (TILE * SPLIT) : per_sm);
   // EMIT runs beside the train-side kernels of the same step (other graph branch): leave them shared memory
@@ -384,8 +408,9 @@ int odk_piece_size(int num_classes) {
 // Internal entry used by odk_decode_score (dense) and odk_decode_nms (emit).
 int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
                             int32_t* classes, float* confs, float* boxes, bool dense, float conf_thr,
-                            unsigned long long* cand_keys, int* piece_count, cudaStream_t stream) {
+                            unsigned long long* cand_keys, int* piece_count, int* score_hist, cudaStream_t stream) {
   DecodeArgs args;
+  args.score_hist = score_hist;
   args.av = odk_view(a);
   args.batch = batch; args.n = a->n; args.c = a->num_classes;
   args.objs = objs; args.clfs = clfs; args.locs = locs;

@@ -105,6 +105,7 @@ struct NmsArgs {
   int n, piece, n_pieces;
   const unsigned long long* cand_keys;  // [B, n_pieces*piece]
   const int* piece_count;               // [B, n_pieces]
+  const int* score_hist;                // [B, ODK_HIST_BINS] per-image score histogram from score_emit, or null
   const float4* boxes;                  // [B, N] decoded boxes, or null ->
   const float4* locs;                   // [B, N] head output, decoded lazily
   float iou_thr;
@@ -246,18 +247,23 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
   // otherwise each pass reads them from L2 through the piece prefix sums.
   const bool cached = total <= p.cache_cap;
   if (cached) {
-    // fire-and-forget 8-byte async copies: every key of the image is in flight at once
-    const int slots = p.n_pieces * p.piece;
-    const int shift = 31 - __clz(p.piece);  // piece heights are powers of two
-    for (int i = tid; i < slots; i += kNmsThreads) {
-      const int q = i >> shift, sl = i & (p.piece - 1);
-      const int q_lo = s_pref[q];
-      if (sl < s_pref[q + 1] - q_lo) odk_cp_async<8>(s_cache + q_lo + sl, keys + i);
+    // fire-and-forget 8-byte async copies: every key of the image is in flight at once.  A warp takes a piece, its
+    // lanes the piece's entries (pieces are mostly sparse: the loop runs over what is there, not over the slots)
+    for (int q = warp; q < p.n_pieces; q += kNmsWarps) {
+      const int q_lo = s_pref[q], cnt = s_pref[q + 1] - q_lo;
+      const unsigned long long* src = keys + (size_t)q * p.piece;
+      for (int sl = lane; sl < cnt; sl += 32) odk_cp_async<8>(s_cache + q_lo + sl, src + sl);
     }
-    odk_cp_async_commit();
-    odk_cp_async_wait<0>();
-    __syncthreads();
+    odk_cp_async_commit();  // waited for just before the first pass that reads the cache (cache_ready below)
   }
+  bool cache_pending = cached;
+  auto cache_ready = [&]() {
+    if (cache_pending) {
+      odk_cp_async_wait<0>();
+      __syncthreads();
+      cache_pending = false;
+    }
+  };
   // Visits every candidate key of the image once (any thread, any order).  Cached: a strided walk over shared memory.
   // Not cached (more candidates than the cache holds, e.g. 57 k per image in the dense-anchor stress shape): a warp takes
   // four pieces at a time and its lanes the pieces' entries — coalesced 8-byte loads from L2, no index search.
@@ -289,6 +295,44 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
   int nkept = 0, processed = 0;
   unsigned long long hi_key = ~0ull;  // keys of earlier bands are >= hi_key (every real key is < ~0)
 
+  // Walks the nb_bins bins of s_hist from the top: n_take = how many top bins to take whole, cnt = keys they hold
+  // (incl. `above`).  Prefers the shortest run of top bins that reaches `want` keys (the sweep rarely needs more); if
+  // the bin that crosses `want` would overflow the band, the bins before it.  All threads call it; uniform result.
+  auto walk_bins = [&](int nb_bins, int above, int want, int& n_take, int& cnt) {
+    constexpr int per = (kBins + kNmsThreads - 1) / kNmsThreads;
+    int loc[per];
+    int lsum = 0;
+#pragma unroll
+    for (int j = 0; j < per; ++j) {
+      const int r = tid * per + j;
+      loc[j] = (r < nb_bins) ? s_hist[nb_bins - 1 - r] : 0;
+      lsum += loc[j];
+    }
+    int tot_in_bucket;
+    int run = above + block_exclusive_scan(lsum, s_scan, tot_in_bucket);
+    // S is monotone over r, so "S < want" and "S <= kBand" each hold on a prefix of the bins
+    int n_ok = 0, last_ok_sum = -1, n_lt = 0, first_ge_sum = INT_MAX;
+#pragma unroll
+    for (int j = 0; j < per; ++j) {
+      run += loc[j];
+      const int r = tid * per + j;
+      if (r < nb_bins) {
+        if (run <= kBand) { ++n_ok; last_ok_sum = run; }
+        if (run < want) ++n_lt;
+        else first_ge_sum = min(first_ge_sum, run);
+      }
+    }
+    if (tid == 0) { s_sel[0] = 0; s_sel[1] = above; s_sel[2] = 0; s_sel[3] = INT_MAX; }
+    __syncthreads();
+    if (n_ok) { atomicAdd(&s_sel[0], n_ok); atomicMax(&s_sel[1], last_ok_sum); }
+    if (n_lt) atomicAdd(&s_sel[2], n_lt);
+    if (first_ge_sum != INT_MAX) atomicMin(&s_sel[3], first_ge_sum);
+    __syncthreads();
+    if (s_sel[2] < s_sel[0]) { n_take = s_sel[2] + 1; cnt = s_sel[3]; }
+    else { n_take = s_sel[0]; cnt = s_sel[1]; }
+    __syncthreads();
+  };
+
   while (processed < total && (STRICT ? nkept2 < p.top_k : nkept < limit)) {
     const int remaining = total - processed;
     // ---- a. threshold of the next band: MSB radix select starting at the first bit in which the
@@ -300,7 +344,24 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     int want = need + (need >> 2) + 32;
     if (STRICT && nkept2 > 0) want = (int)min((long long)kBand, (long long)need * processed / nkept2 * 5 / 4 + 32);
     want = min(kBand, want);
-    if (remaining > kBand) {
+    bool have_lo = remaining <= kBand;
+    if (!have_lo && processed == 0 && p.score_hist != nullptr) {
+      // first round: the score histogram score_emit built while streaming replaces the passes over the keys
+      // (min/max + digit histograms).  A bin's lower bound is a key threshold; if the bin that crosses `want`
+      // overflows the band and too little lies above it, the generic select below refines among all keys.
+      const int* hist = p.score_hist + (size_t)b * ODK_HIST_BINS;
+      for (int i = tid; i < ODK_HIST_BINS; i += kNmsThreads) s_hist[i] = hist[i];
+      __syncthreads();
+      int n_take_bins, cnt_take;
+      walk_bins(ODK_HIST_BINS, 0, want, n_take_bins, cnt_take);
+      if (cnt_take >= max(32, want / 2)) {
+        const int d_star = ODK_HIST_BINS - n_take_bins;  // bins >= d_star are taken whole (n_take_bins >= 1 here)
+        lo_key = d_star > 0 ? odk_bin_lo_key(d_star) : 0ull;
+        have_lo = true;
+      }
+    }
+    cache_ready();
+    if (!have_lo) {
       unsigned long long kmin = ~0ull, kmax = 0ull;
       for_each_key([&](unsigned long long k) {
         if (k < hi_key) {
@@ -334,43 +395,10 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
         __syncthreads();
         // walk the digits from the top: largest r such that above + S(r) <= kBand, S = inclusive sum over reversed bins
         const int nb_bins = 1 << width;
-        constexpr int per = (kBins + kNmsThreads - 1) / kNmsThreads;
-        int loc[per];
-        int lsum = 0;
-#pragma unroll
-        for (int j = 0; j < per; ++j) {
-          const int r = tid * per + j;
-          loc[j] = (r < nb_bins) ? s_hist[nb_bins - 1 - r] : 0;
-          lsum += loc[j];
-        }
-        int tot_in_bucket;
-        int run = above + block_exclusive_scan(lsum, s_scan, tot_in_bucket);
-        // S is monotone over r, so "S < want" and "S <= kBand" each hold on a prefix of the bins
-        int n_ok = 0, last_ok_sum = -1, n_lt = 0, first_ge_sum = INT_MAX;
-#pragma unroll
-        for (int j = 0; j < per; ++j) {
-          run += loc[j];
-          const int r = tid * per + j;
-          if (r < nb_bins) {
-            if (run <= kBand) { ++n_ok; last_ok_sum = run; }
-            if (run < want) ++n_lt;
-            else first_ge_sum = min(first_ge_sum, run);
-          }
-        }
-        if (tid == 0) { s_sel[0] = 0; s_sel[1] = above; s_sel[2] = 0; s_sel[3] = INT_MAX; }
-        __syncthreads();
-        if (n_ok) { atomicAdd(&s_sel[0], n_ok); atomicMax(&s_sel[1], last_ok_sum); }
-        if (n_lt) atomicAdd(&s_sel[2], n_lt);
-        if (first_ge_sum != INT_MAX) atomicMin(&s_sel[3], first_ge_sum);
-        __syncthreads();
-        // Prefer the shortest run of top digits that reaches `want` keys (the sweep rarely needs more); if the
-        // bin that crosses `want` would overflow the band, take the bins before it and, when that is too few,
-        // refine inside the crossing bin.
         int n_take_bins, cnt_take;
-        if (s_sel[2] < s_sel[0]) { n_take_bins = s_sel[2] + 1; cnt_take = s_sel[3]; }
-        else { n_take_bins = s_sel[0]; cnt_take = s_sel[1]; }
+        walk_bins(nb_bins, above, want, n_take_bins, cnt_take);
+        // when the bins taken whole hold too few keys, refine inside the crossing bin
         const int d_star = nb_bins - n_take_bins;  // digits >= d_star are taken whole
-        __syncthreads();
         if (cnt_take >= max(32, want / 2) || shift == 0) {
           if (d_star < nb_bins) lo_key = ((prefix << width) | (unsigned long long)d_star) << shift;
           else lo_key = (prefix + 1ull) << top;  // nothing of this bucket: only the keys above it (top < 64 here)
@@ -636,6 +664,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
 struct NmsWorkspace {
   int* piece_count;               // [B, ceil(N/32)]   (only n_pieces per image are used)
   unsigned long long* cand_keys;  // [B, round_up(N, 256)]
+  int* score_hist;                // [B, ODK_HIST_BINS]
   float4* spill_box;              // strict only: [B, N]
   int2* spill_meta;               // strict only: [B, N]
   size_t bytes;
@@ -647,11 +676,13 @@ static NmsWorkspace nms_layout(void* base, int batch, int n, bool strict = false
   auto take = [&](size_t bytes) { size_t o = off; off = odk_align_up(off + bytes, 256); return o; };
   const size_t o_cnt = take(sizeof(int) * (size_t)batch * ((n + 31) / 32));
   const size_t o_ck = take(8 * (size_t)batch * odk_align_up((size_t)n, 256));
+  const size_t o_hist = take(sizeof(int) * (size_t)batch * ODK_HIST_BINS);
   const size_t o_sb = strict ? take(16 * (size_t)batch * n) : 0;
   const size_t o_sm = strict ? take(8 * (size_t)batch * n) : 0;
   char* p = static_cast<char*>(base);
   w.piece_count = reinterpret_cast<int*>(p + o_cnt);
   w.cand_keys = reinterpret_cast<unsigned long long*>(p + o_ck);
+  w.score_hist = reinterpret_cast<int*>(p + o_hist);
   w.spill_box = strict ? reinterpret_cast<float4*>(p + o_sb) : nullptr;
   w.spill_meta = strict ? reinterpret_cast<int2*>(p + o_sm) : nullptr;
   w.bytes = off;
@@ -674,8 +705,9 @@ static int nms_check(int batch, int n, int num_classes, int top_k, const void* w
 // select + sort + sweep + output on already emitted candidate pieces
 static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch, int n, int piece, const float4* boxes, const float4* locs,
                    float iou_thr, int top_k, int limit, int iou_ge, float* out, int32_t* kept_index, int32_t* out_index, int32_t* out_count,
-                   cudaStream_t stream, bool strict = false, float iou_thr2 = 0.f) {
+                   cudaStream_t stream, bool strict = false, float iou_thr2 = 0.f, bool have_hist = false) {
   NmsArgs a;
+  a.score_hist = have_hist ? w.score_hist : nullptr;
   if (anchors != nullptr) a.av = odk_view(anchors);
   else memset(&a.av, 0, sizeof(a.av));
   a.n = n; a.piece = piece; a.n_pieces = (n + piece - 1) / piece;
@@ -717,7 +749,7 @@ static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch,
 int odk_piece_size(int num_classes);
 int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
                             int32_t* classes, float* confs, float* boxes, bool dense, float conf_thr,
-                            unsigned long long* cand_keys, int* piece_count, cudaStream_t stream);
+                            unsigned long long* cand_keys, int* piece_count, int* score_hist, cudaStream_t stream);
 
 extern "C" size_t odk_nms_workspace_bytes(int batch, int n, int num_classes, int top_k) {
   if (batch < 1 || n < 1 || num_classes < 1 || top_k < 0) return 0;
@@ -759,11 +791,13 @@ static int decode_nms_impl(const odk_anchors* a, int batch, const float* objs, c
   ODK_REQUIRE((((uintptr_t)objs | (uintptr_t)clfs) & 3) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_nms: inputs must be 4-byte aligned");
   ODK_REQUIRE(((uintptr_t)locs & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_nms: locs must be 16-byte aligned");
   NmsWorkspace w = nms_layout(workspace, batch, a->n, strict);
+  static const bool use_hist = !(getenv("ODK_NMS_HIST") && atoi(getenv("ODK_NMS_HIST")) == 0);  // diagnostics: 0 = generic select only
+  if (use_hist) ODK_CUDA(cudaMemsetAsync(w.score_hist, 0, sizeof(int) * (size_t)batch * ODK_HIST_BINS, stream));
   if (int rc = odk_launch_decode_score(a, batch, objs, clfs, locs, nullptr, nullptr, nullptr, false, conf_thr, w.cand_keys, w.piece_count,
-                                       stream))
+                                       use_hist ? w.score_hist : nullptr, stream))
     return rc;
   return nms_run(w, a, batch, a->n, odk_piece_size(a->num_classes), nullptr, reinterpret_cast<const float4*>(locs), iou_thr, top_k, top_k,
-                 iou_ge, out, kept_index, nullptr, nullptr, stream, strict, nms_all_thr);
+                 iou_ge, out, kept_index, nullptr, nullptr, stream, strict, nms_all_thr, use_hist);
 }
 
 extern "C" int odk_nms_layer(int batch, int n, int num_classes, const int32_t* classes, const float* confs, const float* boxes,

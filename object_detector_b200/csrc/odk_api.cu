@@ -19,7 +19,7 @@ int odk_set_error(int code, const char* fmt, ...) {
 
 int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
                             int32_t* classes, float* confs, float* boxes, bool dense, float conf_thr,
-                            unsigned long long* cand_keys, int* piece_count, cudaStream_t stream);
+                            unsigned long long* cand_keys, int* piece_count, int* score_hist, cudaStream_t stream);
 int odk_launch_decode_locs(const odk_anchors* a, long long rows, const float* pred, float* out, cudaStream_t stream);
 int odk_piece_size(int num_classes);
 int odk_launch_decode_locs_f64(const odk_anchors* a, long long rows, const double* pred, double* out, cudaStream_t stream);
@@ -158,6 +158,7 @@ extern "C" int odk_anchors_create(odk_anchors** out, int n, int num_classes, int
   // od_net.py:183-184), so the fused predict path fetches only the runs of valid rows of a tile.  Runs separated by at
   // most two masked rows are merged (a separate bulk copy costs more than the five sectors it saves); a tile keeps at
   // most ODK_MAX_SPANS runs (the narrowest gaps are merged first).
+  static const int span_gap = getenv("ODK_SPAN_GAP") ? atoi(getenv("ODK_SPAN_GAP")) : 2;
   a->span_tile = odk_piece_size(num_classes);
   const int n_tiles = (n + a->span_tile - 1) / a->span_tile;
   std::vector<uint32_t> spans((size_t)n_tiles * ODK_MAX_SPANS, 0u);
@@ -167,7 +168,7 @@ extern "C" int odk_anchors_create(odk_anchors** out, int n, int num_classes, int
     std::vector<std::pair<int, int>> run;  // [first, end)
     for (int i = 0; i < rows; ++i) {
       if (!pb_mask[a0 + i]) continue;
-      if (!run.empty() && i - run.back().second <= 2) run.back().second = i + 1;
+      if (!run.empty() && i - run.back().second <= span_gap) run.back().second = i + 1;
       else run.push_back({i, i + 1});
     }
     while ((int)run.size() > ODK_MAX_SPANS) {
@@ -246,6 +247,6 @@ extern "C" int odk_decode_score(const odk_anchors* a, int batch, const float* ob
   ODK_REQUIRE(a != nullptr && batch >= 1, ODK_ERR_INVALID_ARGUMENT, "decode_score: bad arguments");
   ODK_REQUIRE(objs && clfs && locs && classes && confs && boxes, ODK_ERR_INVALID_ARGUMENT, "decode_score: null pointer");
   ODK_REQUIRE(((uintptr_t)boxes & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "decode_score: boxes must be 16-byte aligned");
-  return odk_launch_decode_score(a, batch, objs, clfs, locs, classes, confs, boxes, true, 0.f, nullptr, nullptr,
+  return odk_launch_decode_score(a, batch, objs, clfs, locs, classes, confs, boxes, true, 0.f, nullptr, nullptr, nullptr,
                                  static_cast<cudaStream_t>(stream));
 }

@@ -168,6 +168,22 @@ __device__ __forceinline__ int odk_key2_class(unsigned long long k) {
 }
 __device__ __forceinline__ float odk_key2_score(unsigned long long k) { return odk_unflip_score((uint32_t)(k >> 32)); }
 
+// ---- per-image score histogram (filled by score_emit, read by the first select round of the NMS kernel) ------------
+// 1024 bins over the fp32 bit pattern of conf: 128 bins per octave from 2^-7 up (bin = (bits >> 16) - 0x3C00, clamped),
+// so the bin index is monotone in conf and a bin's lower bound is a key threshold.  conf <= 2^-7 (or negative) falls
+// into bin 0, conf >= 2 into the last bin: still correct, only coarser.
+#define ODK_HIST_BINS 1024
+__device__ __forceinline__ int odk_score_bin(float conf) {
+  const uint32_t u = __float_as_uint(conf);
+  if (u >> 31) return 0;
+  const int i = (int)(u >> 16) - 0x3C00;
+  return i < 0 ? 0 : (i > ODK_HIST_BINS - 1 ? ODK_HIST_BINS - 1 : i);
+}
+// smallest key2 whose score lies in bin >= d (d >= 1); every key of a lower bin is smaller
+__device__ __forceinline__ unsigned long long odk_bin_lo_key(int d) {
+  return (unsigned long long)((((uint32_t)(d + 0x3C00)) << 16) | 0x80000000u) << 32;
+}
+
 // The fp32 decode of od_pb.py:216-222 as the Keras Lambda evaluates it (od_net.py:189).
 __device__ __forceinline__ float4 odk_decode_box(const float4 pr, const float4 lc, const float2 sc) {
   float4 box;
