@@ -34,6 +34,7 @@ struct AssignArgs {
   int32_t* status;
   int list_len;  // ranked candidates remembered per GT
   int use_walk;  // greedy kernel: the first 32 ranks of every GT are regrouped in walk order (shared memory permitting)
+  int stage_len; // greedy kernel: ranks of every GT staged in shared memory (the rest is read from the workspace on demand)
   int bitmap_words;
   int* ws_list;   // [B, Gmax, list_len] ranked in-cell anchors
   int* ws_ncand;  // [B, Gmax] in-cell valid anchors of the GT
@@ -266,8 +267,10 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   const int b = blockIdx.x;
   const int L = p.list_len;
   unsigned char* sp = greedy_smem;
+  const int SL = p.stage_len;  // 32: the ranks the fast path looks at; deeper ranks (crowded images) come from the workspace
+  const int* glist = p.ws_list + (size_t)b * p.gmax * L;
   float4* gbox = reinterpret_cast<float4*>(sp);            sp += (size_t)p.gmax * 16;
-  int* list = reinterpret_cast<int*>(sp);                  sp += (size_t)p.gmax * L * 4;  // 16-byte aligned (L % 8 == 0)
+  int* list = reinterpret_cast<int*>(sp);                  sp += (size_t)p.gmax * SL * 4;  // 16-byte aligned (SL % 8 == 0)
   float* garea = reinterpret_cast<float*>(sp);             sp += (size_t)p.gmax * 4;
   int* order = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
   int* pick = reinterpret_cast<int*>(sp);                  sp += (size_t)p.gmax * 4;
@@ -304,10 +307,12 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     }
   }
   for (int w = threadIdx.x; w < p.bitmap_words; w += kGreedyThreads) taken[w] = 0u;
-  {  // stage the ranked lists: 16-byte cp.async, all in flight at once (entries beyond nlist[g] are never read)
-    const int4* src = reinterpret_cast<const int4*>(p.ws_list + (size_t)b * p.gmax * L);
-    int4* dst = reinterpret_cast<int4*>(list);
-    for (int i = threadIdx.x; i < G * (L / 4); i += kGreedyThreads) odk_cp_async<16>(dst + i, src + i);
+  {  // stage the first SL ranks of every list: 16-byte cp.async, all in flight at once (entries beyond nlist[g] are never read)
+    const int per = SL / 4;
+    for (int i = threadIdx.x; i < G * per; i += kGreedyThreads) {
+      const int g = i / per, k4 = i - g * per;
+      odk_cp_async<16>(reinterpret_cast<int4*>(list + (size_t)g * SL) + k4, reinterpret_cast<const int4*>(glist + (size_t)g * L) + k4);
+    }
     odk_cp_async_commit();
   }
   __syncthreads();
@@ -329,7 +334,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     // regroup what the walk reads: one independent shared-memory load per step instead of order -> nlist -> list
     for (int i = threadIdx.x; i < G * 32; i += kGreedyThreads) {
       const int g = order[i >> 5], k = i & 31;
-      walk_a[i] = (k < nlist[g]) ? list[(size_t)g * L + k] : -1;
+      walk_a[i] = (k < nlist[g]) ? list[(size_t)g * SL + k] : -1;
     }
     __syncthreads();
   }
@@ -348,7 +353,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
           if (rr >= G) return -1;
           if (p.use_walk) return walk_a[rr * 32 + lane];
           const int gg = order[rr];
-          return (lane < nlist[gg]) ? list[(size_t)gg * L + lane] : -1;
+          return (lane < nlist[gg]) ? list[(size_t)gg * SL + lane] : -1;
         };
         int a0 = fetch(r), a1 = fetch(r + 1);
         for (; r < G; ++r) {
@@ -373,7 +378,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
           int best_a = -1;
           for (int k0 = 32; k0 < nl && best_a < 0; k0 += 32) {
             const int k = k0 + lane;
-            const int a = (k < nl) ? list[(size_t)g * L + k] : -1;
+            const int a = (k < nl) ? __ldg(glist + (size_t)g * L + k) : -1;  // ranks >= 32: rare, straight from the workspace
             const bool is_free = a >= 0 && !((taken[a >> 5] >> (a & 31)) & 1u);
             const unsigned fm2 = __ballot_sync(0xffffffffu, is_free);
             if (fm2) best_a = __shfl_sync(0xffffffffu, a, __ffs(fm2) - 1);
@@ -492,10 +497,10 @@ __global__ void encode_locs_kernel(AnchorView av, int k, const float4* __restric
   out[4 * i + 3] = __ddiv_rn(__ddiv_rn((double)__fsub_rn(box.w, loc.w), sz.y), 0.10);
 }
 
-int assign_list_len(int gmax) {
-  int list_len = (int)((96 * 1024) / (4 * (size_t)gmax)) & ~7;
-  return list_len > 128 ? 128 : (list_len < 8 ? 8 : list_len);
-}
+// Ranked in-cell anchors remembered per GT in the workspace.  The VOC layout has at most 96 anchors whose cell holds a
+// centre (SURVEY A-1), so 128 ranks make the exact re-evaluation path a safeguard; only the first 32 are staged in
+// shared memory by the greedy kernel.
+int assign_list_len(int /*gmax*/) { return 128; }
 
 }  // namespace
 
@@ -524,6 +529,7 @@ static int fill_args(AssignArgs& args, const odk_anchors* a, int batch, const fl
   args.ws_nlist = args.ws_ncand + (size_t)batch * gmax;
   args.ws_ignore = ignore;
   args.use_walk = 0;
+  args.stage_len = 32;
   return ODK_OK;
 }
 
@@ -567,7 +573,7 @@ int odk_launch_assign_greedy(const odk_anchors* a, int batch, const float* gt_bo
                              int gmax, int64_t* pb_indices, int64_t* gt_indices, int32_t* status, void* lists_ws, cudaStream_t stream) {
   AssignArgs args;
   fill_args(args, a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, lists_ws, nullptr);
-  size_t smem = odk_align_up((size_t)gmax * (16 + 20 + 4 * (size_t)args.list_len) + (size_t)args.bitmap_words * 4, 16);
+  size_t smem = odk_align_up((size_t)gmax * (16 + 20 + 4 * (size_t)args.stage_len) + (size_t)args.bitmap_words * 4, 16);
   ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign: N=%d / Gmax=%d need %zu bytes of shared memory per image", a->n, gmax, smem);
   args.use_walk = (smem + (size_t)gmax * 128 <= 200 * 1024) ? 1 : 0;
   if (args.use_walk) smem += (size_t)gmax * 128;

@@ -41,6 +41,7 @@ struct DecodeArgs {
   int* piece_count;               // [B, tiles_per_image]
   int* score_hist;                // [B, ODK_HIST_BINS] (pre-zeroed) or null
   int tiles_per_image;
+  int pieces_per_image;  // EMIT: candidate pieces per image (32-anchor pieces when a thread owns a row, else one per tile)
   int stages;  // depth of the shared-memory ring
   int stream_hint;  // 1: head outputs are fetched with an L2 evict-first policy
   int use_spans;    // EMIT: fetch only the runs of valid anchors of a tile (av.spans); rows outside them have pb_mask = 0
@@ -207,28 +208,23 @@ __global__ void __launch_bounds__(TILE * SPLIT, DENSE ? 1 : (SPLIT > 1 ? 1024 : 
       const bool scan = row_id < rows && (DENSE || !p.use_spans || s_amask[row_id] != 0);
       if (scan) {
         if ((c & 3) == 0) {
-          // four independent running maxima (one per float4 lane) keep the dependency chains short; each is a
-          // first-maximum scan of its own residue class, and the merge prefers the lower index on equal values,
-          // which together is np.argmax's "first maximum wins"
+          // The stream is bound by the ALU pipe (compares and selects issue at half rate), so the scan is arranged to
+          // need few of them: the maximum of a float4 chunk costs two min/max instructions (FMNMX3 + FMNMX), the running
+          // best one compare and two selects per CHUNK, and the position inside the winning chunk is looked up once at
+          // the end.  "First maximum wins" (np.argmax): a later chunk replaces the best only if strictly greater, and
+          // inside the chunk the first element equal to the maximum is taken.  NaNs never win a comparison (as before).
           const int nchunk = c >> 2, per = (nchunk + SPLIT - 1) / SPLIT;
           const int j0 = part * per, j1 = min(nchunk, j0 + per);
-          if (j0 < j1) {
-            const float4* row4 = reinterpret_cast<const float4*>(row);
-            float4 v = row4[j0];
-            float b0 = v.x, b1 = v.y, b2 = v.z, b3 = v.w;
-            int i0 = 4 * j0, i1 = 4 * j0 + 1, i2 = 4 * j0 + 2, i3 = 4 * j0 + 3;
-            for (int j = j0 + 1; j < j1; ++j) {
-              v = row4[j];
-              if (v.x > b0) { b0 = v.x; i0 = 4 * j; }
-              if (v.y > b1) { b1 = v.y; i1 = 4 * j + 1; }
-              if (v.z > b2) { b2 = v.z; i2 = 4 * j + 2; }
-              if (v.w > b3) { b3 = v.w; i3 = 4 * j + 3; }
-            }
-            if (b1 > b0 || (b1 == b0 && i1 < i0)) { b0 = b1; i0 = i1; }
-            if (b3 > b2 || (b3 == b2 && i3 < i2)) { b2 = b3; i2 = i3; }
-            if (b2 > b0 || (b2 == b0 && i2 < i0)) { b0 = b2; i0 = i2; }
-            best = b0;
-            cls = i0;
+          const float4* row4 = reinterpret_cast<const float4*>(row);
+          int jb = -1;
+          for (int j = j0; j < j1; ++j) {
+            const float4 v = row4[j];
+            const float mj = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+            if (mj > best || (jb < 0 && mj == best)) { best = mj; jb = j; }  // second clause: a chunk of -inf values
+          }
+          if (jb >= 0) {
+            const float4 v = row4[jb];
+            cls = 4 * jb + (v.x == best ? 0 : (v.y == best ? 1 : (v.z == best ? 2 : 3)));
           }
         } else {
           const int per = (c + SPLIT - 1) / SPLIT;
@@ -274,23 +270,38 @@ __global__ void __launch_bounds__(TILE * SPLIT, DENSE ? 1 : (SPLIT > 1 ? 1024 : 
       const unsigned m = __ballot_sync(0xffffffffu, is_cand);
       const unsigned lane = odk_lane();
       const int warp = tid >> 5;
-      if (lane == 0) s_wcnt[buf][warp] = __popc(m);
-      __syncthreads();  // ring slot free (all rows are in registers) + warp counts visible
-      if (t_issue < total_tiles) issue(t_issue, slot, sp_next);
-      int base = 0, total = 0;
+      if (SPLIT == 1) {
+        // a warp owns 32 consecutive anchors = one candidate piece: compaction needs no cross-warp scan
+        __syncthreads();  // ring slot free (all rows are in registers)
+        if (t_issue < total_tiles) issue(t_issue, slot, sp_next);
+        const int piece_in_image = tile * kWarps + warp;
+        if (piece_in_image < p.pieces_per_image) {
+          const size_t piece = (size_t)b * p.pieces_per_image + piece_in_image;
+          if (is_cand) {
+            p.cand_keys[piece * 32 + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
+            if (p.score_hist != nullptr) atomicAdd(p.score_hist + (size_t)b * ODK_HIST_BINS + odk_score_bin(conf), 1);
+          }
+          if (lane == 0) p.piece_count[piece] = __popc(m);
+        }
+      } else {
+        if (lane == 0) s_wcnt[buf][warp] = __popc(m);
+        __syncthreads();  // ring slot free (all rows are in registers) + warp counts visible
+        if (t_issue < total_tiles) issue(t_issue, slot, sp_next);
+        int base = 0, total = 0;
 #pragma unroll
-      for (int w = 0; w < kWarps; ++w) {
-        const int v = s_wcnt[buf][w];
-        base += (w < warp) ? v : 0;
-        total += v;
+        for (int w = 0; w < kWarps; ++w) {
+          const int v = s_wcnt[buf][w];
+          base += (w < warp) ? v : 0;
+          total += v;
+        }
+        const size_t piece = (size_t)b * p.tiles_per_image + tile;
+        if (is_cand) {
+          p.cand_keys[piece * TILE + base + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
+          if (p.score_hist != nullptr) atomicAdd(p.score_hist + (size_t)b * ODK_HIST_BINS + odk_score_bin(conf), 1);
+        }
+        if (tid == 0) p.piece_count[piece] = total;
+        buf ^= 1;  // the next tile's counts go to the other buffer; this one is rewritten two barriers later
       }
-      const size_t piece = (size_t)b * p.tiles_per_image + tile;
-      if (is_cand) {
-        p.cand_keys[piece * TILE + base + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
-        if (p.score_hist != nullptr) atomicAdd(p.score_hist + (size_t)b * ODK_HIST_BINS + odk_score_bin(conf), 1);
-      }
-      if (tid == 0) p.piece_count[piece] = total;
-      buf ^= 1;  // the next tile's counts go to the other buffer; this one is rewritten two barriers later
     }
     t_issue += (int)gridDim.x;
     if (++slot == kStages) { slot = 0; phase ^= 1u; }
@@ -377,6 +388,7 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   auto kern = decode_score_kernel<TILE, DENSE, SPLIT>;
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   args.tiles_per_image = (args.n + TILE - 1) / TILE;
+  args.pieces_per_image = SPLIT == 1 ? (args.n + 31) / 32 : args.tiles_per_image;
   const long long total = (long long)args.batch * args.tiles_per_image;
   ODK_REQUIRE(total + 16 * 2048 * 10 < 0x7fffffffLL, ODK_ERR_UNSUPPORTED, "decode_score: %lld tiles", total);
   int per_sm = (int)((220 * 1024) / (smem + 1024));
@@ -397,13 +409,17 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
 
 }  // namespace
 
-// Candidate piece (= tile) height used for `num_classes` channels: chosen so that the shared-memory ring
-// stays under ~100 KB (2+ CTAs per SM).  The NMS workspace layout depends on it.
+// Tile height used for `num_classes` channels: chosen so that the shared-memory ring stays under ~100 KB (2+ CTAs per
+// SM).  The span table of the anchors handle is built for it.
 int odk_piece_size(int num_classes) {
   static const int env_tile = getenv("ODK_EMIT_TILE") ? atoi(getenv("ODK_EMIT_TILE")) : 0;
   if (num_classes <= 32 && env_tile == 128) return 128;
   return num_classes <= 32 ? 256 : (num_classes <= 96 ? 64 : 32);
 }
+
+// Height of the candidate pieces score_emit writes (the NMS workspace layout depends on it): a warp's 32 anchors where a
+// thread owns a whole row (C <= 32), else the tile.
+int odk_emit_piece_size(int num_classes) { return num_classes <= 32 ? 32 : odk_piece_size(num_classes); }
 
 // Internal entry used by odk_decode_score (dense) and odk_decode_nms (emit).
 int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,

@@ -746,7 +746,7 @@ static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch,
   return ODK_OK;
 }
 
-int odk_piece_size(int num_classes);
+int odk_emit_piece_size(int num_classes);
 int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
                             int32_t* classes, float* confs, float* boxes, bool dense, float conf_thr,
                             unsigned long long* cand_keys, int* piece_count, int* score_hist, cudaStream_t stream);
@@ -796,7 +796,7 @@ static int decode_nms_impl(const odk_anchors* a, int batch, const float* objs, c
   if (int rc = odk_launch_decode_score(a, batch, objs, clfs, locs, nullptr, nullptr, nullptr, false, conf_thr, w.cand_keys, w.piece_count,
                                        use_hist ? w.score_hist : nullptr, stream))
     return rc;
-  return nms_run(w, a, batch, a->n, odk_piece_size(a->num_classes), nullptr, reinterpret_cast<const float4*>(locs), iou_thr, top_k, top_k,
+  return nms_run(w, a, batch, a->n, odk_emit_piece_size(a->num_classes), nullptr, reinterpret_cast<const float4*>(locs), iou_thr, top_k, top_k,
                  iou_ge, out, kept_index, nullptr, nullptr, stream, strict, nms_all_thr, use_hist);
 }
 
