@@ -316,8 +316,10 @@ int odk_bbox_flip_rot(int batch, int gmax, const double* boxes /*[dev B,Gmax,4]*
                       int32_t* count_out /*[dev B]*/, void* stream);
 
 /* Diagnostics: in-kernel timeline of the seven kernels of a step (candidates, greedy, rows, patch, emit, nms, ignore).
- * buf = 12 device words, word 2*id = earliest CTA entry (initialise to UINT64_MAX), word 2*id+1 = latest CTA exit
- * (initialise to 0), in %globaltimer nanoseconds; NULL switches it off.  Works inside CUDA-graph replays. */
+ * buf = 14 device words, word 2*id = earliest CTA entry (initialise to UINT64_MAX), word 2*id+1 = latest CTA exit
+ * (initialise to 0), in %globaltimer nanoseconds; NULL switches it off.  The pointer is handed to the kernels as a
+ * launch argument (process-wide host state, diagnostics only): a CUDA graph traces what was installed when it was
+ * CAPTURED, so install the buffer before capturing and reset its words between replays. */
 int odk_timeline_set(unsigned long long* buf /*[dev 14] or NULL*/);
 
 /* Measurement aid (bench.py): when enabled for the calling host thread every kernel launch of the

@@ -39,6 +39,7 @@ struct AssignArgs {
   int* ws_list;   // [B, Gmax, list_len] ranked in-cell anchors
   int* ws_ncand;  // [B, Gmax] in-cell valid anchors of the GT
   int* ws_nlist;  // [B, Gmax] entries stored in its ranked list
+  unsigned long long* tl;  // diagnostics timeline or null
   unsigned* ws_ignore;  // [B, bitmap_words] bit a = "pb_mask[a] and some GT has IoU >= 0.5 with anchor a" (pre-zeroed) or null
 };
 
@@ -106,7 +107,7 @@ __device__ __forceinline__ bool cand_less(double c0, int a0, double c1, int a1) 
 constexpr int kCandThreads = 128;
 constexpr int kCandWarps = kCandThreads / 32;
 __global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(const AssignArgs p) {
-  OdkTimeline tl_(ODK_TL_CANDIDATES);
+  OdkTimeline tl_(ODK_TL_CANDIDATES, p.tl);
   __shared__ double s_cost[kCandWarps * kScratch];
   __shared__ int s_idx[kCandWarps * kScratch];
   const int warp = threadIdx.x >> 5;
@@ -174,7 +175,7 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(cons
 // depends on the ranking above and only encode_rows consumes it: the two chains rank -> greedy walk and
 // ignore -> rows run side by side (odk_assign_encode forks at entry) instead of one after the other inside one warp.
 __global__ void __launch_bounds__(kCandThreads, 8) assign_ignore_kernel(const AssignArgs p) {
-  OdkTimeline tl_(ODK_TL_IGNORE);
+  OdkTimeline tl_(ODK_TL_IGNORE, p.tl);
   __shared__ int4 s_geo[kCandWarps * 32];
   __shared__ int s_end[kCandWarps * 32];
   __shared__ int s_nx[kCandWarps * 32];
@@ -260,7 +261,7 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_ignore_kernel(const As
 
 // Phase B: the sequential greedy walk, one CTA per image.
 __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const AssignArgs p) {
-  OdkTimeline tl_(ODK_TL_GREEDY);
+  OdkTimeline tl_(ODK_TL_GREEDY, p.tl);
   extern __shared__ __align__(16) unsigned char greedy_smem[];
   const int warp = threadIdx.x >> 5;
   const int lane = (int)odk_lane();
@@ -530,6 +531,7 @@ static int fill_args(AssignArgs& args, const odk_anchors* a, int batch, const fl
   args.ws_ignore = ignore;
   args.use_walk = 0;
   args.stage_len = 32;
+  args.tl = odk_timeline_ptr();
   return ODK_OK;
 }
 
@@ -650,5 +652,4 @@ extern "C" int odk_encode_locs(const odk_anchors* a, int k, const float* boxes, 
   return ODK_OK;
 }
 
-ODK_TIMELINE_SETTER(odk_timeline_set_assign)
 

@@ -40,6 +40,7 @@ struct DecodeArgs {
   unsigned long long* cand_keys;  // [B, tiles_per_image * TILE]
   int* piece_count;               // [B, tiles_per_image]
   int* score_hist;                // [B, ODK_HIST_BINS] (pre-zeroed) or null
+  unsigned long long* tl;         // diagnostics timeline or null
   int tiles_per_image;
   int pieces_per_image;  // EMIT: candidate pieces per image (32-anchor pieces when a thread owns a row, else one per tile)
   int stages;  // depth of the shared-memory ring
@@ -61,7 +62,7 @@ struct StageLayout {
 // shuffles), so that a tile of few, long rows still fills the CTA with 256 threads.
 template <int TILE, bool DENSE, int SPLIT>
 __global__ void __launch_bounds__(TILE * SPLIT, DENSE ? 1 : (SPLIT > 1 ? 1024 : 1280) / (TILE * SPLIT)) decode_score_kernel(const DecodeArgs p) {
-  OdkTimeline tl_(ODK_TL_EMIT);
+  OdkTimeline tl_(ODK_TL_EMIT, p.tl);
   using L = StageLayout<TILE, DENSE>;
   constexpr int kThreads = TILE * SPLIT;
   const int kStages = p.stages;
@@ -427,6 +428,7 @@ int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, 
                             unsigned long long* cand_keys, int* piece_count, int* score_hist, cudaStream_t stream) {
   DecodeArgs args;
   args.score_hist = score_hist;
+  args.tl = odk_timeline_ptr();
   args.av = odk_view(a);
   args.batch = batch; args.n = a->n; args.c = a->num_classes;
   args.objs = objs; args.clfs = clfs; args.locs = locs;
@@ -483,4 +485,3 @@ int odk_launch_channel_reduce(long long rows, int c, const float* x, long long* 
   return ODK_OK;
 }
 
-ODK_TIMELINE_SETTER(odk_timeline_set_decode)

@@ -48,6 +48,7 @@ struct EncodeArgs {
   int bitmap_words;
   float* y_true;
   uint8_t* pb_valids;      // optional
+  unsigned long long* tl;  // diagnostics timeline or null
 };
 
 constexpr int kRowsThreads = 256;
@@ -117,7 +118,7 @@ __device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, un
 // One CTA per chunk of kRowsThreads * kRowsPerThread pieces: grid (chunks per image, batch).
 template <int VEC>
 __global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeArgs p, unsigned step_rows, unsigned step_cols) {
-  OdkTimeline tl_(ODK_TL_ROWS);
+  OdkTimeline tl_(ODK_TL_ROWS, p.tl);
   encode_rows_chunk<VEC>(p, blockIdx.y, blockIdx.x, step_rows, step_cols);
 }
 
@@ -128,7 +129,7 @@ __global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeA
 template <int VEC>
 __global__ void __launch_bounds__(kRowsThreads) encode_rows_persistent_kernel(const EncodeArgs p, unsigned step_rows, unsigned step_cols,
                                                                              unsigned chunks_per_image, unsigned total_chunks) {
-  OdkTimeline tl_(ODK_TL_ROWS);
+  OdkTimeline tl_(ODK_TL_ROWS, p.tl);
   for (unsigned item = blockIdx.x; item < total_chunks; item += gridDim.x) {
     const unsigned b = item / chunks_per_image;
     encode_rows_chunk<VEC>(p, (int)b, item - b * chunks_per_image, step_rows, step_cols);
@@ -146,6 +147,7 @@ struct PatchArgs {
   const int32_t* status;
   float* y_true;
   uint8_t* pb_valids;
+  unsigned long long* tl;
 };
 
 // The y_true row of a positive: [w0, 1/G, 1, onehot(C), encode_locs] (od_pb.py:307-311); `row` is pre-zeroed.
@@ -165,7 +167,7 @@ __device__ __forceinline__ void write_positive_row(float* row, const AnchorView&
 
 // One CTA per image: the positives (od_pb.py:307-311), or an all-zero image when the assignment failed.
 __global__ void __launch_bounds__(128) encode_patch_kernel(const PatchArgs p) {
-  OdkTimeline tl_(ODK_TL_PATCH);
+  OdkTimeline tl_(ODK_TL_PATCH, p.tl);
   const int b = blockIdx.x;
   const int W = 3 + p.av.num_classes + 4;
   float* y = p.y_true + (size_t)b * p.av.n * W;
@@ -295,7 +297,7 @@ void fill_patch(PatchArgs& q, const odk_anchors* a, int batch, const float* gt_b
   q.gt_classes = gt_classes; q.gt_count = gt_count;
   q.pb_indices = reinterpret_cast<const long long*>(pb_indices);
   q.gt_indices = reinterpret_cast<const long long*>(gt_indices);
-  q.status = status; q.y_true = y_true; q.pb_valids = pb_valids;
+  q.status = status; q.y_true = y_true; q.pb_valids = pb_valids; q.tl = odk_timeline_ptr();
 }
 
 }  // namespace
@@ -326,7 +328,7 @@ extern "C" int odk_assign_encode(const odk_anchors* a, int batch, const float* g
     e.av = odk_view(a);
     e.batch = batch; e.gmax = gmax;
     e.gt_count = gt_count; e.ignore = ignore; e.bitmap_words = words;
-    e.y_true = y_true; e.pb_valids = pb_valids;
+    e.y_true = y_true; e.pb_valids = pb_valids; e.tl = odk_timeline_ptr();
     rc_side = launch_rows(e, a->n, 3 + a->num_classes + 4, lane->stream);
   }
   ODK_CUDA(cudaEventRecord(lane->join, lane->stream));
@@ -377,4 +379,3 @@ extern "C" int odk_assign_encode_compact(const odk_anchors* a, int batch, const 
   return ODK_OK;
 }
 
-ODK_TIMELINE_SETTER(odk_timeline_set_rows)

@@ -106,6 +106,7 @@ struct NmsArgs {
   const unsigned long long* cand_keys;  // [B, n_pieces*piece]
   const int* piece_count;               // [B, n_pieces]
   const int* score_hist;                // [B, ODK_HIST_BINS] per-image score histogram from score_emit, or null
+  unsigned long long* tl;               // diagnostics timeline or null
   const float4* boxes;                  // [B, N] decoded boxes, or null ->
   const float4* locs;                   // [B, N] head output, decoded lazily
   float iou_thr;
@@ -183,7 +184,7 @@ __device__ __forceinline__ unsigned long long block_sort_desc_1(unsigned long lo
 
 template <bool GE, bool STRICT>
 __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs p) {
-  OdkTimeline tl_(ODK_TL_NMS);
+  OdkTimeline tl_(ODK_TL_NMS, p.tl);
   static_assert(kBand <= kNmsThreads && ODK_MAX_CLASSES / 32 <= kNmsThreads, "one band slot / class word per thread");
   extern __shared__ __align__(16) unsigned char nms_smem[];
   __shared__ int s_hist[kBins];
@@ -708,6 +709,7 @@ static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch,
                    cudaStream_t stream, bool strict = false, float iou_thr2 = 0.f, bool have_hist = false) {
   NmsArgs a;
   a.score_hist = have_hist ? w.score_hist : nullptr;
+  a.tl = odk_timeline_ptr();
   if (anchors != nullptr) a.av = odk_view(anchors);
   else memset(&a.av, 0, sizeof(a.av));
   a.n = n; a.piece = piece; a.n_pieces = (n + piece - 1) / piece;
@@ -855,4 +857,3 @@ extern "C" int odk_nms(const float* boxes, const float* scores, int n, int top_k
                  out_index, out_count, stream);
 }
 
-ODK_TIMELINE_SETTER(odk_timeline_set_nms)

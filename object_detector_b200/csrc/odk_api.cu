@@ -81,15 +81,11 @@ extern "C" int odk_profile_read(char* names, int name_stride, float* total_ms, i
   return ODK_OK;
 }
 
-int odk_timeline_set_rows(unsigned long long*);
-int odk_timeline_set_assign(unsigned long long*);
-int odk_timeline_set_decode(unsigned long long*);
-int odk_timeline_set_nms(unsigned long long*);
+static unsigned long long* g_timeline = nullptr;  // process-wide, diagnostics only (include/odk.h, Conventions)
+unsigned long long* odk_timeline_ptr() { return g_timeline; }
 extern "C" int odk_timeline_set(unsigned long long* buf) {
-  if (int rc = odk_timeline_set_rows(buf)) return rc;
-  if (int rc = odk_timeline_set_assign(buf)) return rc;
-  if (int rc = odk_timeline_set_decode(buf)) return rc;
-  return odk_timeline_set_nms(buf);
+  g_timeline = buf;
+  return ODK_OK;
 }
 
 extern "C" const char* odk_version(void) { return "odk 0.1.0 (sm_100a)"; }

@@ -226,22 +226,24 @@ inline cudaError_t odk_launch_high(void (*kern)(KArgs...), dim3 grid, dim3 block
 
 // ---- optional in-kernel timeline (odk_timeline_set; diagnostics for overlapping launches inside a CUDA graph) --------
 // When a buffer is installed, thread 0 of every CTA of an instrumented kernel records %globaltimer (ns) at entry
-// (atomicMin into slot 2*id) and at exit (atomicMax into slot 2*id+1).  One copy of the pointer per translation unit.
-static __device__ unsigned long long* odk_tl_buf = nullptr;
-#define ODK_TIMELINE_SETTER(fn) \
-  int fn(unsigned long long* buf) { ODK_CUDA(cudaMemcpyToSymbol(odk_tl_buf, &buf, sizeof(buf))); return ODK_OK; }
+// (atomicMin into slot 2*id) and at exit (atomicMax into slot 2*id+1).  The pointer travels in the kernel arguments
+// (constant bank: no load on the product path when it is null; a __device__ global cost every CTA an L2 round trip at
+// entry — 20 % of the stall samples of encode_rows).  Kernel arguments are fixed at capture time: install the buffer
+// before capturing a CUDA graph that should be traced.
+unsigned long long* odk_timeline_ptr();  // host: the installed buffer or null (odk_api.cu)
 struct OdkTimeline {
   int id_;
+  unsigned long long* buf_;
   __device__ __forceinline__ static unsigned long long now() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
   }
-  __device__ __forceinline__ explicit OdkTimeline(int id) : id_(id) {
-    if (threadIdx.x == 0 && odk_tl_buf != nullptr) atomicMin(odk_tl_buf + 2 * id_, now());
+  __device__ __forceinline__ OdkTimeline(int id, unsigned long long* buf) : id_(id), buf_(buf) {
+    if (buf_ != nullptr && threadIdx.x == 0) atomicMin(buf_ + 2 * id_, now());
   }
   __device__ __forceinline__ ~OdkTimeline() {
-    if (threadIdx.x == 0 && odk_tl_buf != nullptr) atomicMax(odk_tl_buf + 2 * id_ + 1, now());
+    if (buf_ != nullptr && threadIdx.x == 0) atomicMax(buf_ + 2 * id_ + 1, now());
   }
 };
 enum { ODK_TL_CANDIDATES = 0, ODK_TL_GREEDY = 1, ODK_TL_ROWS = 2, ODK_TL_PATCH = 3, ODK_TL_EMIT = 4, ODK_TL_NMS = 5, ODK_TL_IGNORE = 6,
