@@ -59,134 +59,135 @@ struct StageLayout {
 };
 
 // SPLIT threads share one anchor row (wide class vectors: each scans 1/SPLIT of the classes, the group merges by
-// shuffles), so that a tile of few, long rows still fills the CTA with 256 threads.
+// shuffles), so that a tile of few, long rows still fills the CTA with 256 consumer threads.
+//
+// Warp roles: kWarps consumer warps (TILE * SPLIT threads) + ONE producer warp.  The producer refills a ring slot the
+// moment every consumer warp has released it (per-slot "empty" mbarrier, one arrival per consumer warp) — no CTA-wide
+// barrier sits between a slot becoming free and its refill, and a consumer warp that is done with its 32 rows moves on
+// to the next tile without waiting for the slowest warp of the CTA.
 template <int TILE, bool DENSE, int SPLIT>
-__global__ void __launch_bounds__(TILE * SPLIT, DENSE ? 1 : (SPLIT > 1 ? 1024 : 1280) / (TILE * SPLIT)) decode_score_kernel(const DecodeArgs p) {
+__global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 1024 : 1280) / (TILE * SPLIT)) decode_score_kernel(const DecodeArgs p) {
   OdkTimeline tl_(ODK_TL_EMIT, p.tl);
   using L = StageLayout<TILE, DENSE>;
-  constexpr int kThreads = TILE * SPLIT;
+  constexpr int kThreads = TILE * SPLIT;  // consumer threads
   const int kStages = p.stages;
-  constexpr int kWarps = kThreads / 32;
+  constexpr int kWarps = kThreads / 32;   // consumer warps; warp kWarps is the producer
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int c = p.c;
   const size_t clf_bytes = (size_t)TILE * c * 4;
   const size_t stage_bytes = clf_bytes + L::kTail;
   __shared__ uint64_t full_bar[L::kMaxStages];
+  __shared__ uint64_t empty_bar[L::kMaxStages];
   __shared__ int s_wcnt[2][kWarps];
 
   const int total_tiles = p.batch * p.tiles_per_image;  // < 2^31 (checked by the launcher): 32-bit tile arithmetic
   const int tid = threadIdx.x;
-  const int row_id = tid / SPLIT, part = tid % SPLIT;  // SPLIT consecutive lanes own one anchor row
+  const int warp = tid >> 5;
+  const unsigned lane = odk_lane();
 
   if (tid == 0) {
-    for (int s = 0; s < kStages; ++s) odk_mbar_init(&full_bar[s], 1);
+    for (int s = 0; s < kStages; ++s) {
+      odk_mbar_init(&full_bar[s], 1);
+      odk_mbar_init(&empty_bar[s], kWarps);
+    }
     odk_mbar_fence_init();
   }
   __syncthreads();
 
   auto stage_ptr = [&](int s) { return smem_raw + (size_t)s * stage_bytes; };
 
-  // Issue the loads of tile `t` into ring slot `s`.  Completion is signalled on the mbarrier in both paths.
-  // `sp`: lanes 0..ODK_MAX_SPANS-1 of warp 0 hold the tile's span words (use_spans only; fetched ahead of time so that no
-  // global load sits between a ring slot becoming free and its refill)
-  auto issue = [&](int t, int s, uint32_t sp) {
-    const int b = t / p.tiles_per_image;
-    const int a0 = (t - b * p.tiles_per_image) * TILE;
-    const int rows = min(TILE, p.n - a0);
-    const size_t row0 = (size_t)b * p.n + a0;
-    const float* src_clf = p.clfs + row0 * c;
-    const float* src_obj = p.objs + row0;
-    const float* src_loc = DENSE ? p.locs + row0 * 4 : nullptr;
-    unsigned char* dst = stage_ptr(s);
-    unsigned char* tail = dst + clf_bytes;
-    bool tma_ok = ((rows & 15) == 0) && ((((uintptr_t)src_clf | (uintptr_t)src_obj) & 15) == 0);
-    if (DENSE) tma_ok = tma_ok && (((uintptr_t)src_loc & 15) == 0);
-    if (tma_ok) {
-      if (!DENSE && p.use_spans) {
-        // warp 0: lane k < ODK_MAX_SPANS fetches the k-th run of valid rows of the tile, lanes 8 / 9 the objectness and
-        // pb_mask slabs of the whole tile.  Rows between the runs are never read from HBM (their pb_mask is 0, so
-        // conf = x * 0 cannot pass conf_thr >= 0) and never looked at below.
-        if (tid < 32) {
+  if (warp == kWarps) {
+    // =========================================== producer warp ===========================================
+    const bool span_lane = !DENSE && p.use_spans && lane < ODK_MAX_SPANS;
+    auto span_word = [&](int t) -> uint32_t {
+      return (span_lane && t < total_tiles) ? __ldg(p.av.spans + (size_t)(t % p.tiles_per_image) * ODK_MAX_SPANS + lane) : 0u;
+    };
+    int slot = 0, fill = 0;  // `fill`: how many times the ring has wrapped (the producer waits for release number fill - 1)
+    uint32_t sp = span_word((int)blockIdx.x);
+    for (int t = (int)blockIdx.x; t < total_tiles; t += (int)gridDim.x) {
+      // span words of the NEXT tile are fetched before this tile's slot is waited for: no global load between a slot
+      // becoming free and its refill
+      const uint32_t sp_next = span_word(t + (int)gridDim.x);
+      if (fill > 0) odk_mbar_wait(&empty_bar[slot], (uint32_t)(fill - 1) & 1u);
+      const int b = t / p.tiles_per_image;
+      const int a0 = (t - b * p.tiles_per_image) * TILE;
+      const int rows = min(TILE, p.n - a0);
+      const size_t row0 = (size_t)b * p.n + a0;
+      const float* src_clf = p.clfs + row0 * c;
+      const float* src_obj = p.objs + row0;
+      const float* src_loc = DENSE ? p.locs + row0 * 4 : nullptr;
+      unsigned char* dst = stage_ptr(slot);
+      unsigned char* tail = dst + clf_bytes;
+      bool tma_ok = ((rows & 15) == 0) && ((((uintptr_t)src_clf | (uintptr_t)src_obj) & 15) == 0);
+      if (DENSE) tma_ok = tma_ok && (((uintptr_t)src_loc & 15) == 0);
+      const uint32_t r = (uint32_t)rows;
+      if (tma_ok) {
+        const uint64_t pol = odk_policy_evict_first();  // head outputs are read exactly once
+        if (!DENSE && p.use_spans) {
+          // lane k < ODK_MAX_SPANS fetches the k-th run of valid rows of the tile, lanes 8 / 9 the objectness and pb_mask
+          // slabs of the whole tile.  Rows between the runs are never read from HBM (their pb_mask is 0, so
+          // conf = x * 0 cannot pass conf_thr >= 0) and never looked at by the consumers.
           const uint32_t first = sp >> 16, len = sp & 0xffffu;
           uint32_t bytes = len * (uint32_t)c * 4u, tot = bytes;
 #pragma unroll
           for (int d = 1; d < ODK_MAX_SPANS; d <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, d);  // lanes 0..7 hold the sum
-          const uint32_t r = (uint32_t)rows;
-          if (tid == 0) odk_mbar_expect_tx(&full_bar[s], tot + r * 4 + r);
+          if (lane == 0) odk_mbar_expect_tx(&full_bar[slot], tot + r * 4 + r);
           __syncwarp();
-          const uint64_t pol = odk_policy_evict_first();
-          if (len) odk_bulk_g2s_stream(dst + (size_t)first * c * 4, src_clf + (size_t)first * c, bytes, &full_bar[s], pol);
-          if (tid == 8) odk_bulk_g2s_stream(tail + L::kOffObj, src_obj, r * 4, &full_bar[s], pol);
-          if (tid == 9) odk_bulk_g2s(tail + L::kOffAMask, p.av.mask + a0, r, &full_bar[s]);
-        }
-      } else if (tid == 0) {
-        const uint32_t r = (uint32_t)rows;
-        odk_mbar_expect_tx(&full_bar[s], r * c * 4 + r * 4 + r + (DENSE ? r * 16 + r * 16 + r * 8 : 0));
-        if (p.stream_hint) {
-          const uint64_t pol = odk_policy_evict_first();
-          odk_bulk_g2s_stream(dst, src_clf, r * c * 4, &full_bar[s], pol);
-          odk_bulk_g2s_stream(tail + L::kOffObj, src_obj, r * 4, &full_bar[s], pol);
+          if (len) odk_bulk_g2s_stream(dst + (size_t)first * c * 4, src_clf + (size_t)first * c, bytes, &full_bar[slot], pol);
+          if (lane == 8) odk_bulk_g2s_stream(tail + L::kOffObj, src_obj, r * 4, &full_bar[slot], pol);
+          if (lane == 9) odk_bulk_g2s(tail + L::kOffAMask, p.av.mask + a0, r, &full_bar[slot]);
         } else {
-          odk_bulk_g2s(dst, src_clf, r * c * 4, &full_bar[s]);
-          odk_bulk_g2s(tail + L::kOffObj, src_obj, r * 4, &full_bar[s]);
+          if (lane == 0) odk_mbar_expect_tx(&full_bar[slot], r * c * 4 + r * 4 + r + (DENSE ? r * 16 + r * 16 + r * 8 : 0));
+          __syncwarp();
+          if (lane == 0) {
+            if (p.stream_hint) odk_bulk_g2s_stream(dst, src_clf, r * c * 4, &full_bar[slot], pol);
+            else odk_bulk_g2s(dst, src_clf, r * c * 4, &full_bar[slot]);
+          }
+          if (lane == 1) {
+            if (p.stream_hint) odk_bulk_g2s_stream(tail + L::kOffObj, src_obj, r * 4, &full_bar[slot], pol);
+            else odk_bulk_g2s(tail + L::kOffObj, src_obj, r * 4, &full_bar[slot]);
+          }
+          if (lane == 2) odk_bulk_g2s(tail + L::kOffAMask, p.av.mask + a0, r, &full_bar[slot]);  // anchor tables are L2-resident
+          if (DENSE) {
+            if (lane == 3) odk_bulk_g2s(tail + L::kOffLoc, src_loc, r * 16, &full_bar[slot]);
+            if (lane == 4) odk_bulk_g2s(tail + L::kOffALoc, p.av.locs + a0, r * 16, &full_bar[slot]);
+            if (lane == 5) odk_bulk_g2s(tail + L::kOffAScale, p.av.scale + a0, r * 8, &full_bar[slot]);
+          }
         }
-        odk_bulk_g2s(tail + L::kOffAMask, p.av.mask + a0, r, &full_bar[s]);  // anchor tables are L2-resident
+      } else {
+        // tiles whose source addresses / sizes are not 16-byte multiples: plain loads by the producer warp
+        float* d0 = reinterpret_cast<float*>(dst);
+        float* d2 = reinterpret_cast<float*>(tail + L::kOffObj);
+        unsigned char* d5 = tail + L::kOffAMask;
+        for (int i = (int)lane; i < rows * c; i += 32) d0[i] = __ldg(src_clf + i);
+        for (int i = (int)lane; i < rows; i += 32) {
+          d2[i] = __ldg(src_obj + i);
+          d5[i] = p.av.mask[a0 + i];
+        }
         if (DENSE) {
-          odk_bulk_g2s(tail + L::kOffLoc, src_loc, r * 16, &full_bar[s]);
-          odk_bulk_g2s(tail + L::kOffALoc, p.av.locs + a0, r * 16, &full_bar[s]);
-          odk_bulk_g2s(tail + L::kOffAScale, p.av.scale + a0, r * 8, &full_bar[s]);
+          float* d1 = reinterpret_cast<float*>(tail + L::kOffLoc);
+          float4* d3 = reinterpret_cast<float4*>(tail + L::kOffALoc);
+          float2* d4 = reinterpret_cast<float2*>(tail + L::kOffAScale);
+          for (int i = (int)lane; i < rows * 4; i += 32) d1[i] = __ldg(src_loc + i);
+          for (int i = (int)lane; i < rows; i += 32) {
+            d3[i] = __ldg(p.av.locs + a0 + i);
+            d4[i] = __ldg(p.av.scale + a0 + i);
+          }
         }
+        __syncwarp();  // the warp's plain stores are ordered before the (releasing) arrive below
+        if (lane == 0) odk_mbar_arrive(&full_bar[slot]);
       }
-    } else {
-      float* d0 = reinterpret_cast<float*>(dst);
-      float* d2 = reinterpret_cast<float*>(tail + L::kOffObj);
-      unsigned char* d5 = tail + L::kOffAMask;
-      for (int i = tid; i < rows * c; i += kThreads) d0[i] = __ldg(src_clf + i);
-      for (int i = tid; i < rows; i += kThreads) {
-        d2[i] = __ldg(src_obj + i);
-        d5[i] = p.av.mask[a0 + i];
-      }
-      if (DENSE) {
-        float* d1 = reinterpret_cast<float*>(tail + L::kOffLoc);
-        float4* d3 = reinterpret_cast<float4*>(tail + L::kOffALoc);
-        float2* d4 = reinterpret_cast<float2*>(tail + L::kOffAScale);
-        for (int i = tid; i < rows * 4; i += kThreads) d1[i] = __ldg(src_loc + i);
-        for (int i = tid; i < rows; i += kThreads) {
-          d3[i] = __ldg(p.av.locs + a0 + i);
-          d4[i] = __ldg(p.av.scale + a0 + i);
-        }
-      }
-      __syncthreads();  // plain stores visible before the single arrive below
-      if (tid == 0) odk_mbar_arrive(&full_bar[s]);
+      sp = sp_next;
+      if (++slot == kStages) { slot = 0; ++fill; }
     }
-  };
-
-  // prologue: fill the ring
-  const bool span_lane = !DENSE && p.use_spans && tid < ODK_MAX_SPANS;
-  auto span_word = [&](int t) -> uint32_t {
-    return (span_lane && t < total_tiles) ? __ldg(p.av.spans + (size_t)(t % p.tiles_per_image) * ODK_MAX_SPANS + tid) : 0u;
-  };
-  // (tile indices stay below total_tiles + (stages + 1) * gridDim.x < 2^31: checked by the launcher)
-  int t_issue = (int)blockIdx.x;
-  {
-    constexpr int kPre = 3;  // ring slots whose span words are fetched together before the first copy is issued
-    uint32_t sp0[kPre];
-#pragma unroll
-    for (int s = 0; s < kPre; ++s) sp0[s] = (s < kStages) ? span_word(t_issue + s * (int)gridDim.x) : 0u;
-#pragma unroll
-    for (int s = 0; s < kPre; ++s)
-      if (s < kStages) {
-        if (t_issue < total_tiles) issue(t_issue, s, sp0[s]);
-        t_issue += (int)gridDim.x;
-      }
-    for (int s = kPre; s < kStages; ++s, t_issue += (int)gridDim.x)
-      if (t_issue < total_tiles) issue(t_issue, s, span_word(t_issue));
+    return;
   }
 
+  // ============================================= consumer warps =============================================
+  const int row_id = tid / SPLIT, part = tid % SPLIT;  // SPLIT consecutive lanes own one anchor row
   int slot = 0, buf = 0;
   uint32_t phase = 0;
-  for (int t = (int)blockIdx.x; t < total_tiles; t += (int)gridDim.x) {  // t + gridDim.x <= total_tiles + grid < 2^31
-    const uint32_t sp_next = span_word(t_issue);  // for the refill of this slot further down; lands while the tile is processed
+  for (int t = (int)blockIdx.x; t < total_tiles; t += (int)gridDim.x) {
     odk_mbar_wait(&full_bar[slot], phase);
     const int b = t / p.tiles_per_image;
     const int tile = t - b * p.tiles_per_image;
@@ -199,6 +200,7 @@ __global__ void __launch_bounds__(TILE * SPLIT, DENSE ? 1 : (SPLIT > 1 ? 1024 : 
 
     int cls = 0;
     float conf = 0.0f;
+    float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
     const int a = a0 + row_id;
     const bool owner = part == 0 && row_id < rows;
     {
@@ -213,7 +215,7 @@ __global__ void __launch_bounds__(TILE * SPLIT, DENSE ? 1 : (SPLIT > 1 ? 1024 : 
           // need few of them: the maximum of a float4 chunk costs two min/max instructions (FMNMX3 + FMNMX), the running
           // best one compare and two selects per CHUNK, and the position inside the winning chunk is looked up once at
           // the end.  "First maximum wins" (np.argmax): a later chunk replaces the best only if strictly greater, and
-          // inside the chunk the first element equal to the maximum is taken.  NaNs never win a comparison (as before).
+          // inside the chunk the first element equal to the maximum is taken.  NaNs never win a comparison.
           const int nchunk = c >> 2, per = (nchunk + SPLIT - 1) / SPLIT;
           const int j0 = part * per, j1 = min(nchunk, j0 + per);
           const float4* row4 = reinterpret_cast<const float4*>(row);
@@ -252,29 +254,29 @@ __global__ void __launch_bounds__(TILE * SPLIT, DENSE ? 1 : (SPLIT > 1 ? 1024 : 
         const float maskf = s_amask[row_id] ? 1.0f : 0.0f;
         conf = __fmul_rn(__fmul_rn(s_obj[row_id], best), maskf);  // (objs*confs)*pb_mask, od_net.py:183-184
       }
-    }
-    if (DENSE) {
-      if (owner) {
+      if (DENSE && owner) {
         const float4* s_loc = reinterpret_cast<const float4*>(st + clf_bytes + L::kOffLoc);
         const float4* s_aloc = reinterpret_cast<const float4*>(st + clf_bytes + L::kOffALoc);
         const float2* s_ascale = reinterpret_cast<const float2*>(st + clf_bytes + L::kOffAScale);
-        const float4 box = odk_decode_box(s_loc[row_id], s_aloc[row_id], s_ascale[row_id]);
+        box = odk_decode_box(s_loc[row_id], s_aloc[row_id], s_ascale[row_id]);
+      }
+    }
+    // this warp's rows are in registers: release the ring slot (one arrival per consumer warp)
+    __syncwarp();
+    if (lane == 0) odk_mbar_arrive(&empty_bar[slot]);
+
+    if (DENSE) {
+      if (owner) {
         const size_t r = (size_t)b * p.n + a;
         p.classes[r] = cls;
         p.confs[r] = conf;
         p.boxes[r] = box;
       }
-      __syncthreads();  // every thread is done with ring slot `slot`
-      if (t_issue < total_tiles) issue(t_issue, slot, 0u);
     } else {
       const bool is_cand = owner && (conf > p.conf_thr);
       const unsigned m = __ballot_sync(0xffffffffu, is_cand);
-      const unsigned lane = odk_lane();
-      const int warp = tid >> 5;
       if (SPLIT == 1) {
         // a warp owns 32 consecutive anchors = one candidate piece: compaction needs no cross-warp scan
-        __syncthreads();  // ring slot free (all rows are in registers)
-        if (t_issue < total_tiles) issue(t_issue, slot, sp_next);
         const int piece_in_image = tile * kWarps + warp;
         if (piece_in_image < p.pieces_per_image) {
           const size_t piece = (size_t)b * p.pieces_per_image + piece_in_image;
@@ -286,8 +288,7 @@ __global__ void __launch_bounds__(TILE * SPLIT, DENSE ? 1 : (SPLIT > 1 ? 1024 : 
         }
       } else {
         if (lane == 0) s_wcnt[buf][warp] = __popc(m);
-        __syncthreads();  // ring slot free (all rows are in registers) + warp counts visible
-        if (t_issue < total_tiles) issue(t_issue, slot, sp_next);
+        asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory");  // consumer warps only: warp counts visible
         int base = 0, total = 0;
 #pragma unroll
         for (int w = 0; w < kWarps; ++w) {
@@ -304,7 +305,6 @@ __global__ void __launch_bounds__(TILE * SPLIT, DENSE ? 1 : (SPLIT > 1 ? 1024 : 
         buf ^= 1;  // the next tile's counts go to the other buffer; this one is rewritten two barriers later
       }
     }
-    t_issue += (int)gridDim.x;
     if (++slot == kStages) { slot = 0; phase ^= 1u; }
   }
 }
@@ -393,7 +393,7 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   const long long total = (long long)args.batch * args.tiles_per_image;
   ODK_REQUIRE(total + 16 * 2048 * 10 < 0x7fffffffLL, ODK_ERR_UNSUPPORTED, "decode_score: %lld tiles", total);
   int per_sm = (int)((220 * 1024) / (smem + 1024));
-  per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / (TILE * SPLIT) ? 2048 / (TILE * SPLIT) : per_sm);
+  per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / (TILE * SPLIT + 32) ? 2048 / (TILE * SPLIT + 32) : per_sm);
   // EMIT runs beside the train-side kernels of the same step (other graph branch): leave them shared memory
   if (!DENSE && per_sm > 3) per_sm = 3;
   if (!DENSE && env_per_sm > 0) per_sm = env_per_sm;
@@ -402,7 +402,7 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   if (grid < 1) grid = 1;
   {
     OdkProfileScope prof_(DENSE ? "decode_score_kernel" : "score_emit_kernel", stream);
-    kern<<<(unsigned)grid, TILE * SPLIT, smem, stream>>>(args);
+    kern<<<(unsigned)grid, TILE * SPLIT + 32, smem, stream>>>(args);
   }
   ODK_LAUNCH_CHECK(DENSE ? "decode_score_kernel" : "score_emit_kernel");
   return ODK_OK;
