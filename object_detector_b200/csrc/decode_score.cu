@@ -42,7 +42,7 @@ struct DecodeArgs {
   int* score_hist;                // [B, ODK_HIST_BINS] (pre-zeroed) or null
   unsigned long long* tl;         // diagnostics timeline or null
   int tiles_per_image;
-  int pieces_per_image;  // EMIT: candidate pieces per image (32-anchor pieces when a thread owns a row, else one per tile)
+  int pieces_per_image;  // EMIT: candidate pieces per image (one per tile)
   int stages;  // depth of the shared-memory ring
   int stream_hint;  // 1: head outputs are fetched with an L2 evict-first policy
   int use_spans;    // EMIT: fetch only the runs of valid anchors of a tile (av.spans); rows outside them have pb_mask = 0
@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
   const size_t stage_bytes = clf_bytes + L::kTail;
   __shared__ uint64_t full_bar[L::kMaxStages];
   __shared__ uint64_t empty_bar[L::kMaxStages];
-  __shared__ int s_wcnt[2][kWarps];
+  __shared__ unsigned s_ctr[L::kMaxStages];  // EMIT: per ring slot, (consumer warps arrived << 16) | candidates so far
 
   const int total_tiles = p.batch * p.tiles_per_image;  // < 2^31 (checked by the launcher): 32-bit tile arithmetic
   const int tid = threadIdx.x;
@@ -89,6 +89,7 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
     for (int s = 0; s < kStages; ++s) {
       odk_mbar_init(&full_bar[s], 1);
       odk_mbar_init(&empty_bar[s], kWarps);
+      s_ctr[s] = 0u;
     }
     odk_mbar_fence_init();
   }
@@ -185,7 +186,7 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
 
   // ============================================= consumer warps =============================================
   const int row_id = tid / SPLIT, part = tid % SPLIT;  // SPLIT consecutive lanes own one anchor row
-  int slot = 0, buf = 0;
+  int slot = 0;
   uint32_t phase = 0;
   for (int t = (int)blockIdx.x; t < total_tiles; t += (int)gridDim.x) {
     odk_mbar_wait(&full_bar[slot], phase);
@@ -261,11 +262,10 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
         box = odk_decode_box(s_loc[row_id], s_aloc[row_id], s_ascale[row_id]);
       }
     }
-    // this warp's rows are in registers: release the ring slot (one arrival per consumer warp)
-    __syncwarp();
-    if (lane == 0) odk_mbar_arrive(&empty_bar[slot]);
-
     if (DENSE) {
+      // this warp's rows are in registers: release the ring slot (one arrival per consumer warp)
+      __syncwarp();
+      if (lane == 0) odk_mbar_arrive(&empty_bar[slot]);
       if (owner) {
         const size_t r = (size_t)b * p.n + a;
         p.classes[r] = cls;
@@ -273,36 +273,27 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
         p.boxes[r] = box;
       }
     } else {
+      // Candidates of the tile are compacted to the front of the tile's slab without a CTA-wide barrier: every consumer
+      // warp adds (its count | one arrival) to the slot's packed shared-memory counter with ONE atomic and gets its base
+      // offset back; the warp that arrives last knows the tile's total, publishes it and clears the counter — all before
+      // it releases the ring slot, so the counter is clean when the slot's next tile starts.  The order of the warps
+      // inside a slab varies from run to run; the NMS kernel sorts the keys, so results do not depend on it.
       const bool is_cand = owner && (conf > p.conf_thr);
       const unsigned m = __ballot_sync(0xffffffffu, is_cand);
-      if (SPLIT == 1) {
-        // a warp owns 32 consecutive anchors = one candidate piece: compaction needs no cross-warp scan
-        const int piece_in_image = tile * kWarps + warp;
-        if (piece_in_image < p.pieces_per_image) {
-          const size_t piece = (size_t)b * p.pieces_per_image + piece_in_image;
-          if (is_cand) {
-            p.cand_keys[piece * 32 + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
-            if (p.score_hist != nullptr) atomicAdd(p.score_hist + (size_t)b * ODK_HIST_BINS + odk_score_bin(conf), 1);
-          }
-          if (lane == 0) p.piece_count[piece] = __popc(m);
-        }
-      } else {
-        if (lane == 0) s_wcnt[buf][warp] = __popc(m);
-        asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory");  // consumer warps only: warp counts visible
-        int base = 0, total = 0;
-#pragma unroll
-        for (int w = 0; w < kWarps; ++w) {
-          const int v = s_wcnt[buf][w];
-          base += (w < warp) ? v : 0;
-          total += v;
-        }
-        const size_t piece = (size_t)b * p.tiles_per_image + tile;
-        if (is_cand) {
-          p.cand_keys[piece * TILE + base + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
-          if (p.score_hist != nullptr) atomicAdd(p.score_hist + (size_t)b * ODK_HIST_BINS + odk_score_bin(conf), 1);
-        }
-        if (tid == 0) p.piece_count[piece] = total;
-        buf ^= 1;  // the next tile's counts go to the other buffer; this one is rewritten two barriers later
+      unsigned old = 0;
+      if (lane == 0) old = atomicAdd(&s_ctr[slot], (unsigned)__popc(m) | (1u << 16));
+      old = __shfl_sync(0xffffffffu, old, 0);
+      const unsigned base = old & 0xffffu;
+      const size_t piece = (size_t)b * p.tiles_per_image + tile;
+      if ((old >> 16) == (unsigned)(kWarps - 1) && lane == 0) {
+        s_ctr[slot] = 0u;
+        p.piece_count[piece] = (int)(base + __popc(m));
+      }
+      __syncwarp();
+      if (lane == 0) odk_mbar_arrive(&empty_bar[slot]);  // rows in registers, counter settled: release the ring slot
+      if (is_cand) {
+        p.cand_keys[piece * TILE + base + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
+        if (p.score_hist != nullptr) atomicAdd(p.score_hist + (size_t)b * ODK_HIST_BINS + odk_score_bin(conf), 1);
       }
     }
     if (++slot == kStages) { slot = 0; phase ^= 1u; }
@@ -381,21 +372,22 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   static const int env_spans = getenv("ODK_EMIT_SPANS") ? atoi(getenv("ODK_EMIT_SPANS")) : 1;
   args.use_spans = (!DENSE && env_spans && (args.c & 3) == 0 && args.av.spans != nullptr && args.av.span_tile == TILE &&
                     args.conf_thr >= 0.0f) ? 1 : 0;
-  // EMIT: a 2-deep ring at 3 CTAs per SM (3 x 43 KB at C = 20).  Same shared memory per SM as 2 CTAs x 3 stages, but the
-  // smaller CTAs still fit two at a time beside a per-image NMS CTA (~120 KB) of another batch in flight
-  // (profiles/emit_sweep_r01i.log: step 46.3 -> 45.5 us, the kernel 26.3 -> 24.1 us).
-  args.stages = (!DENSE && env_stages >= 2 && env_stages <= L::kMaxStages) ? env_stages : (DENSE ? 3 : 2);
+  // EMIT: a 3-deep ring at 2 CTAs per SM (2 x 65 KB at C = 20).  With the producer warp refilling a slot as soon as its
+  // consumers release it, depth pays off (profiles/sweep_r02d.log: step 44.5 us at 2 deep x 3 CTAs, 43.6 us at
+  // 3 deep x 2 CTAs, same shared memory per SM) and two CTAs per SM leave threads and registers to the kernels of the
+  // other batches in flight.
+  args.stages = (!DENSE && env_stages >= 2 && env_stages <= L::kMaxStages) ? env_stages : 3;
   const size_t smem = L::stage_bytes(args.c) * args.stages;
   auto kern = decode_score_kernel<TILE, DENSE, SPLIT>;
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   args.tiles_per_image = (args.n + TILE - 1) / TILE;
-  args.pieces_per_image = SPLIT == 1 ? (args.n + 31) / 32 : args.tiles_per_image;
+  args.pieces_per_image = args.tiles_per_image;
   const long long total = (long long)args.batch * args.tiles_per_image;
   ODK_REQUIRE(total + 16 * 2048 * 10 < 0x7fffffffLL, ODK_ERR_UNSUPPORTED, "decode_score: %lld tiles", total);
   int per_sm = (int)((220 * 1024) / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / (TILE * SPLIT + 32) ? 2048 / (TILE * SPLIT + 32) : per_sm);
   // EMIT runs beside the train-side kernels of the same step (other graph branch): leave them shared memory
-  if (!DENSE && per_sm > 3) per_sm = 3;
+  if (!DENSE && per_sm > 2) per_sm = 2;
   if (!DENSE && env_per_sm > 0) per_sm = env_per_sm;
   long long grid = (long long)sm_count_cached() * per_sm;
   if (grid > total) grid = total;
@@ -418,9 +410,8 @@ int odk_piece_size(int num_classes) {
   return num_classes <= 32 ? 256 : (num_classes <= 96 ? 64 : 32);
 }
 
-// Height of the candidate pieces score_emit writes (the NMS workspace layout depends on it): a warp's 32 anchors where a
-// thread owns a whole row (C <= 32), else the tile.
-int odk_emit_piece_size(int num_classes) { return num_classes <= 32 ? 32 : odk_piece_size(num_classes); }
+// Height of the candidate pieces score_emit writes (the NMS workspace layout depends on it): the tile.
+int odk_emit_piece_size(int num_classes) { return odk_piece_size(num_classes); }
 
 // Internal entry used by odk_decode_score (dense) and odk_decode_nms (emit).
 int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, const float* clfs, const float* locs,
