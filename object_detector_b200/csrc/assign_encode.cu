@@ -19,6 +19,7 @@
 #include <float.h>
 
 #include "odk_common.cuh"
+#include "odk_sort.cuh"
 
 namespace {
 
@@ -33,7 +34,7 @@ struct AssignArgs {
   long long* gt_indices;
   int32_t* status;
   int list_len;  // ranked candidates remembered per GT
-  int use_walk;  // greedy kernel: the first 32 ranks of every GT are regrouped in walk order (shared memory permitting)
+  int use_walk;  // greedy kernel: 1 = the first ranks of every list are staged in shared memory before the transposition
   int stage_len; // greedy kernel: ranks of every GT staged in shared memory (the rest is read from the workspace on demand)
   int bitmap_words;
   int* ws_list;   // [B, Gmax, list_len] ranked in-cell anchors
@@ -259,7 +260,18 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_ignore_kernel(const As
   }
 }
 
-// Phase B: the sequential greedy walk, one CTA per image.
+// Phase B: the greedy walk, one CTA per image.
+//
+// The reference's loop is sequential — GT r takes the best anchor no earlier GT took — but consecutive GTs rarely
+// compete for the same anchor, so the walk is OPTIMISTIC: warp 0 looks at 32 consecutive GTs at once (a lane each);
+// every lane finds the first anchor of its own ranked list that is free in the bitmap as it stood before the batch;
+// lanes whose choice collides with that of an earlier lane of the batch are found with one match.any, and the lanes
+// in front of the first collision commit together (their choices are pairwise distinct and none of them was free-ed
+// or taken in between, so each is exactly what the sequential loop would have picked).  The batch then restarts at the
+// colliding GT, which re-reads the bitmap.  A crowded image degenerates to one GT per step, as before.
+//
+// Shared-memory layout of what the walk reads: walk_t[k][r] = rank-k anchor of the r-th GT of the walk (rank-major,
+// row stride odd: lanes = consecutive r are conflict-free, and so is the transposing store), -1 beyond the list.
 __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const AssignArgs p) {
   OdkTimeline tl_(ODK_TL_GREEDY, p.tl);
   extern __shared__ __align__(16) unsigned char greedy_smem[];
@@ -269,16 +281,18 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   const int L = p.list_len;
   unsigned char* sp = greedy_smem;
   const int SL = p.stage_len;  // 32: the ranks the fast path looks at; deeper ranks (crowded images) come from the workspace
+  const int Gp = p.gmax | 1;   // row stride of walk_t (odd)
   const int* glist = p.ws_list + (size_t)b * p.gmax * L;
   float4* gbox = reinterpret_cast<float4*>(sp);            sp += (size_t)p.gmax * 16;
-  int* list = reinterpret_cast<int*>(sp);                  sp += (size_t)p.gmax * SL * 4;  // 16-byte aligned (SL % 8 == 0)
+  int* list = reinterpret_cast<int*>(sp);                  sp += p.use_walk ? (size_t)p.gmax * SL * 4 : 0;  // 16-byte aligned (SL % 8 == 0)
   float* garea = reinterpret_cast<float*>(sp);             sp += (size_t)p.gmax * 4;
   int* order = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
   int* pick = reinterpret_cast<int*>(sp);                  sp += (size_t)p.gmax * 4;
   int* ncand = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
   int* nlist = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
-  unsigned* taken = reinterpret_cast<unsigned*>(sp);                sp += (size_t)p.bitmap_words * 4;
-  int* walk_a = reinterpret_cast<int*>(sp);  // [gmax][32] (use_walk): rank-0..31 anchors of the r-th GT of the walk, -1 padded
+  unsigned* taken = reinterpret_cast<unsigned*>(sp);       sp += odk_align_up((size_t)p.bitmap_words * 4, 16);
+  int* walk_t = reinterpret_cast<int*>(sp);  // [SL][Gp]; before / after the walk also the scratch of the two sorts
+  unsigned long long* sort_keys = reinterpret_cast<unsigned long long*>(sp);
   __shared__ int s_err;
   __shared__ float s_best_v[kGreedyWarps];
   __shared__ int s_best_a[kGreedyWarps];
@@ -308,7 +322,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     }
   }
   for (int w = threadIdx.x; w < p.bitmap_words; w += kGreedyThreads) taken[w] = 0u;
-  {  // stage the first SL ranks of every list: 16-byte cp.async, all in flight at once (entries beyond nlist[g] are never read)
+  if (p.use_walk) {  // stage the first SL ranks of every list: 16-byte cp.async, all in flight at once (entries beyond nlist[g] are never read)
     const int per = SL / 4;
     for (int i = threadIdx.x; i < G * per; i += kGreedyThreads) {
       const int g = i / per, k4 = i - g * per;
@@ -317,28 +331,42 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     odk_cp_async_commit();
   }
   __syncthreads();
+  // Descending sort of 64-bit keys in the (still unused) walk_t area: used for the two rankings when G is large
+  // (the all-pairs count below costs G^2 / 256 steps per thread); needs next_pow2(G) * 8 <= SL * Gp * 4 bytes: always.
+  int n_sort = 2;
+  while (n_sort < G) n_sort <<= 1;
+  const bool by_sort = G > 128;
   if (s_err == ODK_IMG_OK) {
     // ascending-area rank, ties by index (od_pb.py:327)
-    for (int g = threadIdx.x; g < G; g += kGreedyThreads) {
-      const float ag = garea[g];
-      int r = 0;
-      for (int j = 0; j < G; ++j) {
-        const float aj = garea[j];
-        r += (aj < ag) || (aj == ag && j < g);
+    if (by_sort) {
+      for (int i = threadIdx.x; i < n_sort; i += kGreedyThreads)  // descending (~area, ~index) == ascending (area, index)
+        sort_keys[i] = i < G ? ((unsigned long long)(~odk_flip_score(garea[i])) << 32) | (unsigned long long)(0xffffffffu - (unsigned)i) : 0ull;
+      __syncthreads();
+      bitonic_sort_shared(sort_keys, n_sort, 0, 2, n_sort);
+      for (int r = threadIdx.x; r < G; r += kGreedyThreads) order[r] = (int)(0xffffffffu - (unsigned)(sort_keys[r] & 0xffffffffull));
+    } else {
+      for (int g = threadIdx.x; g < G; g += kGreedyThreads) {
+        const float ag = garea[g];
+        int r = 0;
+        for (int j = 0; j < G; ++j) {
+          const float aj = garea[j];
+          r += (aj < ag) || (aj == ag && j < g);
+        }
+        order[r] = g;
       }
-      order[r] = g;
     }
   }
   odk_cp_async_wait<0>();
   __syncthreads();
-  if (p.use_walk && s_err == ODK_IMG_OK) {
-    // regroup what the walk reads: one independent shared-memory load per step instead of order -> nlist -> list
-    for (int i = threadIdx.x; i < G * 32; i += kGreedyThreads) {
-      const int g = order[i >> 5], k = i & 31;
-      walk_a[i] = (k < nlist[g]) ? list[(size_t)g * SL + k] : -1;
+  if (s_err == ODK_IMG_OK) {
+    // transpose what the walk reads: lanes k of a GT read its staged ranks (conflict-free), the store has stride Gp (odd)
+    for (int i = threadIdx.x; i < G * SL; i += kGreedyThreads) {
+      const int r = i / SL, k = i - r * SL;
+      const int g = order[r];
+      walk_t[(size_t)k * Gp + r] = (k < nlist[g]) ? (p.use_walk ? list[(size_t)g * SL + k] : __ldg(glist + (size_t)g * L + k)) : -1;
     }
-    __syncthreads();
   }
+  __syncthreads();
 
   // Warp 0 walks the GTs; the other warps sleep at the barrier below and wake only to help with a
   // CTA-wide IoU arg-max when some GT has no free in-cell anchor (the crowded / stress case).
@@ -348,41 +376,43 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     int need = -2;
     if (warp == 0) {
       if (!err) {
-        // the first 32 ranks of the next two GTs are fetched while the current one is decided (they do not depend on
-        // `taken`), so the serial chain per GT is: bitmap probe -> ballot -> bitmap update
-        auto fetch = [&](int rr) -> int {
-          if (rr >= G) return -1;
-          if (p.use_walk) return walk_a[rr * 32 + lane];
-          const int gg = order[rr];
-          return (lane < nlist[gg]) ? list[(size_t)gg * SL + lane] : -1;
-        };
-        int a0 = fetch(r), a1 = fetch(r + 1);
-        for (; r < G; ++r) {
-          const int a_first = a0;
-          a0 = a1;
-          a1 = fetch(r + 2);
+        while (r < G) {
+          // ---- one optimistic batch: lane j looks at GT r + j ----
+          const int rr = r + lane;
+          const bool active = rr < G;
+          int a = -1;
+          if (active) {
+            for (int k = 0; k < SL; ++k) {
+              const int x = walk_t[(size_t)k * Gp + rr];
+              if (x < 0) break;
+              if (!((taken[x >> 5] >> (x & 31)) & 1u)) { a = x; break; }
+            }
+          }
+          const bool found = active && a >= 0;
+          // lanes without a choice get a value of their own, so they never match anybody
+          const unsigned peers = __match_any_sync(0xffffffffu, found ? a : -1 - lane);
+          const bool collides = found && (__ffs(peers) - 1) != lane;  // an earlier lane of the batch wants the same anchor
+          const unsigned stop = __ballot_sync(0xffffffffu, collides || (active && !found));
+          const unsigned act = __ballot_sync(0xffffffffu, active);
+          const int n_ok = stop ? (__ffs(stop) - 1) : __popc(act);   // lanes [0, n_ok) commit
+          if (lane < n_ok) {
+            atomicOr(&taken[a >> 5], 1u << (a & 31));  // several lanes may share a word
+            pick[order[rr]] = a;
+          }
+          __syncwarp();
+          r += n_ok;
+          if (n_ok > 0 || !stop) continue;  // progress: restart the batch at the first collision (it re-reads the bitmap)
+          // ---- lane 0's GT has no free anchor among its staged ranks: the rare serial paths ----
           const int g = order[r];
           const int nl = nlist[g];
-          // fast path: some anchor among the first 32 ranks is free (the owning lane records it)
-          const unsigned word = (a_first >= 0) ? taken[a_first >> 5] : 0xffffffffu;
-          const unsigned bit = 1u << (a_first & 31);
-          const unsigned fm = __ballot_sync(0xffffffffu, !(word & bit));
-          if (fm) {
-            if (lane == __ffs(fm) - 1) {
-              taken[a_first >> 5] = word | bit;
-              pick[g] = a_first;
-            }
-            __syncwarp();
-            continue;
-          }
           const int nc = ncand[g];
           int best_a = -1;
-          for (int k0 = 32; k0 < nl && best_a < 0; k0 += 32) {
+          for (int k0 = SL; k0 < nl && best_a < 0; k0 += 32) {
             const int k = k0 + lane;
-            const int a = (k < nl) ? __ldg(glist + (size_t)g * L + k) : -1;  // ranks >= 32: rare, straight from the workspace
-            const bool is_free = a >= 0 && !((taken[a >> 5] >> (a & 31)) & 1u);
+            const int aa = (k < nl) ? __ldg(glist + (size_t)g * L + k) : -1;  // deeper ranks: straight from the workspace
+            const bool is_free = aa >= 0 && !((taken[aa >> 5] >> (aa & 31)) & 1u);
             const unsigned fm2 = __ballot_sync(0xffffffffu, is_free);
-            if (fm2) best_a = __shfl_sync(0xffffffffu, a, __ffs(fm2) - 1);
+            if (fm2) best_a = __shfl_sync(0xffffffffu, aa, __ffs(fm2) - 1);
           }
           if (best_a < 0 && nc > nl) {
             // the ranked prefix is exhausted but more in-cell anchors exist: exact re-evaluation over the free ones
@@ -391,10 +421,10 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
             const float cy = __fmul_rn(__fadd_rn(box.w, box.y), 0.5f);
             double mc = DBL_MAX;
             int ma = INT_MAX;
-            for_each_cell_candidate(p.av, cx, cy, lane, [&](int a, bool ok) {
-              if (!ok || ((taken[a >> 5] >> (a & 31)) & 1u)) return;  // od_pb.py:339
-              const double c = encode_cost(box, __ldg(p.av.locs + a), p.av.sizes[a]);
-              if (cand_less(c, a, mc, ma)) { mc = c; ma = a; }
+            for_each_cell_candidate(p.av, cx, cy, lane, [&](int aa, bool ok) {
+              if (!ok || ((taken[aa >> 5] >> (aa & 31)) & 1u)) return;  // od_pb.py:339
+              const double c = encode_cost(box, __ldg(p.av.locs + aa), p.av.sizes[aa]);
+              if (cand_less(c, aa, mc, ma)) { mc = c; ma = aa; }
             });
 #pragma unroll
             for (int d = 16; d > 0; d >>= 1) {
@@ -410,6 +440,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
             pick[g] = best_a;
           }
           __syncwarp();
+          ++r;
         }
       }
       if (lane == 0) s_state[0] = need;
@@ -452,20 +483,32 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     }
   }
   // every thread holds the same `err` (it changes only in the CTA-wide fallback); pick[] is complete and visible (the
-  // loop's last barrier).  The output order needs each pick's rank among all picks: O(G^2), shared by the whole CTA.
+  // loop's last barrier).
   if (err) {
     for (int g = threadIdx.x; g < p.gmax; g += kGreedyThreads) { out_pb[g] = -1; out_gt[g] = -1; }
     if (threadIdx.x == 0) p.status[b] = err;
     return;
   }
   // np.where(pb_assigned_gt >= 0): ascending anchor index (od_pb.py:359); picks are unique
-  for (int g = threadIdx.x; g < G; g += kGreedyThreads) {
-    const int mine = pick[g];
-    int rk = 0;
+  if (by_sort) {
+    for (int i = threadIdx.x; i < n_sort; i += kGreedyThreads)  // descending ~pick == ascending pick; the GT rides in the low word
+      sort_keys[i] = i < G ? ((unsigned long long)(~(unsigned)pick[i]) << 32) | (unsigned long long)(unsigned)i : 0ull;
+    __syncthreads();
+    bitonic_sort_shared(sort_keys, n_sort, 0, 2, n_sort);
+    for (int rk = threadIdx.x; rk < G; rk += kGreedyThreads) {
+      const unsigned long long k = sort_keys[rk];
+      out_pb[rk] = (long long)(~(unsigned)(k >> 32));
+      out_gt[rk] = (long long)(unsigned)(k & 0xffffffffull);
+    }
+  } else {
+    for (int g = threadIdx.x; g < G; g += kGreedyThreads) {
+      const int mine = pick[g];
+      int rk = 0;
 #pragma unroll 4
-    for (int j = 0; j < G; ++j) rk += pick[j] < mine;
-    out_pb[rk] = mine;
-    out_gt[rk] = g;
+      for (int j = 0; j < G; ++j) rk += pick[j] < mine;
+      out_pb[rk] = mine;
+      out_gt[rk] = g;
+    }
   }
   for (int g = G + threadIdx.x; g < p.gmax; g += kGreedyThreads) { out_pb[g] = -1; out_gt[g] = -1; }
   if (threadIdx.x == 0) p.status[b] = ODK_IMG_OK;
@@ -575,10 +618,15 @@ int odk_launch_assign_greedy(const odk_anchors* a, int batch, const float* gt_bo
                              int gmax, int64_t* pb_indices, int64_t* gt_indices, int32_t* status, void* lists_ws, cudaStream_t stream) {
   AssignArgs args;
   fill_args(args, a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, lists_ws, nullptr);
-  size_t smem = odk_align_up((size_t)gmax * (16 + 20 + 4 * (size_t)args.stage_len) + (size_t)args.bitmap_words * 4, 16);
+  // boxes, staged ranks, five per-GT words, taken bitmap, the rank-major walk table (also the sort scratch)
+  size_t smem = (size_t)gmax * (16 + 20 + 4 * (size_t)args.stage_len) + odk_align_up((size_t)args.bitmap_words * 4, 16) +
+                (size_t)args.stage_len * (gmax | 1) * 4 + 16;
+  args.use_walk = 1;  // ranked lists staged in shared memory with cp.async while the GTs are ranked by area
+  if (smem > 200 * 1024) {  // very large Gmax: no staging area, the walk table is filled straight from the workspace
+    args.use_walk = 0;
+    smem -= (size_t)gmax * 4 * (size_t)args.stage_len;
+  }
   ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign: N=%d / Gmax=%d need %zu bytes of shared memory per image", a->n, gmax, smem);
-  args.use_walk = (smem + (size_t)gmax * 128 <= 200 * 1024) ? 1 : 0;
-  if (args.use_walk) smem += (size_t)gmax * 128;
   ODK_CUDA(cudaFuncSetAttribute(assign_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   {
     OdkProfileScope prof_("assign_greedy_kernel", stream);

@@ -6,7 +6,7 @@ exist there).
 
 The reference is pure Python, so its "build" is byte-compilation: every file ``oracle/ref_loader.py`` loads
  is compiled FROM WHERE IT LIES under /root/reference with ``py_compile`` into a sourceless
-``.pyc`` under ``oracle/_ref/pytoolkit/`` (same layout), plus a manifest with the SHA-256 of each source.
+bytecode file (``.rpyc``) under ``oracle/_ref/pytoolkit/`` (same layout), plus a manifest with the SHA-256 of each source.
 No reference source text is copied into this repository; ``oracle/_ref/`` is git-ignored but not
 gpurun-ignored (like the built ``libodk.so``).  The bytecode is tied to the interpreter version, which is
 the same image here and on the GPU box; the manifest records it and ``ref_loader`` refuses a mismatch.
@@ -23,6 +23,7 @@ import sys
 SRC = pathlib.Path('/root/reference/pytoolkit/pytoolkit')
 DST = pathlib.Path(__file__).resolve().parent / '_ref' / 'pytoolkit'
 # the eight modules ref_loader names plus dl/backend, which dl/losses imports
+SUFFIX = '.rpyc'  # not '.pyc': snapshot tools tend to drop *.pyc; ref_loader loads these files explicitly
 MODULES = ['utils', 'log', 'math', 'draw', 'ndimage', 'ml', 'dl/backend', 'dl/losses', 'dl/od_pb']
 
 
@@ -32,7 +33,7 @@ def make() -> bool:
         return False
     manifest = {}
     for rel in MODULES:
-        src, dst = SRC / (rel + '.py'), DST / (rel + '.pyc')
+        src, dst = SRC / (rel + '.py'), DST / (rel + SUFFIX)
         dst.parent.mkdir(parents=True, exist_ok=True)
         py_compile.compile(str(src), cfile=str(dst), dfile=str(src), doraise=True,
                            invalidation_mode=py_compile.PycInvalidationMode.UNCHECKED_HASH)

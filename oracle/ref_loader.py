@@ -13,6 +13,7 @@ path under a synthetic ``pytoolkit`` package, with three shims:
 ``np.bool`` alias, ``sklearn.externals.joblib`` alias and a stub ``tensorflow``
 (``PriorBoxes.decode_locs`` imports it unconditionally, od_pb.py:218).
 """
+import importlib.machinery
 import importlib.util
 import pathlib
 import sys
@@ -23,11 +24,11 @@ import numpy as np
 _MOUNTED = pathlib.Path('/root/reference/pytoolkit/pytoolkit')
 _COPIED = pathlib.Path(__file__).resolve().parent / '_ref' / 'pytoolkit'
 REFERENCE_ROOT = _MOUNTED if (_MOUNTED / 'dl' / 'od_pb.py').is_file() else _COPIED
-_FILES = ['utils', 'log', 'math', 'draw', 'ndimage', 'ml', 'dl.losses', 'dl.od_pb']
+_FILES = ['utils', 'log', 'math', 'draw', 'ndimage', 'ml', 'dl.backend', 'dl.losses', 'dl.od_pb']  # dl.backend: imported by dl.losses
 
 
 def _suffix() -> str:
-    return '.py' if REFERENCE_ROOT == _MOUNTED else '.pyc'
+    return '.py' if REFERENCE_ROOT == _MOUNTED else '.rpyc'
 
 
 def available() -> bool:
@@ -80,7 +81,8 @@ def load():
     for name in _FILES:
         full = 'pytoolkit.' + name
         path = REFERENCE_ROOT / (name.replace('.', '/') + _suffix())
-        spec = importlib.util.spec_from_file_location(full, path)  # a SourcelessFileLoader for .pyc
+        loader = None if path.suffix == '.py' else importlib.machinery.SourcelessFileLoader(full, str(path))
+        spec = importlib.util.spec_from_file_location(full, path, loader=loader)
         mod = importlib.util.module_from_spec(spec)
         sys.modules[full] = mod
         spec.loader.exec_module(mod)
