@@ -263,12 +263,13 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_ignore_kernel(const As
 // Phase B: the greedy walk, one CTA per image.
 //
 // The reference's loop is sequential — GT r takes the best anchor no earlier GT took — but consecutive GTs rarely
-// compete for the same anchor, so the walk is OPTIMISTIC: warp 0 looks at 32 consecutive GTs at once (a lane each);
-// every lane finds the first anchor of its own ranked list that is free in the bitmap as it stood before the batch;
-// lanes whose choice collides with that of an earlier lane of the batch are found with one match.any, and the lanes
-// in front of the first collision commit together (their choices are pairwise distinct and none of them was free-ed
-// or taken in between, so each is exactly what the sequential loop would have picked).  The batch then restarts at the
-// colliding GT, which re-reads the bitmap.  A crowded image degenerates to one GT per step, as before.
+// compete for the same anchor, so the walk is OPTIMISTIC: warp 0 looks at 32 consecutive GTs at once (a lane each) and
+// at the best-ranked anchor of each.  Lanes whose anchor is free in the bitmap as it stood before the batch, up to the
+// first lane whose anchor is taken or collides with that of a lane in front of it (one match.any), commit together:
+// their choices are pairwise distinct and nothing was taken in between, so each is exactly what the sequential loop
+// would have picked.  The GT the batch stopped at is then decided the way the sequential walk does it — its staged
+// ranks side by side, a lane each, first free one wins — and the next batch starts behind it.  A crowded image
+// degenerates to one GT per step, as before; spread-out GTs (the stress shape: 512 per image) go 32 at a time.
 //
 // Shared-memory layout of what the walk reads: walk_t[k][r] = rank-k anchor of the r-th GT of the walk (rank-major,
 // row stride odd: lanes = consecutive r are conflict-free, and so is the transposing store), -1 beyond the list.
@@ -377,22 +378,15 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     if (warp == 0) {
       if (!err) {
         while (r < G) {
-          // ---- one optimistic batch: lane j looks at GT r + j ----
+          // ---- one optimistic batch: lane j looks at the BEST-ranked anchor of GT r + j ----
           const int rr = r + lane;
           const bool active = rr < G;
-          int a = -1;
-          if (active) {
-            for (int k = 0; k < SL; ++k) {
-              const int x = walk_t[(size_t)k * Gp + rr];
-              if (x < 0) break;
-              if (!((taken[x >> 5] >> (x & 31)) & 1u)) { a = x; break; }
-            }
-          }
-          const bool found = active && a >= 0;
-          // lanes without a choice get a value of their own, so they never match anybody
+          const int a = active ? walk_t[rr] : -1;  // rank 0 (always present: every GT has >= 1 in-cell anchor here)
+          const bool found = a >= 0 && !((taken[a >> 5] >> (a & 31)) & 1u);
+          // lanes without a free first choice get a value of their own, so they never match anybody
           const unsigned peers = __match_any_sync(0xffffffffu, found ? a : -1 - lane);
           const bool collides = found && (__ffs(peers) - 1) != lane;  // an earlier lane of the batch wants the same anchor
-          const unsigned stop = __ballot_sync(0xffffffffu, collides || (active && !found));
+          const unsigned stop = __ballot_sync(0xffffffffu, active && (!found || collides));
           const unsigned act = __ballot_sync(0xffffffffu, active);
           const int n_ok = stop ? (__ffs(stop) - 1) : __popc(act);   // lanes [0, n_ok) commit
           if (lane < n_ok) {
@@ -401,8 +395,24 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
           }
           __syncwarp();
           r += n_ok;
-          if (n_ok > 0 || !stop) continue;  // progress: restart the batch at the first collision (it re-reads the bitmap)
-          // ---- lane 0's GT has no free anchor among its staged ranks: the rare serial paths ----
+          if (!stop) continue;
+          // ---- the first GT whose best anchor is gone (taken earlier, or by a lane in front of it just now): its staged
+          //      ranks side by side, a lane each — the first free one wins ----
+          {
+            const int x = (lane < SL) ? walk_t[(size_t)lane * Gp + r] : -1;
+            const bool is_free = x >= 0 && !((taken[x >> 5] >> (x & 31)) & 1u);
+            const unsigned fm = __ballot_sync(0xffffffffu, is_free);
+            if (fm) {
+              if (lane == __ffs(fm) - 1) {
+                taken[x >> 5] |= 1u << (x & 31);
+                pick[order[r]] = x;
+              }
+              __syncwarp();
+              ++r;
+              continue;
+            }
+          }
+          // ---- no free anchor among its staged ranks: the rare serial paths ----
           const int g = order[r];
           const int nl = nlist[g];
           const int nc = ncand[g];

@@ -340,10 +340,11 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     //         remaining keys differ (fp32 scores share their leading exponent bits) -------------------------
     unsigned long long lo_key = 0ull;
     const int need = STRICT ? p.top_k - nkept2 : limit - nkept;
-    // band size aimed at: 1.25x what is still needed; after its first round strict mode scales that by the survival
-    // ratio of the all-class pass seen so far
-    int want = need + (need >> 2) + 32;
-    if (STRICT && nkept2 > 0) want = (int)min((long long)kBand, (long long)need * processed / nkept2 * 5 / 4 + 32);
+    // band size aimed at: a little more than what is still needed, scaled by the survival ratio seen so far (first round:
+    // 1.125x + 16, which for top_k = 200 keeps the band within a 256-key sort network when little is suppressed)
+    int want = need + (need >> 3) + 16;
+    const int kept_so_far = STRICT ? nkept2 : nkept;
+    if (kept_so_far > 0) want = (int)min((long long)kBand, (long long)need * processed / kept_so_far * 9 / 8 + 32);
     want = min(kBand, want);
     bool have_lo = remaining <= kBand;
     if (!have_lo && processed == 0 && p.score_hist != nullptr) {
