@@ -281,7 +281,8 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   const int b = blockIdx.x;
   const int L = p.list_len;
   unsigned char* sp = greedy_smem;
-  const int SL = p.stage_len;  // 32: the ranks the fast path looks at; deeper ranks (crowded images) come from the workspace
+  const int SL = p.stage_len;  // ranks of every list staged in shared memory (a multiple of 32; deeper ranks come from the workspace)
+  constexpr int WR = 32;       // ranks in the walk table: what a lane-per-rank step looks at
   const int Gp = p.gmax | 1;   // row stride of walk_t (odd)
   const int* glist = p.ws_list + (size_t)b * p.gmax * L;
   float4* gbox = reinterpret_cast<float4*>(sp);            sp += (size_t)p.gmax * 16;
@@ -292,7 +293,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   int* ncand = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
   int* nlist = reinterpret_cast<int*>(sp);                 sp += (size_t)p.gmax * 4;
   unsigned* taken = reinterpret_cast<unsigned*>(sp);       sp += odk_align_up((size_t)p.bitmap_words * 4, 16);
-  int* walk_t = reinterpret_cast<int*>(sp);  // [SL][Gp]; before / after the walk also the scratch of the two sorts
+  int* walk_t = reinterpret_cast<int*>(sp);  // [WR][Gp]; before / after the walk also the scratch of the two sorts
   unsigned long long* sort_keys = reinterpret_cast<unsigned long long*>(sp);
   __shared__ int s_err;
   __shared__ float s_best_v[kGreedyWarps];
@@ -333,7 +334,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   }
   __syncthreads();
   // Descending sort of 64-bit keys in the (still unused) walk_t area: used for the two rankings when G is large
-  // (the all-pairs count below costs G^2 / 256 steps per thread); needs next_pow2(G) * 8 <= SL * Gp * 4 bytes: always.
+  // (the all-pairs count below costs G^2 / 256 steps per thread); needs next_pow2(G) * 8 <= WR * Gp * 4 bytes: always.
   int n_sort = 2;
   while (n_sort < G) n_sort <<= 1;
   const bool by_sort = G > 128;
@@ -361,8 +362,8 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   __syncthreads();
   if (s_err == ODK_IMG_OK) {
     // transpose what the walk reads: lanes k of a GT read its staged ranks (conflict-free), the store has stride Gp (odd)
-    for (int i = threadIdx.x; i < G * SL; i += kGreedyThreads) {
-      const int r = i / SL, k = i - r * SL;
+    for (int i = threadIdx.x; i < G * WR; i += kGreedyThreads) {
+      const int r = i / WR, k = i - r * WR;
       const int g = order[r];
       walk_t[(size_t)k * Gp + r] = (k < nlist[g]) ? (p.use_walk ? list[(size_t)g * SL + k] : __ldg(glist + (size_t)g * L + k)) : -1;
     }
@@ -377,29 +378,35 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     int need = -2;
     if (warp == 0) {
       if (!err) {
+        int serial = 0;  // GTs left to decide one at a time before the next batch attempt (contended neighbourhood)
         while (r < G) {
-          // ---- one optimistic batch: lane j looks at the BEST-ranked anchor of GT r + j ----
-          const int rr = r + lane;
-          const bool active = rr < G;
-          const int a = active ? walk_t[rr] : -1;  // rank 0 (always present: every GT has >= 1 in-cell anchor here)
-          const bool found = a >= 0 && !((taken[a >> 5] >> (a & 31)) & 1u);
-          // lanes without a free first choice get a value of their own, so they never match anybody
-          const unsigned peers = __match_any_sync(0xffffffffu, found ? a : -1 - lane);
-          const bool collides = found && (__ffs(peers) - 1) != lane;  // an earlier lane of the batch wants the same anchor
-          const unsigned stop = __ballot_sync(0xffffffffu, active && (!found || collides));
-          const unsigned act = __ballot_sync(0xffffffffu, active);
-          const int n_ok = stop ? (__ffs(stop) - 1) : __popc(act);   // lanes [0, n_ok) commit
-          if (lane < n_ok) {
-            atomicOr(&taken[a >> 5], 1u << (a & 31));  // several lanes may share a word
-            pick[order[rr]] = a;
+          if (serial == 0) {
+            // ---- one optimistic batch: lane j looks at the BEST-ranked anchor of GT r + j ----
+            const int rr = r + lane;
+            const bool active = rr < G;
+            const int a = active ? walk_t[rr] : -1;  // rank 0 (present whenever the GT has a ranked list)
+            const bool found = a >= 0 && !((taken[a >> 5] >> (a & 31)) & 1u);
+            // lanes without a free first choice get a value of their own, so they never match anybody
+            const unsigned peers = __match_any_sync(0xffffffffu, found ? a : -1 - lane);
+            const bool collides = found && (__ffs(peers) - 1) != lane;  // an earlier lane of the batch wants the same anchor
+            const unsigned stop = __ballot_sync(0xffffffffu, active && (!found || collides));
+            const unsigned act = __ballot_sync(0xffffffffu, active);
+            const int n_ok = stop ? (__ffs(stop) - 1) : __popc(act);   // lanes [0, n_ok) commit
+            if (lane < n_ok) {
+              atomicOr(&taken[a >> 5], 1u << (a & 31));  // several lanes may share a word
+              pick[order[rr]] = a;
+            }
+            __syncwarp();
+            r += n_ok;
+            if (!stop) continue;
+            if (n_ok < 4) serial = 16;  // the batch bought little: a crowded spot, where a batch attempt costs more than it saves
+          } else {
+            --serial;
           }
-          __syncwarp();
-          r += n_ok;
-          if (!stop) continue;
           // ---- the first GT whose best anchor is gone (taken earlier, or by a lane in front of it just now): its staged
           //      ranks side by side, a lane each — the first free one wins ----
           {
-            const int x = (lane < SL) ? walk_t[(size_t)lane * Gp + r] : -1;
+            const int x = walk_t[(size_t)lane * Gp + r];
             const bool is_free = x >= 0 && !((taken[x >> 5] >> (x & 31)) & 1u);
             const unsigned fm = __ballot_sync(0xffffffffu, is_free);
             if (fm) {
@@ -417,9 +424,10 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
           const int nl = nlist[g];
           const int nc = ncand[g];
           int best_a = -1;
-          for (int k0 = SL; k0 < nl && best_a < 0; k0 += 32) {
+          for (int k0 = WR; k0 < nl && best_a < 0; k0 += 32) {
             const int k = k0 + lane;
-            const int aa = (k < nl) ? __ldg(glist + (size_t)g * L + k) : -1;  // deeper ranks: straight from the workspace
+            // deeper ranks (crowded spots): from the staged lists, beyond those straight from the workspace
+            const int aa = (k < nl) ? ((p.use_walk && k < SL) ? list[(size_t)g * SL + k] : __ldg(glist + (size_t)g * L + k)) : -1;
             const bool is_free = aa >= 0 && !((taken[aa >> 5] >> (aa & 31)) & 1u);
             const unsigned fm2 = __ballot_sync(0xffffffffu, is_free);
             if (fm2) best_a = __shfl_sync(0xffffffffu, aa, __ffs(fm2) - 1);
@@ -629,8 +637,10 @@ int odk_launch_assign_greedy(const odk_anchors* a, int batch, const float* gt_bo
   AssignArgs args;
   fill_args(args, a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, lists_ws, nullptr);
   // boxes, staged ranks, five per-GT words, taken bitmap, the rank-major walk table (also the sort scratch)
+  // all 128 ranks staged while that stays under 64 KB (Gmax <= 128), fewer for larger Gmax
+  args.stage_len = gmax <= 128 ? 128 : (gmax <= 256 ? 64 : 32);
   size_t smem = (size_t)gmax * (16 + 20 + 4 * (size_t)args.stage_len) + odk_align_up((size_t)args.bitmap_words * 4, 16) +
-                (size_t)args.stage_len * (gmax | 1) * 4 + 16;
+                (size_t)32 * (gmax | 1) * 4 + 16;
   args.use_walk = 1;  // ranked lists staged in shared memory with cp.async while the GTs are ranked by area
   if (smem > 200 * 1024) {  // very large Gmax: no staging area, the walk table is filled straight from the workspace
     args.use_walk = 0;
