@@ -35,6 +35,7 @@ struct AssignArgs {
   int32_t* status;
   int list_len;  // ranked candidates remembered per GT
   int use_walk;  // greedy kernel: 1 = the first ranks of every list are staged in shared memory before the transposition
+  int walk_mode; // greedy kernel diagnostics (ODK_GREEDY_MODE): 0 adaptive, 1 one GT per step only, 2 batches only
   int stage_len; // greedy kernel: ranks of every GT staged in shared memory (the rest is read from the workspace on demand)
   int bitmap_words;
   int* ws_list;   // [B, Gmax, list_len] ranked in-cell anchors
@@ -378,7 +379,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     int need = -2;
     if (warp == 0) {
       if (!err) {
-        int serial = 0;  // GTs left to decide one at a time before the next batch attempt (contended neighbourhood)
+        int serial = p.walk_mode == 1 ? 0x3fffffff : 0;  // GTs left to decide one at a time before the next batch attempt
         while (r < G) {
           if (serial == 0) {
             // ---- one optimistic batch: lane j looks at the BEST-ranked anchor of GT r + j ----
@@ -394,30 +395,36 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
             const int n_ok = stop ? (__ffs(stop) - 1) : __popc(act);   // lanes [0, n_ok) commit
             if (lane < n_ok) {
               atomicOr(&taken[a >> 5], 1u << (a & 31));  // several lanes may share a word
-              pick[order[rr]] = a;
+              pick[rr] = a;  // by walk position; translated to the GT index when the result is written
             }
             __syncwarp();
             r += n_ok;
             if (!stop) continue;
-            if (n_ok < 4) serial = 16;  // the batch bought little: a crowded spot, where a batch attempt costs more than it saves
-          } else {
-            --serial;
+            // a batch that committed nothing: a crowded spot, where a batch attempt costs more than it saves
+            if (n_ok == 0 && p.walk_mode != 2) serial = 8;
           }
-          // ---- the first GT whose best anchor is gone (taken earlier, or by a lane in front of it just now): its staged
-          //      ranks side by side, a lane each — the first free one wins ----
+          // ---- one GT per step: the staged ranks of GT r side by side, a lane each — the first free one wins.  Runs for
+          //      the GT a batch stopped at and, in a crowded spot, for the next `serial` GTs; the ranks of the following
+          //      GT are fetched a step ahead, so the chain per GT is bitmap probe -> ballot -> bitmap update ----
           {
-            const int x = walk_t[(size_t)lane * Gp + r];
-            const bool is_free = x >= 0 && !((taken[x >> 5] >> (x & 31)) & 1u);
-            const unsigned fm = __ballot_sync(0xffffffffu, is_free);
-            if (fm) {
+            int x = walk_t[(size_t)lane * Gp + r];
+            bool decided = true;
+            while (true) {
+              const int xn = (r + 1 < G) ? walk_t[(size_t)lane * Gp + r + 1] : -1;
+              const bool is_free = x >= 0 && !((taken[x >> 5] >> (x & 31)) & 1u);
+              const unsigned fm = __ballot_sync(0xffffffffu, is_free);
+              if (!fm) { decided = false; break; }
               if (lane == __ffs(fm) - 1) {
                 taken[x >> 5] |= 1u << (x & 31);
-                pick[order[r]] = x;
+                pick[r] = x;
               }
               __syncwarp();
               ++r;
-              continue;
+              x = xn;
+              if (serial == 0 || r >= G) break;
+              --serial;
             }
+            if (decided) continue;
           }
           // ---- no free anchor among its staged ranks: the rare serial paths ----
           const int g = order[r];
@@ -455,7 +462,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
           if (best_a < 0) { need = g; break; }  // -> CTA-wide fallback
           if (lane == 0) {
             taken[best_a >> 5] |= 1u << (best_a & 31);
-            pick[g] = best_a;
+            pick[r] = best_a;
           }
           __syncwarp();
           ++r;
@@ -492,7 +499,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
         s_state[1] = fa;
         if (fa != INT_MAX) {
           taken[fa >> 5] |= 1u << (fa & 31);
-          pick[need] = fa;
+          pick[r] = fa;  // thread 0 belongs to warp 0, whose r is the walk position of the GT in need
         }
       }
       __syncthreads();
@@ -510,7 +517,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
   // np.where(pb_assigned_gt >= 0): ascending anchor index (od_pb.py:359); picks are unique
   if (by_sort) {
     for (int i = threadIdx.x; i < n_sort; i += kGreedyThreads)  // descending ~pick == ascending pick; the GT rides in the low word
-      sort_keys[i] = i < G ? ((unsigned long long)(~(unsigned)pick[i]) << 32) | (unsigned long long)(unsigned)i : 0ull;
+      sort_keys[i] = i < G ? ((unsigned long long)(~(unsigned)pick[i]) << 32) | (unsigned long long)(unsigned)order[i] : 0ull;
     __syncthreads();
     bitonic_sort_shared(sort_keys, n_sort, 0, 2, n_sort);
     for (int rk = threadIdx.x; rk < G; rk += kGreedyThreads) {
@@ -519,13 +526,13 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
       out_gt[rk] = (long long)(unsigned)(k & 0xffffffffull);
     }
   } else {
-    for (int g = threadIdx.x; g < G; g += kGreedyThreads) {
-      const int mine = pick[g];
+    for (int q = threadIdx.x; q < G; q += kGreedyThreads) {  // q: walk position
+      const int mine = pick[q];
       int rk = 0;
 #pragma unroll 4
       for (int j = 0; j < G; ++j) rk += pick[j] < mine;
       out_pb[rk] = mine;
-      out_gt[rk] = g;
+      out_gt[rk] = order[q];
     }
   }
   for (int g = G + threadIdx.x; g < p.gmax; g += kGreedyThreads) { out_pb[g] = -1; out_gt[g] = -1; }
@@ -591,6 +598,7 @@ static int fill_args(AssignArgs& args, const odk_anchors* a, int batch, const fl
   args.ws_nlist = args.ws_ncand + (size_t)batch * gmax;
   args.ws_ignore = ignore;
   args.use_walk = 0;
+  args.walk_mode = 0;
   args.stage_len = 32;
   args.tl = odk_timeline_ptr();
   return ODK_OK;
@@ -641,6 +649,8 @@ int odk_launch_assign_greedy(const odk_anchors* a, int batch, const float* gt_bo
   args.stage_len = gmax <= 128 ? 128 : (gmax <= 256 ? 64 : 32);
   size_t smem = (size_t)gmax * (16 + 20 + 4 * (size_t)args.stage_len) + odk_align_up((size_t)args.bitmap_words * 4, 16) +
                 (size_t)32 * (gmax | 1) * 4 + 16;
+  static const int walk_mode = getenv("ODK_GREEDY_MODE") ? atoi(getenv("ODK_GREEDY_MODE")) : 0;
+  args.walk_mode = walk_mode;
   args.use_walk = 1;  // ranked lists staged in shared memory with cp.async while the GTs are ranked by area
   if (smem > 200 * 1024) {  // very large Gmax: no staging area, the walk table is filled straight from the workspace
     args.use_walk = 0;
