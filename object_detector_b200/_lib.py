@@ -8,7 +8,9 @@ import pathlib
 import threading
 
 _PKG = pathlib.Path(__file__).resolve().parent
-LIB_PATH = _PKG / 'libodk.so'
+import os
+# ODK_LIB_VARIANT=checks selects the build with device-side bounds assertions (build.py --checks); diagnostics only
+LIB_PATH = _PKG / ('libodk_checks.so' if os.environ.get('ODK_LIB_VARIANT') == 'checks' else 'libodk.so')
 
 c_int, c_float, c_size_t, c_void_p, c_int64 = ctypes.c_int, ctypes.c_float, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_int64
 c_double = ctypes.c_double

@@ -12,6 +12,7 @@ PKG = pathlib.Path(__file__).resolve().parent
 SRC = sorted((PKG / 'csrc').glob('*.cu'))
 HDR = sorted((PKG / 'csrc').glob('*.cuh')) + sorted((PKG.parent / 'include').glob('*.h'))
 LIB = PKG / 'libodk.so'
+LIB_CHECKS = PKG / 'libodk_checks.so'  # same sources with -DODK_CHECKS: device-side bounds assertions (csrc/odk_common.cuh)
 
 NVCC_FLAGS = [
     '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
@@ -27,16 +28,17 @@ def needs_build() -> bool:
     return any(p.stat().st_mtime > t for p in SRC + HDR + [pathlib.Path(__file__)])
 
 
-def build(force: bool = False, verbose: bool = False) -> pathlib.Path:
+def build(force: bool = False, verbose: bool = False, checks: bool = False) -> pathlib.Path:
     """One nvcc -c per source file, in parallel (objects under csrc/.obj/, git-ignored), then one link."""
-    if not force and not needs_build():
+    lib = LIB_CHECKS if checks else LIB
+    if not checks and not force and not needs_build():
         return LIB
     import concurrent.futures as cf
     nvcc = shutil.which('nvcc') or '/usr/local/cuda/bin/nvcc'
-    obj_dir = PKG / 'csrc' / '.obj'
+    obj_dir = PKG / 'csrc' / ('.obj_checks' if checks else '.obj')
     obj_dir.mkdir(exist_ok=True)
     hdr_time = max(p.stat().st_mtime for p in HDR + [pathlib.Path(__file__)])
-    compile_flags = [f for f in NVCC_FLAGS if f != '-shared']
+    compile_flags = [f for f in NVCC_FLAGS if f != '-shared'] + (['-DODK_CHECKS=1'] if checks else [])
 
     def compile_one(src):
         obj = obj_dir / (src.stem + '.o')
@@ -53,12 +55,12 @@ def build(force: bool = False, verbose: bool = False) -> pathlib.Path:
     if verbose:
         for _, log in results:
             print(log)
-    res = subprocess.run([nvcc, '-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-Xcompiler', '-fPIC', '-o', str(LIB)]
+    res = subprocess.run([nvcc, '-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-Xcompiler', '-fPIC', '-o', str(lib)]
                          + [str(o) for o, _ in results], capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError('nvcc link failed:\n' + res.stdout + res.stderr)
-    return LIB
+    return lib
 
 
 if __name__ == '__main__':
-    print(build(force='--force' in sys.argv, verbose='-v' in sys.argv))
+    print(build(force='--force' in sys.argv, verbose='-v' in sys.argv, checks='--checks' in sys.argv))

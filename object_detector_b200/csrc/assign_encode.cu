@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_candidates_kernel(cons
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u)
-        if (e0 + u * 32 + lane < total && rk[u] < L) list[rk[u]] = ae[u];
+        if (e0 + u * 32 + lane < total && rk[u] < L) { ODK_ASSERT(rk[u] >= 0 && ae[u] >= 0 && ae[u] < p.av.n); list[rk[u]] = ae[u]; }
     }
     stored = min(total, L);
   }
@@ -256,6 +256,7 @@ __global__ void __launch_bounds__(kCandThreads, 8) assign_ignore_kernel(const As
       const int a = geo.x + iy * geo.y + ix;
       const unsigned char mk = __ldg(p.av.mask + a);
       const float4 lc = __ldg(p.av.locs + a);
+      ODK_ASSERT(a >= 0 && a < p.av.n);
       if (mk && odk_iou_passes<true>(box, ga, lc, odk_area(lc), 0.5f)) atomicOr(ignore + (a >> 5), 1u << (a & 31));
     }
   }
@@ -366,6 +367,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
     for (int i = threadIdx.x; i < G * WR; i += kGreedyThreads) {
       const int r = i / WR, k = i - r * WR;
       const int g = order[r];
+      ODK_ASSERT(g >= 0 && g < G && (size_t)k * Gp + r < (size_t)WR * Gp);
       walk_t[(size_t)k * Gp + r] = (k < nlist[g]) ? (p.use_walk ? list[(size_t)g * SL + k] : __ldg(glist + (size_t)g * L + k)) : -1;
     }
   }
@@ -394,6 +396,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
             const unsigned act = __ballot_sync(0xffffffffu, active);
             const int n_ok = stop ? (__ffs(stop) - 1) : __popc(act);   // lanes [0, n_ok) commit
             if (lane < n_ok) {
+              ODK_ASSERT(a >= 0 && a < p.av.n && rr < G && !((taken[a >> 5] >> (a & 31)) & 1u));
               atomicOr(&taken[a >> 5], 1u << (a & 31));  // several lanes may share a word
               pick[rr] = a;  // by walk position; translated to the GT index when the result is written
             }
@@ -415,6 +418,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
               const unsigned fm = __ballot_sync(0xffffffffu, is_free);
               if (!fm) { decided = false; break; }
               if (lane == __ffs(fm) - 1) {
+                ODK_ASSERT(x >= 0 && x < p.av.n && r < G);
                 taken[x >> 5] |= 1u << (x & 31);
                 pick[r] = x;
               }
@@ -461,6 +465,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
           }
           if (best_a < 0) { need = g; break; }  // -> CTA-wide fallback
           if (lane == 0) {
+            ODK_ASSERT(best_a >= 0 && best_a < p.av.n && r < G);
             taken[best_a >> 5] |= 1u << (best_a & 31);
             pick[r] = best_a;
           }
@@ -531,6 +536,7 @@ __global__ void __launch_bounds__(kGreedyThreads) assign_greedy_kernel(const Ass
       int rk = 0;
 #pragma unroll 4
       for (int j = 0; j < G; ++j) rk += pick[j] < mine;
+      ODK_ASSERT(rk < G && mine >= 0 && mine < p.av.n);
       out_pb[rk] = mine;
       out_gt[rk] = order[q];
     }

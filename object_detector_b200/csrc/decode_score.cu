@@ -291,7 +291,9 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
       }
       __syncwarp();
       if (lane == 0) odk_mbar_arrive(&empty_bar[slot]);  // rows in registers, counter settled: release the ring slot
+      ODK_ASSERT((old >> 16) < (unsigned)kWarps && base + __popc(m) <= (unsigned)TILE);
       if (is_cand) {
+        ODK_ASSERT(cls >= 0 && cls < c && a < p.n);
         p.cand_keys[piece * TILE + base + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
         if (p.score_hist != nullptr) atomicAdd(p.score_hist + (size_t)b * ODK_HIST_BINS + odk_score_bin(conf), 1);
       }

@@ -57,69 +57,58 @@ constexpr int kRowsPerThread = 8;  // 16-byte stores per thread
 #define ODK_ROWS_PER_SM_DEFAULT 0
 #endif
 
-// y_true of one image is a contiguous array of N*W floats, all zero except column 0.  Each thread produces whole
-// 16-byte pieces of it in registers — a piece holds at most one column-0 element because W >= 8 — and stores them
-// with coalesced st.global.v4: no shared memory (the kernel co-resides with anything), nothing to wait for.
-// A thread's pieces are kRowsThreads*VEC floats apart; (row, column) of the first comes from one division, the
-// others by adding the constant step; the bitmap words of all pieces are loaded before the first store.
+// y_true of one image is a contiguous array of N*W floats, all zero except column 0.  A CTA owns a chunk of
+// kRowsThreads * kRowsPerThread 16-byte pieces and writes it in two phases:
+//   1. plain zero fill — coalesced st.global.v4, three instructions per store, no table lookups;
+//   2. after a CTA barrier (which orders the two stores to the same address), the column-0 element of every row whose
+//      first float lies in the chunk: a warp takes 32 consecutive rows, so ONE packed pb_mask word and ONE ignore word
+//      serve the whole warp, and a lane stores w0 only where the row is valid (the zero is already there).
+// The first version of this kernel derived (row, column, bitmap bit) for every 16-byte piece in registers: ~100
+// instructions per piece made it instruction-bound (ncu: math-pipe throttle, 22 us); this one issues ~1/8 of that and is
+// bound by the stores.  The 4-byte stores of phase 2 rewrite 1/27 of the sectors while they are still in L2.
 template <int VEC>
-__device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, unsigned chunk, unsigned step_rows, unsigned step_cols) {
+__device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, unsigned chunk) {
   const unsigned W = 3 + p.av.num_classes + 4;
   const unsigned n = (unsigned)p.av.n;
   const int g_count = p.gt_count[b];
   const bool count_ok = g_count >= 0 && g_count <= p.gmax;   // otherwise the image fails (patch kernel zeroes it)
   const float w0 = count_ok ? __fdiv_rn(1.0f, (float)max(1, g_count)) : 0.0f;  // float32(1/max(1,G)), od_pb.py:306
-  const unsigned* ign = p.ignore + (size_t)b * p.bitmap_words;
-  const unsigned* mb = p.av.maskbits;
   const unsigned total = n * W;  // floats per image (< 2^31, checked by the launcher)
   float* y = p.y_true + (size_t)b * total;
   const unsigned pieces = (total + VEC - 1) / VEC;
-  const unsigned i0 = chunk * (kRowsThreads * kRowsPerThread) + threadIdx.x;
-  unsigned row = (i0 * VEC) / W, col = (i0 * VEC) - row * W;
-  float w[kRowsPerThread];
-  int j[kRowsPerThread];
-#pragma unroll
-  for (int u = 0; u < kRowsPerThread; ++u) {
-    // the next column-0 element at or after this piece: offset jj within the piece, row r
-    const unsigned jj = (col == 0) ? 0u : W - col;
-    const unsigned r = (col == 0) ? row : row + 1;
-    const bool has = jj < (unsigned)VEC && r < n && (i0 + u * kRowsThreads) < pieces;
-    const unsigned rw = has ? (r >> 5) : 0u;
-    const unsigned bits = __ldg(mb + rw) & ign[rw];  // pb_mask and IoU >= 0.5 with some GT (od_pb.py:355-357)
-    w[u] = (has && !((bits >> (r & 31)) & 1u)) ? w0 : 0.0f;
-    j[u] = (int)jj;
-    row += step_rows;
-    col += step_cols;
-    if (col >= W) { col -= W; ++row; }
-  }
+  constexpr unsigned kChunkPieces = kRowsThreads * kRowsPerThread;
+  const unsigned i0 = chunk * kChunkPieces + threadIdx.x;
 #pragma unroll
   for (int u = 0; u < kRowsPerThread; ++u) {
     const unsigned i = i0 + u * kRowsThreads;
     if (i < pieces) {
-      if (VEC == 4)
-        reinterpret_cast<float4*>(y)[i] =
-            make_float4(j[u] == 0 ? w[u] : 0.f, j[u] == 1 ? w[u] : 0.f, j[u] == 2 ? w[u] : 0.f, j[u] == 3 ? w[u] : 0.f);
-      else
-        y[i] = w[u];
+      if (VEC == 4) reinterpret_cast<float4*>(y)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      else y[i] = 0.f;
     }
   }
-  if (p.pb_valids != nullptr) {
-#pragma unroll
-    for (int u = 0; u < kRowsPerThread; ++u) {
-      const unsigned a = i0 + u * kRowsThreads;
-      if (a < n) {
-        const unsigned bits = __ldg(mb + (a >> 5)) & ign[a >> 5];
-        p.pb_valids[(size_t)b * n + a] = (count_ok && !((bits >> (a & 31)) & 1u)) ? 1 : 0;
-      }
+  __syncthreads();
+  // rows whose column-0 float lies in [f0, f1)
+  const unsigned f0 = chunk * kChunkPieces * VEC;
+  const unsigned f1 = min(total, f0 + kChunkPieces * VEC);
+  const unsigned r0 = (f0 + W - 1) / W, r1 = (f1 + W - 1) / W;  // r * W >= f0  and  r * W < f1
+  const unsigned* ign = p.ignore + (size_t)b * p.bitmap_words;
+  const unsigned* mb = p.av.maskbits;
+  // aligned to 32 rows so that a warp reads one word of each bitmap
+  for (unsigned r = (r0 & ~31u) + threadIdx.x; r < r1; r += kRowsThreads) {
+    if (r >= r0) {
+      const unsigned bits = __ldg(mb + (r >> 5)) & ign[r >> 5];  // pb_mask and IoU >= 0.5 with some GT (od_pb.py:355-357)
+      const bool valid = count_ok && !((bits >> (r & 31)) & 1u);
+      if (valid) y[(size_t)r * W] = w0;
+      if (p.pb_valids != nullptr) p.pb_valids[(size_t)b * n + r] = valid ? 1 : 0;
     }
   }
 }
 
 // One CTA per chunk of kRowsThreads * kRowsPerThread pieces: grid (chunks per image, batch).
 template <int VEC>
-__global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeArgs p, unsigned step_rows, unsigned step_cols) {
+__global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeArgs p) {
   OdkTimeline tl_(ODK_TL_ROWS, p.tl);
-  encode_rows_chunk<VEC>(p, blockIdx.y, blockIdx.x, step_rows, step_cols);
+  encode_rows_chunk<VEC>(p, blockIdx.y, blockIdx.x);
 }
 
 // The same chunks walked by a bounded, persistent grid (a few CTAs per SM): the kernel then occupies a fixed share of
@@ -127,12 +116,11 @@ __global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeA
 // kernel launched after it, so the read-streaming kernel of the predict side and the latency-bound kernels of other
 // batches in flight find room beside it.
 template <int VEC>
-__global__ void __launch_bounds__(kRowsThreads) encode_rows_persistent_kernel(const EncodeArgs p, unsigned step_rows, unsigned step_cols,
-                                                                             unsigned chunks_per_image, unsigned total_chunks) {
+__global__ void __launch_bounds__(kRowsThreads) encode_rows_persistent_kernel(const EncodeArgs p, unsigned chunks_per_image, unsigned total_chunks) {
   OdkTimeline tl_(ODK_TL_ROWS, p.tl);
   for (unsigned item = blockIdx.x; item < total_chunks; item += gridDim.x) {
     const unsigned b = item / chunks_per_image;
-    encode_rows_chunk<VEC>(p, (int)b, item - b * chunks_per_image, step_rows, step_cols);
+    encode_rows_chunk<VEC>(p, (int)b, item - b * chunks_per_image);
   }
 }
 
@@ -268,7 +256,6 @@ int launch_rows(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
   const long long pieces = total / v;
   const long long per_cta = (long long)kRowsThreads * kRowsPerThread;
   const long long gx = (pieces + per_cta - 1) / per_cta;  // >= ceil(n / per_cta): the pb_valids loop is covered too
-  const unsigned step = (unsigned)(kRowsThreads * v);     // floats between a thread's consecutive pieces
   // ODK_ROWS_PER_SM = k > 0: persistent grid of k CTAs per SM; 0: one CTA per chunk
   static const int per_sm = getenv("ODK_ROWS_PER_SM") ? atoi(getenv("ODK_ROWS_PER_SM")) : ODK_ROWS_PER_SM_DEFAULT;
   const long long chunks = gx * e.batch;
@@ -277,12 +264,12 @@ int launch_rows(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
     OdkProfileScope prof_("encode_rows_kernel", stream);
     if (per_sm > 0 && chunks > (long long)rows_sm_count() * per_sm) {
       const unsigned grid = (unsigned)(rows_sm_count() * per_sm);
-      if (vec) encode_rows_persistent_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W, (unsigned)gx, (unsigned)chunks);
-      else encode_rows_persistent_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W, (unsigned)gx, (unsigned)chunks);
+      if (vec) encode_rows_persistent_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, (unsigned)gx, (unsigned)chunks);
+      else encode_rows_persistent_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, (unsigned)gx, (unsigned)chunks);
     } else {
       dim3 grid((unsigned)gx, (unsigned)e.batch);
-      if (vec) encode_rows_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W);
-      else encode_rows_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, step / W, step % W);
+      if (vec) encode_rows_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e);
+      else encode_rows_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e);
     }
   }
   ODK_LAUNCH_CHECK("encode_rows_kernel");

@@ -253,6 +253,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     for (int q = warp; q < p.n_pieces; q += kNmsWarps) {
       const int q_lo = s_pref[q], cnt = s_pref[q + 1] - q_lo;
       const unsigned long long* src = keys + (size_t)q * p.piece;
+      ODK_ASSERT(cnt >= 0 && cnt <= p.piece && q_lo + cnt <= p.cache_cap);
       for (int sl = lane; sl < cnt; sl += 32) odk_cp_async<8>(s_cache + q_lo + sl, src + sl);
     }
     odk_cp_async_commit();  // waited for just before the first pass that reads the cache (cache_ready below)
@@ -451,6 +452,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     {
       const unsigned wbits = (tid < ODK_MAX_CLASSES / 32) ? s_clsbits[tid] : 0u;
       int pos = block_exclusive_scan(__popc(wbits), s_scan, n_present);
+      ODK_ASSERT(pos + __popc(wbits) <= kBand);
       for (unsigned rem = wbits; rem; rem &= rem - 1) s_clslist[pos++] = (unsigned short)(tid * 32 + __ffs(rem) - 1);
     }
     __syncthreads();
@@ -463,6 +465,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
         const int i = base + lane;
         const bool is = i < nb && s_cls[i] == c;
         const unsigned m = __ballot_sync(0xffffffffu, is);
+        ODK_ASSERT(nm + __popc(m) <= kBand);
         if (is) mem[nm + __popc(m & ((1u << lane) - 1u))] = (unsigned short)i;
         nm += __popc(m);
       }
@@ -535,6 +538,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
         const int cls = odk_key2_class(my_key);
         const float4 bx = s_box[tid];
         const int r = nkept + pos;
+        ODK_ASSERT(r >= 0 && r < limit && a >= 0 && a < p.n);
         kbox[r] = bx;
         karea[r] = s_area[tid];
         kcls[r] = cls;
@@ -595,6 +599,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
             hit = pair_hit<GE>(s_box[sj], aj, aj * p.ft2.k_hi, aj * p.ft2.k_lo, bi, ai, p.iou_thr2, p.ft2, fast2);
           }
           const unsigned bits = __ballot_sync(0xffffffffu, hit);
+          ODK_ASSERT(nk1 <= kBand && (size_t)(i * nw + w) * 4 < (size_t)kNmsWarps * kBand * 2);
           if (lane == 0) M[i * nw + w] = bits;
         }
       }
@@ -619,6 +624,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
           }
           const int take = min(__popc(keep), room - rk);
           if (take < __popc(keep)) keep &= (1u << (__fns(keep, 0, take + 1) & 31)) - 1u;  // cut at top_k: drop from the (take+1)-th on
+          ODK_ASSERT(rk + __popc(keep) <= kBand);
           if ((keep >> lane) & 1u) rlist[rk + __popc(keep & ((1u << lane) - 1u))] = s_clslist[j];
           rk += take;
           if (lane > w && lane < nw)
@@ -633,6 +639,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
         const unsigned long long key = s_band[i];
         const float4 bx = s_box[i];
         const int r = nkept2 + tid;
+        ODK_ASSERT(r >= 0 && r < p.top_k);
         k2box[r] = bx;
         k2area[r] = s_area[i];
         if (p.out != nullptr) {

@@ -11,6 +11,17 @@
 
 #include "../../include/odk.h"
 
+// Device-side bounds assertions for the checks build (python -m object_detector_b200.build --checks ->
+// libodk_checks.so, selected with ODK_LIB_VARIANT=checks): compute-sanitizer is closed on this GPU pool, so the index
+// arithmetic of the shared-memory structures that are re-typed, bit-packed or written by several warps is guarded by
+// asserts that trap (and fail the CUDA call) instead.  Compiled out of the product library.
+#ifdef ODK_CHECKS
+#include <assert.h>
+#define ODK_ASSERT(cond) assert(cond)
+#else
+#define ODK_ASSERT(cond) ((void)0)
+#endif
+
 #define ODK_MAX_MAPS 8
 #define ODK_IDX_BITS 20                 // anchor index field of the sort keys (N < 2^20)
 #define ODK_IDX_MASK ((1u << ODK_IDX_BITS) - 1u)

@@ -1,0 +1,15 @@
+#!/bin/bash
+# The whole `-m gpu` suite against the checks build (libodk_checks.so: device-side bounds assertions, ODK_ASSERT in
+# csrc/odk_common.cuh) — the stand-in for compute-sanitizer, which is closed on this GPU pool.  A failed assertion traps
+# the kernel and fails the test with a CUDA error.   Usage: gpurun -- 'bash scripts/gpu_checks.sh'
+mkdir -p gpurun_out
+LOG=gpurun_out/checks_build.log
+echo "# ODK_LIB_VARIANT=checks python -m pytest tests -m gpu -q   (libodk_checks.so = same sources, -DODK_CHECKS=1)" > $LOG
+ODK_LIB_VARIANT=checks timeout 900 python -m pytest tests -m gpu -q -p no:cacheprovider >> $LOG 2>&1
+echo "exit $?" >> $LOG
+python - >> $LOG <<'PY'
+import subprocess
+out = subprocess.run(['cuobjdump', '-sass', 'object_detector_b200/libodk_checks.so'], capture_output=True, text=True).stdout
+print('assert call sites compiled into libodk_checks.so (BPT.TRAP / __assertfail):', out.count('__assertfail') + out.count('BPT.TRAP'))
+PY
+tail -6 $LOG

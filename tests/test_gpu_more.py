@@ -225,6 +225,85 @@ def test_host_pipeline_compact_and_fused_modes(prior_boxes, mode):
     ceiling.result(ceiling.submit(*(sets[0] if mode == 'compact' else sets[0][:3])))  # copies only: runs, returns buffers
 
 
+class _Guarded:
+    """Device buffer with 4 KB canary zones (0xA5) on both sides of the payload: an out-of-bounds WRITE by a kernel into
+    its neighbourhood shows up as a changed guard byte (compute-sanitizer is closed on this pool)."""
+    PAD = 4096
+
+    def __init__(self, shape, dtype, fill=None):
+        n = int(np.prod(shape)) * torch.empty((), dtype=dtype).element_size()
+        self.raw = torch.full((n + 2 * self.PAD,), 0xA5, dtype=torch.uint8, device='cuda')
+        self.t = self.raw[self.PAD:self.PAD + n].view(dtype).view(shape)
+        if fill is not None:
+            self.t.copy_(torch.as_tensor(fill).to(dtype).reshape(shape))
+
+    def intact(self):
+        return bool((self.raw[:self.PAD] == 0xA5).all()) and bool((self.raw[-self.PAD:] == 0xA5).all())
+
+
+@pytest.mark.parametrize('name,batch,gmax', [('voc640', 5, 33), ('odd7', 3, 5), ('mid80', 2, 9), ('tiny128', 7, 3), ('mid100', 3, 4)])
+def test_c_abi_writes_stay_inside_caller_buffers(prior_boxes, name, batch, gmax):
+    """Both fused entry points called straight through the C-ABI with every caller-owned buffer — inputs, outputs and the
+    WORKSPACES, sized exactly as odk_*_workspace_bytes says — between canary zones: no guard byte may change, and the
+    results equal the mirror's.  Odd batch sizes, ragged GT counts (incl. 0 and a crowded image), partial last tiles."""
+    pb = prior_boxes(name)
+    dev = torch.device('cuda', 0)
+    h, lib = pb._handle(dev), _lib.load()
+    n, c = len(pb), pb.num_classes
+    w = 3 + c + 4
+    boxes, classes, counts = synth.gt_batch(123, batch, gmax, c, crowded_every=2)
+    counts[0] = 0
+    objs, clfs, locs = synth.predictions(321, batch, n, c, clustered=True)
+    g = {k: _Guarded(sh, dt, fill) for k, (sh, dt, fill) in {
+        'boxes': ((batch, gmax, 4), torch.float32, boxes), 'classes': ((batch, gmax), torch.int32, classes), 'counts': ((batch,), torch.int32, counts),
+        'y': ((batch, n, w), torch.float32, None), 'pbi': ((batch, gmax), torch.int64, None), 'gti': ((batch, gmax), torch.int64, None),
+        'valids': ((batch, n), torch.uint8, None), 'status': ((batch,), torch.int32, None),
+        'ws_a': ((lib.odk_assign_workspace_bytes(h, batch, gmax),), torch.uint8, None),
+        'rows': ((batch, gmax, w), torch.float32, None), 'vbits': ((batch, (n + 31) // 32), torch.int32, None),
+        'objs': ((batch, n, 1), torch.float32, objs), 'clfs': ((batch, n, c), torch.float32, clfs), 'locs': ((batch, n, 4), torch.float32, locs),
+        'out': ((batch, 50, 6), torch.float32, None), 'kept': ((batch, 50), torch.int32, None),
+        'ws_n': ((lib.odk_nms_strict_workspace_bytes(batch, n, c, 50),), torch.uint8, None)}.items()}
+    st = torch.cuda.current_stream().cuda_stream
+    P = lambda k: g[k].t.data_ptr()  # noqa: E731
+    _lib.call('odk_assign_encode', h, batch, P('boxes'), P('classes'), P('counts'), gmax, P('y'), P('pbi'), P('gti'), P('valids'), P('status'),
+              P('ws_a'), g['ws_a'].t.numel(), st)
+    ref = pb.encode_truth_batch(boxes, classes, counts, want_valids=True)
+    assert torch.equal(g['y'].t, ref['y_true']) and torch.equal(g['pbi'].t, ref['pb_indices']) and torch.equal(g['valids'].t.bool(), ref['pb_valids'])
+    _lib.call('odk_assign_encode_compact', h, batch, P('boxes'), P('classes'), P('counts'), gmax, P('rows'), P('vbits'), P('pbi'), P('gti'),
+              P('status'), P('ws_a'), g['ws_a'].t.numel(), st)
+    for strict in (False, True):
+        args = (h, batch, P('objs'), P('clfs'), P('locs'), 0.01, 0.45) + ((0.5,) if strict else ()) + (50, 1, P('out'), P('kept'), P('ws_n'),
+                                                                                                 g['ws_n'].t.numel(), st)
+        _lib.call('odk_decode_nms_strict' if strict else 'odk_decode_nms', *args)
+        want = pb.decode_nms(objs, clfs, locs, top_k=50, nms_all_threshold=0.5 if strict else None)
+        assert torch.equal(g['out'].t, want)
+    torch.cuda.synchronize()
+    bad = [k for k, v in g.items() if not v.intact()]
+    assert not bad, f'guard zones overwritten around: {bad}'
+
+
+def test_repeated_launches_are_bit_identical(prior_boxes):
+    """Race detector of last resort (racecheck is closed on this pool): the kernels whose warps share shared-memory state
+    — packed slot counters and empty barriers in score_emit, the taken bitmap of the batched greedy walk, the re-typed
+    buffers of the strict NMS — must give bit-identical results on 25 back-to-back launches over the same inputs, eager
+    and with several launches in flight on different streams."""
+    pb = prior_boxes('voc640')
+    gt = [torch.from_numpy(x).cuda() for x in synth.gt_batch(9, 24, 48, 20, crowded_every=3)]
+    head = [torch.from_numpy(x).cuda() for x in synth.predictions(9, 24, len(pb), 20, clustered=True)]
+    y0 = pb.encode_truth_batch(*gt)
+    d0, k0 = pb.decode_nms(*head, return_index=True)
+    s0 = pb.decode_nms(*head, nms_all_threshold=0.5)
+    streams = [torch.cuda.Stream() for _ in range(3)]
+    for it in range(25):
+        with torch.cuda.stream(streams[it % 3]):
+            y = pb.encode_truth_batch(*gt)
+            d, k = pb.decode_nms(*head, return_index=True)
+            s = pb.decode_nms(*head, nms_all_threshold=0.5)
+        streams[it % 3].synchronize()
+        assert torch.equal(y['y_true'], y0['y_true']) and torch.equal(y['pb_indices'], y0['pb_indices']), it
+        assert torch.equal(d, d0) and torch.equal(k, k0) and torch.equal(s, s0), it
+
+
 def _score_objects(seed, n_img, classes, **kw):
     gts, preds = synth.eval_set(seed, n_img, classes, **kw)
     y_true = [odk.ml.ObjectsAnnotation('.', w, h, c, b, d) for (w, h, c, b, d) in gts]
