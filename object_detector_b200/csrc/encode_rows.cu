@@ -58,16 +58,17 @@ constexpr int kRowsPerThread = 8;  // 16-byte stores per thread
 #endif
 
 // y_true of one image is a contiguous array of N*W floats, all zero except column 0.  A CTA owns a chunk of
-// kRowsThreads * kRowsPerThread 16-byte pieces and writes it in two phases:
-//   1. plain zero fill — coalesced st.global.v4, three instructions per store, no table lookups;
-//   2. after a CTA barrier (which orders the two stores to the same address), the column-0 element of every row whose
-//      first float lies in the chunk: a warp takes 32 consecutive rows, so ONE packed pb_mask word and ONE ignore word
-//      serve the whole warp, and a lane stores w0 only where the row is valid (the zero is already there).
-// The first version of this kernel derived (row, column, bitmap bit) for every 16-byte piece in registers: ~100
-// instructions per piece made it instruction-bound (ncu: math-pipe throttle, 22 us); this one issues ~1/8 of that and is
-// bound by the stores.  The 4-byte stores of phase 2 rewrite 1/27 of the sectors while they are still in L2.
+// kRowsThreads * kRowsPerThread 16-byte pieces and writes it in two independent passes (no piece is written twice, so
+// no ordering between them is needed):
+//   1. zero fill of the pieces that hold no column-0 element — a piece holds one iff its first float sits at column 0
+//      or in the last three columns of a row (W >= 8), which costs one add, one wrap and two compares per piece;
+//   2. the pieces that do hold one, visited BY ROW: a warp takes 32 consecutive rows, so ONE packed pb_mask word and
+//      ONE ignore word serve the whole warp; a lane builds its row's piece (w0 at the right lane, zeros around it).
+// The first version of this kernel derived (row, column, bitmap word, bit) for every piece in registers: ~100
+// instructions per 16 bytes made it instruction-bound (ncu: math-pipe throttle, 22 us at B = 64); a zero-fill pass
+// followed by 4-byte column-0 stores needed a CTA barrier in between, which waits for the outstanding global stores.
 template <int VEC>
-__device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, unsigned chunk) {
+__device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, unsigned chunk, unsigned step_cols) {
   const unsigned W = 3 + p.av.num_classes + 4;
   const unsigned n = (unsigned)p.av.n;
   const int g_count = p.gt_count[b];
@@ -78,16 +79,19 @@ __device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, un
   const unsigned pieces = (total + VEC - 1) / VEC;
   constexpr unsigned kChunkPieces = kRowsThreads * kRowsPerThread;
   const unsigned i0 = chunk * kChunkPieces + threadIdx.x;
+  unsigned col = (i0 * VEC) % W;  // column of the piece's first float; consecutive pieces of a thread are step_cols (mod W) apart
 #pragma unroll
   for (int u = 0; u < kRowsPerThread; ++u) {
     const unsigned i = i0 + u * kRowsThreads;
-    if (i < pieces) {
+    const bool has = (col == 0u) || (VEC > 1 && col > W - VEC);
+    if (i < pieces && !has) {
       if (VEC == 4) reinterpret_cast<float4*>(y)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
       else y[i] = 0.f;
     }
+    col += step_cols;
+    if (col >= W) col -= W;
   }
-  __syncthreads();
-  // rows whose column-0 float lies in [f0, f1)
+  // rows whose column-0 float lies in a piece of this chunk: pieces [chunk * kChunkPieces, +kChunkPieces)
   const unsigned f0 = chunk * kChunkPieces * VEC;
   const unsigned f1 = min(total, f0 + kChunkPieces * VEC);
   const unsigned r0 = (f0 + W - 1) / W, r1 = (f1 + W - 1) / W;  // r * W >= f0  and  r * W < f1
@@ -98,7 +102,14 @@ __device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, un
     if (r >= r0) {
       const unsigned bits = __ldg(mb + (r >> 5)) & ign[r >> 5];  // pb_mask and IoU >= 0.5 with some GT (od_pb.py:355-357)
       const bool valid = count_ok && !((bits >> (r & 31)) & 1u);
-      if (valid) y[(size_t)r * W] = w0;
+      const float w = valid ? w0 : 0.0f;
+      const unsigned f = r * W;  // the row's first float
+      if (VEC == 4) {
+        const unsigned j = f & 3u;
+        reinterpret_cast<float4*>(y)[f >> 2] = make_float4(j == 0 ? w : 0.f, j == 1 ? w : 0.f, j == 2 ? w : 0.f, j == 3 ? w : 0.f);
+      } else {
+        y[f] = w;
+      }
       if (p.pb_valids != nullptr) p.pb_valids[(size_t)b * n + r] = valid ? 1 : 0;
     }
   }
@@ -106,9 +117,9 @@ __device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, un
 
 // One CTA per chunk of kRowsThreads * kRowsPerThread pieces: grid (chunks per image, batch).
 template <int VEC>
-__global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeArgs p) {
+__global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeArgs p, unsigned step_cols) {
   OdkTimeline tl_(ODK_TL_ROWS, p.tl);
-  encode_rows_chunk<VEC>(p, blockIdx.y, blockIdx.x);
+  encode_rows_chunk<VEC>(p, blockIdx.y, blockIdx.x, step_cols);
 }
 
 // The same chunks walked by a bounded, persistent grid (a few CTAs per SM): the kernel then occupies a fixed share of
@@ -116,11 +127,12 @@ __global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeA
 // kernel launched after it, so the read-streaming kernel of the predict side and the latency-bound kernels of other
 // batches in flight find room beside it.
 template <int VEC>
-__global__ void __launch_bounds__(kRowsThreads) encode_rows_persistent_kernel(const EncodeArgs p, unsigned chunks_per_image, unsigned total_chunks) {
+__global__ void __launch_bounds__(kRowsThreads) encode_rows_persistent_kernel(const EncodeArgs p, unsigned step_cols, unsigned chunks_per_image,
+                                                                             unsigned total_chunks) {
   OdkTimeline tl_(ODK_TL_ROWS, p.tl);
   for (unsigned item = blockIdx.x; item < total_chunks; item += gridDim.x) {
     const unsigned b = item / chunks_per_image;
-    encode_rows_chunk<VEC>(p, (int)b, item - b * chunks_per_image);
+    encode_rows_chunk<VEC>(p, (int)b, item - b * chunks_per_image, step_cols);
   }
 }
 
@@ -255,7 +267,8 @@ int launch_rows(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
   const int v = vec ? 4 : 1;
   const long long pieces = total / v;
   const long long per_cta = (long long)kRowsThreads * kRowsPerThread;
-  const long long gx = (pieces + per_cta - 1) / per_cta;  // >= ceil(n / per_cta): the pb_valids loop is covered too
+  const long long gx = (pieces + per_cta - 1) / per_cta;
+  const unsigned step_cols = (unsigned)((kRowsThreads * v) % W);  // column advance between a thread's consecutive pieces
   // ODK_ROWS_PER_SM = k > 0: persistent grid of k CTAs per SM; 0: one CTA per chunk
   static const int per_sm = getenv("ODK_ROWS_PER_SM") ? atoi(getenv("ODK_ROWS_PER_SM")) : ODK_ROWS_PER_SM_DEFAULT;
   const long long chunks = gx * e.batch;
@@ -264,12 +277,12 @@ int launch_rows(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
     OdkProfileScope prof_("encode_rows_kernel", stream);
     if (per_sm > 0 && chunks > (long long)rows_sm_count() * per_sm) {
       const unsigned grid = (unsigned)(rows_sm_count() * per_sm);
-      if (vec) encode_rows_persistent_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, (unsigned)gx, (unsigned)chunks);
-      else encode_rows_persistent_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, (unsigned)gx, (unsigned)chunks);
+      if (vec) encode_rows_persistent_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, step_cols, (unsigned)gx, (unsigned)chunks);
+      else encode_rows_persistent_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, step_cols, (unsigned)gx, (unsigned)chunks);
     } else {
       dim3 grid((unsigned)gx, (unsigned)e.batch);
-      if (vec) encode_rows_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e);
-      else encode_rows_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e);
+      if (vec) encode_rows_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, step_cols);
+      else encode_rows_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, step_cols);
     }
   }
   ODK_LAUNCH_CHECK("encode_rows_kernel");

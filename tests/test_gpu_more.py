@@ -5,7 +5,7 @@ import pytest
 import torch
 
 import object_detector_b200 as odk
-from object_detector_b200 import pipeline, synth
+from object_detector_b200 import _lib, pipeline, synth
 from oracle import restated as R
 
 pytestmark = pytest.mark.gpu
