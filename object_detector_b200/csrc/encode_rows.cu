@@ -58,17 +58,19 @@ constexpr int kRowsPerThread = 8;  // 16-byte stores per thread
 #endif
 
 // y_true of one image is a contiguous array of N*W floats, all zero except column 0.  A CTA owns a chunk of
-// kRowsThreads * kRowsPerThread 16-byte pieces and writes it in two independent passes (no piece is written twice, so
-// no ordering between them is needed):
-//   1. zero fill of the pieces that hold no column-0 element — a piece holds one iff its first float sits at column 0
-//      or in the last three columns of a row (W >= 8), which costs one add, one wrap and two compares per piece;
-//   2. the pieces that do hold one, visited BY ROW: a warp takes 32 consecutive rows, so ONE packed pb_mask word and
-//      ONE ignore word serve the whole warp; a lane builds its row's piece (w0 at the right lane, zeros around it).
-// The first version of this kernel derived (row, column, bitmap word, bit) for every piece in registers: ~100
-// instructions per 16 bytes made it instruction-bound (ncu: math-pipe throttle, 22 us at B = 64); a zero-fill pass
-// followed by 4-byte column-0 stores needed a CTA barrier in between, which waits for the outstanding global stores.
+// kRowsThreads * kRowsPerThread 16-byte pieces; every piece is stored exactly once, whole, by fully coalesced
+// st.global.v4 (a warp instruction covers 512 contiguous bytes: only full sectors reach L2 — a variant that left the
+// column-0 pieces to a second pass wrote half sectors and ran 50 % slower).
+//   A. by ROW: the rows whose first float lies in the chunk (~kChunkPieces * 4 / W of them).  A warp takes 32
+//      consecutive rows, so ONE packed pb_mask word and ONE ignore word serve the whole warp; a valid row sets the bit
+//      of the piece that holds its column-0 float in a 256-byte shared-memory bitmap (one bit per piece of the chunk).
+//   B. by PIECE: a piece holds a column-0 float iff its first float sits at column 0 or in the last three columns of
+//      a row (W >= 8) — one add, one wrap, two compares from the running column; the bitmap word a warp needs is the
+//      same for all its lanes (bit = lane), so the lookup is one broadcast shared-memory load per store.
+// The first version derived (row, bitmap word, bit) per piece from global tables: ~75 instructions per 16 bytes made the
+// kernel instruction-bound (ncu: math-pipe throttle 20 %, 22 us at B = 64).
 template <int VEC>
-__device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, unsigned chunk, unsigned step_cols) {
+__device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, unsigned chunk, unsigned step_cols, unsigned* s_bits) {
   const unsigned W = 3 + p.av.num_classes + 4;
   const unsigned n = (unsigned)p.av.n;
   const int g_count = p.gt_count[b];
@@ -78,40 +80,46 @@ __device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, un
   float* y = p.y_true + (size_t)b * total;
   const unsigned pieces = (total + VEC - 1) / VEC;
   constexpr unsigned kChunkPieces = kRowsThreads * kRowsPerThread;
+  static_assert(kChunkPieces / 32 <= kRowsThreads, "one thread per bitmap word");
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  // ---- A. piece bitmap of the chunk
+  if (threadIdx.x < kChunkPieces / 32) s_bits[threadIdx.x] = 0u;
+  __syncthreads();
+  const unsigned f0 = chunk * kChunkPieces * VEC;
+  const unsigned f1 = min(total, f0 + kChunkPieces * VEC);
+  const unsigned r0 = (f0 + W - 1) / W, r1 = (f1 + W - 1) / W;  // rows with f0 <= r * W < f1
+  const unsigned* ign = p.ignore + (size_t)b * p.bitmap_words;
+  const unsigned* mb = p.av.maskbits;
+  for (unsigned r = (r0 & ~31u) + threadIdx.x; r < r1; r += kRowsThreads) {  // aligned to 32 rows: one word of each table per warp
+    if (r >= r0) {
+      const unsigned bits = __ldg(mb + (r >> 5)) & ign[r >> 5];  // pb_mask and IoU >= 0.5 with some GT (od_pb.py:355-357)
+      const bool valid = count_ok && !((bits >> (r & 31)) & 1u);
+      if (valid) {
+        const unsigned pl = (r * W - f0) / VEC;  // the piece of the chunk that holds the row's first float
+        atomicOr(&s_bits[pl >> 5], 1u << (pl & 31));
+      }
+      if (p.pb_valids != nullptr) p.pb_valids[(size_t)b * n + r] = valid ? 1 : 0;
+    }
+  }
+  __syncthreads();
+  // ---- B. the stores.  Piece u of this thread is number u * kRowsThreads + threadIdx.x of the chunk: word u * 8 + warp, bit lane
   const unsigned i0 = chunk * kChunkPieces + threadIdx.x;
   unsigned col = (i0 * VEC) % W;  // column of the piece's first float; consecutive pieces of a thread are step_cols (mod W) apart
 #pragma unroll
   for (int u = 0; u < kRowsPerThread; ++u) {
     const unsigned i = i0 + u * kRowsThreads;
     const bool has = (col == 0u) || (VEC > 1 && col > W - VEC);
-    if (i < pieces && !has) {
-      if (VEC == 4) reinterpret_cast<float4*>(y)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-      else y[i] = 0.f;
+    const bool on = has && ((s_bits[u * (kRowsThreads / 32) + warp] >> lane) & 1u);
+    const float w = on ? w0 : 0.0f;
+    const unsigned jj = (col == 0u) ? 0u : W - col;  // position of the column-0 float inside the piece
+    if (i < pieces) {
+      if (VEC == 4)
+        reinterpret_cast<float4*>(y)[i] = make_float4(jj == 0 ? w : 0.f, jj == 1 ? w : 0.f, jj == 2 ? w : 0.f, jj == 3 ? w : 0.f);
+      else
+        y[i] = w;
     }
     col += step_cols;
     if (col >= W) col -= W;
-  }
-  // rows whose column-0 float lies in a piece of this chunk: pieces [chunk * kChunkPieces, +kChunkPieces)
-  const unsigned f0 = chunk * kChunkPieces * VEC;
-  const unsigned f1 = min(total, f0 + kChunkPieces * VEC);
-  const unsigned r0 = (f0 + W - 1) / W, r1 = (f1 + W - 1) / W;  // r * W >= f0  and  r * W < f1
-  const unsigned* ign = p.ignore + (size_t)b * p.bitmap_words;
-  const unsigned* mb = p.av.maskbits;
-  // aligned to 32 rows so that a warp reads one word of each bitmap
-  for (unsigned r = (r0 & ~31u) + threadIdx.x; r < r1; r += kRowsThreads) {
-    if (r >= r0) {
-      const unsigned bits = __ldg(mb + (r >> 5)) & ign[r >> 5];  // pb_mask and IoU >= 0.5 with some GT (od_pb.py:355-357)
-      const bool valid = count_ok && !((bits >> (r & 31)) & 1u);
-      const float w = valid ? w0 : 0.0f;
-      const unsigned f = r * W;  // the row's first float
-      if (VEC == 4) {
-        const unsigned j = f & 3u;
-        reinterpret_cast<float4*>(y)[f >> 2] = make_float4(j == 0 ? w : 0.f, j == 1 ? w : 0.f, j == 2 ? w : 0.f, j == 3 ? w : 0.f);
-      } else {
-        y[f] = w;
-      }
-      if (p.pb_valids != nullptr) p.pb_valids[(size_t)b * n + r] = valid ? 1 : 0;
-    }
   }
 }
 
@@ -119,7 +127,8 @@ __device__ __forceinline__ void encode_rows_chunk(const EncodeArgs& p, int b, un
 template <int VEC>
 __global__ void __launch_bounds__(kRowsThreads) encode_rows_kernel(const EncodeArgs p, unsigned step_cols) {
   OdkTimeline tl_(ODK_TL_ROWS, p.tl);
-  encode_rows_chunk<VEC>(p, blockIdx.y, blockIdx.x, step_cols);
+  __shared__ unsigned s_bits[kRowsThreads * kRowsPerThread / 32];
+  encode_rows_chunk<VEC>(p, blockIdx.y, blockIdx.x, step_cols, s_bits);
 }
 
 // The same chunks walked by a bounded, persistent grid (a few CTAs per SM): the kernel then occupies a fixed share of
@@ -130,9 +139,11 @@ template <int VEC>
 __global__ void __launch_bounds__(kRowsThreads) encode_rows_persistent_kernel(const EncodeArgs p, unsigned step_cols, unsigned chunks_per_image,
                                                                              unsigned total_chunks) {
   OdkTimeline tl_(ODK_TL_ROWS, p.tl);
-  for (unsigned item = blockIdx.x; item < total_chunks; item += gridDim.x) {
+  __shared__ unsigned s_bits[2][kRowsThreads * kRowsPerThread / 32];  // alternating: a chunk's stores may still read while the next is built
+  unsigned k = 0;
+  for (unsigned item = blockIdx.x; item < total_chunks; item += gridDim.x, k ^= 1u) {
     const unsigned b = item / chunks_per_image;
-    encode_rows_chunk<VEC>(p, (int)b, item - b * chunks_per_image, step_cols);
+    encode_rows_chunk<VEC>(p, (int)b, item - b * chunks_per_image, step_cols, s_bits[k]);
   }
 }
 

@@ -40,6 +40,12 @@ constexpr int kDigitBits = 11;
 constexpr int kBins = 1 << kDigitBits;
 constexpr int kCollectPiece = 256;
 constexpr int kMaxPieces = 8192;
+// per-warp member lists [kNmsWarps][kBand] u16; in strict mode the same area is re-typed as the suppression bit matrix
+// M [kBand][kBand / 32] u32 of the all-class stage, which is larger (found by the checks build: the matrix used to overrun
+// the lists' 16 KB into the key cache once a band had more than ~360 class-stage survivors)
+constexpr size_t kMemberBytes = (size_t)kNmsWarps * kBand * 2;
+constexpr size_t kMatrixBytes = (size_t)kBand * (kBand / 32) * 4;
+constexpr size_t member_area_bytes(bool strict) { return strict && kMatrixBytes > kMemberBytes ? kMatrixBytes : kMemberBytes; }
 
 // ---- candidate collection for the unfused entries (layers.py:935) ----------------------------------------
 // One CTA = one piece of 256 anchors, same piece format as score_emit_kernel.
@@ -222,7 +228,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
   int* s_pref = reinterpret_cast<int*>(dyn);                              // [n_pieces + 1]
   dyn += odk_align_up(sizeof(int) * ((size_t)p.n_pieces + 1), 16);
   unsigned short* s_member = reinterpret_cast<unsigned short*>(dyn);      // [kNmsWarps][kBand]
-  dyn += (size_t)kNmsWarps * kBand * 2;
+  dyn += member_area_bytes(STRICT);
   unsigned long long* s_cache = reinterpret_cast<unsigned long long*>(dyn);  // [cache_cap] all candidate keys of the image
   const bool fast = GE && p.ft.enabled;  // the fast form needs positive-extent boxes: guaranteed by the zero-area skip
 
@@ -599,7 +605,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
             hit = pair_hit<GE>(s_box[sj], aj, aj * p.ft2.k_hi, aj * p.ft2.k_lo, bi, ai, p.iou_thr2, p.ft2, fast2);
           }
           const unsigned bits = __ballot_sync(0xffffffffu, hit);
-          ODK_ASSERT(nk1 <= kBand && (size_t)(i * nw + w) * 4 < (size_t)kNmsWarps * kBand * 2);
+          ODK_ASSERT(nk1 <= kBand && (size_t)(i * nw + w) * 4 < member_area_bytes(STRICT));
           if (lane == 0) M[i * nw + w] = bits;
         }
       }
@@ -740,7 +746,7 @@ static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch,
   a.limit = limit; a.top_k = top_k; a.skip_empty = iou_ge ? 1 : 0;
   a.out = out; a.kept_index = kept_index; a.out_index = out_index; a.out_count = out_count;
   const size_t fixed = odk_align_up((size_t)(limit < 1 ? 1 : limit) * 24, 16) + odk_align_up(sizeof(int) * ((size_t)a.n_pieces + 1), 16) +
-                       (size_t)kNmsWarps * kBand * 2 + (strict ? odk_align_up((size_t)(top_k < 1 ? 1 : top_k) * 20, 16) : 0);
+                       member_area_bytes(strict) + (strict ? odk_align_up((size_t)(top_k < 1 ? 1 : top_k) * 20, 16) : 0);
   a.cache_cap = n < 8192 ? n : 8192;
   if (fixed + (size_t)a.cache_cap * 8 > 180 * 1024) a.cache_cap = 0;
   const size_t smem = fixed + (size_t)a.cache_cap * 8;

@@ -423,6 +423,25 @@ def test_strict_nms_layer_class_limit_and_spill(strict_cap_case):
     assert 1 <= int((rk >= 0).sum()) <= 40  # a handful per place survive the class-agnostic pass
 
 
+def test_strict_nms_full_band_of_class_survivors_multi_round():
+    """Regression for an overrun the checks build found (csrc/nms.cu, suppression bit matrix of the all-class stage): 600
+    places x 4 classes with identical boxes — the class stage keeps every box (no same-class overlap), so a band holds
+    up to 512 class-stage survivors (a 32 KB bit matrix), and the all-class stage keeps one box per place, so reaching
+    top_k = 200 takes several rounds, whose keys come from the shared-memory cache the matrix used to overwrite."""
+    rng = np.random.RandomState(17)
+    places = 600
+    gx, gy = np.meshgrid(np.arange(30), np.arange(20))
+    c = np.stack([gx.ravel(), gy.ravel()], axis=1)[:places] / np.array([30.0, 20.0]) + 0.01
+    one = np.concatenate([c, c + np.array([0.025, 0.04])], axis=1).astype(np.float32)
+    boxes = np.repeat(one, 4, axis=0)[None]                      # (1, 2400, 4): four identical boxes per place
+    classes = np.tile(np.arange(4), places)[None].astype(np.int32)
+    confs = rng.permutation(places * 4).astype(np.float32)[None] / (places * 4) * 0.9 + 0.05
+    out, kept = odk.layers.nms()(4, places * 4, nms_all_threshold=0.5)([classes, confs, boxes], return_index=True)
+    ro, rk = R.nms_layer_image(classes[0], confs[0], boxes[0], 4, nms_all_threshold=0.5)
+    assert int((rk >= 0).sum()) == 200
+    assert np.array_equal(kept[0], rk) and np.array_equal(out[0], ro)
+
+
 def test_predict_from_head_strict_flag(prior_boxes, oracle_tables):
     od = odk.ObjectDetector.load_voc((320, 320))
     assert od.strict_nms is True  # od.py:81 default
