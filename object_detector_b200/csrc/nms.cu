@@ -45,7 +45,7 @@ constexpr int kMaxPieces = 8192;
 // the lists' 16 KB into the key cache once a band had more than ~360 class-stage survivors)
 constexpr size_t kMemberBytes = (size_t)kNmsWarps * kBand * 2;
 constexpr size_t kMatrixBytes = (size_t)kBand * (kBand / 32) * 4;
-constexpr size_t member_area_bytes(bool strict) { return strict && kMatrixBytes > kMemberBytes ? kMatrixBytes : kMemberBytes; }
+__host__ __device__ constexpr size_t member_area_bytes(bool strict) { return strict && kMatrixBytes > kMemberBytes ? kMatrixBytes : kMemberBytes; }
 
 // ---- candidate collection for the unfused entries (layers.py:935) ----------------------------------------
 // One CTA = one piece of 256 anchors, same piece format as score_emit_kernel.
