@@ -54,7 +54,7 @@ struct EncodeArgs {
 constexpr int kRowsThreads = 256;
 constexpr int kRowsPerThread = 8;  // 16-byte stores per thread
 #ifndef ODK_ROWS_PER_SM_DEFAULT
-#define ODK_ROWS_PER_SM_DEFAULT 0
+#define ODK_ROWS_PER_SM_DEFAULT 4  // persistent grid: profiles/sweep_r02m.log (step 41.95 -> 40.97 us with batches in flight)
 #endif
 
 // y_true of one image is a contiguous array of N*W floats, all zero except column 0.  A CTA owns a chunk of

@@ -188,7 +188,10 @@ __device__ __forceinline__ unsigned long long block_sort_desc_1(unsigned long lo
   return key;
 }
 
-template <bool GE, bool STRICT>
+// BIG: instantiation for images with so many anchors that the candidate keys rarely fit the shared-memory cache (the
+// dense-anchor stress shape): no cache, and the passes over the keys keep 16 pieces in flight per warp instead of 4 (more
+// registers: kept out of the instantiation that shares its SM with the streaming kernels of other batches).
+template <bool GE, bool STRICT, bool BIG>
 __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs p) {
   OdkTimeline tl_(ODK_TL_NMS, p.tl);
   static_assert(kBand <= kNmsThreads && ODK_MAX_CLASSES / 32 <= kNmsThreads, "one band slot / class word per thread");
@@ -252,7 +255,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
   }
   // The image's keys are pulled into shared memory once when they fit (every later pass is on-chip);
   // otherwise each pass reads them from L2 through the piece prefix sums.
-  const bool cached = total <= p.cache_cap;
+  const bool cached = !BIG && total <= p.cache_cap;
   if (cached) {
     // fire-and-forget 8-byte async copies: every key of the image is in flight at once.  A warp takes a piece, its
     // lanes the piece's entries (pieces are mostly sparse: the loop runs over what is there, not over the slots)
@@ -274,12 +277,13 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
   };
   // Visits every candidate key of the image once (any thread, any order).  Cached: a strided walk over shared memory.
   // Not cached (more candidates than the cache holds, e.g. 57 k per image in the dense-anchor stress shape): a warp takes
-  // four pieces at a time and its lanes the pieces' entries — coalesced 8-byte loads from L2, no index search.
+  // sixteen pieces at a time and its lanes the pieces' entries — coalesced 8-byte loads from L2, no index search.
   auto for_each_key = [&](auto&& f) {
     if (cached) {
       for (int i = tid; i < total; i += kNmsThreads) f(s_cache[i]);
     } else {
-      constexpr int kU = 4;  // pieces in flight per warp: their loads are independent, the L2 round trips overlap
+      constexpr int kU = BIG ? 16 : 4;  // pieces in flight per warp: their loads are independent, the L2 round trips overlap (a pass over the
+                              // 3 216 pieces of a stress-shape image is 4 such round trips per warp instead of 13 at kU = 4)
       for (int q0 = warp * kU; q0 < p.n_pieces; q0 += kNmsWarps * kU) {
         int cnt[kU], maxc = 0;
 #pragma unroll
@@ -749,10 +753,15 @@ static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch,
                        member_area_bytes(strict) + (strict ? odk_align_up((size_t)(top_k < 1 ? 1 : top_k) * 20, 16) : 0);
   a.cache_cap = n < 8192 ? n : 8192;
   if (fixed + (size_t)a.cache_cap * 8 > 180 * 1024) a.cache_cap = 0;
+  const bool big = n >= 65536;
+  if (big) a.cache_cap = 0;
   const size_t smem = fixed + (size_t)a.cache_cap * 8;
   ODK_REQUIRE(smem <= 180 * 1024, ODK_ERR_UNSUPPORTED, "nms: top_k=%d / %d pieces need %zu bytes of shared memory", top_k, a.n_pieces, smem);
-  auto kern = strict ? (iou_ge ? nms_image_kernel<true, true> : nms_image_kernel<false, true>)
-                     : (iou_ge ? nms_image_kernel<true, false> : nms_image_kernel<false, false>);
+  void (*kern)(const NmsArgs) = nullptr;
+  if (big) kern = strict ? (iou_ge ? nms_image_kernel<true, true, true> : nms_image_kernel<false, true, true>)
+                         : (iou_ge ? nms_image_kernel<true, false, true> : nms_image_kernel<false, false, true>);
+  else kern = strict ? (iou_ge ? nms_image_kernel<true, true, false> : nms_image_kernel<false, true, false>)
+                     : (iou_ge ? nms_image_kernel<true, false, false> : nms_image_kernel<false, false, false>);
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 180 * 1024));
   {
     OdkProfileScope prof_(strict ? "nms_image_kernel_strict" : "nms_image_kernel", stream);

@@ -7,9 +7,5 @@ LOG=gpurun_out/checks_build.log
 echo "# ODK_LIB_VARIANT=checks python -m pytest tests -m gpu -q   (libodk_checks.so = same sources, -DODK_CHECKS=1)" > $LOG
 ODK_LIB_VARIANT=checks timeout 900 python -m pytest tests -m gpu -q -p no:cacheprovider >> $LOG 2>&1
 echo "exit $?" >> $LOG
-python - >> $LOG <<'PY'
-import subprocess
-out = subprocess.run(['cuobjdump', '-sass', 'object_detector_b200/libodk_checks.so'], capture_output=True, text=True).stdout
-print('assert call sites compiled into libodk_checks.so (BPT.TRAP / __assertfail):', out.count('__assertfail') + out.count('BPT.TRAP'))
-PY
+echo "ODK_ASSERT sites in the sources: $(cat object_detector_b200/csrc/*.cu | grep -c ODK_ASSERT)" >> $LOG
 tail -6 $LOG
