@@ -389,7 +389,7 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   int per_sm = (int)((220 * 1024) / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 2048 / (TILE * SPLIT + 32) ? 2048 / (TILE * SPLIT + 32) : per_sm);
   // EMIT runs beside the train-side kernels of the same step (other graph branch): leave them shared memory
-  if (!DENSE && per_sm > 2) per_sm = 2;
+  if (!DENSE && per_sm > (SPLIT > 1 ? 3 : 2)) per_sm = SPLIT > 1 ? 3 : 2;  // wide class vectors: more rows in flight per SM
   if (!DENSE && env_per_sm > 0) per_sm = env_per_sm;
   long long grid = (long long)sm_count_cached() * per_sm;
   if (grid > total) grid = total;

@@ -286,7 +286,9 @@ int launch_rows(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
   ODK_REQUIRE(chunks < 0x7fffffffLL, ODK_ERR_UNSUPPORTED, "assign_encode: %lld row chunks", chunks);
   {
     OdkProfileScope prof_("encode_rows_kernel", stream);
-    if (per_sm > 0 && chunks > (long long)rows_sm_count() * per_sm) {
+    // a launch of up to ~16 chunks per persistent CTA shares the SMs with whatever runs beside it; a larger one (B = 256,
+    // the stress shape) is better off with one CTA per chunk and every thread slot (profiles/bench_r02n.json: cfg3 141 vs 107 us)
+    if (per_sm > 0 && chunks > (long long)rows_sm_count() * per_sm && chunks <= (long long)rows_sm_count() * per_sm * 16) {
       const unsigned grid = (unsigned)(rows_sm_count() * per_sm);
       if (vec) encode_rows_persistent_kernel<4><<<grid, kRowsThreads, 0, stream>>>(e, step_cols, (unsigned)gx, (unsigned)chunks);
       else encode_rows_persistent_kernel<1><<<grid, kRowsThreads, 0, stream>>>(e, step_cols, (unsigned)gx, (unsigned)chunks);
