@@ -28,6 +28,22 @@ def _enqueue_step(pb, gt, head, y_true, dets, side, kw):
         pb.decode_nms(*head, out=dets, **kw)
 
 
+def _enqueue_group(pb, slots, branch, side, kw):
+    """The steps of ``slots`` relative to the current stream: slot 0 on it, every other slot on its own branch stream
+    (forked from / joined to the current stream), within a slot the predict side on ``side[k]`` if given."""
+    dev = slots[0][2].device
+    main = torch.cuda.current_stream(dev)
+    for k, (gt, head, y, d) in enumerate(slots):
+        if k == 0:
+            continue
+        branch[k - 1].wait_stream(main)
+        with torch.cuda.stream(branch[k - 1]):
+            _enqueue_step(pb, gt, head, y, d, side[k], kw)
+    _enqueue_step(pb, *slots[0], side[0], kw)
+    for st in branch[:len(slots) - 1]:
+        main.wait_stream(st)
+
+
 def capture_steps(pb, slots, top_k=200, conf_threshold=0.01, nms_threshold=0.45, two_streams=True, nms_all_threshold=None):
     """Captures the steps of all ``slots`` = [(gt, head, y_true, dets)] into ONE CUDA graph, every slot on its own
     branch (and within a slot the train and the predict side on parallel branches when ``two_streams``): one host
@@ -42,16 +58,7 @@ def capture_steps(pb, slots, top_k=200, conf_threshold=0.01, nms_threshold=0.45,
         side = [torch.cuda.Stream(device=dev) if two_streams else None for _ in slots]
     graph = torch.cuda.CUDAGraph()
     with torch.cuda.device(dev), torch.cuda.graph(graph):
-        main = torch.cuda.current_stream(dev)
-        for k, (gt, head, y, d) in enumerate(slots):
-            if k == 0:
-                continue
-            branch[k - 1].wait_stream(main)
-            with torch.cuda.stream(branch[k - 1]):
-                _enqueue_step(pb, gt, head, y, d, side[k], kw)
-        _enqueue_step(pb, *slots[0], side[0], kw)
-        for st in branch:
-            main.wait_stream(st)
+        _enqueue_group(pb, slots, branch, side, kw)
     return graph
 
 
@@ -97,6 +104,35 @@ class StepRing:
         # happens between a caller's timing events
         self._slot_graphs = ({k: capture_step(pb, *slots[k], **self._kw) for k in range(len(slots))}
                              if (use_graph and group > 1) else {})
+        self._run_graphs = {}  # (steps, first slot) -> graph of a whole run (capture_run)
+
+    def capture_run(self, steps, start=0):
+        """ONE CUDA graph for the ``steps`` consecutive steps ``start .. start+steps-1``, laid out exactly as ``run`` queues
+        them (whole groups a branch per slot, lanes in parallel, a slot's reuse ordered by its lane) — so that a caller
+        that knows how many batches it is going to process hands the whole run to the GPU with a single host call: the
+        host (launch rate, scheduling jitter of 8 ranks sharing one machine) is out of the steady state altogether.
+        ``run(steps, start)`` replays it when it exists."""
+        kw = {k: v for k, v in self._kw.items() if v is not None}
+        with torch.cuda.device(self.dev):
+            branch = [[torch.cuda.Stream(device=self.dev) for _ in range(self.group - 1)] for _ in range(self.lanes)]
+            side = [[torch.cuda.Stream(device=self.dev) for _ in range(self.group)] for _ in range(self.lanes)]
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.device(self.dev), torch.cuda.graph(g):
+            main = torch.cuda.current_stream(self.dev)
+            for st in self.streams:
+                st.wait_stream(main)
+            i, end = start, start + steps
+            while i < end:
+                n = self.group if (i % self.group == 0 and i + self.group <= end) else 1
+                k0 = i % len(self.slots)
+                lane = (k0 // self.group) % self.lanes
+                with torch.cuda.stream(self.streams[lane]):
+                    _enqueue_group(self.pb, self.slots[k0:k0 + n], branch[lane], side[lane], kw)
+                i += n
+            for st in self.streams:
+                main.wait_stream(st)
+        self._run_graphs[(steps, start % len(self.slots))] = g
+        return g
 
     def fork(self):
         """Orders every lane after the work already queued on the current stream."""
@@ -120,7 +156,14 @@ class StepRing:
         return k
 
     def run(self, steps, start=0):
-        """Queues steps ``start .. start+steps-1``: whole groups as one graph launch each, the rest step by step."""
+        """Queues steps ``start .. start+steps-1``: whole groups as one graph launch each, the rest step by step — or, when
+        ``capture_run`` has recorded this very run, as one launch on the current stream (``fork``/``join`` are then no-ops
+        for it: the graph forks and joins its lanes internally)."""
+        whole = self._run_graphs.get((steps, start % len(self.slots)))
+        if whole is not None:
+            with torch.cuda.device(self.dev):
+                whole.replay()
+            return
         i, end = start, start + steps
         while i < end:
             if self.use_graph and i % self.group == 0 and i + self.group <= end:

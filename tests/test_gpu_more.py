@@ -830,6 +830,18 @@ def test_step_ring_batches_in_flight(use_graph, lanes, group):
     torch.cuda.synchronize()
     for (gt, head, y, d), (wy, wd) in zip(slots, want):
         assert torch.equal(y, wy) and torch.equal(d, wd)
+    if use_graph:
+        # the same run as ONE graph (capture_run): a single host call, same results in every slot
+        for _, _, y, d in slots:
+            y.fill_(7.0)
+            d.fill_(7.0)
+        ring.capture_run(3 * SLOTS + 1)
+        ring.fork()
+        ring.run(3 * SLOTS + 1)
+        ring.join()
+        torch.cuda.synchronize()
+        for (gt, head, y, d), (wy, wd) in zip(slots, want):
+            assert torch.equal(y, wy) and torch.equal(d, wd)
 
 
 # ----------------------------------------------------------------------------------------- COCO metrics (parity unpinned)
