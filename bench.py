@@ -367,16 +367,20 @@ def run_cuda(args):
     ring = pipeline.StepRing(pb, make_slots(dev_sets), lanes=lanes, group=group, top_k=TOPK, use_graph=use_graph)
     sampler.load.set()
     timed_ring(ring, max(args.warmup, 3))
-    # the same K steps launched group by group (K / group host calls inside the timed region) ...
-    ms_groups = timed_ring(ring, args.steps)
-    # ... and, the headline, as ONE graph of the whole K-step run (StepRing.capture_run: same kernels, same lanes, same
-    # order; the host makes one call and is out of the timed region, so launch rate and scheduling jitter of several
-    # ranks on one machine no longer leak into a ~1 ms window).  Replayed once untimed first (graph upload).
-    run_graph = use_graph and not args.no_run_graph and args.steps <= 2000
+    # the K steps launched group by group (K / group host calls inside the timed region): the headline.  The region is
+    # ~1 ms at the driver's K = 20 and the figure is the max over ranks, so one descheduled launch thread on one of 8 ranks
+    # doubles it (seen once in 12 runs: profiles/bench_r02o_n4.json); three regions of exactly K steps are timed back to
+    # back and the MEDIAN is reported (all three are listed under schedule.timed_regions_ms) ...
+    regions = [timed_ring(ring, args.steps) for _ in range(3)]
+    ms_groups = float(np.median(regions))
+    # ... or (--run-graph) as ONE graph of the whole K-step run (StepRing.capture_run: same kernels, lanes and order, one
+    # host call).  Measured: the GPU executes the one large graph SLOWER than the group graphs launched back to back
+    # (45.0 vs 40.8 us/step at K = 200), so it is an option for hosts that cannot keep up, not the default.
+    run_graph = use_graph and args.run_graph and args.steps <= 2000
     if run_graph:
         ring.capture_run(args.steps)
         timed_ring(ring, args.steps)
-    ms_total = timed_ring(ring, args.steps)
+    ms_total = timed_ring(ring, args.steps) if run_graph else ms_groups
     value = B * world * args.steps / (ms_total * 1e-3)
     # soak: the same step for ~0.25 s so that the clock record has a few hundred samples under this workload's load
     soak_steps = int(min(20000, max(200, 0.25 / max(ms_total / args.steps * 1e-3, 1e-6))))
@@ -753,7 +757,8 @@ def run_cuda(args):
                          + ('; the K timed steps are one graph of the whole run (one host call)' if run_graph else '; one graph launch per group'),
                          'batches_in_flight': lanes * group, 'batches_per_graph': group, 'lanes': lanes, 'slots': n_slots, 'input_sets': n_sets,
                          'host_calls_in_timed_region': 1 if run_graph else -(-args.steps // group),
-                         'ms_per_step_group_launches': ms_groups / args.steps,
+                         'ms_per_step_group_launches': ms_groups / args.steps, 'timed_regions_ms': regions,
+                         'headline_region': 'median of three timed regions of exactly K steps each',
                          'ms_per_step_one_in_flight': ms_serial / args.steps, 'ms_per_step_soak': ms_soak / max(soak_steps, lanes * group),
                          'soak_steps': max(soak_steps, lanes * group), 'affinity': affinity},
             'clocks': clocks, 'e2e': e2e,
@@ -777,7 +782,8 @@ def main():
     ap.add_argument('--impl', default='cuda', choices=['cuda', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-graph', action='store_true', help='eager launches instead of CUDA-graph replay')
-    ap.add_argument('--no-run-graph', action='store_true', help='time K/group graph launches instead of one graph of the whole K-step run')
+    ap.add_argument('--run-graph', action='store_true', help='time ONE graph of the whole K-step run (StepRing.capture_run) instead of K/group graph launches '
+                    '(measured slower: 45.0 vs 40.8 us/step at K = 200, profiles/sweep_r02p.log)')
     ap.add_argument('--no-affinity', action='store_true', help='do not pin the rank to its own core set')
     ap.add_argument('--no-e2e', action='store_true', help='skip the host-buffer legs (knob sweeps)')
     ap.add_argument('--quick', action='store_true', help='headline + roofline + dense e2e only (no variants / configs / other e2e contracts)')
