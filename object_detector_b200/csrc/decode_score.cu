@@ -221,10 +221,25 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
           const int j0 = part * per, j1 = min(nchunk, j0 + per);
           const float4* row4 = reinterpret_cast<const float4*>(row);
           int jb = -1;
-          for (int j = j0; j < j1; ++j) {
-            const float4 v = row4[j];
-            const float mj = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
-            if (mj > best || (jb < 0 && mj == best)) { best = mj; jb = j; }  // second clause: a chunk of -inf values
+          if (j1 - j0 == 5) {
+            // five chunks per thread (C = 20 with a thread per row, C = 80 with four): all five loads are issued before
+            // the first use, so the scan costs one shared-memory latency instead of five in a row — a consumer warp is
+            // latency-bound here (2 warps per scheduler), not throughput-bound
+            const float4 v0 = row4[j0], v1 = row4[j0 + 1], v2 = row4[j0 + 2], v3 = row4[j0 + 3], v4 = row4[j0 + 4];
+            const float m0 = fmaxf(fmaxf(v0.x, v0.y), fmaxf(v0.z, v0.w)), m1 = fmaxf(fmaxf(v1.x, v1.y), fmaxf(v1.z, v1.w));
+            const float m2 = fmaxf(fmaxf(v2.x, v2.y), fmaxf(v2.z, v2.w)), m3 = fmaxf(fmaxf(v3.x, v3.y), fmaxf(v3.z, v3.w));
+            const float m4 = fmaxf(fmaxf(v4.x, v4.y), fmaxf(v4.z, v4.w));
+            if (m0 >= best) { best = m0; jb = j0; }  // ">=" only against the -inf start value: a chunk of -inf still counts
+            if (m1 > best || (jb < 0 && m1 == best)) { best = m1; jb = j0 + 1; }
+            if (m2 > best || (jb < 0 && m2 == best)) { best = m2; jb = j0 + 2; }
+            if (m3 > best || (jb < 0 && m3 == best)) { best = m3; jb = j0 + 3; }
+            if (m4 > best || (jb < 0 && m4 == best)) { best = m4; jb = j0 + 4; }
+          } else {
+            for (int j = j0; j < j1; ++j) {
+              const float4 v = row4[j];
+              const float mj = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+              if (mj > best || (jb < 0 && mj == best)) { best = mj; jb = j; }  // second clause: a chunk of -inf values
+            }
           }
           if (jb >= 0) {
             const float4 v = row4[jb];
@@ -378,7 +393,7 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   // consumers release it, depth pays off (profiles/sweep_r02d.log: step 44.5 us at 2 deep x 3 CTAs, 43.6 us at
   // 3 deep x 2 CTAs, same shared memory per SM) and two CTAs per SM leave threads and registers to the kernels of the
   // other batches in flight.
-  args.stages = (!DENSE && env_stages >= 2 && env_stages <= L::kMaxStages) ? env_stages : 3;
+  args.stages = (!DENSE && env_stages >= 1 && env_stages <= L::kMaxStages) ? env_stages : 3;
   const size_t smem = L::stage_bytes(args.c) * args.stages;
   auto kern = decode_score_kernel<TILE, DENSE, SPLIT>;
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
