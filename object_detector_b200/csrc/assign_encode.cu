@@ -615,6 +615,7 @@ int odk_launch_assign_rank(const odk_anchors* a, int batch, const float* gt_boxe
   AssignArgs args;
   fill_args(args, a, batch, gt_boxes, nullptr, gt_count, gmax, nullptr, nullptr, nullptr, lists_ws, nullptr);
   const long long tasks = (long long)batch * gmax;
+  ODK_MAX_CARVEOUT_ONCE(assign_candidates_kernel);
   {
     OdkProfileScope prof_("assign_candidates_kernel", stream);
     odk_launch_high(assign_candidates_kernel, dim3((unsigned)((tasks + kCandWarps - 1) / kCandWarps)), dim3(kCandThreads), 0, stream, args);
@@ -630,6 +631,7 @@ int odk_launch_assign_ignore(const odk_anchors* a, int batch, const float* gt_bo
   fill_args(args, a, batch, gt_boxes, nullptr, gt_count, gmax, nullptr, nullptr, nullptr, nullptr, ignore);
   ODK_CUDA(cudaMemsetAsync(ignore, 0, sizeof(unsigned) * (size_t)batch * args.bitmap_words, stream));
   const long long tasks = (long long)batch * gmax;
+  ODK_MAX_CARVEOUT_ONCE(assign_ignore_kernel);
   {
     OdkProfileScope prof_("assign_ignore_kernel", stream);
     odk_launch_high(assign_ignore_kernel, dim3((unsigned)((tasks + kCandWarps - 1) / kCandWarps)), dim3(kCandThreads), 0, stream, args);
@@ -664,6 +666,7 @@ int odk_launch_assign_greedy(const odk_anchors* a, int batch, const float* gt_bo
   }
   ODK_REQUIRE(smem <= 200 * 1024, ODK_ERR_UNSUPPORTED, "assign: N=%d / Gmax=%d need %zu bytes of shared memory per image", a->n, gmax, smem);
   ODK_CUDA(cudaFuncSetAttribute(assign_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  ODK_MAX_CARVEOUT_ONCE(assign_greedy_kernel);
   {
     OdkProfileScope prof_("assign_greedy_kernel", stream);
     odk_launch_high(assign_greedy_kernel, dim3(batch), dim3(kGreedyThreads), smem, stream, args);

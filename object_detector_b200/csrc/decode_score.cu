@@ -397,6 +397,7 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   const size_t smem = L::stage_bytes(args.c) * args.stages;
   auto kern = decode_score_kernel<TILE, DENSE, SPLIT>;
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  ODK_MAX_CARVEOUT_ONCE(kern);
   args.tiles_per_image = (args.n + TILE - 1) / TILE;
   args.pieces_per_image = args.tiles_per_image;
   const long long total = (long long)args.batch * args.tiles_per_image;

@@ -284,6 +284,8 @@ int launch_rows(const EncodeArgs& e, int n, int W, cudaStream_t stream) {
   static const int per_sm = getenv("ODK_ROWS_PER_SM") ? atoi(getenv("ODK_ROWS_PER_SM")) : ODK_ROWS_PER_SM_DEFAULT;
   const long long chunks = gx * e.batch;
   ODK_REQUIRE(chunks < 0x7fffffffLL, ODK_ERR_UNSUPPORTED, "assign_encode: %lld row chunks", chunks);
+  ODK_MAX_CARVEOUT_ONCE(encode_rows_persistent_kernel<4>); ODK_MAX_CARVEOUT_ONCE(encode_rows_persistent_kernel<1>);
+  ODK_MAX_CARVEOUT_ONCE(encode_rows_kernel<4>); ODK_MAX_CARVEOUT_ONCE(encode_rows_kernel<1>);
   {
     OdkProfileScope prof_("encode_rows_kernel", stream);
     // a launch of up to ~16 chunks per persistent CTA shares the SMs with whatever runs beside it; a larger one (B = 256,
@@ -354,6 +356,7 @@ extern "C" int odk_assign_encode(const odk_anchors* a, int batch, const float* g
   if (rc_main) return rc_main;
   PatchArgs q;
   fill_patch(q, a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, y_true, pb_valids);
+  ODK_MAX_CARVEOUT_ONCE(encode_patch_kernel);
   {
     OdkProfileScope prof_("encode_patch_kernel", stream);
     odk_launch_high(encode_patch_kernel, dim3(batch), dim3(128), 0, stream, q);
@@ -384,6 +387,7 @@ extern "C" int odk_assign_encode_compact(const odk_anchors* a, int batch, const 
   CompactArgs c;
   fill_patch(c.q, a, batch, gt_boxes, gt_classes, gt_count, gmax, pb_indices, gt_indices, status, nullptr, nullptr);
   c.ignore = ignore; c.bitmap_words = words; c.pos_rows = pos_rows; c.valid_bits = valid_bits;
+  ODK_MAX_CARVEOUT_ONCE(encode_compact_kernel);
   {
     OdkProfileScope prof_("encode_compact_kernel", stream);
     odk_launch_high(encode_compact_kernel, dim3(batch), dim3(128), 0, stream, c);

@@ -763,6 +763,7 @@ static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch,
   else kern = strict ? (iou_ge ? nms_image_kernel<true, true, false> : nms_image_kernel<false, true, false>)
                      : (iou_ge ? nms_image_kernel<true, false, false> : nms_image_kernel<false, false, false>);
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 180 * 1024));
+  odk_prefer_max_smem(kern);
   {
     OdkProfileScope prof_(strict ? "nms_image_kernel_strict" : "nms_image_kernel", stream);
     odk_launch_high(kern, dim3(batch), dim3(kNmsThreads), smem, stream, a);
@@ -785,6 +786,7 @@ static int collect(const NmsWorkspace& w, int batch, int n, int num_classes, con
                    int take_all, cudaStream_t stream) {
   dim3 grid((n + kCollectPiece - 1) / kCollectPiece, batch);
   ODK_REQUIRE(batch <= 65535, ODK_ERR_UNSUPPORTED, "nms: batch=%d > 65535", batch);
+  ODK_MAX_CARVEOUT_ONCE(collect_pieces_kernel);
   {
     OdkProfileScope prof_("collect_pieces_kernel", stream);
     collect_pieces_kernel<<<grid, kCollectPiece, 0, stream>>>(n, num_classes, classes, confs, conf_thr, take_all, w.cand_keys, w.piece_count);

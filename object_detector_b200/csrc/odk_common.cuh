@@ -205,6 +205,18 @@ __device__ __forceinline__ float4 odk_decode_box(const float4 pr, const float4 l
   return box;
 }
 
+// ---- one shared-memory carveout for every kernel of a step -------------------------------------------------------------
+// An SM's L1 / shared-memory split is reconfigured only when the SM is idle.  The step mixes kernels that need a lot of
+// shared memory (score_emit ring, per-image NMS, greedy walk) with kernels that need next to none (rows, candidates,
+// ignore, patch); left to the default, a CTA of the first kind cannot be placed on an SM that currently runs CTAs of the
+// second kind until those have drained — the in-kernel timeline showed the greedy walk waiting 16 us for the persistent
+// rows kernel to END.  Every kernel of the step therefore asks for the maximum shared-memory carveout once.
+template <typename K>
+inline void odk_prefer_max_smem(K kern) {
+  cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+}
+#define ODK_MAX_CARVEOUT_ONCE(kern) do { static const bool once_ = (odk_prefer_max_smem(kern), true); (void)once_; } while (0)
+
 // ---- priority launches ------------------------------------------------------------------------------------------
 // The step mixes HBM-streaming kernels with large grids (encode_rows, score_emit) and short latency-bound kernels of
 // 64..1024 small CTAs (candidates, greedy walk, patch, NMS).  Launched at equal priority, the CTAs of a latency-bound
