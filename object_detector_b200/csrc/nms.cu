@@ -752,6 +752,8 @@ static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch,
   const size_t fixed = odk_align_up((size_t)(limit < 1 ? 1 : limit) * 24, 16) + odk_align_up(sizeof(int) * ((size_t)a.n_pieces + 1), 16) +
                        member_area_bytes(strict) + (strict ? odk_align_up((size_t)(top_k < 1 ? 1 : top_k) * 20, 16) : 0);
   a.cache_cap = n < 8192 ? n : 8192;
+  static const int env_cache = getenv("ODK_NMS_CACHE") ? atoi(getenv("ODK_NMS_CACHE")) : -1;  // diagnostics: key-cache capacity
+  if (env_cache >= 0 && env_cache < a.cache_cap) a.cache_cap = env_cache;
   if (fixed + (size_t)a.cache_cap * 8 > 180 * 1024) a.cache_cap = 0;
   const bool big = n >= 65536;
   if (big) a.cache_cap = 0;
