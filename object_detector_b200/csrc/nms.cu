@@ -305,6 +305,7 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
   };
 
   int nkept = 0, processed = 0;
+  int hist_top = ODK_HIST_BINS;  // bins below it hold exactly the keys not yet processed (0: histogram no longer usable)
   unsigned long long hi_key = ~0ull;  // keys of earlier bands are >= hi_key (every real key is < ~0)
 
   // Walks the nb_bins bins of s_hist from the top: n_take = how many top bins to take whole, cnt = keys they hold
@@ -358,21 +359,25 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     if (kept_so_far > 0) want = (int)min((long long)kBand, (long long)need * processed / kept_so_far * 9 / 8 + 32);
     want = min(kBand, want);
     bool have_lo = remaining <= kBand;
-    if (!have_lo && processed == 0 && p.score_hist != nullptr) {
-      // first round: the score histogram score_emit built while streaming replaces the passes over the keys
-      // (min/max + digit histograms).  A bin's lower bound is a key threshold; if the bin that crosses `want`
-      // overflows the band and too little lies above it, the generic select below refines among all keys.
+    if (!have_lo && hist_top > 0 && p.score_hist != nullptr) {
+      // The score histogram score_emit built while streaming replaces the passes over the keys (min/max + digit
+      // histograms) — in the first round and in every later one, as long as all earlier thresholds were bin boundaries:
+      // the keys not yet processed are then exactly the bins below hist_top.  A bin's lower bound is a key threshold; if
+      // the bin that crosses `want` overflows the band and too little lies above it, the generic select below refines
+      // among the keys themselves (and the histogram is not used again for this image).
       const int* hist = p.score_hist + (size_t)b * ODK_HIST_BINS;
-      for (int i = tid; i < ODK_HIST_BINS; i += kNmsThreads) s_hist[i] = hist[i];
+      for (int i = tid; i < hist_top; i += kNmsThreads) s_hist[i] = hist[i];
       __syncthreads();
       int n_take_bins, cnt_take;
-      walk_bins(ODK_HIST_BINS, 0, want, n_take_bins, cnt_take);
+      walk_bins(hist_top, 0, want, n_take_bins, cnt_take);
       if (cnt_take >= max(32, want / 2)) {
-        const int d_star = ODK_HIST_BINS - n_take_bins;  // bins >= d_star are taken whole (n_take_bins >= 1 here)
+        const int d_star = hist_top - n_take_bins;  // bins [d_star, hist_top) are taken whole (n_take_bins >= 1 here)
         lo_key = d_star > 0 ? odk_bin_lo_key(d_star) : 0ull;
         have_lo = true;
+        hist_top = d_star;
       }
     }
+    if (!have_lo) hist_top = 0;  // the generic select cuts inside a bin
     cache_ready();
     if (!have_lo) {
       unsigned long long kmin = ~0ull, kmax = 0ull;
