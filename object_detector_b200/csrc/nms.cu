@@ -354,7 +354,8 @@ __global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs
     const int need = STRICT ? p.top_k - nkept2 : limit - nkept;
     // band size aimed at: a little more than what is still needed, scaled by the survival ratio seen so far (first round:
     // 1.125x + 16, which for top_k = 200 keeps the band within a 256-key sort network when little is suppressed)
-    int want = need + (need >> 3) + 16;
+    int want = STRICT ? need + (need >> 1) + 16   // the all-class stage removes cross-class duplicates on top: one larger band beats a second round
+                      : need + (need >> 3) + 16;
     const int kept_so_far = STRICT ? nkept2 : nkept;
     if (kept_so_far > 0) want = (int)min((long long)kBand, (long long)need * processed / kept_so_far * 9 / 8 + 32);
     want = min(kBand, want);
