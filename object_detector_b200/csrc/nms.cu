@@ -192,7 +192,7 @@ __device__ __forceinline__ unsigned long long block_sort_desc_1(unsigned long lo
 // dense-anchor stress shape): no cache, and the passes over the keys keep 16 pieces in flight per warp instead of 4 (more
 // registers: kept out of the instantiation that shares its SM with the streaming kernels of other batches).
 template <bool GE, bool STRICT, bool BIG>
-__global__ void __launch_bounds__(kNmsThreads, 1) nms_image_kernel(const NmsArgs p) {
+__global__ void __launch_bounds__(kNmsThreads, BIG ? 1 : 2) nms_image_kernel(const NmsArgs p) {
   OdkTimeline tl_(ODK_TL_NMS, p.tl);
   static_assert(kBand <= kNmsThreads && ODK_MAX_CLASSES / 32 <= kNmsThreads, "one band slot / class word per thread");
   extern __shared__ __align__(16) unsigned char nms_smem[];
@@ -757,7 +757,16 @@ static int nms_run(const NmsWorkspace& w, const odk_anchors* anchors, int batch,
   a.out = out; a.kept_index = kept_index; a.out_index = out_index; a.out_count = out_count;
   const size_t fixed = odk_align_up((size_t)(limit < 1 ? 1 : limit) * 24, 16) + odk_align_up(sizeof(int) * ((size_t)a.n_pieces + 1), 16) +
                        member_area_bytes(strict) + (strict ? odk_align_up((size_t)(top_k < 1 ? 1 : top_k) * 20, 16) : 0);
-  a.cache_cap = n < 8192 ? n : 8192;
+  // Key cache: what is left of a 94 KB shared-memory budget per NMS CTA (34.6 KB static + `fixed` + cache), in 512-key
+  // steps.  The budget — together with the 62 registers the kernel compiles to at two CTAs per SM — is what lets an NMS
+  // CTA share its SM with two score_emit CTAs (2 x 65 KB) of the next batch in flight instead of waiting for that
+  // persistent kernel to end: step 41.2 -> 39.1 us (profiles/sweep_r02v.log).  VOC shape: 4 608 keys (an image with more
+  // candidates reads its keys through L2; with the score histogram a round is one such pass).
+  {
+    const size_t budget = 94 * 1024, used = 34656 + fixed;
+    const size_t room = budget > used ? (budget - used) / 8 / 512 * 512 : 0;
+    a.cache_cap = (int)(room < (size_t)n ? room : (size_t)n);
+  }
   static const int env_cache = getenv("ODK_NMS_CACHE") ? atoi(getenv("ODK_NMS_CACHE")) : -1;  // diagnostics: key-cache capacity
   if (env_cache >= 0 && env_cache < a.cache_cap) a.cache_cap = env_cache;
   if (fixed + (size_t)a.cache_cap * 8 > 180 * 1024) a.cache_cap = 0;
