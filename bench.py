@@ -33,6 +33,7 @@ METRIC = 'images/sec assign+decode+NMS @640x640'
 B, N, C, GMAX, TOPK = 64, 16800, 20, 64, 200
 SETS = 8            # distinct input sets rotated through so every step reads data that is not L2-resident
 SLOTS = 8           # resident batches (each with its own outputs and workspaces); slot k reads input set k % SETS
+CHAIN = 1
 LANES, GROUP = 2, 4  # pipeline.StepRing: GROUP consecutive slots per CUDA graph (a branch each), graphs alternating on LANES streams
 WORKLOAD = 'cfg2+cfg3: Darknet53 640x640 VOC anchors (N=16800, C=20), batch 64: assign+encode (<=64 GT/img) + decode + per-class NMS (top-k 200)'
 EVAL_IMAGES = 4952  # config 4
@@ -117,8 +118,9 @@ class ClockSampler(threading.Thread):
     """Samples SM clock + throttle reasons through NVML every 2 ms from before the warm-up until the end of the soak
     that follows the timed region; samples taken while ``load`` is set count as "under load"."""
 
-    def __init__(self, index):
+    def __init__(self, index, period_s=0.002):
         super().__init__(daemon=True)
+        self.period_s = period_s
         self.index, self.samples, self.loaded, self.reasons, self.max_mhz = index, [], [], set(), None
         self._stop_evt, self.load = threading.Event(), threading.Event()
         try:
@@ -155,7 +157,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(k)
             except Exception:  # noqa: BLE001
                 pass
-            time.sleep(0.002)
+            time.sleep(self.period_s)
 
     def stop(self):
         self._stop_evt.set()
@@ -344,8 +346,11 @@ def run_cuda(args):
     group = max(1, min(args.group, n_slots))
     while n_slots % group:
         group -= 1
-    lanes = max(1, min(args.lanes, n_slots // group))
-    while (n_slots // group) % lanes:
+    chain = max(1, args.chain)
+    while n_slots % (group * chain):
+        chain -= 1
+    lanes = max(1, min(args.lanes, n_slots // (group * chain)))
+    while (n_slots // (group * chain)) % lanes:
         lanes -= 1
 
     def make_slots(sets):
@@ -362,9 +367,9 @@ def run_cuda(args):
         barrier()
         return max_over_ranks(e0.elapsed_time(e1))
 
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local, args.clock_period_ms * 1e-3)
     sampler.start()
-    ring = pipeline.StepRing(pb, make_slots(dev_sets), lanes=lanes, group=group, top_k=TOPK, use_graph=use_graph)
+    ring = pipeline.StepRing(pb, make_slots(dev_sets), lanes=lanes, group=group, top_k=TOPK, use_graph=use_graph, chain=chain)
     sampler.load.set()
     timed_ring(ring, max(args.warmup, 3))
     # the K steps launched group by group (K / group host calls inside the timed region): the headline.  The region is
@@ -454,7 +459,7 @@ def run_cuda(args):
         clustered = [tuple(torch.from_numpy(x).to(dev) for x in synth.gt_batch(7 + 100 * rank + r, B, GMAX, C)
                            + synth.predictions(4321 + 100 * rank + r, B, N, C, clustered=True)) for r in range(n_var)]
         for name, sets, strict in (('clustered', clustered, None), ('strict_nms', dev_sets, 0.5), ('clustered_strict_nms', clustered, 0.5)):
-            rg = pipeline.StepRing(pb, make_slots(sets), lanes=lanes, group=group, top_k=TOPK, use_graph=use_graph, nms_all_threshold=strict)
+            rg = pipeline.StepRing(pb, make_slots(sets), lanes=lanes, group=group, top_k=TOPK, use_graph=use_graph, nms_all_threshold=strict, chain=chain)
             timed_ring(rg, max(args.warmup, 3))
             if run_graph:
                 rg.capture_run(args.steps)
@@ -755,8 +760,8 @@ def run_cuda(args):
                          + f'; {group} consecutive batches per group (a branch each), groups alternating on {lanes} streams'
                          + f' = up to {lanes * group} batches in flight (each slot has its own y_true, detections, workspaces)'
                          + ('; the K timed steps are one graph of the whole run (one host call)' if run_graph else '; one graph launch per group'),
-                         'batches_in_flight': lanes * group, 'batches_per_graph': group, 'lanes': lanes, 'slots': n_slots, 'input_sets': n_sets,
-                         'host_calls_in_timed_region': 1 if run_graph else -(-args.steps // group),
+                         'batches_in_flight': lanes * group, 'batches_per_graph': group * chain, 'groups_chained_per_graph': chain, 'lanes': lanes, 'slots': n_slots, 'input_sets': n_sets,
+                         'host_calls_in_timed_region': 1 if run_graph else -(-args.steps // (group * chain)),
                          'ms_per_step_group_launches': ms_groups / args.steps, 'timed_regions_ms': regions,
                          'headline_region': 'median of three timed regions of exactly K steps each',
                          'ms_per_step_one_in_flight': ms_serial / args.steps, 'ms_per_step_soak': ms_soak / max(soak_steps, lanes * group),
@@ -785,6 +790,7 @@ def main():
     ap.add_argument('--run-graph', action='store_true', help='time ONE graph of the whole K-step run (StepRing.capture_run) instead of K/group graph launches '
                     '(measured slower: 45.0 vs 40.8 us/step at K = 200, profiles/sweep_r02p.log)')
     ap.add_argument('--no-affinity', action='store_true', help='do not pin the rank to its own core set')
+    ap.add_argument('--clock-period-ms', type=float, default=2.0, help='NVML sampling period of the in-run clock record')
     ap.add_argument('--no-e2e', action='store_true', help='skip the host-buffer legs (knob sweeps)')
     ap.add_argument('--quick', action='store_true', help='headline + roofline + dense e2e only (no variants / configs / other e2e contracts)')
     ap.add_argument('--eval-at-one', action='store_true', help='run the config-4 leg on a single GPU too (no collective)')
@@ -792,6 +798,7 @@ def main():
     ap.add_argument('--sets', type=int, default=SETS, help='distinct resident input sets rotated through')
     ap.add_argument('--slots', type=int, default=SLOTS, help='resident batches (outputs + workspaces) in the ring')
     ap.add_argument('--lanes', type=int, default=LANES, help='streams the step graphs alternate on')
+    ap.add_argument('--chain', type=int, default=CHAIN, help='consecutive groups chained inside one CUDA graph (one host launch per group*chain batches)')
     ap.add_argument('--group', type=int, default=GROUP, help='consecutive batches captured into one CUDA graph (a branch each)')
     args = ap.parse_args()
     if args.impl == 'reference':

@@ -87,10 +87,10 @@ class StepRing:
     """
 
     def __init__(self, pb, slots, lanes=2, group=4, top_k=200, conf_threshold=0.01, nms_threshold=0.45, use_graph=True,
-                 nms_all_threshold=None):
-        assert len(slots) >= 1 and lanes >= 1 and group >= 1 and len(slots) % (lanes * group) == 0, \
-            'len(slots) must be a multiple of lanes * group'
-        self.pb, self.slots, self.lanes, self.group = pb, slots, lanes, group
+                 nms_all_threshold=None, chain=1):
+        assert len(slots) >= 1 and lanes >= 1 and group >= 1 and chain >= 1 and len(slots) % (lanes * group * chain) == 0, \
+            'len(slots) must be a multiple of lanes * group * chain'
+        self.pb, self.slots, self.lanes, self.group, self.chain = pb, slots, lanes, group, chain
         self.dev = slots[0][2].device
         self._kw = dict(top_k=top_k, conf_threshold=conf_threshold, nms_threshold=nms_threshold, nms_all_threshold=nms_all_threshold)
         self.n_groups = len(slots) // group
@@ -105,6 +105,24 @@ class StepRing:
         self._slot_graphs = ({k: capture_step(pb, *slots[k], **self._kw) for k in range(len(slots))}
                              if (use_graph and group > 1) else {})
         self._run_graphs = {}  # (steps, first slot) -> graph of a whole run (capture_run)
+        # chain > 1: ``chain`` consecutive groups one after the other in ONE graph — the same ``group`` batches in flight per
+        # lane, but one host launch per group * chain batches (with 8 ranks on one host a graph launch costs ~170 us, more
+        # than the GPU needs for 4 batches)
+        self.chain_graphs = None
+        if use_graph and chain > 1:
+            kw = {k: v for k, v in self._kw.items() if v is not None}
+            self.chain_graphs = []
+            with torch.cuda.device(self.dev):
+                pb._handle(self.dev)
+                branch = [torch.cuda.Stream(device=self.dev) for _ in range(group - 1)]
+                side = [torch.cuda.Stream(device=self.dev) for _ in range(group)]
+            span = group * chain
+            for j in range(len(slots) // span):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.device(self.dev), torch.cuda.graph(g):
+                    for c in range(chain):
+                        _enqueue_group(pb, slots[j * span + c * group:j * span + (c + 1) * group], branch, side, kw)
+                self.chain_graphs.append(g)
 
     def capture_run(self, steps, start=0):
         """ONE CUDA graph for the ``steps`` consecutive steps ``start .. start+steps-1``, laid out exactly as ``run`` queues
@@ -125,7 +143,7 @@ class StepRing:
             while i < end:
                 n = self.group if (i % self.group == 0 and i + self.group <= end) else 1
                 k0 = i % len(self.slots)
-                lane = (k0 // self.group) % self.lanes
+                lane = self._lane_index(k0)
                 with torch.cuda.stream(self.streams[lane]):
                     _enqueue_group(self.pb, self.slots[k0:k0 + n], branch[lane], side[lane], kw)
                 i += n
@@ -141,8 +159,11 @@ class StepRing:
         for st in self.streams:
             st.wait_event(self._ev)
 
+    def _lane_index(self, k):
+        return (k // (self.group * self.chain)) % self.lanes
+
     def _lane_of_slot(self, k):
-        return self.streams[(k // self.group) % self.lanes]
+        return self.streams[self._lane_index(k)]
 
     def submit(self, i):
         """Queues the single step ``i`` (slot ``i % len(slots)``) on its lane; returns the slot index."""
@@ -165,10 +186,16 @@ class StepRing:
                 whole.replay()
             return
         i, end = start, start + steps
+        span = self.group * self.chain
         while i < end:
-            if self.use_graph and i % self.group == 0 and i + self.group <= end:
-                j = (i // self.group) % self.n_groups
+            if self.chain_graphs is not None and i % span == 0 and i + span <= end:
+                j = (i // span) % len(self.chain_graphs)
                 with torch.cuda.device(self.dev), torch.cuda.stream(self.streams[j % self.lanes]):
+                    self.chain_graphs[j].replay()
+                i += span
+            elif self.use_graph and i % self.group == 0 and i + self.group <= end:
+                j = (i // self.group) % self.n_groups
+                with torch.cuda.device(self.dev), torch.cuda.stream(self._lane_of_slot(j * self.group)):
                     self.group_graphs[j].replay()
                 i += self.group
             else:
