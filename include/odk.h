@@ -232,6 +232,19 @@ int odk_nms(const float* boxes /*[dev n,4]*/, const float* scores /*[dev n]*/, i
             float iou_thr, int iou_ge, int32_t* out_index /*[dev max(top_k,2)]*/,
             int32_t* out_count /*[dev 1]*/, void* workspace, size_t workspace_bytes, void* stream);
 
+/* odk_nms without a caller workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same inputs, outputs and semantics as odk_nms; the scratch is a static device array of
+ * 640 KB inside the library (held on every GPU that loads it until the process exits), which limits n to
+ * odk_nms_static_max_boxes() = 65 536 boxes: larger n returns ODK_ERR_UNSUPPORTED with a message naming the limit.
+ * The call makes no cudaMalloc / cudaFree / allocating library call.  All calls on a device share the one array, which
+ * keeps the previous call's contents (nothing in it needs to start at zero): calls that OVERLAP ON THE GPU — different
+ * streams without ordering between them — race; order them on one stream or with events. */
+size_t odk_nms_static_max_boxes(void);
+int odk_nms_static(const float* boxes /*[dev n,4]*/, const float* scores /*[dev n]*/, int n, int top_k,
+                   float iou_thr, int iou_ge, int32_t* out_index /*[dev max(top_k,2)]*/,
+                   int32_t* out_count /*[dev 1]*/, void* stream);
+
 /* data.voc.evaluate (data/voc.py:165-197 -> chainercv eval_detection_voc; PARITY UNPINNED).
  * dets: the NMS layer output for n_img images; rows with conf < conf_thr are dropped
  * (od.py:265).  gt_offsets[n_img+1] indexes the flat GT arrays.  Boxes are converted to integer

@@ -59,6 +59,8 @@ SIGNATURES = {
                                       c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'odk_nms': (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p, c_void_p, c_size_t,
                         c_void_p]),
+    'odk_nms_static_max_boxes': (c_size_t, []),
+    'odk_nms_static': (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p, c_void_p]),
     'odk_voc_ap_workspace_bytes': (c_size_t, [c_int, c_int, c_int, c_int]),
     'odk_voc_ap': (c_int, [c_int, c_int, c_int, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p,
                            c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -30,6 +30,7 @@
 // fast form is used only outside a guard band.
 #include "odk_common.cuh"
 #include "odk_sort.cuh"
+#include <mutex>
 
 namespace {
 
@@ -899,3 +900,65 @@ extern "C" int odk_nms(const float* boxes, const float* scores, int n, int top_k
                  out_index, out_count, stream);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// odk_nms_static: odk_nms for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc).  No counterpart in the reference.  The scratch that odk_nms
+// takes from the caller lives in a file-scope device array instead: ODK_NMS_STATIC_BYTES on every GPU that loads the
+// library, held until the process exits.
+//  * In host code `g_nms_static_scratch` is only the host-side stand-in of the symbol; the device address is looked up
+//    once per device with cudaGetSymbolAddress (with that device current) and cached.
+//  * Nothing in the scratch has to start at zero: collect_pieces_kernel writes the count of every piece and the keys of
+//    every piece it counts before nms_image_kernel reads them, and the score histogram is not used by this path.  The
+//    array keeps the previous call's contents.
+//  * Every call on a device shares the one array: calls that overlap on the GPU (different streams, no ordering) race.
+// ---------------------------------------------------------------------------------------------------------------------
+#define ODK_NMS_STATIC_MAX_N 65536
+#define ODK_NMS_STATIC_BYTES (640 * 1024)  // nms_layout(1, 65536): 8 KB counts + 512 KB keys + 4 KB histogram slot, 256-byte aligned
+static __device__ __align__(256) unsigned char g_nms_static_scratch[ODK_NMS_STATIC_BYTES];
+
+static int nms_static_scratch(void** out) {
+  constexpr int kMaxDevices = 64;
+  static void* ptrs[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  ODK_CUDA(cudaGetDevice(&dev));
+  ODK_REQUIRE(dev >= 0 && dev < kMaxDevices, ODK_ERR_UNSUPPORTED, "nms_static: device ordinal %d >= %d", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    ODK_CUDA(cudaGetSymbolAddress(&p, g_nms_static_scratch));
+    ODK_REQUIRE(p != nullptr && ((uintptr_t)p & 255) == 0, ODK_ERR_CUDA, "nms_static: bad address %p for the scratch symbol", p);
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return ODK_OK;
+}
+
+extern "C" size_t odk_nms_static_max_boxes(void) { return ODK_NMS_STATIC_MAX_N; }
+
+extern "C" int odk_nms_static(const float* boxes, const float* scores, int n, int top_k, float iou_thr, int iou_ge, int32_t* out_index,
+                              int32_t* out_count, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  ODK_REQUIRE(out_index && out_count, ODK_ERR_INVALID_ARGUMENT, "nms_static: null output pointer");
+  ODK_REQUIRE(n >= 0, ODK_ERR_INVALID_ARGUMENT, "nms_static: n=%d < 0", n);
+  ODK_REQUIRE(n <= ODK_NMS_STATIC_MAX_N, ODK_ERR_UNSUPPORTED,
+              "nms_static: n=%d boxes exceed the built-in scratch (at most %d boxes; use odk_nms with a caller workspace)", n,
+              ODK_NMS_STATIC_MAX_N);
+  if (n == 0) {
+    ODK_CUDA(cudaMemsetAsync(out_count, 0, sizeof(int32_t), stream));
+    return ODK_OK;
+  }
+  ODK_REQUIRE(nms_layout(nullptr, 1, n).bytes <= (size_t)ODK_NMS_STATIC_BYTES, ODK_ERR_UNSUPPORTED,
+              "nms_static: n=%d needs %zu bytes of scratch > the built-in %d", n, nms_layout(nullptr, 1, n).bytes, ODK_NMS_STATIC_BYTES);
+  void* scratch = nullptr;
+  if (int rc = nms_static_scratch(&scratch)) return rc;
+  if (int rc = nms_check(1, n, 1, top_k < 0 ? 0 : top_k, scratch, ODK_NMS_STATIC_BYTES)) return rc;
+  ODK_REQUIRE(boxes && scores, ODK_ERR_INVALID_ARGUMENT, "nms_static: null input pointer");
+  ODK_REQUIRE(((uintptr_t)boxes & 15) == 0, ODK_ERR_INVALID_ARGUMENT, "nms_static: boxes must be 16-byte aligned");
+  NmsWorkspace w = nms_layout(scratch, 1, n);
+  if (int rc = collect(w, 1, n, 1, nullptr, scores, 0.f, 1, stream)) return rc;
+  const int limit = iou_ge ? (top_k < 2 ? 2 : top_k) : (top_k < 0 ? 0 : top_k);  // ml.py:612-623, as in odk_nms
+  return nms_run(w, nullptr, 1, n, kCollectPiece, reinterpret_cast<const float4*>(boxes), nullptr, iou_thr, 0, limit, iou_ge, nullptr, nullptr,
+                 out_index, out_count, stream);
+}
