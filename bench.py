@@ -32,9 +32,12 @@ if ROOT not in sys.path:
 METRIC = 'images/sec assign+decode+NMS @640x640'
 B, N, C, GMAX, TOPK = 64, 16800, 20, 64, 200
 SETS = 8            # distinct input sets rotated through so every step reads data that is not L2-resident
-SLOTS = 8           # resident batches (each with its own outputs and workspaces); slot k reads input set k % SETS
-CHAIN = 1
-LANES, GROUP = 2, 4  # pipeline.StepRing: GROUP consecutive slots per CUDA graph (a branch each), graphs alternating on LANES streams
+SLOTS = 20          # resident batches (each with its own outputs and workspaces); slot k reads input set k % SETS
+# pipeline.StepRing: GROUP consecutive slots = a group (a graph branch each), CHAIN consecutive groups per CUDA graph, graphs
+# alternating on LANES streams.  2 x 5 x 2: 10 batches in flight, one host launch per 10 batches.  Chosen on 8 ranks sharing a
+# host (profiles/ring_probe_r02x_n8.log): every extra graph boundary on a lane costs there (2 x 4 x 1: 43.7 us per step at
+# K = 20, 2 x 5 x 2: 41.7-42.8), while one GPU is indifferent to the shape (41.3-41.7 us, profiles/ring_probe_r02x_n1.log).
+LANES, GROUP, CHAIN = 2, 5, 2
 WORKLOAD = 'cfg2+cfg3: Darknet53 640x640 VOC anchors (N=16800, C=20), batch 64: assign+encode (<=64 GT/img) + decode + per-class NMS (top-k 200)'
 EVAL_IMAGES = 4952  # config 4
 
@@ -275,7 +278,7 @@ def run_cuda(args):
     world = int(os.environ.get('WORLD_SIZE', '1'))
     local = int(os.environ.get('LOCAL_RANK', '0'))
     world_local = int(os.environ.get('LOCAL_WORLD_SIZE', str(world)))
-    affinity = pin_affinity(local, world_local, enable=not args.no_affinity)  # before CUDA init / pinned allocations
+    affinity = pin_affinity(local, world_local, enable=args.affinity and not args.no_affinity)  # before CUDA init / pinned allocations
 
     import torch
     import torch.distributed as dist
@@ -353,6 +356,14 @@ def run_cuda(args):
     while (n_slots // (group * chain)) % lanes:
         lanes -= 1
 
+    def host_calls(steps):
+        """The launches StepRing.run makes for `steps` steps from step 0."""
+        span, i, calls = group * chain, 0, 0
+        while i < steps:
+            i += span if (chain > 1 and i % span == 0 and i + span <= steps) else (group if (use_graph and i % group == 0 and i + group <= steps) else 1)
+            calls += 1
+        return calls
+
     def make_slots(sets):
         return [(sets[k % len(sets)][:3], sets[k % len(sets)][3:], y_trues[k], detss[k]) for k in range(n_slots)]
 
@@ -372,6 +383,7 @@ def run_cuda(args):
     ring = pipeline.StepRing(pb, make_slots(dev_sets), lanes=lanes, group=group, top_k=TOPK, use_graph=use_graph, chain=chain)
     sampler.load.set()
     timed_ring(ring, max(args.warmup, 3))
+    timed_ring(ring, n_slots)  # untimed as well: one pass over every slot, so that every graph of the ring has been launched once
     # the K steps launched group by group (K / group host calls inside the timed region): the headline.  The region is
     # ~1 ms at the driver's K = 20 and the figure is the max over ranks, so one descheduled launch thread on one of 8 ranks
     # doubles it (seen once in 12 runs: profiles/bench_r02o_n4.json); three regions of exactly K steps are timed back to
@@ -389,8 +401,8 @@ def run_cuda(args):
     value = B * world * args.steps / (ms_total * 1e-3)
     # soak: the same step for ~0.25 s so that the clock record has a few hundred samples under this workload's load
     soak_steps = int(min(20000, max(200, 0.25 / max(ms_total / args.steps * 1e-3, 1e-6))))
-    soak_steps -= soak_steps % (lanes * group)
-    ms_soak = timed_ring(ring, max(soak_steps, lanes * group))
+    soak_steps -= soak_steps % (lanes * group * chain)
+    ms_soak = timed_ring(ring, max(soak_steps, lanes * group * chain))
     sampler.load.clear()
     clocks = sampler.stop()
     # the same K steps with one batch in flight (latency of a step, and the figure earlier rounds reported)
@@ -461,6 +473,7 @@ def run_cuda(args):
         for name, sets, strict in (('clustered', clustered, None), ('strict_nms', dev_sets, 0.5), ('clustered_strict_nms', clustered, 0.5)):
             rg = pipeline.StepRing(pb, make_slots(sets), lanes=lanes, group=group, top_k=TOPK, use_graph=use_graph, nms_all_threshold=strict, chain=chain)
             timed_ring(rg, max(args.warmup, 3))
+            timed_ring(rg, n_slots)
             if run_graph:
                 rg.capture_run(args.steps)
                 timed_ring(rg, args.steps)
@@ -757,15 +770,15 @@ def run_cuda(args):
             'ms_per_step': ms_total / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'f32', 'data': 'synthetic', 'config': cfg,
             'schedule': {'launch': ('eager' if not use_graph else 'CUDA graphs, train and predict sides of a batch on parallel branches')
-                         + f'; {group} consecutive batches per group (a branch each), groups alternating on {lanes} streams'
+                         + f'; {group} consecutive batches per group (a branch each), {chain} consecutive group(s) per graph, graphs alternating on {lanes} streams'
                          + f' = up to {lanes * group} batches in flight (each slot has its own y_true, detections, workspaces)'
-                         + ('; the K timed steps are one graph of the whole run (one host call)' if run_graph else '; one graph launch per group'),
+                         + ('; the K timed steps are one graph of the whole run (one host call)' if run_graph else f'; one graph launch per {group * chain} batches'),
                          'batches_in_flight': lanes * group, 'batches_per_graph': group * chain, 'groups_chained_per_graph': chain, 'lanes': lanes, 'slots': n_slots, 'input_sets': n_sets,
-                         'host_calls_in_timed_region': 1 if run_graph else -(-args.steps // (group * chain)),
+                         'host_calls_in_timed_region': 1 if run_graph else host_calls(args.steps),
                          'ms_per_step_group_launches': ms_groups / args.steps, 'timed_regions_ms': regions,
                          'headline_region': 'median of three timed regions of exactly K steps each',
-                         'ms_per_step_one_in_flight': ms_serial / args.steps, 'ms_per_step_soak': ms_soak / max(soak_steps, lanes * group),
-                         'soak_steps': max(soak_steps, lanes * group), 'affinity': affinity},
+                         'ms_per_step_one_in_flight': ms_serial / args.steps, 'ms_per_step_soak': ms_soak / max(soak_steps, lanes * group * chain),
+                         'soak_steps': max(soak_steps, lanes * group * chain), 'affinity': affinity},
             'clocks': clocks, 'e2e': e2e,
             'gpu_launches': launches_per_step * args.steps, 'gpu_launches_per_step': launches_per_step,
             'roofline': roofline, 'cpu_baseline': cpu,
@@ -789,7 +802,9 @@ def main():
     ap.add_argument('--no-graph', action='store_true', help='eager launches instead of CUDA-graph replay')
     ap.add_argument('--run-graph', action='store_true', help='time ONE graph of the whole K-step run (StepRing.capture_run) instead of K/group graph launches '
                     '(measured slower: 45.0 vs 40.8 us/step at K = 200, profiles/sweep_r02p.log)')
-    ap.add_argument('--no-affinity', action='store_true', help='do not pin the rank to its own core set')
+    ap.add_argument('--affinity', action='store_true', help='pin the rank to its own share of the cores (off by default: measured on 8 ranks, the launches '
+                    'of a region take 188 us from a 4-core share and 113 us unpinned, profiles/ring_probe_r02x_n8*.log)')
+    ap.add_argument('--no-affinity', action='store_true', help='(default) do not pin the rank to a core set')
     ap.add_argument('--clock-period-ms', type=float, default=2.0, help='NVML sampling period of the in-run clock record')
     ap.add_argument('--no-e2e', action='store_true', help='skip the host-buffer legs (knob sweeps)')
     ap.add_argument('--quick', action='store_true', help='headline + roofline + dense e2e only (no variants / configs / other e2e contracts)')

@@ -44,6 +44,23 @@ def _enqueue_group(pb, slots, branch, side, kw):
         main.wait_stream(st)
 
 
+def _enqueue_chain(pb, groups, branch, side, kw):
+    """Consecutive groups WITHOUT a barrier between them: branch k runs slot k of every group one after the other (slot 0
+    on the current stream); the branches are forked from / joined to the current stream once."""
+    dev = groups[0][0][2].device
+    main = torch.cuda.current_stream(dev)
+    width = len(groups[0])
+    for k in range(1, width):
+        branch[k - 1].wait_stream(main)
+        with torch.cuda.stream(branch[k - 1]):
+            for g in groups:
+                _enqueue_step(pb, *g[k], side[k], kw)
+    for g in groups:
+        _enqueue_step(pb, *g[0], side[0], kw)
+    for st in branch[:width - 1]:
+        main.wait_stream(st)
+
+
 def capture_steps(pb, slots, top_k=200, conf_threshold=0.01, nms_threshold=0.45, two_streams=True, nms_all_threshold=None):
     """Captures the steps of all ``slots`` = [(gt, head, y_true, dets)] into ONE CUDA graph, every slot on its own
     branch (and within a slot the train and the predict side on parallel branches when ``two_streams``): one host
@@ -87,7 +104,7 @@ class StepRing:
     """
 
     def __init__(self, pb, slots, lanes=2, group=4, top_k=200, conf_threshold=0.01, nms_threshold=0.45, use_graph=True,
-                 nms_all_threshold=None, chain=1):
+                 nms_all_threshold=None, chain=1, chain_barrier=True):
         assert len(slots) >= 1 and lanes >= 1 and group >= 1 and chain >= 1 and len(slots) % (lanes * group * chain) == 0, \
             'len(slots) must be a multiple of lanes * group * chain'
         self.pb, self.slots, self.lanes, self.group, self.chain = pb, slots, lanes, group, chain
@@ -107,7 +124,7 @@ class StepRing:
         self._run_graphs = {}  # (steps, first slot) -> graph of a whole run (capture_run)
         # chain > 1: ``chain`` consecutive groups one after the other in ONE graph — the same ``group`` batches in flight per
         # lane, but one host launch per group * chain batches (with 8 ranks on one host a graph launch costs ~170 us, more
-        # than the GPU needs for 4 batches)
+        # than the GPU needs for 4 batches).  ``chain_barrier=False`` drops the barrier between the groups of a chain.
         self.chain_graphs = None
         if use_graph and chain > 1:
             kw = {k: v for k, v in self._kw.items() if v is not None}
@@ -119,9 +136,13 @@ class StepRing:
             span = group * chain
             for j in range(len(slots) // span):
                 g = torch.cuda.CUDAGraph()
+                groups = [slots[j * span + c * group:j * span + (c + 1) * group] for c in range(chain)]
                 with torch.cuda.device(self.dev), torch.cuda.graph(g):
-                    for c in range(chain):
-                        _enqueue_group(pb, slots[j * span + c * group:j * span + (c + 1) * group], branch, side, kw)
+                    if chain_barrier:  # group c+1 starts when every batch of group c has finished
+                        for grp in groups:
+                            _enqueue_group(pb, grp, branch, side, kw)
+                    else:              # branch k runs batch k of every group back to back: `group` independent chains
+                        _enqueue_chain(pb, groups, branch, side, kw)
                 self.chain_graphs.append(g)
 
     def capture_run(self, steps, start=0):

@@ -844,16 +844,17 @@ def test_step_ring_batches_in_flight(use_graph, lanes, group):
             assert torch.equal(y, wy) and torch.equal(d, wd)
     if use_graph and group == 2:
         # two groups chained inside one graph (one host launch per 4 batches, 2 in flight): 11 steps = 2 chained graphs + 1 group + 1 step
-        for _, _, y, d in slots:
-            y.fill_(7.0)
-            d.fill_(7.0)
-        chained = pipeline.StepRing(pb, slots, lanes=1, group=2, chain=2, top_k=TOPK)
-        chained.fork()
-        chained.run(2 * SLOTS + 3)
-        chained.join()
-        torch.cuda.synchronize()
-        for (gt, head, y, d), (wy, wd) in zip(slots, want):
-            assert torch.equal(y, wy) and torch.equal(d, wd)
+        for chain_barrier in (True, False):  # False: no barrier between the groups of a chain (a chain of steps per branch)
+            for _, _, y, d in slots:
+                y.fill_(7.0)
+                d.fill_(7.0)
+            chained = pipeline.StepRing(pb, slots, lanes=1, group=2, chain=2, top_k=TOPK, chain_barrier=chain_barrier)
+            chained.fork()
+            chained.run(2 * SLOTS + 3)
+            chained.join()
+            torch.cuda.synchronize()
+            for (gt, head, y, d), (wy, wd) in zip(slots, want):
+                assert torch.equal(y, wy) and torch.equal(d, wd)
 
 
 # ----------------------------------------------------------------------------------------- COCO metrics (parity unpinned)
