@@ -65,15 +65,16 @@ struct StageLayout {
 // moment every consumer warp has released it (per-slot "empty" mbarrier, one arrival per consumer warp) — no CTA-wide
 // barrier sits between a slot becoming free and its refill, and a consumer warp that is done with its 32 rows moves on
 // to the next tile without waiting for the slowest warp of the CTA.
-template <int TILE, bool DENSE, int SPLIT>
-__global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 1024 : 1280) / (TILE * SPLIT)) decode_score_kernel(const DecodeArgs p) {
+// CFIX: the class count as a compile-time constant (20 = VOC, the reference's default head) or 0 = p.c at run time.
+template <int TILE, bool DENSE, int SPLIT, int CFIX>
+__global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : 1024 / (TILE * SPLIT)) decode_score_kernel(const DecodeArgs p) {
   OdkTimeline tl_(ODK_TL_EMIT, p.tl);
   using L = StageLayout<TILE, DENSE>;
   constexpr int kThreads = TILE * SPLIT;  // consumer threads
   const int kStages = p.stages;
   constexpr int kWarps = kThreads / 32;   // consumer warps; warp kWarps is the producer
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int c = p.c;
+  const int c = CFIX ? CFIX : p.c;
   const size_t clf_bytes = (size_t)TILE * c * 4;
   const size_t stage_bytes = clf_bytes + L::kTail;
   __shared__ uint64_t full_bar[L::kMaxStages];
@@ -96,22 +97,27 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
   __syncthreads();
 
   auto stage_ptr = [&](int s) { return smem_raw + (size_t)s * stage_bytes; };
+  // (image, tile) of the CTA's tiles are tracked incrementally: t advances by gridDim.x = gq * tiles_per_image + gr
+  const int tpi = p.tiles_per_image, gstep = (int)gridDim.x;
+  const int gq = gstep / tpi, gr = gstep - gq * tpi;
 
   if (warp == kWarps) {
     // =========================================== producer warp ===========================================
     const bool span_lane = !DENSE && p.use_spans && lane < ODK_MAX_SPANS;
-    auto span_word = [&](int t) -> uint32_t {
-      return (span_lane && t < total_tiles) ? __ldg(p.av.spans + (size_t)(t % p.tiles_per_image) * ODK_MAX_SPANS + lane) : 0u;
+    auto span_word = [&](int t, int tile_of_t) -> uint32_t {
+      return (span_lane && t < total_tiles) ? __ldg(p.av.spans + (size_t)tile_of_t * ODK_MAX_SPANS + lane) : 0u;
     };
     int slot = 0, fill = 0;  // `fill`: how many times the ring has wrapped (the producer waits for release number fill - 1)
-    uint32_t sp = span_word((int)blockIdx.x);
-    for (int t = (int)blockIdx.x; t < total_tiles; t += (int)gridDim.x) {
+    int b = (int)blockIdx.x / tpi, tile = (int)blockIdx.x - b * tpi;
+    uint32_t sp = span_word((int)blockIdx.x, tile);
+    for (int t = (int)blockIdx.x; t < total_tiles; t += gstep) {
       // span words of the NEXT tile are fetched before this tile's slot is waited for: no global load between a slot
       // becoming free and its refill
-      const uint32_t sp_next = span_word(t + (int)gridDim.x);
+      int tile_next = tile + gr, b_next = b + gq;
+      if (tile_next >= tpi) { tile_next -= tpi; ++b_next; }
+      const uint32_t sp_next = span_word(t + gstep, tile_next);
       if (fill > 0) odk_mbar_wait(&empty_bar[slot], (uint32_t)(fill - 1) & 1u);
-      const int b = t / p.tiles_per_image;
-      const int a0 = (t - b * p.tiles_per_image) * TILE;
+      const int a0 = tile * TILE;
       const int rows = min(TILE, p.n - a0);
       const size_t row0 = (size_t)b * p.n + a0;
       const float* src_clf = p.clfs + row0 * c;
@@ -179,6 +185,7 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
         if (lane == 0) odk_mbar_arrive(&full_bar[slot]);
       }
       sp = sp_next;
+      tile = tile_next; b = b_next;
       if (++slot == kStages) { slot = 0; ++fill; }
     }
     return;
@@ -188,13 +195,13 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
   const int row_id = tid / SPLIT, part = tid % SPLIT;  // SPLIT consecutive lanes own one anchor row
   int slot = 0;
   uint32_t phase = 0;
-  for (int t = (int)blockIdx.x; t < total_tiles; t += (int)gridDim.x) {
+  int b = (int)blockIdx.x / tpi, tile = (int)blockIdx.x - b * tpi;
+  const unsigned char* st = smem_raw;
+  const float conf_thr = p.conf_thr;
+  for (int t = (int)blockIdx.x; t < total_tiles; t += gstep) {
     odk_mbar_wait(&full_bar[slot], phase);
-    const int b = t / p.tiles_per_image;
-    const int tile = t - b * p.tiles_per_image;
     const int a0 = tile * TILE;
     const int rows = min(TILE, p.n - a0);
-    const unsigned char* st = stage_ptr(slot);
     const float* s_clf = reinterpret_cast<const float*>(st);
     const float* s_obj = reinterpret_cast<const float*>(st + clf_bytes + L::kOffObj);
     const unsigned char* s_amask = st + clf_bytes + L::kOffAMask;
@@ -209,7 +216,9 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
       float best = -INFINITY;
       cls = 0x7fffffff;
       // with spans, a row with pb_mask = 0 may hold stale shared memory: it is never scanned (conf = 0, never a candidate)
-      const bool scan = row_id < rows && (DENSE || !p.use_spans || s_amask[row_id] != 0);
+      const unsigned mk = row_id < rows ? (unsigned)s_amask[row_id] : 0u;
+      const float obj = row_id < rows ? s_obj[row_id] : 0.0f;
+      const bool scan = row_id < rows && (DENSE || !p.use_spans || mk != 0u);
       if (scan) {
         if ((c & 3) == 0) {
           // The stream is bound by the ALU pipe (compares and selects issue at half rate), so the scan is arranged to
@@ -229,11 +238,15 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
             const float m0 = fmaxf(fmaxf(v0.x, v0.y), fmaxf(v0.z, v0.w)), m1 = fmaxf(fmaxf(v1.x, v1.y), fmaxf(v1.z, v1.w));
             const float m2 = fmaxf(fmaxf(v2.x, v2.y), fmaxf(v2.z, v2.w)), m3 = fmaxf(fmaxf(v3.x, v3.y), fmaxf(v3.z, v3.w));
             const float m4 = fmaxf(fmaxf(v4.x, v4.y), fmaxf(v4.z, v4.w));
-            if (m0 >= best) { best = m0; jb = j0; }  // ">=" only against the -inf start value: a chunk of -inf still counts
-            if (m1 > best || (jb < 0 && m1 == best)) { best = m1; jb = j0 + 1; }
-            if (m2 > best || (jb < 0 && m2 == best)) { best = m2; jb = j0 + 2; }
-            if (m3 > best || (jb < 0 && m3 == best)) { best = m3; jb = j0 + 3; }
-            if (m4 > best || (jb < 0 && m4 == best)) { best = m4; jb = j0 + 4; }
+            // fmaxf ignores NaNs, so mx is the maximum of the non-NaN values (NaN only if every value is NaN, which then
+            // matches no chunk); the FIRST chunk that attains it wins, a chunk of -inf values included
+            const float mx = fmaxf(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)), m4);
+            jb = (m4 == mx) ? j0 + 4 : jb;  // selects, last chunk first: the lowest matching chunk is written last
+            jb = (m3 == mx) ? j0 + 3 : jb;
+            jb = (m2 == mx) ? j0 + 2 : jb;
+            jb = (m1 == mx) ? j0 + 1 : jb;
+            jb = (m0 == mx) ? j0 : jb;
+            best = (jb >= 0) ? mx : best;
           } else {
             for (int j = j0; j < j1; ++j) {
               const float4 v = row4[j];
@@ -242,8 +255,12 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
             }
           }
           if (jb >= 0) {
-            const float4 v = row4[jb];
-            cls = 4 * jb + (v.x == best ? 0 : (v.y == best ? 1 : (v.z == best ? 2 : 3)));
+            const float4 v = odk_lds_f4(row4 + jb);  // one 16-byte load, then selects (first element equal to the maximum)
+            int pos = 3;
+            pos = (v.z == best) ? 2 : pos;
+            pos = (v.y == best) ? 1 : pos;
+            pos = (v.x == best) ? 0 : pos;
+            cls = 4 * jb + pos;
           }
         } else {
           const int per = (c + SPLIT - 1) / SPLIT;
@@ -267,8 +284,8 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
       if (owner && scan) {
         // a row of NaNs leaves best = -inf in every part: np.argmax returns 0 there
         if (cls == 0x7fffffff) { cls = 0; best = row[0]; }
-        const float maskf = s_amask[row_id] ? 1.0f : 0.0f;
-        conf = __fmul_rn(__fmul_rn(s_obj[row_id], best), maskf);  // (objs*confs)*pb_mask, od_net.py:183-184
+        const float maskf = mk ? 1.0f : 0.0f;
+        conf = __fmul_rn(__fmul_rn(obj, best), maskf);  // (objs*confs)*pb_mask, od_net.py:183-184
       }
       if (DENSE && owner) {
         const float4* s_loc = reinterpret_cast<const float4*>(st + clf_bytes + L::kOffLoc);
@@ -293,27 +310,31 @@ __global__ void __launch_bounds__(TILE * SPLIT + 32, DENSE ? 1 : (SPLIT > 1 ? 10
       // offset back; the warp that arrives last knows the tile's total, publishes it and clears the counter — all before
       // it releases the ring slot, so the counter is clean when the slot's next tile starts.  The order of the warps
       // inside a slab varies from run to run; the NMS kernel sorts the keys, so results do not depend on it.
-      const bool is_cand = owner && (conf > p.conf_thr);
+      const bool is_cand = owner && (conf > conf_thr);
       const unsigned m = __ballot_sync(0xffffffffu, is_cand);
+      const unsigned cnt = (unsigned)__popc(m);
       unsigned old = 0;
-      if (lane == 0) old = atomicAdd(&s_ctr[slot], (unsigned)__popc(m) | (1u << 16));
+      if (lane == 0) old = odk_atoms_add(&s_ctr[slot], cnt | (1u << 16));  // plain atom.shared: no compiler-side warp aggregation
       old = __shfl_sync(0xffffffffu, old, 0);
       const unsigned base = old & 0xffffu;
-      const size_t piece = (size_t)b * p.tiles_per_image + tile;
+      // the piece index of a tile is its global tile index t = b * tiles_per_image + tile
       if ((old >> 16) == (unsigned)(kWarps - 1) && lane == 0) {
         s_ctr[slot] = 0u;
-        p.piece_count[piece] = (int)(base + __popc(m));
+        p.piece_count[t] = (int)(base + cnt);
       }
       __syncwarp();
       if (lane == 0) odk_mbar_arrive(&empty_bar[slot]);  // rows in registers, counter settled: release the ring slot
-      ODK_ASSERT((old >> 16) < (unsigned)kWarps && base + __popc(m) <= (unsigned)TILE);
+      ODK_ASSERT((old >> 16) < (unsigned)kWarps && base + cnt <= (unsigned)TILE);
       if (is_cand) {
-        ODK_ASSERT(cls >= 0 && cls < c && a < p.n);
-        p.cand_keys[piece * TILE + base + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
-        if (p.score_hist != nullptr) atomicAdd(p.score_hist + (size_t)b * ODK_HIST_BINS + odk_score_bin(conf), 1);
+        ODK_ASSERT(cls >= 0 && cls < c && a < p.n && t == b * tpi + tile);
+        p.cand_keys[(size_t)t * TILE + base + __popc(m & ((1u << lane) - 1u))] = odk_make_key2(cls, conf, a);
+        if (p.score_hist != nullptr) atomicAdd(p.score_hist + b * ODK_HIST_BINS + odk_score_bin(conf), 1);
       }
     }
-    if (++slot == kStages) { slot = 0; phase ^= 1u; }
+    tile += gr; b += gq;
+    if (tile >= tpi) { tile -= tpi; ++b; }
+    st += stage_bytes;
+    if (++slot == kStages) { slot = 0; phase ^= 1u; st = smem_raw; }
   }
 }
 
@@ -377,7 +398,7 @@ int sm_count_cached() {
   return sms;
 }
 
-template <int TILE, bool DENSE, int SPLIT>
+template <int TILE, bool DENSE, int SPLIT, int CFIX = 0>
 int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   using L = StageLayout<TILE, DENSE>;
   static const int env_stages = getenv("ODK_EMIT_STAGES") ? atoi(getenv("ODK_EMIT_STAGES")) : 0;
@@ -395,7 +416,7 @@ int launch_tile(DecodeArgs& args, cudaStream_t stream) {
   // other batches in flight.
   args.stages = (!DENSE && env_stages >= 1 && env_stages <= L::kMaxStages) ? env_stages : 3;
   const size_t smem = L::stage_bytes(args.c) * args.stages;
-  auto kern = decode_score_kernel<TILE, DENSE, SPLIT>;
+  auto kern = decode_score_kernel<TILE, DENSE, SPLIT, CFIX>;
   ODK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   ODK_MAX_CARVEOUT_ONCE(kern);
   args.tiles_per_image = (args.n + TILE - 1) / TILE;
@@ -447,7 +468,9 @@ int odk_launch_decode_score(const odk_anchors* a, int batch, const float* objs, 
   const int c = a->num_classes;
   ODK_REQUIRE(c <= 512, ODK_ERR_UNSUPPORTED, "num_classes=%d > 512 not supported by decode_score", c);
   switch (odk_piece_size(c)) {
-    case 256: return dense ? launch_tile<256, true, 1>(args, stream) : launch_tile<256, false, 1>(args, stream);
+    case 256:
+      if (c == 20) return dense ? launch_tile<256, true, 1, 20>(args, stream) : launch_tile<256, false, 1, 20>(args, stream);
+      return dense ? launch_tile<256, true, 1>(args, stream) : launch_tile<256, false, 1>(args, stream);
     case 128: return dense ? launch_tile<128, true, 1>(args, stream) : launch_tile<128, false, 1>(args, stream);
     case 64: return dense ? launch_tile<64, true, 4>(args, stream) : launch_tile<64, false, 4>(args, stream);
     default: return dense ? launch_tile<32, true, 8>(args, stream) : launch_tile<32, false, 8>(args, stream);

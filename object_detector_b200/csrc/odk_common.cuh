@@ -279,6 +279,20 @@ __device__ __forceinline__ unsigned odk_lane() { return threadIdx.x & 31u; }
 __device__ __forceinline__ uint32_t odk_smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
+// one 16-byte shared-memory load (the compiler otherwise splits a dynamically indexed float4 read whose components
+// feed a select chain into predicated scalar loads: two dependent shared-memory round trips instead of one)
+__device__ __forceinline__ float4 odk_lds_f4(const float4* p) {
+  float4 v;
+  asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(odk_smem_u32(p)));
+  return v;
+}
+// atomicAdd on shared memory exactly as written (the compiler wraps a predicated atomicAdd in its own warp aggregation:
+// a vote, a leader election, a shuffle and a multiply-add per call)
+__device__ __forceinline__ unsigned odk_atoms_add(unsigned* p, unsigned v) {
+  unsigned old;
+  asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(odk_smem_u32(p)), "r"(v) : "memory");
+  return old;
+}
 __device__ __forceinline__ void odk_mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(odk_smem_u32(bar)), "r"(count));
 }
