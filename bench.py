@@ -429,7 +429,8 @@ def run_cuda(args):
     achieved = alg_bytes[dom] / (dms / dcnt * 1e-3) / 1e9
     roofline = {'bound': 'hbm', 'kernel': dom, 'achieved': achieved, 'peak': peak, 'peak_source': peak_src, 'unit': 'GB/s',
                 'frac': achieved / peak, 'traffic': load_traffic(dom), 'algorithmic_bytes_per_launch': alg_bytes[dom],
-                'timing': 'CUDA events around every launch of an eager pass over the same K steps (includes ~3 us of launch gap per kernel)',
+                'timing': 'CUDA events around every launch of an eager pass over the same K steps; with the library\'s profiling switch on, odk_assign_encode runs its two '
+                          'chains one after the other, so every kernel is timed alone (includes ~3 us of launch gap per kernel)',
                 'kernels': kernels}
     for k, nbytes in alg_bytes.items():
         if k in prof:

@@ -20,7 +20,9 @@
  *        created on first use, never destroyed) and join them back with events before returning
  *        to the caller's stream order; the fork/join is capturable into a CUDA graph.  Work is
  *        therefore ordered with respect to `stream`, but not every kernel runs ON `stream`;
- *      * odk_profile_enable() switches on per-host-thread CUDA-event timing of every launch;
+ *      * odk_profile_enable() switches on per-host-thread CUDA-event timing of every launch; while it is
+ *        on, odk_assign_encode runs its two chains one after the other on `stream` (no fork), so that
+ *        every event pair brackets one kernel running alone;
  *      * odk_timeline_set() installs a PROCESS-WIDE device pointer (one per device context) that
  *        instrumented kernels write %globaltimer stamps to — a diagnostic for overlap studies,
  *        never set on the product path;

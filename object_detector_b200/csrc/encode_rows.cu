@@ -332,7 +332,9 @@ extern "C" int odk_assign_encode(const odk_anchors* a, int batch, const float* g
   if (int rc = side_lane(&lane)) return rc;
   static const bool single_stream = getenv("ODK_SINGLE_STREAM") != nullptr;  // debugging aid: no fork/join
   SideLane same = {stream, lane->fork, lane->join, true};
-  if (single_stream) lane = &same;
+  // while per-launch event timing is on, the two chains run one after the other: a kernel's event pair then brackets that
+  // kernel alone (with the fork, the rows kernel is timed while the greedy walk of the same call runs beside it)
+  if (single_stream || odk_profile_on()) lane = &same;
 
   // fork at entry: the side stream builds the ignore mask (scattered per GT) and streams out the rows (HBM-bound) ...
   ODK_CUDA(cudaEventRecord(lane->fork, stream));

@@ -47,6 +47,8 @@ OdkProfileScope::~OdkProfileScope() {
   if (slot_ >= 0) cudaEventRecord(g_prof[slot_].stop, stream_);
 }
 
+bool odk_profile_on() { return g_prof_on; }
+
 extern "C" int odk_profile_enable(int on) {
   g_prof_on = on != 0;
   return ODK_OK;

@@ -84,6 +84,7 @@ int odk_set_error(int code, const char* fmt, ...);
 
 __host__ __device__ static inline size_t odk_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 // Optional per-launch CUDA-event timing (odk_profile_enable / odk_profile_read); a no-op unless enabled.
+bool odk_profile_on();  // this host thread's profiling switch (odk_profile_enable)
 struct OdkProfileScope {
   OdkProfileScope(const char* name, cudaStream_t stream);
   ~OdkProfileScope();
